@@ -1,0 +1,167 @@
+/*
+ * orb_oracle.h -- CPU ORACLE for the ORB front-end hot path.
+ *
+ * TEST INFRASTRUCTURE ONLY.  Nothing in the product library (liborbx.so, the
+ * C++ shim in include/orbx/, the python package) may link, import or call
+ * anything declared here; only tests/, __graft_entry__.smoke() and bench.py's
+ * cpu_baseline / --impl reference legs do.
+ *
+ * Parity status: the reference ships NO tests or golden vectors for this path
+ * and cannot be compiled in this image (needs OpenCV-CUDA, Eigen, Pangolin ...;
+ * SURVEY.md F2/F3), so the oracle is pinned against Python cv2 4.13.0 for every
+ * OpenCV primitive it restates (resize, copyMakeBorder, GaussianBlur, FAST,
+ * fastAtan2, ORB descriptor sampling) -- tests/test_oracle_cv2.py and the
+ * committed fixtures in tests/golden/.  DistributeOctTree / matcher logic
+ * follows the cited reference lines.  "parity unpinned by the reference".
+ *
+ * All file:line citations are into /root/reference (geoeo/ORB_SLAM3_V1.0).
+ */
+#ifndef ORB_ORACLE_H
+#define ORB_ORACLE_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* cv::KeyPoint memory layout (28 bytes) -- target ABI, SURVEY 8(a) a16 */
+typedef struct {
+    float x, y, size, angle, response;
+    int32_t octave, class_id;
+} orc_keypoint;
+
+/* ---- OpenCV primitive restatements ---- */
+void orc_resize_linear_u8(const uint8_t* src, int sw, int sh, int sstride,
+                          uint8_t* dst, int dw, int dh, int dstride);
+void orc_border_reflect101(uint8_t* buf, int w, int h, int stride, int border);
+void orc_gaussian7_s2_u8(const uint8_t* src, int w, int h, int sstride,
+                         uint8_t* dst, int dstride);
+/* cv::FAST(img, kps, th, nonmax=true, TYPE_9_16) on a w x h sub-image.
+ * Returns the number of keypoints; (x,y,score) in raster order. */
+int orc_fast9_16(const uint8_t* img, int w, int h, int stride, int threshold,
+                 int* xs, int* ys, int* scores, int max_out);
+float orc_fast_atan2(float y, float x);
+
+/* ---- extractor (upstream ORBextractor semantics) ---- */
+typedef struct orc_extractor orc_extractor;
+orc_extractor* orc_extractor_create(int nfeatures, float scaleFactor, int nlevels,
+                                    int iniThFAST, int minThFAST);
+void orc_extractor_destroy(orc_extractor*);
+/* tables: each array has nlevels entries; umax has 16 */
+void orc_extractor_tables(const orc_extractor*, float* scale, float* inv_scale,
+                          float* sigma2, float* inv_sigma2, int* feat_per_level,
+                          int* umax);
+/* operator(): returns number of keypoints (or -1 on empty image); *mono_index
+ * receives the return value of the reference operator(). kps/desc may be NULL
+ * to query the count. lapping = {x0,x1}. */
+int orc_extract(orc_extractor*, const uint8_t* image, int width, int height,
+                int stride, const int* lapping, orc_keypoint* kps, uint8_t* desc,
+                int max_kps, int* mono_index);
+/* state left by the last orc_extract */
+int orc_level_size(const orc_extractor*, int level, int* w, int* h);
+/* copies the bordered (w+38)x(h+38) level buffer, densely packed */
+void orc_level_bordered(const orc_extractor*, int level, uint8_t* out);
+/* FAST candidates handed to DistributeOctTree at `level` (coords relative to
+ * minBorder); returns count */
+int orc_level_candidates(const orc_extractor*, int level, int* xs, int* ys,
+                         int* resp, int max_out);
+/* per-level keypoints after the quadtree (level coords, incl. border offset
+ * removed: x,y are ROI coordinates), angle filled */
+int orc_level_keypoints(const orc_extractor*, int level, orc_keypoint* out, int max_out);
+
+/* DistributeOctTree + best-per-node (src/ORBextractor.cc:226-431, 514-533).
+ * Inputs are candidate coordinates relative to (minX,minY). Writes the index
+ * (into the input arrays) of each selected keypoint, in list order. */
+int orc_distribute_octtree(int n, const int* xs, const int* ys, const int* resp,
+                           int minX, int maxX, int minY, int maxY, int N,
+                           int* out_idx, int max_out);
+
+/* IC_Angle on a bordered level image: img points at ROI (0,0) */
+float orc_ic_angle(const uint8_t* roi, int stride, int x, int y);
+/* rBRIEF on a blurred image (ROI origin), keypoint at integer (x,y), angle deg */
+void orc_orb_descriptor(const uint8_t* blurred_roi, int stride, int x, int y,
+                        float angle_deg, uint8_t* desc32);
+
+/* ---- matcher ---- */
+int orc_descriptor_distance(const uint8_t* a, const uint8_t* b); /* ORBmatcher.cc:1375-1391 */
+void orc_hamming_pairs(const uint8_t* a, const uint8_t* b, int n, int* out);
+
+/* ORBmatcher::ComputeThreeMaxima (ORBmatcher.cc:1328-1370) on bin counts */
+void orc_three_maxima(const int* counts, int L, int* ind1, int* ind2, int* ind3);
+
+/* Frame grid (Frame.cc:157-176, 404-480) flattened */
+typedef struct {
+    int n;                    /* frame keypoints */
+    const float* kx; const float* ky; const int* koct;   /* mvKeysUn */
+    const uint8_t* desc;      /* n x 32 */
+    const float* uright;      /* mvuRight, may be NULL (treated as -1) */
+    float minx, miny;         /* mnMinX, mnMinY */
+    float gw_inv, gh_inv;     /* mfGridElementWidthInv / HeightInv */
+    int gcols, grows;         /* mFrameGridCols / Rows */
+    const float* scale;       /* mvScaleFactors */
+    int nlevels;
+} orc_frame_view;
+
+/* SearchByProjection(Frame, MapPoints, th, ...) ORBmatcher.cc:31-123.
+ * Map points are flattened: in-view flag, projected x,y, predicted level,
+ * view cos, descriptor. `claimed[i]!=0` marks frame keypoints that already
+ * hold a MapPoint with observations. match_mp[i] receives the map-point index
+ * assigned to frame keypoint i (or -1). Returns nmatches. */
+int orc_search_by_projection(const orc_frame_view* F, int nmp, const uint8_t* mp_inview,
+                             const float* mp_x, const float* mp_y, const int* mp_level,
+                             const float* mp_viewcos, const float* mp_depth,
+                             const uint8_t* mp_desc, const uint8_t* claimed_in,
+                             float th, int bFarPoints, float thFarPoints, float nnRatio,
+                             int* match_mp);
+
+/* SearchByProjection(Frame, KeyFrame, ...) ORBmatcher.cc:1202-1326 with the
+ * projection already done by the host shim: per KF map point i (valid flag,
+ * u,v, predicted level, KF keypoint angle, descriptor). */
+int orc_search_by_projection_kf(const orc_frame_view* F, const float* fangle, int nmp,
+                                const uint8_t* mp_valid, const float* mp_u, const float* mp_v,
+                                const int* mp_level, const float* mp_angle,
+                                const uint8_t* mp_desc, const uint8_t* occupied_in,
+                                float th, int checkOrientation, int* match_mp);
+
+/* SearchForTriangulation ORBmatcher.cc:441-676 flattened: two keyframes,
+ * feature vectors as sorted (node id, CSR offsets, indices). F12 = fundamental
+ * matrix as computed by Pinhole::epipolarConstrain (Pinhole.cpp:104-131),
+ * row-major 3x3; ep = epipole in image 2. */
+typedef struct {
+    int n;
+    const float* kx; const float* ky; const int* koct; const float* kangle;
+    const uint8_t* desc;
+    const uint8_t* has_mp;       /* GetMapPoint(idx)!=null */
+    const float* uright;         /* may be NULL */
+    int nnodes; const int* node_id; const int* node_off; const int* node_idx;
+} orc_kf_view;
+int orc_search_for_triangulation(const orc_kf_view* k1, const orc_kf_view* k2,
+                                 const float* F12, float epx, float epy,
+                                 const float* scale2 /* pKF2->mvScaleFactors */,
+                                 int bOnlyStereo, int bCoarse, int checkOrientation,
+                                 int* pairs /* 2*n1 */, int* npairs);
+
+/* Frame::ComputeStereoMatches (upstream v1.0). Pyramids are
+ * given as per-level ROI pointers + strides (bordered buffers behind them). */
+typedef struct {
+    int n; const float* kx; const float* ky; const int* koct; const uint8_t* desc;
+    int nlevels; const uint8_t* const* lvl; const int* lvl_stride;
+    const int* lvl_w; const int* lvl_h;
+} orc_stereo_side;
+void orc_stereo_matches(const orc_stereo_side* L, const orc_stereo_side* R,
+                        const float* scale, const float* inv_scale,
+                        float bf, float b, float* uRight, float* depth);
+
+/* brute-force kNN k=2: ties -> lowest index. out arrays have nq entries. */
+void orc_knn2(const uint8_t* q, int nq, const uint8_t* db, int ndb,
+              int* d1, int* i1, int* d2, int* i2, int nthreads);
+
+/* timing helper for bench.py: runs `iters` extractions on `nthreads` threads
+ * (independent frames), returns seconds of wall time. */
+double orc_bench_extract(int nfeatures, float scaleFactor, int nlevels, int iniTh, int minTh,
+                         const uint8_t* images, int nimages, int width, int height,
+                         int iters_per_thread, int nthreads, long* total_kps);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

