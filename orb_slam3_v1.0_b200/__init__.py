@@ -4,3 +4,4 @@ Product code = csrc/ (hand-written sm_100a CUDA behind the C ABI of include/orbx
 thin ctypes binding (`orbx`) used by tests and bench.py.  There is no CPU fallback: every
 entry point raises if liborbx.so or a CUDA device is missing."""
 from . import synth  # noqa: F401
+from . import orbx  # noqa: F401

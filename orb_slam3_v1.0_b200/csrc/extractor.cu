@@ -1,0 +1,1326 @@
+/*
+ * extractor.cu -- batched ORB extractor for B200 (sm_100a), behind include/orbx.h.
+ *
+ * Target semantics: upstream ORB-SLAM3 v1.0 ORBextractor, i.e. what
+ * the reference's src/ORBextractor.cc implements minus the fork's Jetson shortcuts; the
+ * citable parts are src/ORBextractor.cc:92-143 (tables), :151-431,:514-533 (quadtree),
+ * src/cuda/Orb_gpu.cu:52-350 (pattern + descriptor), src/cuda/Angle_gpu.cu:26-80 (moments).
+ * NOT a port: every kernel is batched over frames, writes deterministic (reference-order)
+ * outputs without atomics-ordered compaction, and never synchronises with the host.
+ *
+ * Stages (one launch each unless noted), all on the handle's stream:
+ *   0 pyramid   k_level0 (+border) and k_resize per level (+border, recomputed not re-read)
+ *   1 fast      k_fast_cells: one CTA per 35-px cell, smem tile, ini->min retry, ordered output
+ *   2 octree    k_octree: one CTA per (frame, level), exact DistributeOctTree emulation
+ *   3 order     k_order: level offsets + vLappingArea mono/stereo placement
+ *   4 blur      k_blur7: integer 7x7 sigma-2 Gaussian
+ *   5 describe  k_orient_describe: one warp per keypoint, IC angle + rBRIEF
+ */
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <vector>
+
+#include "orbx_internal.h"
+#include "stdsort_emul.h"
+
+/* ------------------------------------------------------------------ errors */
+static thread_local char g_err[512] = "";
+void orbx_set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+extern "C" const char* orbx_last_error(void) { return g_err; }
+extern "C" int orbx_version(void) { return 100; }
+
+/* ------------------------------------------------------------------ device-side level table */
+struct LevelDev {
+    int w, h, pitch, rows;
+    unsigned long long frame_bytes;
+    uint8_t* base;          /* bordered pyramid, frame-major */
+    int bpitch;
+    unsigned long long bframe_bytes;
+    uint8_t* blur;          /* blurred level, w x h */
+    const short4* xtab;     /* resize: per dx {sx, a0, a1, 0} */
+    const short4* ytab;     /* resize: per dy {sy, b0, b1, 0} */
+    int cell_begin, cell_end;
+    int N, nIni;
+    float hX;
+    int cand_off, cand_cap; /* into the per-frame candidate arrays */
+    int sel_off, sel_cap;   /* into the per-frame selected-keypoint arrays */
+    float scale;
+    float patch_size;
+};
+
+struct Cell {
+    short level, x0, y0, cw, ch, offx, offy, pad;
+    int slot_off;           /* into the per-frame candidate-slot array */
+    int idx_in_level;
+};
+
+struct Tables {
+    int nlevels;
+    LevelDev lv[ORBX_MAX_LEVELS];
+};
+
+__device__ __forceinline__ int reflect101(int p, int n) {
+    /* |p| excursions are < n here (border 19 < smallest supported level) but loop anyway */
+    while (p < 0 || p >= n) p = (p < 0) ? -p : 2 * (n - 1) - p;
+    return p;
+}
+
+__device__ __forceinline__ uint8_t* lv_ptr(const LevelDev& L, int f, int x, int y) {
+    return L.base + (size_t)f * L.frame_bytes + (size_t)(y + ORBX_EDGE) * L.pitch + ORBX_XOFF + x;
+}
+
+/* ================================================================== stage 0: pyramid */
+/* level 0 = copyMakeBorder(image, 19, BORDER_REFLECT_101).
+ * One thread per 16 output bytes of the padded row. */
+__global__ void __launch_bounds__(256) k_level0(const uint8_t* __restrict__ src, size_t frame_stride,
+                                                int row_stride, LevelDev L, int batch, int vec_ok) {
+    const int chunks = L.pitch / 16;
+    const long long total = (long long)batch * L.rows * chunks;
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total;
+         t += (long long)gridDim.x * blockDim.x) {
+        const int c = (int)(t % chunks);
+        const int r = (int)((t / chunks) % L.rows);
+        const int f = (int)(t / ((long long)chunks * L.rows));
+        const int x0 = c * 16 - ORBX_XOFF;
+        if (x0 + 16 <= -ORBX_EDGE || x0 >= L.w + ORBX_EDGE) continue;
+        const int sy = reflect101(r - ORBX_EDGE, L.h);
+        const uint8_t* srow = src + (size_t)f * frame_stride + (size_t)sy * row_stride;
+        uint8_t* drow = L.base + (size_t)f * L.frame_bytes + (size_t)r * L.pitch + c * 16;
+        if (vec_ok && x0 >= 0 && x0 + 16 <= L.w) {
+            *reinterpret_cast<uint4*>(drow) = __ldg(reinterpret_cast<const uint4*>(srow + x0));
+        } else {
+            uint32_t wv[4] = {0, 0, 0, 0};
+#pragma unroll
+            for (int k = 0; k < 16; ++k) {
+                const int x = x0 + k;
+                uint32_t v = 0;
+                if (x >= -ORBX_EDGE && x < L.w + ORBX_EDGE) v = __ldg(srow + reflect101(x, L.w));
+                wv[k >> 2] |= v << (8 * (k & 3));
+            }
+            *reinterpret_cast<uint4*>(drow) = make_uint4(wv[0], wv[1], wv[2], wv[3]);
+        }
+    }
+}
+
+/* level l = cv::resize(level l-1, INTER_LINEAR) (11-bit fixed point) + border.
+ * Border pixels are recomputed from the reflected destination coordinate (same value as
+ * copyMakeBorder would copy) so the kernel is a pure map over the padded destination.
+ * One thread per 4 output pixels. */
+__device__ __forceinline__ uint32_t resize_px(const uint8_t* __restrict__ s0, const uint8_t* __restrict__ s1,
+                                              short4 xt, int b0, int b1) {
+    /* source rows are bordered, so column sx+1 always exists (weight 0 when clamped) */
+    const int r0 = s0[xt.x] * xt.y + s0[xt.x + 1] * xt.z;
+    const int r1 = s1[xt.x] * xt.y + s1[xt.x + 1] * xt.z;
+    return (uint32_t)((((b0 * (r0 >> 4)) >> 16) + ((b1 * (r1 >> 4)) >> 16) + 2) >> 2);
+}
+
+__global__ void __launch_bounds__(256) k_resize(LevelDev S, LevelDev D, int batch) {
+    const int chunks = D.pitch / 4;
+    const long long total = (long long)batch * D.rows * chunks;
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total;
+         t += (long long)gridDim.x * blockDim.x) {
+        const int c = (int)(t % chunks);
+        const int r = (int)((t / chunks) % D.rows);
+        const int f = (int)(t / ((long long)chunks * D.rows));
+        const int x0 = c * 4 - ORBX_XOFF;
+        if (x0 + 4 <= -ORBX_EDGE || x0 >= D.w + ORBX_EDGE) continue;
+        const int dy = reflect101(r - ORBX_EDGE, D.h);
+        const short4 yt = __ldg(D.ytab + dy);
+        const uint8_t* s0 = lv_ptr(S, f, 0, yt.x);
+        const uint8_t* s1 = s0 + S.pitch;       /* row sy+1 exists in the bordered source */
+        uint32_t out = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int x = x0 + k;
+            if (x >= -ORBX_EDGE && x < D.w + ORBX_EDGE) {
+                const short4 xt = __ldg(D.xtab + reflect101(x, D.w));
+                out |= resize_px(s0, s1, xt, yt.y, yt.z) << (8 * k);
+            }
+        }
+        *reinterpret_cast<uint32_t*>(D.base + (size_t)f * D.frame_bytes + (size_t)r * D.pitch + c * 4) = out;
+    }
+}
+
+/* ================================================================== stage 1: FAST per cell */
+#define FAST_TP 80            /* smem tile pitch; cells are at most 69+6 wide (checked on host) */
+#define FAST_TH 80
+#define FAST_THREADS 128
+
+__device__ __forceinline__ bool has9(uint32_t m) {
+    m |= m << 16;
+    uint32_t a = m & (m >> 1);
+    a &= a >> 2;
+    a &= a >> 4;         /* bit i: m[i..i+7] all set */
+    a &= m >> 8;         /* ... and m[i+8] */
+    return (a & 0xFFFFu) != 0;
+}
+
+/* A = max over 9-arcs of min(d) for the bright test and of min(-d) for the dark test
+ * (cornerScore, reference src/cuda/Fast_gpu.cu:193-216, equals A-1). */
+__device__ __forceinline__ int arc_strength(const int* d) {
+    int best = -512;
+#pragma unroll
+    for (int sgn = 0; sgn < 2; ++sgn) {
+        int e[16], m2[16], m4[16], m8[16];
+#pragma unroll
+        for (int k = 0; k < 16; ++k) e[k] = sgn ? -d[k] : d[k];
+#pragma unroll
+        for (int k = 0; k < 16; ++k) m2[k] = min(e[k], e[(k + 1) & 15]);
+#pragma unroll
+        for (int k = 0; k < 16; ++k) m4[k] = min(m2[k], m2[(k + 2) & 15]);
+#pragma unroll
+        for (int k = 0; k < 16; ++k) m8[k] = min(m4[k], m4[(k + 4) & 15]);
+#pragma unroll
+        for (int k = 0; k < 16; ++k) best = max(best, min(m8[k], e[(k + 8) & 15]));
+    }
+    return best;
+}
+
+__global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(Tables T, const Cell* __restrict__ cells,
+                                                              int ncells, int ini_th, int min_th,
+                                                              uint32_t* __restrict__ slots, size_t slots_per_frame,
+                                                              int* __restrict__ cell_count) {
+    __shared__ uint8_t tile[FAST_TH * FAST_TP];
+    __shared__ uint8_t score[FAST_TH * FAST_TP];
+    __shared__ int s_warp[FAST_THREADS / 32];
+    __shared__ int s_base;
+
+    const int f = blockIdx.y;
+    const Cell c = cells[blockIdx.x];
+    const LevelDev& L = T.lv[c.level];
+    const int cw = c.cw, ch = c.ch;
+    const int tid = threadIdx.x;
+
+    /* load the cell sub-image; rows are contiguous in global memory */
+    const uint8_t* src = lv_ptr(L, f, c.x0, c.y0);
+    for (int i = tid; i < ch * cw; i += FAST_THREADS) {
+        const int y = i / cw, x = i - y * cw;
+        tile[y * FAST_TP + x] = __ldg(src + (size_t)y * L.pitch + x);
+    }
+    __syncthreads();
+
+    const int dw = cw - 6, dh = ch - 6;          /* detection area (3-px margin) */
+    const int npix = (dw > 0 && dh > 0) ? dw * dh : 0;
+    /* pass 1: score map at min_th (0 = not a corner); border of the score tile = 0 */
+    for (int i = tid; i < ch * cw; i += FAST_THREADS) score[(i / cw) * FAST_TP + (i % cw)] = 0;
+    __syncthreads();
+    for (int i = tid; i < npix; i += FAST_THREADS) {
+        const int y = i / dw + 3, x = i - (y - 3) * dw + 3;
+        const uint8_t* p = tile + y * FAST_TP + x;
+        const int v = p[0];
+        int d[16];
+        d[0] = p[3 * FAST_TP];          d[1] = p[3 * FAST_TP + 1];   d[2] = p[2 * FAST_TP + 2];  d[3] = p[FAST_TP + 3];
+        d[4] = p[3];                    d[5] = p[-FAST_TP + 3];      d[6] = p[-2 * FAST_TP + 2]; d[7] = p[-3 * FAST_TP + 1];
+        d[8] = p[-3 * FAST_TP];         d[9] = p[-3 * FAST_TP - 1];  d[10] = p[-2 * FAST_TP - 2]; d[11] = p[-FAST_TP - 3];
+        d[12] = p[-3];                  d[13] = p[FAST_TP - 3];      d[14] = p[2 * FAST_TP - 2]; d[15] = p[3 * FAST_TP - 1];
+        uint32_t mb = 0, md = 0;
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+            d[k] -= v;
+            mb |= (d[k] > min_th ? 1u : 0u) << k;
+            md |= (d[k] < -min_th ? 1u : 0u) << k;
+        }
+        if (has9(mb) || has9(md)) {
+            const int A = arc_strength(d);           /* A > min_th here */
+            score[y * FAST_TP + x] = (uint8_t)(A - 1);
+        }
+    }
+    __syncthreads();
+
+    /* pass 2: strict local maxima of the min_th score map.  A corner at threshold t has
+     * score >= t, so NMS at ini_th = {local maxima with score >= ini_th}: neighbours that are
+     * corners only at min_th have smaller scores and cannot suppress it either way. */
+    int cnt_ini = 0;
+    for (int base = 0; base < npix; base += FAST_THREADS) {
+        const int i = base + tid;
+        int keep = 0;
+        if (i < npix) {
+            const int y = i / dw + 3, x = i - (y - 3) * dw + 3;
+            const uint8_t* s = score + y * FAST_TP + x;
+            const int v = s[0];
+            /* neighbours outside the detection area read 0 from the zeroed margin */
+            if (v > 0 && v > s[-1] && v > s[1] && v > s[-FAST_TP - 1] && v > s[-FAST_TP] && v > s[-FAST_TP + 1] &&
+                v > s[FAST_TP - 1] && v > s[FAST_TP] && v > s[FAST_TP + 1])
+                keep = (v >= ini_th) ? 2 : 1;
+            if (keep) tile[y * FAST_TP + x] = (uint8_t)keep;   /* reuse tile as the flag map */
+            else tile[y * FAST_TP + x] = 0;
+        }
+        cnt_ini += (keep == 2);
+    }
+    const int any_ini = __syncthreads_or(cnt_ini);
+    const int need = any_ini ? 2 : 1;            /* per-cell retry with minThFAST */
+
+    /* pass 3: ordered (raster) compaction */
+    uint32_t* out = slots + (size_t)f * slots_per_frame + c.slot_off;
+    if (tid == 0) s_base = 0;
+    __syncthreads();
+    for (int base = 0; base < npix; base += FAST_THREADS) {
+        const int i = base + tid;
+        int keep = 0, x = 0, y = 0;
+        if (i < npix) {
+            y = i / dw + 3; x = i - (y - 3) * dw + 3;
+            keep = tile[y * FAST_TP + x] >= need;
+        }
+        const unsigned bal = __ballot_sync(0xffffffffu, keep);
+        const int lane = tid & 31, wid = tid >> 5;
+        if (lane == 0) s_warp[wid] = __popc(bal);
+        __syncthreads();
+        int off = s_base;
+        for (int w = 0; w < wid; ++w) off += s_warp[w];
+        if (keep) {
+            off += __popc(bal & ((1u << lane) - 1));
+            out[off] = (uint32_t)(x + c.offx) | ((uint32_t)(y + c.offy) << 12) | ((uint32_t)score[y * FAST_TP + x] << 24);
+        }
+        __syncthreads();
+        if (tid == 0) {
+            int tot = 0;
+            for (int w = 0; w < FAST_THREADS / 32; ++w) tot += s_warp[w];
+            s_base += tot;
+        }
+        __syncthreads();
+    }
+    if (tid == 0) cell_count[(size_t)f * ncells + blockIdx.x] = s_base;
+}
+
+/* ================================================================== stage 2: quadtree */
+#define OCT_THREADS 256
+
+/* exclusive scan of a[0..n) in shared memory, in place; returns the total. All threads call. */
+__device__ int block_excl_scan(int* a, int n, int* s_tmp /* [OCT_THREADS/32 + 1] */) {
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    int carry = 0;
+    for (int base = 0; base < n; base += OCT_THREADS) {
+        const int i = base + tid;
+        const int v = (i < n) ? a[i] : 0;
+        int inc = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        if (lane == 31) s_tmp[wid] = inc;
+        __syncthreads();
+        int woff = 0, tot = 0;
+        for (int w = 0; w < OCT_THREADS / 32; ++w) {
+            const int t = s_tmp[w];
+            if (w < wid) woff += t;
+            tot += t;
+        }
+        if (i < n) a[i] = carry + woff + inc - v;
+        carry += tot;
+        __syncthreads();
+    }
+    return carry;
+}
+
+struct OctE { int size, ulx, pos; };
+struct OctLess {
+    /* compareNodes, reference src/ORBextractor.cc:209-224 */
+    __device__ bool operator()(const OctE& a, const OctE& b) const {
+        if (a.size < b.size) return true;
+        else if (a.size > b.size) return false;
+        else return a.ulx < b.ulx;
+    }
+};
+
+struct OctSmem {
+    /* carved from dynamic shared memory, capacity MAXN nodes */
+    short* x0[2]; short* y0[2]; short* x1[2]; short* y1[2];
+    int* cnt[2];
+    int* ccnt;       /* [4*MAXN] child counts, then child new positions */
+    int* a;          /* [MAXN] scan scratch: children segments */
+    int* b;          /* [MAXN] scan scratch: stay positions */
+    int* c;          /* [MAXN] scan scratch: E entries */
+    int* em;         /* [MAXN] processing index of a node in the final phase, or -1 */
+    OctE* E[2];      /* [MAXN] */
+    unsigned long long* best;   /* [MAXN] */
+};
+
+__device__ __forceinline__ int quadrant_of(int px, int py, int x0, int y0, int x1, int y1) {
+    /* DivideNode, reference src/ORBextractor.cc:151-196 */
+    const int halfX = (int)ceilf((float)(x1 - x0) / 2.0f);
+    const int halfY = (int)ceilf((float)(y1 - y0) / 2.0f);
+    const int left = px < x0 + halfX, top = py < y0 + halfY;
+    return left ? (top ? 0 : 2) : (top ? 1 : 3);
+}
+
+__device__ __forceinline__ void child_bounds(int q, int x0, int y0, int x1, int y1, short& cx0, short& cy0,
+                                             short& cx1, short& cy1) {
+    const int halfX = (int)ceilf((float)(x1 - x0) / 2.0f);
+    const int halfY = (int)ceilf((float)(y1 - y0) / 2.0f);
+    cx0 = (short)((q & 1) ? x0 + halfX : x0);
+    cx1 = (short)((q & 1) ? x1 : x0 + halfX);
+    cy0 = (short)((q & 2) ? y0 + halfY : y0);
+    cy1 = (short)((q & 2) ? y1 : y0 + halfY);
+}
+
+__global__ void __launch_bounds__(OCT_THREADS) k_octree(Tables T, const Cell* __restrict__ cells, int ncells,
+                                                         const uint32_t* __restrict__ slots, size_t slots_per_frame,
+                                                         const int* __restrict__ cell_count,
+                                                         uint32_t* __restrict__ cand, uint32_t* __restrict__ pnode,
+                                                         size_t cand_per_frame, int* __restrict__ cand_count,
+                                                         uint32_t* __restrict__ sel, size_t sel_per_frame,
+                                                         int* __restrict__ sel_count, int maxn, int max_cells) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ int s_tmp[OCT_THREADS / 32 + 1];
+    __shared__ int s_L, s_nE, s_T, s_CT;
+
+    const int level = blockIdx.x, f = blockIdx.y, tid = threadIdx.x;
+    const LevelDev& Lv = T.lv[level];
+    const int N = Lv.N;
+
+    OctSmem S;
+    {
+        unsigned char* p = smem_raw;
+        for (int k = 0; k < 2; ++k) { S.E[k] = (OctE*)p; p += sizeof(OctE) * maxn; }
+        S.best = (unsigned long long*)p; p += 8 * (size_t)maxn;
+        for (int k = 0; k < 2; ++k) { S.cnt[k] = (int*)p; p += 4 * (size_t)maxn; }
+        S.ccnt = (int*)p; p += 16 * (size_t)maxn;
+        S.a = (int*)p; p += 4 * (size_t)maxn;
+        S.b = (int*)p; p += 4 * (size_t)maxn;
+        S.c = (int*)p; p += 4 * (size_t)maxn;
+        S.em = (int*)p; p += 4 * (size_t)maxn;
+        for (int k = 0; k < 2; ++k) {
+            S.x0[k] = (short*)p; p += 2 * (size_t)maxn;
+            S.y0[k] = (short*)p; p += 2 * (size_t)maxn;
+            S.x1[k] = (short*)p; p += 2 * (size_t)maxn;
+            S.y1[k] = (short*)p; p += 2 * (size_t)maxn;
+        }
+    }
+    int* cellpref = S.ccnt;     /* reuse: needs max_cells+1 <= 4*maxn (checked on host) */
+
+    /* ---- gather the level's candidates in reference order (cell raster, in-cell raster) */
+    const int ncl = Lv.cell_end - Lv.cell_begin;
+    for (int i = tid; i < ncl; i += OCT_THREADS) cellpref[i] = cell_count[(size_t)f * ncells + Lv.cell_begin + i];
+    __syncthreads();
+    const int ncand = block_excl_scan(cellpref, ncl, s_tmp);
+    uint32_t* pc = cand + (size_t)f * cand_per_frame + Lv.cand_off;
+    uint32_t* pn = pnode + (size_t)f * cand_per_frame + Lv.cand_off;
+    {
+        const int lane = tid & 31, wid = tid >> 5;
+        for (int ci = wid; ci < ncl; ci += OCT_THREADS / 32) {
+            const Cell c = cells[Lv.cell_begin + ci];
+            const int n = cell_count[(size_t)f * ncells + Lv.cell_begin + ci];
+            const uint32_t* src = slots + (size_t)f * slots_per_frame + c.slot_off;
+            for (int k = lane; k < n; k += 32) pc[cellpref[ci] + k] = src[k];
+        }
+    }
+    if (tid == 0) cand_count[f * T.nlevels + level] = ncand;
+    __syncthreads();
+
+    uint32_t* psel = sel + (size_t)f * sel_per_frame + Lv.sel_off;
+    if (ncand == 0 || Lv.nIni < 1) {
+        if (tid == 0) sel_count[f * T.nlevels + level] = 0;
+        return;
+    }
+
+    /* ---- initial nodes (reference src/ORBextractor.cc:231-274) */
+    const int nIni = Lv.nIni;
+    const float hX = Lv.hX;
+    const int Wd = Lv.w - 2 * ORBX_MINB, Hd = Lv.h - 2 * ORBX_MINB;
+    int cur = 0;
+    for (int i = tid; i < nIni; i += OCT_THREADS) S.a[i] = 0;
+    __syncthreads();
+    for (int i = tid; i < ncand; i += OCT_THREADS) {
+        const uint32_t e = pc[i];
+        const int ini = (int)__fdiv_rn((float)(e & 0xFFF), hX);
+        pn[i] = (uint32_t)ini;
+        atomicAdd(&S.a[ini], 1);
+    }
+    __syncthreads();
+    /* positions of non-empty initial nodes */
+    for (int i = tid; i < nIni; i += OCT_THREADS) { S.c[i] = S.a[i]; S.b[i] = S.a[i] > 0; }
+    __syncthreads();
+    int L = block_excl_scan(S.b, nIni, s_tmp);
+    for (int i = tid; i < nIni; i += OCT_THREADS) {
+        if (S.c[i] > 0) {
+            const int p = S.b[i];
+            S.x0[cur][p] = (short)(int)__fmul_rn(hX, (float)i);
+            S.x1[cur][p] = (short)(int)__fmul_rn(hX, (float)(i + 1));
+            S.y0[cur][p] = 0;
+            S.y1[cur][p] = (short)Hd;
+            S.cnt[cur][p] = S.c[i];
+        }
+    }
+    __syncthreads();
+    for (int i = tid; i < ncand; i += OCT_THREADS) pn[i] = (uint32_t)S.b[pn[i]];
+    __syncthreads();
+    (void)Wd;
+
+    /* ---- main loop (reference :283-428) */
+    bool finish = false;
+    bool final_phase = false;
+    int nE = 0, ecur = 0;
+    while (!finish) {
+        const int prevL = L;
+        const int nxt = cur ^ 1;
+        if (!final_phase) {
+            /* regular sweep: every node with more than one point is divided */
+            for (int i = tid; i < 4 * L; i += OCT_THREADS) S.ccnt[i] = 0;
+            __syncthreads();
+            for (int i = tid; i < ncand; i += OCT_THREADS) {
+                const uint32_t pos = pn[i] & 0xFFFF;
+                if (S.cnt[cur][pos] > 1) {
+                    const uint32_t e = pc[i];
+                    const int q = quadrant_of(e & 0xFFF, (e >> 12) & 0xFFF, S.x0[cur][pos], S.y0[cur][pos],
+                                              S.x1[cur][pos], S.y1[cur][pos]);
+                    atomicAdd(&S.ccnt[4 * pos + q], 1);
+                    pn[i] = pos | ((uint32_t)q << 16);
+                }
+            }
+            __syncthreads();
+            for (int p = tid; p < L; p += OCT_THREADS) {
+                const bool proc = S.cnt[cur][p] > 1;
+                int nz = 0, big = 0;
+                if (proc)
+                    for (int q = 0; q < 4; ++q) { nz += S.ccnt[4 * p + q] > 0; big += S.ccnt[4 * p + q] > 1; }
+                S.a[p] = nz; S.b[p] = proc ? 0 : 1; S.c[p] = big;
+            }
+            __syncthreads();
+            const int totC = block_excl_scan(S.a, L, s_tmp);
+            const int totStay = block_excl_scan(S.b, L, s_tmp);
+            const int totE = block_excl_scan(S.c, L, s_tmp);
+            /* new list = children of processed nodes, LAST processed first, each as n4,n3,n2,n1
+             * (push_front), followed by the untouched bNoMore nodes in their old order */
+            for (int p = tid; p < L; p += OCT_THREADS) {
+                const bool proc = S.cnt[cur][p] > 1;
+                if (proc) {
+                    int nz = 0;
+                    for (int q = 0; q < 4; ++q) nz += S.ccnt[4 * p + q] > 0;
+                    const int seg = totC - S.a[p] - nz;       /* start of this node's segment */
+                    int k = 0, ek = S.c[p];
+                    const int px0 = S.x0[cur][p], py0 = S.y0[cur][p], px1 = S.x1[cur][p], py1 = S.y1[cur][p];
+                    for (int q = 0; q < 4; ++q) {
+                        const int cc = S.ccnt[4 * p + q];
+                        if (cc > 0) {
+                            const int np = seg + (nz - 1 - k);
+                            ++k;
+                            child_bounds(q, px0, py0, px1, py1, S.x0[nxt][np], S.y0[nxt][np], S.x1[nxt][np], S.y1[nxt][np]);
+                            S.cnt[nxt][np] = cc;
+                            if (cc > 1) { S.E[ecur][ek].size = cc; S.E[ecur][ek].ulx = S.x0[nxt][np]; S.E[ecur][ek].pos = np; ++ek; }
+                            S.ccnt[4 * p + q] = np;          /* child count -> child position */
+                        } else {
+                            S.ccnt[4 * p + q] = -1;
+                        }
+                    }
+                } else {
+                    const int np = totC + S.b[p];
+                    S.x0[nxt][np] = S.x0[cur][p]; S.y0[nxt][np] = S.y0[cur][p];
+                    S.x1[nxt][np] = S.x1[cur][p]; S.y1[nxt][np] = S.y1[cur][p];
+                    S.cnt[nxt][np] = S.cnt[cur][p];
+                    S.em[p] = np;
+                }
+            }
+            __syncthreads();
+            for (int i = tid; i < ncand; i += OCT_THREADS) {
+                const uint32_t v = pn[i];
+                const uint32_t pos = v & 0xFFFF;
+                pn[i] = (S.cnt[cur][pos] > 1) ? (uint32_t)S.ccnt[4 * pos + (v >> 16)] : (uint32_t)S.em[pos];
+            }
+            __syncthreads();
+            L = totC + totStay;
+            nE = totE;
+            cur = nxt;
+            if (L >= N || L == prevL) finish = true;
+            else if (L + nE * 3 > N) final_phase = true;
+        } else {
+            /* final phase (reference :365-426): split the largest nodes first until N is reached */
+            if (tid == 0) orbx_stdsort::sort(S.E[ecur], nE, OctLess());
+            for (int p = tid; p < L; p += OCT_THREADS) S.em[p] = -1;
+            __syncthreads();
+            for (int m = tid; m < nE; m += OCT_THREADS) {
+                const int p = S.E[ecur][nE - 1 - m].pos;     /* m-th node to be divided */
+                S.em[p] = m;
+                S.ccnt[4 * m] = 0; S.ccnt[4 * m + 1] = 0; S.ccnt[4 * m + 2] = 0; S.ccnt[4 * m + 3] = 0;
+            }
+            __syncthreads();
+            for (int i = tid; i < ncand; i += OCT_THREADS) {
+                const uint32_t pos = pn[i] & 0xFFFF;
+                const int m = S.em[pos];
+                if (m >= 0) {
+                    const uint32_t e = pc[i];
+                    const int q = quadrant_of(e & 0xFFF, (e >> 12) & 0xFFF, S.x0[cur][pos], S.y0[cur][pos],
+                                              S.x1[cur][pos], S.y1[cur][pos]);
+                    atomicAdd(&S.ccnt[4 * m + q], 1);
+                    pn[i] = pos | ((uint32_t)q << 16);
+                }
+            }
+            __syncthreads();
+            for (int m = tid; m < nE; m += OCT_THREADS) {
+                int nz = 0;
+                for (int q = 0; q < 4; ++q) nz += S.ccnt[4 * m + q] > 0;
+                S.a[m] = nz;
+            }
+            __syncthreads();
+            if (tid == 0) {
+                /* list size after dividing the m-th node: break as soon as it reaches N (:419-420) */
+                int sz = L, Tn = nE, CT = 0;
+                for (int m = 0; m < nE; ++m) {
+                    sz += S.a[m] - 1;
+                    CT += S.a[m];
+                    if (sz >= N) { Tn = m + 1; break; }
+                }
+                s_T = Tn; s_CT = CT;
+            }
+            __syncthreads();
+            const int Tn = s_T, CT = s_CT;
+            /* segment start for m: children of later-divided nodes come first */
+            for (int m = tid; m < nE; m += OCT_THREADS) {
+                int big = 0;
+                if (m < Tn) for (int q = 0; q < 4; ++q) big += S.ccnt[4 * m + q] > 1;
+                S.c[m] = big;
+                if (m >= Tn) S.a[m] = 0;
+            }
+            for (int p = tid; p < L; p += OCT_THREADS) { const int m = S.em[p]; S.b[p] = (m >= 0 && m < Tn) ? 0 : 1; }
+            __syncthreads();
+            block_excl_scan(S.a, nE, s_tmp);
+            const int totStay = block_excl_scan(S.b, L, s_tmp);
+            const int totE = block_excl_scan(S.c, nE, s_tmp);
+            const int enx = ecur ^ 1;
+            for (int m = tid; m < Tn; m += OCT_THREADS) {
+                const int p = S.E[ecur][nE - 1 - m].pos;
+                int nz = 0;
+                for (int q = 0; q < 4; ++q) nz += S.ccnt[4 * m + q] > 0;
+                const int seg = CT - S.a[m] - nz;
+                int k = 0, ek = S.c[m];
+                const int px0 = S.x0[cur][p], py0 = S.y0[cur][p], px1 = S.x1[cur][p], py1 = S.y1[cur][p];
+                for (int q = 0; q < 4; ++q) {
+                    const int cc = S.ccnt[4 * m + q];
+                    if (cc > 0) {
+                        const int np = seg + (nz - 1 - k);
+                        ++k;
+                        child_bounds(q, px0, py0, px1, py1, S.x0[nxt][np], S.y0[nxt][np], S.x1[nxt][np], S.y1[nxt][np]);
+                        S.cnt[nxt][np] = cc;
+                        if (cc > 1) { S.E[enx][ek].size = cc; S.E[enx][ek].ulx = S.x0[nxt][np]; S.E[enx][ek].pos = np; ++ek; }
+                        S.ccnt[4 * m + q] = np;
+                    } else {
+                        S.ccnt[4 * m + q] = -1;
+                    }
+                }
+            }
+            for (int p = tid; p < L; p += OCT_THREADS) {
+                const int m = S.em[p];
+                if (!(m >= 0 && m < Tn)) {
+                    const int np = CT + S.b[p];
+                    S.x0[nxt][np] = S.x0[cur][p]; S.y0[nxt][np] = S.y0[cur][p];
+                    S.x1[nxt][np] = S.x1[cur][p]; S.y1[nxt][np] = S.y1[cur][p];
+                    S.cnt[nxt][np] = S.cnt[cur][p];
+                    S.b[p] = np;
+                }
+            }
+            __syncthreads();
+            for (int i = tid; i < ncand; i += OCT_THREADS) {
+                const uint32_t v = pn[i];
+                const uint32_t pos = v & 0xFFFF;
+                const int m = S.em[pos];
+                pn[i] = (m >= 0 && m < Tn) ? (uint32_t)S.ccnt[4 * m + (v >> 16)] : (uint32_t)S.b[pos];
+            }
+            __syncthreads();
+            L = CT + totStay;
+            nE = totE;
+            ecur = enx;
+            cur = nxt;
+            if (L >= N || L == prevL) finish = true;
+        }
+    }
+
+    /* ---- best point per node: max response, first in input order on ties (reference :514-533) */
+    for (int p = tid; p < L; p += OCT_THREADS) S.best[p] = 0ull;
+    __syncthreads();
+    for (int i = tid; i < ncand; i += OCT_THREADS) {
+        const uint32_t e = pc[i];
+        const unsigned long long key = ((unsigned long long)(e >> 24) << 32) | (unsigned long long)(0xFFFFFFFFu - (uint32_t)i);
+        atomicMax(&S.best[pn[i] & 0xFFFF], key);
+    }
+    __syncthreads();
+    for (int p = tid; p < L; p += OCT_THREADS) {
+        const uint32_t i = 0xFFFFFFFFu - (uint32_t)(S.best[p] & 0xFFFFFFFFull);
+        psel[p] = pc[i];
+    }
+    if (tid == 0) sel_count[f * T.nlevels + level] = L;
+}
+
+/* ================================================================== stage 3: order */
+/* operator() tail: level-major order, keypoints whose level-0 x lies in
+ * [lap0, lap1] are filled from the back (stereoIndex--), the rest from the front. */
+#define ORD_THREADS 256
+__global__ void __launch_bounds__(ORD_THREADS) k_order(Tables T, const uint32_t* __restrict__ sel, size_t sel_per_frame,
+                                                        const int* __restrict__ sel_count, const int* __restrict__ lapping,
+                                                        int* __restrict__ dest, int* __restrict__ nk_out,
+                                                        int* __restrict__ mono_out) {
+    __shared__ int s_w[ORD_THREADS / 32];
+    __shared__ int s_lvl_off[ORBX_MAX_LEVELS + 1];
+    const int f = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    if (tid == 0) {
+        int o = 0;
+        for (int l = 0; l < T.nlevels; ++l) { s_lvl_off[l] = o; o += sel_count[f * T.nlevels + l]; }
+        s_lvl_off[T.nlevels] = o;
+    }
+    __syncthreads();
+    const int nk = s_lvl_off[T.nlevels];
+    const int lap0 = lapping ? lapping[2 * f] : 0, lap1 = lapping ? lapping[2 * f + 1] : 0;
+    int mono_run = 0;      /* mono keypoints before the current chunk */
+    for (int base = 0; base < nk; base += ORD_THREADS) {
+        const int g = base + tid;
+        int stereo = 0, slot = -1;
+        if (g < nk) {
+            int l = 0;
+            while (g >= s_lvl_off[l + 1]) ++l;
+            const int i = g - s_lvl_off[l];
+            slot = T.lv[l].sel_off + i;
+            const uint32_t e = sel[(size_t)f * sel_per_frame + slot];
+            float x = (float)((int)(e & 0xFFF) + ORBX_MINB);
+            if (l != 0) x = __fmul_rn(x, T.lv[l].scale);
+            stereo = (x >= (float)lap0 && x <= (float)lap1);
+        }
+        const unsigned bal = __ballot_sync(0xffffffffu, g < nk && !stereo);
+        if (lane == 0) s_w[wid] = __popc(bal);
+        __syncthreads();
+        int off = 0, tot = 0;
+        for (int w = 0; w < ORD_THREADS / 32; ++w) { if (w < wid) off += s_w[w]; tot += s_w[w]; }
+        if (g < nk) {
+            const int mono_before = mono_run + off + __popc(bal & ((1u << lane) - 1));
+            const int stereo_before = g - mono_before;
+            dest[(size_t)f * sel_per_frame + slot] = stereo ? (nk - 1 - stereo_before) : mono_before;
+        }
+        mono_run += tot;
+        __syncthreads();
+    }
+    if (tid == 0) { nk_out[f] = nk; mono_out[f] = mono_run; }
+}
+
+/* ================================================================== stage 4: blur */
+/* cv::GaussianBlur(7x7, sigma 2, BORDER_REFLECT_101) on a clone() of the level = integer taps
+ * [18,34,48,56,48,34,18] per axis, (v + 2^15) >> 16.  The level's own 19-px
+ * reflect-101 border supplies the halo, so no edge handling is needed. */
+#define BL_TW 64
+#define BL_TH 16
+__global__ void __launch_bounds__(256) k_blur7(Tables T, const int4* __restrict__ tiles, int batch) {
+    __shared__ uint8_t s_in[(BL_TH + 6) * (BL_TW + 8)];
+    __shared__ unsigned short s_h[(BL_TH + 6) * BL_TW];
+    const int4 t = tiles[blockIdx.x];        /* {level, tx, ty, 0} */
+    const int f = blockIdx.y;
+    const LevelDev& L = T.lv[t.x];
+    const int x0 = t.y * BL_TW, y0 = t.z * BL_TH;
+    const int tid = threadIdx.x;
+    const int P = BL_TW + 8;
+    for (int i = tid; i < (BL_TH + 6) * (BL_TW + 6); i += 256) {
+        const int y = i / (BL_TW + 6), x = i - y * (BL_TW + 6);
+        const int gx = min(x0 + x - 3, L.w + ORBX_EDGE - 1), gy = min(y0 + y - 3, L.h + ORBX_EDGE - 1);
+        s_in[y * P + x] = __ldg(lv_ptr(L, f, gx, gy));
+    }
+    __syncthreads();
+    for (int i = tid; i < (BL_TH + 6) * BL_TW; i += 256) {
+        const int y = i / BL_TW, x = i - y * BL_TW;
+        const uint8_t* p = s_in + y * P + x;
+        s_h[i] = (unsigned short)(18 * (p[0] + p[6]) + 34 * (p[1] + p[5]) + 48 * (p[2] + p[4]) + 56 * p[3]);
+    }
+    __syncthreads();
+    for (int i = tid; i < BL_TH * BL_TW; i += 256) {
+        const int y = i / BL_TW, x = i - y * BL_TW;
+        if (x0 + x < L.w && y0 + y < L.h) {
+            const unsigned short* p = s_h + y * BL_TW + x;
+            const int acc = 18 * (p[0] + p[6 * BL_TW]) + 34 * (p[BL_TW] + p[5 * BL_TW]) +
+                            48 * (p[2 * BL_TW] + p[4 * BL_TW]) + 56 * p[3 * BL_TW];
+            L.blur[(size_t)f * L.bframe_bytes + (size_t)(y0 + y) * L.bpitch + x0 + x] = (uint8_t)((acc + (1 << 15)) >> 16);
+        }
+    }
+}
+
+/* ================================================================== stage 5: orientation + descriptor */
+__device__ const signed char d_pattern[1024] = {
+#include "../../include/orbx_pattern31.inc"
+};
+
+struct UMax { int v[16]; };
+
+/* cv::fastAtan2: fp32, no FMA contraction */
+__device__ __forceinline__ float fast_atan2_deg(float y, float x) {
+    constexpr float sc = (float)(180.0 / 3.14159265358979323846);
+    constexpr float p1 = 0.9997878412794807f * sc, p3 = -0.3258083974640975f * sc;
+    constexpr float p5 = 0.1555786518463281f * sc, p7 = -0.04432655554792128f * sc;
+    const float eps = (float)2.2204460492503131e-16;
+    const float ax = fabsf(x), ay = fabsf(y);
+    float a, c, c2;
+    if (ax >= ay) {
+        c = __fdiv_rn(ay, __fadd_rn(ax, eps));
+        c2 = __fmul_rn(c, c);
+        a = __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c);
+    } else {
+        c = __fdiv_rn(ax, __fadd_rn(ay, eps));
+        c2 = __fmul_rn(c, c);
+        a = __fsub_rn(90.f, __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c));
+    }
+    if (x < 0) a = __fsub_rn(180.f, a);
+    if (y < 0) a = __fsub_rn(360.f, a);
+    return a;
+}
+
+__global__ void __launch_bounds__(256) k_orient_describe(Tables T, UMax um, const uint32_t* __restrict__ sel,
+                                                          size_t sel_per_frame, const int* __restrict__ sel_count,
+                                                          const int* __restrict__ dest, orbx_keypoint* __restrict__ kps,
+                                                          uint8_t* __restrict__ desc, int kcap) {
+    const int lane = threadIdx.x & 31;
+    const int slot = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int f = blockIdx.y;
+    if (slot >= (int)sel_per_frame) return;
+    int l = 0;
+    while (l + 1 < T.nlevels && slot >= T.lv[l + 1].sel_off) ++l;
+    const LevelDev& L = T.lv[l];
+    const int i = slot - L.sel_off;
+    if (i >= sel_count[f * T.nlevels + l]) return;
+    const uint32_t e = sel[(size_t)f * sel_per_frame + slot];
+    const int x = (int)(e & 0xFFF) + ORBX_MINB, y = (int)((e >> 12) & 0xFFF) + ORBX_MINB;
+    const int resp = (int)(e >> 24);
+
+    /* IC_Angle (reference src/cuda/Angle_gpu.cu:39-69): lane = patch row v = lane-15 */
+    int m10 = 0, m01 = 0;
+    if (lane < 31) {
+        const int v = lane - 15;
+        const int d = um.v[v < 0 ? -v : v];
+        const uint8_t* row = lv_ptr(L, f, x, y + v);
+        int su = 0, s = 0;
+        for (int u = -d; u <= d; ++u) {
+            const int val = __ldg(row + u);
+            su += u * val;
+            s += val;
+        }
+        m10 = su;
+        m01 = v * s;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        m10 += __shfl_xor_sync(0xffffffffu, m10, o);
+        m01 += __shfl_xor_sync(0xffffffffu, m01, o);
+    }
+    const float angle = fast_atan2_deg((float)m01, (float)m10);
+
+    /* rBRIEF (reference src/cuda/Orb_gpu.cu:311-350): lane = descriptor byte */
+    constexpr float factorPI = (float)(3.14159265358979323846 / 180.f);
+    const float ar = __fmul_rn(angle, factorPI);
+    /* cosf/sinf of the reference resolve to glibc (<=0.56 ULP); here: fp64 result rounded once */
+    const float a = (float)cos((double)ar), b = (float)sin((double)ar);
+    const uint8_t* center = L.blur + (size_t)f * L.bframe_bytes + (size_t)y * L.bpitch + x;
+    const signed char* pat = d_pattern + 32 * lane;
+    int val = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const float px0 = pat[4 * j], py0 = pat[4 * j + 1], px1 = pat[4 * j + 2], py1 = pat[4 * j + 3];
+        const int iy0 = __float2int_rn(__fadd_rn(__fmul_rn(px0, b), __fmul_rn(py0, a)));
+        const int ix0 = __float2int_rn(__fsub_rn(__fmul_rn(px0, a), __fmul_rn(py0, b)));
+        const int iy1 = __float2int_rn(__fadd_rn(__fmul_rn(px1, b), __fmul_rn(py1, a)));
+        const int ix1 = __float2int_rn(__fsub_rn(__fmul_rn(px1, a), __fmul_rn(py1, b)));
+        const int t0 = __ldg(center + iy0 * L.bpitch + ix0);
+        const int t1 = __ldg(center + iy1 * L.bpitch + ix1);
+        val |= (t0 < t1) << j;
+    }
+    const int d = dest[(size_t)f * sel_per_frame + slot];
+    desc[((size_t)f * kcap + d) * 32 + lane] = (uint8_t)val;
+    if (lane == 0) {
+        orbx_keypoint k;
+        float fx = (float)x, fy = (float)y;
+        if (l != 0) { fx = __fmul_rn(fx, L.scale); fy = __fmul_rn(fy, L.scale); }
+        k.x = fx; k.y = fy; k.size = L.patch_size; k.angle = angle; k.response = (float)resp;
+        k.octave = l; k.class_id = -1;
+        kps[(size_t)f * kcap + d] = k;
+    }
+}
+
+/* ================================================================== host side */
+struct orbx_extractor {
+    orbx_params P;
+    int nlevels;
+    std::vector<float> sf, inv_sf, sigma2, inv_sigma2;
+    std::vector<int> nfeat, umax;
+    Tables T;
+    std::vector<LevelDev> lv;
+    std::vector<Cell> cells;
+    int ncells = 0, max_cells_level = 0;
+    size_t slots_per_frame = 0, cand_per_frame = 0, sel_per_frame = 0;
+    int kcap = 0, maxn = 0;
+    size_t oct_smem = 0;
+    int nblur_tiles = 0;
+    cudaStream_t stream = nullptr;
+    /* device buffers */
+    uint8_t* d_pyr = nullptr;
+    uint8_t* d_blur = nullptr;
+    uint8_t* d_input = nullptr;      /* staging for orbx_extract_host */
+    short4* d_tabs = nullptr;
+    Cell* d_cells = nullptr;
+    int4* d_blur_tiles = nullptr;
+    uint32_t* d_slots = nullptr;
+    int* d_cell_count = nullptr;
+    uint32_t* d_cand = nullptr;
+    uint32_t* d_pnode = nullptr;
+    int* d_cand_count = nullptr;
+    uint32_t* d_sel = nullptr;
+    int* d_sel_count = nullptr;
+    int* d_dest = nullptr;
+    int* d_lapping = nullptr;
+    orbx_keypoint* d_kps = nullptr;
+    uint8_t* d_desc = nullptr;
+    int* d_nk = nullptr;           /* [2*max_batch]: counts then mono indices */
+    /* pinned host mirrors */
+    orbx_keypoint* h_kps = nullptr;
+    uint8_t* h_desc = nullptr;
+    int* h_nk = nullptr;
+    int* h_lapping = nullptr;
+    int last_batch = 0, last_launches = 0;
+    bool synced = false;
+    bool profiling = false;
+    cudaEvent_t ev[7] = {};
+};
+
+static inline int cvRoundf_host(float v) { return (int)lrintf(v); }
+
+static void free_all(orbx_extractor* e) {
+    if (!e) return;
+    cudaSetDevice(e->P.device);
+    void* dptrs[] = {e->d_pyr, e->d_blur, e->d_input, e->d_tabs, e->d_cells, e->d_blur_tiles, e->d_slots,
+                     e->d_cell_count, e->d_cand, e->d_pnode, e->d_cand_count, e->d_sel, e->d_sel_count,
+                     e->d_dest, e->d_lapping, e->d_kps, e->d_desc, e->d_nk};
+    for (void* p : dptrs) if (p) cudaFree(p);
+    void* hptrs[] = {e->h_kps, e->h_desc, e->h_nk, e->h_lapping};
+    for (void* p : hptrs) if (p) cudaFreeHost(p);
+    for (int i = 0; i < 7; ++i) if (e->ev[i]) cudaEventDestroy(e->ev[i]);
+    if (e->stream) cudaStreamDestroy(e->stream);
+    delete e;
+}
+
+extern "C" void orbx_extractor_destroy(orbx_extractor* e) { free_all(e); }
+
+extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extractor** out) {
+    if (!p || !out) { orbx_set_error("null argument"); return ORBX_ERR_INVALID; }
+    *out = nullptr;
+    if (p->nlevels < 1 || p->nlevels > ORBX_MAX_LEVELS || p->nfeatures < 1 || p->scale_factor <= 1.0f ||
+        p->width < 64 || p->height < 64 || p->width > 4000 || p->height > 4000 || p->max_batch < 1 ||
+        p->min_th_fast < 1 || p->ini_th_fast < p->min_th_fast || p->ini_th_fast > 255) {
+        orbx_set_error("unsupported parameters (need 64<=w,h<=4000, 1<=minTh<=iniTh<=255, nlevels<=%d)", ORBX_MAX_LEVELS);
+        return ORBX_ERR_INVALID;
+    }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= p->device) {
+        orbx_set_error("no CUDA device %d (this library has no CPU fallback)", p->device);
+        return ORBX_ERR_CUDA;
+    }
+    ORBX_CUDA(cudaSetDevice(p->device));
+    orbx_extractor* e = new orbx_extractor;
+    e->P = *p;
+    const int nl = e->nlevels = p->nlevels;
+    const int B = p->max_batch;
+
+    /* ---- tables: reference src/ORBextractor.cc:92-143 (same float/double mix) */
+    const double scaleFactor = p->scale_factor;
+    e->sf.resize(nl); e->sigma2.resize(nl); e->inv_sf.resize(nl); e->inv_sigma2.resize(nl);
+    e->sf[0] = 1.0f; e->sigma2[0] = 1.0f;
+    for (int i = 1; i < nl; i++) { e->sf[i] = e->sf[i - 1] * scaleFactor; e->sigma2[i] = e->sf[i] * e->sf[i]; }
+    for (int i = 0; i < nl; i++) { e->inv_sf[i] = 1.0f / e->sf[i]; e->inv_sigma2[i] = 1.0f / e->sigma2[i]; }
+    e->nfeat.resize(nl);
+    {
+        float factor = 1.0f / scaleFactor;
+        float nDesired = p->nfeatures * (1 - factor) / (1 - (float)pow((double)factor, (double)nl));
+        int sum = 0;
+        for (int l = 0; l < nl - 1; l++) { e->nfeat[l] = cvRoundf_host(nDesired); sum += e->nfeat[l]; nDesired *= factor; }
+        e->nfeat[nl - 1] = std::max(p->nfeatures - sum, 0);
+    }
+    {
+        const int HP = 15;
+        e->umax.assign(HP + 1, 0);
+        int v, v0, vmax = (int)floor(HP * sqrt(2.f) / 2 + 1), vmin = (int)ceil(HP * sqrt(2.f) / 2);
+        const double hp2 = HP * HP;
+        for (v = 0; v <= vmax; ++v) e->umax[v] = (int)lrint(sqrt(hp2 - v * v));
+        for (v = HP, v0 = 0; v >= vmin; --v) { while (e->umax[v0] == e->umax[v0 + 1]) ++v0; e->umax[v] = v0; ++v0; }
+    }
+
+    /* ---- level geometry, FAST cells, quadtree capacities */
+    e->lv.resize(nl);
+    size_t pyr_bytes = 0, blur_bytes = 0, tab_entries = 0;
+    size_t slot_off = 0, cand_off = 0, sel_off = 0;
+    std::vector<int4> blur_tiles;
+    int maxn = 8;
+    for (int l = 0; l < nl; ++l) {
+        LevelDev& L = e->lv[l];
+        memset(&L, 0, sizeof(L));
+        L.w = cvRoundf_host((float)p->width * e->inv_sf[l]);       /* reference :596-599 */
+        L.h = cvRoundf_host((float)p->height * e->inv_sf[l]);
+        if (L.w < 2 * ORBX_EDGE + 2 || L.h < 2 * ORBX_EDGE + 2) {
+            orbx_set_error("level %d is %dx%d: smaller than the 19-px border allows", l, L.w, L.h);
+            free_all(e);
+            return ORBX_ERR_INVALID;
+        }
+        L.pitch = (int)orbx_align_up(ORBX_XOFF + L.w + ORBX_EDGE, 64);
+        L.rows = L.h + 2 * ORBX_EDGE;
+        L.frame_bytes = orbx_align_up((size_t)L.pitch * L.rows + 64, 256);
+        L.bpitch = (int)orbx_align_up(L.w, 64);
+        L.bframe_bytes = orbx_align_up((size_t)L.bpitch * L.h, 256);
+        pyr_bytes += L.frame_bytes * B;
+        blur_bytes += L.bframe_bytes * B;
+        tab_entries += L.w + L.h;
+        L.scale = e->sf[l];
+        L.patch_size = (float)(int)(31 * e->sf[l]);
+        /* cells */
+        const int minB = ORBX_MINB, maxBX = L.w - ORBX_EDGE + 3, maxBY = L.h - ORBX_EDGE + 3;
+        const float width = (float)(maxBX - minB), height = (float)(maxBY - minB);
+        const int nCols = (int)(width / 35.f), nRows = (int)(height / 35.f);
+        L.cell_begin = (int)e->cells.size();
+        L.cand_off = (int)cand_off;
+        if (nCols >= 1 && nRows >= 1) {
+            const int wCell = (int)ceilf(width / nCols), hCell = (int)ceilf(height / nRows);
+            for (int i = 0; i < nRows; i++) {
+                const float iniY = minB + i * hCell;
+                float maxY = iniY + hCell + 6;
+                if (iniY >= maxBY - 3) continue;
+                if (maxY > maxBY) maxY = maxBY;
+                for (int j = 0; j < nCols; j++) {
+                    const float iniX = minB + j * wCell;
+                    float maxX = iniX + wCell + 6;
+                    if (iniX >= maxBX - 6) continue;
+                    if (maxX > maxBX) maxX = maxBX;
+                    Cell c;
+                    c.level = (short)l; c.x0 = (short)iniX; c.y0 = (short)iniY;
+                    c.cw = (short)((int)maxX - (int)iniX); c.ch = (short)((int)maxY - (int)iniY);
+                    c.offx = (short)(j * wCell); c.offy = (short)(i * hCell); c.pad = 0;
+                    c.slot_off = (int)slot_off;
+                    c.idx_in_level = (int)e->cells.size() - L.cell_begin;
+                    if (c.cw > FAST_TP || c.ch > FAST_TH) {
+                        orbx_set_error("FAST cell %dx%d exceeds the %d-px tile", c.cw, c.ch, FAST_TP);
+                        free_all(e);
+                        return ORBX_ERR_INVALID;
+                    }
+                    const int dw = c.cw - 6, dh = c.ch - 6;
+                    const int cap = (dw > 0 && dh > 0) ? ((dw + 1) / 2) * ((dh + 1) / 2) : 0;  /* NMS survivors are never 8-adjacent */
+                    slot_off += cap;
+                    cand_off += cap;
+                    e->cells.push_back(c);
+                }
+            }
+        }
+        L.cell_end = (int)e->cells.size();
+        L.cand_cap = (int)cand_off - L.cand_off;
+        e->max_cells_level = std::max(e->max_cells_level, L.cell_end - L.cell_begin);
+        /* quadtree */
+        L.N = e->nfeat[l];
+        const int Wd = maxBX - minB, Hd = maxBY - minB;
+        L.nIni = (int)roundf((float)Wd / Hd);                       /* reference :231 */
+        L.hX = L.nIni >= 1 ? (float)Wd / L.nIni : 0.f;             /* :233 */
+        L.sel_off = (int)sel_off;
+        L.sel_cap = std::max(L.N + 3, 4 * std::max(L.nIni, 0)) + 1;
+        sel_off += L.sel_cap;
+        maxn = std::max(maxn, L.sel_cap + 4);
+        for (int ty = 0; ty < orbx_div_up(L.h, BL_TH); ++ty)
+            for (int tx = 0; tx < orbx_div_up(L.w, BL_TW); ++tx) blur_tiles.push_back(make_int4(l, tx, ty, 0));
+    }
+    e->ncells = (int)e->cells.size();
+    e->slots_per_frame = slot_off;
+    e->cand_per_frame = cand_off;
+    e->sel_per_frame = sel_off;
+    e->kcap = (int)sel_off;
+    maxn = std::max(maxn, orbx_div_up(e->max_cells_level + 1, 4) + 1);
+    if (maxn > 60000) { orbx_set_error("nfeatures too large for 16-bit node positions"); free_all(e); return ORBX_ERR_INVALID; }
+    e->maxn = maxn;
+    e->oct_smem = (size_t)maxn * (2 * sizeof(OctE) + 8 + 2 * 4 + 16 + 4 * 4 + 2 * 4 * 2) + 64;
+    e->nblur_tiles = (int)blur_tiles.size();
+    if (e->oct_smem > 220 * 1024) { orbx_set_error("nfeatures too large for the shared-memory quadtree (%zu B)", e->oct_smem); free_all(e); return ORBX_ERR_INVALID; }
+
+#define CK(call) do { cudaError_t _e = (call); if (_e != cudaSuccess) { orbx_set_error("%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(_e)); free_all(e); return ORBX_ERR_CUDA; } } while (0)
+    CK(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
+    for (int i = 0; i < 7; ++i) CK(cudaEventCreate(&e->ev[i]));
+    CK(cudaFuncSetAttribute(k_octree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)e->oct_smem));
+    CK(cudaMalloc(&e->d_pyr, pyr_bytes));
+    CK(cudaMalloc(&e->d_blur, blur_bytes));
+    CK(cudaMemsetAsync(e->d_pyr, 0, pyr_bytes, e->stream));
+    CK(cudaMalloc(&e->d_input, (size_t)B * p->width * p->height));
+    CK(cudaMalloc(&e->d_tabs, tab_entries * sizeof(short4)));
+    CK(cudaMalloc(&e->d_cells, std::max<size_t>(e->cells.size(), 1) * sizeof(Cell)));
+    CK(cudaMalloc(&e->d_blur_tiles, blur_tiles.size() * sizeof(int4)));
+    CK(cudaMalloc(&e->d_slots, std::max<size_t>(e->slots_per_frame, 1) * B * 4));
+    CK(cudaMalloc(&e->d_cell_count, (size_t)std::max(e->ncells, 1) * B * 4));
+    CK(cudaMalloc(&e->d_cand, std::max<size_t>(e->cand_per_frame, 1) * B * 4));
+    CK(cudaMalloc(&e->d_pnode, std::max<size_t>(e->cand_per_frame, 1) * B * 4));
+    CK(cudaMalloc(&e->d_cand_count, (size_t)B * nl * 4));
+    CK(cudaMalloc(&e->d_sel, e->sel_per_frame * B * 4));
+    CK(cudaMalloc(&e->d_sel_count, (size_t)B * nl * 4));
+    CK(cudaMalloc(&e->d_dest, e->sel_per_frame * B * 4));
+    CK(cudaMalloc(&e->d_lapping, (size_t)B * 2 * 4));
+    CK(cudaMalloc(&e->d_kps, (size_t)B * e->kcap * sizeof(orbx_keypoint)));
+    CK(cudaMalloc(&e->d_desc, (size_t)B * e->kcap * 32));
+    CK(cudaMalloc(&e->d_nk, (size_t)B * 2 * 4));
+    CK(cudaMallocHost(&e->h_kps, (size_t)B * e->kcap * sizeof(orbx_keypoint)));
+    CK(cudaMallocHost(&e->h_desc, (size_t)B * e->kcap * 32));
+    CK(cudaMallocHost(&e->h_nk, (size_t)B * 2 * 4));
+    CK(cudaMallocHost(&e->h_lapping, (size_t)B * 2 * 4));
+
+    /* ---- resize tables, computed on the host in IEEE fp32/fp64 */
+    {
+        std::vector<short4> tabs(tab_entries);
+        size_t off = 0, poff = 0, boff = 0;
+        for (int l = 0; l < nl; ++l) {
+            LevelDev& L = e->lv[l];
+            L.base = e->d_pyr + poff; poff += L.frame_bytes * B;
+            L.blur = e->d_blur + boff; boff += L.bframe_bytes * B;
+            L.xtab = e->d_tabs + off;
+            L.ytab = e->d_tabs + off + L.w;
+            if (l > 0) {
+                const int sw = e->lv[l - 1].w, sh = e->lv[l - 1].h;
+                const double scale_x = (double)sw / L.w, scale_y = (double)sh / L.h;
+                for (int dx = 0; dx < L.w; ++dx) {
+                    float fx = (float)((dx + 0.5) * scale_x - 0.5);
+                    int sx = (int)floorf(fx);
+                    fx -= sx;
+                    if (sx < 0) { fx = 0; sx = 0; }
+                    if (sx >= sw - 1) { fx = 0; sx = sw - 1; }
+                    tabs[off + dx] = make_short4((short)sx, (short)cvRoundf_host((1.f - fx) * 2048), (short)cvRoundf_host(fx * 2048), 0);
+                }
+                for (int dy = 0; dy < L.h; ++dy) {
+                    float fy = (float)((dy + 0.5) * scale_y - 0.5);
+                    int sy = (int)floorf(fy);
+                    fy -= sy;
+                    if (sy < 0) { fy = 0; sy = 0; }
+                    if (sy >= sh - 1) { fy = 0; sy = sh - 1; }
+                    tabs[off + L.w + dy] = make_short4((short)sy, (short)cvRoundf_host((1.f - fy) * 2048), (short)cvRoundf_host(fy * 2048), 0);
+                }
+            }
+            off += L.w + L.h;
+        }
+        CK(cudaMemcpyAsync(e->d_tabs, tabs.data(), tabs.size() * sizeof(short4), cudaMemcpyHostToDevice, e->stream));
+        if (!e->cells.empty())
+            CK(cudaMemcpyAsync(e->d_cells, e->cells.data(), e->cells.size() * sizeof(Cell), cudaMemcpyHostToDevice, e->stream));
+        CK(cudaMemcpyAsync(e->d_blur_tiles, blur_tiles.data(), blur_tiles.size() * sizeof(int4), cudaMemcpyHostToDevice, e->stream));
+        CK(cudaStreamSynchronize(e->stream));
+    }
+    e->T.nlevels = nl;
+    for (int l = 0; l < nl; ++l) e->T.lv[l] = e->lv[l];
+#undef CK
+    *out = e;
+    return ORBX_OK;
+}
+
+extern "C" orbx_status orbx_extractor_tables(const orbx_extractor* e, float* scale, float* inv_scale, float* sigma2,
+                                             float* inv_sigma2, int* feat_per_level, int* umax16) {
+    if (!e) return ORBX_ERR_INVALID;
+    for (int i = 0; i < e->nlevels; ++i) {
+        if (scale) scale[i] = e->sf[i];
+        if (inv_scale) inv_scale[i] = e->inv_sf[i];
+        if (sigma2) sigma2[i] = e->sigma2[i];
+        if (inv_sigma2) inv_sigma2[i] = e->inv_sigma2[i];
+        if (feat_per_level) feat_per_level[i] = e->nfeat[i];
+    }
+    if (umax16) for (int i = 0; i < 16; ++i) umax16[i] = e->umax[i];
+    return ORBX_OK;
+}
+
+extern "C" int orbx_extractor_capacity(const orbx_extractor* e) { return e ? e->kcap : 0; }
+extern "C" void* orbx_extractor_stream(orbx_extractor* e) { return e ? (void*)e->stream : nullptr; }
+extern "C" int orbx_extractor_last_launches(const orbx_extractor* e) { return e ? e->last_launches : 0; }
+extern "C" orbx_status orbx_extractor_set_profiling(orbx_extractor* e, int on) {
+    if (!e) return ORBX_ERR_INVALID;
+    e->profiling = on != 0;
+    return ORBX_OK;
+}
+
+static inline int grid_for(long long work_items, int threads, int cap_blocks) {
+    long long b = (work_items + threads - 1) / threads;
+    if (b > cap_blocks) b = cap_blocks;
+    if (b < 1) b = 1;
+    return (int)b;
+}
+
+extern "C" orbx_status orbx_extract_device(orbx_extractor* e, const uint8_t* d_images, size_t frame_stride,
+                                           int row_stride, int batch, const int* lapping) {
+    if (!e || !d_images) { orbx_set_error("null argument"); return d_images ? ORBX_ERR_INVALID : ORBX_ERR_EMPTY; }
+    if (batch < 1 || batch > e->P.max_batch || row_stride < e->P.width) {
+        orbx_set_error("batch %d outside [1,%d] or row_stride < width", batch, e->P.max_batch);
+        return ORBX_ERR_INVALID;
+    }
+    ORBX_CUDA(cudaSetDevice(e->P.device));
+    cudaStream_t st = e->stream;
+    const int nl = e->nlevels;
+    int launches = 0;
+    const int* d_lap = nullptr;
+    if (lapping) {
+        memcpy(e->h_lapping, lapping, sizeof(int) * 2 * batch);
+        ORBX_CUDA(cudaMemcpyAsync(e->d_lapping, e->h_lapping, sizeof(int) * 2 * batch, cudaMemcpyHostToDevice, st));
+        d_lap = e->d_lapping;
+    }
+    const int kMaxBlocks = 148 * 16;
+    if (e->profiling) ORBX_CUDA(cudaEventRecord(e->ev[0], st));
+    /* stage 0 */
+    {
+        const LevelDev& L0 = e->T.lv[0];
+        const int vec_ok = (row_stride % 16 == 0) && (frame_stride % 16 == 0) && (((uintptr_t)d_images) % 16 == 0);
+        const long long items = (long long)batch * L0.rows * (L0.pitch / 16);
+        k_level0<<<grid_for(items, 256, kMaxBlocks), 256, 0, st>>>(d_images, frame_stride, row_stride, L0, batch, vec_ok);
+        ++launches;
+        for (int l = 1; l < nl; ++l) {
+            const LevelDev& D = e->T.lv[l];
+            const long long it = (long long)batch * D.rows * (D.pitch / 4);
+            k_resize<<<grid_for(it, 256, kMaxBlocks), 256, 0, st>>>(e->T.lv[l - 1], D, batch);
+            ++launches;
+        }
+    }
+    if (e->profiling) ORBX_CUDA(cudaEventRecord(e->ev[1], st));
+    /* stage 1 */
+    if (e->ncells > 0) {
+        k_fast_cells<<<dim3(e->ncells, batch), FAST_THREADS, 0, st>>>(e->T, e->d_cells, e->ncells, e->P.ini_th_fast,
+                                                                       e->P.min_th_fast, e->d_slots, e->slots_per_frame,
+                                                                       e->d_cell_count);
+        ++launches;
+    }
+    if (e->profiling) ORBX_CUDA(cudaEventRecord(e->ev[2], st));
+    /* stage 2 */
+    k_octree<<<dim3(nl, batch), OCT_THREADS, e->oct_smem, st>>>(e->T, e->d_cells, e->ncells, e->d_slots, e->slots_per_frame,
+                                                                 e->d_cell_count, e->d_cand, e->d_pnode, e->cand_per_frame,
+                                                                 e->d_cand_count, e->d_sel, e->sel_per_frame, e->d_sel_count,
+                                                                 e->maxn, e->max_cells_level);
+    ++launches;
+    if (e->profiling) ORBX_CUDA(cudaEventRecord(e->ev[3], st));
+    /* stage 3 */
+    k_order<<<batch, ORD_THREADS, 0, st>>>(e->T, e->d_sel, e->sel_per_frame, e->d_sel_count, d_lap, e->d_dest, e->d_nk,
+                                           e->d_nk + e->P.max_batch);
+    ++launches;
+    if (e->profiling) ORBX_CUDA(cudaEventRecord(e->ev[4], st));
+    /* stage 4 */
+    k_blur7<<<dim3(e->nblur_tiles, batch), 256, 0, st>>>(e->T, e->d_blur_tiles, batch);
+    ++launches;
+    if (e->profiling) ORBX_CUDA(cudaEventRecord(e->ev[5], st));
+    /* stage 5 */
+    {
+        UMax um;
+        for (int i = 0; i < 16; ++i) um.v[i] = e->umax[i];
+        k_orient_describe<<<dim3(orbx_div_up((int)e->sel_per_frame, 8), batch), 256, 0, st>>>(
+            e->T, um, e->d_sel, e->sel_per_frame, e->d_sel_count, e->d_dest, e->d_kps, e->d_desc, e->kcap);
+        ++launches;
+    }
+    if (e->profiling) ORBX_CUDA(cudaEventRecord(e->ev[6], st));
+    ORBX_CUDA(cudaGetLastError());
+    e->last_batch = batch;
+    e->last_launches = launches;
+    e->synced = false;
+    return ORBX_OK;
+}
+
+extern "C" orbx_status orbx_extract_host(orbx_extractor* e, const uint8_t* h_images, size_t frame_stride, int row_stride,
+                                         int batch, const int* lapping) {
+    if (!e) { orbx_set_error("null handle"); return ORBX_ERR_INVALID; }
+    if (!h_images) { orbx_set_error("empty image"); return ORBX_ERR_EMPTY; }
+    if (batch < 1 || batch > e->P.max_batch || row_stride < e->P.width) {
+        orbx_set_error("batch %d outside [1,%d] or row_stride < width", batch, e->P.max_batch);
+        return ORBX_ERR_INVALID;
+    }
+    ORBX_CUDA(cudaSetDevice(e->P.device));
+    const int w = e->P.width, h = e->P.height;
+    if (row_stride == w && frame_stride == (size_t)w * h) {
+        ORBX_CUDA(cudaMemcpyAsync(e->d_input, h_images, (size_t)batch * w * h, cudaMemcpyHostToDevice, e->stream));
+    } else {
+        for (int f = 0; f < batch; ++f)
+            ORBX_CUDA(cudaMemcpy2DAsync(e->d_input + (size_t)f * w * h, w, h_images + f * frame_stride, row_stride, w, h,
+                                        cudaMemcpyHostToDevice, e->stream));
+    }
+    return orbx_extract_device(e, e->d_input, (size_t)w * h, w, batch, lapping);
+}
+
+extern "C" orbx_status orbx_extractor_sync(orbx_extractor* e) {
+    if (!e || e->last_batch < 1) { orbx_set_error("nothing extracted"); return ORBX_ERR_INVALID; }
+    ORBX_CUDA(cudaSetDevice(e->P.device));
+    const int b = e->last_batch, mb = e->P.max_batch;
+    ORBX_CUDA(cudaMemcpyAsync(e->h_nk, e->d_nk, sizeof(int) * b, cudaMemcpyDeviceToHost, e->stream));
+    ORBX_CUDA(cudaMemcpyAsync(e->h_nk + mb, e->d_nk + mb, sizeof(int) * b, cudaMemcpyDeviceToHost, e->stream));
+    ORBX_CUDA(cudaMemcpyAsync(e->h_kps, e->d_kps, (size_t)b * e->kcap * sizeof(orbx_keypoint), cudaMemcpyDeviceToHost, e->stream));
+    ORBX_CUDA(cudaMemcpyAsync(e->h_desc, e->d_desc, (size_t)b * e->kcap * 32, cudaMemcpyDeviceToHost, e->stream));
+    ORBX_CUDA(cudaStreamSynchronize(e->stream));
+    e->synced = true;
+    return ORBX_OK;
+}
+
+extern "C" orbx_status orbx_extractor_counts(orbx_extractor* e, int* n, int* mono_index) {
+    if (!e || !e->synced) { orbx_set_error("call orbx_extractor_sync first"); return ORBX_ERR_INVALID; }
+    for (int f = 0; f < e->last_batch; ++f) {
+        if (n) n[f] = e->h_nk[f];
+        if (mono_index) mono_index[f] = e->h_nk[e->P.max_batch + f];
+    }
+    return ORBX_OK;
+}
+
+extern "C" orbx_status orbx_extractor_fetch(orbx_extractor* e, int f, orbx_keypoint* kps, uint8_t* desc, int cap, int* n,
+                                            int* mono_index) {
+    if (!e || !e->synced || f < 0 || f >= e->last_batch) { orbx_set_error("bad frame index or not synced"); return ORBX_ERR_INVALID; }
+    const int nk = e->h_nk[f];
+    if (n) *n = nk;
+    if (mono_index) *mono_index = e->h_nk[e->P.max_batch + f];
+    if (nk > cap) { orbx_set_error("capacity %d < %d keypoints", cap, nk); return ORBX_ERR_CAPACITY; }
+    if (kps) memcpy(kps, e->h_kps + (size_t)f * e->kcap, sizeof(orbx_keypoint) * nk);
+    if (desc) memcpy(desc, e->h_desc + (size_t)f * e->kcap * 32, (size_t)32 * nk);
+    return ORBX_OK;
+}
+
+extern "C" orbx_status orbx_extractor_level_size(const orbx_extractor* e, int level, int* w, int* h) {
+    if (!e || level < 0 || level >= e->nlevels) return ORBX_ERR_INVALID;
+    if (w) *w = e->lv[level].w;
+    if (h) *h = e->lv[level].h;
+    return ORBX_OK;
+}
+
+extern "C" orbx_status orbx_extractor_level_download(orbx_extractor* e, int f, int level, uint8_t* out) {
+    if (!e || level < 0 || level >= e->nlevels || f < 0 || f >= e->P.max_batch || !out) return ORBX_ERR_INVALID;
+    ORBX_CUDA(cudaSetDevice(e->P.device));
+    const LevelDev& L = e->lv[level];
+    ORBX_CUDA(cudaStreamSynchronize(e->stream));
+    ORBX_CUDA(cudaMemcpy2D(out, L.w + 2 * ORBX_EDGE, L.base + (size_t)f * L.frame_bytes + (ORBX_XOFF - ORBX_EDGE), L.pitch,
+                           L.w + 2 * ORBX_EDGE, L.rows, cudaMemcpyDeviceToHost));
+    return ORBX_OK;
+}
+
+extern "C" orbx_status orbx_extractor_blurred_download(orbx_extractor* e, int f, int level, uint8_t* out) {
+    if (!e || level < 0 || level >= e->nlevels || f < 0 || f >= e->P.max_batch || !out) return ORBX_ERR_INVALID;
+    ORBX_CUDA(cudaSetDevice(e->P.device));
+    const LevelDev& L = e->lv[level];
+    ORBX_CUDA(cudaStreamSynchronize(e->stream));
+    ORBX_CUDA(cudaMemcpy2D(out, L.w, L.blur + (size_t)f * L.bframe_bytes, L.bpitch, L.w, L.h, cudaMemcpyDeviceToHost));
+    return ORBX_OK;
+}
+
+extern "C" orbx_status orbx_extractor_candidates(orbx_extractor* e, int f, int level, int* xs, int* ys, int* resp, int cap,
+                                                 int* n) {
+    if (!e || level < 0 || level >= e->nlevels || f < 0 || f >= e->P.max_batch || !n) return ORBX_ERR_INVALID;
+    ORBX_CUDA(cudaSetDevice(e->P.device));
+    ORBX_CUDA(cudaStreamSynchronize(e->stream));
+    int cnt = 0;
+    ORBX_CUDA(cudaMemcpy(&cnt, e->d_cand_count + f * e->nlevels + level, 4, cudaMemcpyDeviceToHost));
+    *n = cnt;
+    if (cnt > cap) { orbx_set_error("capacity %d < %d candidates", cap, cnt); return ORBX_ERR_CAPACITY; }
+    std::vector<uint32_t> v(std::max(cnt, 1));
+    ORBX_CUDA(cudaMemcpy(v.data(), e->d_cand + (size_t)f * e->cand_per_frame + e->lv[level].cand_off, (size_t)cnt * 4,
+                         cudaMemcpyDeviceToHost));
+    for (int i = 0; i < cnt; ++i) { xs[i] = v[i] & 0xFFF; ys[i] = (v[i] >> 12) & 0xFFF; resp[i] = v[i] >> 24; }
+    return ORBX_OK;
+}
+
+extern "C" orbx_status orbx_extractor_stage_ms(orbx_extractor* e, float* ms6) {
+    if (!e || !ms6 || !e->profiling) { orbx_set_error("profiling is off"); return ORBX_ERR_INVALID; }
+    ORBX_CUDA(cudaEventSynchronize(e->ev[6]));
+    for (int i = 0; i < 6; ++i) ORBX_CUDA(cudaEventElapsedTime(&ms6[i], e->ev[i], e->ev[i + 1]));
+    return ORBX_OK;
+}
+
+/* ------------------------------------------------------------------ memory helpers */
+extern "C" orbx_status orbx_host_alloc(void** p, size_t bytes) { ORBX_CUDA(cudaMallocHost(p, bytes)); return ORBX_OK; }
+extern "C" void orbx_host_free(void* p) { if (p) cudaFreeHost(p); }
+extern "C" orbx_status orbx_device_alloc(int device, void** p, size_t bytes) {
+    ORBX_CUDA(cudaSetDevice(device));
+    ORBX_CUDA(cudaMalloc(p, bytes));
+    return ORBX_OK;
+}
+extern "C" void orbx_device_free(void* p) { if (p) cudaFree(p); }
+extern "C" orbx_status orbx_memcpy_h2d(void* d, const void* h, size_t bytes) { ORBX_CUDA(cudaMemcpy(d, h, bytes, cudaMemcpyHostToDevice)); return ORBX_OK; }
+extern "C" orbx_status orbx_memcpy_d2h(void* h, const void* d, size_t bytes) { ORBX_CUDA(cudaMemcpy(h, d, bytes, cudaMemcpyDeviceToHost)); return ORBX_OK; }
+extern "C" orbx_status orbx_device_synchronize(void) { ORBX_CUDA(cudaDeviceSynchronize()); return ORBX_OK; }

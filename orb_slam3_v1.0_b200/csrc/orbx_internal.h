@@ -1,0 +1,29 @@
+/* Internal definitions shared by the liborbx translation units (not part of the ABI). */
+#ifndef ORBX_INTERNAL_H
+#define ORBX_INTERNAL_H
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+#include "../../include/orbx.h"
+
+#define ORBX_EDGE 19        /* EDGE_THRESHOLD, upstream value */
+#define ORBX_XOFF 32        /* column of ROI x=0 inside a padded pyramid row (16B aligned) */
+#define ORBX_MINB 16        /* minBorderX/Y = EDGE_THRESHOLD-3 */
+#define ORBX_MAX_LEVELS 16
+
+void orbx_set_error(const char* fmt, ...);
+
+#define ORBX_CUDA(call)                                                                   \
+    do {                                                                                  \
+        cudaError_t _e = (call);                                                          \
+        if (_e != cudaSuccess) {                                                          \
+            orbx_set_error("%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(_e)); \
+            return ORBX_ERR_CUDA;                                                         \
+        }                                                                                 \
+    } while (0)
+
+static inline int orbx_div_up(int a, int b) { return (a + b - 1) / b; }
+static inline size_t orbx_align_up(size_t a, size_t b) { return (a + b - 1) / b * b; }
+
+#endif

@@ -1,0 +1,54 @@
+"""CPU-side checks of the product library: it builds, loads, and exports every symbol that
+include/orbx.h declares; without a GPU every compute entry fails loudly (no CPU fallback)."""
+import ctypes as C
+import os
+import re
+import subprocess
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def so(pkg):
+    return pkg.orbx.build()
+
+
+def test_exports_every_declared_symbol(so):
+    hdr = open(os.path.join(ROOT, "include", "orbx.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    names = set(re.findall(r"\b(orbx_[a-z0-9_]+)\s*\(", hdr))
+    assert len(names) >= 20
+    lib = C.CDLL(so)
+    missing = [n for n in sorted(names) if not hasattr(lib, n)]
+    assert not missing, missing
+
+
+def test_no_oracle_in_product():
+    """The product path must not link or import the oracle."""
+    out = subprocess.run(["ldd", os.path.join(ROOT, "orb_slam3_v1.0_b200", "lib", "liborbx.so")],
+                         capture_output=True, text=True).stdout
+    assert "oracle" not in out
+    for dp, _, fs in os.walk(os.path.join(ROOT, "orb_slam3_v1.0_b200")):
+        for f in fs:
+            if f.endswith((".py", ".cu", ".h", ".cuh")):
+                txt = open(os.path.join(dp, f)).read()
+                assert "orb_oracle" not in txt and "from oracle" not in txt and "import oracle" not in txt, f
+
+
+def test_fails_loudly_without_gpu(pkg, so):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    ex = pkg.orbx.ORBextractor()
+    with pytest.raises(pkg.orbx.OrbxError):
+        ex.prepare(752, 480, 1)
+
+
+def test_stdsort_emulation_matches_libstdcxx(tmp_path):
+    exe = str(tmp_path / "t")
+    subprocess.check_call(["g++", "-O2", "-std=c++17", "-o", exe, os.path.join(ROOT, "tests", "cpp", "test_stdsort.cpp")])
+    out = subprocess.run([exe], capture_output=True, text=True)
+    assert out.returncode == 0 and out.stdout.startswith("OK"), out.stdout

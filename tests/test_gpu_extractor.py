@@ -1,0 +1,116 @@
+"""GPU parity: CUDA extractor (through the C ABI) vs the CPU oracle on identical seeded
+synthetic frames.  Pyramid, FAST candidates, keypoint coordinates/octaves/responses and
+order: bit-exact.  Orientation: <= 1e-4 rad.  Descriptors: bit-exact except a documented
+cos/sin ULP allowance (<= 0.1% of descriptors, <= 2 bits each) -- BASELINE.json north_star."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+CONFIGS = [
+    # (w, h, nfeatures, nlevels, seed)
+    (752, 480, 1000, 8, 0xB200),      # EuRoC
+    (512, 512, 1500, 8, 7),           # TUM-VI
+    (1241, 376, 2000, 8, 11),         # KITTI
+    (320, 240, 300, 4, 3),
+]
+
+
+def _compare_frame(gex, oex, img, lapping, f=0, got=None):
+    ok, od, omono = oex(img, lapping)
+    gk, gd, gmono = got
+    assert len(gk) == len(ok), (len(gk), len(ok))
+    assert gmono == omono
+    for fld in ("x", "y", "size", "response", "octave", "class_id"):
+        assert np.array_equal(gk[fld], ok[fld]), fld
+    dang = np.abs(gk["angle"] - ok["angle"])
+    dang = np.minimum(dang, 360 - dang)
+    assert dang.max() <= np.degrees(1e-4)
+    bits = np.unpackbits(gd ^ od, axis=1).sum(1)
+    nbad = int((bits > 0).sum())
+    assert nbad <= max(1, int(0.001 * len(gk))) and bits.max() <= 2, (nbad, bits.max())
+    return nbad
+
+
+@pytest.mark.parametrize("w,h,nf,nl,seed", CONFIGS)
+def test_full_extraction_parity(pkg, oracle, synth, w, h, nf, nl, seed):
+    img = synth.textured_image(w, h, seed)
+    gex = pkg.orbx.ORBextractor(nf, 1.2, nl, 20, 7)
+    oex = oracle.Extractor(nf, 1.2, nl, 20, 7)
+    got = gex(img, (0, 0))
+    # tables
+    assert np.array_equal(gex.mvScaleFactor, oex.scale) and np.array_equal(gex.mvInvScaleFactor, oex.inv_scale)
+    assert np.array_equal(gex.mvLevelSigma2, oex.sigma2) and np.array_equal(gex.mvInvLevelSigma2, oex.inv_sigma2)
+    assert np.array_equal(gex.mnFeaturesPerLevel, oex.feat_per_level) and np.array_equal(gex.umax, oex.umax)
+    _compare_frame(gex, oex, img, (0, 0), got=got)
+    # stage-wise: pyramid (bordered), FAST candidates in reference order, blur
+    for l in range(nl):
+        assert np.array_equal(gex.image_pyramid(l), oex.level(l)), f"pyramid level {l}"
+        gx, gy, gr = gex.candidates(l)
+        ox, oy, orr = oex.candidates(l)
+        assert np.array_equal(gx, ox) and np.array_equal(gy, oy) and np.array_equal(gr, orr), f"candidates level {l}"
+        lv = oex.level(l)
+        assert np.array_equal(gex.blurred(l), oracle.gaussian7(lv[19:-19, 19:-19])), f"blur level {l}"
+    gex.close()
+
+
+def test_lapping_area_and_batch(pkg, oracle, synth):
+    """TUM-VI style: vLappingArea split, several frames per launch, per-frame lapping."""
+    w, h, B = 512, 512, 6
+    imgs = synth.frame_batch(B, w, h, seed=21, distinct=3)
+    laps = [(0, 0), (256, 511), (0, 255), (100, 300), (0, 1000), (511, 511)]
+    gex = pkg.orbx.ORBextractor(1500, 1.2, 8, 20, 7, max_batch=B)
+    oex = oracle.Extractor(1500, 1.2, 8, 20, 7)
+    res = gex.extract_batch(imgs, laps)
+    for f in range(B):
+        _compare_frame(gex, oex, imgs[f], laps[f], got=res[f])
+    gex.close()
+
+
+def test_low_texture_retry_and_blank(pkg, oracle, synth):
+    """Faint texture forces the per-cell minThFAST retry; a constant image yields zero keypoints."""
+    img = (synth.textured_image(400, 300, 3).astype(np.float32) * 0.12 + 100).astype(np.uint8)
+    gex = pkg.orbx.ORBextractor(500, 1.2, 4, 20, 7)
+    oex = oracle.Extractor(500, 1.2, 4, 20, 7)
+    _compare_frame(gex, oex, img, (0, 0), got=gex(img, (0, 0)))
+    blank = np.full((300, 400), 77, np.uint8)
+    k, d, mono = gex(blank, (0, 0))
+    assert len(k) == 0 and mono == 0
+    k, d, mono = gex(np.zeros((0, 0), np.uint8))
+    assert mono == -1 and k is None
+    gex.close()
+
+
+def test_noise_image_dense_candidates(pkg, oracle):
+    """Uniform noise: the densest FAST response the detector can produce (cell slot capacity)."""
+    rng = np.random.default_rng(99)
+    img = rng.integers(0, 256, size=(240, 320), dtype=np.uint8)
+    gex = pkg.orbx.ORBextractor(800, 1.2, 4, 20, 7)
+    oex = oracle.Extractor(800, 1.2, 4, 20, 7)
+    _compare_frame(gex, oex, img, (0, 0), got=gex(img, (0, 0)))
+    gex.close()
+
+
+def test_many_frames_property(pkg, oracle, synth):
+    """Larger batch: every frame equals the oracle; repeated launches are deterministic."""
+    w, h, B = 752, 480, 24
+    imgs = synth.frame_batch(B, w, h, seed=0xB200, distinct=6)
+    gex = pkg.orbx.ORBextractor(1000, 1.2, 8, 20, 7, max_batch=B)
+    oex = oracle.Extractor(1000, 1.2, 8, 20, 7)
+    r1 = gex.extract_batch(imgs)
+    r2 = gex.extract_batch(imgs)
+    for f in range(B):
+        assert np.array_equal(r1[f][0], r2[f][0]) and np.array_equal(r1[f][1], r2[f][1])
+    for f in range(0, B, 3):
+        _compare_frame(gex, oex, imgs[f], (0, 0), got=r1[f])
+    gex.close()
+
+
+def test_hamming_pairs(pkg, oracle):
+    rng = np.random.default_rng(5)
+    a = rng.integers(0, 256, size=(5000, 32), dtype=np.uint8)
+    b = rng.integers(0, 256, size=(5000, 32), dtype=np.uint8)
+    b[:10] = a[:10]; b[10] = ~a[10]
+    got = pkg.orbx.hamming_pairs(a, b)
+    assert np.array_equal(got, oracle.hamming_pairs(a, b))
+    assert got[:10].max() == 0 and got[10] == 256
