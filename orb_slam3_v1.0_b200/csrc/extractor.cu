@@ -61,7 +61,7 @@ struct LevelDev {
 struct Cell {
     short level, x0, y0, cw, ch, offx, offy, pad;
     int slot_off;           /* into the per-frame candidate-slot array */
-    int idx_in_level;
+    unsigned rcp_dw;        /* floor(2^32/(cw-6))+1: exact i/(cw-6) by __umulhi for i < 2^16 */
 };
 
 struct Tables {
@@ -152,9 +152,20 @@ __global__ void __launch_bounds__(256) k_resize(LevelDev S, LevelDev D, int batc
 }
 
 /* ================================================================== stage 1: FAST per cell */
-#define FAST_TP 80            /* smem tile pitch; cells are at most 69+6 wide (checked on host) */
+/* One CTA per 35-px FAST cell.  The cell sub-image is staged in shared memory
+ * with aligned 32-bit loads; three phases keep the warps dense:
+ *   A  every detection pixel: 2 opposite-pair quick reject (any 9-arc of the ring contains one
+ *      pixel of each opposite pair) -> warp-aggregated compaction of the ~30% survivors
+ *   B  survivors only: 16-ring bright/dark masks at minThFAST, 9-contiguity by bit tricks, score
+ *      = (max over arcs of the min |difference|) - 1  == cv::FAST cornerScore
+ *   C  strict 3x3 local maxima of the score map (margin reads 0 = OpenCV's zeroed score rows),
+ *      iniThFAST survivors if any else minThFAST ones, written in raster order at fixed slots.
+ * A corner at threshold t has score >= t, so NMS at iniThFAST = local maxima with score >= ini
+ * of the minThFAST score map: one score pass serves both thresholds. */
+#define FAST_TP 80            /* smem tile pitch (bytes); cells are at most 69+6 wide (+3 align) */
 #define FAST_TH 80
 #define FAST_THREADS 128
+#define FAST_LIST 4800
 
 __device__ __forceinline__ bool has9(uint32_t m) {
     m |= m << 16;
@@ -165,24 +176,17 @@ __device__ __forceinline__ bool has9(uint32_t m) {
     return (a & 0xFFFFu) != 0;
 }
 
-/* A = max over 9-arcs of min(d) for the bright test and of min(-d) for the dark test
- * (cornerScore, reference src/cuda/Fast_gpu.cu:193-216, equals A-1). */
-__device__ __forceinline__ int arc_strength(const int* d) {
-    int best = -512;
+/* max over the 16 arcs of 9 contiguous ring values of min(e) */
+__device__ __forceinline__ int arc_strength(const int* e) {
+    int m2[16], m4[16], m8[16], best = -512;
 #pragma unroll
-    for (int sgn = 0; sgn < 2; ++sgn) {
-        int e[16], m2[16], m4[16], m8[16];
+    for (int k = 0; k < 16; ++k) m2[k] = min(e[k], e[(k + 1) & 15]);
 #pragma unroll
-        for (int k = 0; k < 16; ++k) e[k] = sgn ? -d[k] : d[k];
+    for (int k = 0; k < 16; ++k) m4[k] = min(m2[k], m2[(k + 2) & 15]);
 #pragma unroll
-        for (int k = 0; k < 16; ++k) m2[k] = min(e[k], e[(k + 1) & 15]);
+    for (int k = 0; k < 16; ++k) m8[k] = min(m4[k], m4[(k + 4) & 15]);
 #pragma unroll
-        for (int k = 0; k < 16; ++k) m4[k] = min(m2[k], m2[(k + 2) & 15]);
-#pragma unroll
-        for (int k = 0; k < 16; ++k) m8[k] = min(m4[k], m4[(k + 4) & 15]);
-#pragma unroll
-        for (int k = 0; k < 16; ++k) best = max(best, min(m8[k], e[(k + 8) & 15]));
-    }
+    for (int k = 0; k < 16; ++k) best = max(best, min(m8[k], e[(k + 8) & 15]));
     return best;
 }
 
@@ -190,33 +194,66 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(Tables T, const Cel
                                                               int ncells, int ini_th, int min_th,
                                                               uint32_t* __restrict__ slots, size_t slots_per_frame,
                                                               int* __restrict__ cell_count) {
-    __shared__ uint8_t tile[FAST_TH * FAST_TP];
-    __shared__ uint8_t score[FAST_TH * FAST_TP];
-    __shared__ int s_warp[FAST_THREADS / 32];
-    __shared__ int s_base;
+    __shared__ __align__(16) uint8_t tile[FAST_TH * FAST_TP];
+    __shared__ __align__(16) uint8_t score[FAST_TH * FAST_TP];
+    __shared__ unsigned short list[FAST_LIST];
+    __shared__ int s_n;
+    __shared__ int s_c1[FAST_THREADS / 32], s_c2[FAST_THREADS / 32];
 
     const int f = blockIdx.y;
     const Cell c = cells[blockIdx.x];
     const LevelDev& L = T.lv[c.level];
     const int cw = c.cw, ch = c.ch;
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int shift = c.x0 & 3;                   /* tile column of sub-image x=0 */
 
-    /* load the cell sub-image; rows are contiguous in global memory */
-    const uint8_t* src = lv_ptr(L, f, c.x0, c.y0);
-    for (int i = tid; i < ch * cw; i += FAST_THREADS) {
-        const int y = i / cw, x = i - y * cw;
-        tile[y * FAST_TP + x] = __ldg(src + (size_t)y * L.pitch + x);
+    /* stage the sub-image: warp per row, lane per aligned 32-bit word */
+    {
+        const int nwords = (cw + shift + 3) >> 2;
+        const uint8_t* src = lv_ptr(L, f, c.x0 - shift, c.y0);
+        for (int y = wid; y < ch; y += FAST_THREADS / 32)
+            if (lane < nwords)
+                reinterpret_cast<uint32_t*>(tile + y * FAST_TP)[lane] =
+                    __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)y * L.pitch) + lane);
+        for (int i = tid; i < ch * (FAST_TP / 4); i += FAST_THREADS) reinterpret_cast<uint32_t*>(score)[i] = 0;
+        if (tid == 0) s_n = 0;
     }
     __syncthreads();
 
     const int dw = cw - 6, dh = ch - 6;          /* detection area (3-px margin) */
     const int npix = (dw > 0 && dh > 0) ? dw * dh : 0;
-    /* pass 1: score map at min_th (0 = not a corner); border of the score tile = 0 */
-    for (int i = tid; i < ch * cw; i += FAST_THREADS) score[(i / cw) * FAST_TP + (i % cw)] = 0;
+    const unsigned rcp = c.rcp_dw;
+
+    /* ---- phase A: quick reject + compaction */
+    for (int base = 0; base < npix; base += FAST_THREADS) {
+        const int i = base + tid;
+        bool pass = false;
+        int idx = 0;
+        if (i < npix) {
+            const int y = (int)__umulhi((unsigned)i, rcp);
+            const int x = i - y * dw;
+            idx = (y + 3) * FAST_TP + x + 3 + shift;
+            const uint8_t* p = tile + idx;
+            const int v = p[0];
+            const int d0 = abs((int)p[3 * FAST_TP] - v), d8 = abs((int)p[-3 * FAST_TP] - v);
+            const int d4 = abs((int)p[3] - v), d12 = abs((int)p[-3] - v);
+            pass = !((d0 <= min_th && d8 <= min_th) || (d4 <= min_th && d12 <= min_th));
+        }
+        const unsigned bal = __ballot_sync(0xffffffffu, pass);
+        if (bal) {
+            int b = 0;
+            if (lane == 0) b = atomicAdd(&s_n, __popc(bal));
+            b = __shfl_sync(0xffffffffu, b, 0);
+            if (pass) list[b + __popc(bal & ((1u << lane) - 1))] = (unsigned short)idx;
+        }
+    }
     __syncthreads();
-    for (int i = tid; i < npix; i += FAST_THREADS) {
-        const int y = i / dw + 3, x = i - (y - 3) * dw + 3;
-        const uint8_t* p = tile + y * FAST_TP + x;
+
+    /* ---- phase B: exact test + score for the survivors */
+    const int nsurv = s_n;
+    for (int j = tid; j < nsurv; j += FAST_THREADS) {
+        const int idx = list[j];
+        const uint8_t* p = tile + idx;
         const int v = p[0];
         int d[16];
         d[0] = p[3 * FAST_TP];          d[1] = p[3 * FAST_TP + 1];   d[2] = p[2 * FAST_TP + 2];  d[3] = p[FAST_TP + 3];
@@ -230,66 +267,66 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(Tables T, const Cel
             mb |= (d[k] > min_th ? 1u : 0u) << k;
             md |= (d[k] < -min_th ? 1u : 0u) << k;
         }
-        if (has9(mb) || has9(md)) {
-            const int A = arc_strength(d);           /* A > min_th here */
-            score[y * FAST_TP + x] = (uint8_t)(A - 1);
+        const bool bright = has9(mb), dark = has9(md);   /* mutually exclusive (9+9 > 16) */
+        if (bright || dark) {
+            if (dark) {
+#pragma unroll
+                for (int k = 0; k < 16; ++k) d[k] = -d[k];
+            }
+            score[idx] = (uint8_t)(arc_strength(d) - 1);   /* strength > min_th >= 1 */
         }
     }
     __syncthreads();
 
-    /* pass 2: strict local maxima of the min_th score map.  A corner at threshold t has
-     * score >= t, so NMS at ini_th = {local maxima with score >= ini_th}: neighbours that are
-     * corners only at min_th have smaller scores and cannot suppress it either way. */
-    int cnt_ini = 0;
-    for (int base = 0; base < npix; base += FAST_THREADS) {
-        const int i = base + tid;
+    /* ---- phase C: NMS + ordered output.  Warp w owns a contiguous raster segment. */
+    const int seg = (((npix + FAST_THREADS / 32 - 1) / (FAST_THREADS / 32)) + 31) & ~31;
+    const int beg = wid * seg, end = min(beg + seg, npix);
+    int c1 = 0, c2 = 0;
+    for (int base = beg; base < end; base += 32) {
+        const int i = base + lane;
         int keep = 0;
-        if (i < npix) {
-            const int y = i / dw + 3, x = i - (y - 3) * dw + 3;
-            const uint8_t* s = score + y * FAST_TP + x;
+        if (i < end) {
+            const int y = (int)__umulhi((unsigned)i, rcp);
+            const int x = i - y * dw;
+            const int idx = (y + 3) * FAST_TP + x + 3 + shift;
+            const uint8_t* s = score + idx;
             const int v = s[0];
-            /* neighbours outside the detection area read 0 from the zeroed margin */
             if (v > 0 && v > s[-1] && v > s[1] && v > s[-FAST_TP - 1] && v > s[-FAST_TP] && v > s[-FAST_TP + 1] &&
                 v > s[FAST_TP - 1] && v > s[FAST_TP] && v > s[FAST_TP + 1])
                 keep = (v >= ini_th) ? 2 : 1;
-            if (keep) tile[y * FAST_TP + x] = (uint8_t)keep;   /* reuse tile as the flag map */
-            else tile[y * FAST_TP + x] = 0;
+            tile[idx] = (uint8_t)keep;            /* the image tile is dead after phase B */
         }
-        cnt_ini += (keep == 2);
+        c1 += __popc(__ballot_sync(0xffffffffu, keep >= 1));
+        c2 += __popc(__ballot_sync(0xffffffffu, keep == 2));
     }
-    const int any_ini = __syncthreads_or(cnt_ini);
-    const int need = any_ini ? 2 : 1;            /* per-cell retry with minThFAST */
-
-    /* pass 3: ordered (raster) compaction */
-    uint32_t* out = slots + (size_t)f * slots_per_frame + c.slot_off;
-    if (tid == 0) s_base = 0;
+    if (lane == 0) { s_c1[wid] = c1; s_c2[wid] = c2; }
     __syncthreads();
-    for (int base = 0; base < npix; base += FAST_THREADS) {
-        const int i = base + tid;
-        int keep = 0, x = 0, y = 0;
-        if (i < npix) {
-            y = i / dw + 3; x = i - (y - 3) * dw + 3;
-            keep = tile[y * FAST_TP + x] >= need;
+    int tot1 = 0, tot2 = 0, off1 = 0, off2 = 0;
+#pragma unroll
+    for (int w = 0; w < FAST_THREADS / 32; ++w) {
+        if (w < wid) { off1 += s_c1[w]; off2 += s_c2[w]; }
+        tot1 += s_c1[w]; tot2 += s_c2[w];
+    }
+    const int need = tot2 > 0 ? 2 : 1;            /* per-cell retry with minThFAST */
+    int off = need == 2 ? off2 : off1;
+    uint32_t* out = slots + (size_t)f * slots_per_frame + c.slot_off;
+    for (int base = beg; base < end; base += 32) {
+        const int i = base + lane;
+        bool keep = false;
+        int x = 0, y = 0, idx = 0;
+        if (i < end) {
+            y = (int)__umulhi((unsigned)i, rcp);
+            x = i - y * dw;
+            idx = (y + 3) * FAST_TP + x + 3 + shift;
+            keep = tile[idx] >= need;
         }
         const unsigned bal = __ballot_sync(0xffffffffu, keep);
-        const int lane = tid & 31, wid = tid >> 5;
-        if (lane == 0) s_warp[wid] = __popc(bal);
-        __syncthreads();
-        int off = s_base;
-        for (int w = 0; w < wid; ++w) off += s_warp[w];
-        if (keep) {
-            off += __popc(bal & ((1u << lane) - 1));
-            out[off] = (uint32_t)(x + c.offx) | ((uint32_t)(y + c.offy) << 12) | ((uint32_t)score[y * FAST_TP + x] << 24);
-        }
-        __syncthreads();
-        if (tid == 0) {
-            int tot = 0;
-            for (int w = 0; w < FAST_THREADS / 32; ++w) tot += s_warp[w];
-            s_base += tot;
-        }
-        __syncthreads();
+        if (keep)
+            out[off + __popc(bal & ((1u << lane) - 1))] =
+                (uint32_t)(x + 3 + c.offx) | ((uint32_t)(y + 3 + c.offy) << 12) | ((uint32_t)score[idx] << 24);
+        off += __popc(bal);
     }
-    if (tid == 0) cell_count[(size_t)f * ncells + blockIdx.x] = s_base;
+    if (tid == 0) cell_count[(size_t)f * ncells + blockIdx.x] = need == 2 ? tot2 : tot1;
 }
 
 /* ================================================================== stage 2: quadtree */
@@ -373,7 +410,7 @@ __global__ void __launch_bounds__(OCT_THREADS) k_octree(Tables T, const Cell* __
                                                          int* __restrict__ sel_count, int maxn, int max_cells) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ int s_tmp[OCT_THREADS / 32 + 1];
-    __shared__ int s_L, s_nE, s_T, s_CT;
+    __shared__ int s_T, s_CT;
 
     const int level = blockIdx.x, f = blockIdx.y, tid = threadIdx.x;
     const LevelDev& Lv = T.lv[level];
@@ -991,13 +1028,13 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
                     c.cw = (short)((int)maxX - (int)iniX); c.ch = (short)((int)maxY - (int)iniY);
                     c.offx = (short)(j * wCell); c.offy = (short)(i * hCell); c.pad = 0;
                     c.slot_off = (int)slot_off;
-                    c.idx_in_level = (int)e->cells.size() - L.cell_begin;
                     if (c.cw > FAST_TP || c.ch > FAST_TH) {
                         orbx_set_error("FAST cell %dx%d exceeds the %d-px tile", c.cw, c.ch, FAST_TP);
                         free_all(e);
                         return ORBX_ERR_INVALID;
                     }
                     const int dw = c.cw - 6, dh = c.ch - 6;
+                    c.rcp_dw = dw > 0 ? (unsigned)((1ull << 32) / (unsigned)dw) + 1u : 0u;
                     const int cap = (dw > 0 && dh > 0) ? ((dw + 1) / 2) * ((dh + 1) / 2) : 0;  /* NMS survivors are never 8-adjacent */
                     slot_off += cap;
                     cand_off += cap;
