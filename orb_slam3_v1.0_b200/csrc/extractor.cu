@@ -162,10 +162,8 @@ __global__ void __launch_bounds__(256) k_resize(LevelDev S, LevelDev D, int batc
  *      iniThFAST survivors if any else minThFAST ones, written in raster order at fixed slots.
  * A corner at threshold t has score >= t, so NMS at iniThFAST = local maxima with score >= ini
  * of the minThFAST score map: one score pass serves both thresholds. */
-#define FAST_TP 80            /* smem tile pitch (bytes); cells are at most 69+6 wide (+3 align) */
-#define FAST_TH 80
+#define FAST_MAX_CELL 76      /* cells are at most 69+6 px (nCols==1 levels); tile pitch = cell width + alignment */
 #define FAST_THREADS 128
-#define FAST_LIST 4800
 
 __device__ __forceinline__ bool has9(uint32_t m) {
     m |= m << 16;
@@ -190,15 +188,26 @@ __device__ __forceinline__ int arc_strength(const int* e) {
     return best;
 }
 
+/* per-byte "a > th" for 4 packed u8 (th <= 127): bit 7 of each byte of the result */
+__device__ __forceinline__ uint32_t gt4(uint32_t d, uint32_t k7f_minus_th) {
+    return (((d & 0x7f7f7f7fu) + k7f_minus_th) | d) & 0x80808080u;
+}
+
 __global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(Tables T, const Cell* __restrict__ cells,
                                                               int ncells, int ini_th, int min_th,
                                                               uint32_t* __restrict__ slots, size_t slots_per_frame,
-                                                              int* __restrict__ cell_count) {
-    __shared__ __align__(16) uint8_t tile[FAST_TH * FAST_TP];
-    __shared__ __align__(16) uint8_t score[FAST_TH * FAST_TP];
-    __shared__ unsigned short list[FAST_LIST];
-    __shared__ int s_n;
-    __shared__ int s_c1[FAST_THREADS / 32], s_c2[FAST_THREADS / 32];
+                                                              int* __restrict__ cell_count, int tp, int rows, int list_cap) {
+    /* dynamic smem: tile | score | flag (rows x tp bytes each) | list | clist (list_cap u16 each) */
+    extern __shared__ __align__(16) uint8_t fsm[];
+    const int WP = tp >> 2;                       /* tile pitch in words */
+    const int map_bytes = rows * tp;
+    uint8_t* tile = fsm;
+    uint8_t* score = fsm + map_bytes;
+    uint8_t* flag = fsm + 2 * map_bytes;
+    unsigned short* list = reinterpret_cast<unsigned short*>(fsm + 3 * map_bytes);
+    unsigned short* clist = list + list_cap;
+    __shared__ int s_n, s_nc;
+    __shared__ int s_cnt[FAST_THREADS / 32];
 
     const int f = blockIdx.y;
     const Cell c = cells[blockIdx.x];
@@ -206,127 +215,191 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(Tables T, const Cel
     const int cw = c.cw, ch = c.ch;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int shift = c.x0 & 3;                   /* tile column of sub-image x=0 */
+    const int nwords = (cw + shift + 3) >> 2;     /* <= tp/4 */
+    const unsigned rcp_nw = 0xFFFFFFFFu / (unsigned)nwords + 1u;
+    uint32_t* tile32 = reinterpret_cast<uint32_t*>(tile);
+    uint32_t* flag32 = reinterpret_cast<uint32_t*>(flag);
 
-    /* stage the sub-image: warp per row, lane per aligned 32-bit word */
+    /* stage the sub-image with aligned 32-bit loads; zero score + flag maps */
     {
-        const int nwords = (cw + shift + 3) >> 2;
         const uint8_t* src = lv_ptr(L, f, c.x0 - shift, c.y0);
-        for (int y = wid; y < ch; y += FAST_THREADS / 32)
-            if (lane < nwords)
-                reinterpret_cast<uint32_t*>(tile + y * FAST_TP)[lane] =
-                    __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)y * L.pitch) + lane);
-        for (int i = tid; i < ch * (FAST_TP / 4); i += FAST_THREADS) reinterpret_cast<uint32_t*>(score)[i] = 0;
-        if (tid == 0) s_n = 0;
+        const int nitems = ch * nwords;
+        for (int i = tid; i < nitems; i += FAST_THREADS) {
+            const int y = (int)__umulhi((unsigned)i, rcp_nw);
+            const int wc = i - y * nwords;
+            tile32[y * WP + wc] = __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)y * L.pitch) + wc);
+        }
+        for (int i = tid; i < ch * WP; i += FAST_THREADS) {
+            reinterpret_cast<uint32_t*>(score)[i] = 0;
+            flag32[i] = 0;
+        }
+        if (tid == 0) { s_n = 0; s_nc = 0; }
     }
     __syncthreads();
 
     const int dw = cw - 6, dh = ch - 6;          /* detection area (3-px margin) */
-    const int npix = (dw > 0 && dh > 0) ? dw * dh : 0;
-    const unsigned rcp = c.rcp_dw;
+    const int nitems = (dw > 0 && dh > 0) ? dh * nwords : 0;   /* words covering the detection rows */
+    const int tlo = 3 + shift, thi = cw - 3 + shift;            /* valid tile columns [tlo, thi) */
+    const uint32_t k7f = 0x7f7f7f7fu - (uint32_t)min_th * 0x01010101u;
 
-    /* ---- phase A: quick reject + compaction */
-    for (int base = 0; base < npix; base += FAST_THREADS) {
+    /* ---- phase A: 4 pixels per thread, opposite-pair quick reject, compaction of survivors */
+    for (int base = 0; base < nitems; base += FAST_THREADS) {
         const int i = base + tid;
-        bool pass = false;
+        uint32_t pass = 0;
+        int widx = 0;
+        if (i < nitems) {
+            const int y = (int)__umulhi((unsigned)i, rcp_nw);
+            const int wc = i - y * nwords;
+            widx = (y + 3) * WP + wc;
+            const uint32_t v4 = tile32[widx];
+            const uint32_t up = tile32[widx - 3 * WP], dn = tile32[widx + 3 * WP];
+            const uint32_t lw = tile32[widx - (wc > 0)], rw = tile32[widx + (wc < WP - 1)];
+            const uint32_t l4 = __funnelshift_r(lw, v4, 8);     /* bytes at column-3 */
+            const uint32_t r4 = __funnelshift_r(v4, rw, 24);    /* bytes at column+3 */
+            const uint32_t g0 = gt4(__vabsdiffu4(dn, v4), k7f), g8 = gt4(__vabsdiffu4(up, v4), k7f);
+            const uint32_t g4 = gt4(__vabsdiffu4(r4, v4), k7f), g12 = gt4(__vabsdiffu4(l4, v4), k7f);
+            pass = (g0 | g8) & (g4 | g12);
+            /* mask bytes outside [tlo, thi) */
+            const int lo = max(tlo - 4 * wc, 0), hi = min(thi - 4 * wc, 4);
+            const uint32_t vm = (hi > lo) ? ((0xFFFFFFFFu >> (8 * (4 - hi))) & (0xFFFFFFFFu << (8 * lo))) : 0u;
+            pass &= vm;
+        }
+        const int n = __popc(pass);
+        int inc = n;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        const int wtot = __shfl_sync(0xffffffffu, inc, 31);
+        if (wtot) {
+            int b = 0;
+            if (lane == 31) b = atomicAdd(&s_n, wtot);
+            b = __shfl_sync(0xffffffffu, b, 31) + inc - n;
+            uint32_t m = pass;
+            while (m) {
+                const int bit = __ffs(m) - 1;        /* 7, 15, 23 or 31 */
+                m &= m - 1;
+                list[b++] = (unsigned short)(widx * 4 + (bit >> 3));
+            }
+        }
+    }
+    __syncthreads();
+
+    /* ---- phase B: exact FAST-9 test + score for the survivors */
+    const int nsurv = s_n;
+    for (int base = 0; base < nsurv; base += FAST_THREADS) {
+        const int j = base + tid;
+        bool corner = false;
         int idx = 0;
-        if (i < npix) {
-            const int y = (int)__umulhi((unsigned)i, rcp);
-            const int x = i - y * dw;
-            idx = (y + 3) * FAST_TP + x + 3 + shift;
+        if (j < nsurv) {
+            idx = list[j];
             const uint8_t* p = tile + idx;
             const int v = p[0];
-            const int d0 = abs((int)p[3 * FAST_TP] - v), d8 = abs((int)p[-3 * FAST_TP] - v);
-            const int d4 = abs((int)p[3] - v), d12 = abs((int)p[-3] - v);
-            pass = !((d0 <= min_th && d8 <= min_th) || (d4 <= min_th && d12 <= min_th));
+            /* one IMAD per ring pixel: upper half = (v+th) - r  (negative <=> brighter),
+             * lower half = r - (v-th) (negative <=> darker); a borrow from the lower half can
+             * only happen when r < v-th, where the upper half is >= 2*th+1 and stays positive */
+            const int C = ((v + min_th) << 16) - (v - min_th);
+            uint32_t acc = 0;
+#define FAST_RING(OFF) acc = (acc >> 1) | ((uint32_t)(C - 65535 * (int)p[OFF]) & 0x80008000u)
+            FAST_RING(3 * tp);      FAST_RING(3 * tp + 1);   FAST_RING(2 * tp + 2);   FAST_RING(tp + 3);
+            FAST_RING(3);           FAST_RING(-tp + 3);      FAST_RING(-2 * tp + 2);  FAST_RING(-3 * tp + 1);
+            FAST_RING(-3 * tp);     FAST_RING(-3 * tp - 1);  FAST_RING(-2 * tp - 2);  FAST_RING(-tp - 3);
+            FAST_RING(-3);          FAST_RING(tp - 3);       FAST_RING(2 * tp - 2);   FAST_RING(3 * tp - 1);
+#undef FAST_RING
+            const bool bright = has9(acc >> 16), dark = has9(acc & 0xFFFFu);   /* mutually exclusive */
+            if (bright || dark) {
+                corner = true;
+                const int sgn = dark ? -1 : 1;
+                int e[16];
+                e[0] = p[3 * tp];          e[1] = p[3 * tp + 1];   e[2] = p[2 * tp + 2];   e[3] = p[tp + 3];
+                e[4] = p[3];               e[5] = p[-tp + 3];      e[6] = p[-2 * tp + 2];  e[7] = p[-3 * tp + 1];
+                e[8] = p[-3 * tp];         e[9] = p[-3 * tp - 1];  e[10] = p[-2 * tp - 2]; e[11] = p[-tp - 3];
+                e[12] = p[-3];             e[13] = p[tp - 3];      e[14] = p[2 * tp - 2];  e[15] = p[3 * tp - 1];
+#pragma unroll
+                for (int k = 0; k < 16; ++k) e[k] = sgn * (e[k] - v);
+                score[idx] = (uint8_t)(arc_strength(e) - 1);   /* strength > min_th >= 1 */
+            }
         }
-        const unsigned bal = __ballot_sync(0xffffffffu, pass);
+        const unsigned bal = __ballot_sync(0xffffffffu, corner);
         if (bal) {
             int b = 0;
-            if (lane == 0) b = atomicAdd(&s_n, __popc(bal));
+            if (lane == 0) b = atomicAdd(&s_nc, __popc(bal));
             b = __shfl_sync(0xffffffffu, b, 0);
-            if (pass) list[b + __popc(bal & ((1u << lane) - 1))] = (unsigned short)idx;
+            if (corner) clist[b + __popc(bal & ((1u << lane) - 1))] = (unsigned short)idx;
         }
     }
     __syncthreads();
 
-    /* ---- phase B: exact test + score for the survivors */
-    const int nsurv = s_n;
-    for (int j = tid; j < nsurv; j += FAST_THREADS) {
-        const int idx = list[j];
-        const uint8_t* p = tile + idx;
-        const int v = p[0];
-        int d[16];
-        d[0] = p[3 * FAST_TP];          d[1] = p[3 * FAST_TP + 1];   d[2] = p[2 * FAST_TP + 2];  d[3] = p[FAST_TP + 3];
-        d[4] = p[3];                    d[5] = p[-FAST_TP + 3];      d[6] = p[-2 * FAST_TP + 2]; d[7] = p[-3 * FAST_TP + 1];
-        d[8] = p[-3 * FAST_TP];         d[9] = p[-3 * FAST_TP - 1];  d[10] = p[-2 * FAST_TP - 2]; d[11] = p[-FAST_TP - 3];
-        d[12] = p[-3];                  d[13] = p[FAST_TP - 3];      d[14] = p[2 * FAST_TP - 2]; d[15] = p[3 * FAST_TP - 1];
-        uint32_t mb = 0, md = 0;
-#pragma unroll
-        for (int k = 0; k < 16; ++k) {
-            d[k] -= v;
-            mb |= (d[k] > min_th ? 1u : 0u) << k;
-            md |= (d[k] < -min_th ? 1u : 0u) << k;
-        }
-        const bool bright = has9(mb), dark = has9(md);   /* mutually exclusive (9+9 > 16) */
-        if (bright || dark) {
-            if (dark) {
-#pragma unroll
-                for (int k = 0; k < 16; ++k) d[k] = -d[k];
-            }
-            score[idx] = (uint8_t)(arc_strength(d) - 1);   /* strength > min_th >= 1 */
+    /* ---- phase C1: strict 3x3 local maxima among the corners -> flag map (1 = keep at
+     * minThFAST, 2 = keep at iniThFAST too).  Margin/non-corner scores read 0. */
+    const int ncorn = s_nc;
+    int my2 = 0;
+    for (int j = tid; j < ncorn; j += FAST_THREADS) {
+        const int idx = clist[j];
+        const uint8_t* s = score + idx;
+        const int v = s[0];
+        if (v > s[-1] && v > s[1] && v > s[-tp - 1] && v > s[-tp] && v > s[-tp + 1] &&
+            v > s[tp - 1] && v > s[tp] && v > s[tp + 1]) {
+            const int k = (v >= ini_th) ? 2 : 1;
+            flag[idx] = (uint8_t)k;
+            my2 |= (k == 2);
         }
     }
-    __syncthreads();
+    const int need = __syncthreads_or(my2) ? 2 : 1;      /* per-cell retry with minThFAST */
 
-    /* ---- phase C: NMS + ordered output.  Warp w owns a contiguous raster segment. */
-    const int seg = (((npix + FAST_THREADS / 32 - 1) / (FAST_THREADS / 32)) + 31) & ~31;
-    const int beg = wid * seg, end = min(beg + seg, npix);
-    int c1 = 0, c2 = 0;
-    for (int base = beg; base < end; base += 32) {
-        const int i = base + lane;
-        int keep = 0;
-        if (i < end) {
-            const int y = (int)__umulhi((unsigned)i, rcp);
-            const int x = i - y * dw;
-            const int idx = (y + 3) * FAST_TP + x + 3 + shift;
-            const uint8_t* s = score + idx;
-            const int v = s[0];
-            if (v > 0 && v > s[-1] && v > s[1] && v > s[-FAST_TP - 1] && v > s[-FAST_TP] && v > s[-FAST_TP + 1] &&
-                v > s[FAST_TP - 1] && v > s[FAST_TP] && v > s[FAST_TP + 1])
-                keep = (v >= ini_th) ? 2 : 1;
-            tile[idx] = (uint8_t)keep;            /* the image tile is dead after phase B */
-        }
-        c1 += __popc(__ballot_sync(0xffffffffu, keep >= 1));
-        c2 += __popc(__ballot_sync(0xffffffffu, keep == 2));
+    /* ---- phase C2/C3: ordered (raster) output; warp w owns a contiguous range of flag words */
+    const int seg = (((nitems + FAST_THREADS / 32 - 1) / (FAST_THREADS / 32)) + 31) & ~31;
+    const int beg = wid * seg, end = min(beg + seg, nitems);
+    int cnt = 0;
+    for (int i = beg + lane; i < end; i += 32) {
+        const int y = (int)__umulhi((unsigned)i, rcp_nw);
+        const uint32_t f4 = flag32[(y + 3) * WP + (i - y * nwords)];
+        cnt += __popc(need == 2 ? (f4 & 0x02020202u) : ((f4 | (f4 >> 1)) & 0x01010101u));
     }
-    if (lane == 0) { s_c1[wid] = c1; s_c2[wid] = c2; }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+    if (lane == 0) s_cnt[wid] = cnt;
     __syncthreads();
-    int tot1 = 0, tot2 = 0, off1 = 0, off2 = 0;
+    int off = 0, tot = 0;
 #pragma unroll
     for (int w = 0; w < FAST_THREADS / 32; ++w) {
-        if (w < wid) { off1 += s_c1[w]; off2 += s_c2[w]; }
-        tot1 += s_c1[w]; tot2 += s_c2[w];
+        if (w < wid) off += s_cnt[w];
+        tot += s_cnt[w];
     }
-    const int need = tot2 > 0 ? 2 : 1;            /* per-cell retry with minThFAST */
-    int off = need == 2 ? off2 : off1;
     uint32_t* out = slots + (size_t)f * slots_per_frame + c.slot_off;
-    for (int base = beg; base < end; base += 32) {
-        const int i = base + lane;
-        bool keep = false;
-        int x = 0, y = 0, idx = 0;
-        if (i < end) {
-            y = (int)__umulhi((unsigned)i, rcp);
-            x = i - y * dw;
-            idx = (y + 3) * FAST_TP + x + 3 + shift;
-            keep = tile[idx] >= need;
+    if (cnt) {
+        for (int base = beg; base < end; base += 32) {
+            const int i = base + lane;
+            uint32_t k4 = 0;
+            int y = 0, wc = 0;
+            if (i < end) {
+                y = (int)__umulhi((unsigned)i, rcp_nw);
+                wc = i - y * nwords;
+                const uint32_t f4 = flag32[(y + 3) * WP + wc];
+                k4 = need == 2 ? ((f4 >> 1) & 0x01010101u) : ((f4 | (f4 >> 1)) & 0x01010101u);
+            }
+            const unsigned bal = __ballot_sync(0xffffffffu, k4 != 0);
+            if (!bal) continue;
+            const int n = __popc(k4);
+            int inc = n;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, inc, o);
+                if (lane >= o) inc += t;
+            }
+            int o2 = off + inc - n;
+            while (k4) {
+                const int bit = __ffs(k4) - 1;       /* 0, 8, 16 or 24 */
+                k4 &= k4 - 1;
+                const int t = 4 * wc + (bit >> 3);   /* tile column */
+                const int idx = (y + 3) * tp + t;
+                out[o2++] = (uint32_t)(t - shift + c.offx) | ((uint32_t)(y + 3 + c.offy) << 12) | ((uint32_t)score[idx] << 24);
+            }
+            off += __shfl_sync(0xffffffffu, inc, 31);
         }
-        const unsigned bal = __ballot_sync(0xffffffffu, keep);
-        if (keep)
-            out[off + __popc(bal & ((1u << lane) - 1))] =
-                (uint32_t)(x + 3 + c.offx) | ((uint32_t)(y + 3 + c.offy) << 12) | ((uint32_t)score[idx] << 24);
-        off += __popc(bal);
     }
-    if (tid == 0) cell_count[(size_t)f * ncells + blockIdx.x] = need == 2 ? tot2 : tot1;
+    if (tid == 0) cell_count[(size_t)f * ncells + blockIdx.x] = tot;
 }
 
 /* ================================================================== stage 2: quadtree */
@@ -887,6 +960,7 @@ struct orbx_extractor {
     int kcap = 0, maxn = 0;
     size_t oct_smem = 0;
     int nblur_tiles = 0;
+    int fast_tp = 8, fast_rows = 8, fast_list_cap = 2;
     cudaStream_t stream = nullptr;
     /* device buffers */
     uint8_t* d_pyr = nullptr;
@@ -941,8 +1015,8 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
     *out = nullptr;
     if (p->nlevels < 1 || p->nlevels > ORBX_MAX_LEVELS || p->nfeatures < 1 || p->scale_factor <= 1.0f ||
         p->width < 64 || p->height < 64 || p->width > 4000 || p->height > 4000 || p->max_batch < 1 ||
-        p->min_th_fast < 1 || p->ini_th_fast < p->min_th_fast || p->ini_th_fast > 255) {
-        orbx_set_error("unsupported parameters (need 64<=w,h<=4000, 1<=minTh<=iniTh<=255, nlevels<=%d)", ORBX_MAX_LEVELS);
+        p->min_th_fast < 1 || p->min_th_fast > 127 || p->ini_th_fast < p->min_th_fast || p->ini_th_fast > 255) {
+        orbx_set_error("unsupported parameters (need 64<=w,h<=4000, 1<=minTh<=127, minTh<=iniTh<=255, nlevels<=%d)", ORBX_MAX_LEVELS);
         return ORBX_ERR_INVALID;
     }
     int ndev = 0;
@@ -1028,8 +1102,11 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
                     c.cw = (short)((int)maxX - (int)iniX); c.ch = (short)((int)maxY - (int)iniY);
                     c.offx = (short)(j * wCell); c.offy = (short)(i * hCell); c.pad = 0;
                     c.slot_off = (int)slot_off;
-                    if (c.cw > FAST_TP || c.ch > FAST_TH) {
-                        orbx_set_error("FAST cell %dx%d exceeds the %d-px tile", c.cw, c.ch, FAST_TP);
+                    e->fast_tp = std::max(e->fast_tp, 4 * ((c.cw + 6) >> 2));
+                    e->fast_rows = std::max(e->fast_rows, (int)c.ch);
+                    e->fast_list_cap = std::max(e->fast_list_cap, (std::max(c.cw - 6, 0) * std::max(c.ch - 6, 0) + 1) & ~1);
+                    if (c.cw > FAST_MAX_CELL || c.ch > FAST_MAX_CELL) {
+                        orbx_set_error("FAST cell %dx%d exceeds the %d-px tile", c.cw, c.ch, FAST_MAX_CELL);
                         free_all(e);
                         return ORBX_ERR_INVALID;
                     }
@@ -1208,9 +1285,9 @@ extern "C" orbx_status orbx_extract_device(orbx_extractor* e, const uint8_t* d_i
     if (e->profiling) ORBX_CUDA(cudaEventRecord(e->ev[1], st));
     /* stage 1 */
     if (e->ncells > 0) {
-        k_fast_cells<<<dim3(e->ncells, batch), FAST_THREADS, 0, st>>>(e->T, e->d_cells, e->ncells, e->P.ini_th_fast,
+        k_fast_cells<<<dim3(e->ncells, batch), FAST_THREADS, (size_t)3 * e->fast_rows * e->fast_tp + 4 * (size_t)e->fast_list_cap, st>>>(e->T, e->d_cells, e->ncells, e->P.ini_th_fast,
                                                                        e->P.min_th_fast, e->d_slots, e->slots_per_frame,
-                                                                       e->d_cell_count);
+                                                                       e->d_cell_count, e->fast_tp, e->fast_rows, e->fast_list_cap);
         ++launches;
     }
     if (e->profiling) ORBX_CUDA(cudaEventRecord(e->ev[2], st));
