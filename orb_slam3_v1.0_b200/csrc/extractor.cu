@@ -49,6 +49,10 @@ struct LevelDev {
     uint8_t* blur;          /* blurred level, w x h */
     const short4* xtab;     /* resize: per dx {sx, a0, a1, 0} */
     const short4* ytab;     /* resize: per dy {sy, b0, b1, 0} */
+    const uint4* xcoef;     /* word-wise resize tables over the padded row (k_resize_w4) */
+    const uint32_t* xmeta;
+    const short4* ypad;     /* per padded row {sy, b0, b1, 0} */
+    int fast_resize;
     int cell_begin, cell_end;
     int N, nIni;
     float hX;
@@ -146,6 +150,54 @@ __global__ void __launch_bounds__(256) k_resize(LevelDev S, LevelDev D, int batc
                 const short4 xt = __ldg(D.xtab + reflect101(x, D.w));
                 out |= resize_px(s0, s1, xt, yt.y, yt.z) << (8 * k);
             }
+        }
+        *reinterpret_cast<uint32_t*>(D.base + (size_t)f * D.frame_bytes + (size_t)r * D.pitch + c * 4) = out;
+    }
+}
+
+/* Fast path of the level chain: one thread per 32-bit word (4 pixels) of the PADDED destination
+ * row.  Per-word tables built on the host hold, for the 4 pixels, the packed fixed-point
+ * coefficient pairs (a0 | a1<<16), the byte address of the left-most source pixel and each
+ * pixel's offset from it (reflection of border columns is baked into the tables).  The source
+ * bytes of both rows are fetched as three aligned words, funnel-shifted to the base pixel, and
+ * each horizontal interpolation is one PRMT + one 2-way dot product (IDP.2A). */
+struct ResizeMeta { uint32_t m; };   /* base byte (16b) | off0<<16 | off1<<20 | off2<<24 | off3<<28; ~0 = outside */
+
+__global__ void __launch_bounds__(256) k_resize_w4(LevelDev S, LevelDev D, const uint4* __restrict__ xcoef,
+                                                   const uint32_t* __restrict__ xmeta,
+                                                   const short4* __restrict__ ypad, int batch) {
+    const int chunks = D.pitch / 4;
+    const long long total = (long long)batch * D.rows * chunks;
+    const int spw = S.pitch >> 2;
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total;
+         t += (long long)gridDim.x * blockDim.x) {
+        const int c = (int)(t % chunks);
+        const long long t2 = t / chunks;
+        const int r = (int)(t2 % D.rows);
+        const int f = (int)(t2 / D.rows);
+        const uint32_t meta = __ldg(xmeta + c);
+        if (meta == 0xFFFFFFFFu) continue;
+        const uint4 cf = __ldg(xcoef + c);
+        const short4 yt = __ldg(ypad + r);                 /* {sy, b0, b1} for the padded row r */
+        const uint32_t base = meta & 0xFFFFu;
+        const int sh = (base & 3) * 8;
+        const uint32_t* row0 = reinterpret_cast<const uint32_t*>(S.base + (size_t)f * S.frame_bytes +
+                                                                  (size_t)(yt.x + ORBX_EDGE) * S.pitch) + (base >> 2);
+        const uint32_t* row1 = row0 + spw;                  /* row sy+1 exists in the bordered source */
+        const uint32_t a0 = __ldg(row0), a1 = __ldg(row0 + 1), a2 = __ldg(row0 + 2);
+        const uint32_t b0 = __ldg(row1), b1 = __ldg(row1 + 1), b2 = __ldg(row1 + 2);
+        const uint32_t U0 = __funnelshift_r(a0, a1, sh), V0 = __funnelshift_r(a1, a2, sh);
+        const uint32_t U1 = __funnelshift_r(b0, b1, sh), V1 = __funnelshift_r(b1, b2, sh);
+        const int wy0 = yt.y, wy1 = yt.z;
+        const uint32_t cfs[4] = {cf.x, cf.y, cf.z, cf.w};
+        uint32_t out = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const uint32_t off = (meta >> (16 + 4 * k)) & 7u;
+            const uint32_t sel = off * 0x11u + 0x10u;       /* bytes off, off+1 -> lanes 0,1 */
+            const int r0 = (int)__dp2a_lo(cfs[k], __byte_perm(U0, V0, sel), 0u);
+            const int r1 = (int)__dp2a_lo(cfs[k], __byte_perm(U1, V1, sel), 0u);
+            out |= (uint32_t)((((wy0 * (r0 >> 4)) >> 16) + ((wy1 * (r1 >> 4)) >> 16) + 2) >> 2) << (8 * k);
         }
         *reinterpret_cast<uint32_t*>(D.base + (size_t)f * D.frame_bytes + (size_t)r * D.pitch + c * 4) = out;
     }
@@ -812,37 +864,59 @@ __global__ void __launch_bounds__(ORD_THREADS) k_order(Tables T, const uint32_t*
 /* ================================================================== stage 4: blur */
 /* cv::GaussianBlur(7x7, sigma 2, BORDER_REFLECT_101) on a clone() of the level = integer taps
  * [18,34,48,56,48,34,18] per axis, (v + 2^15) >> 16.  The level's own 19-px
- * reflect-101 border supplies the halo, so no edge handling is needed. */
-#define BL_TW 64
-#define BL_TH 16
-__global__ void __launch_bounds__(256) k_blur7(Tables T, const int4* __restrict__ tiles, int batch) {
-    __shared__ uint8_t s_in[(BL_TH + 6) * (BL_TW + 8)];
-    __shared__ unsigned short s_h[(BL_TH + 6) * BL_TW];
-    const int4 t = tiles[blockIdx.x];        /* {level, tx, ty, 0} */
-    const int f = blockIdx.y;
+ * reflect-101 border supplies the halo, so no edge handling is needed.
+ * One WARP per (120-px column strip x BL_ROWS rows): each lane owns one aligned 32-bit word
+ * (4 pixels) of the strip and marches down the rows with a 7-row register window.  The
+ * vertical pass runs on two u16 lanes per register (sums <= 255*256 fit 16 bits), the
+ * horizontal pass takes its neighbours' column sums by warp shuffle; lanes 0 and 31 are halo.
+ * No shared memory, every global access is a coalesced 128-byte row segment. */
+#define BL_STRIP 120
+#define BL_ROWS 56
+__global__ void __launch_bounds__(128) k_blur7(Tables T, const int4* __restrict__ tiles, int ntiles) {
+    const int wt = blockIdx.x * 4 + (threadIdx.x >> 5);
+    if (wt >= ntiles) return;
+    const int4 t = tiles[wt];                 /* {level, x0, y0, nrows} */
+    const int f = blockIdx.y, lane = threadIdx.x & 31;
     const LevelDev& L = T.lv[t.x];
-    const int x0 = t.y * BL_TW, y0 = t.z * BL_TH;
-    const int tid = threadIdx.x;
-    const int P = BL_TW + 8;
-    for (int i = tid; i < (BL_TH + 6) * (BL_TW + 6); i += 256) {
-        const int y = i / (BL_TW + 6), x = i - y * (BL_TW + 6);
-        const int gx = min(x0 + x - 3, L.w + ORBX_EDGE - 1), gy = min(y0 + y - 3, L.h + ORBX_EDGE - 1);
-        s_in[y * P + x] = __ldg(lv_ptr(L, f, gx, gy));
+    const int x = t.y - 4 + 4 * lane;         /* ROI column of this lane's word */
+    const int xc = min(x, L.pitch - ORBX_XOFF - 4);
+    const uint8_t* src = lv_ptr(L, f, xc, t.z - 3);
+    uint8_t* dst = L.blur + (size_t)f * L.bframe_bytes + (size_t)t.z * L.bpitch + x;
+    const bool store = lane >= 1 && lane <= 30 && x < L.w;
+    const int nrows = t.w, pitch = L.pitch, bpitch = L.bpitch;
+    uint32_t E[7], O[7];
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+        const uint32_t w = __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)j * pitch));
+        E[j] = w & 0x00FF00FFu;
+        O[j] = (w >> 8) & 0x00FF00FFu;
     }
-    __syncthreads();
-    for (int i = tid; i < (BL_TH + 6) * BL_TW; i += 256) {
-        const int y = i / BL_TW, x = i - y * BL_TW;
-        const uint8_t* p = s_in + y * P + x;
-        s_h[i] = (unsigned short)(18 * (p[0] + p[6]) + 34 * (p[1] + p[5]) + 48 * (p[2] + p[4]) + 56 * p[3]);
-    }
-    __syncthreads();
-    for (int i = tid; i < BL_TH * BL_TW; i += 256) {
-        const int y = i / BL_TW, x = i - y * BL_TW;
-        if (x0 + x < L.w && y0 + y < L.h) {
-            const unsigned short* p = s_h + y * BL_TW + x;
-            const int acc = 18 * (p[0] + p[6 * BL_TW]) + 34 * (p[BL_TW] + p[5 * BL_TW]) +
-                            48 * (p[2 * BL_TW] + p[4 * BL_TW]) + 56 * p[3 * BL_TW];
-            L.blur[(size_t)f * L.bframe_bytes + (size_t)(y0 + y) * L.bpitch + x0 + x] = (uint8_t)((acc + (1 << 15)) >> 16);
+    for (int r = 0; r < nrows; r += 7) {
+#pragma unroll
+        for (int j = 0; j < 7; ++j) {
+            const int rr = r + j;
+            if (rr < nrows) {
+                const int s = (6 + j) % 7;
+                const uint32_t w = __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)(6 + rr) * pitch));
+                E[s] = w & 0x00FF00FFu;
+                O[s] = (w >> 8) & 0x00FF00FFu;
+                /* window rows oldest..newest = slots (s+1)%7 .. s */
+                const uint32_t VE = 18u * (E[(s + 1) % 7] + E[s]) + 34u * (E[(s + 2) % 7] + E[(s + 6) % 7]) +
+                                    48u * (E[(s + 3) % 7] + E[(s + 5) % 7]) + 56u * E[(s + 4) % 7];
+                const uint32_t VO = 18u * (O[(s + 1) % 7] + O[s]) + 34u * (O[(s + 2) % 7] + O[(s + 6) % 7]) +
+                                    48u * (O[(s + 3) % 7] + O[(s + 5) % 7]) + 56u * O[(s + 4) % 7];
+                const uint32_t LE = __shfl_up_sync(0xffffffffu, VE, 1), LO = __shfl_up_sync(0xffffffffu, VO, 1);
+                const uint32_t RE = __shfl_down_sync(0xffffffffu, VE, 1), RO = __shfl_down_sync(0xffffffffu, VO, 1);
+                const uint32_t c0 = VE & 0xFFFFu, c2 = VE >> 16, c1 = VO & 0xFFFFu, c3 = VO >> 16;
+                const uint32_t l1 = LO & 0xFFFFu, l2 = LE >> 16, l3 = LO >> 16;
+                const uint32_t r0 = RE & 0xFFFFu, r1 = RO & 0xFFFFu, r2 = RE >> 16;
+                const uint32_t o0 = (18u * (l1 + c3) + 34u * (l2 + c2) + 48u * (l3 + c1) + 56u * c0 + 32768u) >> 16;
+                const uint32_t o1 = (18u * (l2 + r0) + 34u * (l3 + c3) + 48u * (c0 + c2) + 56u * c1 + 32768u) >> 16;
+                const uint32_t o2 = (18u * (l3 + r1) + 34u * (c0 + r0) + 48u * (c1 + c3) + 56u * c2 + 32768u) >> 16;
+                const uint32_t o3 = (18u * (c0 + r2) + 34u * (c1 + r1) + 48u * (c2 + r0) + 56u * c3 + 32768u) >> 16;
+                if (store)
+                    *reinterpret_cast<uint32_t*>(dst + (size_t)rr * bpitch) = o0 | (o1 << 8) | (o2 << 16) | (o3 << 24);
+            }
         }
     }
 }
@@ -919,7 +993,9 @@ __global__ void __launch_bounds__(256) k_orient_describe(Tables T, UMax um, cons
     constexpr float factorPI = (float)(3.14159265358979323846 / 180.f);
     const float ar = __fmul_rn(angle, factorPI);
     /* cosf/sinf of the reference resolve to glibc (<=0.56 ULP); here: fp64 result rounded once */
-    const float a = (float)cos((double)ar), b = (float)sin((double)ar);
+    double sd, cd;
+    sincos((double)ar, &sd, &cd);
+    const float a = (float)cd, b = (float)sd;
     const uint8_t* center = L.blur + (size_t)f * L.bframe_bytes + (size_t)y * L.bpitch + x;
     const signed char* pat = d_pattern + 32 * lane;
     int val = 0;
@@ -967,6 +1043,7 @@ struct orbx_extractor {
     uint8_t* d_blur = nullptr;
     uint8_t* d_input = nullptr;      /* staging for orbx_extract_host */
     short4* d_tabs = nullptr;
+    uint8_t* d_wtabs = nullptr;
     Cell* d_cells = nullptr;
     int4* d_blur_tiles = nullptr;
     uint32_t* d_slots = nullptr;
@@ -997,7 +1074,7 @@ static inline int cvRoundf_host(float v) { return (int)lrintf(v); }
 static void free_all(orbx_extractor* e) {
     if (!e) return;
     cudaSetDevice(e->P.device);
-    void* dptrs[] = {e->d_pyr, e->d_blur, e->d_input, e->d_tabs, e->d_cells, e->d_blur_tiles, e->d_slots,
+    void* dptrs[] = {e->d_pyr, e->d_blur, e->d_input, e->d_tabs, e->d_wtabs, e->d_cells, e->d_blur_tiles, e->d_slots,
                      e->d_cell_count, e->d_cand, e->d_pnode, e->d_cand_count, e->d_sel, e->d_sel_count,
                      e->d_dest, e->d_lapping, e->d_kps, e->d_desc, e->d_nk};
     for (void* p : dptrs) if (p) cudaFree(p);
@@ -1131,8 +1208,8 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
         L.sel_cap = std::max(L.N + 3, 4 * std::max(L.nIni, 0)) + 1;
         sel_off += L.sel_cap;
         maxn = std::max(maxn, L.sel_cap + 4);
-        for (int ty = 0; ty < orbx_div_up(L.h, BL_TH); ++ty)
-            for (int tx = 0; tx < orbx_div_up(L.w, BL_TW); ++tx) blur_tiles.push_back(make_int4(l, tx, ty, 0));
+        for (int y0 = 0; y0 < L.h; y0 += BL_ROWS)
+            for (int x0 = 0; x0 < L.w; x0 += BL_STRIP) blur_tiles.push_back(make_int4(l, x0, y0, std::min(BL_ROWS, L.h - y0)));
     }
     e->ncells = (int)e->cells.size();
     e->slots_per_frame = slot_off;
@@ -1206,6 +1283,54 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
             }
             off += L.w + L.h;
         }
+        /* word-wise tables over the padded destination row/rows (reflection baked in) */
+        {
+            size_t wbytes = 0;
+            for (int l = 1; l < nl; ++l) wbytes += orbx_align_up((size_t)(e->lv[l].pitch / 4) * 20 + (size_t)e->lv[l].rows * 8, 16) + 64;
+            std::vector<uint8_t> wt(std::max<size_t>(wbytes, 16), 0);
+            CK(cudaMalloc(&e->d_wtabs, wt.size()));
+            size_t woff = 0, toff = 0;
+            for (int l = 0; l < nl; ++l) {
+                LevelDev& L = e->lv[l];
+                const short4* xt = tabs.data() + toff;
+                const short4* yt = tabs.data() + toff + L.w;
+                toff += L.w + L.h;
+                if (l == 0) continue;
+                const int nw = L.pitch / 4;
+                uint4* xc = reinterpret_cast<uint4*>(wt.data() + woff);
+                L.xcoef = reinterpret_cast<const uint4*>(e->d_wtabs + woff); woff += (size_t)nw * 16;
+                uint32_t* xm = reinterpret_cast<uint32_t*>(wt.data() + woff);
+                L.xmeta = reinterpret_cast<const uint32_t*>(e->d_wtabs + woff); woff += orbx_align_up((size_t)nw * 4, 16);
+                short4* yp = reinterpret_cast<short4*>(wt.data() + woff);
+                L.ypad = reinterpret_cast<const short4*>(e->d_wtabs + woff); woff += orbx_align_up((size_t)L.rows * 8, 16);
+                bool ok = true;
+                auto refl = [](int p, int n) { while (p < 0 || p >= n) p = (p < 0) ? -p : 2 * (n - 1) - p; return p; };
+                for (int c = 0; c < nw; ++c) {
+                    int sx[4], lo = 1 << 30, hi = -1;
+                    uint32_t cf[4];
+                    bool any = false;
+                    for (int k = 0; k < 4; ++k) {
+                        const int x = 4 * c + k - ORBX_XOFF;
+                        if (x >= -ORBX_EDGE && x < L.w + ORBX_EDGE) {
+                            const short4 tt = xt[refl(x, L.w)];
+                            sx[k] = tt.x; cf[k] = (uint32_t)(uint16_t)tt.y | ((uint32_t)(uint16_t)tt.z << 16);
+                            lo = std::min(lo, sx[k]); hi = std::max(hi, sx[k]);
+                            any = true;
+                        } else { sx[k] = -1; cf[k] = 0; }
+                    }
+                    if (!any) { xm[c] = 0xFFFFFFFFu; xc[c] = make_uint4(0, 0, 0, 0); continue; }
+                    if (hi - lo > 6) ok = false;
+                    uint32_t m = (uint32_t)(ORBX_XOFF + lo);
+                    for (int k = 0; k < 4; ++k) m |= (uint32_t)((sx[k] < 0 ? 0 : sx[k] - lo) & 7) << (16 + 4 * k);
+                    xm[c] = m;
+                    xc[c] = make_uint4(cf[0], cf[1], cf[2], cf[3]);
+                }
+                for (int r = 0; r < L.rows; ++r) yp[r] = yt[refl(r - ORBX_EDGE, L.h)];
+                L.fast_resize = ok ? 1 : 0;
+            }
+            CK(cudaMemcpyAsync(e->d_wtabs, wt.data(), wt.size(), cudaMemcpyHostToDevice, e->stream));
+            CK(cudaStreamSynchronize(e->stream));
+        }
         CK(cudaMemcpyAsync(e->d_tabs, tabs.data(), tabs.size() * sizeof(short4), cudaMemcpyHostToDevice, e->stream));
         if (!e->cells.empty())
             CK(cudaMemcpyAsync(e->d_cells, e->cells.data(), e->cells.size() * sizeof(Cell), cudaMemcpyHostToDevice, e->stream));
@@ -1278,7 +1403,10 @@ extern "C" orbx_status orbx_extract_device(orbx_extractor* e, const uint8_t* d_i
         for (int l = 1; l < nl; ++l) {
             const LevelDev& D = e->T.lv[l];
             const long long it = (long long)batch * D.rows * (D.pitch / 4);
-            k_resize<<<grid_for(it, 256, kMaxBlocks), 256, 0, st>>>(e->T.lv[l - 1], D, batch);
+            if (D.fast_resize)
+                k_resize_w4<<<grid_for(it, 256, kMaxBlocks), 256, 0, st>>>(e->T.lv[l - 1], D, D.xcoef, D.xmeta, D.ypad, batch);
+            else
+                k_resize<<<grid_for(it, 256, kMaxBlocks), 256, 0, st>>>(e->T.lv[l - 1], D, batch);
             ++launches;
         }
     }
@@ -1304,7 +1432,7 @@ extern "C" orbx_status orbx_extract_device(orbx_extractor* e, const uint8_t* d_i
     ++launches;
     if (e->profiling) ORBX_CUDA(cudaEventRecord(e->ev[4], st));
     /* stage 4 */
-    k_blur7<<<dim3(e->nblur_tiles, batch), 256, 0, st>>>(e->T, e->d_blur_tiles, batch);
+    k_blur7<<<dim3(orbx_div_up(e->nblur_tiles, 4), batch), 128, 0, st>>>(e->T, e->d_blur_tiles, e->nblur_tiles);
     ++launches;
     if (e->profiling) ORBX_CUDA(cudaEventRecord(e->ev[5], st));
     /* stage 5 */
