@@ -120,9 +120,136 @@ orbx_status orbx_memcpy_d2h(void* h, const void* d, size_t bytes);
 orbx_status orbx_device_synchronize(void);
 
 /* ---------------------------------------------------------------- matcher
- * ORBmatcher::DescriptorDistance   src/ORBmatcher.cc:1375-1391
+ * All matcher entry points take HOST pointers, are batched over `nprob` independent problems
+ * (one CTA each; nprob = 1 is the reference's single call) and return after the results are
+ * in the caller's buffers.  A matcher handle owns one stream and its staging buffers. */
+typedef struct orbx_matcher orbx_matcher;
+orbx_status orbx_matcher_create(int device, orbx_matcher** out);
+void orbx_matcher_destroy(orbx_matcher* m);
+void* orbx_matcher_stream(orbx_matcher* m);
+/* kernel launches issued by the last matcher call */
+int orbx_matcher_last_launches(const orbx_matcher* m);
+
+/* ORBmatcher::DescriptorDistance   src/ORBmatcher.cc:1375-1391
  * n pairs of 32-byte descriptors (host pointers) -> n ints. */
 orbx_status orbx_hamming_pairs(const uint8_t* a, const uint8_t* b, int n, int* out);
+
+/* ORBmatcher::ComputeThreeMaxima   src/ORBmatcher.cc:1328-1370, on bin counts (host; the
+ * device kernels run the same code inside their rotation-histogram step). */
+orbx_status orbx_three_maxima(const int* counts, int L, int* ind1, int* ind2, int* ind3);
+
+/* The part of Frame the projection searches read (src/Frame.cc:157-176 AssignFeaturesToGrid,
+ * :404-468 GetFeaturesInArea, :470-480 PosInGrid), flattened.  The grid itself is rebuilt on
+ * the device from (kx, ky). */
+typedef struct {
+    int n;                          /* mNumKeypoints */
+    const float* kx; const float* ky; const int32_t* koct;   /* mvKeysUn: pt.x, pt.y, octave */
+    const float* kangle;            /* mvKeysUn angle; may be NULL unless checkOrientation */
+    const uint8_t* desc;            /* mDescriptors, n x 32 */
+    float minx, miny;               /* mnMinX, mnMinY */
+    float gw_inv, gh_inv;           /* mfGridElementWidthInv / HeightInv */
+    int gcols, grows;               /* mFrameGridCols / Rows */
+    const float* scale;             /* mvScaleFactors */
+    int nlevels;
+} orbx_frame_view;
+
+/* MapPoint fields SearchByProjection reads (src/ORBmatcher.cc:37-70) */
+typedef struct {
+    int n;
+    const uint8_t* inview;          /* mbTrackInView && !isBad() */
+    const float* x; const float* y; /* mTrackProjX / mTrackProjY */
+    const int32_t* level;           /* mnTrackScaleLevel */
+    const float* viewcos;           /* mTrackViewCos */
+    const float* depth;             /* mTrackDepth (bFarPoints gate) */
+    const uint8_t* desc;            /* GetDescriptor(), n x 32 */
+} orbx_mappoints;
+
+/* ORBmatcher::SearchByProjection(Frame, vpMapPoints, th, bFarPoints, thFarPoints, nnRatio,
+ * checkOrientation)   src/ORBmatcher.cc:31-123.
+ * claimed[p][i] != 0: frame keypoint i already holds a MapPoint with observations (:77-79);
+ * NULL or claimed[p] == NULL = none.  match_mp[p][i] = index of the map point assigned to
+ * frame keypoint i or -1; nmatches[p] = the function's return value.  The reference's
+ * sequential "first map point claims the keypoint" rule is reproduced exactly. */
+orbx_status orbx_search_by_projection(orbx_matcher* m, int nprob, const orbx_frame_view* F,
+                                      const orbx_mappoints* MP, const uint8_t* const* claimed,
+                                      float th, int bFarPoints, float thFarPoints, float nnRatio,
+                                      int* const* match_mp, int* nmatches);
+
+/* KeyFrame map points already projected into the frame by the host shim
+ * (src/ORBmatcher.cc:1225-1262: pose, frustum and distance gates, PredictScale). */
+typedef struct {
+    int n;
+    const uint8_t* valid;           /* passed the gates, not in sAlreadyFound */
+    const float* u; const float* v; /* projection */
+    const int32_t* level;           /* nPredictedLevel */
+    const float* angle;             /* pKF->mvKeysUn[i].angle */
+    const uint8_t* desc;
+} orbx_kf_points;
+
+/* ORBmatcher::SearchByProjection(Frame, KeyFrame, sAlreadyFound, th, checkOrientation)
+ * src/ORBmatcher.cc:1202-1326 (rotation histogram :1290-1322). */
+orbx_status orbx_search_by_projection_kf(orbx_matcher* m, int nprob, const orbx_frame_view* F,
+                                         const orbx_kf_points* MP, const uint8_t* const* occupied,
+                                         float th, int checkOrientation, int* const* match_mp,
+                                         int* nmatches);
+
+/* KeyFrame fields SearchForTriangulation reads (src/ORBmatcher.cc:441-676); the DBoW2
+ * FeatureVector is flattened to sorted node ids + CSR index lists. */
+typedef struct {
+    int n;
+    const float* kx; const float* ky; const int32_t* koct; const float* kangle;
+    const uint8_t* desc;
+    const uint8_t* has_mp;          /* GetMapPoint(idx) != nullptr; may be NULL */
+    const float* uright;            /* mvuRight; may be NULL (mono) */
+    int nnodes; const int32_t* node_id; const int32_t* node_off; const int32_t* node_idx;
+} orbx_kf_view;
+
+/* ORBmatcher::SearchForTriangulation   src/ORBmatcher.cc:441-676.  F12 (row-major 3x3, as
+ * Pinhole::epipolarConstrain builds it, src/CameraModels/Pinhole.cpp:104-110) and the epipole
+ * `ep` (:453-456) are computed once by the host shim: 9 / 2 floats per problem.  scale2[p] =
+ * pKF2->mvScaleFactors.  pairs[p] receives 2*npairs[p] ints (idx1, idx2) in idx1 order
+ * (capacity 2*k1[p].n); nmatches[p] = the function's return value. */
+orbx_status orbx_search_for_triangulation(orbx_matcher* m, int nprob, const orbx_kf_view* k1,
+                                          const orbx_kf_view* k2, const float* F12,
+                                          const float* ep, const float* const* scale2,
+                                          int bOnlyStereo, int bCoarse, int checkOrientation,
+                                          int* const* pairs, int* npairs, int* nmatches);
+
+/* Frame::ComputeStereoMatches (upstream ORB-SLAM3 v1.0; absent from the fork:
+ * include/Frame.h:53-62).  Works on the DEVICE-RESIDENT results of the
+ * last orbx_extract_* call of each handle (keypoints, descriptors, mvImagePyramid): pair p
+ * matches frame left_frames[p] of `left` against frame right_frames[p] of `right` (`left` and
+ * `right` may be the same handle).  uRight/depth: npairs x stride floats (stride >=
+ * orbx_extractor_capacity(left)), entry i = mvuRight[i] / mvDepth[i] of the left keypoint i. */
+orbx_status orbx_stereo_matches(orbx_extractor* left, orbx_extractor* right, int npairs,
+                                const int* left_frames, const int* right_frames, float bf, float b,
+                                float* uRight, float* depth, int stride);
+/* Same, asynchronous and device-resident: enqueues on left's stream (after right's work) and
+ * leaves mvuRight / mvDepth in the handle; orbx_stereo_fetch copies them out. */
+orbx_status orbx_stereo_matches_async(orbx_extractor* left, orbx_extractor* right, int npairs,
+                                      const int* left_frames, const int* right_frames, float bf,
+                                      float b);
+orbx_status orbx_stereo_fetch(orbx_extractor* left, int npairs, float* uRight, float* depth, int stride);
+
+/* Brute-force 2-nearest-neighbour Hamming search + ratio test (BASELINE.json config 5; the
+ * fork only declares an unused cv::BFMatcher, src/Frame.cc:45).  Ties go to the lowest
+ * database index.  Host pointers; d1/i1/d2/i2: nq ints (257 / -1 when the database has fewer
+ * than 1 / 2 rows); pass (may be NULL): d1 < ratio * d2. */
+orbx_status orbx_knn2(orbx_matcher* m, const uint8_t* q, int nq, const uint8_t* db, int ndb,
+                      float ratio, int* d1, int* i1, int* d2, int* i2, uint8_t* pass);
+/* Device-resident building blocks (multi-GPU database sharding): local top-2 of every query
+ * against db rows [0, ndb) reported with global indices index_base + row, as two packed keys
+ * per query (dist << 32 | index; ~0 = none) in d_keys[2*nq]; asynchronous on m's stream. */
+orbx_status orbx_knn2_device(orbx_matcher* m, const void* d_q, int nq, const void* d_db, int ndb,
+                             long long index_base, unsigned long long* d_keys);
+/* Merge `nparts` key sets (d_parts[(p*nq + q)*2 + {0,1}], e.g. the all-gathered per-rank
+ * results) into final d1/i1/d2/i2/pass device arrays (any may be NULL). */
+orbx_status orbx_knn2_merge_device(orbx_matcher* m, const unsigned long long* d_parts, int nparts,
+                                   int nq, float ratio, int* d_d1, int* d_i1, int* d_d2,
+                                   int* d_i2, uint8_t* d_pass);
+/* tuning knob for the kNN kernel: 0 = 8 POPC per pair, 1 = carry-save adder tree (4 POPC) */
+orbx_status orbx_matcher_set_knn_variant(orbx_matcher* m, int variant);
+orbx_status orbx_matcher_synchronize(orbx_matcher* m);
 
 #ifdef __cplusplus
 }

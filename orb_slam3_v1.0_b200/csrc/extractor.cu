@@ -26,6 +26,7 @@
 #include <vector>
 
 #include "orbx_internal.h"
+#include "extractor_state.h"
 #include "stdsort_emul.h"
 
 /* ------------------------------------------------------------------ errors */
@@ -38,50 +39,6 @@ void orbx_set_error(const char* fmt, ...) {
 }
 extern "C" const char* orbx_last_error(void) { return g_err; }
 extern "C" int orbx_version(void) { return 100; }
-
-/* ------------------------------------------------------------------ device-side level table */
-struct LevelDev {
-    int w, h, pitch, rows;
-    unsigned long long frame_bytes;
-    uint8_t* base;          /* bordered pyramid, frame-major */
-    int bpitch;
-    unsigned long long bframe_bytes;
-    uint8_t* blur;          /* blurred level, w x h */
-    const short4* xtab;     /* resize: per dx {sx, a0, a1, 0} */
-    const short4* ytab;     /* resize: per dy {sy, b0, b1, 0} */
-    const uint4* xcoef;     /* word-wise resize tables over the padded row (k_resize_w4) */
-    const uint32_t* xmeta;
-    const short4* ypad;     /* per padded row {sy, b0, b1, 0} */
-    int fast_resize;
-    int cell_begin, cell_end;
-    int N, nIni;
-    float hX;
-    int cand_off, cand_cap; /* into the per-frame candidate arrays */
-    int sel_off, sel_cap;   /* into the per-frame selected-keypoint arrays */
-    float scale;
-    float patch_size;
-};
-
-struct Cell {
-    short level, x0, y0, cw, ch, offx, offy, pad;
-    int slot_off;           /* into the per-frame candidate-slot array */
-    unsigned rcp_dw;        /* floor(2^32/(cw-6))+1: exact i/(cw-6) by __umulhi for i < 2^16 */
-};
-
-struct Tables {
-    int nlevels;
-    LevelDev lv[ORBX_MAX_LEVELS];
-};
-
-__device__ __forceinline__ int reflect101(int p, int n) {
-    /* |p| excursions are < n here (border 19 < smallest supported level) but loop anyway */
-    while (p < 0 || p >= n) p = (p < 0) ? -p : 2 * (n - 1) - p;
-    return p;
-}
-
-__device__ __forceinline__ uint8_t* lv_ptr(const LevelDev& L, int f, int x, int y) {
-    return L.base + (size_t)f * L.frame_bytes + (size_t)(y + ORBX_EDGE) * L.pitch + ORBX_XOFF + x;
-}
 
 /* ================================================================== stage 0: pyramid */
 /* level 0 = copyMakeBorder(image, 19, BORDER_REFLECT_101).
@@ -1023,52 +980,6 @@ __global__ void __launch_bounds__(256) k_orient_describe(Tables T, UMax um, cons
 }
 
 /* ================================================================== host side */
-struct orbx_extractor {
-    orbx_params P;
-    int nlevels;
-    std::vector<float> sf, inv_sf, sigma2, inv_sigma2;
-    std::vector<int> nfeat, umax;
-    Tables T;
-    std::vector<LevelDev> lv;
-    std::vector<Cell> cells;
-    int ncells = 0, max_cells_level = 0;
-    size_t slots_per_frame = 0, cand_per_frame = 0, sel_per_frame = 0;
-    int kcap = 0, maxn = 0;
-    size_t oct_smem = 0;
-    int nblur_tiles = 0;
-    int fast_tp = 8, fast_rows = 8, fast_list_cap = 2;
-    cudaStream_t stream = nullptr;
-    /* device buffers */
-    uint8_t* d_pyr = nullptr;
-    uint8_t* d_blur = nullptr;
-    uint8_t* d_input = nullptr;      /* staging for orbx_extract_host */
-    short4* d_tabs = nullptr;
-    uint8_t* d_wtabs = nullptr;
-    Cell* d_cells = nullptr;
-    int4* d_blur_tiles = nullptr;
-    uint32_t* d_slots = nullptr;
-    int* d_cell_count = nullptr;
-    uint32_t* d_cand = nullptr;
-    uint32_t* d_pnode = nullptr;
-    int* d_cand_count = nullptr;
-    uint32_t* d_sel = nullptr;
-    int* d_sel_count = nullptr;
-    int* d_dest = nullptr;
-    int* d_lapping = nullptr;
-    orbx_keypoint* d_kps = nullptr;
-    uint8_t* d_desc = nullptr;
-    int* d_nk = nullptr;           /* [2*max_batch]: counts then mono indices */
-    /* pinned host mirrors */
-    orbx_keypoint* h_kps = nullptr;
-    uint8_t* h_desc = nullptr;
-    int* h_nk = nullptr;
-    int* h_lapping = nullptr;
-    int last_batch = 0, last_launches = 0;
-    bool synced = false;
-    bool profiling = false;
-    cudaEvent_t ev[7] = {};
-};
-
 static inline int cvRoundf_host(float v) { return (int)lrintf(v); }
 
 static void free_all(orbx_extractor* e) {
@@ -1076,11 +987,13 @@ static void free_all(orbx_extractor* e) {
     cudaSetDevice(e->P.device);
     void* dptrs[] = {e->d_pyr, e->d_blur, e->d_input, e->d_tabs, e->d_wtabs, e->d_cells, e->d_blur_tiles, e->d_slots,
                      e->d_cell_count, e->d_cand, e->d_pnode, e->d_cand_count, e->d_sel, e->d_sel_count,
-                     e->d_dest, e->d_lapping, e->d_kps, e->d_desc, e->d_nk};
+                     e->d_dest, e->d_lapping, e->d_kps, e->d_desc, e->d_nk, e->d_uright, e->d_depth, e->d_pairs,
+                     e->d_rowent};
     for (void* p : dptrs) if (p) cudaFree(p);
-    void* hptrs[] = {e->h_kps, e->h_desc, e->h_nk, e->h_lapping};
+    void* hptrs[] = {e->h_kps, e->h_desc, e->h_nk, e->h_lapping, e->h_uright, e->h_depth, e->h_pairs};
     for (void* p : hptrs) if (p) cudaFreeHost(p);
     for (int i = 0; i < 7; ++i) if (e->ev[i]) cudaEventDestroy(e->ev[i]);
+    if (e->ev_stereo) cudaEventDestroy(e->ev_stereo);
     if (e->stream) cudaStreamDestroy(e->stream);
     delete e;
 }

@@ -1,0 +1,110 @@
+/* Extractor state shared by the liborbx translation units (extractor.cu owns it; the stereo
+ * matcher in matcher.cu reads the device-resident pyramids / keypoints / descriptors).
+ * Not part of the ABI. */
+#ifndef ORBX_EXTRACTOR_STATE_H
+#define ORBX_EXTRACTOR_STATE_H
+#include <vector>
+#include "orbx_internal.h"
+
+/* ------------------------------------------------------------------ device-side level table */
+struct LevelDev {
+    int w, h, pitch, rows;
+    unsigned long long frame_bytes;
+    uint8_t* base;          /* bordered pyramid, frame-major */
+    int bpitch;
+    unsigned long long bframe_bytes;
+    uint8_t* blur;          /* blurred level, w x h */
+    const short4* xtab;     /* resize: per dx {sx, a0, a1, 0} */
+    const short4* ytab;     /* resize: per dy {sy, b0, b1, 0} */
+    const uint4* xcoef;     /* word-wise resize tables over the padded row (k_resize_w4) */
+    const uint32_t* xmeta;
+    const short4* ypad;     /* per padded row {sy, b0, b1, 0} */
+    int fast_resize;
+    int cell_begin, cell_end;
+    int N, nIni;
+    float hX;
+    int cand_off, cand_cap; /* into the per-frame candidate arrays */
+    int sel_off, sel_cap;   /* into the per-frame selected-keypoint arrays */
+    float scale;
+    float patch_size;
+};
+
+struct Cell {
+    short level, x0, y0, cw, ch, offx, offy, pad;
+    int slot_off;           /* into the per-frame candidate-slot array */
+    unsigned rcp_dw;        /* floor(2^32/(cw-6))+1: exact i/(cw-6) by __umulhi for i < 2^16 */
+};
+
+struct Tables {
+    int nlevels;
+    LevelDev lv[ORBX_MAX_LEVELS];
+};
+
+__device__ __forceinline__ int reflect101(int p, int n) {
+    /* |p| excursions are < n here (border 19 < smallest supported level) but loop anyway */
+    while (p < 0 || p >= n) p = (p < 0) ? -p : 2 * (n - 1) - p;
+    return p;
+}
+
+__device__ __forceinline__ uint8_t* lv_ptr(const LevelDev& L, int f, int x, int y) {
+    return L.base + (size_t)f * L.frame_bytes + (size_t)(y + ORBX_EDGE) * L.pitch + ORBX_XOFF + x;
+}
+
+struct orbx_extractor {
+    orbx_params P;
+    int nlevels;
+    std::vector<float> sf, inv_sf, sigma2, inv_sigma2;
+    std::vector<int> nfeat, umax;
+    Tables T;
+    std::vector<LevelDev> lv;
+    std::vector<Cell> cells;
+    int ncells = 0, max_cells_level = 0;
+    size_t slots_per_frame = 0, cand_per_frame = 0, sel_per_frame = 0;
+    int kcap = 0, maxn = 0;
+    size_t oct_smem = 0;
+    int nblur_tiles = 0;
+    int fast_tp = 8, fast_rows = 8, fast_list_cap = 2;
+    cudaStream_t stream = nullptr;
+    /* device buffers */
+    uint8_t* d_pyr = nullptr;
+    uint8_t* d_blur = nullptr;
+    uint8_t* d_input = nullptr;      /* staging for orbx_extract_host */
+    short4* d_tabs = nullptr;
+    uint8_t* d_wtabs = nullptr;
+    Cell* d_cells = nullptr;
+    int4* d_blur_tiles = nullptr;
+    uint32_t* d_slots = nullptr;
+    int* d_cell_count = nullptr;
+    uint32_t* d_cand = nullptr;
+    uint32_t* d_pnode = nullptr;
+    int* d_cand_count = nullptr;
+    uint32_t* d_sel = nullptr;
+    int* d_sel_count = nullptr;
+    int* d_dest = nullptr;
+    int* d_lapping = nullptr;
+    orbx_keypoint* d_kps = nullptr;
+    uint8_t* d_desc = nullptr;
+    int* d_nk = nullptr;           /* [2*max_batch]: counts then mono indices */
+    /* pinned host mirrors */
+    orbx_keypoint* h_kps = nullptr;
+    uint8_t* h_desc = nullptr;
+    int* h_nk = nullptr;
+    int* h_lapping = nullptr;
+    int last_batch = 0, last_launches = 0;
+    bool synced = false;
+    bool profiling = false;
+    cudaEvent_t ev[7] = {};
+    /* Frame::ComputeStereoMatches state (stereo.cu), allocated on first use */
+    float* d_uright = nullptr;     /* [max_batch * kcap] mvuRight of the left frames */
+    float* d_depth = nullptr;
+    float* h_uright = nullptr;
+    float* h_depth = nullptr;
+    int* d_pairs = nullptr;        /* [2*max_batch] left / right frame index per pair */
+    int* h_pairs = nullptr;
+    unsigned short* d_rowent = nullptr;   /* per pair: right-keypoint indices per image row (vRowIndices) */
+    size_t rowent_per_pair = 0;
+    cudaEvent_t ev_stereo = nullptr;
+    int last_pairs = 0;
+};
+
+#endif

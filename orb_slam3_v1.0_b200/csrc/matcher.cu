@@ -1,16 +1,215 @@
 /*
- * matcher.cu -- Hamming-distance kernels behind include/orbx.h (popc/LOP3; no tensor cores:
- * binary descriptors are not a dense floating-point contraction).
- * Reference: ORBmatcher::DescriptorDistance src/ORBmatcher.cc:1375-1391.
+ * matcher.cu -- Hamming matching for B200 (sm_100a), behind include/orbx.h.
+ *
+ * popc/LOP3 kernels, no tensor cores: binary descriptors are not a dense floating-point
+ * contraction (BASELINE.json north_star).  Reference semantics (all under /root/reference):
+ *   DescriptorDistance            src/ORBmatcher.cc:1375-1391
+ *   SearchByProjection (map pts)  src/ORBmatcher.cc:31-131   + Frame grid src/Frame.cc:157-176,404-480
+ *   SearchByProjection (KeyFrame) src/ORBmatcher.cc:1202-1326
+ *   SearchForTriangulation        src/ORBmatcher.cc:441-676  + Pinhole::epipolarConstrain Pinhole.cpp:104-131
+ *   ComputeThreeMaxima            src/ORBmatcher.cc:1328-1370
+ *   brute-force kNN (k=2)         BASELINE.json config 5 (absent from the fork)
+ * Frame::ComputeStereoMatches lives in stereo.cu.
+ *
+ * NOT a port: every search is batched (one CTA per problem), the reference's sequential
+ * "first map point claims the keypoint" dependence is resolved by a fixed-point iteration
+ * over per-keypoint owners, tie-breaks are carried in packed (distance, order) keys, and the
+ * kNN kernel streams the database through shared memory with TMA bulk copies + mbarriers.
  */
 #include <cuda_runtime.h>
+#include <string.h>
+
+#include <algorithm>
+#include <vector>
+
 #include "orbx_internal.h"
+
+#define TH_LOW 30          /* include/ORBmatcher.h:73-75 */
+#define TH_HIGH 100
+#define HISTO_LENGTH 30
+
+/* ================================================================== small device helpers */
+template <int IMM>
+__device__ __forceinline__ uint32_t lop3(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t r;
+    asm("lop3.b32 %0, %1, %2, %3, %4;" : "=r"(r) : "r"(a), "r"(b), "r"(c), "n"(IMM));
+    return r;
+}
+#define XOR3(a, b, c) lop3<0x96>(a, b, c)
+#define MAJ3(a, b, c) lop3<0xE8>(a, b, c)
 
 __device__ __forceinline__ int hamming256(const uint4 a0, const uint4 a1, const uint4 b0, const uint4 b1) {
     return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
            __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
 }
 
+/* ComputeThreeMaxima, reference src/ORBmatcher.cc:1328-1370 */
+__host__ __device__ inline void three_maxima(const int* counts, int L, int& ind1, int& ind2, int& ind3) {
+    int max1 = 0, max2 = 0, max3 = 0;
+    ind1 = ind2 = ind3 = -1;
+    for (int i = 0; i < L; i++) {
+        const int s = counts[i];
+        if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+        else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+        else if (s > max3) { max3 = s; ind3 = i; }
+    }
+    if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+    else if (max3 < 0.1f * (float)max1) { ind3 = -1; }
+}
+
+/* rotation-histogram bin, e.g. reference src/ORBmatcher.cc:1294-1300 (factor = 1/HISTO_LENGTH) */
+__device__ __forceinline__ int rot_bin(float a1, float a2) {
+    float rot = a1 - a2;
+    if (rot < 0.0f) rot += 360.0f;
+    int bin = (int)roundf(rot * (1.0f / HISTO_LENGTH));
+    if (bin == HISTO_LENGTH) bin = 0;
+    return bin;
+}
+
+#define MT 256   /* threads per CTA of the search kernels */
+
+/* exclusive scan of a[0..n) in shared memory, in place; returns the total. All MT threads call. */
+__device__ int mt_excl_scan(uint32_t* a, int n, uint32_t* s_tmp /* [MT/32] */) {
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    uint32_t carry = 0;
+    for (int base = 0; base < n; base += MT) {
+        const int i = base + tid;
+        const uint32_t v = (i < n) ? a[i] : 0u;
+        uint32_t inc = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        if (lane == 31) s_tmp[wid] = inc;
+        __syncthreads();
+        uint32_t woff = 0, tot = 0;
+#pragma unroll
+        for (int w = 0; w < MT / 32; ++w) {
+            const uint32_t t = s_tmp[w];
+            if (w < wid) woff += t;
+            tot += t;
+        }
+        if (i < n) a[i] = carry + woff + inc - v;
+        carry += tot;
+        __syncthreads();
+    }
+    return (int)carry;
+}
+
+/* ================================================================== host-side staging */
+struct orbx_matcher {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    uint8_t *h_in = nullptr, *d_in = nullptr, *h_out = nullptr, *d_out = nullptr;
+    size_t in_cap = 0, out_cap = 0;
+    uint8_t* d_scratch = nullptr;
+    size_t scratch_cap = 0;
+    int last_launches = 0;
+    int knn_variant = 1;
+};
+
+struct Packer {
+    struct Item { const void* src; size_t bytes, off; };
+    std::vector<Item> items;
+    size_t total = 0;
+    size_t add(const void* src, size_t bytes) {      /* src == NULL: zero-filled */
+        const size_t off = total;
+        items.push_back({src, bytes, off});
+        total = orbx_align_up(total + bytes, 16);
+        return off;
+    }
+    void copy_to(uint8_t* base) const {
+        for (const Item& it : items) {
+            if (!it.bytes) continue;
+            if (it.src) memcpy(base + it.off, it.src, it.bytes);
+            else memset(base + it.off, 0, it.bytes);
+        }
+    }
+};
+
+static orbx_status ensure_io(orbx_matcher* m, size_t in_bytes, size_t out_bytes) {
+    if (in_bytes > m->in_cap) {
+        if (m->h_in) cudaFreeHost(m->h_in);
+        if (m->d_in) cudaFree(m->d_in);
+        m->h_in = m->d_in = nullptr; m->in_cap = 0;
+        const size_t cap = orbx_align_up(in_bytes + in_bytes / 2, 4096);
+        ORBX_CUDA(cudaMallocHost(&m->h_in, cap));
+        ORBX_CUDA(cudaMalloc(&m->d_in, cap));
+        m->in_cap = cap;
+    }
+    if (out_bytes > m->out_cap) {
+        if (m->h_out) cudaFreeHost(m->h_out);
+        if (m->d_out) cudaFree(m->d_out);
+        m->h_out = m->d_out = nullptr; m->out_cap = 0;
+        const size_t cap = orbx_align_up(out_bytes + out_bytes / 2, 4096);
+        ORBX_CUDA(cudaMallocHost(&m->h_out, cap));
+        ORBX_CUDA(cudaMalloc(&m->d_out, cap));
+        m->out_cap = cap;
+    }
+    return ORBX_OK;
+}
+
+static orbx_status ensure_scratch(orbx_matcher* m, size_t bytes) {
+    if (bytes > m->scratch_cap) {
+        if (m->d_scratch) cudaFree(m->d_scratch);
+        m->d_scratch = nullptr; m->scratch_cap = 0;
+        const size_t cap = orbx_align_up(bytes + bytes / 4, 4096);
+        ORBX_CUDA(cudaMalloc(&m->d_scratch, cap));
+        m->scratch_cap = cap;
+    }
+    return ORBX_OK;
+}
+
+extern "C" orbx_status orbx_matcher_create(int device, orbx_matcher** out) {
+    if (!out) { orbx_set_error("null argument"); return ORBX_ERR_INVALID; }
+    *out = nullptr;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= device || device < 0) {
+        orbx_set_error("no CUDA device %d (this library has no CPU fallback)", device);
+        return ORBX_ERR_CUDA;
+    }
+    ORBX_CUDA(cudaSetDevice(device));
+    orbx_matcher* m = new orbx_matcher;
+    m->device = device;
+    cudaError_t e = cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) { orbx_set_error("cudaStreamCreate -> %s", cudaGetErrorString(e)); delete m; return ORBX_ERR_CUDA; }
+    *out = m;
+    return ORBX_OK;
+}
+
+extern "C" void orbx_matcher_destroy(orbx_matcher* m) {
+    if (!m) return;
+    cudaSetDevice(m->device);
+    if (m->h_in) cudaFreeHost(m->h_in);
+    if (m->h_out) cudaFreeHost(m->h_out);
+    if (m->d_in) cudaFree(m->d_in);
+    if (m->d_out) cudaFree(m->d_out);
+    if (m->d_scratch) cudaFree(m->d_scratch);
+    if (m->stream) cudaStreamDestroy(m->stream);
+    delete m;
+}
+extern "C" void* orbx_matcher_stream(orbx_matcher* m) { return m ? (void*)m->stream : nullptr; }
+extern "C" int orbx_matcher_last_launches(const orbx_matcher* m) { return m ? m->last_launches : 0; }
+extern "C" orbx_status orbx_matcher_set_knn_variant(orbx_matcher* m, int v) {
+    if (!m || v < 0 || v > 1) { orbx_set_error("bad knn variant"); return ORBX_ERR_INVALID; }
+    m->knn_variant = v;
+    return ORBX_OK;
+}
+extern "C" orbx_status orbx_matcher_synchronize(orbx_matcher* m) {
+    if (!m) return ORBX_ERR_INVALID;
+    ORBX_CUDA(cudaSetDevice(m->device));
+    ORBX_CUDA(cudaStreamSynchronize(m->stream));
+    return ORBX_OK;
+}
+
+extern "C" orbx_status orbx_three_maxima(const int* counts, int L, int* ind1, int* ind2, int* ind3) {
+    if (!counts || L < 0 || !ind1 || !ind2 || !ind3) { orbx_set_error("null argument"); return ORBX_ERR_INVALID; }
+    three_maxima(counts, L, *ind1, *ind2, *ind3);
+    return ORBX_OK;
+}
+
+/* ================================================================== DescriptorDistance */
 __global__ void __launch_bounds__(256) k_hamming_pairs(const uint4* __restrict__ a, const uint4* __restrict__ b, int n,
                                                         int* __restrict__ out) {
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
@@ -32,5 +231,712 @@ extern "C" orbx_status orbx_hamming_pairs(const uint8_t* a, const uint8_t* b, in
     ORBX_CUDA(cudaGetLastError());
     ORBX_CUDA(cudaMemcpy(out, dout, (size_t)n * 4, cudaMemcpyDeviceToHost));
     cudaFree(da); cudaFree(db); cudaFree(dout);
+    return ORBX_OK;
+}
+
+/* ================================================================== SearchByProjection (both overloads) */
+struct SbpProb {
+    int n, nmp, gcols, grows, nlevels, mode, bFar, checkOri;
+    float minx, miny, gw_inv, gh_inv, th, thFar, nnRatio, pad;
+    unsigned long long kx, ky, koct, kangle, desc, claimed, scale;      /* offsets into the input arena */
+    unsigned long long mflag, mx, my, mlevel, maux, mdepth, mdesc;
+    unsigned long long out_match;                                       /* offset into the output arena */
+};
+
+/* One CTA per problem.
+ *  1. Frame grid (AssignFeaturesToGrid) as a CSR over the cells, built in shared memory.
+ *  2. Rounds of "every map point picks its best / second-best unclaimed candidate" until the
+ *     per-keypoint owner array stops changing.  Map point i treats keypoint k as claimed when
+ *     an EARLIER map point owned k in the previous round, so the fixed point is exactly the
+ *     reference's sequential result (round r fixes at least the first r map points).
+ *  3. KeyFrame overload: rotation histogram + ComputeThreeMaxima on the final matches.
+ * Candidate order of the reference (cell columns, then rows, then insertion order) only matters
+ * for ties; it is carried in the low bits of the 64-bit keys (dist << 32 | CSR position). */
+__global__ void __launch_bounds__(MT) k_search_by_projection(const uint8_t* __restrict__ in, uint8_t* __restrict__ out,
+                                                              const SbpProb* __restrict__ probs, int* __restrict__ counts) {
+    extern __shared__ __align__(16) uint32_t sm[];
+    __shared__ uint32_t s_tmp[MT / 32];
+    __shared__ int s_hist[HISTO_LENGTH];
+    __shared__ int s_ind[3];
+    __shared__ int s_count;
+
+    const SbpProb P = probs[blockIdx.x];
+    const int tid = threadIdx.x;
+    const int n = P.n, nmp = P.nmp, ncell = P.gcols * P.grows;
+    const float* kx = reinterpret_cast<const float*>(in + P.kx);
+    const float* ky = reinterpret_cast<const float*>(in + P.ky);
+    const int* koct = reinterpret_cast<const int*>(in + P.koct);
+    const float* kangle = reinterpret_cast<const float*>(in + P.kangle);
+    const uint4* kdesc = reinterpret_cast<const uint4*>(in + P.desc);
+    const uint8_t* claimed = in + P.claimed;
+    const float* scale = reinterpret_cast<const float*>(in + P.scale);
+    const uint8_t* mflag = in + P.mflag;
+    const float* mx = reinterpret_cast<const float*>(in + P.mx);
+    const float* my = reinterpret_cast<const float*>(in + P.my);
+    const int* mlevel = reinterpret_cast<const int*>(in + P.mlevel);
+    const float* maux = reinterpret_cast<const float*>(in + P.maux);
+    const float* mdepth = reinterpret_cast<const float*>(in + P.mdepth);
+    const uint4* mdesc = reinterpret_cast<const uint4*>(in + P.mdesc);
+    int* match = reinterpret_cast<int*>(out + P.out_match);
+
+    uint32_t* cell_start = sm;                        /* [ncell + 1], column-major cells (ix*grows + iy) */
+    uint32_t* cell_fill = cell_start + ncell + 1;     /* [ncell] */
+    uint32_t* owner_a = cell_fill + ncell;            /* [n] */
+    uint32_t* owner_b = owner_a + n;                  /* [n] */
+    unsigned short* csr = reinterpret_cast<unsigned short*>(owner_b + n);   /* [n] */
+
+    /* ---- 1. grid: PosInGrid + AssignFeaturesToGrid (reference src/Frame.cc:157-176, 470-480) */
+    for (int i = tid; i <= ncell; i += MT) cell_start[i] = 0;
+    if (tid < HISTO_LENGTH) s_hist[tid] = 0;
+    if (tid == 0) s_count = 0;
+    __syncthreads();
+    for (int i = tid; i < n; i += MT) {
+        const int px = (int)roundf((kx[i] - P.minx) * P.gw_inv);
+        const int py = (int)roundf((ky[i] - P.miny) * P.gh_inv);
+        const int lin = py * P.gcols + px;            /* computeLinearGridIndex: the reference's bound test */
+        /* lin in range does not imply px in range: the reference then files the keypoint under
+         * cell (lin % gcols, lin / gcols); reproduce that */
+        if (lin >= 0 && lin < ncell) atomicAdd(&cell_start[(lin % P.gcols) * P.grows + lin / P.gcols], 1u);
+    }
+    __syncthreads();
+    mt_excl_scan(cell_start, ncell + 1, s_tmp);
+    for (int i = tid; i < ncell; i += MT) cell_fill[i] = cell_start[i];
+    __syncthreads();
+    for (int i = tid; i < n; i += MT) {
+        const int px = (int)roundf((kx[i] - P.minx) * P.gw_inv);
+        const int py = (int)roundf((ky[i] - P.miny) * P.gh_inv);
+        const int lin = py * P.gcols + px;
+        if (lin >= 0 && lin < ncell) csr[atomicAdd(&cell_fill[(lin % P.gcols) * P.grows + lin / P.gcols], 1u)] = (unsigned short)i;
+    }
+    for (int i = tid; i < n; i += MT) owner_a[i] = 0xFFFFFFFFu;
+    __syncthreads();
+    /* push_back order inside a cell = keypoint index order: sort the (short) cell lists so that a
+     * CSR position is monotone in the reference's candidate order (columns, rows, insertion) */
+    for (int c = tid; c < ncell; c += MT) {
+        const int e0 = (int)cell_start[c], e1 = (int)cell_start[c + 1];
+        for (int a = e0 + 1; a < e1; ++a) {
+            const unsigned short v = csr[a];
+            int b = a - 1;
+            while (b >= e0 && csr[b] > v) { csr[b + 1] = csr[b]; --b; }
+            csr[b + 1] = v;
+        }
+    }
+    __syncthreads();
+
+    /* ---- 2. fixed-point rounds */
+    uint32_t* prev = owner_a;
+    uint32_t* cur = owner_b;
+    const bool bFactor = P.th != 1.0f;
+    for (int round = 0; round <= nmp; ++round) {
+        for (int i = tid; i < n; i += MT) cur[i] = 0xFFFFFFFFu;
+        __syncthreads();
+        for (int i = tid; i < nmp; i += MT) {
+            if (!mflag[i]) continue;
+            const int level = mlevel[i];
+            float r;
+            int minLevel, maxLevel;
+            if (P.mode == 0) {
+                if (P.bFar && mdepth[i] > P.thFar) continue;
+                r = ((double)maux[i] > 0.998) ? 2.5f : 4.0f;         /* RadiusByViewingCos :125-131 */
+                if (bFactor) r *= P.th;
+                r *= scale[level];
+                minLevel = level - 1; maxLevel = level;
+            } else {
+                r = P.th * scale[level];
+                minLevel = level - 1; maxLevel = level + 1;
+            }
+            const float x = mx[i], y = my[i];
+            /* GetFeaturesInArea, reference src/Frame.cc:404-468 */
+            const int c0 = max(0, (int)floorf((x - P.minx - r) * P.gw_inv));
+            if (c0 >= P.gcols) continue;
+            const int c1 = min(P.gcols - 1, (int)ceilf((x - P.minx + r) * P.gw_inv));
+            if (c1 < 0) continue;
+            const int r0 = max(0, (int)floorf((y - P.miny - r) * P.gh_inv));
+            if (r0 >= P.grows) continue;
+            const int r1 = min(P.grows - 1, (int)ceilf((y - P.miny + r) * P.gh_inv));
+            if (r1 < 0) continue;
+            const bool bCheckLevels = (minLevel > 0) || (maxLevel >= 0);
+            const uint4 q0 = __ldg(mdesc + 2 * i), q1 = __ldg(mdesc + 2 * i + 1);
+            unsigned long long b1 = ~0ull, b2 = ~0ull;
+            for (int ix = c0; ix <= c1; ++ix) {
+                const uint32_t e0 = cell_start[ix * P.grows + r0], e1 = cell_start[ix * P.grows + r1 + 1];
+                for (uint32_t e = e0; e < e1; ++e) {
+                    const int idx = csr[e];
+                    const int oc = koct[idx];
+                    if (bCheckLevels && (oc < minLevel || (maxLevel >= 0 && oc > maxLevel))) continue;
+                    if (!(fabsf(kx[idx] - x) < r && fabsf(ky[idx] - y) < r)) continue;
+                    if (claimed[idx] || prev[idx] < (uint32_t)i) continue;
+                    const int dist = hamming256(q0, q1, __ldg(kdesc + 2 * idx), __ldg(kdesc + 2 * idx + 1));
+                    if (dist >= 256) continue;                      /* bestDist / bestDist2 start at 256, strict < */
+                    const unsigned long long key = ((unsigned long long)dist << 32) | e;
+                    if (key < b1) { b2 = b1; b1 = key; }
+                    else if (key < b2) b2 = key;
+                }
+            }
+            if (b1 == ~0ull) continue;
+            const int bestDist = (int)(b1 >> 32), bestIdx = csr[(uint32_t)b1];
+            bool accept;
+            if (P.mode == 0) {
+                const int bestDist2 = (b2 == ~0ull) ? 256 : (int)(b2 >> 32);
+                const int bestLevel = koct[bestIdx];
+                const int bestLevel2 = (b2 == ~0ull) ? -1 : koct[csr[(uint32_t)b2]];
+                accept = bestDist <= TH_HIGH && !(bestLevel == bestLevel2 && (float)bestDist > P.nnRatio * (float)bestDist2);
+            } else {
+                accept = bestDist <= TH_HIGH;
+            }
+            if (accept) atomicMin(&cur[bestIdx], (uint32_t)i);
+        }
+        __syncthreads();
+        int changed = 0;
+        for (int i = tid; i < n; i += MT) changed |= (cur[i] != prev[i]);
+        uint32_t* t = prev; prev = cur; cur = t;
+        if (!__syncthreads_or(changed)) break;
+    }
+
+    /* ---- 3. results (+ rotation histogram for the KeyFrame overload, reference :1290-1322) */
+    const bool hist = P.mode == 1 && P.checkOri;
+    int mycount = 0;
+    for (int i = tid; i < n; i += MT) {
+        const uint32_t o = prev[i];
+        if (o != 0xFFFFFFFFu) {
+            ++mycount;
+            if (hist) atomicAdd(&s_hist[rot_bin(maux[o], kangle[i])], 1);
+        }
+    }
+    __syncthreads();
+    if (hist && tid == 0) three_maxima(s_hist, HISTO_LENGTH, s_ind[0], s_ind[1], s_ind[2]);
+    __syncthreads();
+    for (int i = tid; i < n; i += MT) {
+        const uint32_t o = prev[i];
+        int mval = (o == 0xFFFFFFFFu) ? -1 : (int)o;
+        if (hist && mval >= 0) {
+            const int bin = rot_bin(maux[o], kangle[i]);
+            if (bin != s_ind[0] && bin != s_ind[1] && bin != s_ind[2]) { mval = -1; --mycount; }
+        }
+        match[i] = mval;
+    }
+    if (mycount) atomicAdd(&s_count, mycount);
+    __syncthreads();
+    if (tid == 0) counts[blockIdx.x] = s_count;
+}
+
+static orbx_status run_sbp(orbx_matcher* m, int nprob, const orbx_frame_view* F, int mode, const orbx_mappoints* MP0,
+                           const orbx_kf_points* MP1, const uint8_t* const* claimed, float th, int bFar, float thFar,
+                           float nnRatio, int checkOri, int* const* match_mp, int* nmatches) {
+    if (!m || nprob < 0 || (nprob > 0 && (!F || (!MP0 && !MP1) || !match_mp || !nmatches))) {
+        orbx_set_error("null argument");
+        return ORBX_ERR_INVALID;
+    }
+    if (nprob == 0) return ORBX_OK;
+    ORBX_CUDA(cudaSetDevice(m->device));
+    Packer in, out;
+    std::vector<SbpProb> probs(nprob);
+    size_t smem = 0;
+    for (int p = 0; p < nprob; ++p) {
+        const orbx_frame_view& f = F[p];
+        SbpProb& P = probs[p];
+        memset(&P, 0, sizeof(P));
+        const int nmp = mode == 0 ? MP0[p].n : MP1[p].n;
+        if (f.n < 0 || f.n > 65535 || nmp < 0 || f.gcols < 1 || f.grows < 1 || (long long)f.gcols * f.grows > 65535 ||
+            f.nlevels < 1 || (f.n > 0 && (!f.kx || !f.ky || !f.koct || !f.desc)) || !f.scale ||
+            (mode == 1 && checkOri && f.n > 0 && !f.kangle)) {
+            orbx_set_error("problem %d: unsupported frame view (n <= 65535, gcols*grows <= 65535, non-null arrays)", p);
+            return ORBX_ERR_INVALID;
+        }
+        P.n = f.n; P.nmp = nmp; P.gcols = f.gcols; P.grows = f.grows; P.nlevels = f.nlevels; P.mode = mode;
+        P.bFar = bFar; P.checkOri = checkOri;
+        P.minx = f.minx; P.miny = f.miny; P.gw_inv = f.gw_inv; P.gh_inv = f.gh_inv;
+        P.th = th; P.thFar = thFar; P.nnRatio = nnRatio;
+        P.kx = in.add(f.kx, 4 * (size_t)f.n); P.ky = in.add(f.ky, 4 * (size_t)f.n);
+        P.koct = in.add(f.koct, 4 * (size_t)f.n);
+        P.kangle = in.add(f.kangle, f.kangle ? 4 * (size_t)f.n : 0);
+        P.desc = in.add(f.desc, 32 * (size_t)f.n);
+        P.claimed = in.add(claimed ? claimed[p] : nullptr, (size_t)f.n);
+        P.scale = in.add(f.scale, 4 * (size_t)f.nlevels);
+        if (mode == 0) {
+            const orbx_mappoints& M = MP0[p];
+            if (nmp > 0 && (!M.inview || !M.x || !M.y || !M.level || !M.viewcos || !M.desc || (bFar && !M.depth))) {
+                orbx_set_error("problem %d: null map-point array", p);
+                return ORBX_ERR_INVALID;
+            }
+            P.mflag = in.add(M.inview, nmp); P.mx = in.add(M.x, 4 * (size_t)nmp); P.my = in.add(M.y, 4 * (size_t)nmp);
+            P.mlevel = in.add(M.level, 4 * (size_t)nmp); P.maux = in.add(M.viewcos, 4 * (size_t)nmp);
+            P.mdepth = in.add(M.depth, M.depth ? 4 * (size_t)nmp : 0); P.mdesc = in.add(M.desc, 32 * (size_t)nmp);
+        } else {
+            const orbx_kf_points& M = MP1[p];
+            if (nmp > 0 && (!M.valid || !M.u || !M.v || !M.level || !M.desc || (checkOri && !M.angle))) {
+                orbx_set_error("problem %d: null keyframe-point array", p);
+                return ORBX_ERR_INVALID;
+            }
+            P.mflag = in.add(M.valid, nmp); P.mx = in.add(M.u, 4 * (size_t)nmp); P.my = in.add(M.v, 4 * (size_t)nmp);
+            P.mlevel = in.add(M.level, 4 * (size_t)nmp); P.maux = in.add(M.angle, M.angle ? 4 * (size_t)nmp : 0);
+            P.mdepth = in.add(nullptr, 0); P.mdesc = in.add(M.desc, 32 * (size_t)nmp);
+        }
+        /* map-point levels index mvScaleFactors: validate on the host, as a bad level is UB in the reference */
+        const int32_t* lv = mode == 0 ? MP0[p].level : MP1[p].level;
+        for (int i = 0; i < nmp; ++i)
+            if (lv[i] < 0 || lv[i] >= f.nlevels) { orbx_set_error("problem %d: map point %d level %d outside [0,%d)", p, i, lv[i], f.nlevels); return ORBX_ERR_INVALID; }
+        P.out_match = out.add(nullptr, 4 * (size_t)f.n);
+        smem = std::max(smem, (size_t)4 * (2 * (size_t)f.gcols * f.grows + 1 + 2 * (size_t)f.n) + 2 * (size_t)f.n + 16);
+    }
+    const size_t probs_off = in.add(probs.data(), sizeof(SbpProb) * (size_t)nprob);
+    const size_t counts_off = out.add(nullptr, 4 * (size_t)nprob);
+    if (smem > 200 * 1024) { orbx_set_error("frame grid + keypoints need %zu B of shared memory (> 200 KB)", smem); return ORBX_ERR_INVALID; }
+    orbx_status st = ensure_io(m, in.total, out.total);
+    if (st != ORBX_OK) return st;
+    in.copy_to(m->h_in);
+    ORBX_CUDA(cudaMemcpyAsync(m->d_in, m->h_in, in.total, cudaMemcpyHostToDevice, m->stream));
+    ORBX_CUDA(cudaFuncSetAttribute(k_search_by_projection, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max(smem, (size_t)48 * 1024)));
+    k_search_by_projection<<<nprob, MT, smem, m->stream>>>(m->d_in, m->d_out, reinterpret_cast<const SbpProb*>(m->d_in + probs_off),
+                                                           reinterpret_cast<int*>(m->d_out + counts_off));
+    ORBX_CUDA(cudaGetLastError());
+    m->last_launches = 1;
+    ORBX_CUDA(cudaMemcpyAsync(m->h_out, m->d_out, out.total, cudaMemcpyDeviceToHost, m->stream));
+    ORBX_CUDA(cudaStreamSynchronize(m->stream));
+    for (int p = 0; p < nprob; ++p) {
+        if (F[p].n > 0) memcpy(match_mp[p], m->h_out + probs[p].out_match, 4 * (size_t)F[p].n);
+        nmatches[p] = reinterpret_cast<const int*>(m->h_out + counts_off)[p];
+    }
+    return ORBX_OK;
+}
+
+extern "C" orbx_status orbx_search_by_projection(orbx_matcher* m, int nprob, const orbx_frame_view* F,
+                                                 const orbx_mappoints* MP, const uint8_t* const* claimed, float th,
+                                                 int bFarPoints, float thFarPoints, float nnRatio, int* const* match_mp,
+                                                 int* nmatches) {
+    return run_sbp(m, nprob, F, 0, MP, nullptr, claimed, th, bFarPoints, thFarPoints, nnRatio, 0, match_mp, nmatches);
+}
+
+extern "C" orbx_status orbx_search_by_projection_kf(orbx_matcher* m, int nprob, const orbx_frame_view* F,
+                                                    const orbx_kf_points* MP, const uint8_t* const* occupied, float th,
+                                                    int checkOrientation, int* const* match_mp, int* nmatches) {
+    return run_sbp(m, nprob, F, 1, nullptr, MP, occupied, th, 0, 0.f, 0.f, checkOrientation, match_mp, nmatches);
+}
+
+/* ================================================================== SearchForTriangulation */
+struct TriProb {
+    int n1, n2, ntasks, bOnlyStereo, bCoarse, checkOri, has_ur1, has_ur2;
+    float F12[9];
+    float epx, epy, pad;
+    unsigned long long kx1, ky1, kang1, desc1, hasmp1, ur1;
+    unsigned long long kx2, ky2, koct2, kang2, desc2, hasmp2, ur2, scale2, nidx2;
+    unsigned long long tasks;      /* int4 {idx1, off2, len2, 0}: the shared-node walk of :494-642, flattened on the host */
+    unsigned long long out_pairs;
+};
+
+/* One CTA per KeyFrame pair; one thread per keypoint of KF1 that shares a vocabulary node with
+ * KF2.  The inner loop is the reference's (:527-612) verbatim -- `dist > TH_LOW || dist >
+ * bestDist` keeps the LAST candidate among equal distances -- then the rotation histogram and
+ * an ordered compaction of vMatches12. */
+__global__ void __launch_bounds__(MT) k_search_for_triangulation(const uint8_t* __restrict__ in, uint8_t* __restrict__ out,
+                                                                  const TriProb* __restrict__ probs, int* __restrict__ counts) {
+    extern __shared__ __align__(16) uint32_t sm[];
+    __shared__ uint32_t s_tmp[MT / 32];
+    __shared__ int s_hist[HISTO_LENGTH];
+    __shared__ int s_ind[3];
+    const TriProb P = probs[blockIdx.x];
+    const int tid = threadIdx.x, n1 = P.n1;
+    const float* kx1 = reinterpret_cast<const float*>(in + P.kx1);
+    const float* ky1 = reinterpret_cast<const float*>(in + P.ky1);
+    const float* kang1 = reinterpret_cast<const float*>(in + P.kang1);
+    const uint4* desc1 = reinterpret_cast<const uint4*>(in + P.desc1);
+    const uint8_t* hasmp1 = in + P.hasmp1;
+    const float* ur1 = reinterpret_cast<const float*>(in + P.ur1);
+    const float* kx2 = reinterpret_cast<const float*>(in + P.kx2);
+    const float* ky2 = reinterpret_cast<const float*>(in + P.ky2);
+    const int* koct2 = reinterpret_cast<const int*>(in + P.koct2);
+    const float* kang2 = reinterpret_cast<const float*>(in + P.kang2);
+    const uint4* desc2 = reinterpret_cast<const uint4*>(in + P.desc2);
+    const uint8_t* hasmp2 = in + P.hasmp2;
+    const float* ur2 = reinterpret_cast<const float*>(in + P.ur2);
+    const float* scale2 = reinterpret_cast<const float*>(in + P.scale2);
+    const int* nidx2 = reinterpret_cast<const int*>(in + P.nidx2);
+    const int4* tasks = reinterpret_cast<const int4*>(in + P.tasks);
+    int* pairs = reinterpret_cast<int*>(out + P.out_pairs);
+
+    int* m12 = reinterpret_cast<int*>(sm);              /* vMatches12 [n1] */
+    uint32_t* flag = sm + n1;                           /* [n1] compaction scan */
+    for (int i = tid; i < n1; i += MT) m12[i] = -1;
+    if (tid < HISTO_LENGTH) s_hist[tid] = 0;
+    __syncthreads();
+
+    for (int t = tid; t < P.ntasks; t += MT) {
+        const int4 tk = tasks[t];
+        const int idx1 = tk.x;
+        if (hasmp1[idx1]) continue;
+        const bool bStereo1 = P.has_ur1 && ur1[idx1] >= 0;
+        if (P.bOnlyStereo && !bStereo1) continue;
+        const uint4 q0 = __ldg(desc1 + 2 * idx1), q1 = __ldg(desc1 + 2 * idx1 + 1);
+        /* epipolar line of kp1 in image 2 (Pinhole.cpp:112-115) */
+        const float x1 = kx1[idx1], y1 = ky1[idx1];
+        const float a = x1 * P.F12[0] + y1 * P.F12[3] + P.F12[6];
+        const float b = x1 * P.F12[1] + y1 * P.F12[4] + P.F12[7];
+        const float c = x1 * P.F12[2] + y1 * P.F12[5] + P.F12[8];
+        const float den = a * a + b * b;
+        int bestDist = TH_LOW, bestIdx2 = -1;
+        for (int k = 0; k < tk.z; ++k) {
+            const int idx2 = nidx2[tk.y + k];
+            if (hasmp2[idx2]) continue;                     /* vbMatched2 is never set (:485,537) */
+            const bool bStereo2 = P.has_ur2 && ur2[idx2] >= 0;
+            if (P.bOnlyStereo && !bStereo2) continue;
+            const int dist = hamming256(q0, q1, __ldg(desc2 + 2 * idx2), __ldg(desc2 + 2 * idx2 + 1));
+            if (dist > TH_LOW || dist > bestDist) continue;
+            const float x2 = kx2[idx2], y2 = ky2[idx2];
+            if (!bStereo1 && !bStereo2) {
+                const float distex = P.epx - x2, distey = P.epy - y2;
+                if (distex * distex + distey * distey < 100 * scale2[koct2[idx2]]) continue;
+            }
+            bool ok = false;
+            if (den != 0) {
+                const float num = a * x2 + b * y2 + c;
+                ok = num * num / den < 3.84f;               /* unc = 1.0 (:603) */
+            }
+            if (P.bCoarse || ok) { bestIdx2 = idx2; bestDist = dist; }
+        }
+        if (bestIdx2 >= 0) {
+            m12[idx1] = bestIdx2;
+            if (P.checkOri) atomicAdd(&s_hist[rot_bin(kang1[idx1], kang2[bestIdx2])], 1);
+        }
+    }
+    __syncthreads();
+    if (P.checkOri) {
+        if (tid == 0) three_maxima(s_hist, HISTO_LENGTH, s_ind[0], s_ind[1], s_ind[2]);
+        __syncthreads();
+        for (int i = tid; i < n1; i += MT) {
+            const int j = m12[i];
+            if (j >= 0) {
+                const int bin = rot_bin(kang1[i], kang2[j]);
+                if (bin != s_ind[0] && bin != s_ind[1] && bin != s_ind[2]) m12[i] = -1;
+            }
+        }
+        __syncthreads();
+    }
+    for (int i = tid; i < n1; i += MT) flag[i] = m12[i] >= 0;
+    __syncthreads();
+    const int total = mt_excl_scan(flag, n1, s_tmp);
+    for (int i = tid; i < n1; i += MT)
+        if (m12[i] >= 0) { pairs[2 * flag[i]] = i; pairs[2 * flag[i] + 1] = m12[i]; }
+    if (tid == 0) counts[blockIdx.x] = total;
+}
+
+extern "C" orbx_status orbx_search_for_triangulation(orbx_matcher* m, int nprob, const orbx_kf_view* k1,
+                                                     const orbx_kf_view* k2, const float* F12, const float* ep,
+                                                     const float* const* scale2, int bOnlyStereo, int bCoarse,
+                                                     int checkOrientation, int* const* pairs, int* npairs, int* nmatches) {
+    if (!m || nprob < 0 || (nprob > 0 && (!k1 || !k2 || !F12 || !ep || !scale2 || !pairs || !npairs))) {
+        orbx_set_error("null argument");
+        return ORBX_ERR_INVALID;
+    }
+    if (nprob == 0) return ORBX_OK;
+    ORBX_CUDA(cudaSetDevice(m->device));
+    Packer in, out;
+    std::vector<TriProb> probs(nprob);
+    std::vector<std::vector<int4>> tasks(nprob);
+    size_t smem = 0;
+    for (int p = 0; p < nprob; ++p) {
+        const orbx_kf_view &A = k1[p], &B = k2[p];
+        TriProb& P = probs[p];
+        memset(&P, 0, sizeof(P));
+        if (A.n < 0 || B.n < 0 || A.nnodes < 0 || B.nnodes < 0 ||
+            (A.n > 0 && (!A.kx || !A.ky || !A.desc || (checkOrientation && !A.kangle))) ||
+            (B.n > 0 && (!B.kx || !B.ky || !B.koct || !B.desc || (checkOrientation && !B.kangle))) ||
+            (A.nnodes > 0 && (!A.node_id || !A.node_off || !A.node_idx)) ||
+            (B.nnodes > 0 && (!B.node_id || !B.node_off || !B.node_idx)) || !scale2[p]) {
+            orbx_set_error("problem %d: null keyframe array", p);
+            return ORBX_ERR_INVALID;
+        }
+        /* lockstep walk over the two FeatureVectors (reference :494-500, 639-642) */
+        int f1 = 0, f2 = 0, max_oct = 0;
+        while (f1 < A.nnodes && f2 < B.nnodes) {
+            if (A.node_id[f1] == B.node_id[f2]) {
+                const int off2 = B.node_off[f2], len2 = B.node_off[f2 + 1] - off2;
+                for (int i1 = A.node_off[f1]; i1 < A.node_off[f1 + 1]; ++i1) {
+                    const int idx1 = A.node_idx[i1];
+                    if (idx1 < 0 || idx1 >= A.n) { orbx_set_error("problem %d: node index out of range", p); return ORBX_ERR_INVALID; }
+                    tasks[p].push_back(make_int4(idx1, off2, len2, 0));
+                }
+                ++f1; ++f2;
+            } else if (A.node_id[f1] < B.node_id[f2]) {
+                while (f1 < A.nnodes && A.node_id[f1] < B.node_id[f2]) ++f1;
+            } else {
+                while (f2 < B.nnodes && B.node_id[f2] < A.node_id[f1]) ++f2;
+            }
+        }
+        const int nidx2 = B.nnodes > 0 ? B.node_off[B.nnodes] : 0;
+        for (int i = 0; i < nidx2; ++i)
+            if (B.node_idx[i] < 0 || B.node_idx[i] >= B.n) { orbx_set_error("problem %d: node index out of range", p); return ORBX_ERR_INVALID; }
+        for (int i = 0; i < B.n; ++i) max_oct = std::max(max_oct, (int)B.koct[i]);
+        P.n1 = A.n; P.n2 = B.n; P.ntasks = (int)tasks[p].size();
+        P.bOnlyStereo = bOnlyStereo; P.bCoarse = bCoarse; P.checkOri = checkOrientation;
+        P.has_ur1 = A.uright != nullptr; P.has_ur2 = B.uright != nullptr;
+        memcpy(P.F12, F12 + 9 * (size_t)p, sizeof(float) * 9);
+        P.epx = ep[2 * p]; P.epy = ep[2 * p + 1];
+        P.kx1 = in.add(A.kx, 4 * (size_t)A.n); P.ky1 = in.add(A.ky, 4 * (size_t)A.n);
+        P.kang1 = in.add(A.kangle, A.kangle ? 4 * (size_t)A.n : 0); P.desc1 = in.add(A.desc, 32 * (size_t)A.n);
+        P.hasmp1 = in.add(A.has_mp, (size_t)A.n); P.ur1 = in.add(A.uright, A.uright ? 4 * (size_t)A.n : 0);
+        P.kx2 = in.add(B.kx, 4 * (size_t)B.n); P.ky2 = in.add(B.ky, 4 * (size_t)B.n);
+        P.koct2 = in.add(B.koct, 4 * (size_t)B.n);
+        P.kang2 = in.add(B.kangle, B.kangle ? 4 * (size_t)B.n : 0); P.desc2 = in.add(B.desc, 32 * (size_t)B.n);
+        P.hasmp2 = in.add(B.has_mp, (size_t)B.n); P.ur2 = in.add(B.uright, B.uright ? 4 * (size_t)B.n : 0);
+        P.scale2 = in.add(scale2[p], 4 * (size_t)(max_oct + 1));
+        P.nidx2 = in.add(B.node_idx, 4 * (size_t)nidx2);
+        P.tasks = in.add(tasks[p].data(), sizeof(int4) * tasks[p].size());
+        P.out_pairs = out.add(nullptr, 8 * (size_t)A.n);
+        smem = std::max(smem, (size_t)8 * A.n + 16);
+    }
+    const size_t probs_off = in.add(probs.data(), sizeof(TriProb) * (size_t)nprob);
+    const size_t counts_off = out.add(nullptr, 4 * (size_t)nprob);
+    if (smem > 200 * 1024) { orbx_set_error("keyframe too large for the shared-memory match table"); return ORBX_ERR_INVALID; }
+    orbx_status st = ensure_io(m, in.total, out.total);
+    if (st != ORBX_OK) return st;
+    in.copy_to(m->h_in);
+    ORBX_CUDA(cudaMemcpyAsync(m->d_in, m->h_in, in.total, cudaMemcpyHostToDevice, m->stream));
+    ORBX_CUDA(cudaFuncSetAttribute(k_search_for_triangulation, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max(smem, (size_t)48 * 1024)));
+    k_search_for_triangulation<<<nprob, MT, smem, m->stream>>>(m->d_in, m->d_out, reinterpret_cast<const TriProb*>(m->d_in + probs_off),
+                                                               reinterpret_cast<int*>(m->d_out + counts_off));
+    ORBX_CUDA(cudaGetLastError());
+    m->last_launches = 1;
+    ORBX_CUDA(cudaMemcpyAsync(m->h_out, m->d_out, out.total, cudaMemcpyDeviceToHost, m->stream));
+    ORBX_CUDA(cudaStreamSynchronize(m->stream));
+    for (int p = 0; p < nprob; ++p) {
+        const int np = reinterpret_cast<const int*>(m->h_out + counts_off)[p];
+        npairs[p] = np;
+        if (nmatches) nmatches[p] = np;      /* nmatches == surviving entries of vMatches12 (:614-668) */
+        if (np > 0) memcpy(pairs[p], m->h_out + probs[p].out_pairs, 8 * (size_t)np);
+    }
+    return ORBX_OK;
+}
+
+/* ================================================================== brute-force 2-NN */
+/* Every thread keeps KNN_QPT query descriptors in registers; the database streams through
+ * shared memory in KNN_TILE-row tiles fetched by TMA bulk copies (cp.async.bulk, completion on
+ * an mbarrier) KNN_STAGES deep, and every thread of a warp reads the same database row (LDS
+ * broadcast).  Distances: 8 XOR + either 8 POPC, or a carry-save-adder tree (8 LOP3) + 4 POPC --
+ * POPC issues at a quarter of the LOP3 rate.  The running top-2 lives in registers as packed
+ * (dist << 22 | row) keys and is only touched when a distance beats the query's current
+ * second-best (rare after the first few hundred rows), so the steady-state loop is
+ * LDS + LOP3 + POPC + one compare per pair.  Rows are visited in ascending order and updates use
+ * a strict <, i.e. ties go to the lowest index (= the packed-key order). */
+#define KNN_THREADS 256
+#define KNN_QPT 4
+#define KNN_TILE 256
+#define KNN_STAGES 3
+#define KNN_SPLIT_ROWS (1 << 22)    /* rows per grid.y slice: row index fits the 22-bit key field */
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    do {
+        asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+                     : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    } while (!ok);
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+template <int VARIANT>
+__device__ __forceinline__ int knn_dist(const uint32_t (&q)[8], const uint4 a, const uint4 b) {
+    const uint32_t w0 = q[0] ^ a.x, w1 = q[1] ^ a.y, w2 = q[2] ^ a.z, w3 = q[3] ^ a.w;
+    const uint32_t w4 = q[4] ^ b.x, w5 = q[5] ^ b.y, w6 = q[6] ^ b.z, w7 = q[7] ^ b.w;
+    if (VARIANT == 0) {
+        return __popc(w0) + __popc(w1) + __popc(w2) + __popc(w3) + __popc(w4) + __popc(w5) + __popc(w6) + __popc(w7);
+    } else {
+        /* w0..w6 = s3 + 2*(c1 + c2 + c3) = s3 + 2*s5 + 4*c5 bit-column-wise */
+        const uint32_t s1 = XOR3(w0, w1, w2), c1 = MAJ3(w0, w1, w2);
+        const uint32_t s2 = XOR3(w3, w4, w5), c2 = MAJ3(w3, w4, w5);
+        const uint32_t s3 = XOR3(s1, s2, w6), c3 = MAJ3(s1, s2, w6);
+        const uint32_t s5 = XOR3(c1, c2, c3), c5 = MAJ3(c1, c2, c3);
+        return __popc(s3) + __popc(w7) + 2 * __popc(s5) + 4 * __popc(c5);
+    }
+}
+
+template <int VARIANT>
+__global__ void __launch_bounds__(KNN_THREADS) k_knn2(const uint4* __restrict__ q, int nq, const uint4* __restrict__ db, int ndb,
+                                                       long long index_base, unsigned long long* __restrict__ keys /* [gridDim.y][nq][2] */) {
+    __shared__ __align__(128) uint4 s_tile[KNN_STAGES][KNN_TILE * 2];
+    __shared__ __align__(8) uint64_t s_full[KNN_STAGES];
+    const int tid = threadIdx.x;
+    const int row0 = blockIdx.y * KNN_SPLIT_ROWS;
+    const int nrows = min(ndb - row0, KNN_SPLIT_ROWS);
+    const int ntiles = (nrows + KNN_TILE - 1) / KNN_TILE;
+    const uint4* dbs = db + 2 * (size_t)row0;
+
+    if (tid == 0) {
+        for (int s = 0; s < KNN_STAGES; ++s) mbar_init(&s_full[s], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (tid == 0) {
+        for (int s = 0; s < KNN_STAGES && s < ntiles; ++s) {
+            const uint32_t bytes = (uint32_t)min(KNN_TILE, nrows - s * KNN_TILE) * 32u;
+            mbar_expect_tx(&s_full[s], bytes);
+            bulk_g2s(s_tile[s], dbs + 2 * (size_t)s * KNN_TILE, bytes, &s_full[s]);
+        }
+    }
+
+    uint32_t qr[KNN_QPT][8];
+    uint32_t b1[KNN_QPT], b2[KNN_QPT];
+    int thr[KNN_QPT];
+    const int qbase = blockIdx.x * (KNN_THREADS * KNN_QPT);
+#pragma unroll
+    for (int k = 0; k < KNN_QPT; ++k) {
+        const int qi = min(qbase + k * KNN_THREADS + tid, nq - 1);
+        const uint4 a = __ldg(q + 2 * (size_t)qi), b = __ldg(q + 2 * (size_t)qi + 1);
+        qr[k][0] = a.x; qr[k][1] = a.y; qr[k][2] = a.z; qr[k][3] = a.w;
+        qr[k][4] = b.x; qr[k][5] = b.y; qr[k][6] = b.z; qr[k][7] = b.w;
+        b1[k] = b2[k] = 0xFFFFFFFFu;
+        thr[k] = 1023;
+    }
+
+    for (int t = 0; t < ntiles; ++t) {
+        const int s = t % KNN_STAGES;
+        mbar_wait(&s_full[s], (uint32_t)(t / KNN_STAGES) & 1u);
+        const int cnt = min(KNN_TILE, nrows - t * KNN_TILE);
+        const uint4* tile = s_tile[s];
+        const int jb = t * KNN_TILE;
+#pragma unroll 2
+        for (int j = 0; j < cnt; ++j) {
+            const uint4 d0 = tile[2 * j], d1 = tile[2 * j + 1];
+            int dist[KNN_QPT];
+            bool any = false;
+#pragma unroll
+            for (int k = 0; k < KNN_QPT; ++k) {
+                dist[k] = knn_dist<VARIANT>(qr[k], d0, d1);
+                any |= dist[k] < thr[k];
+            }
+            if (any) {
+#pragma unroll
+                for (int k = 0; k < KNN_QPT; ++k) {
+                    if (dist[k] < thr[k]) {
+                        const uint32_t key = ((uint32_t)dist[k] << 22) | (uint32_t)(jb + j);
+                        b2[k] = min(b2[k], max(b1[k], key));
+                        b1[k] = min(b1[k], key);
+                        thr[k] = (int)(b2[k] >> 22);
+                    }
+                }
+            }
+        }
+        __syncthreads();                                   /* everyone is done with stage s */
+        if (tid == 0 && t + KNN_STAGES < ntiles) {
+            const int tn = t + KNN_STAGES;
+            const uint32_t bytes = (uint32_t)min(KNN_TILE, nrows - tn * KNN_TILE) * 32u;
+            mbar_expect_tx(&s_full[s], bytes);
+            bulk_g2s(s_tile[s], dbs + 2 * (size_t)tn * KNN_TILE, bytes, &s_full[s]);
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < KNN_QPT; ++k) {
+        const int qi = qbase + k * KNN_THREADS + tid;
+        if (qi < nq) {
+            unsigned long long* o = keys + ((size_t)blockIdx.y * nq + qi) * 2;
+            const unsigned long long base = (unsigned long long)(index_base + row0);
+            o[0] = b1[k] == 0xFFFFFFFFu ? ~0ull : (((unsigned long long)(b1[k] >> 22) << 32) | (base + (b1[k] & 0x3FFFFFu)));
+            o[1] = b2[k] == 0xFFFFFFFFu ? ~0ull : (((unsigned long long)(b2[k] >> 22) << 32) | (base + (b2[k] & 0x3FFFFFu)));
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256) k_knn2_merge(const unsigned long long* __restrict__ parts, int nparts, int nq, float ratio,
+                                                     int* __restrict__ d1, int* __restrict__ i1, int* __restrict__ d2,
+                                                     int* __restrict__ i2, uint8_t* __restrict__ pass,
+                                                     unsigned long long* __restrict__ keys_out) {
+    for (int qi = blockIdx.x * blockDim.x + threadIdx.x; qi < nq; qi += gridDim.x * blockDim.x) {
+        unsigned long long a = ~0ull, b = ~0ull;
+        for (int p = 0; p < nparts; ++p) {
+            const ulonglong2 v = *reinterpret_cast<const ulonglong2*>(parts + ((size_t)p * nq + qi) * 2);
+            if (v.x < a) { b = a; a = v.x; } else if (v.x < b) b = v.x;
+            if (v.y < a) { b = a; a = v.y; } else if (v.y < b) b = v.y;
+        }
+        const int dd1 = a == ~0ull ? 257 : (int)(a >> 32), dd2 = b == ~0ull ? 257 : (int)(b >> 32);
+        if (d1) d1[qi] = dd1;
+        if (i1) i1[qi] = a == ~0ull ? -1 : (int)(a & 0xFFFFFFFFull);
+        if (d2) d2[qi] = dd2;
+        if (i2) i2[qi] = b == ~0ull ? -1 : (int)(b & 0xFFFFFFFFull);
+        if (pass) pass[qi] = (float)dd1 < ratio * (float)dd2;
+        if (keys_out) { keys_out[2 * (size_t)qi] = a; keys_out[2 * (size_t)qi + 1] = b; }
+    }
+}
+
+static int knn_splits(int ndb) { return std::max(1, (int)(((long long)ndb + KNN_SPLIT_ROWS - 1) / KNN_SPLIT_ROWS)); }
+
+extern "C" orbx_status orbx_knn2_device(orbx_matcher* m, const void* d_q, int nq, const void* d_db, int ndb,
+                                        long long index_base, unsigned long long* d_keys) {
+    if (!m || nq < 0 || ndb < 0 || (nq > 0 && (!d_q || !d_keys)) || (ndb > 0 && !d_db) || index_base < 0 ||
+        index_base + ndb > 0xFFFFFFFFll) {
+        orbx_set_error("bad kNN arguments");
+        return ORBX_ERR_INVALID;
+    }
+    if (nq == 0) return ORBX_OK;
+    ORBX_CUDA(cudaSetDevice(m->device));
+    const int ns = knn_splits(ndb);
+    unsigned long long* part = d_keys;
+    if (ns > 1) {
+        orbx_status st = ensure_scratch(m, (size_t)ns * nq * 16);
+        if (st != ORBX_OK) return st;
+        part = reinterpret_cast<unsigned long long*>(m->d_scratch);
+    }
+    const dim3 grid((nq + KNN_THREADS * KNN_QPT - 1) / (KNN_THREADS * KNN_QPT), ns);
+    if (m->knn_variant == 0)
+        k_knn2<0><<<grid, KNN_THREADS, 0, m->stream>>>((const uint4*)d_q, nq, (const uint4*)d_db, ndb, index_base, part);
+    else
+        k_knn2<1><<<grid, KNN_THREADS, 0, m->stream>>>((const uint4*)d_q, nq, (const uint4*)d_db, ndb, index_base, part);
+    m->last_launches = 1;
+    if (ns > 1) {
+        k_knn2_merge<<<std::min((nq + 255) / 256, 148 * 8), 256, 0, m->stream>>>(part, ns, nq, 0.f, nullptr, nullptr, nullptr, nullptr,
+                                                                                   nullptr, d_keys);
+        m->last_launches = 2;
+    }
+    ORBX_CUDA(cudaGetLastError());
+    return ORBX_OK;
+}
+
+extern "C" orbx_status orbx_knn2_merge_device(orbx_matcher* m, const unsigned long long* d_parts, int nparts, int nq,
+                                              float ratio, int* d_d1, int* d_i1, int* d_d2, int* d_i2, uint8_t* d_pass) {
+    if (!m || nparts < 1 || nq < 0 || (nq > 0 && !d_parts)) { orbx_set_error("bad kNN merge arguments"); return ORBX_ERR_INVALID; }
+    if (nq == 0) return ORBX_OK;
+    ORBX_CUDA(cudaSetDevice(m->device));
+    k_knn2_merge<<<std::min((nq + 255) / 256, 148 * 8), 256, 0, m->stream>>>(d_parts, nparts, nq, ratio, d_d1, d_i1, d_d2, d_i2, d_pass,
+                                                                               nullptr);
+    ORBX_CUDA(cudaGetLastError());
+    m->last_launches = 1;
+    return ORBX_OK;
+}
+
+extern "C" orbx_status orbx_knn2(orbx_matcher* m, const uint8_t* q, int nq, const uint8_t* db, int ndb, float ratio, int* d1,
+                                 int* i1, int* d2, int* i2, uint8_t* pass) {
+    if (!m || nq < 0 || ndb < 0 || (nq > 0 && !q) || (ndb > 0 && !db)) { orbx_set_error("null argument"); return ORBX_ERR_INVALID; }
+    if (nq == 0) return ORBX_OK;
+    ORBX_CUDA(cudaSetDevice(m->device));
+    /* input arena: queries | database; output arena: d1 i1 d2 i2 pass; keys in scratch-free device memory */
+    const size_t qb = orbx_align_up((size_t)nq * 32, 256), dbb = orbx_align_up((size_t)ndb * 32, 256);
+    const size_t ob = orbx_align_up((size_t)nq * 4, 256);
+    orbx_status st = ensure_io(m, qb + dbb + 256, 5 * ob + (size_t)nq * 16 + 256);
+    if (st != ORBX_OK) return st;
+    memcpy(m->h_in, q, (size_t)nq * 32);
+    if (ndb) memcpy(m->h_in + qb, db, (size_t)ndb * 32);
+    ORBX_CUDA(cudaMemcpyAsync(m->d_in, m->h_in, qb + dbb, cudaMemcpyHostToDevice, m->stream));
+    unsigned long long* d_keys = reinterpret_cast<unsigned long long*>(m->d_out + 5 * ob);
+    st = orbx_knn2_device(m, m->d_in, nq, m->d_in + qb, ndb, 0, d_keys);
+    if (st != ORBX_OK) return st;
+    const int l0 = m->last_launches;
+    st = orbx_knn2_merge_device(m, d_keys, 1, nq, ratio, (int*)(m->d_out), (int*)(m->d_out + ob), (int*)(m->d_out + 2 * ob),
+                                (int*)(m->d_out + 3 * ob), m->d_out + 4 * ob);
+    if (st != ORBX_OK) return st;
+    m->last_launches += l0;
+    ORBX_CUDA(cudaMemcpyAsync(m->h_out, m->d_out, 5 * ob, cudaMemcpyDeviceToHost, m->stream));
+    ORBX_CUDA(cudaStreamSynchronize(m->stream));
+    if (d1) memcpy(d1, m->h_out, (size_t)nq * 4);
+    if (i1) memcpy(i1, m->h_out + ob, (size_t)nq * 4);
+    if (d2) memcpy(d2, m->h_out + 2 * ob, (size_t)nq * 4);
+    if (i2) memcpy(i2, m->h_out + 3 * ob, (size_t)nq * 4);
+    if (pass) memcpy(pass, m->h_out + 4 * ob, (size_t)nq);
     return ORBX_OK;
 }

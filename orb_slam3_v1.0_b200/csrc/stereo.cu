@@ -1,0 +1,344 @@
+/*
+ * stereo.cu -- Frame::ComputeStereoMatches for B200 (sm_100a), behind include/orbx.h.
+ *
+ * Target semantics: upstream ORB-SLAM3 v1.0 Frame::ComputeStereoMatches.
+ * The fork under /root/reference removed the stereo path (include/Frame.h:53-62 has only the
+ * mono constructor; src/Frame.cc:89-90 fills mvuRight with -1), so the citable anchors are the
+ * constants TH_HIGH/TH_LOW (include/ORBmatcher.h:73-74), DescriptorDistance
+ * (src/ORBmatcher.cc:1375-1391) and the pyramid / scale tables of ORBextractor
+ * (src/ORBextractor.cc:92-108, 587-623).
+ *
+ * One CTA per stereo pair, working on the device-resident outputs of the extractor (no host
+ * round trip between extraction and stereo matching):
+ *   1. vRowIndices: CSR of right keypoints per image row (+-2*scale rows each), shared memory
+ *      counters + a global index list;
+ *   2. one warp per left keypoint: lanes scan the row's candidates (octave +-1, uR in
+ *      [uL-maxD, uL]) for the best Hamming distance as a packed (dist, iR) key -- first minimum
+ *      in iR order, as the reference's strict `<` over an ascending list gives -- then the
+ *      11x11 SAD over +-5 px at the keypoint's pyramid level (121 row-tasks spread over the
+ *      lanes), parabola fit, disparity/depth;
+ *   3. median of the accepted SADs by a two-level shared-memory histogram select, and the
+ *      1.5*1.4*median outlier cut.
+ */
+#include <cuda_runtime.h>
+#include <limits.h>
+#include <string.h>
+
+#include <algorithm>
+
+#include "orbx_internal.h"
+#include "extractor_state.h"
+
+#define ST_THREADS 256
+#define TH_LOW 30
+#define TH_HIGH 100
+
+struct PyrLv { const uint8_t* base; unsigned long long frame_bytes; int pitch, w, h, pad; };
+struct StereoSide {
+    const orbx_keypoint* kps;
+    const uint8_t* desc;
+    const int* nk;
+    int kcap, nlevels;
+    PyrLv lv[ORBX_MAX_LEVELS];
+};
+struct StereoTables { float scale[ORBX_MAX_LEVELS], inv_scale[ORBX_MAX_LEVELS]; };
+
+__device__ __forceinline__ int st_hamming(const uint4 a0, const uint4 a1, const uint4 b0, const uint4 b1) {
+    return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
+           __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+}
+
+__device__ __forceinline__ const uint8_t* st_px(const PyrLv& L, int f, int x, int y) {
+    return L.base + (size_t)f * L.frame_bytes + (size_t)(y + ORBX_EDGE) * L.pitch + ORBX_XOFF + x;
+}
+
+__global__ void __launch_bounds__(ST_THREADS) k_stereo(StereoSide SL, StereoSide SR, StereoTables TB,
+                                                        const int* __restrict__ pairs, int pair_stride, float mbf, float mb,
+                                                        unsigned short* __restrict__ rowent, size_t rowent_per_pair,
+                                                        float* __restrict__ uright, float* __restrict__ depth) {
+    extern __shared__ __align__(16) uint32_t sm[];
+    __shared__ uint32_t s_tmp[ST_THREADS / 32];
+    __shared__ int s_sadw[ST_THREADS / 32][12];
+    __shared__ int s_h1[256], s_h2[128];
+    __shared__ int s_sel[3];
+
+    const int p = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int fL = pairs[p], fR = pairs[pair_stride + p];
+    const int nL = SL.nk[fL], nR = SR.nk[fR];
+    const int nRows = SL.lv[0].h;
+    const orbx_keypoint* kL = SL.kps + (size_t)fL * SL.kcap;
+    const orbx_keypoint* kR = SR.kps + (size_t)fR * SR.kcap;
+    const uint4* dL = reinterpret_cast<const uint4*>(SL.desc + (size_t)fL * SL.kcap * 32);
+    const uint4* dR = reinterpret_cast<const uint4*>(SR.desc + (size_t)fR * SR.kcap * 32);
+    float* oU = uright + (size_t)p * SL.kcap;
+    float* oD = depth + (size_t)p * SL.kcap;
+    unsigned short* ent = rowent + (size_t)p * rowent_per_pair;
+
+    uint32_t* row_start = sm;                      /* [nRows + 1] */
+    uint32_t* row_fill = row_start + nRows + 1;    /* [nRows] */
+    int* sad = reinterpret_cast<int*>(row_fill + nRows);   /* [kcap] accepted bestSAD or -1 */
+
+    for (int i = tid; i <= nRows; i += ST_THREADS) row_start[i] = 0;
+    for (int i = tid; i < SL.kcap; i += ST_THREADS) { sad[i] = -1; oU[i] = -1.0f; oD[i] = -1.0f; }
+    s_h1[tid] = 0;
+    if (tid < 128) s_h2[tid] = 0;
+    __syncthreads();
+
+    /* ---- 1. vRowIndices */
+    for (int iR = tid; iR < nR; iR += ST_THREADS) {
+        const float kpY = kR[iR].y;
+        const float r = 2.0f * TB.scale[kR[iR].octave];
+        const int maxr = min((int)ceilf(kpY + r), nRows - 1), minr = max((int)floorf(kpY - r), 0);
+        for (int yi = minr; yi <= maxr; ++yi) atomicAdd(&row_start[yi], 1u);
+    }
+    __syncthreads();
+    {
+        /* exclusive scan over nRows + 1 counters */
+        uint32_t carry = 0;
+        for (int base = 0; base <= nRows; base += ST_THREADS) {
+            const int i = base + tid;
+            const uint32_t v = (i <= nRows) ? row_start[i] : 0u;
+            uint32_t inc = v;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+                if (lane >= o) inc += t;
+            }
+            if (lane == 31) s_tmp[wid] = inc;
+            __syncthreads();
+            uint32_t woff = 0, tot = 0;
+#pragma unroll
+            for (int w = 0; w < ST_THREADS / 32; ++w) {
+                const uint32_t t = s_tmp[w];
+                if (w < wid) woff += t;
+                tot += t;
+            }
+            if (i <= nRows) row_start[i] = carry + woff + inc - v;
+            carry += tot;
+            __syncthreads();
+        }
+    }
+    for (int i = tid; i < nRows; i += ST_THREADS) row_fill[i] = row_start[i];
+    __syncthreads();
+    for (int iR = tid; iR < nR; iR += ST_THREADS) {
+        const float kpY = kR[iR].y;
+        const float r = 2.0f * TB.scale[kR[iR].octave];
+        const int maxr = min((int)ceilf(kpY + r), nRows - 1), minr = max((int)floorf(kpY - r), 0);
+        for (int yi = minr; yi <= maxr; ++yi) ent[atomicAdd(&row_fill[yi], 1u)] = (unsigned short)iR;
+    }
+    __syncthreads();
+
+    /* ---- 2. per left keypoint: row-band Hamming search + SAD refinement */
+    const float minZ = mb, minD = 0.f, maxD = mbf / minZ;
+    const int thOrbDist = (TH_HIGH + TH_LOW) / 2;
+    int* sadw = s_sadw[wid];
+    for (int iL = wid; iL < nL; iL += ST_THREADS / 32) {
+        const orbx_keypoint kp = kL[iL];
+        const int levelL = kp.octave;
+        const float vL = kp.y, uL = kp.x;
+        const int row = (int)vL;
+        if (row < 0 || row >= nRows) continue;
+        const uint32_t e0 = row_start[row], e1 = row_start[row + 1];
+        if (e0 == e1) continue;
+        const float minU = uL - maxD, maxU = uL - minD;
+        if (maxU < 0) continue;
+        const uint4 q0 = __ldg(dL + 2 * iL), q1 = __ldg(dL + 2 * iL + 1);
+        uint32_t best = 0xFFFFFFFFu;
+        for (uint32_t e = e0 + lane; e < e1; e += 32) {
+            const int iR = ent[e];
+            const int oc = kR[iR].octave;
+            if (oc < levelL - 1 || oc > levelL + 1) continue;
+            const float uR = kR[iR].x;
+            if (uR >= minU && uR <= maxU) {
+                const int dist = st_hamming(q0, q1, __ldg(dR + 2 * iR), __ldg(dR + 2 * iR + 1));
+                if (dist < TH_HIGH) best = min(best, ((uint32_t)dist << 16) | (uint32_t)iR);
+            }
+        }
+        best = __reduce_min_sync(0xffffffffu, best);
+        if (best == 0xFFFFFFFFu) continue;
+        const int bestDist = (int)(best >> 16), bestIdxR = (int)(best & 0xFFFFu);
+        if (!(bestDist < thOrbDist)) continue;
+
+        const float uR0 = kR[bestIdxR].x;
+        const float scaleFactor = TB.inv_scale[levelL];
+        const float scaleduL = roundf(uL * scaleFactor);
+        const float scaledvL = roundf(vL * scaleFactor);
+        const float scaleduR0 = roundf(uR0 * scaleFactor);
+        const int w = 5, Lw = 5;
+        const PyrLv& PL = SL.lv[levelL];
+        const PyrLv& PR = SR.lv[levelL];
+        const float iniu = scaleduR0 + Lw - w, endu = scaleduR0 + Lw + w + 1;
+        if (iniu < 0 || endu >= PR.w) continue;
+        const int y0 = (int)(scaledvL - w), xl0 = (int)(scaleduL - w), xr00 = (int)(scaleduR0 - w);
+        if (lane < 11) sadw[lane] = 0;
+        __syncwarp();
+        for (int t = lane; t < 121; t += 32) {
+            const int yy = t / 11, inc = t - yy * 11 - Lw;
+            const uint8_t* a = st_px(PL, fL, xl0, y0 + yy);
+            const uint8_t* b = st_px(PR, fR, xr00 + inc, y0 + yy);
+            int s = 0;
+#pragma unroll
+            for (int xx = 0; xx < 11; ++xx) s += abs((int)a[xx] - (int)b[xx]);
+            atomicAdd(&sadw[inc + Lw], s);
+        }
+        __syncwarp();
+        if (lane == 0) {
+            int bestSAD = INT_MAX, bestincR = 0;
+            for (int k = 0; k < 11; ++k)
+                if (sadw[k] < bestSAD) { bestSAD = sadw[k]; bestincR = k - Lw; }
+            if (bestincR != -Lw && bestincR != Lw) {
+                const float dist1 = (float)sadw[Lw + bestincR - 1], dist2 = (float)sadw[Lw + bestincR], dist3 = (float)sadw[Lw + bestincR + 1];
+                const float deltaR = (dist1 - dist3) / (2.0f * (dist1 + dist3 - 2.0f * dist2));
+                if (!(deltaR < -1 || deltaR > 1)) {
+                    float bestuR = TB.scale[levelL] * (scaleduR0 + (float)bestincR + deltaR);
+                    float disparity = uL - bestuR;
+                    if (disparity >= minD && disparity < maxD) {
+                        if (disparity <= 0) { disparity = 0.01f; bestuR = (float)((double)uL - 0.01); }
+                        oD[iL] = mbf / disparity;
+                        oU[iL] = bestuR;
+                        sad[iL] = bestSAD;
+                    }
+                }
+            }
+        }
+        __syncwarp();
+    }
+    __syncthreads();
+
+    /* ---- 3. median of the accepted SADs (vDistIdx[size/2].first) + outlier cut */
+    for (int i = tid; i < nL; i += ST_THREADS) {
+        const int s = sad[i];
+        if (s >= 0) atomicAdd(&s_h1[min(s >> 7, 255)], 1);
+    }
+    __syncthreads();
+    if (tid == 0) {
+        int total = 0;
+        for (int b = 0; b < 256; ++b) total += s_h1[b];
+        int k = total / 2, b = 0, acc = 0;
+        if (total > 0) {
+            while (acc + s_h1[b] <= k) { acc += s_h1[b]; ++b; }
+        }
+        s_sel[0] = total; s_sel[1] = b; s_sel[2] = k - acc;    /* rank inside bin b */
+    }
+    __syncthreads();
+    if (s_sel[0] == 0) return;                   /* upstream reads vDistIdx[0] of an empty vector here (UB) */
+    const int bsel = s_sel[1];
+    for (int i = tid; i < nL; i += ST_THREADS) {
+        const int s = sad[i];
+        if (s >= 0 && min(s >> 7, 255) == bsel) atomicAdd(&s_h2[s & 127], 1);
+    }
+    __syncthreads();
+    if (tid == 0) {
+        int k = s_sel[2], b = 0, acc = 0;
+        while (acc + s_h2[b] <= k) { acc += s_h2[b]; ++b; }
+        s_sel[2] = (bsel << 7) | b;
+    }
+    __syncthreads();
+    const float median = (float)s_sel[2];
+    const float thDist = 1.5f * 1.4f * median;
+    for (int i = tid; i < nL; i += ST_THREADS) {
+        const int s = sad[i];
+        if (s >= 0 && !((float)s < thDist)) { oU[i] = -1.0f; oD[i] = -1.0f; }
+    }
+}
+
+static void fill_side(StereoSide& S, const orbx_extractor* e) {
+    S.kps = e->d_kps; S.desc = e->d_desc; S.nk = e->d_nk; S.kcap = e->kcap; S.nlevels = e->nlevels;
+    for (int l = 0; l < e->nlevels; ++l) {
+        const LevelDev& L = e->lv[l];
+        S.lv[l].base = L.base; S.lv[l].frame_bytes = L.frame_bytes; S.lv[l].pitch = L.pitch;
+        S.lv[l].w = L.w; S.lv[l].h = L.h; S.lv[l].pad = 0;
+    }
+}
+
+extern "C" orbx_status orbx_stereo_matches_async(orbx_extractor* left, orbx_extractor* right, int npairs,
+                                                 const int* left_frames, const int* right_frames, float bf, float b) {
+    if (!left || !right || !left_frames || !right_frames) { orbx_set_error("null argument"); return ORBX_ERR_INVALID; }
+    if (npairs < 1 || npairs > left->P.max_batch || left->last_batch < 1 || right->last_batch < 1) {
+        orbx_set_error("npairs %d outside [1,%d] or nothing extracted yet", npairs, left->P.max_batch);
+        return ORBX_ERR_INVALID;
+    }
+    if (left->P.device != right->P.device || left->nlevels != right->nlevels || left->P.width != right->P.width ||
+        left->P.height != right->P.height || left->P.scale_factor != right->P.scale_factor) {
+        orbx_set_error("left and right extractors must share device, image size, scale factor and level count");
+        return ORBX_ERR_INVALID;
+    }
+    for (int p = 0; p < npairs; ++p)
+        if (left_frames[p] < 0 || left_frames[p] >= left->last_batch || right_frames[p] < 0 || right_frames[p] >= right->last_batch) {
+            orbx_set_error("pair %d: frame index outside the last batch", p);
+            return ORBX_ERR_INVALID;
+        }
+    if (left->kcap > 65535 || right->kcap > 65535) { orbx_set_error("more than 65535 keypoints per frame"); return ORBX_ERR_INVALID; }
+    ORBX_CUDA(cudaSetDevice(left->P.device));
+    const int B = left->P.max_batch;
+    if (!left->d_uright) {
+        /* a right keypoint is listed in at most ceil(2r)+2 rows, r = 2*scale[octave] */
+        const int span = (int)ceilf(4.0f * right->sf[right->nlevels - 1]) + 2;
+        left->rowent_per_pair = orbx_align_up((size_t)right->kcap * span, 8);
+        ORBX_CUDA(cudaMalloc(&left->d_uright, (size_t)B * left->kcap * 4));
+        ORBX_CUDA(cudaMalloc(&left->d_depth, (size_t)B * left->kcap * 4));
+        ORBX_CUDA(cudaMalloc(&left->d_pairs, (size_t)B * 2 * 4));
+        ORBX_CUDA(cudaMalloc(&left->d_rowent, (size_t)B * left->rowent_per_pair * 2));
+        ORBX_CUDA(cudaMallocHost(&left->h_uright, (size_t)B * left->kcap * 4));
+        ORBX_CUDA(cudaMallocHost(&left->h_depth, (size_t)B * left->kcap * 4));
+        ORBX_CUDA(cudaMallocHost(&left->h_pairs, (size_t)B * 2 * 4));
+        ORBX_CUDA(cudaEventCreateWithFlags(&left->ev_stereo, cudaEventDisableTiming));
+    } else {
+        const int span = (int)ceilf(4.0f * right->sf[right->nlevels - 1]) + 2;
+        if (orbx_align_up((size_t)right->kcap * span, 8) > left->rowent_per_pair) {
+            orbx_set_error("right extractor has a larger keypoint capacity than the one this handle was first paired with");
+            return ORBX_ERR_INVALID;
+        }
+    }
+    cudaStream_t st = left->stream;
+    if (right != left) {
+        ORBX_CUDA(cudaEventRecord(left->ev_stereo, right->stream));
+        ORBX_CUDA(cudaStreamWaitEvent(st, left->ev_stereo, 0));
+    }
+    memcpy(left->h_pairs, left_frames, sizeof(int) * npairs);
+    memcpy(left->h_pairs + B, right_frames, sizeof(int) * npairs);
+    ORBX_CUDA(cudaMemcpyAsync(left->d_pairs, left->h_pairs, sizeof(int) * 2 * B, cudaMemcpyHostToDevice, st));
+    StereoSide SL, SR;
+    StereoTables TB;
+    memset(&SL, 0, sizeof(SL)); memset(&SR, 0, sizeof(SR)); memset(&TB, 0, sizeof(TB));
+    fill_side(SL, left); fill_side(SR, right);
+    for (int l = 0; l < left->nlevels; ++l) { TB.scale[l] = left->sf[l]; TB.inv_scale[l] = left->inv_sf[l]; }
+    const size_t smem = 4 * ((size_t)2 * left->lv[0].h + 1 + left->kcap) + 16;
+    if (smem > 200 * 1024) { orbx_set_error("image too tall / too many keypoints for the stereo row table"); return ORBX_ERR_INVALID; }
+    ORBX_CUDA(cudaFuncSetAttribute(k_stereo, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max(smem, (size_t)48 * 1024)));
+    k_stereo<<<npairs, ST_THREADS, smem, st>>>(SL, SR, TB, left->d_pairs, B, bf, b, left->d_rowent, left->rowent_per_pair,
+                                               left->d_uright, left->d_depth);
+    ORBX_CUDA(cudaGetLastError());
+    if (right != left) {
+        /* right's next extraction must not overwrite its pyramid before this kernel has read it */
+        ORBX_CUDA(cudaEventRecord(left->ev_stereo, st));
+        ORBX_CUDA(cudaStreamWaitEvent(right->stream, left->ev_stereo, 0));
+    }
+    left->last_pairs = npairs;
+    return ORBX_OK;
+}
+
+extern "C" orbx_status orbx_stereo_fetch(orbx_extractor* left, int npairs, float* uRight, float* depth, int stride) {
+    if (!left || npairs < 1 || npairs > left->last_pairs || stride < left->kcap || (!uRight && !depth)) {
+        orbx_set_error("bad stereo fetch arguments (stride must be >= capacity)");
+        return ORBX_ERR_INVALID;
+    }
+    ORBX_CUDA(cudaSetDevice(left->P.device));
+    const size_t bytes = (size_t)npairs * left->kcap * 4;
+    ORBX_CUDA(cudaMemcpyAsync(left->h_uright, left->d_uright, bytes, cudaMemcpyDeviceToHost, left->stream));
+    ORBX_CUDA(cudaMemcpyAsync(left->h_depth, left->d_depth, bytes, cudaMemcpyDeviceToHost, left->stream));
+    ORBX_CUDA(cudaStreamSynchronize(left->stream));
+    for (int p = 0; p < npairs; ++p) {
+        if (uRight) memcpy(uRight + (size_t)p * stride, left->h_uright + (size_t)p * left->kcap, (size_t)left->kcap * 4);
+        if (depth) memcpy(depth + (size_t)p * stride, left->h_depth + (size_t)p * left->kcap, (size_t)left->kcap * 4);
+    }
+    return ORBX_OK;
+}
+
+extern "C" orbx_status orbx_stereo_matches(orbx_extractor* left, orbx_extractor* right, int npairs, const int* left_frames,
+                                           const int* right_frames, float bf, float b, float* uRight, float* depth,
+                                           int stride) {
+    orbx_status st = orbx_stereo_matches_async(left, right, npairs, left_frames, right_frames, bf, b);
+    if (st != ORBX_OK) return st;
+    return orbx_stereo_fetch(left, npairs, uRight, depth, stride);
+}

@@ -71,6 +71,29 @@ def lib():
         L.orbx_memcpy_h2d.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
         L.orbx_memcpy_d2h.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
         L.orbx_hamming_pairs.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+        L.orbx_three_maxima.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orbx_matcher_create.argtypes = [C.c_int, C.POINTER(C.c_void_p)]
+        L.orbx_matcher_destroy.argtypes = [C.c_void_p]
+        L.orbx_matcher_stream.restype = C.c_void_p
+        L.orbx_matcher_stream.argtypes = [C.c_void_p]
+        L.orbx_matcher_last_launches.argtypes = [C.c_void_p]
+        L.orbx_matcher_set_knn_variant.argtypes = [C.c_void_p, C.c_int]
+        L.orbx_matcher_synchronize.argtypes = [C.c_void_p]
+        L.orbx_search_by_projection.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float,
+                                                C.c_int, C.c_float, C.c_float, C.c_void_p, C.c_void_p]
+        L.orbx_search_by_projection_kf.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float,
+                                                   C.c_int, C.c_void_p, C.c_void_p]
+        L.orbx_search_for_triangulation.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                                    C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                                    C.c_void_p]
+        L.orbx_stereo_matches.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_float, C.c_float,
+                                          C.c_void_p, C.c_void_p, C.c_int]
+        L.orbx_stereo_matches_async.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_float,
+                                                C.c_float]
+        L.orbx_stereo_fetch.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int]
+        L.orbx_knn2.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_float] + [C.c_void_p] * 5
+        L.orbx_knn2_device.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_longlong, C.c_void_p]
+        L.orbx_knn2_merge_device.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_float] + [C.c_void_p] * 5
         _lib = L
     return _lib
 
@@ -253,3 +276,200 @@ def hamming_pairs(a, b):
     out = np.empty(len(a), np.int32)
     _ck(lib().orbx_hamming_pairs(_p(a), _p(b), len(a), _p(out)))
     return out
+
+
+def three_maxima(counts):
+    """ORBmatcher::ComputeThreeMaxima (reference src/ORBmatcher.cc:1328-1370)."""
+    counts = np.ascontiguousarray(counts, np.int32)
+    i = [C.c_int(), C.c_int(), C.c_int()]
+    _ck(lib().orbx_three_maxima(_p(counts), len(counts), C.byref(i[0]), C.byref(i[1]), C.byref(i[2])))
+    return tuple(v.value for v in i)
+
+
+# ------------------------------------------------------------------ stereo (Frame::ComputeStereoMatches)
+def stereo_matches(left, right, left_frames, right_frames, bf, b):
+    """mvuRight / mvDepth of `left`'s frames left_frames[p] against `right`'s frames
+    right_frames[p] (device-resident results of the last extract of both handles)."""
+    lf = np.ascontiguousarray(left_frames, np.int32); rf = np.ascontiguousarray(right_frames, np.int32)
+    n = len(lf)
+    ur = np.empty((n, left.capacity), np.float32); dp = np.empty((n, left.capacity), np.float32)
+    _ck(lib().orbx_stereo_matches(left._h, right._h, n, _p(lf), _p(rf), bf, b, _p(ur), _p(dp), left.capacity))
+    return ur, dp
+
+
+def stereo_matches_async(left, right, left_frames, right_frames, bf, b):
+    lf = np.ascontiguousarray(left_frames, np.int32); rf = np.ascontiguousarray(right_frames, np.int32)
+    _ck(lib().orbx_stereo_matches_async(left._h, right._h, len(lf), _p(lf), _p(rf), bf, b))
+
+
+def stereo_fetch(left, npairs):
+    ur = np.empty((npairs, left.capacity), np.float32); dp = np.empty((npairs, left.capacity), np.float32)
+    _ck(lib().orbx_stereo_fetch(left._h, npairs, _p(ur), _p(dp), left.capacity))
+    return ur, dp
+
+
+# ------------------------------------------------------------------ matcher
+class _FrameView(C.Structure):
+    _fields_ = [("n", C.c_int), ("kx", C.c_void_p), ("ky", C.c_void_p), ("koct", C.c_void_p), ("kangle", C.c_void_p),
+                ("desc", C.c_void_p), ("minx", C.c_float), ("miny", C.c_float), ("gw_inv", C.c_float),
+                ("gh_inv", C.c_float), ("gcols", C.c_int), ("grows", C.c_int), ("scale", C.c_void_p),
+                ("nlevels", C.c_int)]
+
+
+class _MapPoints(C.Structure):
+    _fields_ = [("n", C.c_int), ("inview", C.c_void_p), ("x", C.c_void_p), ("y", C.c_void_p), ("level", C.c_void_p),
+                ("viewcos", C.c_void_p), ("depth", C.c_void_p), ("desc", C.c_void_p)]
+
+
+class _KFPoints(C.Structure):
+    _fields_ = [("n", C.c_int), ("valid", C.c_void_p), ("u", C.c_void_p), ("v", C.c_void_p), ("level", C.c_void_p),
+                ("angle", C.c_void_p), ("desc", C.c_void_p)]
+
+
+class _KFView(C.Structure):
+    _fields_ = [("n", C.c_int), ("kx", C.c_void_p), ("ky", C.c_void_p), ("koct", C.c_void_p), ("kangle", C.c_void_p),
+                ("desc", C.c_void_p), ("has_mp", C.c_void_p), ("uright", C.c_void_p), ("nnodes", C.c_int),
+                ("node_id", C.c_void_p), ("node_off", C.c_void_p), ("node_idx", C.c_void_p)]
+
+
+def _arr(a, dt, keep):
+    if a is None:
+        return None
+    a = np.ascontiguousarray(a, dt)
+    keep.append(a)
+    return a.ctypes.data
+
+
+def _frame_view(F, keep):
+    """F: dict with kx, ky, koct, [kangle], desc, minx, miny, gw_inv, gh_inv, gcols, grows, scale
+    (the Frame members named in include/orbx.h)."""
+    return _FrameView(len(F["kx"]), _arr(F["kx"], np.float32, keep), _arr(F["ky"], np.float32, keep),
+                      _arr(F["koct"], np.int32, keep), _arr(F.get("kangle"), np.float32, keep),
+                      _arr(F["desc"], np.uint8, keep), F["minx"], F["miny"], F["gw_inv"], F["gh_inv"],
+                      F["gcols"], F["grows"], _arr(F["scale"], np.float32, keep), len(F["scale"]))
+
+
+def _ptr_array(arrs, keep):
+    pa = (C.c_void_p * len(arrs))(*[a if a is None else a.ctypes.data for a in arrs])
+    keep.append(pa)
+    return pa
+
+
+class ORBmatcher:
+    """Batched device matcher behind the reference's static ORBmatcher functions
+    (include/ORBmatcher.h:40-70).  Every method takes a LIST of problems (one CTA each); a single
+    dict is accepted as a batch of one and returns un-listed results."""
+    TH_LOW, TH_HIGH, HISTO_LENGTH = 30, 100, 30
+
+    def __init__(self, device=0):
+        self._h = C.c_void_p()
+        _ck(lib().orbx_matcher_create(device, C.byref(self._h)))
+
+    def close(self):
+        if self._h:
+            lib().orbx_matcher_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def stream(self):
+        return lib().orbx_matcher_stream(self._h)
+
+    def last_launches(self):
+        return lib().orbx_matcher_last_launches(self._h)
+
+    def synchronize(self):
+        _ck(lib().orbx_matcher_synchronize(self._h))
+
+    def set_knn_variant(self, v):
+        _ck(lib().orbx_matcher_set_knn_variant(self._h, v))
+
+    @staticmethod
+    def DescriptorDistance(a, b):
+        return int(hamming_pairs(np.asarray(a, np.uint8).reshape(1, 32), np.asarray(b, np.uint8).reshape(1, 32))[0])
+
+    def SearchByProjection(self, F, MP, th, bFarPoints=False, thFarPoints=0.0, nnRatio=0.8, claimed=None):
+        """SearchByProjection(Frame, vpMapPoints, th, bFarPoints, thFarPoints, nnRatio, ...)
+        reference src/ORBmatcher.cc:31-123 -> (nmatches, match_mp[n])."""
+        single = isinstance(F, dict)
+        Fs, MPs = ([F], [MP]) if single else (F, MP)
+        cl = [claimed] if single else (claimed if claimed is not None else [None] * len(Fs))
+        keep = []
+        fv = (_FrameView * len(Fs))(*[_frame_view(f, keep) for f in Fs])
+        mp = (_MapPoints * len(Fs))(*[_MapPoints(len(m["x"]), _arr(m["inview"], np.uint8, keep), _arr(m["x"], np.float32, keep),
+                                                 _arr(m["y"], np.float32, keep), _arr(m["level"], np.int32, keep),
+                                                 _arr(m["viewcos"], np.float32, keep), _arr(m.get("depth"), np.float32, keep),
+                                                 _arr(m["desc"], np.uint8, keep)) for m in MPs])
+        cla = [None if c is None else np.ascontiguousarray(c, np.uint8) for c in cl]
+        keep.append(cla)
+        outs = [np.empty(len(f["kx"]), np.int32) for f in Fs]
+        nm = np.empty(len(Fs), np.int32)
+        _ck(lib().orbx_search_by_projection(self._h, len(Fs), fv, mp, _ptr_array(cla, keep), th, int(bFarPoints),
+                                            thFarPoints, nnRatio, _ptr_array(outs, keep), _p(nm)))
+        return (int(nm[0]), outs[0]) if single else (nm, outs)
+
+    def SearchByProjectionKF(self, F, MP, th, checkOrientation=True, occupied=None):
+        """SearchByProjection(Frame, KeyFrame, sAlreadyFound, th, checkOrientation)
+        reference src/ORBmatcher.cc:1202-1326 -> (nmatches, match_mp[n])."""
+        single = isinstance(F, dict)
+        Fs, MPs = ([F], [MP]) if single else (F, MP)
+        oc = [occupied] if single else (occupied if occupied is not None else [None] * len(Fs))
+        keep = []
+        fv = (_FrameView * len(Fs))(*[_frame_view(f, keep) for f in Fs])
+        mp = (_KFPoints * len(Fs))(*[_KFPoints(len(m["u"]), _arr(m["valid"], np.uint8, keep), _arr(m["u"], np.float32, keep),
+                                               _arr(m["v"], np.float32, keep), _arr(m["level"], np.int32, keep),
+                                               _arr(m.get("angle"), np.float32, keep), _arr(m["desc"], np.uint8, keep))
+                                     for m in MPs])
+        oca = [None if c is None else np.ascontiguousarray(c, np.uint8) for c in oc]
+        keep.append(oca)
+        outs = [np.empty(len(f["kx"]), np.int32) for f in Fs]
+        nm = np.empty(len(Fs), np.int32)
+        _ck(lib().orbx_search_by_projection_kf(self._h, len(Fs), fv, mp, _ptr_array(oca, keep), th, int(checkOrientation),
+                                               _ptr_array(outs, keep), _p(nm)))
+        return (int(nm[0]), outs[0]) if single else (nm, outs)
+
+    def SearchForTriangulation(self, K1, K2, F12, ep, scale2, bOnlyStereo=False, bCoarse=False, checkOrientation=True):
+        """reference src/ORBmatcher.cc:441-676 -> (nmatches, pairs[npairs, 2])."""
+        single = isinstance(K1, dict)
+        if single:
+            K1, K2, F12, ep, scale2 = [K1], [K2], [F12], [ep], [scale2]
+        keep = []
+
+        def kv(K):
+            return _KFView(len(K["kx"]), _arr(K["kx"], np.float32, keep), _arr(K["ky"], np.float32, keep),
+                           _arr(K["koct"], np.int32, keep), _arr(K.get("kangle"), np.float32, keep),
+                           _arr(K["desc"], np.uint8, keep), _arr(K.get("has_mp"), np.uint8, keep),
+                           _arr(K.get("uright"), np.float32, keep), len(K["node_id"]), _arr(K["node_id"], np.int32, keep),
+                           _arr(K["node_off"], np.int32, keep), _arr(K["node_idx"], np.int32, keep))
+        v1 = (_KFView * len(K1))(*[kv(k) for k in K1])
+        v2 = (_KFView * len(K2))(*[kv(k) for k in K2])
+        Fm = np.ascontiguousarray(np.stack([np.asarray(f, np.float32).reshape(9) for f in F12]))
+        E = np.ascontiguousarray(np.asarray(ep, np.float32).reshape(len(K1), 2))
+        sc = [np.ascontiguousarray(s_, np.float32) for s_ in scale2]
+        keep.append(sc)
+        pairs = [np.empty((max(len(k["kx"]), 1), 2), np.int32) for k in K1]
+        npairs = np.empty(len(K1), np.int32); nm = np.empty(len(K1), np.int32)
+        _ck(lib().orbx_search_for_triangulation(self._h, len(K1), v1, v2, _p(Fm), _p(E), _ptr_array(sc, keep),
+                                                int(bOnlyStereo), int(bCoarse), int(checkOrientation),
+                                                _ptr_array(pairs, keep), _p(npairs), _p(nm)))
+        res = [p[:k].copy() for p, k in zip(pairs, npairs)]
+        return (int(nm[0]), res[0]) if single else (nm, res)
+
+    def knn2(self, q, db, ratio=0.8):
+        """brute-force 2-NN + ratio test -> d1, i1, d2, i2, pass."""
+        q = np.ascontiguousarray(q, np.uint8); db = np.ascontiguousarray(db, np.uint8)
+        o = [np.empty(len(q), np.int32) for _ in range(4)]
+        ps = np.empty(len(q), np.uint8)
+        _ck(lib().orbx_knn2(self._h, _p(q), len(q), _p(db), len(db), ratio, _p(o[0]), _p(o[1]), _p(o[2]), _p(o[3]), _p(ps)))
+        return o[0], o[1], o[2], o[3], ps.astype(bool)
+
+    def knn2_device(self, d_q, nq, d_db, ndb, index_base, d_keys):
+        """device pointers (ints); asynchronous on the matcher's stream."""
+        _ck(lib().orbx_knn2_device(self._h, d_q, nq, d_db, ndb, index_base, d_keys))
+
+    def knn2_merge_device(self, d_parts, nparts, nq, ratio, d_d1=None, d_i1=None, d_d2=None, d_i2=None, d_pass=None):
+        _ck(lib().orbx_knn2_merge_device(self._h, d_parts, nparts, nq, ratio, d_d1, d_i1, d_d2, d_i2, d_pass))

@@ -76,3 +76,79 @@ def descriptor_sets(nq, ndb, seed=5, planted=0.5, flip_p=0.06):
     flips = (rng.random((npl, 256)) < flip_p)
     q[:npl] = db[src] ^ np.packbits(flips, axis=1, bitorder="little")
     return q, db, src
+
+
+# ---------------------------------------------------------------------------- matcher problems
+def _flip_bits(rng, desc, p):
+    flips = rng.random((len(desc), 256)) < p
+    return desc ^ np.packbits(flips, axis=1, bitorder="little")
+
+
+def frame_view(n=1000, width=752, height=480, nlevels=8, seed=1, gcols=64, grows=48):
+    """A flattened Frame (include/orbx.h orbx_frame_view): random keypoints + descriptors and the
+    grid constants Frame::Frame derives (mfGridElementWidthInv = cols / (maxX - minX))."""
+    rng = np.random.default_rng(seed)
+    sf = np.cumprod(np.r_[1.0, np.full(nlevels - 1, 1.2)]).astype(np.float32)
+    return {
+        "kx": rng.uniform(0, width, n).astype(np.float32), "ky": rng.uniform(0, height, n).astype(np.float32),
+        "koct": rng.integers(0, nlevels, n).astype(np.int32), "kangle": rng.uniform(0, 360, n).astype(np.float32),
+        "desc": rng.integers(0, 256, (n, 32), dtype=np.uint8),
+        "minx": 0.0, "miny": 0.0, "gw_inv": float(np.float32(gcols) / np.float32(width)),
+        "gh_inv": float(np.float32(grows) / np.float32(height)), "gcols": gcols, "grows": grows, "scale": sf,
+    }
+
+
+def projection_problem(F, nmp=1500, seed=2, jitter=3.0, flip_p=0.05, dup=0.3):
+    """Map points projected near the frame's keypoints: `dup` of them target a keypoint another map
+    point already targets (exercises the first-come claim rule); the rest are fresh or random."""
+    rng = np.random.default_rng(seed)
+    n = len(F["kx"])
+    src = rng.integers(0, n, nmp)
+    ndup = int(nmp * dup)
+    src[nmp - ndup:] = src[rng.integers(0, nmp - ndup, ndup)]
+    rng.shuffle(src)
+    desc = _flip_bits(rng, F["desc"][src], flip_p)
+    rnd = rng.random(nmp) < 0.15
+    desc[rnd] = rng.integers(0, 256, (int(rnd.sum()), 32), dtype=np.uint8)
+    lvl = np.clip(F["koct"][src] + rng.integers(0, 2, nmp), 0, len(F["scale"]) - 1).astype(np.int32)
+    return {
+        "inview": (rng.random(nmp) < 0.9).astype(np.uint8),
+        "x": (F["kx"][src] + rng.normal(0, jitter, nmp)).astype(np.float32),
+        "y": (F["ky"][src] + rng.normal(0, jitter, nmp)).astype(np.float32),
+        "level": lvl, "viewcos": rng.uniform(0.99, 1.0, nmp).astype(np.float32),
+        "depth": rng.uniform(0.5, 40.0, nmp).astype(np.float32), "desc": desc,
+        # KeyFrame overload names
+        "valid": (rng.random(nmp) < 0.9).astype(np.uint8),
+        "angle": ((F["kangle"][src] + rng.choice([0.0, 0.0, 0.0, 40.0, 95.0, 200.0], nmp) + rng.normal(0, 4, nmp)) % 360).astype(np.float32),
+    }
+
+
+def keyframe_pair(n1=1000, n2=1100, nnodes=90, seed=3, width=752, height=480, nlevels=8):
+    """Two flattened KeyFrames (orbx_kf_view) with DBoW2-style feature vectors (a partition of the
+    keypoints over sorted node ids, most nodes shared), a fundamental matrix and an epipole."""
+    rng = np.random.default_rng(seed)
+    sf = np.cumprod(np.r_[1.0, np.full(nlevels - 1, 1.2)]).astype(np.float32)
+    K2 = frame_view(n2, width, height, nlevels, seed + 1)
+    src = rng.integers(0, n2, n1)
+    k1 = {"kx": (K2["kx"][src] + rng.normal(0, 6, n1)).astype(np.float32),
+          "ky": (K2["ky"][src] + rng.normal(0, 1.0, n1)).astype(np.float32),
+          "koct": K2["koct"][src].copy(), "kangle": ((K2["kangle"][src] + rng.normal(0, 5, n1)) % 360).astype(np.float32),
+          "desc": _flip_bits(rng, K2["desc"][src], 0.03)}
+    k2 = {k: K2[k] for k in ("kx", "ky", "koct", "kangle", "desc")}
+    ids = np.sort(rng.choice(10000, nnodes + 10, replace=False)).astype(np.int32)
+    node_of_2 = rng.integers(0, nnodes, n2)
+    node_of_1 = np.where(rng.random(n1) < 0.85, node_of_2[src], rng.integers(0, nnodes + 10, n1))
+
+    def fv(node_of, nid):
+        order = np.argsort(node_of, kind="stable")
+        used, counts = np.unique(node_of, return_counts=True)
+        return {"node_id": nid[used].astype(np.int32), "node_off": np.r_[0, np.cumsum(counts)].astype(np.int32),
+                "node_idx": order.astype(np.int32)}
+    k1.update(fv(node_of_1, ids)); k2.update(fv(node_of_2, ids))
+    k1["has_mp"] = (rng.random(n1) < 0.2).astype(np.uint8); k2["has_mp"] = (rng.random(n2) < 0.2).astype(np.uint8)
+    k1["uright"] = np.where(rng.random(n1) < 0.3, k1["kx"] - 5, -1).astype(np.float32)
+    k2["uright"] = np.where(rng.random(n2) < 0.3, k2["kx"] - 5, -1).astype(np.float32)
+    # rectified-like geometry: horizontal epipolar lines (F = [t]x for t = (1,0,0)) plus a small tilt
+    F12 = np.array([[0, 0, 0.002], [0, 0, -1.0], [-0.002, 1.0, 0.3]], np.float32)
+    ep = np.array([width * 0.5 + 40, height * 0.5 - 10], np.float32)
+    return k1, k2, F12, ep, sf

@@ -1,0 +1,205 @@
+"""GPU parity: CUDA matcher / stereo kernels (through the C ABI) vs the CPU oracle on identical
+seeded inputs.  Match indices, distances, counts: bit-exact (BASELINE.json north_star)."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def matcher(pkg):
+    m = pkg.orbx.ORBmatcher()
+    yield m
+    m.close()
+
+
+# ---------------------------------------------------------------- SearchByProjection (map points)
+@pytest.mark.parametrize("n,nmp,th,nnRatio,seed", [
+    (1000, 1500, 1.0, 0.8, 1), (1000, 2000, 3.0, 0.75, 2), (2000, 3000, 15.0, 0.9, 3), (300, 50, 1.0, 0.8, 4),
+    (1, 5, 3.0, 0.8, 5),
+])
+def test_search_by_projection(matcher, oracle, synth, n, nmp, th, nnRatio, seed):
+    F = synth.frame_view(n, seed=seed)
+    MP = synth.projection_problem(F, nmp, seed=seed + 100)
+    rng = np.random.default_rng(seed)
+    claimed = (rng.random(n) < 0.1).astype(np.uint8)
+    for far, cl in ((False, None), (True, claimed)):
+        on, om = oracle.search_by_projection(F, MP, th, far, 25.0, nnRatio, cl)
+        gn, gm = matcher.SearchByProjection(F, MP, th, far, 25.0, nnRatio, cl)
+        assert gn == on and np.array_equal(gm, om)
+        if n > 100:
+            assert on > 0.2 * min(n, nmp)          # the problem is not vacuous
+
+
+def test_search_by_projection_chained_claims(matcher, oracle, synth):
+    """Many map points with IDENTICAL descriptors around the same keypoints: long claim chains
+    (map point i takes what i-1 left), the worst case for the fixed-point rounds."""
+    F = synth.frame_view(400, seed=9)
+    rng = np.random.default_rng(9)
+    base = rng.integers(0, 256, 32, dtype=np.uint8)
+    F["desc"][:] = base
+    F["desc"] ^= np.packbits(rng.random((400, 256)) < 0.02, axis=1, bitorder="little")
+    F["kx"][:] = rng.uniform(300, 360, 400).astype(np.float32); F["ky"][:] = rng.uniform(200, 240, 400).astype(np.float32)
+    F["koct"][:] = 2
+    nmp = 600
+    MP = {"inview": np.ones(nmp, np.uint8), "x": rng.uniform(300, 360, nmp).astype(np.float32),
+          "y": rng.uniform(200, 240, nmp).astype(np.float32), "level": np.full(nmp, 2, np.int32),
+          "viewcos": np.ones(nmp, np.float32), "depth": np.ones(nmp, np.float32),
+          "desc": np.tile(base, (nmp, 1))}
+    on, om = oracle.search_by_projection(F, MP, 10.0, False, 0.0, 1.0)
+    gn, gm = matcher.SearchByProjection(F, MP, 10.0, False, 0.0, 1.0)
+    assert gn == on and np.array_equal(gm, om) and on >= 300
+
+
+def test_search_by_projection_batched(matcher, oracle, synth):
+    Fs = [synth.frame_view(600 + 50 * i, seed=20 + i) for i in range(7)]
+    MPs = [synth.projection_problem(F, 900 + 10 * i, seed=40 + i) for i, F in enumerate(Fs)]
+    nm, outs = matcher.SearchByProjection(Fs, MPs, 3.0, False, 0.0, 0.8)
+    for F, MP, n_, o_ in zip(Fs, MPs, nm, outs):
+        on, om = oracle.search_by_projection(F, MP, 3.0, False, 0.0, 0.8)
+        assert n_ == on and np.array_equal(o_, om)
+    assert matcher.last_launches() == 1
+
+
+# ---------------------------------------------------------------- SearchByProjection (KeyFrame)
+@pytest.mark.parametrize("n,nmp,th,ori,seed", [(1000, 1200, 15.0, True, 1), (1000, 1200, 15.0, False, 2),
+                                               (1500, 2500, 40.0, True, 3), (64, 10, 5.0, True, 4)])
+def test_search_by_projection_kf(matcher, oracle, synth, n, nmp, th, ori, seed):
+    F = synth.frame_view(n, seed=seed + 50)
+    P = synth.projection_problem(F, nmp, seed=seed + 150)
+    MP = {"valid": P["valid"], "u": P["x"], "v": P["y"], "level": P["level"], "angle": P["angle"], "desc": P["desc"]}
+    rng = np.random.default_rng(seed)
+    occ = (rng.random(n) < 0.05).astype(np.uint8)
+    on, om = oracle.search_by_projection_kf(F, MP, th, ori, occ)
+    gn, gm = matcher.SearchByProjectionKF(F, MP, th, ori, occ)
+    assert gn == on and np.array_equal(gm, om)
+    if n > 100:
+        assert on > 50
+        if ori:      # the histogram filter removed something
+            on2, _ = oracle.search_by_projection_kf(F, MP, th, False, occ)
+            assert on2 > on
+
+
+# ---------------------------------------------------------------- SearchForTriangulation
+@pytest.mark.parametrize("stereo,coarse,ori,seed", [(False, False, True, 1), (False, True, True, 2),
+                                                    (True, False, False, 3), (False, False, False, 4)])
+def test_search_for_triangulation(matcher, oracle, synth, stereo, coarse, ori, seed):
+    k1, k2, F12, ep, sf = synth.keyframe_pair(1000, 1100, 90, seed=seed)
+    on, op = oracle.search_for_triangulation(k1, k2, F12, ep, sf, stereo, coarse, ori)
+    gn, gp = matcher.SearchForTriangulation(k1, k2, F12, ep, sf, stereo, coarse, ori)
+    assert gn == on and np.array_equal(gp, op)
+    assert len(op) > 20
+
+
+def test_search_for_triangulation_mono_batched(matcher, oracle, synth):
+    probs = [synth.keyframe_pair(500 + 40 * i, 600, 60, seed=30 + i) for i in range(5)]
+    for p in probs:             # mono KeyFrames: no mvuRight at all
+        p[0]["uright"] = None; p[1]["uright"] = None
+    nm, res = matcher.SearchForTriangulation([p[0] for p in probs], [p[1] for p in probs], [p[2] for p in probs],
+                                             [p[3] for p in probs], [p[4] for p in probs])
+    for p, n_, r_ in zip(probs, nm, res):
+        on, op = oracle.search_for_triangulation(p[0], p[1], p[2], p[3], p[4])
+        assert n_ == on and np.array_equal(r_, op)
+
+
+def test_three_maxima(pkg, oracle):
+    rng = np.random.default_rng(3)
+    cases = [rng.integers(0, 50, 30) for _ in range(50)] + [np.zeros(30, int), np.r_[100, np.zeros(29, int)],
+                                                            np.r_[100, 9, 9, np.zeros(27, int)], np.r_[100, 10, 9, np.zeros(27, int)]]
+    for c in cases:
+        assert pkg.orbx.three_maxima(c) == oracle.three_maxima(c)
+
+
+# ---------------------------------------------------------------- brute-force 2-NN
+@pytest.mark.parametrize("nq,ndb,variant", [(3000, 20000, 1), (3000, 20000, 0), (1, 1, 1), (5, 2, 1), (1030, 257, 1), (7, 0, 1)])
+def test_knn2_vs_oracle(matcher, oracle, synth, nq, ndb, variant):
+    q, db, _ = synth.descriptor_sets(nq, max(ndb, 1), seed=5)
+    db = db[:ndb]
+    if ndb > 10:
+        db[7] = db[3]; q[0] = db[3]          # exact duplicates: tie -> lowest index
+    matcher.set_knn_variant(variant)
+    d1, i1, d2, i2, ps = matcher.knn2(q, db, 0.8)
+    o1, oi1, o2, oi2 = oracle.knn2(q, db, nthreads=8)
+    assert np.array_equal(d1, o1) and np.array_equal(i1, oi1) and np.array_equal(d2, o2) and np.array_equal(i2, oi2)
+    assert np.array_equal(ps, d1.astype(np.float32) < np.float32(0.8) * d2.astype(np.float32))
+    matcher.set_knn_variant(1)
+
+
+def test_knn2_large_properties(matcher, synth):
+    """Sizes the oracle cannot finish: planted neighbours are found (also across the 4M-row slice
+    boundary of the kernel's grid), ties resolve to the lowest index, d1 <= d2."""
+    nq, ndb = 4096, (1 << 22) + 5000
+    q, db, src = synth.descriptor_sets(nq, ndb, seed=6, planted=0.5, flip_p=0.04)
+    q[4000] = db[(1 << 22) + 17]; q[4001] = db[(1 << 22) - 1]
+    db[(1 << 22) + 100] = db[50]; q[4002] = db[50]
+    d1, i1, d2, i2, ps = matcher.knn2(q, db, 0.8)
+    npl = nq // 2
+    host_d = np.unpackbits(q[:npl] ^ db[src], axis=1).sum(1)
+    assert np.all(d1[:npl] <= host_d) and np.mean(i1[:npl] == src) > 0.999
+    assert np.all(d1 <= d2) and np.all(i1 != i2)
+    assert (d1[4000], i1[4000]) == (0, (1 << 22) + 17) and (d1[4001], i1[4001]) == (0, (1 << 22) - 1)
+    assert (d1[4002], i1[4002], d2[4002], i2[4002]) == (0, 50, 0, (1 << 22) + 100)
+    # spot-check 16 queries exhaustively on the host
+    for k in range(0, nq, nq // 16):
+        d = np.unpackbits(q[k][None] ^ db, axis=1).sum(1)
+        o = np.lexsort((np.arange(ndb), d))[:2]
+        assert (d1[k], i1[k], d2[k], i2[k]) == (d[o[0]], o[0], d[o[1]], o[1])
+    assert ps[:npl].mean() > 0.95 and ps[npl:4000].mean() < 0.05
+
+
+# ---------------------------------------------------------------- Frame::ComputeStereoMatches
+def _stereo_case(pkg, oracle, synth, w, h, nf, seed, same_handle):
+    left, right = synth.stereo_pair(w, h, seed)
+    ox = pkg.orbx
+    if same_handle:
+        ex = ox.ORBextractor(nf, 1.2, 8, 20, 7, max_batch=2)
+        res = ex.extract_batch(np.stack([left, right]))
+        exL = exR = ex
+        fL, fR = 0, 1
+    else:
+        exL = ox.ORBextractor(nf, 1.2, 8, 20, 7); exR = ox.ORBextractor(nf, 1.2, 8, 20, 7)
+        res = [exL(left, (0, 0)), exR(right, (0, 0))]
+        fL = fR = 0
+    (kL, dL, _), (kR, dR, _) = res
+    bf, b = 435.2 * 0.11, 0.11          # EuRoC: fx * baseline, baseline
+    ur, dp = ox.stereo_matches(exL, exR, [fL], [fR], bf, b)
+    lvL = [exL.image_pyramid(l, fL) for l in range(8)]
+    lvR = [exR.image_pyramid(l, fR) for l in range(8)]
+    our, odp = oracle.stereo_matches(kL, dL, lvL, kR, dR, lvR, exL.mvScaleFactor, exL.mvInvScaleFactor, bf, b)
+    n = len(kL)
+    assert np.array_equal(ur[0, :n], our) and np.array_equal(dp[0, :n], odp)
+    assert np.all(ur[0, n:] == -1)
+    nmatch = int((our >= 0).sum())
+    assert nmatch > 0.2 * n, (nmatch, n)
+    exL.close()
+    if exR is not exL:
+        exR.close()
+    return nmatch
+
+
+def test_stereo_matches_euroc_same_handle(pkg, oracle, synth):
+    _stereo_case(pkg, oracle, synth, 752, 480, 1000, 0xB200, True)
+
+
+def test_stereo_matches_two_extractors(pkg, oracle, synth):
+    _stereo_case(pkg, oracle, synth, 752, 480, 1000, 77, False)
+
+
+def test_stereo_matches_kitti(pkg, oracle, synth):
+    _stereo_case(pkg, oracle, synth, 1241, 376, 2000, 11, True)
+
+
+def test_stereo_matches_batch(pkg, oracle, synth):
+    """4 pairs per launch, frames interleaved L,R,L,R,... in one extractor batch."""
+    ox = pkg.orbx
+    pairs = [synth.stereo_pair(640, 400, 100 + i) for i in range(4)]
+    imgs = np.stack([im for p in pairs for im in p])
+    ex = ox.ORBextractor(800, 1.2, 8, 20, 7, max_batch=8)
+    res = ex.extract_batch(imgs)
+    ur, dp = ox.stereo_matches(ex, ex, [0, 2, 4, 6], [1, 3, 5, 7], 40.0, 0.1)
+    for p in range(4):
+        kL, dL, _ = res[2 * p]; kR, dR, _ = res[2 * p + 1]
+        lvL = [ex.image_pyramid(l, 2 * p) for l in range(8)]; lvR = [ex.image_pyramid(l, 2 * p + 1) for l in range(8)]
+        our, odp = oracle.stereo_matches(kL, dL, lvL, kR, dR, lvR, ex.mvScaleFactor, ex.mvInvScaleFactor, 40.0, 0.1)
+        assert np.array_equal(ur[p, :len(kL)], our) and np.array_equal(dp[p, :len(kL)], odp)
+    ex.close()
