@@ -5,3 +5,4 @@ thin ctypes binding (`orbx`) used by tests and bench.py.  There is no CPU fallba
 entry point raises if liborbx.so or a CUDA device is missing."""
 from . import synth  # noqa: F401
 from . import orbx  # noqa: F401
+from . import sharding  # noqa: F401

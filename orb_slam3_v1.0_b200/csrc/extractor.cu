@@ -44,32 +44,32 @@ extern "C" int orbx_version(void) { return 100; }
 /* level 0 = copyMakeBorder(image, 19, BORDER_REFLECT_101).
  * One thread per 16 output bytes of the padded row. */
 __global__ void __launch_bounds__(256) k_level0(const uint8_t* __restrict__ src, size_t frame_stride,
-                                                int row_stride, LevelDev L, int batch, int vec_ok) {
+                                                int row_stride, LevelDev L, unsigned rcp_chunks, int vec_ok) {
+    /* grid: x over (row, 16-byte chunk) of one padded frame, y = frame; the division by the chunk
+     * count is one __umulhi (exact: items < 2^20, chunks < 2^9) */
     const int chunks = L.pitch / 16;
-    const long long total = (long long)batch * L.rows * chunks;
-    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total;
-         t += (long long)gridDim.x * blockDim.x) {
-        const int c = (int)(t % chunks);
-        const int r = (int)((t / chunks) % L.rows);
-        const int f = (int)(t / ((long long)chunks * L.rows));
-        const int x0 = c * 16 - ORBX_XOFF;
-        if (x0 + 16 <= -ORBX_EDGE || x0 >= L.w + ORBX_EDGE) continue;
-        const int sy = reflect101(r - ORBX_EDGE, L.h);
-        const uint8_t* srow = src + (size_t)f * frame_stride + (size_t)sy * row_stride;
-        uint8_t* drow = L.base + (size_t)f * L.frame_bytes + (size_t)r * L.pitch + c * 16;
-        if (vec_ok && x0 >= 0 && x0 + 16 <= L.w) {
-            *reinterpret_cast<uint4*>(drow) = __ldg(reinterpret_cast<const uint4*>(srow + x0));
-        } else {
-            uint32_t wv[4] = {0, 0, 0, 0};
+    const unsigned i = blockIdx.x * 256u + threadIdx.x;
+    const int r = (int)__umulhi(i, rcp_chunks);
+    if (r >= L.rows) return;
+    const int c = (int)i - r * chunks;
+    const int f = blockIdx.y;
+    const int x0 = c * 16 - ORBX_XOFF;
+    if (x0 + 16 <= -ORBX_EDGE || x0 >= L.w + ORBX_EDGE) return;
+    const int sy = reflect101(r - ORBX_EDGE, L.h);
+    const uint8_t* srow = src + (size_t)f * frame_stride + (size_t)sy * row_stride;
+    uint8_t* drow = L.base + (size_t)f * L.frame_bytes + (size_t)r * L.pitch + c * 16;
+    if (vec_ok && x0 >= 0 && x0 + 16 <= L.w) {
+        *reinterpret_cast<uint4*>(drow) = __ldg(reinterpret_cast<const uint4*>(srow + x0));
+    } else {
+        uint32_t wv[4] = {0, 0, 0, 0};
 #pragma unroll
-            for (int k = 0; k < 16; ++k) {
-                const int x = x0 + k;
-                uint32_t v = 0;
-                if (x >= -ORBX_EDGE && x < L.w + ORBX_EDGE) v = __ldg(srow + reflect101(x, L.w));
-                wv[k >> 2] |= v << (8 * (k & 3));
-            }
-            *reinterpret_cast<uint4*>(drow) = make_uint4(wv[0], wv[1], wv[2], wv[3]);
+        for (int k = 0; k < 16; ++k) {
+            const int x = x0 + k;
+            uint32_t v = 0;
+            if (x >= -ORBX_EDGE && x < L.w + ORBX_EDGE) v = __ldg(srow + reflect101(x, L.w));
+            wv[k >> 2] |= v << (8 * (k & 3));
         }
+        *reinterpret_cast<uint4*>(drow) = make_uint4(wv[0], wv[1], wv[2], wv[3]);
     }
 }
 
@@ -85,31 +85,29 @@ __device__ __forceinline__ uint32_t resize_px(const uint8_t* __restrict__ s0, co
     return (uint32_t)((((b0 * (r0 >> 4)) >> 16) + ((b1 * (r1 >> 4)) >> 16) + 2) >> 2);
 }
 
-__global__ void __launch_bounds__(256) k_resize(LevelDev S, LevelDev D, int batch) {
+__global__ void __launch_bounds__(256) k_resize(LevelDev S, LevelDev D, unsigned rcp_chunks) {
     const int chunks = D.pitch / 4;
-    const long long total = (long long)batch * D.rows * chunks;
-    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total;
-         t += (long long)gridDim.x * blockDim.x) {
-        const int c = (int)(t % chunks);
-        const int r = (int)((t / chunks) % D.rows);
-        const int f = (int)(t / ((long long)chunks * D.rows));
-        const int x0 = c * 4 - ORBX_XOFF;
-        if (x0 + 4 <= -ORBX_EDGE || x0 >= D.w + ORBX_EDGE) continue;
-        const int dy = reflect101(r - ORBX_EDGE, D.h);
-        const short4 yt = __ldg(D.ytab + dy);
-        const uint8_t* s0 = lv_ptr(S, f, 0, yt.x);
-        const uint8_t* s1 = s0 + S.pitch;       /* row sy+1 exists in the bordered source */
-        uint32_t out = 0;
+    const unsigned i = blockIdx.x * 256u + threadIdx.x;
+    const int r = (int)__umulhi(i, rcp_chunks);
+    if (r >= D.rows) return;
+    const int c = (int)i - r * chunks;
+    const int f = blockIdx.y;
+    const int x0 = c * 4 - ORBX_XOFF;
+    if (x0 + 4 <= -ORBX_EDGE || x0 >= D.w + ORBX_EDGE) return;
+    const int dy = reflect101(r - ORBX_EDGE, D.h);
+    const short4 yt = __ldg(D.ytab + dy);
+    const uint8_t* s0 = lv_ptr(S, f, 0, yt.x);
+    const uint8_t* s1 = s0 + S.pitch;       /* row sy+1 exists in the bordered source */
+    uint32_t out = 0;
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const int x = x0 + k;
-            if (x >= -ORBX_EDGE && x < D.w + ORBX_EDGE) {
-                const short4 xt = __ldg(D.xtab + reflect101(x, D.w));
-                out |= resize_px(s0, s1, xt, yt.y, yt.z) << (8 * k);
-            }
+    for (int k = 0; k < 4; ++k) {
+        const int x = x0 + k;
+        if (x >= -ORBX_EDGE && x < D.w + ORBX_EDGE) {
+            const short4 xt = __ldg(D.xtab + reflect101(x, D.w));
+            out |= resize_px(s0, s1, xt, yt.y, yt.z) << (8 * k);
         }
-        *reinterpret_cast<uint32_t*>(D.base + (size_t)f * D.frame_bytes + (size_t)r * D.pitch + c * 4) = out;
     }
+    *reinterpret_cast<uint32_t*>(D.base + (size_t)f * D.frame_bytes + (size_t)r * D.pitch + c * 4) = out;
 }
 
 /* Fast path of the level chain: one thread per 32-bit word (4 pixels) of the PADDED destination
@@ -122,42 +120,38 @@ struct ResizeMeta { uint32_t m; };   /* base byte (16b) | off0<<16 | off1<<20 | 
 
 __global__ void __launch_bounds__(256) k_resize_w4(LevelDev S, LevelDev D, const uint4* __restrict__ xcoef,
                                                    const uint32_t* __restrict__ xmeta,
-                                                   const short4* __restrict__ ypad, int batch) {
+                                                   const short4* __restrict__ ypad, unsigned rcp_chunks) {
     const int chunks = D.pitch / 4;
-    const long long total = (long long)batch * D.rows * chunks;
-    const int spw = S.pitch >> 2;
-    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total;
-         t += (long long)gridDim.x * blockDim.x) {
-        const int c = (int)(t % chunks);
-        const long long t2 = t / chunks;
-        const int r = (int)(t2 % D.rows);
-        const int f = (int)(t2 / D.rows);
-        const uint32_t meta = __ldg(xmeta + c);
-        if (meta == 0xFFFFFFFFu) continue;
-        const uint4 cf = __ldg(xcoef + c);
-        const short4 yt = __ldg(ypad + r);                 /* {sy, b0, b1} for the padded row r */
-        const uint32_t base = meta & 0xFFFFu;
-        const int sh = (base & 3) * 8;
-        const uint32_t* row0 = reinterpret_cast<const uint32_t*>(S.base + (size_t)f * S.frame_bytes +
-                                                                  (size_t)(yt.x + ORBX_EDGE) * S.pitch) + (base >> 2);
-        const uint32_t* row1 = row0 + spw;                  /* row sy+1 exists in the bordered source */
-        const uint32_t a0 = __ldg(row0), a1 = __ldg(row0 + 1), a2 = __ldg(row0 + 2);
-        const uint32_t b0 = __ldg(row1), b1 = __ldg(row1 + 1), b2 = __ldg(row1 + 2);
-        const uint32_t U0 = __funnelshift_r(a0, a1, sh), V0 = __funnelshift_r(a1, a2, sh);
-        const uint32_t U1 = __funnelshift_r(b0, b1, sh), V1 = __funnelshift_r(b1, b2, sh);
-        const int wy0 = yt.y, wy1 = yt.z;
-        const uint32_t cfs[4] = {cf.x, cf.y, cf.z, cf.w};
-        uint32_t out = 0;
+    const unsigned i = blockIdx.x * 256u + threadIdx.x;
+    const int r = (int)__umulhi(i, rcp_chunks);
+    if (r >= D.rows) return;
+    const int c = (int)i - r * chunks;
+    const int f = blockIdx.y;
+    const uint32_t meta = __ldg(xmeta + c);
+    if (meta == 0xFFFFFFFFu) return;
+    const uint4 cf = __ldg(xcoef + c);
+    const short4 yt = __ldg(ypad + r);                 /* {sy, b0, b1} for the padded row r */
+    const uint32_t base = meta & 0xFFFFu;
+    const int sh = (base & 3) * 8;
+    const uint32_t* row0 = reinterpret_cast<const uint32_t*>(S.base + (size_t)f * S.frame_bytes +
+                                                              (size_t)(yt.x + ORBX_EDGE) * S.pitch) + (base >> 2);
+    const uint32_t* row1 = row0 + (S.pitch >> 2);      /* row sy+1 exists in the bordered source */
+    const uint32_t a0 = __ldg(row0), a1 = __ldg(row0 + 1), a2 = __ldg(row0 + 2);
+    const uint32_t b0 = __ldg(row1), b1 = __ldg(row1 + 1), b2 = __ldg(row1 + 2);
+    const uint32_t U0 = __funnelshift_r(a0, a1, sh), V0 = __funnelshift_r(a1, a2, sh);
+    const uint32_t U1 = __funnelshift_r(b0, b1, sh), V1 = __funnelshift_r(b1, b2, sh);
+    const int wy0 = yt.y, wy1 = yt.z;
+    const uint32_t cfs[4] = {cf.x, cf.y, cf.z, cf.w};
+    uint32_t out = 0;
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const uint32_t off = (meta >> (16 + 4 * k)) & 7u;
-            const uint32_t sel = off * 0x11u + 0x10u;       /* bytes off, off+1 -> lanes 0,1 */
-            const int r0 = (int)__dp2a_lo(cfs[k], __byte_perm(U0, V0, sel), 0u);
-            const int r1 = (int)__dp2a_lo(cfs[k], __byte_perm(U1, V1, sel), 0u);
-            out |= (uint32_t)((((wy0 * (r0 >> 4)) >> 16) + ((wy1 * (r1 >> 4)) >> 16) + 2) >> 2) << (8 * k);
-        }
-        *reinterpret_cast<uint32_t*>(D.base + (size_t)f * D.frame_bytes + (size_t)r * D.pitch + c * 4) = out;
+    for (int k = 0; k < 4; ++k) {
+        const uint32_t off = (meta >> (16 + 4 * k)) & 7u;
+        const uint32_t sel = off * 0x11u + 0x10u;       /* bytes off, off+1 -> lanes 0,1 */
+        const int r0 = (int)__dp2a_lo(cfs[k], __byte_perm(U0, V0, sel), 0u);
+        const int r1 = (int)__dp2a_lo(cfs[k], __byte_perm(U1, V1, sel), 0u);
+        out |= (uint32_t)((((wy0 * (r0 >> 4)) >> 16) + ((wy1 * (r1 >> 4)) >> 16) + 2) >> 2) << (8 * k);
     }
+    *reinterpret_cast<uint32_t*>(D.base + (size_t)f * D.frame_bytes + (size_t)r * D.pitch + c * 4) = out;
 }
 
 /* ================================================================== stage 1: FAST per cell */
@@ -907,12 +901,22 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
     return a;
 }
 
-__global__ void __launch_bounds__(256) k_orient_describe(Tables T, UMax um, const uint32_t* __restrict__ sel,
+/* One warp per keypoint.
+ *  IC_Angle: lane = patch column u = lane-15; the warp walks the 31 patch rows, so every load is
+ *  one contiguous 31-byte row segment (1-2 L1 wavefronts) instead of 31 scattered bytes.
+ *  rBRIEF: the 37x37 blurred window (max rotated pattern radius 18.4 -> +-18) is staged in
+ *  shared memory with aligned word loads (3 rows x 10 words per warp request), then lane = descriptor
+ *  byte gathers its 16 samples from shared memory. */
+#define OD_WARPS 8
+#define OD_WIN 37
+#define OD_WP 12            /* window pitch in words (10 used) */
+__global__ void __launch_bounds__(32 * OD_WARPS) k_orient_describe(Tables T, UMax um, const uint32_t* __restrict__ sel,
                                                           size_t sel_per_frame, const int* __restrict__ sel_count,
                                                           const int* __restrict__ dest, orbx_keypoint* __restrict__ kps,
                                                           uint8_t* __restrict__ desc, int kcap) {
-    const int lane = threadIdx.x & 31;
-    const int slot = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    __shared__ uint32_t s_win[OD_WARPS][OD_WIN * OD_WP];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int slot = blockIdx.x * OD_WARPS + wid;
     const int f = blockIdx.y;
     if (slot >= (int)sel_per_frame) return;
     int l = 0;
@@ -924,20 +928,36 @@ __global__ void __launch_bounds__(256) k_orient_describe(Tables T, UMax um, cons
     const int x = (int)(e & 0xFFF) + ORBX_MINB, y = (int)((e >> 12) & 0xFFF) + ORBX_MINB;
     const int resp = (int)(e >> 24);
 
-    /* IC_Angle (reference src/cuda/Angle_gpu.cu:39-69): lane = patch row v = lane-15 */
-    int m10 = 0, m01 = 0;
-    if (lane < 31) {
-        const int v = lane - 15;
-        const int d = um.v[v < 0 ? -v : v];
-        const uint8_t* row = lv_ptr(L, f, x, y + v);
-        int su = 0, s = 0;
-        for (int u = -d; u <= d; ++u) {
-            const int val = __ldg(row + u);
-            su += u * val;
-            s += val;
+    /* stage the blurred window: rows y-18..y+18, words from the aligned column below x-18 */
+    uint32_t* win = s_win[wid];
+    const int xa = (x - 18) & ~3;
+    {
+        const uint8_t* b0 = L.blur + (size_t)f * L.bframe_bytes + (size_t)(y - 18) * L.bpitch + xa;
+        const int sub = lane / 10, wc = lane - sub * 10;     /* 3 rows x 10 words per request; lanes 30,31 idle */
+        const int nw = ((x + 18 - xa) >> 2) + 1;             /* words that start inside the window (<= 10) */
+#pragma unroll
+        for (int r0 = 0; r0 < OD_WIN + 2; r0 += 3) {
+            const int r = r0 + sub;
+            if (sub < 3 && r < OD_WIN && wc < nw)
+                win[r * OD_WP + wc] = __ldg(reinterpret_cast<const uint32_t*>(b0 + (size_t)r * L.bpitch) + wc);
         }
-        m10 = su;
-        m01 = v * s;
+    }
+
+    /* IC_Angle (reference src/cuda/Angle_gpu.cu:39-69): m10 = sum u*I, m01 = sum v*I over the disc */
+    int m10 = 0, m01 = 0;
+    {
+        const int u = lane - 15, au = u < 0 ? -u : u;
+        const uint8_t* p = lv_ptr(L, f, x + u, y - 15);
+        const int pitch = L.pitch;
+#pragma unroll
+        for (int v = -15; v <= 15; ++v) {
+            const int d = um.v[v < 0 ? -v : v];
+            if (lane < 31 && au <= d) {
+                const int val = __ldg(p + (size_t)(v + 15) * pitch);
+                m10 += u * val;
+                m01 += v * val;
+            }
+        }
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -953,7 +973,8 @@ __global__ void __launch_bounds__(256) k_orient_describe(Tables T, UMax um, cons
     double sd, cd;
     sincos((double)ar, &sd, &cd);
     const float a = (float)cd, b = (float)sd;
-    const uint8_t* center = L.blur + (size_t)f * L.bframe_bytes + (size_t)y * L.bpitch + x;
+    __syncwarp();
+    const uint8_t* center = reinterpret_cast<const uint8_t*>(win) + 18 * (OD_WP * 4) + (x - xa);
     const signed char* pat = d_pattern + 32 * lane;
     int val = 0;
 #pragma unroll
@@ -963,8 +984,8 @@ __global__ void __launch_bounds__(256) k_orient_describe(Tables T, UMax um, cons
         const int ix0 = __float2int_rn(__fsub_rn(__fmul_rn(px0, a), __fmul_rn(py0, b)));
         const int iy1 = __float2int_rn(__fadd_rn(__fmul_rn(px1, b), __fmul_rn(py1, a)));
         const int ix1 = __float2int_rn(__fsub_rn(__fmul_rn(px1, a), __fmul_rn(py1, b)));
-        const int t0 = __ldg(center + iy0 * L.bpitch + ix0);
-        const int t1 = __ldg(center + iy1 * L.bpitch + ix1);
+        const int t0 = center[iy0 * (OD_WP * 4) + ix0];
+        const int t1 = center[iy1 * (OD_WP * 4) + ix1];
         val |= (t0 < t1) << j;
     }
     const int d = dest[(size_t)f * sel_per_frame + slot];
@@ -1141,7 +1162,7 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
     for (int i = 0; i < 7; ++i) CK(cudaEventCreate(&e->ev[i]));
     CK(cudaFuncSetAttribute(k_octree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)e->oct_smem));
     CK(cudaMalloc(&e->d_pyr, pyr_bytes));
-    CK(cudaMalloc(&e->d_blur, blur_bytes));
+    CK(cudaMalloc(&e->d_blur, blur_bytes + 256));    /* + slack: window staging reads whole words */
     CK(cudaMemsetAsync(e->d_pyr, 0, pyr_bytes, e->stream));
     CK(cudaMalloc(&e->d_input, (size_t)B * p->width * p->height));
     CK(cudaMalloc(&e->d_tabs, tab_entries * sizeof(short4)));
@@ -1280,13 +1301,6 @@ extern "C" orbx_status orbx_extractor_set_profiling(orbx_extractor* e, int on) {
     return ORBX_OK;
 }
 
-static inline int grid_for(long long work_items, int threads, int cap_blocks) {
-    long long b = (work_items + threads - 1) / threads;
-    if (b > cap_blocks) b = cap_blocks;
-    if (b < 1) b = 1;
-    return (int)b;
-}
-
 extern "C" orbx_status orbx_extract_device(orbx_extractor* e, const uint8_t* d_images, size_t frame_stride,
                                            int row_stride, int batch, const int* lapping) {
     if (!e || !d_images) { orbx_set_error("null argument"); return d_images ? ORBX_ERR_INVALID : ORBX_ERR_EMPTY; }
@@ -1304,22 +1318,23 @@ extern "C" orbx_status orbx_extract_device(orbx_extractor* e, const uint8_t* d_i
         ORBX_CUDA(cudaMemcpyAsync(e->d_lapping, e->h_lapping, sizeof(int) * 2 * batch, cudaMemcpyHostToDevice, st));
         d_lap = e->d_lapping;
     }
-    const int kMaxBlocks = 148 * 16;
     if (e->profiling) ORBX_CUDA(cudaEventRecord(e->ev[0], st));
     /* stage 0 */
     {
         const LevelDev& L0 = e->T.lv[0];
         const int vec_ok = (row_stride % 16 == 0) && (frame_stride % 16 == 0) && (((uintptr_t)d_images) % 16 == 0);
-        const long long items = (long long)batch * L0.rows * (L0.pitch / 16);
-        k_level0<<<grid_for(items, 256, kMaxBlocks), 256, 0, st>>>(d_images, frame_stride, row_stride, L0, batch, vec_ok);
+        const unsigned ch0 = L0.pitch / 16;
+        k_level0<<<dim3(orbx_div_up(L0.rows * ch0, 256), batch), 256, 0, st>>>(d_images, frame_stride, row_stride, L0,
+                                                                               0xFFFFFFFFu / ch0 + 1u, vec_ok);
         ++launches;
         for (int l = 1; l < nl; ++l) {
             const LevelDev& D = e->T.lv[l];
-            const long long it = (long long)batch * D.rows * (D.pitch / 4);
+            const unsigned ch = D.pitch / 4;
+            const dim3 grid(orbx_div_up(D.rows * ch, 256), batch);
             if (D.fast_resize)
-                k_resize_w4<<<grid_for(it, 256, kMaxBlocks), 256, 0, st>>>(e->T.lv[l - 1], D, D.xcoef, D.xmeta, D.ypad, batch);
+                k_resize_w4<<<grid, 256, 0, st>>>(e->T.lv[l - 1], D, D.xcoef, D.xmeta, D.ypad, 0xFFFFFFFFu / ch + 1u);
             else
-                k_resize<<<grid_for(it, 256, kMaxBlocks), 256, 0, st>>>(e->T.lv[l - 1], D, batch);
+                k_resize<<<grid, 256, 0, st>>>(e->T.lv[l - 1], D, 0xFFFFFFFFu / ch + 1u);
             ++launches;
         }
     }
@@ -1352,7 +1367,7 @@ extern "C" orbx_status orbx_extract_device(orbx_extractor* e, const uint8_t* d_i
     {
         UMax um;
         for (int i = 0; i < 16; ++i) um.v[i] = e->umax[i];
-        k_orient_describe<<<dim3(orbx_div_up((int)e->sel_per_frame, 8), batch), 256, 0, st>>>(
+        k_orient_describe<<<dim3(orbx_div_up((int)e->sel_per_frame, OD_WARPS), batch), 32 * OD_WARPS, 0, st>>>(
             e->T, um, e->d_sel, e->sel_per_frame, e->d_sel_count, e->d_dest, e->d_kps, e->d_desc, e->kcap);
         ++launches;
     }

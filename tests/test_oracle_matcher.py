@@ -1,0 +1,143 @@
+"""CPU checks of the oracle's matcher half (no GPU): known answers, an independent numpy
+restatement of the projection search, cv2.BFMatcher for the kNN, and geometric properties of
+the stereo matcher on a synthetic pair with known disparities."""
+import numpy as np
+import pytest
+
+
+def _popcount_rows(a, b):
+    return np.unpackbits(np.asarray(a, np.uint8) ^ np.asarray(b, np.uint8), axis=-1).sum(-1)
+
+
+def test_descriptor_distance_known_answers(oracle):
+    z = np.zeros(32, np.uint8); o = np.full(32, 255, np.uint8)
+    assert oracle.descriptor_distance(z, z) == 0 and oracle.descriptor_distance(z, o) == 256
+    for bit in (0, 7, 8, 100, 255):
+        v = z.copy(); v[bit // 8] |= 1 << (bit % 8)
+        assert oracle.descriptor_distance(z, v) == 1 and oracle.descriptor_distance(o, v) == 255
+    rng = np.random.default_rng(0)
+    a = rng.integers(0, 256, (20000, 32), dtype=np.uint8); b = rng.integers(0, 256, (20000, 32), dtype=np.uint8)
+    d = oracle.hamming_pairs(a, b)
+    assert np.array_equal(d, _popcount_rows(a, b))          # the SWAR bit-hack (ORBmatcher.cc:1382-1388) == popcount
+    assert np.array_equal(d, oracle.hamming_pairs(b, a))
+
+
+def test_three_maxima_known_answers(oracle):
+    c = np.zeros(30, int); assert oracle.three_maxima(c) == (-1, -1, -1)
+    c[4] = 10; assert oracle.three_maxima(c) == (4, -1, -1)
+    c[7] = 10; assert oracle.three_maxima(c) == (4, 7, -1)            # strict >: first wins
+    c[2] = 1;  assert oracle.three_maxima(c) == (4, 7, 2)            # 1 >= 0.1*10
+    c[2] = 0; c[9] = 0; assert oracle.three_maxima(c) == (4, 7, -1)
+    c[:] = 0; c[1] = 100; c[3] = 9; c[5] = 50
+    assert oracle.three_maxima(c) == (1, 5, -1)                       # 9 < 0.1*100 dropped
+
+
+def test_knn2_matches_cv2_bfmatcher(oracle, synth):
+    cv2 = pytest.importorskip("cv2")
+    q, db, _ = synth.descriptor_sets(400, 3000, seed=8)
+    d1, i1, d2, i2 = oracle.knn2(q, db, nthreads=4)
+    m = cv2.BFMatcher(cv2.NORM_HAMMING).knnMatch(q, db, k=2)
+    cd1 = np.array([x[0].distance for x in m]); cd2 = np.array([x[1].distance for x in m])
+    ci1 = np.array([x[0].trainIdx for x in m])
+    assert np.array_equal(d1, cd1) and np.array_equal(d2, cd2)
+    uniq = d1 < d2
+    assert np.array_equal(i1[uniq], ci1[uniq])
+    # exhaustive definition
+    D = _popcount_rows(q[:, None, :], db[None, :, :])
+    o = np.argsort(D, axis=1, kind="stable")[:, :2]
+    assert np.array_equal(i1, o[:, 0]) and np.array_equal(i2, o[:, 1])
+
+
+def _sbp_numpy(F, MP, th, nnRatio, claimed=None):
+    """Independent restatement of SearchByProjection (reference src/ORBmatcher.cc:31-123): no grid
+    structure -- candidates are gathered by brute force and ordered the way the grid walk of
+    GetFeaturesInArea (src/Frame.cc:404-468) would deliver them."""
+    f32 = np.float32
+    n = len(F["kx"])
+    px = np.round((F["kx"] - f32(F["minx"])) * f32(F["gw_inv"])).astype(int)     # np.round is half-even; inputs avoid .5
+    py = np.round((F["ky"] - f32(F["miny"])) * f32(F["gh_inv"])).astype(int)
+    ok_cell = (py * F["gcols"] + px >= 0) & (py * F["gcols"] + px < F["gcols"] * F["grows"])
+    cl = np.zeros(n, bool) if claimed is None else np.asarray(claimed, bool).copy()
+    match = np.full(n, -1, np.int32)
+    nm = 0
+    for i in range(len(MP["x"])):
+        if not MP["inview"][i]:
+            continue
+        lvl = int(MP["level"][i])
+        r = f32(2.5) if np.float64(MP["viewcos"][i]) > 0.998 else f32(4.0)
+        if th != 1.0:
+            r = f32(r * f32(th))
+        r = f32(r * F["scale"][lvl])
+        x, y = MP["x"][i], MP["y"][i]
+        c0 = max(0, int(np.floor(f32(f32(x - f32(F["minx"]) - r) * f32(F["gw_inv"])))))
+        c1 = min(F["gcols"] - 1, int(np.ceil(f32(f32(x - f32(F["minx"]) + r) * f32(F["gw_inv"])))))
+        r0 = max(0, int(np.floor(f32(f32(y - f32(F["miny"]) - r) * f32(F["gh_inv"])))))
+        r1 = min(F["grows"] - 1, int(np.ceil(f32(f32(y - f32(F["miny"]) + r) * f32(F["gh_inv"])))))
+        cand = np.nonzero(ok_cell & (px >= c0) & (px <= c1) & (py >= r0) & (py <= r1) &
+                          (F["koct"] >= lvl - 1) & (F["koct"] <= lvl) &
+                          (np.abs(F["kx"] - x) < r) & (np.abs(F["ky"] - y) < r) & ~cl)[0]
+        if len(cand) == 0:
+            continue
+        cand = cand[np.lexsort((cand, py[cand], px[cand]))]
+        d = _popcount_rows(MP["desc"][i][None], F["desc"][cand])
+        best, best2, bl, bl2, bi = 256, 256, -1, -1, -1
+        for k, dist in zip(cand, d):
+            if dist < best:
+                best2, bl2 = best, bl
+                best, bl, bi = dist, F["koct"][k], k
+            elif dist < best2:
+                best2, bl2 = dist, F["koct"][k]
+        if best <= 100 and not (bl == bl2 and f32(best) > f32(nnRatio) * f32(best2)):
+            match[bi] = i; cl[bi] = True; nm += 1
+    return nm, match
+
+
+@pytest.mark.parametrize("th,seed", [(1.0, 1), (3.0, 2), (12.0, 3)])
+def test_search_by_projection_vs_numpy(oracle, synth, th, seed):
+    F = synth.frame_view(500, seed=seed)
+    MP = synth.projection_problem(F, 700, seed=seed + 10)
+    on, om = oracle.search_by_projection(F, MP, th, False, 0.0, 0.8)
+    nn, nmch = _sbp_numpy(F, MP, th, 0.8)
+    assert on == nn and np.array_equal(om, nmch) and on > 50
+
+
+def test_search_for_triangulation_properties(oracle, synth):
+    k1, k2, F12, ep, sf = synth.keyframe_pair(600, 700, 50, seed=5)
+    n, pairs = oracle.search_for_triangulation(k1, k2, F12, ep, sf, False, False, False)
+    assert n == len(pairs) > 20
+    d = _popcount_rows(k1["desc"][pairs[:, 0]], k2["desc"][pairs[:, 1]])
+    assert d.max() <= 30                                           # TH_LOW
+    assert not k1["has_mp"][pairs[:, 0]].any() and not k2["has_mp"][pairs[:, 1]].any()
+    # epipolar gate: |y2 - y1 + 0.3 - 0.002 (x2 - x1)| / sqrt(1 + 0.002^2) < sqrt(3.84)
+    x1, y1 = k1["kx"][pairs[:, 0]], k1["ky"][pairs[:, 0]]
+    x2, y2 = k2["kx"][pairs[:, 1]], k2["ky"][pairs[:, 1]]
+    dist2 = (y2 - y1 + 0.3 - 0.002 * (x2 - x1)) ** 2 / (1 + 0.002 ** 2)
+    assert dist2.max() < 3.85
+    n_ori, pairs_ori = oracle.search_for_triangulation(k1, k2, F12, ep, sf, False, False, True)
+    assert n_ori <= n and set(map(tuple, pairs_ori)) <= set(map(tuple, pairs))
+    n_c, _ = oracle.search_for_triangulation(k1, k2, F12, ep, sf, False, True, False)
+    assert n_c >= n                                                # bCoarse skips the epipolar gate
+
+
+def test_stereo_matches_recover_known_disparity(oracle, synth):
+    """Right image = left shifted by a per-32-row-band disparity: matched keypoints must report it."""
+    w, h = 640, 400
+    left, right = synth.stereo_pair(w, h, 31)
+    rng = np.random.default_rng(31 ^ 0x5EED)                       # stereo_pair's own generator
+    band_d = [int(rng.integers(4, 61)) for _ in range(0, h, 32)]
+    exL = oracle.Extractor(800, 1.2, 8, 20, 7); exR = oracle.Extractor(800, 1.2, 8, 20, 7)
+    kL, dL, _ = exL(left); kR, dR, _ = exR(right)
+    lvL = [exL.level(l) for l in range(8)]; lvR = [exR.level(l) for l in range(8)]
+    bf, b = 40.0, 0.1                                              # maxD = 400 px
+    ur, dp = oracle.stereo_matches(kL, dL, lvL, kR, dR, lvR, exL.scale, exL.inv_scale, bf, b)
+    m = ur >= 0
+    assert m.sum() > 0.3 * len(kL)
+    disp = kL["x"][m] - ur[m]
+    assert np.allclose(dp[m], bf / disp, rtol=1e-6)
+    # keypoints whose +-8 px SAD rows stay inside one band report that band's disparity (octave-scaled tolerance)
+    yy = kL["y"][m]; sc = exL.scale[kL["octave"][m]]
+    inside = ((yy - 8 * sc) // 32 == (yy + 8 * sc) // 32)
+    expect = np.array(band_d)[(yy // 32).astype(int)]
+    err = np.abs(disp - expect)[inside]
+    assert inside.sum() > 50 and np.mean(err < 1.0 * sc[inside]) > 0.9
+    assert np.all(ur[~m] == -1) and np.all(dp[~m] == -1)
