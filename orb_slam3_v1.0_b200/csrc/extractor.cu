@@ -10,7 +10,7 @@
  *
  * Stages (one launch each unless noted), all on the handle's stream:
  *   0 pyramid   k_level0 (+border) and k_resize per level (+border, recomputed not re-read)
- *   1 fast      k_fast_cells: one CTA per 35-px cell, smem tile, ini->min retry, ordered output
+ *   1 fast      k_fast_units: one CTA per run of <= 6 cells of a cell row, smem strip, ini->min retry per cell, ordered output
  *   2 octree    k_octree: one CTA per (frame, level), exact DistributeOctTree emulation
  *   3 order     k_order: level offsets + vLappingArea mono/stereo placement
  *   4 blur      k_blur7: integer 7x7 sigma-2 Gaussian
@@ -155,18 +155,31 @@ __global__ void __launch_bounds__(256) k_resize_w4(LevelDev S, LevelDev D, const
 }
 
 /* ================================================================== stage 1: FAST per cell */
-/* One CTA per 35-px FAST cell.  The cell sub-image is staged in shared memory
- * with aligned 32-bit loads; three phases keep the warps dense:
- *   A  every detection pixel: 2 opposite-pair quick reject (any 9-arc of the ring contains one
- *      pixel of each opposite pair) -> warp-aggregated compaction of the ~30% survivors
- *   B  survivors only: 16-ring bright/dark masks at minThFAST, 9-contiguity by bit tricks, score
- *      = (max over arcs of the min |difference|) - 1  == cv::FAST cornerScore
- *   C  strict 3x3 local maxima of the score map (margin reads 0 = OpenCV's zeroed score rows),
- *      iniThFAST survivors if any else minThFAST ones, written in raster order at fixed slots.
- * A corner at threshold t has score >= t, so NMS at iniThFAST = local maxima with score >= ini
- * of the minThFAST score map: one score pass serves both thresholds. */
-#define FAST_MAX_CELL 76      /* cells are at most 69+6 px (nCols==1 levels); tile pitch = cell width + alignment */
-#define FAST_THREADS 128
+/* One CTA per UNIT = a run of up to FAST_UC consecutive 35-px cells of one cell row (SURVEY App.
+ * A3).  The cells' detection areas tile the unit exactly, so the unit is processed as one dense
+ * image strip staged in shared memory, and the cell structure only enters where upstream's
+ * semantics need it: (i) NMS treats neighbours outside the pixel's own cell as score 0 (cv::FAST
+ * ran on the cell sub-image, whose 3-px margin has no scores), (ii) a cell with no keypoint at
+ * iniThFAST is redone at minThFAST, (iii) output order is cell by cell, raster inside the cell.
+ *   A  every detection pixel, 4 per thread: opposite-pair quick reject (any 9-arc of the ring
+ *      contains one pixel of each opposite pair) -> warp-aggregated compaction of the survivors
+ *   B  survivors only: 16-ring bright/dark masks, 9-contiguity by bit tricks, score = (max over
+ *      arcs of the min |difference|) - 1 == cv::FAST cornerScore, into a u8 score map
+ *   C  strict 3x3 local maxima of the score map -> per-cell buckets (unordered, global scratch)
+ *   D  one warp per cell: rank the (few) bucket entries by raster position -> ordered slots.
+ * Pass 0 runs A-C at iniThFAST over the whole unit; pass 1 re-runs them at minThFAST over the
+ * runs of cells that came out empty.  A corner at threshold t has score >= t, so the score map of
+ * pass 1 is a superset of pass 0's and needs no reset. */
+#define FAST_UC 6             /* cells per unit */
+#define FAST_THREADS 256
+#define FAST_MAX_ROWS 76      /* cells are at most 69+6 px high (nRows==1 levels) */
+
+struct Unit {
+    short level, x0, y0, tw, th, ncell, wc, pad;   /* tile origin (ROI coords), tile size, cells, wCell */
+    int cell0;                                      /* first cell in the cell table */
+    int offx0, offy;                                /* candidate coords of tile pixel (0,0) */
+    unsigned rcp_wc;                                /* floor(2^32/wc)+1 */
+};
 
 __device__ __forceinline__ bool has9(uint32_t m) {
     m |= m << 16;
@@ -191,218 +204,208 @@ __device__ __forceinline__ int arc_strength(const int* e) {
     return best;
 }
 
-/* per-byte "a > th" for 4 packed u8 (th <= 127): bit 7 of each byte of the result */
-__device__ __forceinline__ uint32_t gt4(uint32_t d, uint32_t k7f_minus_th) {
-    return (((d & 0x7f7f7f7fu) + k7f_minus_th) | d) & 0x80808080u;
+/* per-byte "d > th" for 4 packed u8: bit 7 of each byte of the result.  th <= 127: bit 7 of d
+ * decides or the low 7 bits carry; th >= 128: bit 7 of d AND the low 7 bits beat th-128. */
+__device__ __forceinline__ uint32_t gt4(uint32_t d, uint32_t k7f, bool hi) {
+    const uint32_t c = (d & 0x7f7f7f7fu) + k7f;
+    return (hi ? (c & d) : (c | d)) & 0x80808080u;
 }
 
-__global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(Tables T, const Cell* __restrict__ cells,
-                                                              int ncells, int ini_th, int min_th,
-                                                              uint32_t* __restrict__ slots, size_t slots_per_frame,
-                                                              int* __restrict__ cell_count, int tp, int rows, int list_cap) {
-    /* dynamic smem: tile | score | flag (rows x tp bytes each) | list | clist (list_cap u16 each) */
+__global__ void __launch_bounds__(FAST_THREADS) k_fast_units(Tables T, const Unit* __restrict__ units,
+                                                              const Cell* __restrict__ cells, int ncells, int ini_th,
+                                                              int min_th, uint32_t* __restrict__ slots, uint32_t* scratch,
+                                                              size_t slots_per_frame, int* __restrict__ cell_count, int tp,
+                                                              int rows, int list_cap) {
+    /* dynamic smem: tile | score (rows x tp bytes each) | list (list_cap u16) */
     extern __shared__ __align__(16) uint8_t fsm[];
-    const int WP = tp >> 2;                       /* tile pitch in words */
+    const int WP = tp >> 2;
     const int map_bytes = rows * tp;
     uint8_t* tile = fsm;
     uint8_t* score = fsm + map_bytes;
-    uint8_t* flag = fsm + 2 * map_bytes;
-    unsigned short* list = reinterpret_cast<unsigned short*>(fsm + 3 * map_bytes);
-    unsigned short* clist = list + list_cap;
-    __shared__ int s_n, s_nc;
-    __shared__ int s_cnt[FAST_THREADS / 32];
+    unsigned short* list = reinterpret_cast<unsigned short*>(fsm + 2 * map_bytes);
+    __shared__ int s_n[2];          /* survivor counters, alternating per chunk */
+    __shared__ int s_cnt[FAST_UC];
 
     const int f = blockIdx.y;
-    const Cell c = cells[blockIdx.x];
-    const LevelDev& L = T.lv[c.level];
-    const int cw = c.cw, ch = c.ch;
+    const Unit U = units[blockIdx.x];
+    const LevelDev& L = T.lv[U.level];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    const int shift = c.x0 & 3;                   /* tile column of sub-image x=0 */
-    const int nwords = (cw + shift + 3) >> 2;     /* <= tp/4 */
-    const unsigned rcp_nw = 0xFFFFFFFFu / (unsigned)nwords + 1u;
+    const int shift = U.x0 & 3;                   /* tile column of sub-image x=0 */
+    const int nwords = (U.tw + shift + 3) >> 2;   /* <= WP */
     uint32_t* tile32 = reinterpret_cast<uint32_t*>(tile);
-    uint32_t* flag32 = reinterpret_cast<uint32_t*>(flag);
+    uint32_t* score32 = reinterpret_cast<uint32_t*>(score);
+    const int wc = U.wc, ncell = U.ncell;
+    const int dh = U.th - 6;                      /* detection rows [3, th-3) */
 
-    /* stage the sub-image with aligned 32-bit loads; zero score + flag maps */
+    /* stage the strip with aligned 32-bit loads; zero the score map */
     {
-        const uint8_t* src = lv_ptr(L, f, c.x0 - shift, c.y0);
-        const int nitems = ch * nwords;
+        const unsigned rcp_nw = 0xFFFFFFFFu / (unsigned)nwords + 1u;
+        const uint8_t* src = lv_ptr(L, f, U.x0 - shift, U.y0);
+        const int nitems = U.th * nwords;
         for (int i = tid; i < nitems; i += FAST_THREADS) {
             const int y = (int)__umulhi((unsigned)i, rcp_nw);
-            const int wc = i - y * nwords;
-            tile32[y * WP + wc] = __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)y * L.pitch) + wc);
+            const int w = i - y * nwords;
+            tile32[y * WP + w] = __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)y * L.pitch) + w);
         }
-        for (int i = tid; i < ch * WP; i += FAST_THREADS) {
-            reinterpret_cast<uint32_t*>(score)[i] = 0;
-            flag32[i] = 0;
-        }
-        if (tid == 0) { s_n = 0; s_nc = 0; }
+        for (int i = tid; i < U.th * WP; i += FAST_THREADS) score32[i] = 0;
+        if (tid < FAST_UC) s_cnt[tid] = 0;
+        if (tid == 0) { s_n[0] = 0; s_n[1] = 0; }
     }
     __syncthreads();
 
-    const int dw = cw - 6, dh = ch - 6;          /* detection area (3-px margin) */
-    const int nitems = (dw > 0 && dh > 0) ? dh * nwords : 0;   /* words covering the detection rows */
-    const int tlo = 3 + shift, thi = cw - 3 + shift;            /* valid tile columns [tlo, thi) */
-    const uint32_t k7f = 0x7f7f7f7fu - (uint32_t)min_th * 0x01010101u;
-
-    /* ---- phase A: 4 pixels per thread, opposite-pair quick reject, compaction of survivors */
-    for (int base = 0; base < nitems; base += FAST_THREADS) {
-        const int i = base + tid;
-        uint32_t pass = 0;
-        int widx = 0;
-        if (i < nitems) {
-            const int y = (int)__umulhi((unsigned)i, rcp_nw);
-            const int wc = i - y * nwords;
-            widx = (y + 3) * WP + wc;
-            const uint32_t v4 = tile32[widx];
-            const uint32_t up = tile32[widx - 3 * WP], dn = tile32[widx + 3 * WP];
-            const uint32_t lw = tile32[widx - (wc > 0)], rw = tile32[widx + (wc < WP - 1)];
-            const uint32_t l4 = __funnelshift_r(lw, v4, 8);     /* bytes at column-3 */
-            const uint32_t r4 = __funnelshift_r(v4, rw, 24);    /* bytes at column+3 */
-            const uint32_t g0 = gt4(__vabsdiffu4(dn, v4), k7f), g8 = gt4(__vabsdiffu4(up, v4), k7f);
-            const uint32_t g4 = gt4(__vabsdiffu4(r4, v4), k7f), g12 = gt4(__vabsdiffu4(l4, v4), k7f);
-            pass = (g0 | g8) & (g4 | g12);
-            /* mask bytes outside [tlo, thi) */
-            const int lo = max(tlo - 4 * wc, 0), hi = min(thi - 4 * wc, 4);
-            const uint32_t vm = (hi > lo) ? ((0xFFFFFFFFu >> (8 * (4 - hi))) & (0xFFFFFFFFu << (8 * lo))) : 0u;
-            pass &= vm;
+    int chunk = 0;
+    uint32_t* bucket = scratch + (size_t)f * slots_per_frame;     /* unordered NMS survivors, per cell at slot_off */
+    for (int pass = 0; pass < 2 && dh > 0; ++pass) {
+        const int th = pass ? min_th : ini_th;
+        unsigned active = (1u << ncell) - 1u;
+        if (pass) {
+            if (min_th == ini_th) break;
+            active = 0;
+            for (int k = 0; k < ncell; ++k) active |= (unsigned)(s_cnt[k] == 0) << k;
+            if (!active) break;
         }
-        const int n = __popc(pass);
-        int inc = n;
+        const bool hi = th > 127;
+        const uint32_t k7f = (0x7fu - (uint32_t)(hi ? th - 128 : th)) * 0x01010101u;
+        for (int k0 = 0; k0 < ncell;) {
+            if (!((active >> k0) & 1u)) { ++k0; continue; }
+            int k1 = k0 + 1;
+            while (k1 < ncell && ((active >> k1) & 1u)) ++k1;
+            /* region = cells [k0, k1): tile columns [tlo, thi) */
+            const int tlo = 3 + k0 * wc + shift;
+            const int thi = (k1 == ncell ? U.tw - 3 : 3 + k1 * wc) + shift;
+            k0 = k1;
+            if (thi <= tlo) continue;
+            const int w0 = tlo >> 2, rw = ((thi - 1) >> 2) - w0 + 1;
+            const unsigned rcp_rw = 0xFFFFFFFFu / (unsigned)rw + 1u;
+            const int R = max(1, list_cap / (thi - tlo));
+
+            for (int ry = 0; ry < dh; ry += R) {
+                const int nitems = min(R, dh - ry) * rw;
+                /* ---- phase A: 4 pixels per thread, quick reject, compaction of survivors */
+                for (int base = 0; base < nitems; base += FAST_THREADS) {
+                    const int i = base + tid;
+                    uint32_t pass4 = 0;
+                    int widx = 0;
+                    if (i < nitems) {
+                        const int y = (int)__umulhi((unsigned)i, rcp_rw);
+                        const int w = w0 + i - y * rw;
+                        widx = (y + ry + 3) * WP + w;
+                        const uint32_t v4 = tile32[widx];
+                        const uint32_t up = tile32[widx - 3 * WP], dn = tile32[widx + 3 * WP];
+                        const uint32_t lw = tile32[widx - (w > 0)], rgt = tile32[widx + (w < WP - 1)];
+                        const uint32_t l4 = __funnelshift_r(lw, v4, 8);      /* bytes at column-3 */
+                        const uint32_t r4 = __funnelshift_r(v4, rgt, 24);    /* bytes at column+3 */
+                        const uint32_t g0 = gt4(__vabsdiffu4(dn, v4), k7f, hi), g8 = gt4(__vabsdiffu4(up, v4), k7f, hi);
+                        const uint32_t g4 = gt4(__vabsdiffu4(r4, v4), k7f, hi), g12 = gt4(__vabsdiffu4(l4, v4), k7f, hi);
+                        pass4 = (g0 | g8) & (g4 | g12);
+                        /* mask bytes outside [tlo, thi) */
+                        const int lo = max(tlo - 4 * w, 0), hi4 = min(thi - 4 * w, 4);
+                        const uint32_t vm = (hi4 > lo) ? ((0xFFFFFFFFu >> (8 * (4 - hi4))) & (0xFFFFFFFFu << (8 * lo))) : 0u;
+                        pass4 &= vm;
+                    }
+                    const int n = __popc(pass4);
+                    int inc = n;
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const int t = __shfl_up_sync(0xffffffffu, inc, o);
-            if (lane >= o) inc += t;
-        }
-        const int wtot = __shfl_sync(0xffffffffu, inc, 31);
-        if (wtot) {
-            int b = 0;
-            if (lane == 31) b = atomicAdd(&s_n, wtot);
-            b = __shfl_sync(0xffffffffu, b, 31) + inc - n;
-            uint32_t m = pass;
-            while (m) {
-                const int bit = __ffs(m) - 1;        /* 7, 15, 23 or 31 */
-                m &= m - 1;
-                list[b++] = (unsigned short)(widx * 4 + (bit >> 3));
-            }
-        }
-    }
-    __syncthreads();
+                    for (int o = 1; o < 32; o <<= 1) {
+                        const int t = __shfl_up_sync(0xffffffffu, inc, o);
+                        if (lane >= o) inc += t;
+                    }
+                    const int wtot = __shfl_sync(0xffffffffu, inc, 31);
+                    if (wtot) {
+                        int b = 0;
+                        if (lane == 31) b = atomicAdd(&s_n[chunk & 1], wtot);
+                        b = __shfl_sync(0xffffffffu, b, 31) + inc - n;
+                        uint32_t m = pass4;
+                        while (m) {
+                            const int bit = __ffs(m) - 1;        /* 7, 15, 23 or 31 */
+                            m &= m - 1;
+                            list[b++] = (unsigned short)(widx * 4 + (bit >> 3));
+                        }
+                    }
+                }
+                __syncthreads();
 
-    /* ---- phase B: exact FAST-9 test + score for the survivors */
-    const int nsurv = s_n;
-    for (int base = 0; base < nsurv; base += FAST_THREADS) {
-        const int j = base + tid;
-        bool corner = false;
-        int idx = 0;
-        if (j < nsurv) {
-            idx = list[j];
-            const uint8_t* p = tile + idx;
-            const int v = p[0];
-            /* one IMAD per ring pixel: upper half = (v+th) - r  (negative <=> brighter),
-             * lower half = r - (v-th) (negative <=> darker); a borrow from the lower half can
-             * only happen when r < v-th, where the upper half is >= 2*th+1 and stays positive */
-            const int C = ((v + min_th) << 16) - (v - min_th);
-            uint32_t acc = 0;
+                /* ---- phase B: exact FAST-9 test + score for the survivors */
+                const int nsurv = s_n[chunk & 1];
+                if (tid == 0) s_n[(chunk + 1) & 1] = 0;      /* nobody touches the other counter before the next barrier */
+                for (int j = tid; j < nsurv; j += FAST_THREADS) {
+                    const int idx = list[j];
+                    const uint8_t* p = tile + idx;
+                    const int v = p[0];
+                    /* one IMAD per ring pixel: upper half = (v+th) - r  (negative <=> brighter),
+                     * lower half = r - (v-th) (negative <=> darker); a borrow from the lower half can
+                     * only happen when r < v-th, where the upper half is >= 2*th+1 and stays positive */
+                    const int C = ((v + th) << 16) - (v - th);
+                    uint32_t acc = 0;
 #define FAST_RING(OFF) acc = (acc >> 1) | ((uint32_t)(C - 65535 * (int)p[OFF]) & 0x80008000u)
-            FAST_RING(3 * tp);      FAST_RING(3 * tp + 1);   FAST_RING(2 * tp + 2);   FAST_RING(tp + 3);
-            FAST_RING(3);           FAST_RING(-tp + 3);      FAST_RING(-2 * tp + 2);  FAST_RING(-3 * tp + 1);
-            FAST_RING(-3 * tp);     FAST_RING(-3 * tp - 1);  FAST_RING(-2 * tp - 2);  FAST_RING(-tp - 3);
-            FAST_RING(-3);          FAST_RING(tp - 3);       FAST_RING(2 * tp - 2);   FAST_RING(3 * tp - 1);
+                    FAST_RING(3 * tp);      FAST_RING(3 * tp + 1);   FAST_RING(2 * tp + 2);   FAST_RING(tp + 3);
+                    FAST_RING(3);           FAST_RING(-tp + 3);      FAST_RING(-2 * tp + 2);  FAST_RING(-3 * tp + 1);
+                    FAST_RING(-3 * tp);     FAST_RING(-3 * tp - 1);  FAST_RING(-2 * tp - 2);  FAST_RING(-tp - 3);
+                    FAST_RING(-3);          FAST_RING(tp - 3);       FAST_RING(2 * tp - 2);   FAST_RING(3 * tp - 1);
 #undef FAST_RING
-            const bool bright = has9(acc >> 16), dark = has9(acc & 0xFFFFu);   /* mutually exclusive */
-            if (bright || dark) {
-                corner = true;
-                const int sgn = dark ? -1 : 1;
-                int e[16];
-                e[0] = p[3 * tp];          e[1] = p[3 * tp + 1];   e[2] = p[2 * tp + 2];   e[3] = p[tp + 3];
-                e[4] = p[3];               e[5] = p[-tp + 3];      e[6] = p[-2 * tp + 2];  e[7] = p[-3 * tp + 1];
-                e[8] = p[-3 * tp];         e[9] = p[-3 * tp - 1];  e[10] = p[-2 * tp - 2]; e[11] = p[-tp - 3];
-                e[12] = p[-3];             e[13] = p[tp - 3];      e[14] = p[2 * tp - 2];  e[15] = p[3 * tp - 1];
+                    const bool bright = has9(acc >> 16), dark = has9(acc & 0xFFFFu);   /* mutually exclusive */
+                    if (bright || dark) {
+                        const int sgn = dark ? -1 : 1;
+                        int e[16];
+                        e[0] = p[3 * tp];          e[1] = p[3 * tp + 1];   e[2] = p[2 * tp + 2];   e[3] = p[tp + 3];
+                        e[4] = p[3];               e[5] = p[-tp + 3];      e[6] = p[-2 * tp + 2];  e[7] = p[-3 * tp + 1];
+                        e[8] = p[-3 * tp];         e[9] = p[-3 * tp - 1];  e[10] = p[-2 * tp - 2]; e[11] = p[-tp - 3];
+                        e[12] = p[-3];             e[13] = p[tp - 3];      e[14] = p[2 * tp - 2];  e[15] = p[3 * tp - 1];
 #pragma unroll
-                for (int k = 0; k < 16; ++k) e[k] = sgn * (e[k] - v);
-                score[idx] = (uint8_t)(arc_strength(e) - 1);   /* strength > min_th >= 1 */
+                        for (int k = 0; k < 16; ++k) e[k] = sgn * (e[k] - v);
+                        score[idx] = (uint8_t)(arc_strength(e) - 1);   /* strength > th >= 1 */
+                    }
+                }
+                __syncthreads();
+                ++chunk;
             }
-        }
-        const unsigned bal = __ballot_sync(0xffffffffu, corner);
-        if (bal) {
-            int b = 0;
-            if (lane == 0) b = atomicAdd(&s_nc, __popc(bal));
-            b = __shfl_sync(0xffffffffu, b, 0);
-            if (corner) clist[b + __popc(bal & ((1u << lane) - 1))] = (unsigned short)idx;
-        }
-    }
-    __syncthreads();
 
-    /* ---- phase C1: strict 3x3 local maxima among the corners -> flag map (1 = keep at
-     * minThFAST, 2 = keep at iniThFAST too).  Margin/non-corner scores read 0. */
-    const int ncorn = s_nc;
-    int my2 = 0;
-    for (int j = tid; j < ncorn; j += FAST_THREADS) {
-        const int idx = clist[j];
-        const uint8_t* s = score + idx;
-        const int v = s[0];
-        if (v > s[-1] && v > s[1] && v > s[-tp - 1] && v > s[-tp] && v > s[-tp + 1] &&
-            v > s[tp - 1] && v > s[tp] && v > s[tp + 1]) {
-            const int k = (v >= ini_th) ? 2 : 1;
-            flag[idx] = (uint8_t)k;
-            my2 |= (k == 2);
+            /* ---- phase C: strict 3x3 local maxima inside the pixel's own cell -> cell buckets */
+            const int citems = dh * rw;
+            for (int i = tid; i < citems; i += FAST_THREADS) {
+                const int y = (int)__umulhi((unsigned)i, rcp_rw);
+                const int w = w0 + i - y * rw;
+                uint32_t s4 = score32[(y + 3) * WP + w];
+                if (!s4) continue;
+                const int lo = max(tlo - 4 * w, 0), hi4 = min(thi - 4 * w, 4);
+                for (int bb = lo; bb < hi4; ++bb) {
+                    const int v = (s4 >> (8 * bb)) & 0xFF;
+                    if (!v) continue;
+                    const int t = 4 * w + bb;                       /* tile column */
+                    const int xs = t - shift - 3;                   /* column inside the unit's detection area */
+                    const int k = min((int)__umulhi((unsigned)xs, U.rcp_wc), ncell - 1);
+                    const bool lft = xs != k * wc;                  /* left / right neighbours belong to the same cell */
+                    const bool rgt = (k == ncell - 1) ? (t + 1 < U.tw - 3 + shift) : (xs + 1 != (k + 1) * wc);
+                    const uint8_t* sp = score + (y + 3) * tp + t;
+                    bool mx = v > sp[-tp] && v > sp[tp];
+                    if (lft) mx = mx && v > sp[-1] && v > sp[-tp - 1] && v > sp[tp - 1];
+                    if (rgt) mx = mx && v > sp[1] && v > sp[-tp + 1] && v > sp[tp + 1];
+                    if (mx) {
+                        const int pos = atomicAdd(&s_cnt[k], 1);
+                        bucket[cells[U.cell0 + k].slot_off + pos] =
+                            (uint32_t)(t - shift + U.offx0) | ((uint32_t)(y + 3 + U.offy) << 12) | ((uint32_t)v << 24);
+                    }
+                }
+            }
+            __syncthreads();
         }
     }
-    const int need = __syncthreads_or(my2) ? 2 : 1;      /* per-cell retry with minThFAST */
 
-    /* ---- phase C2/C3: ordered (raster) output; warp w owns a contiguous range of flag words */
-    const int seg = (((nitems + FAST_THREADS / 32 - 1) / (FAST_THREADS / 32)) + 31) & ~31;
-    const int beg = wid * seg, end = min(beg + seg, nitems);
-    int cnt = 0;
-    for (int i = beg + lane; i < end; i += 32) {
-        const int y = (int)__umulhi((unsigned)i, rcp_nw);
-        const uint32_t f4 = flag32[(y + 3) * WP + (i - y * nwords)];
-        cnt += __popc(need == 2 ? (f4 & 0x02020202u) : ((f4 | (f4 >> 1)) & 0x01010101u));
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
-    if (lane == 0) s_cnt[wid] = cnt;
-    __syncthreads();
-    int off = 0, tot = 0;
-#pragma unroll
-    for (int w = 0; w < FAST_THREADS / 32; ++w) {
-        if (w < wid) off += s_cnt[w];
-        tot += s_cnt[w];
-    }
-    uint32_t* out = slots + (size_t)f * slots_per_frame + c.slot_off;
-    if (cnt) {
-        for (int base = beg; base < end; base += 32) {
-            const int i = base + lane;
-            uint32_t k4 = 0;
-            int y = 0, wc = 0;
-            if (i < end) {
-                y = (int)__umulhi((unsigned)i, rcp_nw);
-                wc = i - y * nwords;
-                const uint32_t f4 = flag32[(y + 3) * WP + wc];
-                k4 = need == 2 ? ((f4 >> 1) & 0x01010101u) : ((f4 | (f4 >> 1)) & 0x01010101u);
-            }
-            const unsigned bal = __ballot_sync(0xffffffffu, k4 != 0);
-            if (!bal) continue;
-            const int n = __popc(k4);
-            int inc = n;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const int t = __shfl_up_sync(0xffffffffu, inc, o);
-                if (lane >= o) inc += t;
-            }
-            int o2 = off + inc - n;
-            while (k4) {
-                const int bit = __ffs(k4) - 1;       /* 0, 8, 16 or 24 */
-                k4 &= k4 - 1;
-                const int t = 4 * wc + (bit >> 3);   /* tile column */
-                const int idx = (y + 3) * tp + t;
-                out[o2++] = (uint32_t)(t - shift + c.offx) | ((uint32_t)(y + 3 + c.offy) << 12) | ((uint32_t)score[idx] << 24);
-            }
-            off += __shfl_sync(0xffffffffu, inc, 31);
+    /* ---- phase D: cell by cell, raster order inside the cell (rank by packed y|x) */
+    for (int k = wid; k < ncell; k += FAST_THREADS / 32) {
+        const int n = s_cnt[k];
+        const int so = cells[U.cell0 + k].slot_off;
+        const uint32_t* src = bucket + so;
+        uint32_t* dst = slots + (size_t)f * slots_per_frame + so;
+        for (int e = lane; e < n; e += 32) {
+            const uint32_t ent = src[e];
+            const uint32_t key = ent & 0xFFFFFFu;
+            int rank = 0;
+            for (int j = 0; j < n; ++j) rank += (src[j] & 0xFFFFFFu) < key;
+            dst[rank] = ent;
         }
+        if (lane == 0) cell_count[(size_t)f * ncells + U.cell0 + k] = n;
     }
-    if (tid == 0) cell_count[(size_t)f * ncells + blockIdx.x] = tot;
 }
 
 /* ================================================================== stage 2: quadtree */
@@ -1008,7 +1011,7 @@ static void free_all(orbx_extractor* e) {
     cudaSetDevice(e->P.device);
     void* dptrs[] = {e->d_pyr, e->d_blur, e->d_input, e->d_tabs, e->d_wtabs, e->d_cells, e->d_blur_tiles, e->d_slots,
                      e->d_cell_count, e->d_cand, e->d_pnode, e->d_cand_count, e->d_sel, e->d_sel_count,
-                     e->d_dest, e->d_lapping, e->d_kps, e->d_desc, e->d_nk, e->d_uright, e->d_depth, e->d_pairs,
+                     e->d_dest, e->d_lapping, e->d_kps, e->d_desc, e->d_nk, e->d_units, e->d_uright, e->d_depth, e->d_pairs,
                      e->d_rowent};
     for (void* p : dptrs) if (p) cudaFree(p);
     void* hptrs[] = {e->h_kps, e->h_desc, e->h_nk, e->h_lapping, e->h_uright, e->h_depth, e->h_pairs};
@@ -1069,6 +1072,7 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
     size_t pyr_bytes = 0, blur_bytes = 0, tab_entries = 0;
     size_t slot_off = 0, cand_off = 0, sel_off = 0;
     std::vector<int4> blur_tiles;
+    std::vector<Unit> units;
     int maxn = 8;
     for (int l = 0; l < nl; ++l) {
         LevelDev& L = e->lv[l];
@@ -1103,6 +1107,7 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
                 float maxY = iniY + hCell + 6;
                 if (iniY >= maxBY - 3) continue;
                 if (maxY > maxBY) maxY = maxBY;
+                const int row_first = (int)e->cells.size();
                 for (int j = 0; j < nCols; j++) {
                     const float iniX = minB + j * wCell;
                     float maxX = iniX + wCell + 6;
@@ -1113,11 +1118,8 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
                     c.cw = (short)((int)maxX - (int)iniX); c.ch = (short)((int)maxY - (int)iniY);
                     c.offx = (short)(j * wCell); c.offy = (short)(i * hCell); c.pad = 0;
                     c.slot_off = (int)slot_off;
-                    e->fast_tp = std::max(e->fast_tp, 4 * ((c.cw + 6) >> 2));
-                    e->fast_rows = std::max(e->fast_rows, (int)c.ch);
-                    e->fast_list_cap = std::max(e->fast_list_cap, (std::max(c.cw - 6, 0) * std::max(c.ch - 6, 0) + 1) & ~1);
-                    if (c.cw > FAST_MAX_CELL || c.ch > FAST_MAX_CELL) {
-                        orbx_set_error("FAST cell %dx%d exceeds the %d-px tile", c.cw, c.ch, FAST_MAX_CELL);
+                    if (c.ch > FAST_MAX_ROWS) {
+                        orbx_set_error("FAST cell %dx%d exceeds the %d-row tile", c.cw, c.ch, FAST_MAX_ROWS);
                         free_all(e);
                         return ORBX_ERR_INVALID;
                     }
@@ -1127,6 +1129,22 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
                     slot_off += cap;
                     cand_off += cap;
                     e->cells.push_back(c);
+                }
+                /* FAST units: the row's cells in runs of <= FAST_UC, evenly sized */
+                const int nrow = (int)e->cells.size() - row_first;
+                const int nun = orbx_div_up(nrow, FAST_UC);
+                for (int u = 0, k = 0; u < nun; ++u) {
+                    const int nc = (nrow - k + (nun - u) - 1) / (nun - u);
+                    const Cell& a = e->cells[row_first + k];
+                    const Cell& z = e->cells[row_first + k + nc - 1];
+                    Unit U;
+                    U.level = (short)l; U.x0 = a.x0; U.y0 = a.y0; U.tw = (short)(z.x0 + z.cw - a.x0); U.th = a.ch;
+                    U.ncell = (short)nc; U.wc = (short)wCell; U.pad = 0; U.cell0 = row_first + k;
+                    U.offx0 = a.offx; U.offy = a.offy; U.rcp_wc = 0xFFFFFFFFu / (unsigned)wCell + 1u;
+                    units.push_back(U);
+                    e->fast_tp = std::max(e->fast_tp, 4 * ((U.tw + 6) >> 2));
+                    e->fast_rows = std::max(e->fast_rows, (int)U.th);
+                    k += nc;
                 }
             }
         }
@@ -1167,6 +1185,12 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
     CK(cudaMalloc(&e->d_input, (size_t)B * p->width * p->height));
     CK(cudaMalloc(&e->d_tabs, tab_entries * sizeof(short4)));
     CK(cudaMalloc(&e->d_cells, std::max<size_t>(e->cells.size(), 1) * sizeof(Cell)));
+    e->nunits = (int)units.size();
+    e->fast_list_cap = 4096;            /* u16 entries; >= FAST_UC * widest cell, so a one-row chunk always fits */
+    CK(cudaMalloc(&e->d_units, std::max<size_t>(units.size(), 1) * sizeof(Unit)));
+    if (!units.empty()) CK(cudaMemcpy(e->d_units, units.data(), units.size() * sizeof(Unit), cudaMemcpyHostToDevice));
+    CK(cudaFuncSetAttribute(k_fast_units, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                            (int)std::max<size_t>((size_t)2 * e->fast_rows * e->fast_tp + 2 * (size_t)e->fast_list_cap, 48 * 1024)));
     CK(cudaMalloc(&e->d_blur_tiles, blur_tiles.size() * sizeof(int4)));
     CK(cudaMalloc(&e->d_slots, std::max<size_t>(e->slots_per_frame, 1) * B * 4));
     CK(cudaMalloc(&e->d_cell_count, (size_t)std::max(e->ncells, 1) * B * 4));
@@ -1341,9 +1365,9 @@ extern "C" orbx_status orbx_extract_device(orbx_extractor* e, const uint8_t* d_i
     if (e->profiling) ORBX_CUDA(cudaEventRecord(e->ev[1], st));
     /* stage 1 */
     if (e->ncells > 0) {
-        k_fast_cells<<<dim3(e->ncells, batch), FAST_THREADS, (size_t)3 * e->fast_rows * e->fast_tp + 4 * (size_t)e->fast_list_cap, st>>>(e->T, e->d_cells, e->ncells, e->P.ini_th_fast,
-                                                                       e->P.min_th_fast, e->d_slots, e->slots_per_frame,
-                                                                       e->d_cell_count, e->fast_tp, e->fast_rows, e->fast_list_cap);
+        k_fast_units<<<dim3(e->nunits, batch), FAST_THREADS, (size_t)2 * e->fast_rows * e->fast_tp + 2 * (size_t)e->fast_list_cap, st>>>(
+            e->T, static_cast<const Unit*>(e->d_units), e->d_cells, e->ncells, e->P.ini_th_fast, e->P.min_th_fast, e->d_slots,
+            e->d_cand, e->slots_per_frame, e->d_cell_count, e->fast_tp, e->fast_rows, e->fast_list_cap);
         ++launches;
     }
     if (e->profiling) ORBX_CUDA(cudaEventRecord(e->ev[2], st));

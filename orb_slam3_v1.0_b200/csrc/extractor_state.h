@@ -64,6 +64,8 @@ struct orbx_extractor {
     size_t oct_smem = 0;
     int nblur_tiles = 0;
     int fast_tp = 8, fast_rows = 8, fast_list_cap = 2;
+    int nunits = 0;
+    void* d_units = nullptr;        /* FAST units (extractor.cu: struct Unit) */
     cudaStream_t stream = nullptr;
     /* device buffers */
     uint8_t* d_pyr = nullptr;
