@@ -216,14 +216,14 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_units(Tables T, const Uni
                                                               int min_th, uint32_t* __restrict__ slots, uint32_t* scratch,
                                                               size_t slots_per_frame, int* __restrict__ cell_count, int tp,
                                                               int rows, int list_cap) {
-    /* dynamic smem: tile | score (rows x tp bytes each) | list (list_cap u16) */
+    /* dynamic smem: tile | score (rows x tp bytes each) | list (list_cap u16) | clist (2 x list_cap u16) */
     extern __shared__ __align__(16) uint8_t fsm[];
     const int WP = tp >> 2;
     const int map_bytes = rows * tp;
     uint8_t* tile = fsm;
     uint8_t* score = fsm + map_bytes;
     unsigned short* list = reinterpret_cast<unsigned short*>(fsm + 2 * map_bytes);
-    __shared__ int s_n[2];          /* survivor counters, alternating per chunk */
+    __shared__ int s_n[2], s_nc[2]; /* survivor / corner counters, alternating per chunk */
     __shared__ int s_cnt[FAST_UC];
 
     const int f = blockIdx.y;
@@ -249,12 +249,15 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_units(Tables T, const Uni
         }
         for (int i = tid; i < U.th * WP; i += FAST_THREADS) score32[i] = 0;
         if (tid < FAST_UC) s_cnt[tid] = 0;
-        if (tid == 0) { s_n[0] = 0; s_n[1] = 0; }
+        if (tid == 0) { s_n[0] = 0; s_n[1] = 0; s_nc[0] = 0; s_nc[1] = 0; }
     }
     __syncthreads();
 
-    int chunk = 0;
+    const unsigned rcp_tp = 0xFFFFFFFFu / (unsigned)tp + 1u;
     uint32_t* bucket = scratch + (size_t)f * slots_per_frame;     /* unordered NMS survivors, per cell at slot_off */
+    unsigned short* clist = list + list_cap;                      /* [2][list_cap] corners of the current / previous chunk */
+    const unsigned lt_mask = (1u << lane) - 1u;
+    int chunk = 0;
     for (int pass = 0; pass < 2 && dh > 0; ++pass) {
         const int th = pass ? min_th : ini_th;
         unsigned active = (1u << ncell) - 1u;
@@ -275,117 +278,144 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_units(Tables T, const Uni
             const int thi = (k1 == ncell ? U.tw - 3 : 3 + k1 * wc) + shift;
             k0 = k1;
             if (thi <= tlo) continue;
-            const int w0 = tlo >> 2, rw = ((thi - 1) >> 2) - w0 + 1;
-            const unsigned rcp_rw = 0xFFFFFFFFu / (unsigned)rw + 1u;
+            const int w0 = tlo >> 2, wl = (thi - 1) >> 2, rw = wl - w0 + 1;
+            const uint32_t m_first = 0xFFFFFFFFu << (8 * (tlo & 3));
+            const uint32_t m_last = 0xFFFFFFFFu >> (8 * (3 - ((thi - 1) & 3)));
             const int R = max(1, list_cap / (thi - tlo));
+            /* flat (row, word) walk with stride FAST_THREADS, advanced incrementally */
+            const int dy = FAST_THREADS / rw, dw = FAST_THREADS - dy * rw;
+            const int y_init = tid / rw, w_init = tid - y_init * rw;
+            int ncorn_prev = 0;
 
-            for (int ry = 0; ry < dh; ry += R) {
-                const int nitems = min(R, dh - ry) * rw;
+            for (int ry = 0; ry < dh; ry += R, ++chunk) {
+                const int nrow = min(R, dh - ry);
+                int* cnt_a = &s_n[chunk & 1];
+                int* cnt_c = &s_nc[chunk & 1];
+                unsigned short* cl = clist + (chunk & 1) * list_cap;
                 /* ---- phase A: 4 pixels per thread, quick reject, compaction of survivors */
-                for (int base = 0; base < nitems; base += FAST_THREADS) {
-                    const int i = base + tid;
-                    uint32_t pass4 = 0;
-                    int widx = 0;
-                    if (i < nitems) {
-                        const int y = (int)__umulhi((unsigned)i, rcp_rw);
-                        const int w = w0 + i - y * rw;
-                        widx = (y + ry + 3) * WP + w;
-                        const uint32_t v4 = tile32[widx];
-                        const uint32_t up = tile32[widx - 3 * WP], dn = tile32[widx + 3 * WP];
-                        const uint32_t lw = tile32[widx - (w > 0)], rgt = tile32[widx + (w < WP - 1)];
-                        const uint32_t l4 = __funnelshift_r(lw, v4, 8);      /* bytes at column-3 */
-                        const uint32_t r4 = __funnelshift_r(v4, rgt, 24);    /* bytes at column+3 */
-                        const uint32_t g0 = gt4(__vabsdiffu4(dn, v4), k7f, hi), g8 = gt4(__vabsdiffu4(up, v4), k7f, hi);
-                        const uint32_t g4 = gt4(__vabsdiffu4(r4, v4), k7f, hi), g12 = gt4(__vabsdiffu4(l4, v4), k7f, hi);
-                        pass4 = (g0 | g8) & (g4 | g12);
-                        /* mask bytes outside [tlo, thi) */
-                        const int lo = max(tlo - 4 * w, 0), hi4 = min(thi - 4 * w, 4);
-                        const uint32_t vm = (hi4 > lo) ? ((0xFFFFFFFFu >> (8 * (4 - hi4))) & (0xFFFFFFFFu << (8 * lo))) : 0u;
-                        pass4 &= vm;
+                {
+                    int y = y_init, w = w_init;
+                    const int iters = (nrow * rw + FAST_THREADS - 1) / FAST_THREADS;
+                    for (int it = 0; it < iters; ++it) {
+                        uint32_t pass4 = 0;
+                        int widx = 0;
+                        if (y < nrow) {
+                            widx = (y + ry + 3) * WP + w0 + w;
+                            const uint32_t v4 = tile32[widx];
+                            const uint32_t up = tile32[widx - 3 * WP], dn = tile32[widx + 3 * WP];
+                            const uint32_t lw = tile32[widx - 1], rgt = tile32[widx + 1];   /* in-tile: rows 3..th-4 */
+                            const uint32_t l4 = __funnelshift_r(lw, v4, 8);      /* bytes at column-3 */
+                            const uint32_t r4 = __funnelshift_r(v4, rgt, 24);    /* bytes at column+3 */
+                            const uint32_t g0 = gt4(__vabsdiffu4(dn, v4), k7f, hi), g8 = gt4(__vabsdiffu4(up, v4), k7f, hi);
+                            const uint32_t g4 = gt4(__vabsdiffu4(r4, v4), k7f, hi), g12 = gt4(__vabsdiffu4(l4, v4), k7f, hi);
+                            pass4 = (g0 | g8) & (g4 | g12);
+                            if (w == 0) pass4 &= m_first;
+                            if (w == rw - 1) pass4 &= m_last;
+                        }
+                        /* warp prefix of the per-lane survivor counts (0..4) from three ballots */
+                        const int n = __popc(pass4);
+                        const unsigned b0 = __ballot_sync(0xffffffffu, n & 1), b1 = __ballot_sync(0xffffffffu, n & 2),
+                                       b2 = __ballot_sync(0xffffffffu, n & 4);
+                        const int wtot = __popc(b0) + 2 * __popc(b1) + 4 * __popc(b2);
+                        if (wtot) {
+                            int b = 0;
+                            if (lane == 0) b = atomicAdd(cnt_a, wtot);
+                            b = __shfl_sync(0xffffffffu, b, 0) + __popc(b0 & lt_mask) + 2 * __popc(b1 & lt_mask) + 4 * __popc(b2 & lt_mask);
+                            const int p4 = widx * 4;
+                            if (pass4 & 0x00000080u) list[b++] = (unsigned short)(p4);
+                            if (pass4 & 0x00008000u) list[b++] = (unsigned short)(p4 + 1);
+                            if (pass4 & 0x00800000u) list[b++] = (unsigned short)(p4 + 2);
+                            if (pass4 & 0x80000000u) list[b] = (unsigned short)(p4 + 3);
+                        }
+                        y += dy; w += dw;
+                        if (w >= rw) { w -= rw; ++y; }
                     }
-                    const int n = __popc(pass4);
-                    int inc = n;
-#pragma unroll
-                    for (int o = 1; o < 32; o <<= 1) {
-                        const int t = __shfl_up_sync(0xffffffffu, inc, o);
-                        if (lane >= o) inc += t;
+                }
+                __syncthreads();
+                /* ---- phase B1: exact FAST-9 test on the survivors -> corner list */
+                const int nsurv = *cnt_a;
+                if (tid == 0) s_n[(chunk + 1) & 1] = 0;      /* nobody touches the other counter before the next barrier */
+                for (int base = 0; base < nsurv; base += FAST_THREADS) {
+                    const int j = base + tid;
+                    bool corner = false;
+                    int idx = 0;
+                    if (j < nsurv) {
+                        idx = list[j];
+                        const uint8_t* p = tile + idx;
+                        const int v = p[0];
+                        /* one IMAD per ring pixel: upper half = (v+th) - r  (negative <=> brighter),
+                         * lower half = r - (v-th) (negative <=> darker); a borrow from the lower half can
+                         * only happen when r < v-th, where the upper half is >= 2*th+1 and stays positive */
+                        const int C = ((v + th) << 16) - (v - th);
+                        uint32_t acc = 0;
+#define FAST_RING(OFF) acc = (acc >> 1) | ((uint32_t)(C - 65535 * (int)p[OFF]) & 0x80008000u)
+                        FAST_RING(3 * tp);      FAST_RING(3 * tp + 1);   FAST_RING(2 * tp + 2);   FAST_RING(tp + 3);
+                        FAST_RING(3);           FAST_RING(-tp + 3);      FAST_RING(-2 * tp + 2);  FAST_RING(-3 * tp + 1);
+                        FAST_RING(-3 * tp);     FAST_RING(-3 * tp - 1);  FAST_RING(-2 * tp - 2);  FAST_RING(-tp - 3);
+                        FAST_RING(-3);          FAST_RING(tp - 3);       FAST_RING(2 * tp - 2);   FAST_RING(3 * tp - 1);
+#undef FAST_RING
+                        const bool dark = has9(acc & 0xFFFFu);
+                        corner = dark || has9(acc >> 16);             /* bright and dark are mutually exclusive */
+                        idx |= dark ? 0x8000 : 0;                     /* tile index < 2^15 (checked on the host) */
                     }
-                    const int wtot = __shfl_sync(0xffffffffu, inc, 31);
-                    if (wtot) {
+                    const unsigned bal = __ballot_sync(0xffffffffu, corner);
+                    if (bal) {
                         int b = 0;
-                        if (lane == 31) b = atomicAdd(&s_n[chunk & 1], wtot);
-                        b = __shfl_sync(0xffffffffu, b, 31) + inc - n;
-                        uint32_t m = pass4;
-                        while (m) {
-                            const int bit = __ffs(m) - 1;        /* 7, 15, 23 or 31 */
-                            m &= m - 1;
-                            list[b++] = (unsigned short)(widx * 4 + (bit >> 3));
+                        if (lane == 0) b = atomicAdd(cnt_c, __popc(bal));
+                        b = __shfl_sync(0xffffffffu, b, 0);
+                        if (corner) cl[b + __popc(bal & lt_mask)] = (unsigned short)idx;
+                    }
+                }
+                __syncthreads();
+
+                /* ---- phase B2: corner score, one thread per corner (dense) */
+                const int ncorn = *cnt_c;
+                if (tid == 0) s_nc[(chunk + 1) & 1] = 0;     /* its last readers took it before two barriers ago */
+                for (int j = tid; j < ncorn; j += FAST_THREADS) {
+                    const int ce = cl[j];
+                    const int idx = ce & 0x7FFF;
+                    const uint8_t* p = tile + idx;
+                    const int v = p[0];
+                    const int sgn = (ce & 0x8000) ? -1 : 1;
+                    int e[16];
+                    e[0] = p[3 * tp];          e[1] = p[3 * tp + 1];   e[2] = p[2 * tp + 2];   e[3] = p[tp + 3];
+                    e[4] = p[3];               e[5] = p[-tp + 3];      e[6] = p[-2 * tp + 2];  e[7] = p[-3 * tp + 1];
+                    e[8] = p[-3 * tp];         e[9] = p[-3 * tp - 1];  e[10] = p[-2 * tp - 2]; e[11] = p[-tp - 3];
+                    e[12] = p[-3];             e[13] = p[tp - 3];      e[14] = p[2 * tp - 2];  e[15] = p[3 * tp - 1];
+#pragma unroll
+                    for (int k = 0; k < 16; ++k) e[k] = sgn * (e[k] - v);
+                    score[idx] = (uint8_t)(arc_strength(e) - 1);   /* strength > th >= 1 */
+                }
+                __syncthreads();
+
+                /* ---- phase C (one chunk behind: its last row needs this chunk's first score row):
+                 * strict 3x3 local maxima inside the pixel's own cell -> cell buckets */
+                for (int half = 0; half < 2; ++half) {
+                    const bool last = ry + R >= dh;
+                    if (half == 1 && !last) break;
+                    const int nc_ = half ? ncorn : ncorn_prev;
+                    const unsigned short* cc = half ? cl : clist + ((chunk + 1) & 1) * list_cap;
+                    for (int j = tid; j < nc_; j += FAST_THREADS) {
+                        const int idx = cc[j] & 0x7FFF;
+                        const int y = (int)__umulhi((unsigned)idx, rcp_tp);
+                        const int t = idx - y * tp;                       /* tile column */
+                        const int xs = t - shift - 3;                     /* column inside the unit's detection area */
+                        const int k = min((int)__umulhi((unsigned)xs, U.rcp_wc), ncell - 1);
+                        const bool lft = xs != k * wc;                    /* left / right neighbours belong to the same cell */
+                        const bool rgt = (k == ncell - 1) ? (t + 1 < U.tw - 3 + shift) : (xs + 1 != (k + 1) * wc);
+                        const uint8_t* sp = score + idx;
+                        const int v = sp[0];
+                        bool mx = v > sp[-tp] && v > sp[tp];
+                        if (lft) mx = mx && v > sp[-1] && v > sp[-tp - 1] && v > sp[tp - 1];
+                        if (rgt) mx = mx && v > sp[1] && v > sp[-tp + 1] && v > sp[tp + 1];
+                        if (mx) {
+                            const int pos = atomicAdd(&s_cnt[k], 1);
+                            bucket[cells[U.cell0 + k].slot_off + pos] =
+                                (uint32_t)(t - shift + U.offx0) | ((uint32_t)(y + U.offy) << 12) | ((uint32_t)v << 24);
                         }
                     }
                 }
-                __syncthreads();
-
-                /* ---- phase B: exact FAST-9 test + score for the survivors */
-                const int nsurv = s_n[chunk & 1];
-                if (tid == 0) s_n[(chunk + 1) & 1] = 0;      /* nobody touches the other counter before the next barrier */
-                for (int j = tid; j < nsurv; j += FAST_THREADS) {
-                    const int idx = list[j];
-                    const uint8_t* p = tile + idx;
-                    const int v = p[0];
-                    /* one IMAD per ring pixel: upper half = (v+th) - r  (negative <=> brighter),
-                     * lower half = r - (v-th) (negative <=> darker); a borrow from the lower half can
-                     * only happen when r < v-th, where the upper half is >= 2*th+1 and stays positive */
-                    const int C = ((v + th) << 16) - (v - th);
-                    uint32_t acc = 0;
-#define FAST_RING(OFF) acc = (acc >> 1) | ((uint32_t)(C - 65535 * (int)p[OFF]) & 0x80008000u)
-                    FAST_RING(3 * tp);      FAST_RING(3 * tp + 1);   FAST_RING(2 * tp + 2);   FAST_RING(tp + 3);
-                    FAST_RING(3);           FAST_RING(-tp + 3);      FAST_RING(-2 * tp + 2);  FAST_RING(-3 * tp + 1);
-                    FAST_RING(-3 * tp);     FAST_RING(-3 * tp - 1);  FAST_RING(-2 * tp - 2);  FAST_RING(-tp - 3);
-                    FAST_RING(-3);          FAST_RING(tp - 3);       FAST_RING(2 * tp - 2);   FAST_RING(3 * tp - 1);
-#undef FAST_RING
-                    const bool bright = has9(acc >> 16), dark = has9(acc & 0xFFFFu);   /* mutually exclusive */
-                    if (bright || dark) {
-                        const int sgn = dark ? -1 : 1;
-                        int e[16];
-                        e[0] = p[3 * tp];          e[1] = p[3 * tp + 1];   e[2] = p[2 * tp + 2];   e[3] = p[tp + 3];
-                        e[4] = p[3];               e[5] = p[-tp + 3];      e[6] = p[-2 * tp + 2];  e[7] = p[-3 * tp + 1];
-                        e[8] = p[-3 * tp];         e[9] = p[-3 * tp - 1];  e[10] = p[-2 * tp - 2]; e[11] = p[-tp - 3];
-                        e[12] = p[-3];             e[13] = p[tp - 3];      e[14] = p[2 * tp - 2];  e[15] = p[3 * tp - 1];
-#pragma unroll
-                        for (int k = 0; k < 16; ++k) e[k] = sgn * (e[k] - v);
-                        score[idx] = (uint8_t)(arc_strength(e) - 1);   /* strength > th >= 1 */
-                    }
-                }
-                __syncthreads();
-                ++chunk;
-            }
-
-            /* ---- phase C: strict 3x3 local maxima inside the pixel's own cell -> cell buckets */
-            const int citems = dh * rw;
-            for (int i = tid; i < citems; i += FAST_THREADS) {
-                const int y = (int)__umulhi((unsigned)i, rcp_rw);
-                const int w = w0 + i - y * rw;
-                uint32_t s4 = score32[(y + 3) * WP + w];
-                if (!s4) continue;
-                const int lo = max(tlo - 4 * w, 0), hi4 = min(thi - 4 * w, 4);
-                for (int bb = lo; bb < hi4; ++bb) {
-                    const int v = (s4 >> (8 * bb)) & 0xFF;
-                    if (!v) continue;
-                    const int t = 4 * w + bb;                       /* tile column */
-                    const int xs = t - shift - 3;                   /* column inside the unit's detection area */
-                    const int k = min((int)__umulhi((unsigned)xs, U.rcp_wc), ncell - 1);
-                    const bool lft = xs != k * wc;                  /* left / right neighbours belong to the same cell */
-                    const bool rgt = (k == ncell - 1) ? (t + 1 < U.tw - 3 + shift) : (xs + 1 != (k + 1) * wc);
-                    const uint8_t* sp = score + (y + 3) * tp + t;
-                    bool mx = v > sp[-tp] && v > sp[tp];
-                    if (lft) mx = mx && v > sp[-1] && v > sp[-tp - 1] && v > sp[tp - 1];
-                    if (rgt) mx = mx && v > sp[1] && v > sp[-tp + 1] && v > sp[tp + 1];
-                    if (mx) {
-                        const int pos = atomicAdd(&s_cnt[k], 1);
-                        bucket[cells[U.cell0 + k].slot_off + pos] =
-                            (uint32_t)(t - shift + U.offx0) | ((uint32_t)(y + 3 + U.offy) << 12) | ((uint32_t)v << 24);
-                    }
-                }
+                ncorn_prev = ncorn;
             }
             __syncthreads();
         }
@@ -1186,11 +1216,12 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
     CK(cudaMalloc(&e->d_tabs, tab_entries * sizeof(short4)));
     CK(cudaMalloc(&e->d_cells, std::max<size_t>(e->cells.size(), 1) * sizeof(Cell)));
     e->nunits = (int)units.size();
-    e->fast_list_cap = 4096;            /* u16 entries; >= FAST_UC * widest cell, so a one-row chunk always fits */
+    e->fast_list_cap = 3072;            /* u16 entries; >= FAST_UC * widest cell, so a one-row chunk always fits */
+    if ((size_t)e->fast_rows * e->fast_tp > 32767) { orbx_set_error("FAST strip %dx%d exceeds the 15-bit tile index", e->fast_tp, e->fast_rows); free_all(e); return ORBX_ERR_INVALID; }
     CK(cudaMalloc(&e->d_units, std::max<size_t>(units.size(), 1) * sizeof(Unit)));
     if (!units.empty()) CK(cudaMemcpy(e->d_units, units.data(), units.size() * sizeof(Unit), cudaMemcpyHostToDevice));
     CK(cudaFuncSetAttribute(k_fast_units, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                            (int)std::max<size_t>((size_t)2 * e->fast_rows * e->fast_tp + 2 * (size_t)e->fast_list_cap, 48 * 1024)));
+                            (int)std::max<size_t>((size_t)2 * e->fast_rows * e->fast_tp + 6 * (size_t)e->fast_list_cap, 48 * 1024)));
     CK(cudaMalloc(&e->d_blur_tiles, blur_tiles.size() * sizeof(int4)));
     CK(cudaMalloc(&e->d_slots, std::max<size_t>(e->slots_per_frame, 1) * B * 4));
     CK(cudaMalloc(&e->d_cell_count, (size_t)std::max(e->ncells, 1) * B * 4));
@@ -1365,7 +1396,7 @@ extern "C" orbx_status orbx_extract_device(orbx_extractor* e, const uint8_t* d_i
     if (e->profiling) ORBX_CUDA(cudaEventRecord(e->ev[1], st));
     /* stage 1 */
     if (e->ncells > 0) {
-        k_fast_units<<<dim3(e->nunits, batch), FAST_THREADS, (size_t)2 * e->fast_rows * e->fast_tp + 2 * (size_t)e->fast_list_cap, st>>>(
+        k_fast_units<<<dim3(e->nunits, batch), FAST_THREADS, (size_t)2 * e->fast_rows * e->fast_tp + 6 * (size_t)e->fast_list_cap, st>>>(
             e->T, static_cast<const Unit*>(e->d_units), e->d_cells, e->ncells, e->P.ini_th_fast, e->P.min_th_fast, e->d_slots,
             e->d_cand, e->slots_per_frame, e->d_cell_count, e->fast_tp, e->fast_rows, e->fast_list_cap);
         ++launches;
