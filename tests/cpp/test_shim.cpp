@@ -1,0 +1,41 @@
+// Drives include/orbx/ORBextractor.h + ORBmatcher.h the way Frame::ExtractORB would
+// (reference src/Frame.cc:178-189): one image in, keypoints + descriptors out.
+// usage: test_shim <raw u8 image file> <w> <h> <nfeatures> <out file>
+#include <cstdio>
+#include <cstdlib>
+#include <vector>
+#include "../../include/orbx/ORBextractor.h"
+#include "../../include/orbx/ORBmatcher.h"
+
+int main(int argc, char** argv) {
+    if (argc < 6) return 2;
+    const int w = atoi(argv[2]), h = atoi(argv[3]), nf = atoi(argv[4]);
+    std::vector<uint8_t> img((size_t)w * h);
+    FILE* f = fopen(argv[1], "rb");
+    if (!f || fread(img.data(), 1, img.size(), f) != img.size()) return 3;
+    fclose(f);
+    try {
+        ORB_SLAM3::ORBextractor ex(nf, 1.2f, 8, 20, 7);
+        std::vector<float> sf = ex.GetScaleFactors();          // before the first image, like Frame's ctor
+        std::vector<orbx_keypoint> kps;
+        std::vector<uint8_t> desc;
+        std::vector<int> lap = {0, 0};
+        const int mono = ex(ORB_SLAM3::ImageView{img.data(), w, h, (size_t)w}, ORB_SLAM3::ImageView{}, kps, desc, lap);
+        const auto& L1 = ex.ImagePyramid(1);
+        const int d01 = kps.size() > 1 ? ORB_SLAM3::ORBmatcher::DescriptorDistance(&desc[0], &desc[32]) : -1;
+        FILE* o = fopen(argv[5], "wb");
+        int hdr[6] = {(int)kps.size(), mono, L1.w, L1.h, d01, (int)sf.size()};
+        fwrite(hdr, sizeof(int), 6, o);
+        fwrite(kps.data(), sizeof(orbx_keypoint), kps.size(), o);
+        fwrite(desc.data(), 1, desc.size(), o);
+        fwrite(L1.bordered.data(), 1, L1.bordered.size(), o);
+        fclose(o);
+        ORB_SLAM3::ImageView none;
+        if (ex(none, none, kps, desc, lap) != -1) return 4;    // empty image -> -1
+    } catch (const std::exception& e) {
+        fprintf(stderr, "%s\n", e.what());
+        return 1;
+    }
+    printf("OK\n");
+    return 0;
+}

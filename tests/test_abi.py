@@ -52,3 +52,23 @@ def test_stdsort_emulation_matches_libstdcxx(tmp_path):
     subprocess.check_call(["g++", "-O2", "-std=c++17", "-o", exe, os.path.join(ROOT, "tests", "cpp", "test_stdsort.cpp")])
     out = subprocess.run([exe], capture_output=True, text=True)
     assert out.returncode == 0 and out.stdout.startswith("OK"), out.stdout
+
+
+def build_shim_test(so, out_dir):
+    """Compiles tests/cpp/test_shim.cpp (C++ drop-in headers include/orbx/*.h) against liborbx.so."""
+    exe = os.path.join(str(out_dir), "test_shim")
+    subprocess.check_call(["g++", "-std=c++17", "-O1", "-Wall", "-Werror", "-o", exe,
+                           os.path.join(ROOT, "tests", "cpp", "test_shim.cpp"), "-L" + os.path.dirname(so), "-lorbx",
+                           "-Wl,-rpath," + os.path.dirname(so)])
+    return exe
+
+
+def test_cpp_shim_compiles_and_fails_loudly_without_gpu(so, tmp_path):
+    exe = build_shim_test(so, tmp_path)
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    img = tmp_path / "img.raw"
+    img.write_bytes(bytes(128 * 96))
+    r = subprocess.run([exe, str(img), "128", "96", "100", str(tmp_path / "out.bin")], capture_output=True, text=True)
+    assert r.returncode == 1 and "no CUDA device" in r.stderr      # the shim throws; no CPU path

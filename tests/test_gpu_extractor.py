@@ -2,10 +2,14 @@
 synthetic frames.  Pyramid, FAST candidates, keypoint coordinates/octaves/responses and
 order: bit-exact.  Orientation: <= 1e-4 rad.  Descriptors: bit-exact except a documented
 cos/sin ULP allowance (<= 0.1% of descriptors, <= 2 bits each) -- BASELINE.json north_star."""
+import os
+import sys
+
 import numpy as np
 import pytest
 
 pytestmark = pytest.mark.gpu
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
 
 CONFIGS = [
     # (w, h, nfeatures, nlevels, seed)
@@ -114,3 +118,25 @@ def test_hamming_pairs(pkg, oracle):
     got = pkg.orbx.hamming_pairs(a, b)
     assert np.array_equal(got, oracle.hamming_pairs(a, b))
     assert got[:10].max() == 0 and got[10] == 256
+
+
+def test_cpp_shim_matches_oracle(pkg, oracle, synth, tmp_path):
+    """include/orbx/ORBextractor.h (C++ drop-in) -> same keypoints/descriptors/pyramid as the oracle."""
+    from test_abi import build_shim_test
+    exe = build_shim_test(pkg.orbx.build(), tmp_path)
+    import subprocess
+    w, h, nf = 640, 400, 700
+    img = synth.textured_image(w, h, 5)
+    (tmp_path / "img.raw").write_bytes(img.tobytes())
+    out = tmp_path / "out.bin"
+    r = subprocess.run([exe, str(tmp_path / "img.raw"), str(w), str(h), str(nf), str(out)], capture_output=True, text=True)
+    assert r.returncode == 0 and r.stdout.startswith("OK"), r.stderr
+    raw = out.read_bytes()
+    n, mono, l1w, l1h, d01, nsf = np.frombuffer(raw[:24], np.int32)
+    kps = np.frombuffer(raw[24:24 + 28 * n], pkg.orbx.KP_DTYPE)
+    desc = np.frombuffer(raw[24 + 28 * n:24 + 60 * n], np.uint8).reshape(n, 32)
+    lvl1 = np.frombuffer(raw[24 + 60 * n:], np.uint8).reshape(l1h + 38, l1w + 38)
+    oex = oracle.Extractor(nf, 1.2, 8, 20, 7)
+    _compare_frame(None, oex, img, (0, 0), got=(kps, desc, int(mono)))
+    assert np.array_equal(lvl1, oex.level(1)) and nsf == 8
+    assert d01 == oracle.descriptor_distance(desc[0], desc[1])
