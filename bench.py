@@ -113,6 +113,76 @@ def cpu_baseline(nthreads, seconds_target=12.0):
             "single_thread_fps": 1.0 / per_frame}
 
 
+def matching_bench(pkg, torch, local, ex, B):
+    """Secondary numbers of BASELINE.json's metric ("Hamming matches/sec"): device-timed stereo
+    row search on the extractor's resident output, batched projection search through the C ABI
+    (host buffers, copies included), and brute-force 2-NN descriptor pairs/s (both kernel variants)."""
+    ox = pkg.orbx
+    out = {}
+    dev = torch.device("cuda", local)
+    # ---- Frame::ComputeStereoMatches: frames (2p, 2p+1) of the last batch as L/R pairs
+    st = torch.cuda.ExternalStream(ex.stream(), device=dev)
+    lf = np.arange(0, B, 2); rf = lf + 1
+    for _ in range(2):
+        ox.stereo_matches_async(ex, ex, lf, rf, 435.2 * 0.11, 0.11)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reps = 10
+    e0.record(st)
+    for _ in range(reps):
+        ox.stereo_matches_async(ex, ex, lf, rf, 435.2 * 0.11, 0.11)
+    e1.record(st)
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    ur, _ = ox.stereo_fetch(ex, len(lf))
+    out["stereo"] = {"pairs_per_s": len(lf) / (ms * 1e-3), "ms_per_launch": ms, "pairs_per_launch": int(len(lf)),
+                     "matched_per_pair": float((ur >= 0).sum() / len(lf)),
+                     "note": "consecutive synthetic frames paired as L/R (not a rectified pair): times the row search + SAD, match count is incidental"}
+    # ---- SearchByProjection, 64 problems per call, 1000 keypoints x 1500 map points, th = 3
+    m = ox.ORBmatcher(local)
+    Fs = [pkg.synth.frame_view(1000, seed=100 + i) for i in range(8)]
+    MPs = [pkg.synth.projection_problem(F, 1500, seed=200 + i) for i, F in enumerate(Fs)]
+    Fs, MPs = Fs * 8, MPs * 8
+    m.SearchByProjection(Fs, MPs, 3.0, False, 0.0, 0.8)
+    t0 = time.perf_counter()
+    reps = 5
+    for _ in range(reps):
+        nm, _ = m.SearchByProjection(Fs, MPs, 3.0, False, 0.0, 0.8)
+    dt = (time.perf_counter() - t0) / reps
+    out["search_by_projection"] = {"problems_per_s": len(Fs) / dt, "matches_per_s": float(nm.sum()) / dt,
+                                   "ms_per_call": dt * 1e3, "problems_per_call": len(Fs),
+                                   "note": "through the C ABI with host buffers (packing + H2D + kernel + D2H)"}
+    # ---- brute-force 2-NN: 16384 queries x 1M database rows, device resident
+    nq, ndb = 16384, 1 << 20
+    g = torch.Generator(device=dev); g.manual_seed(5)
+    q = torch.randint(0, 256, (nq, 32), dtype=torch.uint8, device=dev, generator=g)
+    db = torch.randint(0, 256, (ndb, 32), dtype=torch.uint8, device=dev, generator=g)
+    keys = torch.empty((nq, 2), dtype=torch.int64, device=dev)
+    ms_ = torch.cuda.ExternalStream(m.stream(), device=dev)
+    torch.cuda.synchronize()
+    knn = {}
+    for variant in (0, 1):
+        m.set_knn_variant(variant)
+        m.knn2_device(q.data_ptr(), nq, db.data_ptr(), ndb, 0, keys.data_ptr())
+        m.synchronize()
+        e0.record(ms_)
+        for _ in range(3):
+            m.knn2_device(q.data_ptr(), nq, db.data_ptr(), ndb, 0, keys.data_ptr())
+        e1.record(ms_)
+        m.synchronize()
+        t = e0.elapsed_time(e1) / 3
+        knn["popc8" if variant == 0 else "csa_popc4"] = {"pairs_per_s": nq * ndb / (t * 1e-3), "ms": t}
+    m.set_knn_variant(1)
+    best = max(v["pairs_per_s"] for v in knn.values())
+    # nominal POPC issue rate: 16 lanes/clk/SM (quarter rate) x 148 SMs x max SM clock
+    popc_peak = 16 * 148 * 1.965e9
+    knn.update({"queries": nq, "database_rows": ndb,
+                "popc32_per_s_equiv": best * 8, "frac_of_nominal_popc8_rate": best * 8 / popc_peak,
+                "note": "8 POPC32 per pair is the plain formulation; the carry-save variant issues 4, so its 8-POPC-equivalent rate can exceed the nominal POPC ceiling"})
+    out["knn2"] = knn
+    m.close()
+    return out
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -144,6 +214,7 @@ def main():
     ap.add_argument("--impl", default="orbx")
     ap.add_argument("--batch", type=int, default=BATCH)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-matching", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
     if args.impl == "reference":
@@ -277,6 +348,8 @@ def main():
                          "peak_source": "measured" if peaks else "fallback"},
             "stages": stages,
         }
+        if not args.no_matching:
+            line["matching"] = matching_bench(pkg, torch, local, ex, B)
         if not args.no_cpu_baseline and world == 1:
             line["cpu_baseline"] = cpu_baseline(os.cpu_count() or 1)
         print(json.dumps(line))

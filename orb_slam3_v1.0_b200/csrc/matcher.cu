@@ -760,12 +760,13 @@ __device__ __forceinline__ int knn_dist(const uint32_t (&q)[8], const uint4 a, c
 
 template <int VARIANT>
 __global__ void __launch_bounds__(KNN_THREADS) k_knn2(const uint4* __restrict__ q, int nq, const uint4* __restrict__ db, int ndb,
-                                                       long long index_base, unsigned long long* __restrict__ keys /* [gridDim.y][nq][2] */) {
+                                                       long long index_base, int split_rows,
+                                                       unsigned long long* __restrict__ keys /* [gridDim.y][nq][2] */) {
     __shared__ __align__(128) uint4 s_tile[KNN_STAGES][KNN_TILE * 2];
     __shared__ __align__(8) uint64_t s_full[KNN_STAGES];
     const int tid = threadIdx.x;
-    const int row0 = blockIdx.y * KNN_SPLIT_ROWS;
-    const int nrows = min(ndb - row0, KNN_SPLIT_ROWS);
+    const int row0 = blockIdx.y * split_rows;
+    const int nrows = min(ndb - row0, split_rows);
     const int ntiles = (nrows + KNN_TILE - 1) / KNN_TILE;
     const uint4* dbs = db + 2 * (size_t)row0;
 
@@ -865,7 +866,15 @@ __global__ void __launch_bounds__(256) k_knn2_merge(const unsigned long long* __
     }
 }
 
-static int knn_splits(int ndb) { return std::max(1, (int)(((long long)ndb + KNN_SPLIT_ROWS - 1) / KNN_SPLIT_ROWS)); }
+/* rows per grid.y slice: at most KNN_SPLIT_ROWS (22-bit row field), and small enough that a
+ * search with few queries still puts >= ~3 CTAs on each of the 148 SMs; multiple of the tile */
+static int knn_split_rows(int nq, int ndb) {
+    const long long gx = (nq + KNN_THREADS * KNN_QPT - 1) / (KNN_THREADS * KNN_QPT);
+    const long long want = std::max<long long>(1, (3 * 148 + gx - 1) / gx);
+    long long rows = ((long long)ndb + want - 1) / want;
+    rows = std::max<long long>((rows + KNN_TILE - 1) / KNN_TILE * KNN_TILE, 16 * KNN_TILE);
+    return (int)std::min<long long>(rows, KNN_SPLIT_ROWS);
+}
 
 extern "C" orbx_status orbx_knn2_device(orbx_matcher* m, const void* d_q, int nq, const void* d_db, int ndb,
                                         long long index_base, unsigned long long* d_keys) {
@@ -876,7 +885,8 @@ extern "C" orbx_status orbx_knn2_device(orbx_matcher* m, const void* d_q, int nq
     }
     if (nq == 0) return ORBX_OK;
     ORBX_CUDA(cudaSetDevice(m->device));
-    const int ns = knn_splits(ndb);
+    const int srows = knn_split_rows(nq, ndb);
+    const int ns = std::max(1, (int)(((long long)ndb + srows - 1) / srows));
     unsigned long long* part = d_keys;
     if (ns > 1) {
         orbx_status st = ensure_scratch(m, (size_t)ns * nq * 16);
@@ -885,9 +895,9 @@ extern "C" orbx_status orbx_knn2_device(orbx_matcher* m, const void* d_q, int nq
     }
     const dim3 grid((nq + KNN_THREADS * KNN_QPT - 1) / (KNN_THREADS * KNN_QPT), ns);
     if (m->knn_variant == 0)
-        k_knn2<0><<<grid, KNN_THREADS, 0, m->stream>>>((const uint4*)d_q, nq, (const uint4*)d_db, ndb, index_base, part);
+        k_knn2<0><<<grid, KNN_THREADS, 0, m->stream>>>((const uint4*)d_q, nq, (const uint4*)d_db, ndb, index_base, srows, part);
     else
-        k_knn2<1><<<grid, KNN_THREADS, 0, m->stream>>>((const uint4*)d_q, nq, (const uint4*)d_db, ndb, index_base, part);
+        k_knn2<1><<<grid, KNN_THREADS, 0, m->stream>>>((const uint4*)d_q, nq, (const uint4*)d_db, ndb, index_base, srows, part);
     m->last_launches = 1;
     if (ns > 1) {
         k_knn2_merge<<<std::min((nq + 255) / 256, 148 * 8), 256, 0, m->stream>>>(part, ns, nq, 0.f, nullptr, nullptr, nullptr, nullptr,
