@@ -42,23 +42,35 @@ extern "C" int orbx_version(void) { return 100; }
 
 /* ================================================================== stage 0: pyramid */
 /* level 0 = copyMakeBorder(image, 19, BORDER_REFLECT_101).
- * One thread per 16 output bytes of the padded row. */
+ * One thread per 16 output bytes of the padded row.  Work items are ordered so that warps are
+ * homogeneous: first every (row, interior chunk) -- a plain 128-bit copy -- then every
+ * (row, border chunk), whose 16 bytes are gathered one by one through the reflection. */
+struct L0Split { int c_lo, ni, nb; int bc[6]; unsigned rcp_ni, rcp_nb; };
+
 __global__ void __launch_bounds__(256) k_level0(const uint8_t* __restrict__ src, size_t frame_stride,
-                                                int row_stride, LevelDev L, unsigned rcp_chunks, int vec_ok) {
-    /* grid: x over (row, 16-byte chunk) of one padded frame, y = frame; the division by the chunk
-     * count is one __umulhi (exact: items < 2^20, chunks < 2^9) */
-    const int chunks = L.pitch / 16;
+                                                int row_stride, LevelDev L, L0Split S, int vec_ok) {
     const unsigned i = blockIdx.x * 256u + threadIdx.x;
-    const int r = (int)__umulhi(i, rcp_chunks);
-    if (r >= L.rows) return;
-    const int c = (int)i - r * chunks;
+    const unsigned n_int = (unsigned)L.rows * S.ni;
     const int f = blockIdx.y;
+    int r, c;
+    bool interior;
+    if (i < n_int) {
+        r = (int)__umulhi(i, S.rcp_ni);
+        c = S.c_lo + (int)i - r * S.ni;
+        interior = true;
+    } else {
+        const unsigned j = i - n_int;
+        r = (int)__umulhi(j, S.rcp_nb);
+        if (r >= L.rows) return;
+        c = S.bc[(int)j - r * S.nb];
+        interior = false;
+    }
     const int x0 = c * 16 - ORBX_XOFF;
-    if (x0 + 16 <= -ORBX_EDGE || x0 >= L.w + ORBX_EDGE) return;
-    const int sy = reflect101(r - ORBX_EDGE, L.h);
+    int sy = r - ORBX_EDGE;
+    sy = sy < 0 ? -sy : (sy >= L.h ? 2 * (L.h - 1) - sy : sy);
     const uint8_t* srow = src + (size_t)f * frame_stride + (size_t)sy * row_stride;
     uint8_t* drow = L.base + (size_t)f * L.frame_bytes + (size_t)r * L.pitch + c * 16;
-    if (vec_ok && x0 >= 0 && x0 + 16 <= L.w) {
+    if (interior && vec_ok) {
         *reinterpret_cast<uint4*>(drow) = __ldg(reinterpret_cast<const uint4*>(srow + x0));
     } else {
         uint32_t wv[4] = {0, 0, 0, 0};
@@ -66,7 +78,7 @@ __global__ void __launch_bounds__(256) k_level0(const uint8_t* __restrict__ src,
         for (int k = 0; k < 16; ++k) {
             const int x = x0 + k;
             uint32_t v = 0;
-            if (x >= -ORBX_EDGE && x < L.w + ORBX_EDGE) v = __ldg(srow + reflect101(x, L.w));
+            if (x >= -ORBX_EDGE && x < L.w + ORBX_EDGE) v = __ldg(srow + (x < 0 ? -x : (x >= L.w ? 2 * (L.w - 1) - x : x)));
             wv[k >> 2] |= v << (8 * (k & 3));
         }
         *reinterpret_cast<uint4*>(drow) = make_uint4(wv[0], wv[1], wv[2], wv[3]);
@@ -129,6 +141,7 @@ __global__ void __launch_bounds__(256) k_resize_w4(LevelDev S, LevelDev D, const
     const int f = blockIdx.y;
     const uint32_t meta = __ldg(xmeta + c);
     if (meta == 0xFFFFFFFFu) return;
+    const uint32_t selw = __ldg(D.xsel + c);
     const uint4 cf = __ldg(xcoef + c);
     const short4 yt = __ldg(ypad + r);                 /* {sy, b0, b1} for the padded row r */
     const uint32_t base = meta & 0xFFFFu;
@@ -140,16 +153,16 @@ __global__ void __launch_bounds__(256) k_resize_w4(LevelDev S, LevelDev D, const
     const uint32_t b0 = __ldg(row1), b1 = __ldg(row1 + 1), b2 = __ldg(row1 + 2);
     const uint32_t U0 = __funnelshift_r(a0, a1, sh), V0 = __funnelshift_r(a1, a2, sh);
     const uint32_t U1 = __funnelshift_r(b0, b1, sh), V1 = __funnelshift_r(b1, b2, sh);
-    const int wy0 = yt.y, wy1 = yt.z;
+    /* (b * (H >> 4)) >> 16 as one IMAD.HI: b is pre-shifted by 16 */
+    const uint32_t wy0 = (uint32_t)yt.y << 16, wy1 = (uint32_t)yt.z << 16;
     const uint32_t cfs[4] = {cf.x, cf.y, cf.z, cf.w};
     uint32_t out = 0;
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-        const uint32_t off = (meta >> (16 + 4 * k)) & 7u;
-        const uint32_t sel = off * 0x11u + 0x10u;       /* bytes off, off+1 -> lanes 0,1 */
-        const int r0 = (int)__dp2a_lo(cfs[k], __byte_perm(U0, V0, sel), 0u);
-        const int r1 = (int)__dp2a_lo(cfs[k], __byte_perm(U1, V1, sel), 0u);
-        out |= (uint32_t)((((wy0 * (r0 >> 4)) >> 16) + ((wy1 * (r1 >> 4)) >> 16) + 2) >> 2) << (8 * k);
+        const uint32_t sel = selw >> (8 * k);            /* PRMT reads the low 2 selector nibbles we need */
+        const uint32_t r0 = __dp2a_lo(cfs[k], __byte_perm(U0, V0, sel), 0u);
+        const uint32_t r1 = __dp2a_lo(cfs[k], __byte_perm(U1, V1, sel), 0u);
+        out |= ((__umulhi(wy0, r0 >> 4) + __umulhi(wy1, r1 >> 4) + 2u) >> 2) << (8 * k);
     }
     *reinterpret_cast<uint32_t*>(D.base + (size_t)f * D.frame_bytes + (size_t)r * D.pitch + c * 4) = out;
 }
@@ -875,13 +888,24 @@ __global__ void __launch_bounds__(128) k_blur7(Tables T, const int4* __restrict_
         E[j] = w & 0x00FF00FFu;
         O[j] = (w >> 8) & 0x00FF00FFu;
     }
+    /* the 7 rows of the NEXT block are requested before the current block is computed, so the
+     * global-load latency hides behind ~400 instructions instead of stalling every row */
+    uint32_t nx[7];
+#pragma unroll
+    for (int j = 0; j < 7; ++j) nx[j] = (j < nrows) ? __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)(6 + j) * pitch)) : 0u;
     for (int r = 0; r < nrows; r += 7) {
+        uint32_t cu[7];
+#pragma unroll
+        for (int j = 0; j < 7; ++j) {
+            cu[j] = nx[j];
+            if (r + 7 + j < nrows) nx[j] = __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)(13 + r + j) * pitch));
+        }
 #pragma unroll
         for (int j = 0; j < 7; ++j) {
             const int rr = r + j;
             if (rr < nrows) {
                 const int s = (6 + j) % 7;
-                const uint32_t w = __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)(6 + rr) * pitch));
+                const uint32_t w = cu[j];
                 E[s] = w & 0x00FF00FFu;
                 O[s] = (w >> 8) & 0x00FF00FFu;
                 /* window rows oldest..newest = slots (s+1)%7 .. s */
@@ -891,13 +915,22 @@ __global__ void __launch_bounds__(128) k_blur7(Tables T, const int4* __restrict_
                                     48u * (O[(s + 3) % 7] + O[(s + 5) % 7]) + 56u * O[(s + 4) % 7];
                 const uint32_t LE = __shfl_up_sync(0xffffffffu, VE, 1), LO = __shfl_up_sync(0xffffffffu, VO, 1);
                 const uint32_t RE = __shfl_down_sync(0xffffffffu, VE, 1), RO = __shfl_down_sync(0xffffffffu, VO, 1);
-                const uint32_t c0 = VE & 0xFFFFu, c2 = VE >> 16, c1 = VO & 0xFFFFu, c3 = VO >> 16;
-                const uint32_t l1 = LO & 0xFFFFu, l2 = LE >> 16, l3 = LO >> 16;
-                const uint32_t r0 = RE & 0xFFFFu, r1 = RO & 0xFFFFu, r2 = RE >> 16;
-                const uint32_t o0 = (18u * (l1 + c3) + 34u * (l2 + c2) + 48u * (l3 + c1) + 56u * c0 + 32768u) >> 16;
-                const uint32_t o1 = (18u * (l2 + r0) + 34u * (l3 + c3) + 48u * (c0 + c2) + 56u * c1 + 32768u) >> 16;
-                const uint32_t o2 = (18u * (l3 + r1) + 34u * (c0 + r0) + 48u * (c1 + c3) + 56u * c2 + 32768u) >> 16;
-                const uint32_t o3 = (18u * (c0 + r2) + 34u * (c1 + r1) + 48u * (c2 + r0) + 56u * c3 + 32768u) >> 16;
+                /* horizontal taps as 2-way dot products of the packed u16 column sums (IDP.2A):
+                 * VE = c0|c2, VO = c1|c3 of this word, L* / R* the neighbour words' (c-4|c-2, c-3|c-1, c4|c6, c5|c7);
+                 * the byte pair of each constant holds the taps that hit the (low, high) half */
+#define T2(lo, hi) ((uint32_t)(lo) | ((uint32_t)(hi) << 8))
+                uint32_t o0 = __dp2a_lo(LO, T2(18, 48), 32768u);
+                o0 = __dp2a_lo(LE, T2(0, 34), o0); o0 = __dp2a_lo(VE, T2(56, 34), o0); o0 = __dp2a_lo(VO, T2(48, 18), o0);
+                uint32_t o1 = __dp2a_lo(LE, T2(0, 18), 32768u);
+                o1 = __dp2a_lo(LO, T2(0, 34), o1); o1 = __dp2a_lo(VE, T2(48, 48), o1); o1 = __dp2a_lo(VO, T2(56, 34), o1);
+                o1 = __dp2a_lo(RE, T2(18, 0), o1);
+                uint32_t o2 = __dp2a_lo(LO, T2(0, 18), 32768u);
+                o2 = __dp2a_lo(VE, T2(34, 56), o2); o2 = __dp2a_lo(VO, T2(48, 48), o2); o2 = __dp2a_lo(RE, T2(34, 0), o2);
+                o2 = __dp2a_lo(RO, T2(18, 0), o2);
+                uint32_t o3 = __dp2a_lo(VE, T2(18, 48), 32768u);
+                o3 = __dp2a_lo(VO, T2(34, 56), o3); o3 = __dp2a_lo(RE, T2(48, 18), o3); o3 = __dp2a_lo(RO, T2(34, 0), o3);
+#undef T2
+                o0 >>= 16; o1 >>= 16; o2 >>= 16; o3 >>= 16;
                 if (store)
                     *reinterpret_cast<uint32_t*>(dst + (size_t)rr * bpitch) = o0 | (o1 << 8) | (o2 << 16) | (o3 << 24);
             }
@@ -906,11 +939,14 @@ __global__ void __launch_bounds__(128) k_blur7(Tables T, const int4* __restrict_
 }
 
 /* ================================================================== stage 5: orientation + descriptor */
-__device__ const signed char d_pattern[1024] = {
+/* the same 512 points as floats: the rotation multiplies them, and I2F is a quarter-rate op */
+__device__ __align__(16) const float d_patternf[1024] = {
 #include "../../include/orbx_pattern31.inc"
 };
 
 struct UMax { int v[16]; };
+
+__device__ __forceinline__ int rint_magic(float x) { return __float_as_int(__fadd_rn(x, 12582912.0f)) - 0x4B400000; }
 
 /* cv::fastAtan2: fp32, no FMA contraction */
 __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
@@ -965,13 +1001,13 @@ __global__ void __launch_bounds__(32 * OD_WARPS) k_orient_describe(Tables T, UMa
     uint32_t* win = s_win[wid];
     const int xa = (x - 18) & ~3;
     {
+        /* stage the blurred window: rows y-18..y+18, 10 aligned words from the column below x-18 */
         const uint8_t* b0 = L.blur + (size_t)f * L.bframe_bytes + (size_t)(y - 18) * L.bpitch + xa;
         const int sub = lane / 10, wc = lane - sub * 10;     /* 3 rows x 10 words per request; lanes 30,31 idle */
-        const int nw = ((x + 18 - xa) >> 2) + 1;             /* words that start inside the window (<= 10) */
 #pragma unroll
         for (int r0 = 0; r0 < OD_WIN + 2; r0 += 3) {
             const int r = r0 + sub;
-            if (sub < 3 && r < OD_WIN && wc < nw)
+            if (sub < 3 && r < OD_WIN)
                 win[r * OD_WP + wc] = __ldg(reinterpret_cast<const uint32_t*>(b0 + (size_t)r * L.bpitch) + wc);
         }
     }
@@ -1008,15 +1044,17 @@ __global__ void __launch_bounds__(32 * OD_WARPS) k_orient_describe(Tables T, UMa
     const float a = (float)cd, b = (float)sd;
     __syncwarp();
     const uint8_t* center = reinterpret_cast<const uint8_t*>(win) + 18 * (OD_WP * 4) + (x - xa);
-    const signed char* pat = d_pattern + 32 * lane;
+    const float4* pat = reinterpret_cast<const float4*>(d_patternf) + 8 * lane;
     int val = 0;
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-        const float px0 = pat[4 * j], py0 = pat[4 * j + 1], px1 = pat[4 * j + 2], py1 = pat[4 * j + 3];
-        const int iy0 = __float2int_rn(__fadd_rn(__fmul_rn(px0, b), __fmul_rn(py0, a)));
-        const int ix0 = __float2int_rn(__fsub_rn(__fmul_rn(px0, a), __fmul_rn(py0, b)));
-        const int iy1 = __float2int_rn(__fadd_rn(__fmul_rn(px1, b), __fmul_rn(py1, a)));
-        const int ix1 = __float2int_rn(__fsub_rn(__fmul_rn(px1, a), __fmul_rn(py1, b)));
+        const float4 pp = __ldg(pat + j);          /* {x0, y0, x1, y1} of test pair 8*lane + j */
+        /* cvRound == round-half-even: adding 1.5*2^23 leaves the rounded integer in the mantissa
+         * (|offset| <= 19), which replaces the quarter-rate F2I by one FADD + IADD */
+        const int iy0 = rint_magic(__fadd_rn(__fmul_rn(pp.x, b), __fmul_rn(pp.y, a)));
+        const int ix0 = rint_magic(__fsub_rn(__fmul_rn(pp.x, a), __fmul_rn(pp.y, b)));
+        const int iy1 = rint_magic(__fadd_rn(__fmul_rn(pp.z, b), __fmul_rn(pp.w, a)));
+        const int ix1 = rint_magic(__fsub_rn(__fmul_rn(pp.z, a), __fmul_rn(pp.w, b)));
         const int t0 = center[iy0 * (OD_WP * 4) + ix0];
         const int t1 = center[iy1 * (OD_WP * 4) + ix1];
         val |= (t0 < t1) << j;
@@ -1275,7 +1313,7 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
         /* word-wise tables over the padded destination row/rows (reflection baked in) */
         {
             size_t wbytes = 0;
-            for (int l = 1; l < nl; ++l) wbytes += orbx_align_up((size_t)(e->lv[l].pitch / 4) * 20 + (size_t)e->lv[l].rows * 8, 16) + 64;
+            for (int l = 1; l < nl; ++l) wbytes += orbx_align_up((size_t)(e->lv[l].pitch / 4) * 24 + (size_t)e->lv[l].rows * 8, 16) + 96;
             std::vector<uint8_t> wt(std::max<size_t>(wbytes, 16), 0);
             CK(cudaMalloc(&e->d_wtabs, wt.size()));
             size_t woff = 0, toff = 0;
@@ -1290,6 +1328,8 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
                 L.xcoef = reinterpret_cast<const uint4*>(e->d_wtabs + woff); woff += (size_t)nw * 16;
                 uint32_t* xm = reinterpret_cast<uint32_t*>(wt.data() + woff);
                 L.xmeta = reinterpret_cast<const uint32_t*>(e->d_wtabs + woff); woff += orbx_align_up((size_t)nw * 4, 16);
+                uint32_t* xs = reinterpret_cast<uint32_t*>(wt.data() + woff);
+                L.xsel = reinterpret_cast<const uint32_t*>(e->d_wtabs + woff); woff += orbx_align_up((size_t)nw * 4, 16);
                 short4* yp = reinterpret_cast<short4*>(wt.data() + woff);
                 L.ypad = reinterpret_cast<const short4*>(e->d_wtabs + woff); woff += orbx_align_up((size_t)L.rows * 8, 16);
                 bool ok = true;
@@ -1307,11 +1347,14 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
                             any = true;
                         } else { sx[k] = -1; cf[k] = 0; }
                     }
-                    if (!any) { xm[c] = 0xFFFFFFFFu; xc[c] = make_uint4(0, 0, 0, 0); continue; }
+                    if (!any) { xm[c] = 0xFFFFFFFFu; xs[c] = 0; xc[c] = make_uint4(0, 0, 0, 0); continue; }
                     if (hi - lo > 6) ok = false;
                     uint32_t m = (uint32_t)(ORBX_XOFF + lo);
                     for (int k = 0; k < 4; ++k) m |= (uint32_t)((sx[k] < 0 ? 0 : sx[k] - lo) & 7) << (16 + 4 * k);
                     xm[c] = m;
+                    uint32_t sw = 0;
+                    for (int k = 0; k < 4; ++k) { const uint32_t off = (uint32_t)((sx[k] < 0 ? 0 : sx[k] - lo) & 7); sw |= (off * 0x11u + 0x10u) << (8 * k); }
+                    xs[c] = sw;
                     xc[c] = make_uint4(cf[0], cf[1], cf[2], cf[3]);
                 }
                 for (int r = 0; r < L.rows; ++r) yp[r] = yt[refl(r - ORBX_EDGE, L.h)];
@@ -1378,9 +1421,18 @@ extern "C" orbx_status orbx_extract_device(orbx_extractor* e, const uint8_t* d_i
     {
         const LevelDev& L0 = e->T.lv[0];
         const int vec_ok = (row_stride % 16 == 0) && (frame_stride % 16 == 0) && (((uintptr_t)d_images) % 16 == 0);
-        const unsigned ch0 = L0.pitch / 16;
-        k_level0<<<dim3(orbx_div_up(L0.rows * ch0, 256), batch), 256, 0, st>>>(d_images, frame_stride, row_stride, L0,
-                                                                               0xFFFFFFFFu / ch0 + 1u, vec_ok);
+        L0Split S;
+        memset(&S, 0, sizeof(S));
+        S.c_lo = ORBX_XOFF / 16; S.ni = L0.w / 16;                 /* chunks fully inside the ROI */
+        for (int c = 0; c < L0.pitch / 16; ++c) {
+            const int x0 = c * 16 - ORBX_XOFF;
+            if (c >= S.c_lo && c < S.c_lo + S.ni) continue;
+            if (x0 + 16 <= -ORBX_EDGE || x0 >= L0.w + ORBX_EDGE) continue;
+            if (S.nb < 6) S.bc[S.nb++] = c;      /* <= 2 left + <= 3 right */
+        }
+        S.rcp_ni = 0xFFFFFFFFu / (unsigned)std::max(S.ni, 1) + 1u;
+        S.rcp_nb = 0xFFFFFFFFu / (unsigned)std::max(S.nb, 1) + 1u;
+        k_level0<<<dim3(orbx_div_up(L0.rows * (S.ni + S.nb), 256), batch), 256, 0, st>>>(d_images, frame_stride, row_stride, L0, S, vec_ok);
         ++launches;
         for (int l = 1; l < nl; ++l) {
             const LevelDev& D = e->T.lv[l];

@@ -18,6 +18,7 @@ struct LevelDev {
     const short4* ytab;     /* resize: per dy {sy, b0, b1, 0} */
     const uint4* xcoef;     /* word-wise resize tables over the padded row (k_resize_w4) */
     const uint32_t* xmeta;
+    const uint32_t* xsel;   /* per word: 4 PRMT selectors (source byte offsets off, off+1 of each pixel) */
     const short4* ypad;     /* per padded row {sy, b0, b1, 0} */
     int fast_resize;
     int cell_begin, cell_end;
