@@ -452,7 +452,7 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_units(Tables T, const Uni
 }
 
 /* ================================================================== stage 2: quadtree */
-#define OCT_THREADS 256
+#define OCT_THREADS 128
 
 /* exclusive scan of a[0..n) in shared memory, in place; returns the total. All threads call. */
 __device__ int block_excl_scan(int* a, int n, int* s_tmp /* [OCT_THREADS/32 + 1] */) {
@@ -482,15 +482,77 @@ __device__ int block_excl_scan(int* a, int n, int* s_tmp /* [OCT_THREADS/32 + 1]
     return carry;
 }
 
-struct OctE { int size, ulx, pos; };
+/* sort element of the final phase: size << 32 | UL.x << 16 | list position.  compareNodes
+ * (reference src/ORBextractor.cc:209-224) orders by (size, UL.x) = the key's upper 48 bits. */
+typedef unsigned long long OctE;
+__device__ __forceinline__ OctE oct_pack(int size, int ulx, int pos) {
+    return ((OctE)(unsigned)size << 32) | ((OctE)(unsigned)ulx << 16) | (OctE)(unsigned)pos;
+}
+__device__ __forceinline__ bool oct_less(OctE a, OctE b) { return (a >> 16) < (b >> 16); }
 struct OctLess {
-    /* compareNodes, reference src/ORBextractor.cc:209-224 */
-    __device__ bool operator()(const OctE& a, const OctE& b) const {
-        if (a.size < b.size) return true;
-        else if (a.size > b.size) return false;
-        else return a.ulx < b.ulx;
-    }
+    __device__ bool operator()(const OctE& a, const OctE& b) const { return oct_less(a, b); }
 };
+
+/* std::sort's __introsort_loop (see stdsort_emul.h) run by ONE WARP: the stack of ranges is
+ * walked as in the scalar emulation, but each __unguarded_partition is evaluated in parallel.
+ * With pivot v at a[first] and the untouched range (first, last):
+ *   L_k = k-th position from the left  with !(a < v)   (where `first` stops)
+ *   R_k = k-th position from the right with !(v < a)   (where `last` stops)
+ * the scalar loop swaps (L_k, R_k) while L_k < R_k -- both scans only ever cross elements no
+ * swap has touched -- and returns min(L_K, R_{K-1}) at the first K with L_K >= R_K (the `first`
+ * scan is stopped at the latest by the element the previous swap put at R_{K-1}). */
+__device__ void oct_introsort_warp(OctE* a, int n, int* Lpos, int* Rasc, int lane) {
+    if (n <= 16) return;
+    int stF[40], stL[40], stD[40];
+    int sp = 1;
+    stF[0] = 0; stL[0] = n; stD[0] = 2 * (31 - __clz(n));
+    const unsigned lt = (1u << lane) - 1u;
+    while (sp > 0) {
+        --sp;
+        int first = stF[sp], last = stL[sp], depth = stD[sp];
+        while (last - first > 16) {
+            if (depth == 0) {
+                if (lane == 0) orbx_stdsort::heap_sort_(a + first, last - first, OctLess());
+                __syncwarp();
+                break;
+            }
+            --depth;
+            if (lane == 0)
+                orbx_stdsort::move_median_to_first_(a, first, first + 1, first + (last - first) / 2, last - 1, OctLess());
+            __syncwarp();
+            const OctE pv = a[first];
+            int totL = 0, totR = 0;
+            for (int base = first + 1; base < last; base += 32) {
+                const int p = base + lane;
+                const bool valid = p < last;
+                const OctE x = valid ? a[p] : 0ull;
+                const bool fl = valid && !oct_less(x, pv), fr = valid && !oct_less(pv, x);
+                const unsigned bl = __ballot_sync(0xffffffffu, fl), br = __ballot_sync(0xffffffffu, fr);
+                if (fl) Lpos[totL + __popc(bl & lt)] = p;
+                if (fr) Rasc[totR + __popc(br & lt)] = p;
+                totL += __popc(bl); totR += __popc(br);
+            }
+            __syncwarp();
+            const int kmax = min(totL, totR);
+            int K = 0;
+            for (int base = 0; base < kmax; base += 32) {
+                const int k = base + lane;
+                const bool ok = k < kmax && Lpos[k] < Rasc[totR - 1 - k];
+                const unsigned b = __ballot_sync(0xffffffffu, ok);
+                K += __popc(b);
+                if (b != 0xffffffffu) break;
+            }
+            int cut = min(K < totL ? Lpos[K] : last, K > 0 ? Rasc[totR - K] : last);
+            for (int k = lane; k < K; k += 32) {
+                const int p = Lpos[k], q = Rasc[totR - 1 - k];
+                const OctE t = a[p]; a[p] = a[q]; a[q] = t;
+            }
+            __syncwarp();
+            stF[sp] = cut; stL[sp] = last; stD[sp] = depth; ++sp;
+            last = cut;
+        }
+    }
+}
 
 struct OctSmem {
     /* carved from dynamic shared memory, capacity MAXN nodes */
@@ -666,7 +728,7 @@ __global__ void __launch_bounds__(OCT_THREADS) k_octree(Tables T, const Cell* __
                             ++k;
                             child_bounds(q, px0, py0, px1, py1, S.x0[nxt][np], S.y0[nxt][np], S.x1[nxt][np], S.y1[nxt][np]);
                             S.cnt[nxt][np] = cc;
-                            if (cc > 1) { S.E[ecur][ek].size = cc; S.E[ecur][ek].ulx = S.x0[nxt][np]; S.E[ecur][ek].pos = np; ++ek; }
+                            if (cc > 1) S.E[ecur][ek++] = oct_pack(cc, S.x0[nxt][np], np);
                             S.ccnt[4 * p + q] = np;          /* child count -> child position */
                         } else {
                             S.ccnt[4 * p + q] = -1;
@@ -694,11 +756,26 @@ __global__ void __launch_bounds__(OCT_THREADS) k_octree(Tables T, const Cell* __
             else if (L + nE * 3 > N) final_phase = true;
         } else {
             /* final phase (reference :365-426): split the largest nodes first until N is reached */
-            if (tid == 0) orbx_stdsort::sort(S.E[ecur], nE, OctLess());
+            /* std::sort = introsort loop (warp 0) + final insertion sort; the insertion sort
+             * is a STABLE sort of whatever the loop left, so it is done as a rank sort */
+            if (tid < 32) oct_introsort_warp(S.E[ecur], nE, S.a, S.b, tid);
             for (int p = tid; p < L; p += OCT_THREADS) S.em[p] = -1;
             __syncthreads();
+            {
+                const OctE* src = S.E[ecur];
+                OctE* dst = S.E[ecur ^ 1];
+                for (int i = tid; i < nE; i += OCT_THREADS) {
+                    const OctE x = src[i];
+                    const OctE ci = (x & ~0xFFFFull) | (OctE)i;
+                    int r = 0;
+                    for (int j = 0; j < nE; ++j) r += ((src[j] & ~0xFFFFull) | (OctE)j) < ci;
+                    dst[r] = x;
+                }
+                ecur ^= 1;
+            }
+            __syncthreads();
             for (int m = tid; m < nE; m += OCT_THREADS) {
-                const int p = S.E[ecur][nE - 1 - m].pos;     /* m-th node to be divided */
+                const int p = (int)(S.E[ecur][nE - 1 - m] & 0xFFFFull);     /* m-th node to be divided */
                 S.em[p] = m;
                 S.ccnt[4 * m] = 0; S.ccnt[4 * m + 1] = 0; S.ccnt[4 * m + 2] = 0; S.ccnt[4 * m + 3] = 0;
             }
@@ -747,7 +824,7 @@ __global__ void __launch_bounds__(OCT_THREADS) k_octree(Tables T, const Cell* __
             const int totE = block_excl_scan(S.c, nE, s_tmp);
             const int enx = ecur ^ 1;
             for (int m = tid; m < Tn; m += OCT_THREADS) {
-                const int p = S.E[ecur][nE - 1 - m].pos;
+                const int p = (int)(S.E[ecur][nE - 1 - m] & 0xFFFFull);
                 int nz = 0;
                 for (int q = 0; q < 4; ++q) nz += S.ccnt[4 * m + q] > 0;
                 const int seg = CT - S.a[m] - nz;
@@ -760,7 +837,7 @@ __global__ void __launch_bounds__(OCT_THREADS) k_octree(Tables T, const Cell* __
                         ++k;
                         child_bounds(q, px0, py0, px1, py1, S.x0[nxt][np], S.y0[nxt][np], S.x1[nxt][np], S.y1[nxt][np]);
                         S.cnt[nxt][np] = cc;
-                        if (cc > 1) { S.E[enx][ek].size = cc; S.E[enx][ek].ulx = S.x0[nxt][np]; S.E[enx][ek].pos = np; ++ek; }
+                        if (cc > 1) S.E[enx][ek++] = oct_pack(cc, S.x0[nxt][np], np);
                         S.ccnt[4 * m + q] = np;
                     } else {
                         S.ccnt[4 * m + q] = -1;

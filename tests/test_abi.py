@@ -72,3 +72,14 @@ def test_cpp_shim_compiles_and_fails_loudly_without_gpu(so, tmp_path):
     img.write_bytes(bytes(128 * 96))
     r = subprocess.run([exe, str(img), "128", "96", "100", str(tmp_path / "out.bin")], capture_output=True, text=True)
     assert r.returncode == 1 and "no CUDA device" in r.stderr      # the shim throws; no CPU path
+
+
+def test_octree_sort_closed_form_matches_std_sort(tmp_path):
+    """extractor.cu evaluates std::sort's Hoare partition in closed form per warp and replaces the
+    final insertion sort by a stable rank sort; the same formulation must equal libstdc++'s
+    std::sort on tie-heavy (size, UL.x) keys (reference src/ORBextractor.cc:209-224, :373)."""
+    exe = str(tmp_path / "tpp")
+    subprocess.check_call(["g++", "-std=c++17", "-O2", "-w", "-o", exe,
+                           os.path.join(ROOT, "tests", "cpp", "test_parallel_partition.cpp")])
+    r = subprocess.run([exe, "20000"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and r.stdout.startswith("OK"), r.stdout + r.stderr
