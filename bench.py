@@ -331,6 +331,14 @@ def main():
             stages[n] = {"ms": round(float(stage[i]), 4), "alg_bytes_per_frame": alg[n], "gbs": round(gbs, 1),
                          "frac_hbm": round(gbs / hbm_peak, 4)}
         dom_gbs = stages[names[dom]]["gbs"]
+        kern = {"pyramid": "k_resize_w4", "fast": "k_fast_units", "octree": "k_octree", "order": "k_order",
+                "blur": "k_blur7", "describe": "k_orient_describe"}[names[dom]]
+        traffic = None          # DRAM bytes per launch of the dominant kernel, from the committed ncu --set full capture
+        try:
+            tr = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))["kernels"][kern]
+            traffic = int(tr["dram_bytes"] / tr["launches"] * B / 256)
+        except Exception:
+            pass
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -343,8 +351,9 @@ def main():
                     "device_ms_per_step": e2e_ms / args.steps},
             "gpu_launches": int(launches),
             "clocks": clocks,
-            "roofline": {"bound": "hbm", "kernel": names[dom], "achieved": dom_gbs, "peak": hbm_peak, "unit": "GB/s",
-                         "frac": round(dom_gbs / hbm_peak, 4), "traffic": None,
+            "roofline": {"bound": "hbm", "kernel": kern, "stage": names[dom], "achieved": dom_gbs, "peak": hbm_peak, "unit": "GB/s",
+                         "frac": round(dom_gbs / hbm_peak, 4), "traffic": traffic,
+                         "algorithmic_bytes_per_launch": int(alg[names[dom]] * B), "launch_ms": round(float(stage[dom]), 4),
                          "peak_source": "measured" if peaks else "fallback"},
             "stages": stages,
         }
