@@ -1066,7 +1066,8 @@ __global__ void __launch_bounds__(32 * OD_WARPS) k_orient_describe(Tables T, UMa
     const int f = blockIdx.y;
     if (slot >= (int)sel_per_frame) return;
     int l = 0;
-    while (l + 1 < T.nlevels && slot >= T.lv[l + 1].sel_off) ++l;
+#pragma unroll
+    for (int k = 1; k < ORBX_MAX_LEVELS; ++k) l += (k < T.nlevels && slot >= T.lv[k].sel_off);
     const LevelDev& L = T.lv[l];
     const int i = slot - L.sel_off;
     if (i >= sel_count[f * T.nlevels + l]) return;
@@ -1089,19 +1090,38 @@ __global__ void __launch_bounds__(32 * OD_WARPS) k_orient_describe(Tables T, UMa
         }
     }
 
-    /* IC_Angle (reference src/cuda/Angle_gpu.cu:39-69): m10 = sum u*I, m01 = sum v*I over the disc */
+    /* IC_Angle (reference src/cuda/Angle_gpu.cu:39-69): m10 = sum u*I, m01 = sum v*I over the disc.
+     * 3 patch rows x 9 aligned words per warp request; a word's four columns are masked to the
+     * row's half-width umax[|v|] with byte arithmetic and reduced by two IDP.4A (weights 1 and u). */
     int m10 = 0, m01 = 0;
     {
-        const int u = lane - 15, au = u < 0 ? -u : u;
-        const uint8_t* p = lv_ptr(L, f, x + u, y - 15);
+        const int xs = x - 15, al = xs & 3;                 /* level rows are 64-byte aligned */
+        const int sub = lane / 9, wc = lane - sub * 9;      /* lanes 27..31 idle */
+        const uint8_t* p0 = lv_ptr(L, f, xs - al, y - 15) + 4 * wc;
         const int pitch = L.pitch;
+        const int ub = 4 * wc - al - 15;                    /* column offset u of the word's byte 0: -18..17 */
+        uint32_t u4 = 0, au4 = 0;                           /* per byte: u (s8) and |u| (>= 16 outside the patch) */
 #pragma unroll
-        for (int v = -15; v <= 15; ++v) {
-            const int d = um.v[v < 0 ? -v : v];
-            if (lane < 31 && au <= d) {
-                const int val = __ldg(p + (size_t)(v + 15) * pitch);
-                m10 += u * val;
-                m01 += v * val;
+        for (int k = 0; k < 4; ++k) {
+            const int u = ub + k;
+            u4 |= (uint32_t)(u & 0xFF) << (8 * k);
+            au4 |= (uint32_t)(u < 0 ? -u : u) << (8 * k);
+        }
+#pragma unroll
+        for (int r0 = 0; r0 < 33; r0 += 3) {
+            const int r = r0 + sub;
+            if (sub < 3 && r < 31) {
+                const int d0 = um.v[r0 < 15 ? 15 - r0 : r0 - 15];
+                const int d1 = um.v[r0 + 1 < 15 ? 14 - r0 : r0 - 14];
+                const int d2 = r0 + 2 < 31 ? um.v[r0 + 2 < 15 ? 13 - r0 : r0 - 13] : 0;
+                const int d = sub == 0 ? d0 : (sub == 1 ? d1 : d2);
+                const uint32_t w = __ldg(reinterpret_cast<const uint32_t*>(p0 + (size_t)r * pitch));
+                /* byte k kept iff |u_k| <= d: (0x80 + d - |u_k|) has bit 7 set, no borrow between bytes */
+                const uint32_t t = ((uint32_t)d * 0x01010101u + 0x80808080u - au4) & 0x80808080u;
+                const uint32_t wm = w & ((t >> 7) * 0xFFu);
+                const int rowsum = (int)__dp4a(wm, 0x01010101u, 0u);
+                asm("dp4a.u32.s32 %0, %1, %2, %0;" : "+r"(m10) : "r"(wm), "r"(u4));
+                m01 += (r - 15) * rowsum;
             }
         }
     }
