@@ -1017,7 +1017,7 @@ __global__ void __launch_bounds__(128) k_blur7(Tables T, const int4* __restrict_
 
 /* ================================================================== stage 5: orientation + descriptor */
 /* the same 512 points as floats: the rotation multiplies them, and I2F is a quarter-rate op */
-__device__ __align__(16) const float d_patternf[1024] = {
+static const float h_patternf[1024] = {
 #include "../../include/orbx_pattern31.inc"
 };
 
@@ -1047,124 +1047,195 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
     return a;
 }
 
-/* One warp per keypoint.
- *  IC_Angle: lane = patch column u = lane-15; the warp walks the 31 patch rows, so every load is
- *  one contiguous 31-byte row segment (1-2 L1 wavefronts) instead of 31 scattered bytes.
- *  rBRIEF: the 37x37 blurred window (max rotated pattern radius 18.4 -> +-18) is staged in
- *  shared memory with aligned word loads (3 rows x 10 words per warp request), then lane = descriptor
- *  byte gathers its 16 samples from shared memory. */
+/* One warp per run of OD_KPW consecutive keypoint slots, software-pipelined: while keypoint k is
+ * computed, the 37x37 blurred window (max rotated pattern radius 18.4 -> +-18) and the 31x31
+ * level patch of keypoint k+1 stream into the warp's other shared-memory buffer with cp.async
+ * (8- and 16-byte aligned chunks, 48-byte row pitch), so no register waits on a global load.
+ *  IC_Angle: 3 patch rows x 9 words per step; a word's four columns are masked to the row's
+ *  half-width umax[|v|] with byte arithmetic and reduced by two IDP.4A (weights 1 and u).
+ *  rBRIEF: lane = descriptor byte, gathers its 16 samples from the staged window. */
 #define OD_WARPS 8
+#define OD_KPW 8
 #define OD_WIN 37
-#define OD_WP 12            /* window pitch in words (10 used) */
+#define OD_WP 12            /* window pitch in words: 37 + 7 bytes of 8-byte alignment slack <= 48 */
+#define OD_PP 12            /* patch pitch in words: 31 + 15 bytes of 16-byte alignment slack <= 48 */
+#define OD_BUF (OD_WIN * OD_WP + 31 * OD_PP)
+
+/* test pairs transposed for the warp: d_pattern_t[j * 32 + lane] = pair 8 * lane + j */
+__device__ float4 d_pattern_t[256];
+/* per patch row v = r - 15: umax[|v|] replicated in every byte, + 0x80 per byte */
+__constant__ uint32_t c_d4[32];
+
+__device__ __forceinline__ void cp_async8(uint32_t saddr, const void* g) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(saddr), "l"(g) : "memory");
+}
+__device__ __forceinline__ void cp_async16(uint32_t saddr, const void* g) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(saddr), "l"(g) : "memory");
+}
+
+__device__ __forceinline__ void od_stage(const Tables& T, int f, int l, int x, int y, uint32_t sbuf, int lane) {
+    const LevelDev& L = T.lv[l];
+    {
+        const int xa = (x - 18) & ~7;
+        const int sub = lane / 6, c = lane - sub * 6;        /* 5 rows x 6 chunks of 8 bytes per request; lanes 30,31 idle */
+        const uint8_t* b0 = L.blur + (size_t)f * L.bframe_bytes + (size_t)(y - 18 + sub) * L.bpitch + xa + 8 * c;
+        const uint32_t s0 = sbuf + (uint32_t)(sub * (OD_WP * 4) + 8 * c);
+        const size_t step = 5 * (size_t)L.bpitch;
+        if (sub < 5) {
+#pragma unroll
+            for (int r0 = 0; r0 < OD_WIN; r0 += 5) {
+                if (r0 + 4 < OD_WIN || r0 + sub < OD_WIN) cp_async8(s0 + (uint32_t)(r0 * OD_WP * 4), b0);
+                b0 += step;
+            }
+        }
+    }
+    {
+        const int xs = (x - 15) & ~15;                       /* level rows are 64-byte aligned */
+        const int sub = lane / 3, c = lane - sub * 3;        /* 10 rows x 3 chunks of 16 bytes; lanes 30,31 idle */
+        const uint8_t* p0 = lv_ptr(L, f, xs, y - 15 + sub) + 16 * c;
+        const uint32_t s0 = sbuf + (uint32_t)(OD_WIN * OD_WP * 4 + sub * (OD_PP * 4) + 16 * c);
+        const size_t step = 10 * (size_t)L.pitch;
+        if (sub < 10) {
+#pragma unroll
+            for (int r0 = 0; r0 < 31; r0 += 10) {
+                if (r0 + 9 < 31 || r0 + sub < 31) cp_async16(s0 + (uint32_t)(r0 * OD_PP * 4), p0);
+                p0 += step;
+            }
+        }
+    }
+}
+
 __global__ void __launch_bounds__(32 * OD_WARPS) k_orient_describe(Tables T, UMax um, const uint32_t* __restrict__ sel,
                                                           size_t sel_per_frame, const int* __restrict__ sel_count,
                                                           const int* __restrict__ dest, orbx_keypoint* __restrict__ kps,
                                                           uint8_t* __restrict__ desc, int kcap) {
-    __shared__ uint32_t s_win[OD_WARPS][OD_WIN * OD_WP];
+    extern __shared__ __align__(16) uint32_t s_od[];      /* [OD_WARPS][2][OD_BUF] */
+    __shared__ uint32_t s_d4[32];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const int slot = blockIdx.x * OD_WARPS + wid;
     const int f = blockIdx.y;
-    if (slot >= (int)sel_per_frame) return;
-    int l = 0;
-#pragma unroll
-    for (int k = 1; k < ORBX_MAX_LEVELS; ++k) l += (k < T.nlevels && slot >= T.lv[k].sel_off);
-    const LevelDev& L = T.lv[l];
-    const int i = slot - L.sel_off;
-    if (i >= sel_count[f * T.nlevels + l]) return;
-    const uint32_t e = sel[(size_t)f * sel_per_frame + slot];
-    const int x = (int)(e & 0xFFF) + ORBX_MINB, y = (int)((e >> 12) & 0xFFF) + ORBX_MINB;
-    const int resp = (int)(e >> 24);
+    if (threadIdx.x < 32) s_d4[threadIdx.x] = c_d4[threadIdx.x];
+    __syncthreads();
+    const int slot0 = (blockIdx.x * OD_WARPS + wid) * OD_KPW;
+    if (slot0 >= (int)sel_per_frame) return;
 
-    /* stage the blurred window: rows y-18..y+18, words from the aligned column below x-18 */
-    uint32_t* win = s_win[wid];
-    const int xa = (x - 18) & ~3;
+    /* lane k < OD_KPW fetches slot k's record: all loads independent, one round trip per run */
+    int my_l = 0, my_d = 0;
+    uint32_t my_e = 0;
+    bool my_ok = false;
     {
-        /* stage the blurred window: rows y-18..y+18, 10 aligned words from the column below x-18 */
-        const uint8_t* b0 = L.blur + (size_t)f * L.bframe_bytes + (size_t)(y - 18) * L.bpitch + xa;
-        const int sub = lane / 10, wc = lane - sub * 10;     /* 3 rows x 10 words per request; lanes 30,31 idle */
+        const int slot = slot0 + lane;
+        if (lane < OD_KPW && slot < (int)sel_per_frame) {
 #pragma unroll
-        for (int r0 = 0; r0 < OD_WIN + 2; r0 += 3) {
-            const int r = r0 + sub;
-            if (sub < 3 && r < OD_WIN)
-                win[r * OD_WP + wc] = __ldg(reinterpret_cast<const uint32_t*>(b0 + (size_t)r * L.bpitch) + wc);
+            for (int k = 1; k < ORBX_MAX_LEVELS; ++k) my_l += (k < T.nlevels && slot >= T.lv[k].sel_off);
+            const int cnt = __ldg(sel_count + f * T.nlevels + my_l);
+            my_e = __ldg(sel + (size_t)f * sel_per_frame + slot);
+            my_d = __ldg(dest + (size_t)f * sel_per_frame + slot);
+            my_ok = slot - T.lv[my_l].sel_off < cnt;
         }
     }
+    const unsigned okmask = __ballot_sync(0xffffffffu, my_ok);
+    if (okmask == 0) return;
+    uint32_t* const wbuf = s_od + wid * (2 * OD_BUF);
+    const uint32_t sb0 = (uint32_t)__cvta_generic_to_shared(wbuf);
 
-    /* IC_Angle (reference src/cuda/Angle_gpu.cu:39-69): m10 = sum u*I, m01 = sum v*I over the disc.
-     * 3 patch rows x 9 aligned words per warp request; a word's four columns are masked to the
-     * row's half-width umax[|v|] with byte arithmetic and reduced by two IDP.4A (weights 1 and u). */
-    int m10 = 0, m01 = 0;
+    int k = __ffs(okmask) - 1;
     {
-        const int xs = x - 15, al = xs & 3;                 /* level rows are 64-byte aligned */
-        const int sub = lane / 9, wc = lane - sub * 9;      /* lanes 27..31 idle */
-        const uint8_t* p0 = lv_ptr(L, f, xs - al, y - 15) + 4 * wc;
-        const int pitch = L.pitch;
-        const int ub = 4 * wc - al - 15;                    /* column offset u of the word's byte 0: -18..17 */
-        uint32_t u4 = 0, au4 = 0;                           /* per byte: u (s8) and |u| (>= 16 outside the patch) */
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const int u = ub + k;
-            u4 |= (uint32_t)(u & 0xFF) << (8 * k);
-            au4 |= (uint32_t)(u < 0 ? -u : u) << (8 * k);
+        const uint32_t e = __shfl_sync(0xffffffffu, my_e, k);
+        od_stage(T, f, __shfl_sync(0xffffffffu, my_l, k), (int)(e & 0xFFF) + ORBX_MINB, (int)((e >> 12) & 0xFFF) + ORBX_MINB, sb0, lane);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+    int par = 0;
+    while (k >= 0) {
+        const unsigned rest = okmask & ~((2u << k) - 1u);
+        const int kn = rest ? __ffs(rest) - 1 : -1;
+        if (kn >= 0) {
+            const uint32_t en = __shfl_sync(0xffffffffu, my_e, kn);
+            od_stage(T, f, __shfl_sync(0xffffffffu, my_l, kn), (int)(en & 0xFFF) + ORBX_MINB, (int)((en >> 12) & 0xFFF) + ORBX_MINB,
+                     sb0 + 4u * OD_BUF * (uint32_t)(par ^ 1), lane);
         }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        asm volatile("cp.async.wait_group 1;" ::: "memory");
+        __syncwarp();
+
+        const uint32_t e = __shfl_sync(0xffffffffu, my_e, k);
+        const int l = __shfl_sync(0xffffffffu, my_l, k);
+        const int d = __shfl_sync(0xffffffffu, my_d, k);
+        const LevelDev& L = T.lv[l];
+        const int x = (int)(e & 0xFFF) + ORBX_MINB, y = (int)((e >> 12) & 0xFFF) + ORBX_MINB;
+        const int resp = (int)(e >> 24);
+        const uint32_t* win = wbuf + par * OD_BUF;
+        const uint32_t* patch = win + OD_WIN * OD_WP;
+
+        /* IC_Angle (reference src/cuda/Angle_gpu.cu:39-69): m10 = sum u*I, m01 = sum v*I over the disc */
+        int m10 = 0, m01 = 0;
+        {
+            const int al = (x - 15) & 3, bw = ((x - 15) & 15) >> 2;   /* byte / word offset of column x-15 in the staged row */
+            const int sub = lane / 9, wc = lane - sub * 9;
+            const int ub = 4 * wc - al - 15;                    /* column offset u of the word's byte 0: -18..17 */
+            uint32_t u4 = 0, au4 = 0;                           /* per byte: u (s8) and |u| (>= 16 outside the patch) */
 #pragma unroll
-        for (int r0 = 0; r0 < 33; r0 += 3) {
-            const int r = r0 + sub;
-            if (sub < 3 && r < 31) {
-                const int d0 = um.v[r0 < 15 ? 15 - r0 : r0 - 15];
-                const int d1 = um.v[r0 + 1 < 15 ? 14 - r0 : r0 - 14];
-                const int d2 = r0 + 2 < 31 ? um.v[r0 + 2 < 15 ? 13 - r0 : r0 - 13] : 0;
-                const int d = sub == 0 ? d0 : (sub == 1 ? d1 : d2);
-                const uint32_t w = __ldg(reinterpret_cast<const uint32_t*>(p0 + (size_t)r * pitch));
-                /* byte k kept iff |u_k| <= d: (0x80 + d - |u_k|) has bit 7 set, no borrow between bytes */
-                const uint32_t t = ((uint32_t)d * 0x01010101u + 0x80808080u - au4) & 0x80808080u;
-                const uint32_t wm = w & ((t >> 7) * 0xFFu);
-                const int rowsum = (int)__dp4a(wm, 0x01010101u, 0u);
-                asm("dp4a.u32.s32 %0, %1, %2, %0;" : "+r"(m10) : "r"(wm), "r"(u4));
-                m01 += (r - 15) * rowsum;
+            for (int q = 0; q < 4; ++q) {
+                const int u = ub + q;
+                u4 |= (uint32_t)(u & 0xFF) << (8 * q);
+                au4 |= (uint32_t)(u < 0 ? -u : u) << (8 * q);
+            }
+            const uint32_t* pw = patch + sub * OD_PP + bw + wc;
+            int rv = sub - 15;
+            if (sub < 3) {
+#pragma unroll
+                for (int r0 = 0; r0 < 33; r0 += 3) {
+                    if (r0 + 2 < 31 || r0 + sub < 31) {
+                        const uint32_t w = pw[r0 * OD_PP];
+                        /* byte q kept iff |u_q| <= umax: (0x80 + umax - |u_q|) has bit 7 set, no borrow between bytes */
+                        const uint32_t t = (s_d4[r0 + sub] - au4) & 0x80808080u;
+                        const uint32_t wm = w & ((t >> 7) * 0xFFu);
+                        const int rowsum = (int)__dp4a(wm, 0x01010101u, 0u);
+                        asm("dp4a.u32.s32 %0, %1, %2, %0;" : "+r"(m10) : "r"(wm), "r"(u4));
+                        m01 += rv * rowsum;
+                    }
+                    rv += 3;
+                }
             }
         }
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        m10 += __shfl_xor_sync(0xffffffffu, m10, o);
-        m01 += __shfl_xor_sync(0xffffffffu, m01, o);
-    }
-    const float angle = fast_atan2_deg((float)m01, (float)m10);
+        m10 = __reduce_add_sync(0xffffffffu, m10);
+        m01 = __reduce_add_sync(0xffffffffu, m01);
+        const float angle = fast_atan2_deg((float)m01, (float)m10);
 
-    /* rBRIEF (reference src/cuda/Orb_gpu.cu:311-350): lane = descriptor byte */
-    constexpr float factorPI = (float)(3.14159265358979323846 / 180.f);
-    const float ar = __fmul_rn(angle, factorPI);
-    /* cosf/sinf of the reference resolve to glibc (<=0.56 ULP); here: fp64 result rounded once */
-    double sd, cd;
-    sincos((double)ar, &sd, &cd);
-    const float a = (float)cd, b = (float)sd;
-    __syncwarp();
-    const uint8_t* center = reinterpret_cast<const uint8_t*>(win) + 18 * (OD_WP * 4) + (x - xa);
-    const float4* pat = reinterpret_cast<const float4*>(d_patternf) + 8 * lane;
-    int val = 0;
+        /* rBRIEF (reference src/cuda/Orb_gpu.cu:311-350): lane = descriptor byte */
+        constexpr float factorPI = (float)(3.14159265358979323846 / 180.f);
+        const float ar = __fmul_rn(angle, factorPI);
+        /* cosf/sinf of the reference resolve to glibc (<=0.56 ULP); here: fp64 result rounded once */
+        double sd, cd;
+        sincos((double)ar, &sd, &cd);
+        const float a = (float)cd, b = (float)sd;
+        const uint8_t* center = reinterpret_cast<const uint8_t*>(win) + 18 * (OD_WP * 4) + (x - ((x - 18) & ~7));
+        const float4* pat = d_pattern_t + lane;
+        int val = 0;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-        const float4 pp = __ldg(pat + j);          /* {x0, y0, x1, y1} of test pair 8*lane + j */
-        /* cvRound == round-half-even: adding 1.5*2^23 leaves the rounded integer in the mantissa
-         * (|offset| <= 19), which replaces the quarter-rate F2I by one FADD + IADD */
-        const int iy0 = rint_magic(__fadd_rn(__fmul_rn(pp.x, b), __fmul_rn(pp.y, a)));
-        const int ix0 = rint_magic(__fsub_rn(__fmul_rn(pp.x, a), __fmul_rn(pp.y, b)));
-        const int iy1 = rint_magic(__fadd_rn(__fmul_rn(pp.z, b), __fmul_rn(pp.w, a)));
-        const int ix1 = rint_magic(__fsub_rn(__fmul_rn(pp.z, a), __fmul_rn(pp.w, b)));
-        const int t0 = center[iy0 * (OD_WP * 4) + ix0];
-        const int t1 = center[iy1 * (OD_WP * 4) + ix1];
-        val |= (t0 < t1) << j;
-    }
-    const int d = dest[(size_t)f * sel_per_frame + slot];
-    desc[((size_t)f * kcap + d) * 32 + lane] = (uint8_t)val;
-    if (lane == 0) {
-        orbx_keypoint k;
-        float fx = (float)x, fy = (float)y;
-        if (l != 0) { fx = __fmul_rn(fx, L.scale); fy = __fmul_rn(fy, L.scale); }
-        k.x = fx; k.y = fy; k.size = L.patch_size; k.angle = angle; k.response = (float)resp;
-        k.octave = l; k.class_id = -1;
-        kps[(size_t)f * kcap + d] = k;
+        for (int j = 0; j < 8; ++j) {
+            const float4 pp = __ldg(pat + 32 * j);     /* {x0, y0, x1, y1} of test pair 8*lane + j */
+            /* cvRound == round-half-even: adding 1.5*2^23 leaves the rounded integer in the mantissa
+             * (|offset| <= 19), which replaces the quarter-rate F2I by one FADD + IADD */
+            const int iy0 = rint_magic(__fadd_rn(__fmul_rn(pp.x, b), __fmul_rn(pp.y, a)));
+            const int ix0 = rint_magic(__fsub_rn(__fmul_rn(pp.x, a), __fmul_rn(pp.y, b)));
+            const int iy1 = rint_magic(__fadd_rn(__fmul_rn(pp.z, b), __fmul_rn(pp.w, a)));
+            const int ix1 = rint_magic(__fsub_rn(__fmul_rn(pp.z, a), __fmul_rn(pp.w, b)));
+            const int t0 = center[iy0 * (OD_WP * 4) + ix0];
+            const int t1 = center[iy1 * (OD_WP * 4) + ix1];
+            val |= (t0 < t1) << j;
+        }
+        desc[((size_t)f * kcap + d) * 32 + lane] = (uint8_t)val;
+        if (lane == 0) {
+            orbx_keypoint kp;
+            float fx = (float)x, fy = (float)y;
+            if (l != 0) { fx = __fmul_rn(fx, L.scale); fy = __fmul_rn(fy, L.scale); }
+            kp.x = fx; kp.y = fy; kp.size = L.patch_size; kp.angle = angle; kp.response = (float)resp;
+            kp.octave = l; kp.class_id = -1;
+            kps[(size_t)f * kcap + d] = kp;
+        }
+        __syncwarp();          /* every lane is done with this buffer before it is refilled */
+        k = kn;
+        par ^= 1;
     }
 }
 
@@ -1344,6 +1415,17 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
     CK(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
     for (int i = 0; i < 7; ++i) CK(cudaEventCreate(&e->ev[i]));
     CK(cudaFuncSetAttribute(k_octree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)e->oct_smem));
+    {
+        /* rBRIEF test pairs, transposed so that a warp's j-th load is one contiguous 512-byte row */
+        std::vector<float> pt(1024);
+        for (int lane = 0; lane < 32; ++lane)
+            for (int j = 0; j < 8; ++j) memcpy(&pt[4 * (j * 32 + lane)], &h_patternf[4 * (8 * lane + j)], 16);
+        CK(cudaMemcpyToSymbol(d_pattern_t, pt.data(), sizeof(float) * 1024));
+        uint32_t d4[32] = {0};
+        for (int r = 0; r < 31; ++r) d4[r] = (uint32_t)e->umax[r < 15 ? 15 - r : r - 15] * 0x01010101u + 0x80808080u;
+        CK(cudaMemcpyToSymbol(c_d4, d4, sizeof(d4)));
+        CK(cudaFuncSetAttribute(k_orient_describe, cudaFuncAttributeMaxDynamicSharedMemorySize, OD_WARPS * 2 * OD_BUF * 4));
+    }
     CK(cudaMalloc(&e->d_pyr, pyr_bytes));
     CK(cudaMalloc(&e->d_blur, blur_bytes + 256));    /* + slack: window staging reads whole words */
     CK(cudaMemsetAsync(e->d_pyr, 0, pyr_bytes, e->stream));
@@ -1571,7 +1653,7 @@ extern "C" orbx_status orbx_extract_device(orbx_extractor* e, const uint8_t* d_i
     {
         UMax um;
         for (int i = 0; i < 16; ++i) um.v[i] = e->umax[i];
-        k_orient_describe<<<dim3(orbx_div_up((int)e->sel_per_frame, OD_WARPS), batch), 32 * OD_WARPS, 0, st>>>(
+        k_orient_describe<<<dim3(orbx_div_up((int)e->sel_per_frame, OD_WARPS * OD_KPW), batch), 32 * OD_WARPS, OD_WARPS * 2 * OD_BUF * 4, st>>>(
             e->T, um, e->d_sel, e->sel_per_frame, e->d_sel_count, e->d_dest, e->d_kps, e->d_desc, e->kcap);
         ++launches;
     }
