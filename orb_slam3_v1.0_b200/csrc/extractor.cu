@@ -16,6 +16,7 @@
  *   4 blur      k_blur7: integer 7x7 sigma-2 Gaussian
  *   5 describe  k_orient_describe: one warp per keypoint, IC angle + rBRIEF
  */
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdarg.h>
@@ -1024,6 +1025,7 @@ static const float h_patternf[1024] = {
 struct UMax { int v[16]; };
 
 __device__ __forceinline__ int rint_magic(float x) { return __float_as_int(__fadd_rn(x, 12582912.0f)) - 0x4B400000; }
+__device__ __forceinline__ uint32_t rint_bits(float x) { return (uint32_t)__float_as_int(__fadd_rn(x, 12582912.0f)); }
 
 /* cv::fastAtan2: fp32, no FMA contraction */
 __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
@@ -1047,73 +1049,71 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
     return a;
 }
 
-/* One warp per run of OD_KPW consecutive keypoint slots, software-pipelined: while keypoint k is
- * computed, the 37x37 blurred window (max rotated pattern radius 18.4 -> +-18) and the 31x31
- * level patch of keypoint k+1 stream into the warp's other shared-memory buffer with cp.async
- * (8- and 16-byte aligned chunks, 48-byte row pitch), so no register waits on a global load.
+/* One warp per run of OD_KPW consecutive keypoint slots, software-pipelined with TMA: the 37-row
+ * blurred window (the rotated pattern reaches radius 18.4 -> +-18) and the 31-row level patch of
+ * a keypoint arrive by one cp.async.bulk.tensor.3d each (tensor maps over (row bytes, rows,
+ * frames), issued by one elected lane, completion on an mbarrier).  The window of keypoint k+1 is
+ * in flight while keypoint k is computed (two window buffers); the single patch buffer is
+ * refilled as soon as IC_Angle has consumed it.  TMA wants the box's first byte 16-byte aligned
+ * (measured: an unaligned inner coordinate faults, tools/scratch/tma_probe.cu), so boxes start at
+ * the aligned column below and are 64 / 48 bytes wide.
  *  IC_Angle: 3 patch rows x 9 words per step; a word's four columns are masked to the row's
  *  half-width umax[|v|] with byte arithmetic and reduced by two IDP.4A (weights 1 and u).
  *  rBRIEF: lane = descriptor byte, gathers its 16 samples from the staged window. */
 #define OD_WARPS 8
 #define OD_KPW 8
 #define OD_WIN 37
-#define OD_WP 12            /* window pitch in words: 37 + 7 bytes of 8-byte alignment slack <= 48 */
-#define OD_PP 12            /* patch pitch in words: 31 + 15 bytes of 16-byte alignment slack <= 48 */
-#define OD_BUF (OD_WIN * OD_WP + 31 * OD_PP)
+#define OD_WPB 64           /* window pitch in bytes: 37 columns + up to 15 bytes of 16-byte alignment */
+#define OD_PPB 48           /* patch pitch in bytes: 31 columns + up to 15 */
+#define OD_WIN_BYTES (OD_WIN * OD_WPB)                    /* 2368 */
+#define OD_WIN_SLOT 2432                                  /* 128-byte aligned */
+#define OD_PATCH_BYTES (31 * OD_PPB)                      /* 1488 */
+#define OD_WARP_BYTES (2 * OD_WIN_SLOT + 1536)            /* two windows + one patch = 6400 */
+#define OD_SMEM (OD_WARPS * OD_WARP_BYTES + 128)
+
+struct ODMaps { CUtensorMap blur[ORBX_MAX_LEVELS]; CUtensorMap pyr[ORBX_MAX_LEVELS]; };
 
 /* test pairs transposed for the warp: d_pattern_t[j * 32 + lane] = pair 8 * lane + j */
 __device__ float4 d_pattern_t[256];
 /* per patch row v = r - 15: umax[|v|] replicated in every byte, + 0x80 per byte */
 __constant__ uint32_t c_d4[32];
 
-__device__ __forceinline__ void cp_async8(uint32_t saddr, const void* g) {
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(saddr), "l"(g) : "memory");
+__device__ __forceinline__ void od_tma3(uint32_t dst, const CUtensorMap* map, int c0, int c1, int c2, uint32_t bar) {
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                 ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(bar) : "memory");
 }
-__device__ __forceinline__ void cp_async16(uint32_t saddr, const void* g) {
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(saddr), "l"(g) : "memory");
+/* TMA needs the box's first byte 16-byte aligned: boxes start at the aligned column below */
+__device__ __forceinline__ void od_issue_win(const ODMaps* M, int f, int l, int x, int y, uint32_t dst, uint32_t bar) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "n"(OD_WIN_BYTES) : "memory");
+    od_tma3(dst, &M->blur[l], (x - 18) & ~15, y - 18, f, bar);
 }
-
-__device__ __forceinline__ void od_stage(const Tables& T, int f, int l, int x, int y, uint32_t sbuf, int lane) {
-    const LevelDev& L = T.lv[l];
-    {
-        const int xa = (x - 18) & ~7;
-        const int sub = lane / 6, c = lane - sub * 6;        /* 5 rows x 6 chunks of 8 bytes per request; lanes 30,31 idle */
-        const uint8_t* b0 = L.blur + (size_t)f * L.bframe_bytes + (size_t)(y - 18 + sub) * L.bpitch + xa + 8 * c;
-        const uint32_t s0 = sbuf + (uint32_t)(sub * (OD_WP * 4) + 8 * c);
-        const size_t step = 5 * (size_t)L.bpitch;
-        if (sub < 5) {
-#pragma unroll
-            for (int r0 = 0; r0 < OD_WIN; r0 += 5) {
-                if (r0 + 4 < OD_WIN || r0 + sub < OD_WIN) cp_async8(s0 + (uint32_t)(r0 * OD_WP * 4), b0);
-                b0 += step;
-            }
-        }
-    }
-    {
-        const int xs = (x - 15) & ~15;                       /* level rows are 64-byte aligned */
-        const int sub = lane / 3, c = lane - sub * 3;        /* 10 rows x 3 chunks of 16 bytes; lanes 30,31 idle */
-        const uint8_t* p0 = lv_ptr(L, f, xs, y - 15 + sub) + 16 * c;
-        const uint32_t s0 = sbuf + (uint32_t)(OD_WIN * OD_WP * 4 + sub * (OD_PP * 4) + 16 * c);
-        const size_t step = 10 * (size_t)L.pitch;
-        if (sub < 10) {
-#pragma unroll
-            for (int r0 = 0; r0 < 31; r0 += 10) {
-                if (r0 + 9 < 31 || r0 + sub < 31) cp_async16(s0 + (uint32_t)(r0 * OD_PP * 4), p0);
-                p0 += step;
-            }
-        }
-    }
+__device__ __forceinline__ void od_issue_patch(const ODMaps* M, int f, int l, int x, int y, uint32_t dst, uint32_t bar) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "n"(OD_PATCH_BYTES) : "memory");
+    od_tma3(dst, &M->pyr[l], ORBX_XOFF + ((x - 15) & ~15), ORBX_EDGE + y - 15, f, bar);
+}
+__device__ __forceinline__ void od_wait(uint32_t bar, uint32_t parity) {
+    uint32_t done;
+    do {
+        asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+                     : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+    } while (!done);
 }
 
-__global__ void __launch_bounds__(32 * OD_WARPS) k_orient_describe(Tables T, UMax um, const uint32_t* __restrict__ sel,
+__global__ void __launch_bounds__(32 * OD_WARPS) k_orient_describe(Tables T, const ODMaps* __restrict__ Mp,
+                                                          const uint32_t* __restrict__ sel,
                                                           size_t sel_per_frame, const int* __restrict__ sel_count,
                                                           const int* __restrict__ dest, orbx_keypoint* __restrict__ kps,
                                                           uint8_t* __restrict__ desc, int kcap) {
-    extern __shared__ __align__(16) uint32_t s_od[];      /* [OD_WARPS][2][OD_BUF] */
+    extern __shared__ __align__(128) uint8_t s_od[];      /* [OD_WARPS][2][OD_BUF_BYTES] */
     __shared__ uint32_t s_d4[32];
+    __shared__ __align__(8) uint64_t s_bar[OD_WARPS][4];      /* window 0, window 1, patch */
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int f = blockIdx.y;
     if (threadIdx.x < 32) s_d4[threadIdx.x] = c_d4[threadIdx.x];
+    if (lane < 3) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"((uint32_t)__cvta_generic_to_shared(&s_bar[wid][lane])) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
     __syncthreads();
     const int slot0 = (blockIdx.x * OD_WARPS + wid) * OD_KPW;
     if (slot0 >= (int)sel_per_frame) return;
@@ -1135,27 +1135,32 @@ __global__ void __launch_bounds__(32 * OD_WARPS) k_orient_describe(Tables T, UMa
     }
     const unsigned okmask = __ballot_sync(0xffffffffu, my_ok);
     if (okmask == 0) return;
-    uint32_t* const wbuf = s_od + wid * (2 * OD_BUF);
-    const uint32_t sb0 = (uint32_t)__cvta_generic_to_shared(wbuf);
+    const uint32_t sb0 = (((uint32_t)__cvta_generic_to_shared(s_od) + 127u) & ~127u) + (uint32_t)wid * OD_WARP_BYTES;
+    const uint32_t spatch = sb0 + 2 * OD_WIN_SLOT;
+    const uint32_t bar0 = (uint32_t)__cvta_generic_to_shared(&s_bar[wid][0]), barp = bar0 + 16u;
 
     int k = __ffs(okmask) - 1;
     {
         const uint32_t e = __shfl_sync(0xffffffffu, my_e, k);
-        od_stage(T, f, __shfl_sync(0xffffffffu, my_l, k), (int)(e & 0xFFF) + ORBX_MINB, (int)((e >> 12) & 0xFFF) + ORBX_MINB, sb0, lane);
-        asm volatile("cp.async.commit_group;" ::: "memory");
+        const int l = __shfl_sync(0xffffffffu, my_l, k);
+        if (lane == 0) {
+            const int x = (int)(e & 0xFFF) + ORBX_MINB, y = (int)((e >> 12) & 0xFFF) + ORBX_MINB;
+            od_issue_patch(Mp, f, l, x, y, spatch, barp);
+            od_issue_win(Mp, f, l, x, y, sb0, bar0);
+        }
     }
     int par = 0;
+    uint32_t phase = 0;                                     /* bit b = parity to wait for on barrier b */
     while (k >= 0) {
         const unsigned rest = okmask & ~((2u << k) - 1u);
         const int kn = rest ? __ffs(rest) - 1 : -1;
+        int xn = 0, yn = 0, ln = 0;
         if (kn >= 0) {
             const uint32_t en = __shfl_sync(0xffffffffu, my_e, kn);
-            od_stage(T, f, __shfl_sync(0xffffffffu, my_l, kn), (int)(en & 0xFFF) + ORBX_MINB, (int)((en >> 12) & 0xFFF) + ORBX_MINB,
-                     sb0 + 4u * OD_BUF * (uint32_t)(par ^ 1), lane);
+            ln = __shfl_sync(0xffffffffu, my_l, kn);
+            xn = (int)(en & 0xFFF) + ORBX_MINB; yn = (int)((en >> 12) & 0xFFF) + ORBX_MINB;
+            if (lane == 0) od_issue_win(Mp, f, ln, xn, yn, sb0 + (uint32_t)(par ^ 1) * OD_WIN_SLOT, bar0 + 8u * (uint32_t)(par ^ 1));
         }
-        asm volatile("cp.async.commit_group;" ::: "memory");
-        asm volatile("cp.async.wait_group 1;" ::: "memory");
-        __syncwarp();
 
         const uint32_t e = __shfl_sync(0xffffffffu, my_e, k);
         const int l = __shfl_sync(0xffffffffu, my_l, k);
@@ -1163,14 +1168,12 @@ __global__ void __launch_bounds__(32 * OD_WARPS) k_orient_describe(Tables T, UMa
         const LevelDev& L = T.lv[l];
         const int x = (int)(e & 0xFFF) + ORBX_MINB, y = (int)((e >> 12) & 0xFFF) + ORBX_MINB;
         const int resp = (int)(e >> 24);
-        const uint32_t* win = wbuf + par * OD_BUF;
-        const uint32_t* patch = win + OD_WIN * OD_WP;
 
         /* IC_Angle (reference src/cuda/Angle_gpu.cu:39-69): m10 = sum u*I, m01 = sum v*I over the disc */
         int m10 = 0, m01 = 0;
         {
-            const int al = (x - 15) & 3, bw = ((x - 15) & 15) >> 2;   /* byte / word offset of column x-15 in the staged row */
-            const int sub = lane / 9, wc = lane - sub * 9;
+            const int al16 = (x - 15) & 15, al = al16 & 3;
+            const int sub = lane / 9, wc = lane - sub * 9;      /* 3 rows x 9 words per step; lanes 27..31 idle */
             const int ub = 4 * wc - al - 15;                    /* column offset u of the word's byte 0: -18..17 */
             uint32_t u4 = 0, au4 = 0;                           /* per byte: u (s8) and |u| (>= 16 outside the patch) */
 #pragma unroll
@@ -1179,13 +1182,16 @@ __global__ void __launch_bounds__(32 * OD_WARPS) k_orient_describe(Tables T, UMa
                 u4 |= (uint32_t)(u & 0xFF) << (8 * q);
                 au4 |= (uint32_t)(u < 0 ? -u : u) << (8 * q);
             }
-            const uint32_t* pw = patch + sub * OD_PP + bw + wc;
+            const uint32_t pa = spatch + (uint32_t)(sub * OD_PPB + (al16 & ~3) + 4 * wc);
             int rv = sub - 15;
+            od_wait(barp, (phase >> 2) & 1u);
+            phase ^= 4u;
             if (sub < 3) {
 #pragma unroll
                 for (int r0 = 0; r0 < 33; r0 += 3) {
                     if (r0 + 2 < 31 || r0 + sub < 31) {
-                        const uint32_t w = pw[r0 * OD_PP];
+                        uint32_t w;
+                        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w) : "r"(pa + (uint32_t)(r0 * OD_PPB)));
                         /* byte q kept iff |u_q| <= umax: (0x80 + umax - |u_q|) has bit 7 set, no borrow between bytes */
                         const uint32_t t = (s_d4[r0 + sub] - au4) & 0x80808080u;
                         const uint32_t wm = w & ((t >> 7) * 0xFFu);
@@ -1197,6 +1203,8 @@ __global__ void __launch_bounds__(32 * OD_WARPS) k_orient_describe(Tables T, UMa
                 }
             }
         }
+        __syncwarp();                                       /* every lane has read the patch: refill it */
+        if (kn >= 0 && lane == 0) od_issue_patch(Mp, f, ln, xn, yn, spatch, barp);
         m10 = __reduce_add_sync(0xffffffffu, m10);
         m01 = __reduce_add_sync(0xffffffffu, m01);
         const float angle = fast_atan2_deg((float)m01, (float)m10);
@@ -1208,20 +1216,24 @@ __global__ void __launch_bounds__(32 * OD_WARPS) k_orient_describe(Tables T, UMa
         double sd, cd;
         sincos((double)ar, &sd, &cd);
         const float a = (float)cd, b = (float)sd;
-        const uint8_t* center = reinterpret_cast<const uint8_t*>(win) + 18 * (OD_WP * 4) + (x - ((x - 18) & ~7));
+        /* cvRound == round-half-even: adding 1.5*2^23 leaves K + n in the float's bit pattern
+         * (K = 0x4B400000, |n| <= 19), which replaces the quarter-rate F2I; the two K's are folded
+         * into the window base address (32-bit shared addresses wrap) */
+        const uint32_t cbase = sb0 + (uint32_t)par * OD_WIN_SLOT + 18u * OD_WPB + 18u + (uint32_t)((x - 18) & 15) - (OD_WPB + 1) * 0x4B400000u;
+        od_wait(bar0 + 8u * (uint32_t)par, (phase >> par) & 1u);
+        phase ^= 1u << par;
         const float4* pat = d_pattern_t + lane;
         int val = 0;
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
             const float4 pp = __ldg(pat + 32 * j);     /* {x0, y0, x1, y1} of test pair 8*lane + j */
-            /* cvRound == round-half-even: adding 1.5*2^23 leaves the rounded integer in the mantissa
-             * (|offset| <= 19), which replaces the quarter-rate F2I by one FADD + IADD */
-            const int iy0 = rint_magic(__fadd_rn(__fmul_rn(pp.x, b), __fmul_rn(pp.y, a)));
-            const int ix0 = rint_magic(__fsub_rn(__fmul_rn(pp.x, a), __fmul_rn(pp.y, b)));
-            const int iy1 = rint_magic(__fadd_rn(__fmul_rn(pp.z, b), __fmul_rn(pp.w, a)));
-            const int ix1 = rint_magic(__fsub_rn(__fmul_rn(pp.z, a), __fmul_rn(pp.w, b)));
-            const int t0 = center[iy0 * (OD_WP * 4) + ix0];
-            const int t1 = center[iy1 * (OD_WP * 4) + ix1];
+            const uint32_t iy0 = rint_bits(__fadd_rn(__fmul_rn(pp.x, b), __fmul_rn(pp.y, a)));
+            const uint32_t ix0 = rint_bits(__fsub_rn(__fmul_rn(pp.x, a), __fmul_rn(pp.y, b)));
+            const uint32_t iy1 = rint_bits(__fadd_rn(__fmul_rn(pp.z, b), __fmul_rn(pp.w, a)));
+            const uint32_t ix1 = rint_bits(__fsub_rn(__fmul_rn(pp.z, a), __fmul_rn(pp.w, b)));
+            uint32_t t0, t1;
+            asm volatile("ld.shared.u8 %0, [%1];" : "=r"(t0) : "r"(cbase + iy0 * OD_WPB + ix0));
+            asm volatile("ld.shared.u8 %0, [%1];" : "=r"(t1) : "r"(cbase + iy1 * OD_WPB + ix1));
             val |= (t0 < t1) << j;
         }
         desc[((size_t)f * kcap + d) * 32 + lane] = (uint8_t)val;
@@ -1247,7 +1259,7 @@ static void free_all(orbx_extractor* e) {
     cudaSetDevice(e->P.device);
     void* dptrs[] = {e->d_pyr, e->d_blur, e->d_input, e->d_tabs, e->d_wtabs, e->d_cells, e->d_blur_tiles, e->d_slots,
                      e->d_cell_count, e->d_cand, e->d_pnode, e->d_cand_count, e->d_sel, e->d_sel_count,
-                     e->d_dest, e->d_lapping, e->d_kps, e->d_desc, e->d_nk, e->d_units, e->d_uright, e->d_depth, e->d_pairs,
+                     e->d_dest, e->d_lapping, e->d_kps, e->d_desc, e->d_nk, e->d_units, e->d_odmaps, e->d_uright, e->d_depth, e->d_pairs,
                      e->d_rowent};
     for (void* p : dptrs) if (p) cudaFree(p);
     void* hptrs[] = {e->h_kps, e->h_desc, e->h_nk, e->h_lapping, e->h_uright, e->h_depth, e->h_pairs};
@@ -1424,7 +1436,7 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
         uint32_t d4[32] = {0};
         for (int r = 0; r < 31; ++r) d4[r] = (uint32_t)e->umax[r < 15 ? 15 - r : r - 15] * 0x01010101u + 0x80808080u;
         CK(cudaMemcpyToSymbol(c_d4, d4, sizeof(d4)));
-        CK(cudaFuncSetAttribute(k_orient_describe, cudaFuncAttributeMaxDynamicSharedMemorySize, OD_WARPS * 2 * OD_BUF * 4));
+        CK(cudaFuncSetAttribute(k_orient_describe, cudaFuncAttributeMaxDynamicSharedMemorySize, OD_SMEM));
     }
     CK(cudaMalloc(&e->d_pyr, pyr_bytes));
     CK(cudaMalloc(&e->d_blur, blur_bytes + 256));    /* + slack: window staging reads whole words */
@@ -1550,6 +1562,44 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
     }
     e->T.nlevels = nl;
     for (int l = 0; l < nl; ++l) e->T.lv[l] = e->lv[l];
+    {
+        /* TMA tensor maps for the describe stage: (row bytes, rows, frames) u8 views of every
+         * blurred level (box 48 x 37) and bordered pyramid level (box 32 x 31) */
+        typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                     const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                     CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        CK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+        if (!fn || qres != cudaDriverEntryPointSuccess) { orbx_set_error("cuTensorMapEncodeTiled not available"); free_all(e); return ORBX_ERR_CUDA; }
+        std::vector<ODMaps> Mh(1);
+        ODMaps* M = Mh.data();
+        memset(M, 0, sizeof(ODMaps));
+        for (int l = 0; l < nl; ++l) {
+            const LevelDev& L = e->lv[l];
+            const cuuint32_t estr[3] = {1, 1, 1};
+            {
+                const cuuint64_t dims[3] = {(cuuint64_t)L.bpitch, (cuuint64_t)L.h, (cuuint64_t)B};
+                const cuuint64_t strides[2] = {(cuuint64_t)L.bpitch, (cuuint64_t)L.bframe_bytes};
+                const cuuint32_t box[3] = {OD_WPB, OD_WIN, 1};
+                const CUresult r = ((EncodeFn)fn)(&M->blur[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, L.blur, dims, strides, box, estr,
+                                                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                                  CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                if (r != CUDA_SUCCESS) { orbx_set_error("cuTensorMapEncodeTiled(blur level %d) -> %d", l, (int)r); free_all(e); return ORBX_ERR_CUDA; }
+            }
+            {
+                const cuuint64_t dims[3] = {(cuuint64_t)L.pitch, (cuuint64_t)L.rows, (cuuint64_t)B};
+                const cuuint64_t strides[2] = {(cuuint64_t)L.pitch, (cuuint64_t)L.frame_bytes};
+                const cuuint32_t box[3] = {OD_PPB, 31, 1};
+                const CUresult r = ((EncodeFn)fn)(&M->pyr[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, L.base, dims, strides, box, estr,
+                                                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                                  CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                if (r != CUDA_SUCCESS) { orbx_set_error("cuTensorMapEncodeTiled(pyramid level %d) -> %d", l, (int)r); free_all(e); return ORBX_ERR_CUDA; }
+            }
+        }
+        CK(cudaMalloc(&e->d_odmaps, sizeof(ODMaps)));
+        CK(cudaMemcpy(e->d_odmaps, M, sizeof(ODMaps), cudaMemcpyHostToDevice));
+    }
 #undef CK
     *out = e;
     return ORBX_OK;
@@ -1651,10 +1701,8 @@ extern "C" orbx_status orbx_extract_device(orbx_extractor* e, const uint8_t* d_i
     if (e->profiling) ORBX_CUDA(cudaEventRecord(e->ev[5], st));
     /* stage 5 */
     {
-        UMax um;
-        for (int i = 0; i < 16; ++i) um.v[i] = e->umax[i];
-        k_orient_describe<<<dim3(orbx_div_up((int)e->sel_per_frame, OD_WARPS * OD_KPW), batch), 32 * OD_WARPS, OD_WARPS * 2 * OD_BUF * 4, st>>>(
-            e->T, um, e->d_sel, e->sel_per_frame, e->d_sel_count, e->d_dest, e->d_kps, e->d_desc, e->kcap);
+        k_orient_describe<<<dim3(orbx_div_up((int)e->sel_per_frame, OD_WARPS * OD_KPW), batch), 32 * OD_WARPS, OD_SMEM, st>>>(
+            e->T, (const ODMaps*)e->d_odmaps, e->d_sel, e->sel_per_frame, e->d_sel_count, e->d_dest, e->d_kps, e->d_desc, e->kcap);
         ++launches;
     }
     if (e->profiling) ORBX_CUDA(cudaEventRecord(e->ev[6], st));

@@ -67,6 +67,7 @@ struct orbx_extractor {
     int fast_tp = 8, fast_rows = 8, fast_list_cap = 2;
     int nunits = 0;
     void* d_units = nullptr;        /* FAST units (extractor.cu: struct Unit) */
+    void* d_odmaps = nullptr;       /* TMA tensor maps of the describe stage (extractor.cu: struct ODMaps) */
     cudaStream_t stream = nullptr;
     /* device buffers */
     uint8_t* d_pyr = nullptr;
