@@ -195,6 +195,23 @@ struct Unit {
     unsigned rcp_wc;                                /* floor(2^32/wc)+1 */
 };
 
+/* TMA tensor maps, one per level: (row bytes, rows, frames) u8 views of the blurred level (describe
+ * window box), of the bordered pyramid level (describe patch box) and again of the pyramid level
+ * with the FAST strip box.  Kept in global memory, written once at create. */
+struct ODMaps { CUtensorMap blur[ORBX_MAX_LEVELS]; CUtensorMap pyr[ORBX_MAX_LEVELS]; CUtensorMap fast[ORBX_MAX_LEVELS]; };
+
+__device__ __forceinline__ void od_tma3(uint32_t dst, const CUtensorMap* map, int c0, int c1, int c2, uint32_t bar) {
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                 ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void od_wait(uint32_t bar, uint32_t parity) {
+    uint32_t done;
+    do {
+        asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+                     : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+    } while (!done);
+}
+
 __device__ __forceinline__ bool has9(uint32_t m) {
     m |= m << 16;
     uint32_t a = m & (m >> 1);
@@ -229,9 +246,11 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_units(Tables T, const Uni
                                                               const Cell* __restrict__ cells, int ncells, int ini_th,
                                                               int min_th, uint32_t* __restrict__ slots, uint32_t* scratch,
                                                               size_t slots_per_frame, int* __restrict__ cell_count, int tp,
-                                                              int rows, int list_cap) {
+                                                              int rows, int list_cap, const ODMaps* __restrict__ maps) {
     /* dynamic smem: tile | score (rows x tp bytes each) | list (list_cap u16) | clist (2 x list_cap u16) */
-    extern __shared__ __align__(16) uint8_t fsm[];
+    extern __shared__ __align__(128) uint8_t fsm_raw[];
+    uint8_t* fsm = fsm_raw + ((128u - ((uint32_t)__cvta_generic_to_shared(fsm_raw) & 127u)) & 127u);   /* TMA destination */
+    __shared__ __align__(8) uint64_t s_tbar;
     const int WP = tp >> 2;
     const int map_bytes = rows * tp;
     uint8_t* tile = fsm;
@@ -244,28 +263,28 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_units(Tables T, const Uni
     const Unit U = units[blockIdx.x];
     const LevelDev& L = T.lv[U.level];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    const int shift = U.x0 & 3;                   /* tile column of sub-image x=0 */
-    const int nwords = (U.tw + shift + 3) >> 2;   /* <= WP */
+    const int shift = U.x0 & 15;                  /* tile column of sub-image x=0 (TMA boxes start 16-byte aligned) */
     uint32_t* tile32 = reinterpret_cast<uint32_t*>(tile);
     uint32_t* score32 = reinterpret_cast<uint32_t*>(score);
     const int wc = U.wc, ncell = U.ncell;
     const int dh = U.th - 6;                      /* detection rows [3, th-3) */
 
-    /* stage the strip with aligned 32-bit loads; zero the score map */
+    /* stage the strip: ONE TMA tensor copy (box tp x the level's tallest strip) into the tile,
+     * issued by thread 0; everybody else zeroes the score map meanwhile */
     {
-        const unsigned rcp_nw = 0xFFFFFFFFu / (unsigned)nwords + 1u;
-        const uint8_t* src = lv_ptr(L, f, U.x0 - shift, U.y0);
-        const int nitems = U.th * nwords;
-        for (int i = tid; i < nitems; i += FAST_THREADS) {
-            const int y = (int)__umulhi((unsigned)i, rcp_nw);
-            const int w = i - y * nwords;
-            tile32[y * WP + w] = __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)y * L.pitch) + w);
+        const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&s_tbar);
+        if (tid == 0) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar) : "memory");
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(L.fast_box_rows * tp) : "memory");
+            od_tma3((uint32_t)__cvta_generic_to_shared(tile), &maps->fast[U.level], ORBX_XOFF + U.x0 - shift, ORBX_EDGE + U.y0, f, bar);
         }
         for (int i = tid; i < U.th * WP; i += FAST_THREADS) score32[i] = 0;
         if (tid < FAST_UC) s_cnt[tid] = 0;
         if (tid == 0) { s_n[0] = 0; s_n[1] = 0; s_nc[0] = 0; s_nc[1] = 0; }
+        __syncthreads();            /* barrier init visible to all waiters */
+        od_wait(bar, 0u);
     }
-    __syncthreads();
 
     const unsigned rcp_tp = 0xFFFFFFFFu / (unsigned)tp + 1u;
     uint32_t* bucket = scratch + (size_t)f * slots_per_frame;     /* unordered NMS survivors, per cell at slot_off */
@@ -1071,17 +1090,12 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
 #define OD_WARP_BYTES (2 * OD_WIN_SLOT + 1536)            /* two windows + one patch = 6400 */
 #define OD_SMEM (OD_WARPS * OD_WARP_BYTES + 128)
 
-struct ODMaps { CUtensorMap blur[ORBX_MAX_LEVELS]; CUtensorMap pyr[ORBX_MAX_LEVELS]; };
 
 /* test pairs transposed for the warp: d_pattern_t[j * 32 + lane] = pair 8 * lane + j */
 __device__ float4 d_pattern_t[256];
 /* per patch row v = r - 15: umax[|v|] replicated in every byte, + 0x80 per byte */
 __constant__ uint32_t c_d4[32];
 
-__device__ __forceinline__ void od_tma3(uint32_t dst, const CUtensorMap* map, int c0, int c1, int c2, uint32_t bar) {
-    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
-                 ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(bar) : "memory");
-}
 /* TMA needs the box's first byte 16-byte aligned: boxes start at the aligned column below */
 __device__ __forceinline__ void od_issue_win(const ODMaps* M, int f, int l, int x, int y, uint32_t dst, uint32_t bar) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "n"(OD_WIN_BYTES) : "memory");
@@ -1091,14 +1105,6 @@ __device__ __forceinline__ void od_issue_patch(const ODMaps* M, int f, int l, in
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "n"(OD_PATCH_BYTES) : "memory");
     od_tma3(dst, &M->pyr[l], ORBX_XOFF + ((x - 15) & ~15), ORBX_EDGE + y - 15, f, bar);
 }
-__device__ __forceinline__ void od_wait(uint32_t bar, uint32_t parity) {
-    uint32_t done;
-    do {
-        asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
-                     : "=r"(done) : "r"(bar), "r"(parity) : "memory");
-    } while (!done);
-}
-
 __global__ void __launch_bounds__(32 * OD_WARPS) k_orient_describe(Tables T, const ODMaps* __restrict__ Mp,
                                                           const uint32_t* __restrict__ sel,
                                                           size_t sel_per_frame, const int* __restrict__ sel_count,
@@ -1390,7 +1396,8 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
                     U.ncell = (short)nc; U.wc = (short)wCell; U.pad = 0; U.cell0 = row_first + k;
                     U.offx0 = a.offx; U.offy = a.offy; U.rcp_wc = 0xFFFFFFFFu / (unsigned)wCell + 1u;
                     units.push_back(U);
-                    e->fast_tp = std::max(e->fast_tp, 4 * ((U.tw + 6) >> 2));
+                    e->fast_tp = std::max(e->fast_tp, (int)orbx_align_up(U.tw + 15, 16));
+                    L.fast_box_rows = std::max(L.fast_box_rows, (int)U.th);
                     e->fast_rows = std::max(e->fast_rows, (int)U.th);
                     k += nc;
                 }
@@ -1446,11 +1453,12 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
     CK(cudaMalloc(&e->d_cells, std::max<size_t>(e->cells.size(), 1) * sizeof(Cell)));
     e->nunits = (int)units.size();
     e->fast_list_cap = 3072;            /* u16 entries; >= FAST_UC * widest cell, so a one-row chunk always fits */
+    if (e->fast_tp > 256) { orbx_set_error("FAST strip width %d exceeds the 256-byte TMA box", e->fast_tp); free_all(e); return ORBX_ERR_INVALID; }
     if ((size_t)e->fast_rows * e->fast_tp > 32767) { orbx_set_error("FAST strip %dx%d exceeds the 15-bit tile index", e->fast_tp, e->fast_rows); free_all(e); return ORBX_ERR_INVALID; }
     CK(cudaMalloc(&e->d_units, std::max<size_t>(units.size(), 1) * sizeof(Unit)));
     if (!units.empty()) CK(cudaMemcpy(e->d_units, units.data(), units.size() * sizeof(Unit), cudaMemcpyHostToDevice));
     CK(cudaFuncSetAttribute(k_fast_units, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                            (int)std::max<size_t>((size_t)2 * e->fast_rows * e->fast_tp + 6 * (size_t)e->fast_list_cap, 48 * 1024)));
+                            (int)std::max<size_t>((size_t)2 * e->fast_rows * e->fast_tp + 6 * (size_t)e->fast_list_cap + 128, 48 * 1024)));
     CK(cudaMalloc(&e->d_blur_tiles, blur_tiles.size() * sizeof(int4)));
     CK(cudaMalloc(&e->d_slots, std::max<size_t>(e->slots_per_frame, 1) * B * 4));
     CK(cudaMalloc(&e->d_cell_count, (size_t)std::max(e->ncells, 1) * B * 4));
@@ -1595,6 +1603,11 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
                                                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
                                                   CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
                 if (r != CUDA_SUCCESS) { orbx_set_error("cuTensorMapEncodeTiled(pyramid level %d) -> %d", l, (int)r); free_all(e); return ORBX_ERR_CUDA; }
+                const cuuint32_t fbox[3] = {(cuuint32_t)e->fast_tp, (cuuint32_t)std::max(L.fast_box_rows, 1), 1};
+                const CUresult r2 = ((EncodeFn)fn)(&M->fast[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, L.base, dims, strides, fbox, estr,
+                                                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                                   CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                if (r2 != CUDA_SUCCESS) { orbx_set_error("cuTensorMapEncodeTiled(FAST strip level %d, box %dx%d) -> %d", l, e->fast_tp, L.fast_box_rows, (int)r2); free_all(e); return ORBX_ERR_CUDA; }
             }
         }
         CK(cudaMalloc(&e->d_odmaps, sizeof(ODMaps)));
@@ -1677,9 +1690,9 @@ extern "C" orbx_status orbx_extract_device(orbx_extractor* e, const uint8_t* d_i
     if (e->profiling) ORBX_CUDA(cudaEventRecord(e->ev[1], st));
     /* stage 1 */
     if (e->ncells > 0) {
-        k_fast_units<<<dim3(e->nunits, batch), FAST_THREADS, (size_t)2 * e->fast_rows * e->fast_tp + 6 * (size_t)e->fast_list_cap, st>>>(
+        k_fast_units<<<dim3(e->nunits, batch), FAST_THREADS, (size_t)2 * e->fast_rows * e->fast_tp + 6 * (size_t)e->fast_list_cap + 128, st>>>(
             e->T, static_cast<const Unit*>(e->d_units), e->d_cells, e->ncells, e->P.ini_th_fast, e->P.min_th_fast, e->d_slots,
-            e->d_cand, e->slots_per_frame, e->d_cell_count, e->fast_tp, e->fast_rows, e->fast_list_cap);
+            e->d_cand, e->slots_per_frame, e->d_cell_count, e->fast_tp, e->fast_rows, e->fast_list_cap, (const ODMaps*)e->d_odmaps);
         ++launches;
     }
     if (e->profiling) ORBX_CUDA(cudaEventRecord(e->ev[2], st));

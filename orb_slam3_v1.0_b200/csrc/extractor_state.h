@@ -22,6 +22,7 @@ struct LevelDev {
     const short4* ypad;     /* per padded row {sy, b0, b1, 0} */
     int fast_resize;
     int cell_begin, cell_end;
+    int fast_box_rows;      /* tallest FAST strip of the level = rows of its TMA box */
     int N, nIni;
     float hX;
     int cand_off, cand_cap; /* into the per-frame candidate arrays */
