@@ -186,6 +186,10 @@ __global__ void __launch_bounds__(256) k_resize_w4(LevelDev S, LevelDev D, const
  * pass 1 is a superset of pass 0's and needs no reset. */
 #define FAST_UC 6             /* cells per unit */
 #define FAST_THREADS 256
+#define FAST_WQ 160           /* survivor queue per warp: < 32 left over + up to 128 new */
+#define FAST_CQ 64            /* corner queue per warp: < 32 left over + up to 32 new */
+#define FAST_CL 1024          /* scored corners of a region kept as a list for the NMS pass (2 buffers); overflow -> map scan */
+#define FAST_QBYTES ((FAST_THREADS / 32) * (FAST_WQ + FAST_CQ) * 2 + 2 * FAST_CL * 2)
 #define FAST_MAX_ROWS 76      /* cells are at most 69+6 px high (nRows==1 levels) */
 
 struct Unit {
@@ -210,6 +214,15 @@ __device__ __forceinline__ void od_wait(uint32_t bar, uint32_t parity) {
         asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
                      : "=r"(done) : "r"(bar), "r"(parity) : "memory");
     } while (!done);
+}
+
+/* lane 0 adds v to a shared counter and gets the old value; other lanes keep `old`.  Written as a
+ * predicated ATOMS: nvcc turns `if (lane == 0) atomicAdd()` into its generic warp-aggregation
+ * sequence (~18 instructions) even though one lane is active. */
+__device__ __forceinline__ int lane0_atomic_add(int* counter, int v, int lane, int old) {
+    asm volatile("{\n.reg .pred p;\nsetp.eq.s32 p, %2, 0;\n@p atom.shared.add.u32 %0, [%1], %3;\n}"
+                 : "+r"(old) : "r"((uint32_t)__cvta_generic_to_shared(counter)), "r"(lane), "r"(v) : "memory");
+    return old;
 }
 
 __device__ __forceinline__ bool has9(uint32_t m) {
@@ -246,8 +259,8 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_units(Tables T, const Uni
                                                               const Cell* __restrict__ cells, int ncells, int ini_th,
                                                               int min_th, uint32_t* __restrict__ slots, uint32_t* scratch,
                                                               size_t slots_per_frame, int* __restrict__ cell_count, int tp,
-                                                              int rows, int list_cap, const ODMaps* __restrict__ maps) {
-    /* dynamic smem: tile | score (rows x tp bytes each) | list (list_cap u16) | clist (2 x list_cap u16) */
+                                                              int rows, const ODMaps* __restrict__ maps) {
+    /* dynamic smem: tile | score (rows x tp bytes each) | per-warp queues */
     extern __shared__ __align__(128) uint8_t fsm_raw[];
     uint8_t* fsm = fsm_raw + ((128u - ((uint32_t)__cvta_generic_to_shared(fsm_raw) & 127u)) & 127u);   /* TMA destination */
     __shared__ __align__(8) uint64_t s_tbar;
@@ -255,8 +268,9 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_units(Tables T, const Uni
     const int map_bytes = rows * tp;
     uint8_t* tile = fsm;
     uint8_t* score = fsm + map_bytes;
-    unsigned short* list = reinterpret_cast<unsigned short*>(fsm + 2 * map_bytes);
-    __shared__ int s_n[2], s_nc[2]; /* survivor / corner counters, alternating per chunk */
+    unsigned short* wq = reinterpret_cast<unsigned short*>(fsm + 2 * map_bytes);   /* [warps][FAST_WQ + FAST_CQ] */
+    unsigned short* clist = wq + (FAST_THREADS / 32) * (FAST_WQ + FAST_CQ);        /* [2][FAST_CL] */
+    __shared__ int s_ncl[3];        /* corners appended to the region's list (may exceed FAST_CL = overflow), by region % 3 */
     __shared__ int s_cnt[FAST_UC];
 
     const int f = blockIdx.y;
@@ -281,16 +295,18 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_units(Tables T, const Uni
         }
         for (int i = tid; i < U.th * WP; i += FAST_THREADS) score32[i] = 0;
         if (tid < FAST_UC) s_cnt[tid] = 0;
-        if (tid == 0) { s_n[0] = 0; s_n[1] = 0; s_nc[0] = 0; s_nc[1] = 0; }
+        if (tid < 3) s_ncl[tid] = 0;
         __syncthreads();            /* barrier init visible to all waiters */
         od_wait(bar, 0u);
     }
 
-    const unsigned rcp_tp = 0xFFFFFFFFu / (unsigned)tp + 1u;
     uint32_t* bucket = scratch + (size_t)f * slots_per_frame;     /* unordered NMS survivors, per cell at slot_off */
-    unsigned short* clist = list + list_cap;                      /* [2][list_cap] corners of the current / previous chunk */
     const unsigned lt_mask = (1u << lane) - 1u;
-    int chunk = 0;
+    /* warp-private work queues (tile indices): quick-test survivors and corners awaiting their score */
+    unsigned short* q = wq + wid * (FAST_WQ + FAST_CQ);
+    unsigned short* cq = q + FAST_WQ;
+    int rseq = 0;                                                 /* regions processed so far */
+    const unsigned rcp_tp = 0xFFFFFFFFu / (unsigned)tp + 1u;
     for (int pass = 0; pass < 2 && dh > 0; ++pass) {
         const int th = pass ? min_th : ini_th;
         unsigned active = (1u << ncell) - 1u;
@@ -314,98 +330,20 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_units(Tables T, const Uni
             const int w0 = tlo >> 2, wl = (thi - 1) >> 2, rw = wl - w0 + 1;
             const uint32_t m_first = 0xFFFFFFFFu << (8 * (tlo & 3));
             const uint32_t m_last = 0xFFFFFFFFu >> (8 * (3 - ((thi - 1) & 3)));
-            const int R = max(1, list_cap / (thi - tlo));
             /* flat (row, word) walk with stride FAST_THREADS, advanced incrementally */
             const int dy = FAST_THREADS / rw, dw = FAST_THREADS - dy * rw;
             const int y_init = tid / rw, w_init = tid - y_init * rw;
-            int ncorn_prev = 0;
+            const int iters = (dh * rw + FAST_THREADS - 1) / FAST_THREADS;
 
-            for (int ry = 0; ry < dh; ry += R, ++chunk) {
-                const int nrow = min(R, dh - ry);
-                int* cnt_a = &s_n[chunk & 1];
-                int* cnt_c = &s_nc[chunk & 1];
-                unsigned short* cl = clist + (chunk & 1) * list_cap;
-                /* ---- phase A: 4 pixels per thread, quick reject, compaction of survivors */
-                {
-                    int y = y_init, w = w_init;
-                    const int iters = (nrow * rw + FAST_THREADS - 1) / FAST_THREADS;
-                    for (int it = 0; it < iters; ++it) {
-                        uint32_t pass4 = 0;
-                        int widx = 0;
-                        if (y < nrow) {
-                            widx = (y + ry + 3) * WP + w0 + w;
-                            const uint32_t v4 = tile32[widx];
-                            const uint32_t up = tile32[widx - 3 * WP], dn = tile32[widx + 3 * WP];
-                            const uint32_t lw = tile32[widx - 1], rgt = tile32[widx + 1];   /* in-tile: rows 3..th-4 */
-                            const uint32_t l4 = __funnelshift_r(lw, v4, 8);      /* bytes at column-3 */
-                            const uint32_t r4 = __funnelshift_r(v4, rgt, 24);    /* bytes at column+3 */
-                            const uint32_t g0 = gt4(__vabsdiffu4(dn, v4), k7f, hi), g8 = gt4(__vabsdiffu4(up, v4), k7f, hi);
-                            const uint32_t g4 = gt4(__vabsdiffu4(r4, v4), k7f, hi), g12 = gt4(__vabsdiffu4(l4, v4), k7f, hi);
-                            pass4 = (g0 | g8) & (g4 | g12);
-                            if (w == 0) pass4 &= m_first;
-                            if (w == rw - 1) pass4 &= m_last;
-                        }
-                        /* warp prefix of the per-lane survivor counts (0..4) from three ballots */
-                        const int n = __popc(pass4);
-                        const unsigned b0 = __ballot_sync(0xffffffffu, n & 1), b1 = __ballot_sync(0xffffffffu, n & 2),
-                                       b2 = __ballot_sync(0xffffffffu, n & 4);
-                        const int wtot = __popc(b0) + 2 * __popc(b1) + 4 * __popc(b2);
-                        if (wtot) {
-                            int b = 0;
-                            if (lane == 0) b = atomicAdd(cnt_a, wtot);
-                            b = __shfl_sync(0xffffffffu, b, 0) + __popc(b0 & lt_mask) + 2 * __popc(b1 & lt_mask) + 4 * __popc(b2 & lt_mask);
-                            const int p4 = widx * 4;
-                            if (pass4 & 0x00000080u) list[b++] = (unsigned short)(p4);
-                            if (pass4 & 0x00008000u) list[b++] = (unsigned short)(p4 + 1);
-                            if (pass4 & 0x00800000u) list[b++] = (unsigned short)(p4 + 2);
-                            if (pass4 & 0x80000000u) list[b] = (unsigned short)(p4 + 3);
-                        }
-                        y += dy; w += dw;
-                        if (w >= rw) { w -= rw; ++y; }
-                    }
-                }
-                __syncthreads();
-                /* ---- phase B1: exact FAST-9 test on the survivors -> corner list */
-                const int nsurv = *cnt_a;
-                if (tid == 0) s_n[(chunk + 1) & 1] = 0;      /* nobody touches the other counter before the next barrier */
-                for (int base = 0; base < nsurv; base += FAST_THREADS) {
-                    const int j = base + tid;
-                    bool corner = false;
-                    int idx = 0;
-                    if (j < nsurv) {
-                        idx = list[j];
-                        const uint8_t* p = tile + idx;
-                        const int v = p[0];
-                        /* one IMAD per ring pixel: upper half = (v+th) - r  (negative <=> brighter),
-                         * lower half = r - (v-th) (negative <=> darker); a borrow from the lower half can
-                         * only happen when r < v-th, where the upper half is >= 2*th+1 and stays positive */
-                        const int C = ((v + th) << 16) - (v - th);
-                        uint32_t acc = 0;
-#define FAST_RING(OFF) acc = (acc >> 1) | ((uint32_t)(C - 65535 * (int)p[OFF]) & 0x80008000u)
-                        FAST_RING(3 * tp);      FAST_RING(3 * tp + 1);   FAST_RING(2 * tp + 2);   FAST_RING(tp + 3);
-                        FAST_RING(3);           FAST_RING(-tp + 3);      FAST_RING(-2 * tp + 2);  FAST_RING(-3 * tp + 1);
-                        FAST_RING(-3 * tp);     FAST_RING(-3 * tp - 1);  FAST_RING(-2 * tp - 2);  FAST_RING(-tp - 3);
-                        FAST_RING(-3);          FAST_RING(tp - 3);       FAST_RING(2 * tp - 2);   FAST_RING(3 * tp - 1);
-#undef FAST_RING
-                        const bool dark = has9(acc & 0xFFFFu);
-                        corner = dark || has9(acc >> 16);             /* bright and dark are mutually exclusive */
-                        idx |= dark ? 0x8000 : 0;                     /* tile index < 2^15 (checked on the host) */
-                    }
-                    const unsigned bal = __ballot_sync(0xffffffffu, corner);
-                    if (bal) {
-                        int b = 0;
-                        if (lane == 0) b = atomicAdd(cnt_c, __popc(bal));
-                        b = __shfl_sync(0xffffffffu, b, 0);
-                        if (corner) cl[b + __popc(bal & lt_mask)] = (unsigned short)idx;
-                    }
-                }
-                __syncthreads();
-
-                /* ---- phase B2: corner score, one thread per corner (dense) */
-                const int ncorn = *cnt_c;
-                if (tid == 0) s_nc[(chunk + 1) & 1] = 0;     /* its last readers took it before two barriers ago */
-                for (int j = tid; j < ncorn; j += FAST_THREADS) {
-                    const int ce = cl[j];
+            /* ---- detection: quick reject on 4 px/thread -> survivor queue -> exact FAST-9 test in
+             * full batches of 32 -> corner queue -> corner score in batches of 32.  No block barrier:
+             * the queues belong to the warp, the score map is written at distinct bytes. */
+            int nq = 0, ncq = 0;                                  /* warp-uniform queue fills */
+            int* ncl = &s_ncl[rseq % 3];
+            unsigned short* cl = clist + (rseq & 1) * FAST_CL;
+            auto score_batch = [&](const unsigned short* src, int cnt) {
+                if (lane < cnt) {
+                    const int ce = src[lane];
                     const int idx = ce & 0x7FFF;
                     const uint8_t* p = tile + idx;
                     const int v = p[0];
@@ -419,39 +357,128 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_units(Tables T, const Uni
                     for (int k = 0; k < 16; ++k) e[k] = sgn * (e[k] - v);
                     score[idx] = (uint8_t)(arc_strength(e) - 1);   /* strength > th >= 1 */
                 }
-                __syncthreads();
-
-                /* ---- phase C (one chunk behind: its last row needs this chunk's first score row):
-                 * strict 3x3 local maxima inside the pixel's own cell -> cell buckets */
-                for (int half = 0; half < 2; ++half) {
-                    const bool last = ry + R >= dh;
-                    if (half == 1 && !last) break;
-                    const int nc_ = half ? ncorn : ncorn_prev;
-                    const unsigned short* cc = half ? cl : clist + ((chunk + 1) & 1) * list_cap;
-                    for (int j = tid; j < nc_; j += FAST_THREADS) {
-                        const int idx = cc[j] & 0x7FFF;
-                        const int y = (int)__umulhi((unsigned)idx, rcp_tp);
-                        const int t = idx - y * tp;                       /* tile column */
-                        const int xs = t - shift - 3;                     /* column inside the unit's detection area */
-                        const int k = min((int)__umulhi((unsigned)xs, U.rcp_wc), ncell - 1);
-                        const bool lft = xs != k * wc;                    /* left / right neighbours belong to the same cell */
-                        const bool rgt = (k == ncell - 1) ? (t + 1 < U.tw - 3 + shift) : (xs + 1 != (k + 1) * wc);
-                        const uint8_t* sp = score + idx;
-                        const int v = sp[0];
-                        bool mx = v > sp[-tp] && v > sp[tp];
-                        if (lft) mx = mx && v > sp[-1] && v > sp[-tp - 1] && v > sp[tp - 1];
-                        if (rgt) mx = mx && v > sp[1] && v > sp[-tp + 1] && v > sp[tp + 1];
-                        if (mx) {
-                            const int pos = atomicAdd(&s_cnt[k], 1);
-                            bucket[cells[U.cell0 + k].slot_off + pos] =
-                                (uint32_t)(t - shift + U.offx0) | ((uint32_t)(y + U.offy) << 12) | ((uint32_t)v << 24);
-                        }
-                    }
+                const int base = __shfl_sync(0xffffffffu, lane0_atomic_add(ncl, cnt, lane, 0), 0);
+                if (lane < cnt && base + lane < FAST_CL) cl[base + lane] = src[lane] & 0x7FFF;
+                __syncwarp();
+            };
+            auto exact_batch = [&](const unsigned short* src, int cnt) {
+                bool corner = false;
+                int idx = 0;
+                if (lane < cnt) {
+                    idx = src[lane];
+                    const uint8_t* p = tile + idx;
+                    const int v = p[0];
+                    /* one IMAD per ring pixel: upper half = (v+th) - r  (negative <=> brighter),
+                     * lower half = r - (v-th) (negative <=> darker); a borrow from the lower half can
+                     * only happen when r < v-th, where the upper half is >= 2*th+1 and stays positive */
+                    const int C = ((v + th) << 16) - (v - th);
+                    uint32_t acc = 0;
+#define FAST_RING(OFF) acc = (acc >> 1) | ((uint32_t)(C - 65535 * (int)p[OFF]) & 0x80008000u)
+                    FAST_RING(3 * tp);      FAST_RING(3 * tp + 1);   FAST_RING(2 * tp + 2);   FAST_RING(tp + 3);
+                    FAST_RING(3);           FAST_RING(-tp + 3);      FAST_RING(-2 * tp + 2);  FAST_RING(-3 * tp + 1);
+                    FAST_RING(-3 * tp);     FAST_RING(-3 * tp - 1);  FAST_RING(-2 * tp - 2);  FAST_RING(-tp - 3);
+                    FAST_RING(-3);          FAST_RING(tp - 3);       FAST_RING(2 * tp - 2);   FAST_RING(3 * tp - 1);
+#undef FAST_RING
+                    const bool dark = has9(acc & 0xFFFFu);
+                    corner = dark || has9(acc >> 16);             /* bright and dark are mutually exclusive */
+                    idx |= dark ? 0x8000 : 0;                     /* tile index < 2^15 (checked on the host) */
                 }
-                ncorn_prev = ncorn;
+                const unsigned bal = __ballot_sync(0xffffffffu, corner);
+                if (corner) cq[ncq + __popc(bal & lt_mask)] = (unsigned short)idx;
+                ncq += __popc(bal);
+                __syncwarp();
+                if (ncq >= 32) { ncq -= 32; score_batch(cq + ncq, 32); }
+            };
+            {
+                int y = y_init, w = w_init;
+                for (int it = 0; it < iters; ++it) {
+                    uint32_t pass4 = 0;
+                    int widx = 0;
+                    if (y < dh) {
+                        widx = (y + 3) * WP + w0 + w;
+                        const uint32_t v4 = tile32[widx];
+                        const uint32_t up = tile32[widx - 3 * WP], dn = tile32[widx + 3 * WP];
+                        const uint32_t lw = tile32[widx - 1], rgt = tile32[widx + 1];   /* in-tile: rows 3..th-4 */
+                        const uint32_t l4 = __funnelshift_r(lw, v4, 8);      /* bytes at column-3 */
+                        const uint32_t r4 = __funnelshift_r(v4, rgt, 24);    /* bytes at column+3 */
+                        const uint32_t g0 = gt4(__vabsdiffu4(dn, v4), k7f, hi), g8 = gt4(__vabsdiffu4(up, v4), k7f, hi);
+                        const uint32_t g4 = gt4(__vabsdiffu4(r4, v4), k7f, hi), g12 = gt4(__vabsdiffu4(l4, v4), k7f, hi);
+                        pass4 = (g0 | g8) & (g4 | g12);
+                        if (w == 0) pass4 &= m_first;
+                        if (w == rw - 1) pass4 &= m_last;
+                    }
+                    /* warp prefix of the per-lane survivor counts (0..4) from three ballots */
+                    const int n = __popc(pass4);
+                    const unsigned b0 = __ballot_sync(0xffffffffu, n & 1), b1 = __ballot_sync(0xffffffffu, n & 2),
+                                   b2 = __ballot_sync(0xffffffffu, n & 4);
+                    const int wtot = __popc(b0) + 2 * __popc(b1) + 4 * __popc(b2);
+                    if (wtot) {
+                        int b = nq + __popc(b0 & lt_mask) + 2 * __popc(b1 & lt_mask) + 4 * __popc(b2 & lt_mask);
+                        const int p4 = widx * 4;
+                        if (pass4 & 0x00000080u) q[b++] = (unsigned short)(p4);
+                        if (pass4 & 0x00008000u) q[b++] = (unsigned short)(p4 + 1);
+                        if (pass4 & 0x00800000u) q[b++] = (unsigned short)(p4 + 2);
+                        if (pass4 & 0x80000000u) q[b] = (unsigned short)(p4 + 3);
+                        nq += wtot;
+                        __syncwarp();
+                        while (nq >= 32) { nq -= 32; exact_batch(q + nq, 32); }
+                    }
+                    y += dy; w += dw;
+                    if (w >= rw) { w -= rw; ++y; }
+                }
+                if (nq) exact_batch(q, nq);
+                if (ncq) score_batch(cq, ncq);
             }
             __syncthreads();
+
+            /* ---- non-maximum suppression: strict 3x3 local maxima inside the pixel's own cell go to
+             * the cell buckets.  Dense over the region's corner list; if that overflowed, the score
+             * map itself is scanned. */
+            auto nms = [&](int yt, int t) {
+                const int xs = t - shift - 3;                     /* column inside the unit's detection area */
+                const int k = min((int)__umulhi((unsigned)xs, U.rcp_wc), ncell - 1);
+                const bool lft = xs != k * wc;                    /* left / right neighbours belong to the same cell */
+                const bool rgt = (k == ncell - 1) ? (t + 1 < U.tw - 3 + shift) : (xs + 1 != (k + 1) * wc);
+                const uint8_t* sp = score + yt * tp + t;
+                const int v = sp[0];
+                bool mx = v > sp[-tp] && v > sp[tp];
+                if (lft) mx = mx && v > sp[-1] && v > sp[-tp - 1] && v > sp[tp - 1];
+                if (rgt) mx = mx && v > sp[1] && v > sp[-tp + 1] && v > sp[tp + 1];
+                if (mx) {
+                    const int pos = atomicAdd(&s_cnt[k], 1);
+                    bucket[cells[U.cell0 + k].slot_off + pos] =
+                        (uint32_t)(t - shift + U.offx0) | ((uint32_t)(yt + U.offy) << 12) | ((uint32_t)v << 24);
+                }
+            };
+            const int ncorn = *ncl;
+            if (tid == 0) s_ncl[(rseq + 2) % 3] = 0;             /* next user: region rseq+2, after the next barrier */
+            if (ncorn <= FAST_CL) {
+                for (int j = tid; j < ncorn; j += FAST_THREADS) {
+                    const int idx = cl[j];
+                    const int yt = (int)__umulhi((unsigned)idx, rcp_tp);
+                    nms(yt, idx - yt * tp);
+                }
+            } else {
+                int y = y_init, w = w_init;
+                for (int it = 0; it < iters; ++it) {
+                    if (y < dh) {
+                        const int widx = (y + 3) * WP + w0 + w;
+                        uint32_t s4 = score32[widx];
+                        if (w == 0) s4 &= m_first;
+                        if (w == rw - 1) s4 &= m_last;
+                        while (s4) {
+                            const int bsel = (__ffs(s4) - 1) >> 3;
+                            s4 &= ~(0xFFu << (8 * bsel));
+                            nms(y + 3, (w0 + w) * 4 + bsel);
+                        }
+                    }
+                    y += dy; w += dw;
+                    if (w >= rw) { w -= rw; ++y; }
+                }
+            }
+            ++rseq;
         }
+        __syncthreads();
     }
 
     /* ---- phase D: cell by cell, raster order inside the cell (rank by packed y|x) */
@@ -1452,13 +1479,12 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
     CK(cudaMalloc(&e->d_tabs, tab_entries * sizeof(short4)));
     CK(cudaMalloc(&e->d_cells, std::max<size_t>(e->cells.size(), 1) * sizeof(Cell)));
     e->nunits = (int)units.size();
-    e->fast_list_cap = 3072;            /* u16 entries; >= FAST_UC * widest cell, so a one-row chunk always fits */
     if (e->fast_tp > 256) { orbx_set_error("FAST strip width %d exceeds the 256-byte TMA box", e->fast_tp); free_all(e); return ORBX_ERR_INVALID; }
     if ((size_t)e->fast_rows * e->fast_tp > 32767) { orbx_set_error("FAST strip %dx%d exceeds the 15-bit tile index", e->fast_tp, e->fast_rows); free_all(e); return ORBX_ERR_INVALID; }
     CK(cudaMalloc(&e->d_units, std::max<size_t>(units.size(), 1) * sizeof(Unit)));
     if (!units.empty()) CK(cudaMemcpy(e->d_units, units.data(), units.size() * sizeof(Unit), cudaMemcpyHostToDevice));
     CK(cudaFuncSetAttribute(k_fast_units, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                            (int)std::max<size_t>((size_t)2 * e->fast_rows * e->fast_tp + 6 * (size_t)e->fast_list_cap + 128, 48 * 1024)));
+                            (int)std::max<size_t>((size_t)2 * e->fast_rows * e->fast_tp + FAST_QBYTES + 128, 48 * 1024)));
     CK(cudaMalloc(&e->d_blur_tiles, blur_tiles.size() * sizeof(int4)));
     CK(cudaMalloc(&e->d_slots, std::max<size_t>(e->slots_per_frame, 1) * B * 4));
     CK(cudaMalloc(&e->d_cell_count, (size_t)std::max(e->ncells, 1) * B * 4));
@@ -1690,9 +1716,9 @@ extern "C" orbx_status orbx_extract_device(orbx_extractor* e, const uint8_t* d_i
     if (e->profiling) ORBX_CUDA(cudaEventRecord(e->ev[1], st));
     /* stage 1 */
     if (e->ncells > 0) {
-        k_fast_units<<<dim3(e->nunits, batch), FAST_THREADS, (size_t)2 * e->fast_rows * e->fast_tp + 6 * (size_t)e->fast_list_cap + 128, st>>>(
+        k_fast_units<<<dim3(e->nunits, batch), FAST_THREADS, (size_t)2 * e->fast_rows * e->fast_tp + FAST_QBYTES + 128, st>>>(
             e->T, static_cast<const Unit*>(e->d_units), e->d_cells, e->ncells, e->P.ini_th_fast, e->P.min_th_fast, e->d_slots,
-            e->d_cand, e->slots_per_frame, e->d_cell_count, e->fast_tp, e->fast_rows, e->fast_list_cap, (const ODMaps*)e->d_odmaps);
+            e->d_cand, e->slots_per_frame, e->d_cell_count, e->fast_tp, e->fast_rows, (const ODMaps*)e->d_odmaps);
         ++launches;
     }
     if (e->profiling) ORBX_CUDA(cudaEventRecord(e->ev[2], st));
