@@ -131,41 +131,50 @@ __global__ void __launch_bounds__(256) k_resize(LevelDev S, LevelDev D, unsigned
  * each horizontal interpolation is one PRMT + one 2-way dot product (IDP.2A). */
 struct ResizeMeta { uint32_t m; };   /* base byte (16b) | off0<<16 | off1<<20 | off2<<24 | off3<<28; ~0 = outside */
 
+#define RS_RPT 4        /* destination rows per thread: the per-word column tables are loaded once for all of them */
 __global__ void __launch_bounds__(256) k_resize_w4(LevelDev S, LevelDev D, const uint4* __restrict__ xcoef,
                                                    const uint32_t* __restrict__ xmeta,
                                                    const short4* __restrict__ ypad, unsigned rcp_chunks) {
     const int chunks = D.pitch / 4;
     const unsigned i = blockIdx.x * 256u + threadIdx.x;
-    const int r = (int)__umulhi(i, rcp_chunks);
-    if (r >= D.rows) return;
-    const int c = (int)i - r * chunks;
+    const int rg = (int)__umulhi(i, rcp_chunks);
+    const int r_first = rg * RS_RPT;
+    if (r_first >= D.rows) return;
+    const int c = (int)i - rg * chunks;
     const int f = blockIdx.y;
     const uint32_t meta = __ldg(xmeta + c);
     if (meta == 0xFFFFFFFFu) return;
     const uint32_t selw = __ldg(D.xsel + c);
     const uint4 cf = __ldg(xcoef + c);
-    const short4 yt = __ldg(ypad + r);                 /* {sy, b0, b1} for the padded row r */
+    const uint32_t cfs[4] = {cf.x, cf.y, cf.z, cf.w};
     const uint32_t base = meta & 0xFFFFu;
     const int sh = (base & 3) * 8;
-    const uint32_t* row0 = reinterpret_cast<const uint32_t*>(S.base + (size_t)f * S.frame_bytes +
-                                                              (size_t)(yt.x + ORBX_EDGE) * S.pitch) + (base >> 2);
-    const uint32_t* row1 = row0 + (S.pitch >> 2);      /* row sy+1 exists in the bordered source */
-    const uint32_t a0 = __ldg(row0), a1 = __ldg(row0 + 1), a2 = __ldg(row0 + 2);
-    const uint32_t b0 = __ldg(row1), b1 = __ldg(row1 + 1), b2 = __ldg(row1 + 2);
-    const uint32_t U0 = __funnelshift_r(a0, a1, sh), V0 = __funnelshift_r(a1, a2, sh);
-    const uint32_t U1 = __funnelshift_r(b0, b1, sh), V1 = __funnelshift_r(b1, b2, sh);
-    /* (b * (H >> 4)) >> 16 as one IMAD.HI: b is pre-shifted by 16 */
-    const uint32_t wy0 = (uint32_t)yt.y << 16, wy1 = (uint32_t)yt.z << 16;
-    const uint32_t cfs[4] = {cf.x, cf.y, cf.z, cf.w};
-    uint32_t out = 0;
+    const uint32_t spw = (uint32_t)S.pitch >> 2;
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(S.base + (size_t)f * S.frame_bytes + (size_t)ORBX_EDGE * S.pitch) + (base >> 2);
+    uint32_t* dst = reinterpret_cast<uint32_t*>(D.base + (size_t)f * D.frame_bytes + (size_t)r_first * D.pitch) + c;
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        const uint32_t sel = selw >> (8 * k);            /* PRMT reads the low 2 selector nibbles we need */
-        const uint32_t r0 = __dp2a_lo(cfs[k], __byte_perm(U0, V0, sel), 0u);
-        const uint32_t r1 = __dp2a_lo(cfs[k], __byte_perm(U1, V1, sel), 0u);
-        out |= ((__umulhi(wy0, r0 >> 4) + __umulhi(wy1, r1 >> 4) + 2u) >> 2) << (8 * k);
+    for (int j = 0; j < RS_RPT; ++j) {
+        if (r_first + j < D.rows) {
+            const short4 yt = __ldg(ypad + r_first + j);       /* {sy, b0, b1} for the padded row */
+            const uint32_t* row0 = src + (uint32_t)yt.x * spw;
+            const uint32_t* row1 = row0 + spw;                 /* row sy+1 exists in the bordered source */
+            const uint32_t a0 = __ldg(row0), a1 = __ldg(row0 + 1), a2 = __ldg(row0 + 2);
+            const uint32_t b0 = __ldg(row1), b1 = __ldg(row1 + 1), b2 = __ldg(row1 + 2);
+            const uint32_t U0 = __funnelshift_r(a0, a1, sh), V0 = __funnelshift_r(a1, a2, sh);
+            const uint32_t U1 = __funnelshift_r(b0, b1, sh), V1 = __funnelshift_r(b1, b2, sh);
+            /* (b * (H >> 4)) >> 16 as one IMAD.HI: b is pre-shifted by 16 */
+            const uint32_t wy0 = (uint32_t)yt.y << 16, wy1 = (uint32_t)yt.z << 16;
+            uint32_t out = 0;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const uint32_t sel = selw >> (8 * k);            /* PRMT reads the low 2 selector nibbles we need */
+                const uint32_t r0 = __dp2a_lo(cfs[k], __byte_perm(U0, V0, sel), 0u);
+                const uint32_t r1 = __dp2a_lo(cfs[k], __byte_perm(U1, V1, sel), 0u);
+                out |= ((__umulhi(wy0, r0 >> 4) + __umulhi(wy1, r1 >> 4) + 2u) >> 2) << (8 * k);
+            }
+            dst[(size_t)j * (D.pitch >> 2)] = out;
+        }
     }
-    *reinterpret_cast<uint32_t*>(D.base + (size_t)f * D.frame_bytes + (size_t)r * D.pitch + c * 4) = out;
 }
 
 /* ================================================================== stage 1: FAST per cell */
@@ -259,7 +268,7 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_units(Tables T, const Uni
                                                               const Cell* __restrict__ cells, int ncells, int ini_th,
                                                               int min_th, uint32_t* __restrict__ slots, uint32_t* scratch,
                                                               size_t slots_per_frame, int* __restrict__ cell_count, int tp,
-                                                              int rows, const ODMaps* __restrict__ maps) {
+                                                              int rows, int cl_cap, const ODMaps* __restrict__ maps) {
     /* dynamic smem: tile | score (rows x tp bytes each) | per-warp queues */
     extern __shared__ __align__(128) uint8_t fsm_raw[];
     uint8_t* fsm = fsm_raw + ((128u - ((uint32_t)__cvta_generic_to_shared(fsm_raw) & 127u)) & 127u);   /* TMA destination */
@@ -358,7 +367,7 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_units(Tables T, const Uni
                     score[idx] = (uint8_t)(arc_strength(e) - 1);   /* strength > th >= 1 */
                 }
                 const int base = __shfl_sync(0xffffffffu, lane0_atomic_add(ncl, cnt, lane, 0), 0);
-                if (lane < cnt && base + lane < FAST_CL) cl[base + lane] = src[lane] & 0x7FFF;
+                if (lane < cnt && base + lane < cl_cap) cl[base + lane] = src[lane] & 0x7FFF;
                 __syncwarp();
             };
             auto exact_batch = [&](const unsigned short* src, int cnt) {
@@ -452,7 +461,7 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_units(Tables T, const Uni
             };
             const int ncorn = *ncl;
             if (tid == 0) s_ncl[(rseq + 2) % 3] = 0;             /* next user: region rseq+2, after the next barrier */
-            if (ncorn <= FAST_CL) {
+            if (ncorn <= cl_cap) {
                 for (int j = tid; j < ncorn; j += FAST_THREADS) {
                     const int idx = cl[j];
                     const int yt = (int)__umulhi((unsigned)idx, rcp_tp);
@@ -1661,6 +1670,12 @@ extern "C" orbx_status orbx_extractor_tables(const orbx_extractor* e, float* sca
 extern "C" int orbx_extractor_capacity(const orbx_extractor* e) { return e ? e->kcap : 0; }
 extern "C" void* orbx_extractor_stream(orbx_extractor* e) { return e ? (void*)e->stream : nullptr; }
 extern "C" int orbx_extractor_last_launches(const orbx_extractor* e) { return e ? e->last_launches : 0; }
+extern "C" orbx_status orbx_extractor_set_fast_corner_list(orbx_extractor* e, int entries) {
+    if (!e || entries < 1 || entries > FAST_CL) { orbx_set_error("corner list capacity outside [1,%d]", FAST_CL); return ORBX_ERR_INVALID; }
+    e->fast_cl_cap = entries;
+    return ORBX_OK;
+}
+
 extern "C" orbx_status orbx_extractor_set_profiling(orbx_extractor* e, int on) {
     if (!e) return ORBX_ERR_INVALID;
     e->profiling = on != 0;
@@ -1707,7 +1722,7 @@ extern "C" orbx_status orbx_extract_device(orbx_extractor* e, const uint8_t* d_i
             const unsigned ch = D.pitch / 4;
             const dim3 grid(orbx_div_up(D.rows * ch, 256), batch);
             if (D.fast_resize)
-                k_resize_w4<<<grid, 256, 0, st>>>(e->T.lv[l - 1], D, D.xcoef, D.xmeta, D.ypad, 0xFFFFFFFFu / ch + 1u);
+                k_resize_w4<<<dim3(orbx_div_up(orbx_div_up(D.rows, RS_RPT) * ch, 256), batch), 256, 0, st>>>(e->T.lv[l - 1], D, D.xcoef, D.xmeta, D.ypad, 0xFFFFFFFFu / ch + 1u);
             else
                 k_resize<<<grid, 256, 0, st>>>(e->T.lv[l - 1], D, 0xFFFFFFFFu / ch + 1u);
             ++launches;
@@ -1718,7 +1733,7 @@ extern "C" orbx_status orbx_extract_device(orbx_extractor* e, const uint8_t* d_i
     if (e->ncells > 0) {
         k_fast_units<<<dim3(e->nunits, batch), FAST_THREADS, (size_t)2 * e->fast_rows * e->fast_tp + FAST_QBYTES + 128, st>>>(
             e->T, static_cast<const Unit*>(e->d_units), e->d_cells, e->ncells, e->P.ini_th_fast, e->P.min_th_fast, e->d_slots,
-            e->d_cand, e->slots_per_frame, e->d_cell_count, e->fast_tp, e->fast_rows, (const ODMaps*)e->d_odmaps);
+            e->d_cand, e->slots_per_frame, e->d_cell_count, e->fast_tp, e->fast_rows, e->fast_cl_cap, (const ODMaps*)e->d_odmaps);
         ++launches;
     }
     if (e->profiling) ORBX_CUDA(cudaEventRecord(e->ev[2], st));

@@ -67,6 +67,7 @@ struct orbx_extractor {
     int nblur_tiles = 0;
     int fast_tp = 8, fast_rows = 8, fast_list_cap = 2;
     int nunits = 0;
+    int fast_cl_cap = 1024;         /* FAST corner-list entries in use (<= FAST_CL) */
     void* d_units = nullptr;        /* FAST units (extractor.cu: struct Unit) */
     void* d_odmaps = nullptr;       /* TMA tensor maps of the describe stage (extractor.cu: struct ODMaps) */
     cudaStream_t stream = nullptr;

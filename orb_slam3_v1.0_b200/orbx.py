@@ -63,6 +63,7 @@ def lib():
         L.orbx_extractor_candidates.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         L.orbx_extractor_last_launches.argtypes = [C.c_void_p]
         L.orbx_extractor_set_profiling.argtypes = [C.c_void_p, C.c_int]
+        L.orbx_extractor_set_fast_corner_list.argtypes = [C.c_void_p, C.c_int]
         L.orbx_extractor_stage_ms.argtypes = [C.c_void_p, C.c_void_p]
         L.orbx_host_alloc.argtypes = [C.POINTER(C.c_void_p), C.c_size_t]
         L.orbx_host_free.argtypes = [C.c_void_p]
@@ -260,6 +261,9 @@ class ORBextractor:
 
     def set_profiling(self, on=True):
         _ck(lib().orbx_extractor_set_profiling(self._h, int(on)))
+
+    def set_fast_corner_list(self, entries):
+        _ck(lib().orbx_extractor_set_fast_corner_list(self._h, int(entries)))
 
     def stage_ms(self):
         ms = np.empty(6, np.float32)

@@ -95,6 +95,17 @@ def test_noise_image_dense_candidates(pkg, oracle):
     gex.close()
 
 
+def test_fast_nms_scan_path(pkg, oracle, synth):
+    """A tiny FAST corner list forces every region through the score-map scan variant of the
+    non-maximum suppression; results must not change."""
+    img = synth.textured_image(640, 400, seed=31)
+    gex = pkg.orbx.ORBextractor(900, 1.2, 6, 20, 7).prepare(640, 400, 1)
+    gex.set_fast_corner_list(4)
+    oex = oracle.Extractor(900, 1.2, 6, 20, 7)
+    _compare_frame(gex, oex, img, (0, 0), got=gex(img, (0, 0)))
+    gex.close()
+
+
 def test_many_frames_property(pkg, oracle, synth):
     """Larger batch: every frame equals the oracle; repeated launches are deterministic."""
     w, h, B = 752, 480, 24
