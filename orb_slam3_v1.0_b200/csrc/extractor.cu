@@ -131,7 +131,9 @@ __global__ void __launch_bounds__(256) k_resize(LevelDev S, LevelDev D, unsigned
  * each horizontal interpolation is one PRMT + one 2-way dot product (IDP.2A). */
 struct ResizeMeta { uint32_t m; };   /* base byte (16b) | off0<<16 | off1<<20 | off2<<24 | off3<<28; ~0 = outside */
 
+#ifndef RS_RPT
 #define RS_RPT 4        /* destination rows per thread: the per-word column tables are loaded once for all of them */
+#endif
 __global__ void __launch_bounds__(256) k_resize_w4(LevelDev S, LevelDev D, const uint4* __restrict__ xcoef,
                                                    const uint32_t* __restrict__ xmeta,
                                                    const short4* __restrict__ ypad, unsigned rcp_chunks) {
@@ -508,7 +510,9 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_units(Tables T, const Uni
 }
 
 /* ================================================================== stage 2: quadtree */
+#ifndef OCT_THREADS
 #define OCT_THREADS 128
+#endif
 
 /* exclusive scan of a[0..n) in shared memory, in place; returns the total. All threads call. */
 __device__ int block_excl_scan(int* a, int n, int* s_tmp /* [OCT_THREADS/32 + 1] */) {
@@ -1115,8 +1119,12 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
  *  IC_Angle: 3 patch rows x 9 words per step; a word's four columns are masked to the row's
  *  half-width umax[|v|] with byte arithmetic and reduced by two IDP.4A (weights 1 and u).
  *  rBRIEF: lane = descriptor byte, gathers its 16 samples from the staged window. */
+#ifndef OD_WARPS
 #define OD_WARPS 8
+#endif
+#ifndef OD_KPW
 #define OD_KPW 8
+#endif
 #define OD_WIN 37
 #define OD_WPB 64           /* window pitch in bytes: 37 columns + up to 15 bytes of 16-byte alignment */
 #define OD_PPB 48           /* patch pitch in bytes: 31 columns + up to 15 */
