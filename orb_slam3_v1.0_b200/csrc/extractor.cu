@@ -1430,7 +1430,9 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
                 }
                 /* FAST units: the row's cells in runs of <= FAST_UC, evenly sized */
                 const int nrow = (int)e->cells.size() - row_first;
-                const int nun = orbx_div_up(nrow, FAST_UC);
+                /* a unit's strip (cells + 6 px overlap + up to 15 px of TMA alignment) must fit the 256-byte box */
+                const int ucap = std::max(1, std::min(FAST_UC, (256 - 15 - 6) / std::max(wCell, 1)));
+                const int nun = orbx_div_up(nrow, ucap);
                 for (int u = 0, k = 0; u < nun; ++u) {
                     const int nc = (nrow - k + (nun - u) - 1) / (nun - u);
                     const Cell& a = e->cells[row_first + k];

@@ -17,6 +17,7 @@ CONFIGS = [
     (512, 512, 1500, 8, 7),           # TUM-VI
     (1241, 376, 2000, 8, 11),         # KITTI
     (320, 240, 300, 4, 3),
+    (276, 200, 300, 3, 13),           # 6 cells of 41 px per row: widest FAST unit strip (TMA box limit)
 ]
 
 
