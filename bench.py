@@ -113,6 +113,26 @@ def cpu_baseline(nthreads, seconds_target=12.0):
             "single_thread_fps": 1.0 / per_frame}
 
 
+def single_frame_latency(pkg, local, frame):
+    """operator() as the tracking thread calls it: ONE frame from a host buffer, keypoints and
+    descriptors back on the host (orbx_extract_host + sync + fetch), wall clock per call."""
+    ox = pkg.orbx
+    ex1 = ox.ORBextractor(NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH, device=local, max_batch=1).prepare(W, H, 1)
+    pin = ox.PinnedBuffer((1, H, W))
+    pin.array[0] = frame
+    for _ in range(20):
+        ex1(pin.array[0], (0, 0))
+    ts = []
+    for _ in range(200):
+        t0 = time.perf_counter()
+        ex1(pin.array[0], (0, 0))
+        ts.append(time.perf_counter() - t0)
+    ex1.close()
+    ts = np.array(ts) * 1e3
+    return {"median_ms": float(np.median(ts)), "p95_ms": float(np.percentile(ts, 95)), "calls": 200,
+            "note": "batch 1 through the C ABI with host buffers; 13 kernel launches + H2D + D2H + sync per call"}
+
+
 def matching_bench(pkg, torch, local, ex, B):
     """Secondary numbers of BASELINE.json's metric ("Hamming matches/sec"): device-timed stereo
     row search on the extractor's resident output, batched projection search through the C ABI
@@ -366,6 +386,7 @@ def main():
         }
         if not args.no_matching:
             line["matching"] = matching_bench(pkg, torch, local, ex, B)
+            line["single_frame_latency"] = single_frame_latency(pkg, local, frames[0])
         if not args.no_cpu_baseline and world == 1:
             line["cpu_baseline"] = cpu_baseline(os.cpu_count() or 1)
         print(json.dumps(line))
