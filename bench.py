@@ -157,6 +157,17 @@ def matching_bench(pkg, torch, local, ex, B):
     out["stereo"] = {"pairs_per_s": len(lf) / (ms * 1e-3), "ms_per_launch": ms, "pairs_per_launch": int(len(lf)),
                      "matched_per_pair": float((ur >= 0).sum() / len(lf)),
                      "note": "consecutive synthetic frames paired as L/R (not a rectified pair): times the row search + SAD, match count is incidental"}
+    # ---- Frame::AssignFeaturesToGrid on the device-resident keypoints of the whole batch
+    gw_inv, gh_inv = float(np.float32(64) / np.float32(W)), float(np.float32(48) / np.float32(H))
+    ex.assign_grid(0.0, 0.0, gw_inv, gh_inv, 64, 48)
+    e0.record(st)
+    for _ in range(reps):
+        ex.assign_grid(0.0, 0.0, gw_inv, gh_inv, 64, 48)
+    e1.record(st)
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    out["frame_grid"] = {"frames_per_s": B / (ms * 1e-3), "ms_per_launch": ms, "frames_per_launch": int(B),
+                         "note": "64x48 CSR grid of every frame of the batch from its device-resident keypoints"}
     # ---- SearchByProjection, 64 problems per call, 1000 keypoints x 1500 map points, th = 3
     m = ox.ORBmatcher(local)
     Fs = [pkg.synth.frame_view(1000, seed=100 + i) for i in range(8)]

@@ -168,6 +168,24 @@ typedef struct {
     const uint8_t* desc;            /* GetDescriptor(), n x 32 */
 } orbx_mappoints;
 
+/* Frame::AssignFeaturesToGrid + PosInGrid   src/Frame.cc:157-176, 470-480, for nframes frames:
+ * cell_off[p][gcols*grows + 1] / cell_idx[p][F[p].n] = CSR over the cells in the reference's linear
+ * order (y*cols + x), keypoints in push_back order inside a cell; the unused tail of cell_idx
+ * (keypoints outside the grid) is -1.  Only n, kx, ky and the grid fields of F are read. */
+orbx_status orbx_assign_features_to_grid(orbx_matcher* m, int nframes, const orbx_frame_view* F,
+                                         int* const* cell_off, int* const* cell_idx);
+/* Frame::GetFeaturesInArea   src/Frame.cc:404-468, nq queries against one frame: out_count[q] =
+ * vIndices.size(), out_idx[q*cap .. ) = the first min(count, cap) indices in the reference's order. */
+orbx_status orbx_features_in_area(orbx_matcher* m, const orbx_frame_view* F, int nq, const float* x, const float* y,
+                                  const float* r, const int* minLevel, const int* maxLevel, int* out_count,
+                                  int* out_idx, int cap);
+/* The same grid for every frame of an extractor's last batch, built on the device from its
+ * resident keypoints on its stream (mvKeysUn == mvKeys: rectified / distortion-free cameras), and
+ * its read-back (cell_idx receives min(idx_cap, capacity) entries). */
+orbx_status orbx_extractor_assign_grid(orbx_extractor* e, float minx, float miny, float gw_inv, float gh_inv,
+                                       int gcols, int grows);
+orbx_status orbx_extractor_grid_fetch(orbx_extractor* e, int f, int* cell_off, int* cell_idx, int idx_cap);
+
 /* ORBmatcher::SearchByProjection(Frame, vpMapPoints, th, bFarPoints, thFarPoints, nnRatio,
  * checkOrientation)   src/ORBmatcher.cc:31-123.
  * claimed[p][i] != 0: frame keypoint i already holds a MapPoint with observations (:77-79);

@@ -191,6 +191,26 @@ def _frame_view(F, keep):
                       sc.ctypes.data, len(sc))
 
 
+def assign_features_to_grid(F):
+    keep = []
+    fv = _frame_view(F, keep)
+    off = np.empty(F["gcols"] * F["grows"] + 1, np.int32)
+    idx = np.empty(max(fv.n, 1), np.int32)
+    lib().orc_assign_features_to_grid(C.byref(fv), _p(off), _p(idx))
+    return off, idx[:fv.n]
+
+
+def features_in_area(F, x, y, r, minLevel, maxLevel, cap=256):
+    keep = []
+    fv = _frame_view(F, keep)
+    x, y, r = _f32(x), _f32(y), _f32(r)
+    a, b = _i32(minLevel), _i32(maxLevel)
+    cnt = np.empty(len(x), np.int32)
+    idx = np.full((len(x), cap), -1, np.int32)
+    lib().orc_features_in_area(C.byref(fv), len(x), _p(x), _p(y), _p(r), _p(a), _p(b), _p(cnt), _p(idx), cap)
+    return cnt, idx
+
+
 def search_by_projection(F, mp, th, bFarPoints=False, thFarPoints=0.0, nnRatio=0.8, claimed=None):
     keep = []
     fv = _frame_view(F, keep)

@@ -691,6 +691,30 @@ void features_in_area(const orc_frame_view* F, const std::vector<std::vector<int
 }
 } // namespace
 
+/* Frame::AssignFeaturesToGrid as CSR (cells in linear order, push_back order inside a cell) */
+void orc_assign_features_to_grid(const orc_frame_view* F, int* cell_off, int* cell_idx) {
+    const std::vector<std::vector<int>> grid = build_grid(F);
+    int o = 0;
+    for (size_t c = 0; c < grid.size(); ++c) {
+        cell_off[c] = o;
+        for (int i : grid[c]) cell_idx[o++] = i;
+    }
+    cell_off[grid.size()] = o;
+    for (; o < F->n; ++o) cell_idx[o] = -1;
+}
+
+/* Frame::GetFeaturesInArea for nq queries; out_idx is [nq][cap], out_count the full vIndices sizes */
+void orc_features_in_area(const orc_frame_view* F, int nq, const float* x, const float* y, const float* r,
+                          const int* minLevel, const int* maxLevel, int* out_count, int* out_idx, int cap) {
+    const std::vector<std::vector<int>> grid = build_grid(F);
+    std::vector<int> v;
+    for (int q = 0; q < nq; ++q) {
+        features_in_area(F, grid, x[q], y[q], r[q], minLevel[q], maxLevel[q], v);
+        out_count[q] = (int)v.size();
+        for (int k = 0; k < (int)v.size() && k < cap; ++k) out_idx[(size_t)q * cap + k] = v[k];
+    }
+}
+
 int orc_search_by_projection(const orc_frame_view* F, int nmp, const uint8_t* mp_inview,
                              const float* mp_x, const float* mp_y, const int* mp_level,
                              const float* mp_viewcos, const float* mp_depth, const uint8_t* mp_desc,

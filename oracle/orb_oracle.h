@@ -101,6 +101,15 @@ typedef struct {
     int nlevels;
 } orc_frame_view;
 
+/* Frame::AssignFeaturesToGrid + PosInGrid (Frame.cc:157-176, 470-480) as a CSR over the cells
+ * (linear index y*cols + x, push_back order inside a cell); cell_idx has F->n entries, the unused
+ * tail (keypoints outside the grid) is -1. */
+void orc_assign_features_to_grid(const orc_frame_view* F, int* cell_off, int* cell_idx);
+/* Frame::GetFeaturesInArea (Frame.cc:404-468) for nq queries: out_count[q] = vIndices.size(),
+ * out_idx[q][0..min(count,cap)) = vIndices in the reference's order. */
+void orc_features_in_area(const orc_frame_view* F, int nq, const float* x, const float* y, const float* r,
+                          const int* minLevel, const int* maxLevel, int* out_count, int* out_idx, int cap);
+
 /* SearchByProjection(Frame, MapPoints, th, ...) ORBmatcher.cc:31-123.
  * Map points are flattened: in-view flag, projected x,y, predicted level,
  * view cos, descriptor. `claimed[i]!=0` marks frame keypoints that already

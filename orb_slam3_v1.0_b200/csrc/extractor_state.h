@@ -69,6 +69,10 @@ struct orbx_extractor {
     int nunits = 0;
     int fast_cl_cap = 1024;         /* FAST corner-list entries in use (<= FAST_CL) */
     void* d_units = nullptr;        /* FAST units (extractor.cu: struct Unit) */
+    /* device-side Frame grid of the last batch (matcher.cu: orbx_extractor_assign_grid) */
+    int *d_grid_off = nullptr, *d_grid_idx = nullptr;
+    void *d_grid_probs = nullptr, *h_grid_probs = nullptr;
+    int grid_cells = 0, grid_cells_cap = 0;
     void* d_odmaps = nullptr;       /* TMA tensor maps of the describe stage (extractor.cu: struct ODMaps) */
     cudaStream_t stream = nullptr;
     /* device buffers */

@@ -23,6 +23,7 @@
 #include <vector>
 
 #include "orbx_internal.h"
+#include "extractor_state.h"
 
 #define TH_LOW 30          /* include/ORBmatcher.h:73-75 */
 #define TH_HIGH 100
@@ -948,5 +949,273 @@ extern "C" orbx_status orbx_knn2(orbx_matcher* m, const uint8_t* q, int nq, cons
     if (d2) memcpy(d2, m->h_out + 2 * ob, (size_t)nq * 4);
     if (i2) memcpy(i2, m->h_out + 3 * ob, (size_t)nq * 4);
     if (pass) memcpy(pass, m->h_out + 4 * ob, (size_t)nq);
+    return ORBX_OK;
+}
+
+/* ================================================================== Frame grid */
+/* Frame::AssignFeaturesToGrid + PosInGrid (reference src/Frame.cc:157-176, 470-480) and
+ * Frame::GetFeaturesInArea (:404-468) as batched device functions.  The grid is a CSR over the
+ * cells in the reference's linear order (lin = y * cols + x); inside a cell the keypoints keep
+ * their push_back order (= ascending keypoint index). */
+struct GridProb {
+    int n, gcols, grows, pad;
+    float minx, miny, gw_inv, gh_inv;
+    const uint8_t* kx; const uint8_t* ky;     /* first x / y; consecutive keypoints `stride` bytes apart */
+    int stride, pad2;
+    const int* n_dev;                         /* if set: keypoint count read on the device */
+    int* cell_off;                            /* [gcols*grows + 1] */
+    int* cell_idx;                            /* [n] */
+};
+
+__global__ void __launch_bounds__(MT) k_assign_grid(const GridProb* __restrict__ probs) {
+    extern __shared__ uint32_t gsm[];        /* [ncell + 1] offsets, [ncell] fill */
+    __shared__ uint32_t s_tmp[MT / 32 + 1];
+    GridProb P = probs[blockIdx.x];
+    if (P.n_dev) P.n = *P.n_dev;
+    const int tid = threadIdx.x, ncell = P.gcols * P.grows;
+    uint32_t* off = gsm;
+    uint32_t* fill = gsm + ncell + 1;
+    for (int i = tid; i <= ncell; i += MT) off[i] = 0;
+    __syncthreads();
+    auto lin_of = [&](int i) {
+        const float x = *reinterpret_cast<const float*>(P.kx + (size_t)i * P.stride);
+        const float y = *reinterpret_cast<const float*>(P.ky + (size_t)i * P.stride);
+        /* PosInGrid: round() of a float expression = roundf; only the LINEAR index is range-checked */
+        const int px = (int)roundf(__fmul_rn(__fsub_rn(x, P.minx), P.gw_inv));
+        const int py = (int)roundf(__fmul_rn(__fsub_rn(y, P.miny), P.gh_inv));
+        return py * P.gcols + px;
+    };
+    for (int i = tid; i < P.n; i += MT) {
+        const int lin = lin_of(i);
+        if (lin >= 0 && lin < ncell) atomicAdd(&off[lin], 1u);
+    }
+    __syncthreads();
+    mt_excl_scan(off, ncell + 1, s_tmp);
+    for (int i = tid; i < ncell; i += MT) fill[i] = off[i];
+    __syncthreads();
+    for (int i = tid; i < P.n; i += MT) {
+        const int lin = lin_of(i);
+        if (lin >= 0 && lin < ncell) P.cell_idx[atomicAdd(&fill[lin], 1u)] = i;
+    }
+    __syncthreads();
+    /* restore push_back order inside each (short) cell list */
+    for (int c = tid; c < ncell; c += MT) {
+        const int a = (int)off[c], b = (int)off[c + 1];
+        for (int i = a + 1; i < b; ++i) {
+            const int v = P.cell_idx[i];
+            int j = i - 1;
+            while (j >= a && P.cell_idx[j] > v) { P.cell_idx[j + 1] = P.cell_idx[j]; --j; }
+            P.cell_idx[j + 1] = v;
+        }
+    }
+    for (int i = tid; i <= ncell; i += MT) P.cell_off[i] = (int)off[i];
+    /* keypoints that fell outside the grid leave the tail of cell_idx unused */
+    for (int i = (int)off[ncell] + tid; i < P.n; i += MT) P.cell_idx[i] = -1;
+}
+
+struct AreaProb {
+    int n, gcols, grows, nq;
+    float minx, miny, gw_inv, gh_inv;
+    const float* kx; const float* ky; const int* koct;
+    const int* cell_off; const int* cell_idx;
+    const float* qx; const float* qy; const float* qr;
+    const int* qmin; const int* qmax;
+    int* out_count; int* out_idx;             /* [nq], [nq][cap] */
+    int cap, pad;
+};
+
+/* one warp per query; cells in the reference's order (ix outer, iy inner), entries in list order */
+__global__ void __launch_bounds__(256) k_features_in_area(AreaProb P) {
+    const int q = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (q >= P.nq) return;
+    const float x = P.qx[q], y = P.qy[q], r = P.qr[q];
+    const int minLevel = P.qmin[q], maxLevel = P.qmax[q];
+    int count = 0;
+    const int nMinCellX = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(x, P.minx), r), P.gw_inv)));
+    const int nMaxCellX = min(P.gcols - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(x, P.minx), r), P.gw_inv)));
+    const int nMinCellY = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(y, P.miny), r), P.gh_inv)));
+    const int nMaxCellY = min(P.grows - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, P.miny), r), P.gh_inv)));
+    if (nMinCellX < P.gcols && nMaxCellX >= 0 && nMinCellY < P.grows && nMaxCellY >= 0) {
+        const bool bCheckLevels = (minLevel > 0) || (maxLevel >= 0);
+        int* out = P.out_idx + (size_t)q * P.cap;
+        for (int ix = nMinCellX; ix <= nMaxCellX; ++ix)
+            for (int iy = nMinCellY; iy <= nMaxCellY; ++iy) {
+                const int a = P.cell_off[iy * P.gcols + ix], b = P.cell_off[iy * P.gcols + ix + 1];
+                for (int base = a; base < b; base += 32) {
+                    const int j = base + lane;
+                    bool ok = false;
+                    int idx = -1;
+                    if (j < b) {
+                        idx = P.cell_idx[j];
+                        const int oct = P.koct[idx];
+                        ok = !(bCheckLevels && (oct < minLevel || (maxLevel >= 0 && oct > maxLevel)));
+                        const float distx = __fsub_rn(P.kx[idx], x), disty = __fsub_rn(P.ky[idx], y);
+                        ok = ok && fabsf(distx) < r && fabsf(disty) < r;
+                    }
+                    const unsigned bal = __ballot_sync(0xffffffffu, ok);
+                    const int pos = count + __popc(bal & ((1u << lane) - 1u));
+                    if (ok && pos < P.cap) out[pos] = idx;
+                    count += __popc(bal);
+                }
+            }
+    }
+    if (lane == 0) P.out_count[q] = count;
+}
+
+static orbx_status grid_check(const orbx_frame_view& f, int p) {
+    if (f.n < 0 || f.gcols < 1 || f.grows < 1 || (long long)f.gcols * f.grows > 20000 || (f.n > 0 && (!f.kx || !f.ky))) {
+        orbx_set_error("frame %d: unsupported frame view (gcols*grows <= 20000, non-null kx/ky)", p);
+        return ORBX_ERR_INVALID;
+    }
+    return ORBX_OK;
+}
+
+extern "C" orbx_status orbx_assign_features_to_grid(orbx_matcher* m, int nframes, const orbx_frame_view* F,
+                                                    int* const* cell_off, int* const* cell_idx) {
+    if (!m || nframes < 0 || (nframes > 0 && (!F || !cell_off || !cell_idx))) { orbx_set_error("null argument"); return ORBX_ERR_INVALID; }
+    if (nframes == 0) return ORBX_OK;
+    ORBX_CUDA(cudaSetDevice(m->device));
+    Packer in, out;
+    std::vector<GridProb> probs(nframes);
+    std::vector<size_t> o_off(nframes), o_idx(nframes), i_x(nframes), i_y(nframes);
+    size_t smem = 0;
+    for (int p = 0; p < nframes; ++p) {
+        const orbx_frame_view& f = F[p];
+        const orbx_status st = grid_check(f, p);
+        if (st != ORBX_OK) return st;
+        i_x[p] = in.add(f.kx, 4 * (size_t)f.n); i_y[p] = in.add(f.ky, 4 * (size_t)f.n);
+        const size_t ncell = (size_t)f.gcols * f.grows;
+        o_off[p] = out.add(nullptr, 4 * (ncell + 1)); o_idx[p] = out.add(nullptr, 4 * (size_t)std::max(f.n, 1));
+        smem = std::max(smem, 4 * (2 * ncell + 1));
+    }
+    const size_t probs_off = in.add(nullptr, sizeof(GridProb) * (size_t)nframes);
+    orbx_status st = ensure_io(m, in.total, out.total);
+    if (st != ORBX_OK) return st;
+    for (int p = 0; p < nframes; ++p) {
+        const orbx_frame_view& f = F[p];
+        GridProb& P = probs[p];
+        memset(&P, 0, sizeof(P));
+        P.n = f.n; P.gcols = f.gcols; P.grows = f.grows; P.minx = f.minx; P.miny = f.miny; P.gw_inv = f.gw_inv; P.gh_inv = f.gh_inv;
+        P.kx = m->d_in + i_x[p]; P.ky = m->d_in + i_y[p]; P.stride = 4;
+        P.cell_off = reinterpret_cast<int*>(m->d_out + o_off[p]); P.cell_idx = reinterpret_cast<int*>(m->d_out + o_idx[p]);
+    }
+    in.copy_to(m->h_in);
+    memcpy(m->h_in + probs_off, probs.data(), sizeof(GridProb) * (size_t)nframes);
+    ORBX_CUDA(cudaMemcpyAsync(m->d_in, m->h_in, in.total, cudaMemcpyHostToDevice, m->stream));
+    ORBX_CUDA(cudaFuncSetAttribute(k_assign_grid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max(smem, (size_t)48 * 1024)));
+    k_assign_grid<<<nframes, MT, smem, m->stream>>>(reinterpret_cast<const GridProb*>(m->d_in + probs_off));
+    ORBX_CUDA(cudaGetLastError());
+    m->last_launches = 1;
+    ORBX_CUDA(cudaMemcpyAsync(m->h_out, m->d_out, out.total, cudaMemcpyDeviceToHost, m->stream));
+    ORBX_CUDA(cudaStreamSynchronize(m->stream));
+    for (int p = 0; p < nframes; ++p) {
+        memcpy(cell_off[p], m->h_out + o_off[p], 4 * ((size_t)F[p].gcols * F[p].grows + 1));
+        if (F[p].n > 0) memcpy(cell_idx[p], m->h_out + o_idx[p], 4 * (size_t)F[p].n);
+    }
+    return ORBX_OK;
+}
+
+extern "C" orbx_status orbx_features_in_area(orbx_matcher* m, const orbx_frame_view* F, int nq, const float* x, const float* y,
+                                             const float* r, const int* minLevel, const int* maxLevel, int* out_count,
+                                             int* out_idx, int cap) {
+    if (!m || !F || nq < 0 || cap < 1 || (nq > 0 && (!x || !y || !r || !minLevel || !maxLevel || !out_count || !out_idx))) {
+        orbx_set_error("null argument");
+        return ORBX_ERR_INVALID;
+    }
+    if (nq == 0) return ORBX_OK;
+    orbx_status st = grid_check(*F, 0);
+    if (st != ORBX_OK) return st;
+    if (F->n > 0 && !F->koct) { orbx_set_error("null koct"); return ORBX_ERR_INVALID; }
+    ORBX_CUDA(cudaSetDevice(m->device));
+    const size_t ncell = (size_t)F->gcols * F->grows;
+    Packer in, out;
+    const size_t ix = in.add(F->kx, 4 * (size_t)F->n), iy = in.add(F->ky, 4 * (size_t)F->n), io = in.add(F->koct, 4 * (size_t)F->n);
+    const size_t qx = in.add(x, 4 * (size_t)nq), qy = in.add(y, 4 * (size_t)nq), qr = in.add(r, 4 * (size_t)nq);
+    const size_t qa = in.add(minLevel, 4 * (size_t)nq), qb = in.add(maxLevel, 4 * (size_t)nq);
+    const size_t gp = in.add(nullptr, sizeof(GridProb));
+    const size_t oc = out.add(nullptr, 4 * (size_t)nq), oi = out.add(nullptr, 4 * (size_t)nq * cap);
+    const size_t go = out.add(nullptr, 4 * (ncell + 1)), gi = out.add(nullptr, 4 * (size_t)std::max(F->n, 1));
+    st = ensure_io(m, in.total, out.total);
+    if (st != ORBX_OK) return st;
+    GridProb G;
+    memset(&G, 0, sizeof(G));
+    G.n = F->n; G.gcols = F->gcols; G.grows = F->grows; G.minx = F->minx; G.miny = F->miny; G.gw_inv = F->gw_inv; G.gh_inv = F->gh_inv;
+    G.kx = m->d_in + ix; G.ky = m->d_in + iy; G.stride = 4;
+    G.cell_off = reinterpret_cast<int*>(m->d_out + go); G.cell_idx = reinterpret_cast<int*>(m->d_out + gi);
+    in.copy_to(m->h_in);
+    memcpy(m->h_in + gp, &G, sizeof(G));
+    ORBX_CUDA(cudaMemcpyAsync(m->d_in, m->h_in, in.total, cudaMemcpyHostToDevice, m->stream));
+    const size_t smem = 4 * (2 * ncell + 1);
+    ORBX_CUDA(cudaFuncSetAttribute(k_assign_grid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max(smem, (size_t)48 * 1024)));
+    k_assign_grid<<<1, MT, smem, m->stream>>>(reinterpret_cast<const GridProb*>(m->d_in + gp));
+    AreaProb A;
+    memset(&A, 0, sizeof(A));
+    A.n = F->n; A.gcols = F->gcols; A.grows = F->grows; A.nq = nq; A.minx = F->minx; A.miny = F->miny; A.gw_inv = F->gw_inv; A.gh_inv = F->gh_inv;
+    A.kx = reinterpret_cast<const float*>(m->d_in + ix); A.ky = reinterpret_cast<const float*>(m->d_in + iy);
+    A.koct = reinterpret_cast<const int*>(m->d_in + io);
+    A.cell_off = G.cell_off; A.cell_idx = G.cell_idx;
+    A.qx = reinterpret_cast<const float*>(m->d_in + qx); A.qy = reinterpret_cast<const float*>(m->d_in + qy);
+    A.qr = reinterpret_cast<const float*>(m->d_in + qr);
+    A.qmin = reinterpret_cast<const int*>(m->d_in + qa); A.qmax = reinterpret_cast<const int*>(m->d_in + qb);
+    A.out_count = reinterpret_cast<int*>(m->d_out + oc); A.out_idx = reinterpret_cast<int*>(m->d_out + oi); A.cap = cap;
+    k_features_in_area<<<(nq + 7) / 8, 256, 0, m->stream>>>(A);
+    ORBX_CUDA(cudaGetLastError());
+    m->last_launches = 2;
+    ORBX_CUDA(cudaMemcpyAsync(m->h_out, m->d_out, oi + 4 * (size_t)nq * cap, cudaMemcpyDeviceToHost, m->stream));
+    ORBX_CUDA(cudaStreamSynchronize(m->stream));
+    memcpy(out_count, m->h_out + oc, 4 * (size_t)nq);
+    memcpy(out_idx, m->h_out + oi, 4 * (size_t)nq * cap);
+    return ORBX_OK;
+}
+
+/* Device-resident variant for the step right after extraction (Frame ctor: ExtractORB ->
+ * AssignFeaturesToGrid, reference src/Frame.cc:113-141): grids of all frames of the handle's last
+ * batch, built from its device keypoints on its stream (mvKeysUn == mvKeys, i.e. rectified or
+ * distortion-free input; distorted cameras go through orbx_assign_features_to_grid with mvKeysUn). */
+extern "C" orbx_status orbx_extractor_assign_grid(orbx_extractor* e, float minx, float miny, float gw_inv, float gh_inv,
+                                                  int gcols, int grows) {
+    if (!e || gcols < 1 || grows < 1 || (long long)gcols * grows > 20000) { orbx_set_error("invalid grid"); return ORBX_ERR_INVALID; }
+    if (e->last_batch < 1) { orbx_set_error("no extraction enqueued"); return ORBX_ERR_INVALID; }
+    ORBX_CUDA(cudaSetDevice(e->P.device));
+    const int B = e->P.max_batch, ncell = gcols * grows;
+    if (ncell > e->grid_cells_cap) {
+        if (e->d_grid_off) cudaFree(e->d_grid_off);
+        e->d_grid_off = nullptr; e->grid_cells_cap = 0;
+        ORBX_CUDA(cudaMalloc(&e->d_grid_off, (size_t)B * (ncell + 1) * 4));
+        e->grid_cells_cap = ncell;
+    }
+    if (!e->d_grid_idx) ORBX_CUDA(cudaMalloc(&e->d_grid_idx, (size_t)B * e->kcap * 4));
+    if (!e->d_grid_probs) {
+        ORBX_CUDA(cudaMalloc(&e->d_grid_probs, sizeof(GridProb) * (size_t)B));
+        ORBX_CUDA(cudaMallocHost(&e->h_grid_probs, sizeof(GridProb) * (size_t)B));
+    }
+    e->grid_cells = ncell;
+    GridProb* hp = static_cast<GridProb*>(e->h_grid_probs);
+    for (int f = 0; f < e->last_batch; ++f) {
+        GridProb& P = hp[f];
+        memset(&P, 0, sizeof(P));
+        P.gcols = gcols; P.grows = grows; P.minx = minx; P.miny = miny; P.gw_inv = gw_inv; P.gh_inv = gh_inv;
+        const uint8_t* k0 = reinterpret_cast<const uint8_t*>(e->d_kps + (size_t)f * e->kcap);
+        P.kx = k0; P.ky = k0 + 4; P.stride = (int)sizeof(orbx_keypoint);
+        P.n_dev = e->d_nk + f;
+        P.cell_off = e->d_grid_off + (size_t)f * (ncell + 1);
+        P.cell_idx = e->d_grid_idx + (size_t)f * e->kcap;
+    }
+    ORBX_CUDA(cudaMemcpyAsync(e->d_grid_probs, hp, sizeof(GridProb) * (size_t)e->last_batch, cudaMemcpyHostToDevice, e->stream));
+    const size_t smem = 4 * (2 * (size_t)ncell + 1);
+    ORBX_CUDA(cudaFuncSetAttribute(k_assign_grid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max(smem, (size_t)48 * 1024)));
+    k_assign_grid<<<e->last_batch, MT, smem, e->stream>>>(static_cast<const GridProb*>(e->d_grid_probs));
+    ORBX_CUDA(cudaGetLastError());
+    return ORBX_OK;
+}
+
+extern "C" orbx_status orbx_extractor_grid_fetch(orbx_extractor* e, int f, int* cell_off, int* cell_idx, int idx_cap) {
+    if (!e || f < 0 || f >= e->last_batch || !e->d_grid_off || !cell_off || !cell_idx || idx_cap < 0) { orbx_set_error("invalid argument"); return ORBX_ERR_INVALID; }
+    ORBX_CUDA(cudaSetDevice(e->P.device));
+    ORBX_CUDA(cudaMemcpyAsync(cell_off, e->d_grid_off + (size_t)f * (e->grid_cells + 1), 4 * (size_t)(e->grid_cells + 1),
+                              cudaMemcpyDeviceToHost, e->stream));
+    ORBX_CUDA(cudaMemcpyAsync(cell_idx, e->d_grid_idx + (size_t)f * e->kcap, 4 * (size_t)std::min(idx_cap, e->kcap),
+                              cudaMemcpyDeviceToHost, e->stream));
+    ORBX_CUDA(cudaStreamSynchronize(e->stream));
     return ORBX_OK;
 }

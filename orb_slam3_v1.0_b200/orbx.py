@@ -64,6 +64,10 @@ def lib():
         L.orbx_extractor_last_launches.argtypes = [C.c_void_p]
         L.orbx_extractor_set_profiling.argtypes = [C.c_void_p, C.c_int]
         L.orbx_extractor_set_fast_corner_list.argtypes = [C.c_void_p, C.c_int]
+        L.orbx_extractor_assign_grid.argtypes = [C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, C.c_int]
+        L.orbx_extractor_grid_fetch.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int]
+        L.orbx_assign_features_to_grid.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orbx_features_in_area.argtypes = [C.c_void_p, C.c_void_p, C.c_int] + [C.c_void_p] * 7 + [C.c_int]
         L.orbx_extractor_stage_ms.argtypes = [C.c_void_p, C.c_void_p]
         L.orbx_host_alloc.argtypes = [C.POINTER(C.c_void_p), C.c_size_t]
         L.orbx_host_free.argtypes = [C.c_void_p]
@@ -262,6 +266,18 @@ class ORBextractor:
     def set_profiling(self, on=True):
         _ck(lib().orbx_extractor_set_profiling(self._h, int(on)))
 
+    def assign_grid(self, minx, miny, gw_inv, gh_inv, gcols, grows):
+        """Device-side Frame::AssignFeaturesToGrid for every frame of the last batch (enqueued)."""
+        _ck(lib().orbx_extractor_assign_grid(self._h, C.c_float(minx), C.c_float(miny), C.c_float(gw_inv), C.c_float(gh_inv),
+                                             int(gcols), int(grows)))
+        self._grid_cells = int(gcols) * int(grows)
+
+    def grid_fetch(self, f, n):
+        off = np.empty(self._grid_cells + 1, np.int32)
+        idx = np.empty(max(n, 1), np.int32)
+        _ck(lib().orbx_extractor_grid_fetch(self._h, int(f), _p(off), _p(idx), int(n)))
+        return off, idx[:n]
+
     def set_fast_corner_list(self, entries):
         _ck(lib().orbx_extractor_set_fast_corner_list(self._h, int(entries)))
 
@@ -395,6 +411,33 @@ class ORBmatcher:
     @staticmethod
     def DescriptorDistance(a, b):
         return int(hamming_pairs(np.asarray(a, np.uint8).reshape(1, 32), np.asarray(b, np.uint8).reshape(1, 32))[0])
+
+    def AssignFeaturesToGrid(self, Fs):
+        """Frame::AssignFeaturesToGrid for a list of frame views -> [(cell_off, cell_idx)]."""
+        single = isinstance(Fs, dict)
+        Fs = [Fs] if single else list(Fs)
+        keep = []
+        fv = (_FrameView * len(Fs))(*[_frame_view(f, keep) for f in Fs])
+        offs = [np.empty(f["gcols"] * f["grows"] + 1, np.int32) for f in Fs]
+        idxs = [np.empty(max(len(f["kx"]), 1), np.int32) for f in Fs]
+        po = (C.c_void_p * len(Fs))(*[o.ctypes.data for o in offs])
+        pi = (C.c_void_p * len(Fs))(*[i.ctypes.data for i in idxs])
+        _ck(lib().orbx_assign_features_to_grid(self._h, len(Fs), fv, po, pi))
+        out = [(o, i[:len(f["kx"])]) for o, i, f in zip(offs, idxs, Fs)]
+        return out[0] if single else out
+
+    def GetFeaturesInArea(self, F, x, y, r, minLevel, maxLevel, cap=256):
+        """Frame::GetFeaturesInArea for arrays of queries -> (counts, indices[nq, cap])."""
+        keep = []
+        fv = _frame_view(F, keep)
+        x, y, r = (np.ascontiguousarray(v, np.float32) for v in (x, y, r))
+        a, b = (np.ascontiguousarray(v, np.int32) for v in (minLevel, maxLevel))
+        cnt = np.empty(len(x), np.int32)
+        idx = np.full((len(x), cap), -1, np.int32)
+        _ck(lib().orbx_features_in_area(self._h, C.byref(fv), len(x), _p(x), _p(y), _p(r), _p(a), _p(b), _p(cnt), _p(idx), cap))
+        for q in range(len(x)):
+            idx[q, min(cnt[q], cap):] = -1
+        return cnt, idx
 
     def SearchByProjection(self, F, MP, th, bFarPoints=False, thFarPoints=0.0, nnRatio=0.8, claimed=None):
         """SearchByProjection(Frame, vpMapPoints, th, bFarPoints, thFarPoints, nnRatio, ...)

@@ -203,3 +203,56 @@ def test_stereo_matches_batch(pkg, oracle, synth):
         our, odp = oracle.stereo_matches(kL, dL, lvL, kR, dR, lvR, ex.mvScaleFactor, ex.mvInvScaleFactor, 40.0, 0.1)
         assert np.array_equal(ur[p, :len(kL)], our) and np.array_equal(dp[p, :len(kL)], odp)
     ex.close()
+
+
+# ------------------------------------------------------------------ Frame grid
+@pytest.mark.parametrize("n,seed", [(1000, 51), (37, 52), (0, 53), (3000, 54)])
+def test_assign_features_to_grid(matcher, oracle, synth, n, seed):
+    F = synth.frame_view(n, seed=seed)
+    if n >= 5:
+        F["kx"][:5] = [-3.0, 751.9, 760.0, 0.2, 375.5]      # the fork range-checks only the LINEAR cell index
+    off, idx = matcher.AssignFeaturesToGrid(F)
+    o_off, o_idx = oracle.assign_features_to_grid(F)
+    assert np.array_equal(off, o_off) and np.array_equal(idx, o_idx)
+
+
+def test_assign_features_to_grid_batched(matcher, oracle, synth):
+    Fs = [synth.frame_view(200 + 97 * i, seed=60 + i, gcols=32 + 8 * (i % 3), grows=24 + 4 * (i % 2)) for i in range(9)]
+    for (off, idx), F in zip(matcher.AssignFeaturesToGrid(Fs), Fs):
+        o_off, o_idx = oracle.assign_features_to_grid(F)
+        assert np.array_equal(off, o_off) and np.array_equal(idx, o_idx)
+
+
+def test_get_features_in_area(matcher, oracle, synth):
+    F = synth.frame_view(1500, seed=71)
+    rng = np.random.default_rng(72)
+    nq = 500
+    x = rng.uniform(-30, 790, nq).astype(np.float32); y = rng.uniform(-30, 510, nq).astype(np.float32)
+    r = rng.uniform(1, 60, nq).astype(np.float32)
+    lo = rng.integers(-1, 6, nq).astype(np.int32)
+    hi = np.where(rng.random(nq) < 0.3, -1, lo + rng.integers(0, 3, nq)).astype(np.int32)
+    cnt, idx = matcher.GetFeaturesInArea(F, x, y, r, lo, hi, cap=128)
+    o_cnt, o_idx = oracle.features_in_area(F, x, y, r, lo, hi, cap=128)
+    assert np.array_equal(cnt, o_cnt) and cnt.max() > 20
+    assert np.array_equal(idx, o_idx)          # same candidates in the same (cell, push_back) order
+
+
+def test_extractor_device_grid(pkg, matcher, oracle, synth):
+    """Grid built on the device from the extractor's resident keypoints == oracle grid of the fetched keypoints."""
+    W, H, B = 640, 400, 3
+    frames = synth.frame_batch(B, W, H, seed=77, distinct=B)
+    ex = pkg.orbx.ORBextractor(800, 1.2, 6, 20, 7, max_batch=B).prepare(W, H, B)
+    ex.extract_host(frames)
+    gcols, grows = 64, 48
+    gw_inv, gh_inv = float(np.float32(gcols) / np.float32(W)), float(np.float32(grows) / np.float32(H))
+    ex.assign_grid(0.0, 0.0, gw_inv, gh_inv, gcols, grows)
+    ex.sync()
+    for f in range(B):
+        kps, _, _ = ex.fetch(f)
+        F = {"kx": kps["x"].copy(), "ky": kps["y"].copy(), "koct": kps["octave"].astype(np.int32),
+             "desc": np.zeros((len(kps), 32), np.uint8), "minx": 0.0, "miny": 0.0, "gw_inv": gw_inv, "gh_inv": gh_inv,
+             "gcols": gcols, "grows": grows, "scale": np.ones(6, np.float32)}
+        off, idx = ex.grid_fetch(f, len(kps))
+        o_off, o_idx = oracle.assign_features_to_grid(F)
+        assert len(kps) > 300 and np.array_equal(off, o_off) and np.array_equal(idx, o_idx)
+    ex.close()

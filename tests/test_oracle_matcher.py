@@ -141,3 +141,53 @@ def test_stereo_matches_recover_known_disparity(oracle, synth):
     err = np.abs(disp - expect)[inside]
     assert inside.sum() > 50 and np.mean(err < 1.0 * sc[inside]) > 0.9
     assert np.all(ur[~m] == -1) and np.all(dp[~m] == -1)
+
+
+def _grid_numpy(F):
+    """Independent restatement of AssignFeaturesToGrid/PosInGrid (reference src/Frame.cc:157-176, 470-480)."""
+    ncell = F["gcols"] * F["grows"]
+    cells = [[] for _ in range(ncell)]
+    for i, (x, y) in enumerate(zip(F["kx"], F["ky"])):
+        # C round() on a float expression: half away from zero
+        fx = np.float32(np.float32(x - np.float32(F["minx"])) * np.float32(F["gw_inv"]))
+        fy = np.float32(np.float32(y - np.float32(F["miny"])) * np.float32(F["gh_inv"]))
+        px = int(np.sign(fx) * np.floor(abs(float(fx)) + 0.5)); py = int(np.sign(fy) * np.floor(abs(float(fy)) + 0.5))
+        lin = py * F["gcols"] + px
+        if 0 <= lin < ncell:
+            cells[lin].append(i)
+    return cells
+
+
+def test_frame_grid_vs_numpy(oracle, synth):
+    F = synth.frame_view(700, seed=41)
+    F["kx"][:5] = [-3.0, 751.9, 760.0, 0.2, 375.5]          # out-of-image x wraps into a neighbouring row's cell
+    off, idx = oracle.assign_features_to_grid(F)
+    cells = _grid_numpy(F)
+    assert off[-1] == sum(len(c) for c in cells)
+    for c, lst in enumerate(cells):
+        assert list(idx[off[c]:off[c + 1]]) == lst
+    # GetFeaturesInArea: brute-force window + level filter must give the same SET; order = cell order
+    rng = np.random.default_rng(3)
+    nq = 64
+    x = rng.uniform(-20, 780, nq).astype(np.float32); y = rng.uniform(-20, 500, nq).astype(np.float32)
+    r = rng.uniform(2, 40, nq).astype(np.float32)
+    lo = rng.integers(-1, 5, nq).astype(np.int32); hi = np.where(rng.random(nq) < 0.3, -1, lo + rng.integers(0, 3, nq)).astype(np.int32)
+    cnt, got = oracle.features_in_area(F, x, y, r, lo, hi, cap=700)
+    ingrid = set(int(i) for i in idx[:off[-1]])
+    for q in range(nq):
+        check = (lo[q] > 0) or (hi[q] >= 0)
+        want = set()
+        for i in ingrid:
+            if check and (F["koct"][i] < lo[q] or (hi[q] >= 0 and F["koct"][i] > hi[q])):
+                continue
+            if abs(np.float32(F["kx"][i] - x[q])) < r[q] and abs(np.float32(F["ky"][i] - y[q])) < r[q]:
+                # the reference only visits cells within the window's cell range
+                want.add(i)
+        g = set(int(v) for v in got[q, :cnt[q]])
+        assert g <= want
+        # a keypoint whose rounded cell lies inside the grid sits in a cell of the window's cell range
+        for i in want - g:
+            fx = np.float32(np.float32(F["kx"][i] - np.float32(F["minx"])) * np.float32(F["gw_inv"]))
+            fy = np.float32(np.float32(F["ky"][i] - np.float32(F["miny"])) * np.float32(F["gh_inv"]))
+            px, py = int(np.floor(abs(float(fx)) + 0.5) * np.sign(fx)), int(np.floor(abs(float(fy)) + 0.5) * np.sign(fy))
+            assert not (0 <= px < F["gcols"] and 0 <= py < F["grows"])
