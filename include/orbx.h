@@ -168,6 +168,13 @@ typedef struct {
     const uint8_t* desc;            /* GetDescriptor(), n x 32 */
 } orbx_mappoints;
 
+/* MapPoint::ComputeDistinctiveDescriptors   src/MapPoint.cc:343-412, batched over nsets map points:
+ * desc rows set_off[s] .. set_off[s+1] are the observation descriptors of map point s (set_off[0]
+ * = 0); best[s] = row (within the set) with the least median Hamming distance to the set, first
+ * on ties, -1 for an empty set; median (may be NULL) receives that median. */
+orbx_status orbx_distinctive_descriptors(orbx_matcher* m, int nsets, const int* set_off, const uint8_t* desc,
+                                         int* best, int* median);
+
 /* Frame::AssignFeaturesToGrid + PosInGrid   src/Frame.cc:157-176, 470-480, for nframes frames:
  * cell_off[p][gcols*grows + 1] / cell_idx[p][F[p].n] = CSR over the cells in the reference's linear
  * order (y*cols + x), keypoints in push_back order inside a cell; the unused tail of cell_idx

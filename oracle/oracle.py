@@ -191,6 +191,12 @@ def _frame_view(F, keep):
                       sc.ctypes.data, len(sc))
 
 
+def distinctive_descriptor(desc):
+    d = _u8(desc)
+    med = C.c_int()
+    return lib().orc_distinctive_descriptor(_p(d), len(d), C.byref(med)), med.value
+
+
 def assign_features_to_grid(F):
     keep = []
     fv = _frame_view(F, keep)

@@ -691,6 +691,29 @@ void features_in_area(const orc_frame_view* F, const std::vector<std::vector<int
 }
 } // namespace
 
+/* MapPoint::ComputeDistinctiveDescriptors, src/MapPoint.cc:343-412, for one descriptor set */
+int orc_distinctive_descriptor(const uint8_t* desc, int N, int* median_out) {
+    if (N <= 0) { if (median_out) *median_out = -1; return -1; }
+    std::vector<float> Distances((size_t)N * N);
+    for (int i = 0; i < N; i++) {
+        Distances[(size_t)i * N + i] = 0;
+        for (int j = i + 1; j < N; j++) {
+            const int distij = orc_descriptor_distance(desc + (size_t)i * 32, desc + (size_t)j * 32);
+            Distances[(size_t)i * N + j] = (float)distij;
+            Distances[(size_t)j * N + i] = (float)distij;
+        }
+    }
+    int BestMedian = INT_MAX, BestIdx = 0;
+    for (int i = 0; i < N; i++) {
+        std::vector<int> vDists(Distances.begin() + (size_t)i * N, Distances.begin() + (size_t)(i + 1) * N);
+        std::sort(vDists.begin(), vDists.end());
+        const int median = vDists[(size_t)(0.5 * (N - 1))];
+        if (median < BestMedian) { BestMedian = median; BestIdx = i; }
+    }
+    if (median_out) *median_out = BestMedian;
+    return BestIdx;
+}
+
 /* Frame::AssignFeaturesToGrid as CSR (cells in linear order, push_back order inside a cell) */
 void orc_assign_features_to_grid(const orc_frame_view* F, int* cell_off, int* cell_idx) {
     const std::vector<std::vector<int>> grid = build_grid(F);

@@ -101,6 +101,10 @@ typedef struct {
     int nlevels;
 } orc_frame_view;
 
+/* MapPoint::ComputeDistinctiveDescriptors (MapPoint.cc:343-412) on N observation descriptors:
+ * index of the descriptor with the least median distance to the rest (first on ties), -1 if N==0. */
+int orc_distinctive_descriptor(const uint8_t* desc, int N, int* median_out);
+
 /* Frame::AssignFeaturesToGrid + PosInGrid (Frame.cc:157-176, 470-480) as a CSR over the cells
  * (linear index y*cols + x, push_back order inside a cell); cell_idx has F->n entries, the unused
  * tail (keypoints outside the grid) is -1. */

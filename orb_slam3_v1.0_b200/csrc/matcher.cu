@@ -1219,3 +1219,72 @@ extern "C" orbx_status orbx_extractor_grid_fetch(orbx_extractor* e, int f, int* 
     ORBX_CUDA(cudaStreamSynchronize(e->stream));
     return ORBX_OK;
 }
+
+/* ================================================================== distinctive descriptors */
+/* MapPoint::ComputeDistinctiveDescriptors (reference src/MapPoint.cc:343-412), batched over map
+ * points: the observation descriptors of set s are rows set_off[s] .. set_off[s+1]; the result is
+ * the row whose MEDIAN Hamming distance to all rows of the set (itself included, distance 0;
+ * median = sorted[(int)(0.5*(N-1))]) is smallest, first row on ties.
+ * One CTA per set, descriptors staged in shared memory, one thread per row; the order statistic
+ * is found by bisection on the distance value (9 counting passes over the row), so no N x N
+ * matrix is stored. */
+#define DD_THREADS 128
+__global__ void __launch_bounds__(DD_THREADS) k_distinctive(const int* __restrict__ set_off, const uint4* __restrict__ desc,
+                                                            int* __restrict__ best, int* __restrict__ median, int max_rows) {
+    extern __shared__ uint4 s_desc[];            /* [min(N, max_rows)][2] */
+    __shared__ unsigned long long s_best;
+    const int s = blockIdx.x, tid = threadIdx.x;
+    const int a = set_off[s], N = set_off[s + 1] - a;
+    if (tid == 0) s_best = ~0ull;
+    const bool staged = N <= max_rows;
+    if (staged)
+        for (int i = tid; i < 2 * N; i += DD_THREADS) s_desc[i] = desc[2 * (size_t)a + i];
+    __syncthreads();
+    const uint4* D = staged ? s_desc : desc + 2 * (size_t)a;
+    const int k = (N - 1) / 2;                   /* (int)(0.5 * (N - 1)) */
+    for (int i = tid; i < N; i += DD_THREADS) {
+        const uint4 p0 = D[2 * i], p1 = D[2 * i + 1];
+        int lo = 0, hi = 256;                    /* smallest v with #{j: d(i,j) <= v} >= k + 1 */
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            int c = 0;
+            for (int j = 0; j < N; ++j) c += hamming256(p0, p1, D[2 * j], D[2 * j + 1]) <= mid;
+            if (c >= k + 1) hi = mid; else lo = mid + 1;
+        }
+        atomicMin(&s_best, ((unsigned long long)lo << 32) | (unsigned)i);
+    }
+    __syncthreads();
+    if (tid == 0) {
+        best[s] = N > 0 ? (int)(s_best & 0xFFFFFFFFull) : -1;
+        if (median) median[s] = N > 0 ? (int)(s_best >> 32) : -1;
+    }
+}
+
+extern "C" orbx_status orbx_distinctive_descriptors(orbx_matcher* m, int nsets, const int* set_off, const uint8_t* desc,
+                                                    int* best, int* median) {
+    if (!m || nsets < 0 || (nsets > 0 && (!set_off || !best))) { orbx_set_error("null argument"); return ORBX_ERR_INVALID; }
+    if (nsets == 0) return ORBX_OK;
+    const int total = set_off[nsets];
+    if (set_off[0] != 0 || total < 0 || (total > 0 && !desc)) { orbx_set_error("bad set offsets"); return ORBX_ERR_INVALID; }
+    for (int s = 0; s < nsets; ++s)
+        if (set_off[s + 1] < set_off[s]) { orbx_set_error("set offsets not ascending at %d", s); return ORBX_ERR_INVALID; }
+    ORBX_CUDA(cudaSetDevice(m->device));
+    Packer in, out;
+    const size_t io = in.add(set_off, 4 * (size_t)(nsets + 1)), id = in.add(desc, 32 * (size_t)total);
+    const size_t ob = out.add(nullptr, 4 * (size_t)nsets), om = out.add(nullptr, 4 * (size_t)nsets);
+    orbx_status st = ensure_io(m, in.total, out.total);
+    if (st != ORBX_OK) return st;
+    in.copy_to(m->h_in);
+    ORBX_CUDA(cudaMemcpyAsync(m->d_in, m->h_in, in.total, cudaMemcpyHostToDevice, m->stream));
+    const int max_rows = 1024;                   /* 32 KB of shared memory; larger sets read global memory */
+    k_distinctive<<<nsets, DD_THREADS, (size_t)max_rows * 32, m->stream>>>(
+        reinterpret_cast<const int*>(m->d_in + io), reinterpret_cast<const uint4*>(m->d_in + id),
+        reinterpret_cast<int*>(m->d_out + ob), reinterpret_cast<int*>(m->d_out + om), max_rows);
+    ORBX_CUDA(cudaGetLastError());
+    m->last_launches = 1;
+    ORBX_CUDA(cudaMemcpyAsync(m->h_out, m->d_out, out.total, cudaMemcpyDeviceToHost, m->stream));
+    ORBX_CUDA(cudaStreamSynchronize(m->stream));
+    memcpy(best, m->h_out + ob, 4 * (size_t)nsets);
+    if (median) memcpy(median, m->h_out + om, 4 * (size_t)nsets);
+    return ORBX_OK;
+}

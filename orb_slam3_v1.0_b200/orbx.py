@@ -66,6 +66,7 @@ def lib():
         L.orbx_extractor_set_fast_corner_list.argtypes = [C.c_void_p, C.c_int]
         L.orbx_extractor_assign_grid.argtypes = [C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, C.c_int]
         L.orbx_extractor_grid_fetch.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int]
+        L.orbx_distinctive_descriptors.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 4
         L.orbx_assign_features_to_grid.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orbx_features_in_area.argtypes = [C.c_void_p, C.c_void_p, C.c_int] + [C.c_void_p] * 7 + [C.c_int]
         L.orbx_extractor_stage_ms.argtypes = [C.c_void_p, C.c_void_p]
@@ -411,6 +412,17 @@ class ORBmatcher:
     @staticmethod
     def DescriptorDistance(a, b):
         return int(hamming_pairs(np.asarray(a, np.uint8).reshape(1, 32), np.asarray(b, np.uint8).reshape(1, 32))[0])
+
+    def ComputeDistinctiveDescriptors(self, sets):
+        """MapPoint::ComputeDistinctiveDescriptors for a list of (N_s, 32) u8 descriptor sets ->
+        (best row per set, its median distance)."""
+        off = np.zeros(len(sets) + 1, np.int32)
+        off[1:] = np.cumsum([len(d) for d in sets])
+        desc = np.ascontiguousarray(np.concatenate([np.asarray(d, np.uint8).reshape(-1, 32) for d in sets]) if len(sets)
+                                    else np.zeros((0, 32), np.uint8))
+        best = np.empty(len(sets), np.int32); med = np.empty(len(sets), np.int32)
+        _ck(lib().orbx_distinctive_descriptors(self._h, len(sets), _p(off), _p(desc), _p(best), _p(med)))
+        return best, med
 
     def AssignFeaturesToGrid(self, Fs):
         """Frame::AssignFeaturesToGrid for a list of frame views -> [(cell_off, cell_idx)]."""

@@ -256,3 +256,21 @@ def test_extractor_device_grid(pkg, matcher, oracle, synth):
         o_off, o_idx = oracle.assign_features_to_grid(F)
         assert len(kps) > 300 and np.array_equal(off, o_off) and np.array_equal(idx, o_idx)
     ex.close()
+
+
+# ------------------------------------------------------------------ distinctive descriptors
+def test_distinctive_descriptors(matcher, oracle, synth):
+    rng = np.random.default_rng(91)
+    sizes = [0, 1, 2, 3, 7, 33, 128, 129, 200, 1500] + list(rng.integers(2, 40, 60))
+    sets = []
+    for n in sizes:
+        base = rng.integers(0, 256, 32, dtype=np.uint8)
+        d = np.repeat(base[None], n, axis=0)
+        flips = rng.random((n, 256)) < rng.uniform(0.02, 0.3)
+        d = d ^ np.packbits(flips, axis=1)
+        if n > 4:
+            d[rng.integers(0, n)] = rng.integers(0, 256, 32, dtype=np.uint8)      # an outlier observation
+        sets.append(np.ascontiguousarray(d, np.uint8))
+    best, med = matcher.ComputeDistinctiveDescriptors(sets)
+    for s, d in enumerate(sets):
+        assert (int(best[s]), int(med[s])) == oracle.distinctive_descriptor(d), f"set {s} (N={len(d)})"

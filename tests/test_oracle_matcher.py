@@ -191,3 +191,21 @@ def test_frame_grid_vs_numpy(oracle, synth):
             fy = np.float32(np.float32(F["ky"][i] - np.float32(F["miny"])) * np.float32(F["gh_inv"]))
             px, py = int(np.floor(abs(float(fx)) + 0.5) * np.sign(fx)), int(np.floor(abs(float(fy)) + 0.5) * np.sign(fy))
             assert not (0 <= px < F["gcols"] and 0 <= py < F["grows"])
+
+
+def test_distinctive_descriptor_known_answers(oracle):
+    """MapPoint::ComputeDistinctiveDescriptors (reference src/MapPoint.cc:343-412)."""
+    z = np.zeros((1, 32), np.uint8)
+    assert oracle.distinctive_descriptor(z) == (0, 0)
+    assert oracle.distinctive_descriptor(np.zeros((0, 32), np.uint8))[0] == -1
+    # N = 2: median index (int)(0.5 * 1) = 0 -> the self distance 0 for both rows, the first wins
+    two = np.zeros((2, 32), np.uint8); two[1] = 255
+    assert oracle.distinctive_descriptor(two) == (0, 0)
+    # a tight cluster of 4 plus an outlier: the winner is in the cluster, and equals a numpy restatement
+    rng = np.random.default_rng(8)
+    base = rng.integers(0, 256, 32, dtype=np.uint8)
+    d = np.stack([base ^ np.uint8(1 << k) for k in range(4)] + [rng.integers(0, 256, 32, dtype=np.uint8)])
+    best, med = oracle.distinctive_descriptor(d)
+    D = np.unpackbits(d[:, None, :] ^ d[None, :, :], axis=2).sum(2)
+    meds = np.sort(D, axis=1)[:, int(0.5 * (len(d) - 1))]
+    assert best == int(np.argmin(meds)) and med == int(meds.min()) and best < 4
