@@ -259,6 +259,14 @@ def _kf_view(K, keep):
                    len(a[6]), a[6].ctypes.data, a[7].ctypes.data, a[8].ctypes.data)
 
 
+def search_by_bow(KF, F, nnRatio=0.7, checkOrientation=True, nleft=-1):
+    keep = []
+    a, b = _kf_view(KF, keep), _kf_view(F, keep)
+    out = np.empty(max(b.n, 1), np.int32)
+    n = lib().orc_search_by_bow(C.byref(a), C.byref(b), int(nleft), C.c_float(nnRatio), int(checkOrientation), _p(out))
+    return n, out[:b.n]
+
+
 def search_for_triangulation(K1, K2, F12, ep, scale2, bOnlyStereo=False, bCoarse=False, checkOrientation=True):
     keep = []
     v1, v2 = _kf_view(K1, keep), _kf_view(K2, keep)

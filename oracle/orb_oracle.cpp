@@ -837,6 +837,81 @@ int orc_search_by_projection_kf(const orc_frame_view* F, const float* fangle, in
     return nmatches;
 }
 
+int orc_search_by_bow(const orc_kf_view* KF, const orc_kf_view* F, int Nleft, float nnRatio,
+                      int checkOrientation, int* match_kf) {
+    /* src/ORBmatcher.cc:133-327.  match_kf[i] = KeyFrame keypoint whose MapPoint lands in
+     * vpMapPointMatches[i], or -1; KF->has_mp[i] = (pMP && !pMP->isBad()). */
+    for (int i = 0; i < F->n; ++i) match_kf[i] = -1;
+    int nmatches = 0;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = 1.0f / HISTO_LENGTH;
+    int KFit = 0, Fit = 0;
+    while (KFit < KF->nnodes && Fit < F->nnodes) {
+        if (KF->node_id[KFit] == F->node_id[Fit]) {
+            for (int iKF = KF->node_off[KFit]; iKF < KF->node_off[KFit + 1]; iKF++) {
+                const int realIdxKF = KF->node_idx[iKF];
+                if (!KF->has_mp[realIdxKF]) continue;
+                const uint8_t* dKF = KF->desc + (size_t)realIdxKF * 32;
+                int bestDist1 = 256, bestIdxF = -1, bestDist2 = 256;
+                int bestDist1R = 256, bestIdxFR = -1, bestDist2R = 256;
+                for (int iF = F->node_off[Fit]; iF < F->node_off[Fit + 1]; iF++) {
+                    const int realIdxF = F->node_idx[iF];
+                    if (match_kf[realIdxF] >= 0) continue;
+                    const int dist = orc_descriptor_distance(dKF, F->desc + (size_t)realIdxF * 32);
+                    if (Nleft == -1) {
+                        if (dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdxF = realIdxF; }
+                        else if (dist < bestDist2) bestDist2 = dist;
+                    } else {
+                        if (realIdxF < Nleft && dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdxF = realIdxF; }
+                        else if (realIdxF < Nleft && dist < bestDist2) bestDist2 = dist;
+                        if (realIdxF >= Nleft && dist < bestDist1R) { bestDist2R = bestDist1R; bestDist1R = dist; bestIdxFR = realIdxF; }
+                        else if (realIdxF >= Nleft && dist < bestDist2R) bestDist2R = dist;
+                    }
+                }
+                if (bestDist1 <= TH_LOW) {
+                    if ((float)bestDist1 < nnRatio * (float)bestDist2) {
+                        match_kf[bestIdxF] = realIdxKF;
+                        if (checkOrientation) {
+                            float rot = KF->kangle[realIdxKF] - F->kangle[bestIdxF];
+                            if (rot < 0.0) rot += 360.0f;
+                            int bin = (int)roundf(rot * factor);
+                            if (bin == HISTO_LENGTH) bin = 0;
+                            rotHist[bin].push_back(bestIdxF);
+                        }
+                        nmatches++;
+                    }
+                    if (bestDist1R <= TH_LOW) {
+                        match_kf[bestIdxFR] = realIdxKF;         /* ratio test is `|| true` in the fork */
+                        if (checkOrientation) {
+                            float rot = KF->kangle[realIdxKF] - F->kangle[bestIdxFR];
+                            if (rot < 0.0) rot += 360.0f;
+                            int bin = (int)roundf(rot * factor);
+                            if (bin == HISTO_LENGTH) bin = 0;
+                            rotHist[bin].push_back(bestIdxFR);
+                        }
+                        nmatches++;
+                    }
+                }
+            }
+            KFit++; Fit++;
+        } else if (KF->node_id[KFit] < F->node_id[Fit]) {
+            while (KFit < KF->nnodes && KF->node_id[KFit] < F->node_id[Fit]) KFit++;   /* lower_bound */
+        } else {
+            while (Fit < F->nnodes && F->node_id[Fit] < KF->node_id[KFit]) Fit++;
+        }
+    }
+    if (checkOrientation) {
+        int counts[HISTO_LENGTH], ind1, ind2, ind3;
+        for (int i = 0; i < HISTO_LENGTH; i++) counts[i] = (int)rotHist[i].size();
+        orc_three_maxima(counts, HISTO_LENGTH, &ind1, &ind2, &ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (size_t j = 0; j < rotHist[i].size(); j++) { match_kf[rotHist[i][j]] = -1; nmatches--; }
+        }
+    }
+    return nmatches;
+}
+
 int orc_search_for_triangulation(const orc_kf_view* k1, const orc_kf_view* k2, const float* F12,
                                  float epx, float epy, const float* scale2, int bOnlyStereo,
                                  int bCoarse, int checkOrientation, int* pairs, int* npairs) {

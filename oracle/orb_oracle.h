@@ -147,6 +147,12 @@ typedef struct {
     const float* uright;         /* may be NULL */
     int nnodes; const int* node_id; const int* node_off; const int* node_idx;
 } orc_kf_view;
+/* SearchByBoW(KeyFrame, Frame, ...) ORBmatcher.cc:133-327: F is flattened like a keyframe (angles,
+ * descriptors, feature vector); match_kf[i] (F->n entries) = KeyFrame keypoint whose MapPoint goes
+ * to Frame keypoint i, or -1.  Nleft = F->Nleft (-1: one camera). */
+int orc_search_by_bow(const orc_kf_view* KF, const orc_kf_view* F, int Nleft, float nnRatio,
+                      int checkOrientation, int* match_kf);
+
 int orc_search_for_triangulation(const orc_kf_view* k1, const orc_kf_view* k2,
                                  const float* F12, float epx, float epy,
                                  const float* scale2 /* pKF2->mvScaleFactors */,

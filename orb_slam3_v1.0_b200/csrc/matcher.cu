@@ -1288,3 +1288,149 @@ extern "C" orbx_status orbx_distinctive_descriptors(orbx_matcher* m, int nsets, 
     if (median) memcpy(median, m->h_out + om, 4 * (size_t)nsets);
     return ORBX_OK;
 }
+
+/* ================================================================== SearchByBoW */
+/* ORBmatcher::SearchByBoW(KeyFrame, Frame, vpMapPointMatches, nnRatio, checkOrientation),
+ * reference src/ORBmatcher.cc:133-327.  A feature index sits under exactly one vocabulary node, so
+ * the reference's sequential "first KeyFrame point claims the Frame keypoint" rule only couples
+ * points of the same node: one thread walks one shared node in the reference's order (exact), the
+ * nodes of a problem run in parallel, one CTA per (KeyFrame, Frame) problem.  Includes the fork's
+ * right-camera branch (Nleft != -1), whose acceptance is nested under the left test (:238-283). */
+struct BowProb {
+    int nF, ntasks, nleft, checkOri;
+    float nnRatio, pad0, pad1, pad2;
+    unsigned long long hasmpK, kangK, descK, nidxK;
+    unsigned long long kangF, descF, nidxF;
+    unsigned long long tasks;           /* int4 {offK, lenK, offF, lenF} per shared node */
+    unsigned long long out_match;       /* [nF] KeyFrame keypoint index or -1 */
+};
+
+__global__ void __launch_bounds__(MT) k_search_by_bow(const uint8_t* __restrict__ in, uint8_t* __restrict__ out,
+                                                       const BowProb* __restrict__ probs, int* __restrict__ counts) {
+    __shared__ int s_hist[HISTO_LENGTH];
+    __shared__ int s_ind[3];
+    __shared__ int s_count;
+    const BowProb P = probs[blockIdx.x];
+    const int tid = threadIdx.x;
+    const uint8_t* hasmpK = in + P.hasmpK;
+    const float* kangK = reinterpret_cast<const float*>(in + P.kangK);
+    const uint4* descK = reinterpret_cast<const uint4*>(in + P.descK);
+    const int* nidxK = reinterpret_cast<const int*>(in + P.nidxK);
+    const float* kangF = reinterpret_cast<const float*>(in + P.kangF);
+    const uint4* descF = reinterpret_cast<const uint4*>(in + P.descF);
+    const int* nidxF = reinterpret_cast<const int*>(in + P.nidxF);
+    const int4* tasks = reinterpret_cast<const int4*>(in + P.tasks);
+    int* match = reinterpret_cast<int*>(out + P.out_match);
+    if (tid < HISTO_LENGTH) s_hist[tid] = 0;
+    if (tid == 0) s_count = 0;
+    for (int i = tid; i < P.nF; i += MT) match[i] = -1;
+    __syncthreads();
+    int mycount = 0;
+    for (int t = tid; t < P.ntasks; t += MT) {
+        const int4 T = tasks[t];
+        for (int a = 0; a < T.y; ++a) {
+            const int realIdxKF = nidxK[T.x + a];
+            if (!hasmpK[realIdxKF]) continue;                      /* !pMP || pMP->isBad() */
+            const uint4 q0 = descK[2 * realIdxKF], q1 = descK[2 * realIdxKF + 1];
+            int bestDist1 = 256, bestIdxF = -1, bestDist2 = 256;
+            int bestDist1R = 256, bestIdxFR = -1, bestDist2R = 256;
+            for (int b = 0; b < T.w; ++b) {
+                const int realIdxF = nidxF[T.z + b];
+                if (match[realIdxF] >= 0) continue;                /* vpMapPointMatches[realIdxF] */
+                const int dist = hamming256(q0, q1, descF[2 * realIdxF], descF[2 * realIdxF + 1]);
+                if (P.nleft == -1 || realIdxF < P.nleft) {
+                    if (dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdxF = realIdxF; }
+                    else if (dist < bestDist2) bestDist2 = dist;
+                } else {
+                    if (dist < bestDist1R) { bestDist2R = bestDist1R; bestDist1R = dist; bestIdxFR = realIdxF; }
+                    else if (dist < bestDist2R) bestDist2R = dist;
+                }
+            }
+            if (bestDist1 <= TH_LOW) {
+                if ((float)bestDist1 < P.nnRatio * (float)bestDist2) {
+                    match[bestIdxF] = realIdxKF;
+                    if (P.checkOri) atomicAdd(&s_hist[rot_bin(kangK[realIdxKF], kangF[bestIdxF])], 1);
+                    ++mycount;
+                }
+                if (bestDist1R <= TH_LOW) {                        /* `|| true` in the fork: no ratio test */
+                    match[bestIdxFR] = realIdxKF;
+                    if (P.checkOri) atomicAdd(&s_hist[rot_bin(kangK[realIdxKF], kangF[bestIdxFR])], 1);
+                    ++mycount;
+                }
+            }
+        }
+    }
+    __syncthreads();
+    if (P.checkOri) {
+        if (tid == 0) three_maxima(s_hist, HISTO_LENGTH, s_ind[0], s_ind[1], s_ind[2]);
+        __syncthreads();
+        for (int i = tid; i < P.nF; i += MT) {
+            const int k = match[i];
+            if (k >= 0) {
+                const int bin = rot_bin(kangK[k], kangF[i]);
+                if (bin != s_ind[0] && bin != s_ind[1] && bin != s_ind[2]) { match[i] = -1; --mycount; }
+            }
+        }
+    }
+    if (mycount) atomicAdd(&s_count, mycount);
+    __syncthreads();
+    if (tid == 0) counts[blockIdx.x] = s_count;
+}
+
+extern "C" orbx_status orbx_search_by_bow(orbx_matcher* m, int nprob, const orbx_kf_view* KF, const orbx_kf_view* F,
+                                          const int* nleft, float nnRatio, int checkOrientation, int* const* match_kf,
+                                          int* nmatches) {
+    if (!m || nprob < 0 || (nprob > 0 && (!KF || !F || !match_kf || !nmatches))) { orbx_set_error("null argument"); return ORBX_ERR_INVALID; }
+    if (nprob == 0) return ORBX_OK;
+    ORBX_CUDA(cudaSetDevice(m->device));
+    Packer in, out;
+    std::vector<BowProb> probs(nprob);
+    std::vector<std::vector<int4>> tasks(nprob);
+    for (int p = 0; p < nprob; ++p) {
+        const orbx_kf_view &A = KF[p], &B = F[p];
+        BowProb& P = probs[p];
+        memset(&P, 0, sizeof(P));
+        if (A.n < 0 || B.n < 0 || A.nnodes < 0 || B.nnodes < 0 || (A.n > 0 && (!A.desc || !A.has_mp || (checkOrientation && !A.kangle))) ||
+            (B.n > 0 && (!B.desc || (checkOrientation && !B.kangle))) ||
+            (A.nnodes > 0 && (!A.node_id || !A.node_off || !A.node_idx)) || (B.nnodes > 0 && (!B.node_id || !B.node_off || !B.node_idx))) {
+            orbx_set_error("problem %d: null array", p);
+            return ORBX_ERR_INVALID;
+        }
+        const int nidxA = A.nnodes > 0 ? A.node_off[A.nnodes] : 0, nidxB = B.nnodes > 0 ? B.node_off[B.nnodes] : 0;
+        for (int i = 0; i < nidxA; ++i) if (A.node_idx[i] < 0 || A.node_idx[i] >= A.n) { orbx_set_error("problem %d: node index out of range", p); return ORBX_ERR_INVALID; }
+        for (int i = 0; i < nidxB; ++i) if (B.node_idx[i] < 0 || B.node_idx[i] >= B.n) { orbx_set_error("problem %d: node index out of range", p); return ORBX_ERR_INVALID; }
+        /* lockstep walk over the two FeatureVectors (reference :152-157, 296-303: lower_bound jumps) */
+        int f1 = 0, f2 = 0;
+        while (f1 < A.nnodes && f2 < B.nnodes) {
+            if (A.node_id[f1] == B.node_id[f2]) {
+                tasks[p].push_back(make_int4(A.node_off[f1], A.node_off[f1 + 1] - A.node_off[f1], B.node_off[f2], B.node_off[f2 + 1] - B.node_off[f2]));
+                ++f1; ++f2;
+            } else if (A.node_id[f1] < B.node_id[f2]) ++f1;
+            else ++f2;
+        }
+        P.nF = B.n; P.ntasks = (int)tasks[p].size(); P.nleft = nleft ? nleft[p] : -1; P.checkOri = checkOrientation; P.nnRatio = nnRatio;
+        P.hasmpK = in.add(A.has_mp, (size_t)A.n); P.kangK = in.add(A.kangle, A.kangle ? 4 * (size_t)A.n : 0);
+        P.descK = in.add(A.desc, 32 * (size_t)A.n); P.nidxK = in.add(A.node_idx, 4 * (size_t)nidxA);
+        P.kangF = in.add(B.kangle, B.kangle ? 4 * (size_t)B.n : 0); P.descF = in.add(B.desc, 32 * (size_t)B.n);
+        P.nidxF = in.add(B.node_idx, 4 * (size_t)nidxB);
+        P.tasks = in.add(tasks[p].data(), sizeof(int4) * tasks[p].size());
+        P.out_match = out.add(nullptr, 4 * (size_t)B.n);
+    }
+    const size_t probs_off = in.add(probs.data(), sizeof(BowProb) * (size_t)nprob);
+    const size_t counts_off = out.add(nullptr, 4 * (size_t)nprob);
+    orbx_status st = ensure_io(m, in.total, out.total);
+    if (st != ORBX_OK) return st;
+    in.copy_to(m->h_in);
+    ORBX_CUDA(cudaMemcpyAsync(m->d_in, m->h_in, in.total, cudaMemcpyHostToDevice, m->stream));
+    k_search_by_bow<<<nprob, MT, 0, m->stream>>>(m->d_in, m->d_out, reinterpret_cast<const BowProb*>(m->d_in + probs_off),
+                                                 reinterpret_cast<int*>(m->d_out + counts_off));
+    ORBX_CUDA(cudaGetLastError());
+    m->last_launches = 1;
+    ORBX_CUDA(cudaMemcpyAsync(m->h_out, m->d_out, out.total, cudaMemcpyDeviceToHost, m->stream));
+    ORBX_CUDA(cudaStreamSynchronize(m->stream));
+    for (int p = 0; p < nprob; ++p) {
+        if (F[p].n > 0) memcpy(match_kf[p], m->h_out + probs[p].out_match, 4 * (size_t)F[p].n);
+        nmatches[p] = reinterpret_cast<const int*>(m->h_out + counts_off)[p];
+    }
+    return ORBX_OK;
+}

@@ -66,6 +66,7 @@ def lib():
         L.orbx_extractor_set_fast_corner_list.argtypes = [C.c_void_p, C.c_int]
         L.orbx_extractor_assign_grid.argtypes = [C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, C.c_int]
         L.orbx_extractor_grid_fetch.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int]
+        L.orbx_search_by_bow.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_void_p, C.c_void_p]
         L.orbx_distinctive_descriptors.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 4
         L.orbx_assign_features_to_grid.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orbx_features_in_area.argtypes = [C.c_void_p, C.c_void_p, C.c_int] + [C.c_void_p] * 7 + [C.c_int]
@@ -361,6 +362,16 @@ def _arr(a, dt, keep):
     return a.ctypes.data
 
 
+def _kf_view(K, keep):
+    """K: dict with kx, ky, koct, [kangle], desc, [has_mp], [uright], node_id, node_off, node_idx
+    (include/orbx.h orbx_kf_view)."""
+    return _KFView(len(K["desc"]), _arr(K.get("kx"), np.float32, keep), _arr(K.get("ky"), np.float32, keep),
+                   _arr(K.get("koct"), np.int32, keep), _arr(K.get("kangle"), np.float32, keep),
+                   _arr(K["desc"], np.uint8, keep), _arr(K.get("has_mp"), np.uint8, keep),
+                   _arr(K.get("uright"), np.float32, keep), len(K["node_id"]), _arr(K["node_id"], np.int32, keep),
+                   _arr(K["node_off"], np.int32, keep), _arr(K["node_idx"], np.int32, keep))
+
+
 def _frame_view(F, keep):
     """F: dict with kx, ky, koct, [kangle], desc, minx, miny, gw_inv, gh_inv, gcols, grows, scale
     (the Frame members named in include/orbx.h)."""
@@ -412,6 +423,23 @@ class ORBmatcher:
     @staticmethod
     def DescriptorDistance(a, b):
         return int(hamming_pairs(np.asarray(a, np.uint8).reshape(1, 32), np.asarray(b, np.uint8).reshape(1, 32))[0])
+
+    def SearchByBoW(self, KFs, Fs, nnRatio=0.7, checkOrientation=True, nleft=None):
+        """ORBmatcher::SearchByBoW(KeyFrame, Frame): list of problems -> [(nmatches, match_kf)]."""
+        single = isinstance(KFs, dict)
+        if single:
+            KFs, Fs = [KFs], [Fs]
+            nleft = None if nleft is None else [nleft]
+        keep = []
+        a = (_KFView * len(KFs))(*[_kf_view(k, keep) for k in KFs])
+        b = (_KFView * len(Fs))(*[_kf_view(f, keep) for f in Fs])
+        outs = [np.empty(max(len(f["desc"]), 1), np.int32) for f in Fs]
+        po = (C.c_void_p * len(Fs))(*[o.ctypes.data for o in outs])
+        nm = np.empty(len(Fs), np.int32)
+        nl = None if nleft is None else np.ascontiguousarray(nleft, np.int32)
+        _ck(lib().orbx_search_by_bow(self._h, len(KFs), a, b, _p(nl), C.c_float(nnRatio), int(checkOrientation), po, _p(nm)))
+        res = [(int(nm[p]), outs[p][:len(Fs[p]["desc"])]) for p in range(len(Fs))]
+        return res[0] if single else res
 
     def ComputeDistinctiveDescriptors(self, sets):
         """MapPoint::ComputeDistinctiveDescriptors for a list of (N_s, 32) u8 descriptor sets ->

@@ -274,3 +274,34 @@ def test_distinctive_descriptors(matcher, oracle, synth):
     best, med = matcher.ComputeDistinctiveDescriptors(sets)
     for s, d in enumerate(sets):
         assert (int(best[s]), int(med[s])) == oracle.distinctive_descriptor(d), f"set {s} (N={len(d)})"
+
+
+# ------------------------------------------------------------------ SearchByBoW
+@pytest.mark.parametrize("n1,n2,nnodes,ori,nleft,seed", [
+    (1000, 1100, 90, True, -1, 101), (1000, 1100, 90, False, -1, 102), (300, 250, 12, True, -1, 103),
+    (1000, 1100, 90, True, 600, 104), (50, 40, 3, True, 20, 105), (0, 10, 2, True, -1, 106),
+])
+def test_search_by_bow(matcher, oracle, synth, n1, n2, nnodes, ori, nleft, seed):
+    if n1 == 0:
+        K1, K2, _, _, _ = synth.keyframe_pair(5, n2, nnodes, seed)
+        for k in ("kx", "ky", "koct", "kangle", "has_mp", "uright"):
+            K1[k] = K1[k][:0]
+        K1["desc"] = K1["desc"][:0]; K1["node_id"] = K1["node_id"][:0]; K1["node_off"] = np.zeros(1, np.int32); K1["node_idx"] = K1["node_idx"][:0]
+    else:
+        K1, K2, _, _, _ = synth.keyframe_pair(n1, n2, nnodes, seed)
+        K1["has_mp"] = (np.random.default_rng(seed).random(n1) < 0.8).astype(np.uint8)      # most KeyFrame points carry a MapPoint
+    n, m = matcher.SearchByBoW(K1, K2, 0.7, ori, None if nleft == -1 else nleft)
+    on, om = oracle.search_by_bow(K1, K2, 0.7, ori, nleft)
+    assert n == on and np.array_equal(m, om)
+    if n1 >= 300:
+        assert n > 20
+
+
+def test_search_by_bow_batched(matcher, oracle, synth):
+    probs = [synth.keyframe_pair(400 + 50 * i, 380 + 30 * i, 20 + 7 * i, 110 + i) for i in range(10)]
+    for i, p in enumerate(probs):
+        p[0]["has_mp"] = (np.random.default_rng(i).random(len(p[0]["kx"])) < 0.7).astype(np.uint8)
+    res = matcher.SearchByBoW([p[0] for p in probs], [p[1] for p in probs], 0.75, True)
+    for (n, m), p in zip(res, probs):
+        on, om = oracle.search_by_bow(p[0], p[1], 0.75, True)
+        assert n == on and np.array_equal(m, om)

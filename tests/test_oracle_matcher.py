@@ -209,3 +209,23 @@ def test_distinctive_descriptor_known_answers(oracle):
     D = np.unpackbits(d[:, None, :] ^ d[None, :, :], axis=2).sum(2)
     meds = np.sort(D, axis=1)[:, int(0.5 * (len(d) - 1))]
     assert best == int(np.argmin(meds)) and med == int(meds.min()) and best < 4
+
+
+def test_search_by_bow_properties(oracle, synth):
+    """SearchByBoW (reference src/ORBmatcher.cc:133-327): matches only inside shared nodes, only
+    KeyFrame points with a MapPoint, each Frame keypoint matched once, planted twins found."""
+    K1, K2, _, _, _ = synth.keyframe_pair(800, 900, 60, 31)
+    K1["has_mp"] = (np.random.default_rng(1).random(800) < 0.8).astype(np.uint8)
+    n, m = oracle.search_by_bow(K1, K2, 0.7, False)
+    assert n == int((m >= 0).sum()) and n > 50
+    node1 = np.empty(800, np.int64); node2 = np.empty(900, np.int64)
+    for K, node in ((K1, node1), (K2, node2)):
+        for j in range(len(K["node_id"])):
+            node[K["node_idx"][K["node_off"][j]:K["node_off"][j + 1]]] = K["node_id"][j]
+    for i2 in np.nonzero(m >= 0)[0]:
+        i1 = m[i2]
+        assert K1["has_mp"][i1] and node1[i1] == node2[i2]
+        d = int(np.unpackbits(K1["desc"][i1] ^ K2["desc"][i2]).sum())
+        assert d <= 30            # TH_LOW (include/ORBmatcher.h:73)
+    n2, m2 = oracle.search_by_bow(K1, K2, 0.7, True)
+    assert n2 <= n and set(np.nonzero(m2 >= 0)[0]) <= set(np.nonzero(m >= 0)[0])
