@@ -168,16 +168,6 @@ typedef struct {
     const uint8_t* desc;            /* GetDescriptor(), n x 32 */
 } orbx_mappoints;
 
-/* ORBmatcher::SearchByBoW(pKF, F, vpMapPointMatches, nnRatio, checkOrientation)
- * src/ORBmatcher.cc:133-327, nprob (KeyFrame, Frame) problems per call.  Both sides are flattened
- * as orbx_kf_view (of F only n, kangle, desc and the feature vector are read; KF.has_mp[i] =
- * pMP && !pMP->isBad()).  nleft[p] = F->Nleft (NULL or -1: one camera; otherwise keypoints >=
- * Nleft belong to the right camera and take the fork's second branch).  match_kf[p][i] = KeyFrame
- * keypoint whose MapPoint the reference stores in vpMapPointMatches[i], or -1. */
-orbx_status orbx_search_by_bow(orbx_matcher* m, int nprob, const orbx_kf_view* KF, const orbx_kf_view* F,
-                               const int* nleft, float nnRatio, int checkOrientation, int* const* match_kf,
-                               int* nmatches);
-
 /* MapPoint::ComputeDistinctiveDescriptors   src/MapPoint.cc:343-412, batched over nsets map points:
  * desc rows set_off[s] .. set_off[s+1] are the observation descriptors of map point s (set_off[0]
  * = 0); best[s] = row (within the set) with the least median Hamming distance to the set, first
@@ -253,6 +243,17 @@ orbx_status orbx_search_for_triangulation(orbx_matcher* m, int nprob, const orbx
                                           const float* ep, const float* const* scale2,
                                           int bOnlyStereo, int bCoarse, int checkOrientation,
                                           int* const* pairs, int* npairs, int* nmatches);
+
+/* ORBmatcher::SearchByBoW(pKF, F, vpMapPointMatches, nnRatio, checkOrientation)
+ * src/ORBmatcher.cc:133-327, nprob (KeyFrame, Frame) problems per call.  Both sides are flattened
+ * as orbx_kf_view (of F only n, kangle, desc and the feature vector are read; KF.has_mp[i] =
+ * pMP && !pMP->isBad()).  nleft[p] = F->Nleft (NULL or -1: one camera; otherwise keypoints >=
+ * Nleft belong to the right camera and take the fork's second branch).  match_kf[p][i] = KeyFrame
+ * keypoint whose MapPoint the reference stores in vpMapPointMatches[i], or -1. */
+orbx_status orbx_search_by_bow(orbx_matcher* m, int nprob, const orbx_kf_view* KF, const orbx_kf_view* F,
+                               const int* nleft, float nnRatio, int checkOrientation, int* const* match_kf,
+                               int* nmatches);
+
 
 /* Frame::ComputeStereoMatches (upstream ORB-SLAM3 v1.0; absent from the fork:
  * include/Frame.h:53-62).  Works on the DEVICE-RESIDENT results of the
