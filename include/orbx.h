@@ -168,6 +168,29 @@ typedef struct {
     const uint8_t* desc;            /* GetDescriptor(), n x 32 */
 } orbx_mappoints;
 
+/* Map points handed to Fuse, after the host-side projection of src/ORBmatcher.cc:702-760 (:880-917
+ * for the Sim3 overload): valid[i] = 0 for points the reference skips before the search (null,
+ * bad, already in the KeyFrame, behind the camera, outside the image or the distance range). */
+typedef struct {
+    int32_t n;
+    const uint8_t* valid;
+    const float* u; const float* v;     /* projection uv */
+    const float* ur;                    /* u - bf/z (first overload; may be NULL = no stereo gate) */
+    const int32_t* level;               /* pMP->PredictScale(dist3D, pKF) */
+    const uint8_t* desc;                /* pMP->GetDescriptor(), n x 32 */
+} orbx_fuse_points;
+
+/* Search core of ORBmatcher::Fuse(pKF, vpMapPoints, th, bRight)   src/ORBmatcher.cc:678-862
+ * (variant 0) and Fuse(pKF, Scw, vpPoints, th, vpReplacePoint)   :864-975 (variant 1), nprob
+ * KeyFrames per call.  KF = the KeyFrame's mvKeysUn/descriptors/grid/mvScaleFactors; uright[p] =
+ * mvuRight (NULL: monocular), inv_sigma2[p] = mvInvLevelSigma2 (variant 0).  best_idx[p][i] =
+ * the keypoint the reference selects for map point i if bestDist <= TH_LOW, else -1; best_dist
+ * (may be NULL) its distance.  The graph updates (:826-848 / :958-968: Replace / AddObservation /
+ * AddMapPoint, nFused++) are applied by the caller in map-point order. */
+orbx_status orbx_fuse_search(orbx_matcher* m, int nprob, const orbx_frame_view* KF, const float* const* uright,
+                             const float* const* inv_sigma2, const orbx_fuse_points* MP, float th, int variant,
+                             int* const* best_idx, int* const* best_dist);
+
 /* MapPoint::ComputeDistinctiveDescriptors   src/MapPoint.cc:343-412, batched over nsets map points:
  * desc rows set_off[s] .. set_off[s+1] are the observation descriptors of map point s (set_off[0]
  * = 0); best[s] = row (within the set) with the least median Hamming distance to the set, first

@@ -259,6 +259,19 @@ def _kf_view(K, keep):
                    len(a[6]), a[6].ctypes.data, a[7].ctypes.data, a[8].ctypes.data)
 
 
+def fuse_search(KF, mp, th=3.0, variant=0, uright=None, inv_sigma2=None):
+    keep = []
+    fv = _frame_view(KF, keep)
+    valid, u, v, lvl, d = _u8(mp["valid"]), _f32(mp["u"]), _f32(mp["v"]), _i32(mp["level"]), _u8(mp["desc"])
+    ur = _f32(mp["ur"]) if mp.get("ur") is not None else None
+    kur = _f32(uright) if uright is not None else None
+    isg = _f32(inv_sigma2) if inv_sigma2 is not None else None
+    bi = np.empty(max(len(u), 1), np.int32); bd = np.empty(max(len(u), 1), np.int32)
+    lib().orc_fuse_search(C.byref(fv), _p(kur), _p(isg), len(u), _p(valid), _p(u), _p(v), _p(ur), _p(lvl), _p(d),
+                          C.c_float(th), int(variant), _p(bi), _p(bd))
+    return bi[:len(u)], bd[:len(u)]
+
+
 def search_by_bow(KF, F, nnRatio=0.7, checkOrientation=True, nleft=-1):
     keep = []
     a, b = _kf_view(KF, keep), _kf_view(F, keep)

@@ -837,6 +837,46 @@ int orc_search_by_projection_kf(const orc_frame_view* F, const float* fangle, in
     return nmatches;
 }
 
+void orc_fuse_search(const orc_frame_view* KF, const float* uright, const float* inv_sigma2, int nmp,
+                     const uint8_t* valid, const float* mu, const float* mv, const float* mur, const int* mlevel,
+                     const uint8_t* mdesc, float th, int variant, int* best_idx, int* best_dist) {
+    /* search core of Fuse, src/ORBmatcher.cc:762-824 (variant 0) and :919-956 (variant 1);
+     * KeyFrame::GetFeaturesInArea (src/KeyFrame.cc:790-833) has no octave filter */
+    const std::vector<std::vector<int>> grid = build_grid(KF);
+    std::vector<int> vIndices;
+    for (int i = 0; i < nmp; ++i) {
+        best_idx[i] = -1; best_dist[i] = -1;
+        if (!valid[i]) continue;
+        const int nPredictedLevel = mlevel[i];
+        const float radius = th * KF->scale[nPredictedLevel];
+        features_in_area(KF, grid, mu[i], mv[i], radius, -1, -1, vIndices);
+        if (vIndices.empty()) continue;
+        const uint8_t* dMP = mdesc + (size_t)i * 32;
+        int bestDist = variant == 0 ? 256 : INT_MAX, bestIdx = -1;
+        for (int idx : vIndices) {
+            const int kpLevel = KF->koct[idx];
+            if (kpLevel < nPredictedLevel - 1 || kpLevel > nPredictedLevel) continue;
+            if (variant == 0) {
+                const float kpx = KF->kx[idx], kpy = KF->ky[idx];
+                if (uright && mur && uright[idx] >= 0) {
+                    const float kpr = uright[idx];
+                    const float ex = mu[i] - kpx, ey = mv[i] - kpy, er = mur[i] - kpr;
+                    const float e2 = ex * ex + ey * ey + er * er;
+                    if (e2 * inv_sigma2[kpLevel] > 7.8) continue;
+                } else {
+                    const float ex = mu[i] - kpx, ey = mv[i] - kpy;
+                    const float e2 = ex * ex + ey * ey;
+                    if (e2 * inv_sigma2[kpLevel] > 5.99) continue;
+                }
+            }
+            const int dist = orc_descriptor_distance(dMP, KF->desc + (size_t)idx * 32);
+            if (dist < bestDist) { bestDist = dist; bestIdx = idx; }
+        }
+        if (bestIdx >= 0) best_dist[i] = bestDist;
+        if (bestDist <= TH_LOW) best_idx[i] = bestIdx;
+    }
+}
+
 int orc_search_by_bow(const orc_kf_view* KF, const orc_kf_view* F, int Nleft, float nnRatio,
                       int checkOrientation, int* match_kf) {
     /* src/ORBmatcher.cc:133-327.  match_kf[i] = KeyFrame keypoint whose MapPoint lands in

@@ -147,6 +147,13 @@ typedef struct {
     const float* uright;         /* may be NULL */
     int nnodes; const int* node_id; const int* node_off; const int* node_idx;
 } orc_kf_view;
+/* Search core of Fuse (ORBmatcher.cc:678-862 variant 0, :864-975 variant 1) on projected map
+ * points (valid, u, v, ur, predicted level, descriptor): best_idx[i] = selected keypoint if
+ * bestDist <= TH_LOW else -1; best_dist[i] = its distance (-1 if no candidate). */
+void orc_fuse_search(const orc_frame_view* KF, const float* uright, const float* inv_sigma2, int nmp,
+                     const uint8_t* valid, const float* mu, const float* mv, const float* mur, const int* mlevel,
+                     const uint8_t* mdesc, float th, int variant, int* best_idx, int* best_dist);
+
 /* SearchByBoW(KeyFrame, Frame, ...) ORBmatcher.cc:133-327: F is flattened like a keyframe (angles,
  * descriptors, feature vector); match_kf[i] (F->n entries) = KeyFrame keypoint whose MapPoint goes
  * to Frame keypoint i, or -1.  Nleft = F->Nleft (-1: one camera). */

@@ -1434,3 +1434,175 @@ extern "C" orbx_status orbx_search_by_bow(orbx_matcher* m, int nprob, const orbx
     }
     return ORBX_OK;
 }
+
+/* ================================================================== Fuse */
+/* The search core shared by ORBmatcher::Fuse(pKF, vpMapPoints, th, bRight) (reference
+ * src/ORBmatcher.cc:678-862, variant 0) and Fuse(pKF, Scw, vpPoints, th, vpReplacePoint)
+ * (:864-975, variant 1): for every projected map point the most similar KeyFrame keypoint inside
+ * the window KeyFrame::GetFeaturesInArea(u, v, th * scale[level]) (src/KeyFrame.cc:790-833, no
+ * octave filter there) whose octave is in [level-1, level] and -- variant 0 -- whose
+ * reprojection error passes the chi-square gate (:789-816); first strictly smaller distance wins.
+ * Map points are independent (the graph updates of :826-848 stay with the caller, applied in
+ * order), so: CTA per problem, grid CSR in shared memory, one thread per map point. */
+struct FuseProb {
+    int n, nmp, gcols, grows, nlevels, variant, has_ur, pad;
+    float minx, miny, gw_inv, gh_inv, th, pad1, pad2, pad3;
+    unsigned long long kx, ky, koct, desc, uright, scale, inv_sigma2;
+    unsigned long long mvalid, mu, mv, mur, mlevel, mdesc;
+    unsigned long long out_idx, out_dist;
+};
+
+__global__ void __launch_bounds__(MT) k_fuse_search(const uint8_t* __restrict__ in, uint8_t* __restrict__ out,
+                                                     const FuseProb* __restrict__ probs) {
+    extern __shared__ __align__(16) uint32_t sm[];
+    __shared__ uint32_t s_tmp[MT / 32];
+    const FuseProb P = probs[blockIdx.x];
+    const int tid = threadIdx.x;
+    const int n = P.n, ncell = P.gcols * P.grows;
+    const float* kx = reinterpret_cast<const float*>(in + P.kx);
+    const float* ky = reinterpret_cast<const float*>(in + P.ky);
+    const int* koct = reinterpret_cast<const int*>(in + P.koct);
+    const uint4* kdesc = reinterpret_cast<const uint4*>(in + P.desc);
+    const float* uright = reinterpret_cast<const float*>(in + P.uright);
+    const float* scale = reinterpret_cast<const float*>(in + P.scale);
+    const float* inv_sigma2 = reinterpret_cast<const float*>(in + P.inv_sigma2);
+    const uint8_t* mvalid = in + P.mvalid;
+    const float* mu = reinterpret_cast<const float*>(in + P.mu);
+    const float* mv = reinterpret_cast<const float*>(in + P.mv);
+    const float* mur = reinterpret_cast<const float*>(in + P.mur);
+    const int* mlevel = reinterpret_cast<const int*>(in + P.mlevel);
+    const uint4* mdesc = reinterpret_cast<const uint4*>(in + P.mdesc);
+    int* oidx = reinterpret_cast<int*>(out + P.out_idx);
+    int* odist = reinterpret_cast<int*>(out + P.out_dist);
+
+    uint32_t* cell_start = sm;                        /* [ncell + 1], column-major cells (ix*grows + iy) */
+    uint32_t* cell_fill = cell_start + ncell + 1;     /* [ncell] */
+    unsigned short* csr = reinterpret_cast<unsigned short*>(cell_fill + ncell);   /* [n] */
+    /* grid: PosInGrid + AssignFeaturesToGrid (reference src/Frame.cc:157-176, 470-480; KeyFrame copies it) */
+    for (int i = tid; i <= ncell; i += MT) cell_start[i] = 0;
+    __syncthreads();
+    for (int i = tid; i < n; i += MT) {
+        const int px = (int)roundf((kx[i] - P.minx) * P.gw_inv), py = (int)roundf((ky[i] - P.miny) * P.gh_inv);
+        const int lin = py * P.gcols + px;
+        if (lin >= 0 && lin < ncell) atomicAdd(&cell_start[(lin % P.gcols) * P.grows + lin / P.gcols], 1u);
+    }
+    __syncthreads();
+    mt_excl_scan(cell_start, ncell + 1, s_tmp);
+    for (int i = tid; i < ncell; i += MT) cell_fill[i] = cell_start[i];
+    __syncthreads();
+    for (int i = tid; i < n; i += MT) {
+        const int px = (int)roundf((kx[i] - P.minx) * P.gw_inv), py = (int)roundf((ky[i] - P.miny) * P.gh_inv);
+        const int lin = py * P.gcols + px;
+        if (lin >= 0 && lin < ncell) csr[atomicAdd(&cell_fill[(lin % P.gcols) * P.grows + lin / P.gcols], 1u)] = (unsigned short)i;
+    }
+    __syncthreads();
+    for (int c = tid; c < ncell; c += MT) {
+        const int e0 = (int)cell_start[c], e1 = (int)cell_start[c + 1];
+        for (int a = e0 + 1; a < e1; ++a) {
+            const unsigned short v = csr[a];
+            int b = a - 1;
+            while (b >= e0 && csr[b] > v) { csr[b + 1] = csr[b]; --b; }
+            csr[b + 1] = v;
+        }
+    }
+    __syncthreads();
+
+    for (int i = tid; i < P.nmp; i += MT) {
+        int bestIdx = -1, bestDist = P.variant == 0 ? 256 : 0x7fffffff;
+        if (mvalid[i]) {
+            const int level = mlevel[i];
+            const float r = P.th * scale[level];
+            const float x = mu[i], y = mv[i];
+            const int c0 = max(0, (int)floorf((x - P.minx - r) * P.gw_inv));
+            const int c1 = min(P.gcols - 1, (int)ceilf((x - P.minx + r) * P.gw_inv));
+            const int r0 = max(0, (int)floorf((y - P.miny - r) * P.gh_inv));
+            const int r1 = min(P.grows - 1, (int)ceilf((y - P.miny + r) * P.gh_inv));
+            if (c0 < P.gcols && c1 >= 0 && r0 < P.grows && r1 >= 0) {
+                const uint4 q0 = __ldg(mdesc + 2 * i), q1 = __ldg(mdesc + 2 * i + 1);
+                const float ur = (P.variant == 0 && P.has_ur) ? mur[i] : 0.f;
+                for (int ix = c0; ix <= c1; ++ix) {
+                    const uint32_t e0 = cell_start[ix * P.grows + r0], e1 = cell_start[ix * P.grows + r1 + 1];
+                    for (uint32_t e = e0; e < e1; ++e) {
+                        const int idx = csr[e];
+                        const float kpx = kx[idx], kpy = ky[idx];
+                        if (!(fabsf(kpx - x) < r && fabsf(kpy - y) < r)) continue;
+                        const int kpLevel = koct[idx];
+                        if (kpLevel < level - 1 || kpLevel > level) continue;
+                        if (P.variant == 0) {
+                            const float ex = x - kpx, ey = y - kpy;
+                            if (P.has_ur && uright[idx] >= 0) {
+                                const float er = ur - uright[idx];
+                                const float e2 = __fadd_rn(__fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey)), __fmul_rn(er, er));
+                                if ((double)__fmul_rn(e2, inv_sigma2[kpLevel]) > 7.8) continue;
+                            } else {
+                                const float e2 = __fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey));
+                                if ((double)__fmul_rn(e2, inv_sigma2[kpLevel]) > 5.99) continue;
+                            }
+                        }
+                        const int dist = hamming256(q0, q1, __ldg(kdesc + 2 * idx), __ldg(kdesc + 2 * idx + 1));
+                        if (dist < bestDist) { bestDist = dist; bestIdx = idx; }
+                    }
+                }
+            }
+        }
+        oidx[i] = bestDist <= TH_LOW ? bestIdx : -1;
+        odist[i] = bestIdx >= 0 ? bestDist : -1;
+    }
+}
+
+extern "C" orbx_status orbx_fuse_search(orbx_matcher* m, int nprob, const orbx_frame_view* KF, const float* const* uright,
+                                        const float* const* inv_sigma2, const orbx_fuse_points* MP, float th, int variant,
+                                        int* const* best_idx, int* const* best_dist) {
+    if (!m || nprob < 0 || (nprob > 0 && (!KF || !MP || !best_idx)) || (variant != 0 && variant != 1)) { orbx_set_error("invalid argument"); return ORBX_ERR_INVALID; }
+    if (nprob == 0) return ORBX_OK;
+    ORBX_CUDA(cudaSetDevice(m->device));
+    Packer in, out;
+    std::vector<FuseProb> probs(nprob);
+    size_t smem = 0;
+    for (int p = 0; p < nprob; ++p) {
+        const orbx_frame_view& f = KF[p];
+        const orbx_fuse_points& M = MP[p];
+        FuseProb& P = probs[p];
+        memset(&P, 0, sizeof(P));
+        if (f.n < 0 || f.n > 65535 || M.n < 0 || f.gcols < 1 || f.grows < 1 || (long long)f.gcols * f.grows > 20000 || f.nlevels < 1 ||
+            (f.n > 0 && (!f.kx || !f.ky || !f.koct || !f.desc)) || !f.scale || (variant == 0 && (!inv_sigma2 || !inv_sigma2[p])) ||
+            (M.n > 0 && (!M.valid || !M.u || !M.v || !M.level || !M.desc))) {
+            orbx_set_error("problem %d: unsupported view or null array", p);
+            return ORBX_ERR_INVALID;
+        }
+        for (int i = 0; i < M.n; ++i)
+            if (M.valid[i] && (M.level[i] < 0 || M.level[i] >= f.nlevels)) { orbx_set_error("problem %d: map point %d level out of range", p, i); return ORBX_ERR_INVALID; }
+        const float* ur = uright ? uright[p] : nullptr;
+        P.n = f.n; P.nmp = M.n; P.gcols = f.gcols; P.grows = f.grows; P.nlevels = f.nlevels; P.variant = variant;
+        P.has_ur = (ur != nullptr && M.ur != nullptr);
+        P.minx = f.minx; P.miny = f.miny; P.gw_inv = f.gw_inv; P.gh_inv = f.gh_inv; P.th = th;
+        P.kx = in.add(f.kx, 4 * (size_t)f.n); P.ky = in.add(f.ky, 4 * (size_t)f.n); P.koct = in.add(f.koct, 4 * (size_t)f.n);
+        P.desc = in.add(f.desc, 32 * (size_t)f.n); P.uright = in.add(ur, ur ? 4 * (size_t)f.n : 0);
+        P.scale = in.add(f.scale, 4 * (size_t)f.nlevels);
+        P.inv_sigma2 = in.add(variant == 0 ? inv_sigma2[p] : nullptr, variant == 0 ? 4 * (size_t)f.nlevels : 0);
+        P.mvalid = in.add(M.valid, (size_t)M.n); P.mu = in.add(M.u, 4 * (size_t)M.n); P.mv = in.add(M.v, 4 * (size_t)M.n);
+        P.mur = in.add(M.ur, M.ur ? 4 * (size_t)M.n : 0); P.mlevel = in.add(M.level, 4 * (size_t)M.n);
+        P.mdesc = in.add(M.desc, 32 * (size_t)M.n);
+        P.out_idx = out.add(nullptr, 4 * (size_t)std::max(M.n, 1)); P.out_dist = out.add(nullptr, 4 * (size_t)std::max(M.n, 1));
+        smem = std::max(smem, (size_t)4 * (2 * (size_t)f.gcols * f.grows + 1) + 2 * (size_t)f.n + 16);
+    }
+    const size_t probs_off = in.add(probs.data(), sizeof(FuseProb) * (size_t)nprob);
+    if (smem > 200 * 1024) { orbx_set_error("keyframe grid + keypoints need %zu B of shared memory (> 200 KB)", smem); return ORBX_ERR_INVALID; }
+    orbx_status st = ensure_io(m, in.total, out.total);
+    if (st != ORBX_OK) return st;
+    in.copy_to(m->h_in);
+    ORBX_CUDA(cudaMemcpyAsync(m->d_in, m->h_in, in.total, cudaMemcpyHostToDevice, m->stream));
+    ORBX_CUDA(cudaFuncSetAttribute(k_fuse_search, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max(smem, (size_t)48 * 1024)));
+    k_fuse_search<<<nprob, MT, smem, m->stream>>>(m->d_in, m->d_out, reinterpret_cast<const FuseProb*>(m->d_in + probs_off));
+    ORBX_CUDA(cudaGetLastError());
+    m->last_launches = 1;
+    ORBX_CUDA(cudaMemcpyAsync(m->h_out, m->d_out, out.total, cudaMemcpyDeviceToHost, m->stream));
+    ORBX_CUDA(cudaStreamSynchronize(m->stream));
+    for (int p = 0; p < nprob; ++p) {
+        if (MP[p].n > 0) {
+            memcpy(best_idx[p], m->h_out + probs[p].out_idx, 4 * (size_t)MP[p].n);
+            if (best_dist && best_dist[p]) memcpy(best_dist[p], m->h_out + probs[p].out_dist, 4 * (size_t)MP[p].n);
+        }
+    }
+    return ORBX_OK;
+}

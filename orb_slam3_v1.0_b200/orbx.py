@@ -66,6 +66,7 @@ def lib():
         L.orbx_extractor_set_fast_corner_list.argtypes = [C.c_void_p, C.c_int]
         L.orbx_extractor_assign_grid.argtypes = [C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, C.c_int]
         L.orbx_extractor_grid_fetch.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int]
+        L.orbx_fuse_search.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_void_p, C.c_void_p]
         L.orbx_search_by_bow.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_void_p, C.c_void_p]
         L.orbx_distinctive_descriptors.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 4
         L.orbx_assign_features_to_grid.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
@@ -348,6 +349,11 @@ class _KFPoints(C.Structure):
                 ("angle", C.c_void_p), ("desc", C.c_void_p)]
 
 
+class _FusePoints(C.Structure):
+    _fields_ = [("n", C.c_int), ("valid", C.c_void_p), ("u", C.c_void_p), ("v", C.c_void_p), ("ur", C.c_void_p),
+                ("level", C.c_void_p), ("desc", C.c_void_p)]
+
+
 class _KFView(C.Structure):
     _fields_ = [("n", C.c_int), ("kx", C.c_void_p), ("ky", C.c_void_p), ("koct", C.c_void_p), ("kangle", C.c_void_p),
                 ("desc", C.c_void_p), ("has_mp", C.c_void_p), ("uright", C.c_void_p), ("nnodes", C.c_int),
@@ -439,6 +445,29 @@ class ORBmatcher:
         nl = None if nleft is None else np.ascontiguousarray(nleft, np.int32)
         _ck(lib().orbx_search_by_bow(self._h, len(KFs), a, b, _p(nl), C.c_float(nnRatio), int(checkOrientation), po, _p(nm)))
         res = [(int(nm[p]), outs[p][:len(Fs[p]["desc"])]) for p in range(len(Fs))]
+        return res[0] if single else res
+
+    def FuseSearch(self, KFs, MPs, th=3.0, variant=0, uright=None, inv_sigma2=None):
+        """Search core of ORBmatcher::Fuse (variant 0: KeyFrame/MapPoints overload with the
+        chi-square gates; 1: Sim3 overload) -> [(best_idx, best_dist)] per problem."""
+        single = isinstance(KFs, dict)
+        if single:
+            KFs, MPs = [KFs], [MPs]
+            uright = None if uright is None else [uright]
+            inv_sigma2 = None if inv_sigma2 is None else [inv_sigma2]
+        keep = []
+        fv = (_FrameView * len(KFs))(*[_frame_view(f, keep) for f in KFs])
+        mp = (_FusePoints * len(MPs))(*[_FusePoints(len(M["u"]), _arr(M["valid"], np.uint8, keep), _arr(M["u"], np.float32, keep),
+                                                    _arr(M["v"], np.float32, keep), _arr(M.get("ur"), np.float32, keep),
+                                                    _arr(M["level"], np.int32, keep), _arr(M["desc"], np.uint8, keep)) for M in MPs])
+        bi = [np.empty(max(len(M["u"]), 1), np.int32) for M in MPs]
+        bd = [np.empty(max(len(M["u"]), 1), np.int32) for M in MPs]
+        pur = None if uright is None else (C.c_void_p * len(KFs))(*[_arr(a, np.float32, keep) for a in uright])
+        pis = None if inv_sigma2 is None else (C.c_void_p * len(KFs))(*[_arr(a, np.float32, keep) for a in inv_sigma2])
+        _ck(lib().orbx_fuse_search(self._h, len(KFs), fv, pur, pis, mp, C.c_float(th), int(variant),
+                                   (C.c_void_p * len(MPs))(*[a.ctypes.data for a in bi]),
+                                   (C.c_void_p * len(MPs))(*[a.ctypes.data for a in bd])))
+        res = [(bi[p][:len(MPs[p]["u"])], bd[p][:len(MPs[p]["u"])]) for p in range(len(MPs))]
         return res[0] if single else res
 
     def ComputeDistinctiveDescriptors(self, sets):

@@ -152,3 +152,24 @@ def keyframe_pair(n1=1000, n2=1100, nnodes=90, seed=3, width=752, height=480, nl
     F12 = np.array([[0, 0, 0.002], [0, 0, -1.0], [-0.002, 1.0, 0.3]], np.float32)
     ep = np.array([width * 0.5 + 40, height * 0.5 - 10], np.float32)
     return k1, k2, F12, ep, sf
+
+
+def fuse_problem(F, nmp=1200, seed=4, jitter=1.5, flip_p=0.04, bf=47.9):
+    """Projected map points for ORBmatcher::Fuse against the KeyFrame view F: most land near a
+    keypoint with a similar descriptor, some are random; also the KeyFrame's mvuRight and
+    mvInvLevelSigma2."""
+    rng = np.random.default_rng(seed)
+    n = len(F["kx"])
+    src = rng.integers(0, n, nmp)
+    desc = _flip_bits(rng, F["desc"][src], flip_p)
+    rnd = rng.random(nmp) < 0.2
+    desc[rnd] = rng.integers(0, 256, (int(rnd.sum()), 32), dtype=np.uint8)
+    u = (F["kx"][src] + rng.normal(0, jitter, nmp)).astype(np.float32)
+    v = (F["ky"][src] + rng.normal(0, jitter, nmp)).astype(np.float32)
+    z = rng.uniform(2, 30, nmp).astype(np.float32)
+    uright = np.where(rng.random(n) < 0.5, F["kx"] - np.float32(bf) / rng.uniform(2, 30, n).astype(np.float32), -1).astype(np.float32)
+    mp = {"valid": (rng.random(nmp) < 0.9).astype(np.uint8), "u": u, "v": v,
+          "ur": (u - np.float32(bf) / z).astype(np.float32),
+          "level": np.clip(F["koct"][src] + rng.integers(0, 2, nmp), 0, len(F["scale"]) - 1).astype(np.int32), "desc": desc}
+    inv_sigma2 = (1.0 / (F["scale"].astype(np.float32) ** 2)).astype(np.float32)
+    return mp, uright, inv_sigma2

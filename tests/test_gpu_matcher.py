@@ -305,3 +305,32 @@ def test_search_by_bow_batched(matcher, oracle, synth):
     for (n, m), p in zip(res, probs):
         on, om = oracle.search_by_bow(p[0], p[1], 0.75, True)
         assert n == on and np.array_equal(m, om)
+
+
+# ------------------------------------------------------------------ Fuse search core
+@pytest.mark.parametrize("n,nmp,th,variant,stereo,seed", [
+    (1000, 1200, 3.0, 0, True, 121), (1000, 1200, 3.0, 0, False, 122), (1000, 1500, 4.0, 1, False, 123),
+    (60, 40, 2.5, 0, True, 124), (0, 10, 3.0, 0, True, 125), (500, 0, 3.0, 1, False, 126),
+])
+def test_fuse_search(matcher, oracle, synth, n, nmp, th, variant, stereo, seed):
+    F = synth.frame_view(n, seed=seed)
+    mp, ur, isg = synth.fuse_problem(F, nmp, seed + 1) if n > 0 else (
+        {"valid": np.ones(nmp, np.uint8), "u": np.full(nmp, 100, np.float32), "v": np.full(nmp, 100, np.float32),
+         "ur": np.full(nmp, 90, np.float32), "level": np.zeros(nmp, np.int32), "desc": np.zeros((nmp, 32), np.uint8)},
+        np.zeros(0, np.float32), np.ones(8, np.float32))
+    if not stereo:
+        ur = None
+    bi, bd = matcher.FuseSearch(F, mp, th, variant, ur, isg)
+    obi, obd = oracle.fuse_search(F, mp, th, variant, ur, isg)
+    assert np.array_equal(bi, obi) and np.array_equal(bd, obd)
+    if n >= 500 and nmp >= 1000:
+        assert (bi >= 0).sum() > 200
+
+
+def test_fuse_search_batched(matcher, oracle, synth):
+    Fs = [synth.frame_view(300 + 111 * i, seed=130 + i) for i in range(7)]
+    P = [synth.fuse_problem(F, 200 + 90 * i, 140 + i) for i, F in enumerate(Fs)]
+    res = matcher.FuseSearch(Fs, [p[0] for p in P], 3.0, 0, [p[1] for p in P], [p[2] for p in P])
+    for (bi, bd), F, p in zip(res, Fs, P):
+        obi, obd = oracle.fuse_search(F, p[0], 3.0, 0, p[1], p[2])
+        assert np.array_equal(bi, obi) and np.array_equal(bd, obd)

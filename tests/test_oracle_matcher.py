@@ -229,3 +229,54 @@ def test_search_by_bow_properties(oracle, synth):
         assert d <= 30            # TH_LOW (include/ORBmatcher.h:73)
     n2, m2 = oracle.search_by_bow(K1, K2, 0.7, True)
     assert n2 <= n and set(np.nonzero(m2 >= 0)[0]) <= set(np.nonzero(m >= 0)[0])
+
+
+def test_fuse_search_vs_numpy(oracle, synth):
+    """Fuse search core (reference src/ORBmatcher.cc:762-824) against a brute-force restatement."""
+    F = synth.frame_view(600, seed=61)
+    mp, ur, isg = synth.fuse_problem(F, 500, 62)
+    bi, bd = oracle.fuse_search(F, mp, 3.0, 0, ur, isg)
+    ncell = F["gcols"] * F["grows"]
+    hits = 0
+    for i in range(len(mp["u"])):
+        if not mp["valid"][i]:
+            assert bi[i] == -1
+            continue
+        lvl = mp["level"][i]
+        r = np.float32(3.0) * F["scale"][lvl]
+        best, bidx = 256, -1
+        # the reference visits the cells of the window's cell range (columns, then rows), keypoints in index order
+        lo = lambda c, inv: max(0, int(np.floor(np.float32(np.float32(np.float32(c) - r) * np.float32(inv)))))
+        hi = lambda c, inv, m: min(m - 1, int(np.ceil(np.float32(np.float32(np.float32(c) + r) * np.float32(inv)))))
+        c0, c1 = lo(mp["u"][i], F["gw_inv"]), hi(mp["u"][i], F["gw_inv"], F["gcols"])
+        r0, r1 = lo(mp["v"][i], F["gh_inv"]), hi(mp["v"][i], F["gh_inv"], F["grows"])
+        cand = []
+        for k in range(len(F["kx"])):
+            fx = np.float32(np.float32(F["kx"][k] - np.float32(F["minx"])) * np.float32(F["gw_inv"]))
+            fy = np.float32(np.float32(F["ky"][k] - np.float32(F["miny"])) * np.float32(F["gh_inv"]))
+            px, py = int(np.floor(abs(float(fx)) + 0.5) * np.sign(fx)), int(np.floor(abs(float(fy)) + 0.5) * np.sign(fy))
+            lin = py * F["gcols"] + px
+            if not (0 <= lin < ncell):
+                continue
+            if abs(np.float32(F["kx"][k] - mp["u"][i])) < r and abs(np.float32(F["ky"][k] - mp["v"][i])) < r:
+                if c0 <= lin % F["gcols"] <= c1 and r0 <= lin // F["gcols"] <= r1:
+                    cand.append((lin % F["gcols"], lin // F["gcols"], k))
+        for _, _, k in sorted(cand):
+            if F["koct"][k] < lvl - 1 or F["koct"][k] > lvl:
+                continue
+            ex = np.float32(mp["u"][i] - F["kx"][k]); ey = np.float32(mp["v"][i] - F["ky"][k])
+            if ur[k] >= 0:
+                er = np.float32(mp["ur"][i] - ur[k])
+                e2 = np.float32(np.float32(np.float32(ex * ex) + np.float32(ey * ey)) + np.float32(er * er))
+                if float(np.float32(e2 * isg[F["koct"][k]])) > 7.8:
+                    continue
+            else:
+                e2 = np.float32(np.float32(ex * ex) + np.float32(ey * ey))
+                if float(np.float32(e2 * isg[F["koct"][k]])) > 5.99:
+                    continue
+            d = int(np.unpackbits(mp["desc"][i] ^ F["desc"][k]).sum())
+            if d < best:
+                best, bidx = d, k
+        assert bi[i] == (bidx if best <= 30 else -1) and bd[i] == (best if bidx >= 0 else -1)
+        hits += bi[i] >= 0
+    assert hits > 100
