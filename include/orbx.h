@@ -191,6 +191,16 @@ orbx_status orbx_fuse_search(orbx_matcher* m, int nprob, const orbx_frame_view* 
                              const float* const* inv_sigma2, const orbx_fuse_points* MP, float th, int variant,
                              int* const* best_idx, int* const* best_dist);
 
+/* ORBmatcher::SearchBySim3(pKF1, pKF2, vpMatches12, S12, th)   src/ORBmatcher.cc:977-1200.
+ * MP1in2[p] holds one entry per KeyFrame-1 keypoint: its map point projected into KeyFrame 2 with
+ * S21 (valid = 0 if there is none, it is bad or already matched, or it fails the checks of
+ * :1022-1050); MP2in1[p] the converse (:1084-1113).  match12[p][i1] = keypoint of KeyFrame 2 whose
+ * map point the reference stores in vpMatches12[i1] (both directed searches agree), else -1;
+ * nfound[p] = the return value. */
+orbx_status orbx_search_by_sim3(orbx_matcher* m, int nprob, const orbx_frame_view* KF1, const orbx_frame_view* KF2,
+                                const orbx_fuse_points* MP1in2, const orbx_fuse_points* MP2in1, float th,
+                                int* const* match12, int* nfound);
+
 /* MapPoint::ComputeDistinctiveDescriptors   src/MapPoint.cc:343-412, batched over nsets map points:
  * desc rows set_off[s] .. set_off[s+1] are the observation descriptors of map point s (set_off[0]
  * = 0); best[s] = row (within the set) with the least median Hamming distance to the set, first

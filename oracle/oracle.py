@@ -272,6 +272,19 @@ def fuse_search(KF, mp, th=3.0, variant=0, uright=None, inv_sigma2=None):
     return bi[:len(u)], bd[:len(u)]
 
 
+def search_by_sim3(KF1, KF2, mp1in2, mp2in1, th=7.5):
+    keep = []
+    a, b = _frame_view(KF1, keep), _frame_view(KF2, keep)
+    args = []
+    for mp in (mp1in2, mp2in1):
+        arrs = [_u8(mp["valid"]), _f32(mp["u"]), _f32(mp["v"]), _i32(mp["level"]), _u8(mp["desc"])]
+        keep += arrs
+        args += [_p(x) for x in arrs]
+    out = np.empty(max(a.n, 1), np.int32)
+    n = lib().orc_search_by_sim3(C.byref(a), C.byref(b), *args, C.c_float(th), _p(out))
+    return n, out[:a.n]
+
+
 def search_by_bow(KF, F, nnRatio=0.7, checkOrientation=True, nleft=-1):
     keep = []
     a, b = _kf_view(KF, keep), _kf_view(F, keep)

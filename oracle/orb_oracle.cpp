@@ -837,9 +837,9 @@ int orc_search_by_projection_kf(const orc_frame_view* F, const float* fangle, in
     return nmatches;
 }
 
-void orc_fuse_search(const orc_frame_view* KF, const float* uright, const float* inv_sigma2, int nmp,
-                     const uint8_t* valid, const float* mu, const float* mv, const float* mur, const int* mlevel,
-                     const uint8_t* mdesc, float th, int variant, int* best_idx, int* best_dist) {
+static void fuse_search_impl(const orc_frame_view* KF, const float* uright, const float* inv_sigma2, int nmp,
+                             const uint8_t* valid, const float* mu, const float* mv, const float* mur, const int* mlevel,
+                             const uint8_t* mdesc, float th, int variant, int accept, int* best_idx, int* best_dist) {
     /* search core of Fuse, src/ORBmatcher.cc:762-824 (variant 0) and :919-956 (variant 1);
      * KeyFrame::GetFeaturesInArea (src/KeyFrame.cc:790-833) has no octave filter */
     const std::vector<std::vector<int>> grid = build_grid(KF);
@@ -873,8 +873,36 @@ void orc_fuse_search(const orc_frame_view* KF, const float* uright, const float*
             if (dist < bestDist) { bestDist = dist; bestIdx = idx; }
         }
         if (bestIdx >= 0) best_dist[i] = bestDist;
-        if (bestDist <= TH_LOW) best_idx[i] = bestIdx;
+        if (bestDist <= accept) best_idx[i] = bestIdx;
     }
+}
+
+void orc_fuse_search(const orc_frame_view* KF, const float* uright, const float* inv_sigma2, int nmp,
+                     const uint8_t* valid, const float* mu, const float* mv, const float* mur, const int* mlevel,
+                     const uint8_t* mdesc, float th, int variant, int* best_idx, int* best_dist) {
+    fuse_search_impl(KF, uright, inv_sigma2, nmp, valid, mu, mv, mur, mlevel, mdesc, th, variant, TH_LOW, best_idx, best_dist);
+}
+
+int orc_search_by_sim3(const orc_frame_view* KF1, const orc_frame_view* KF2,
+                       const uint8_t* valid1, const float* u1in2, const float* v1in2, const int* level1, const uint8_t* desc1,
+                       const uint8_t* valid2, const float* u2in1, const float* v2in1, const int* level2, const uint8_t* desc2,
+                       float th, int* match12) {
+    /* src/ORBmatcher.cc:977-1200 after the projections: vnMatch1 / vnMatch2 with bestDist <= TH_HIGH
+     * (:1076-1079, :1140-1143), then the agreement check (:1148-1163) */
+    const int N1 = KF1->n, N2 = KF2->n;
+    std::vector<int> vnMatch1(std::max(N1, 1), -1), vnMatch2(std::max(N2, 1), -1), d1(std::max(N1, 1)), d2(std::max(N2, 1));
+    fuse_search_impl(KF2, nullptr, nullptr, N1, valid1, u1in2, v1in2, nullptr, level1, desc1, th, 1, TH_HIGH, vnMatch1.data(), d1.data());
+    fuse_search_impl(KF1, nullptr, nullptr, N2, valid2, u2in1, v2in1, nullptr, level2, desc2, th, 1, TH_HIGH, vnMatch2.data(), d2.data());
+    int nFound = 0;
+    for (int i1 = 0; i1 < N1; i1++) {
+        match12[i1] = -1;
+        const int idx2 = vnMatch1[i1];
+        if (idx2 >= 0) {
+            const int idx1 = vnMatch2[idx2];
+            if (idx1 == i1) { match12[i1] = idx2; nFound++; }
+        }
+    }
+    return nFound;
 }
 
 int orc_search_by_bow(const orc_kf_view* KF, const orc_kf_view* F, int Nleft, float nnRatio,

@@ -154,6 +154,14 @@ void orc_fuse_search(const orc_frame_view* KF, const float* uright, const float*
                      const uint8_t* valid, const float* mu, const float* mv, const float* mur, const int* mlevel,
                      const uint8_t* mdesc, float th, int variant, int* best_idx, int* best_dist);
 
+/* SearchBySim3 (ORBmatcher.cc:977-1200) after the host-side projections: per KF1 keypoint its map
+ * point projected into KF2 (valid, u, v, predicted level, descriptor) and the converse;
+ * match12[i1] = keypoint of KF2 on agreement, else -1; returns nFound. */
+int orc_search_by_sim3(const orc_frame_view* KF1, const orc_frame_view* KF2,
+                       const uint8_t* valid1, const float* u1in2, const float* v1in2, const int* level1, const uint8_t* desc1,
+                       const uint8_t* valid2, const float* u2in1, const float* v2in1, const int* level2, const uint8_t* desc2,
+                       float th, int* match12);
+
 /* SearchByBoW(KeyFrame, Frame, ...) ORBmatcher.cc:133-327: F is flattened like a keyframe (angles,
  * descriptors, feature vector); match_kf[i] (F->n entries) = KeyFrame keypoint whose MapPoint goes
  * to Frame keypoint i, or -1.  Nleft = F->Nleft (-1: one camera). */

@@ -1445,7 +1445,7 @@ extern "C" orbx_status orbx_search_by_bow(orbx_matcher* m, int nprob, const orbx
  * Map points are independent (the graph updates of :826-848 stay with the caller, applied in
  * order), so: CTA per problem, grid CSR in shared memory, one thread per map point. */
 struct FuseProb {
-    int n, nmp, gcols, grows, nlevels, variant, has_ur, pad;
+    int n, nmp, gcols, grows, nlevels, variant, has_ur, accept;   /* accept: TH_LOW (Fuse) or TH_HIGH (SearchBySim3) */
     float minx, miny, gw_inv, gh_inv, th, pad1, pad2, pad3;
     unsigned long long kx, ky, koct, desc, uright, scale, inv_sigma2;
     unsigned long long mvalid, mu, mv, mur, mlevel, mdesc;
@@ -1545,14 +1545,14 @@ __global__ void __launch_bounds__(MT) k_fuse_search(const uint8_t* __restrict__ 
                 }
             }
         }
-        oidx[i] = bestDist <= TH_LOW ? bestIdx : -1;
+        oidx[i] = bestDist <= P.accept ? bestIdx : -1;
         odist[i] = bestIdx >= 0 ? bestDist : -1;
     }
 }
 
-extern "C" orbx_status orbx_fuse_search(orbx_matcher* m, int nprob, const orbx_frame_view* KF, const float* const* uright,
-                                        const float* const* inv_sigma2, const orbx_fuse_points* MP, float th, int variant,
-                                        int* const* best_idx, int* const* best_dist) {
+static orbx_status run_fuse(orbx_matcher* m, int nprob, const orbx_frame_view* KF, const float* const* uright,
+                            const float* const* inv_sigma2, const orbx_fuse_points* MP, float th, int variant, int accept,
+                            int* const* best_idx, int* const* best_dist) {
     if (!m || nprob < 0 || (nprob > 0 && (!KF || !MP || !best_idx)) || (variant != 0 && variant != 1)) { orbx_set_error("invalid argument"); return ORBX_ERR_INVALID; }
     if (nprob == 0) return ORBX_OK;
     ORBX_CUDA(cudaSetDevice(m->device));
@@ -1573,7 +1573,7 @@ extern "C" orbx_status orbx_fuse_search(orbx_matcher* m, int nprob, const orbx_f
         for (int i = 0; i < M.n; ++i)
             if (M.valid[i] && (M.level[i] < 0 || M.level[i] >= f.nlevels)) { orbx_set_error("problem %d: map point %d level out of range", p, i); return ORBX_ERR_INVALID; }
         const float* ur = uright ? uright[p] : nullptr;
-        P.n = f.n; P.nmp = M.n; P.gcols = f.gcols; P.grows = f.grows; P.nlevels = f.nlevels; P.variant = variant;
+        P.n = f.n; P.nmp = M.n; P.gcols = f.gcols; P.grows = f.grows; P.nlevels = f.nlevels; P.variant = variant; P.accept = accept;
         P.has_ur = (ur != nullptr && M.ur != nullptr);
         P.minx = f.minx; P.miny = f.miny; P.gw_inv = f.gw_inv; P.gh_inv = f.gh_inv; P.th = th;
         P.kx = in.add(f.kx, 4 * (size_t)f.n); P.ky = in.add(f.ky, 4 * (size_t)f.n); P.koct = in.add(f.koct, 4 * (size_t)f.n);
@@ -1603,6 +1603,47 @@ extern "C" orbx_status orbx_fuse_search(orbx_matcher* m, int nprob, const orbx_f
             memcpy(best_idx[p], m->h_out + probs[p].out_idx, 4 * (size_t)MP[p].n);
             if (best_dist && best_dist[p]) memcpy(best_dist[p], m->h_out + probs[p].out_dist, 4 * (size_t)MP[p].n);
         }
+    }
+    return ORBX_OK;
+}
+
+extern "C" orbx_status orbx_fuse_search(orbx_matcher* m, int nprob, const orbx_frame_view* KF, const float* const* uright,
+                                        const float* const* inv_sigma2, const orbx_fuse_points* MP, float th, int variant,
+                                        int* const* best_idx, int* const* best_dist) {
+    return run_fuse(m, nprob, KF, uright, inv_sigma2, MP, th, variant, TH_LOW, best_idx, best_dist);
+}
+
+/* ORBmatcher::SearchBySim3(pKF1, pKF2, vpMatches12, S12, th), reference src/ORBmatcher.cc:977-1200:
+ * the two directed searches (:1022-1081 KF1 points in KF2, :1084-1145 KF2 points in KF1) are the
+ * Sim3 Fuse search with the TH_HIGH acceptance, run as 2*nprob problems of ONE launch; then the
+ * agreement check of :1148-1163. */
+extern "C" orbx_status orbx_search_by_sim3(orbx_matcher* m, int nprob, const orbx_frame_view* KF1, const orbx_frame_view* KF2,
+                                           const orbx_fuse_points* MP1in2, const orbx_fuse_points* MP2in1, float th,
+                                           int* const* match12, int* nfound) {
+    if (!m || nprob < 0 || (nprob > 0 && (!KF1 || !KF2 || !MP1in2 || !MP2in1 || !match12 || !nfound))) { orbx_set_error("null argument"); return ORBX_ERR_INVALID; }
+    if (nprob == 0) return ORBX_OK;
+    std::vector<orbx_frame_view> views(2 * (size_t)nprob);
+    std::vector<orbx_fuse_points> pts(2 * (size_t)nprob);
+    std::vector<std::vector<int>> res(2 * (size_t)nprob);
+    std::vector<int*> rp(2 * (size_t)nprob);
+    for (int p = 0; p < nprob; ++p) {
+        if (MP1in2[p].n != KF1[p].n || MP2in1[p].n != KF2[p].n) { orbx_set_error("problem %d: one (possibly invalid) map point per keypoint expected", p); return ORBX_ERR_INVALID; }
+        views[p] = KF2[p]; pts[p] = MP1in2[p];                       /* KF1's points searched in KF2 */
+        views[nprob + p] = KF1[p]; pts[nprob + p] = MP2in1[p];
+        res[p].assign(std::max(KF1[p].n, 1), -1); res[nprob + p].assign(std::max(KF2[p].n, 1), -1);
+        rp[p] = res[p].data(); rp[nprob + p] = res[nprob + p].data();
+    }
+    const orbx_status st = run_fuse(m, 2 * nprob, views.data(), nullptr, nullptr, pts.data(), th, 1, TH_HIGH, rp.data(), nullptr);
+    if (st != ORBX_OK) return st;
+    for (int p = 0; p < nprob; ++p) {
+        int n = 0;
+        for (int i1 = 0; i1 < KF1[p].n; ++i1) {
+            const int idx2 = res[p][i1];
+            const bool ok = idx2 >= 0 && res[nprob + p][idx2] == i1;
+            match12[p][i1] = ok ? idx2 : -1;
+            n += ok;
+        }
+        nfound[p] = n;
     }
     return ORBX_OK;
 }

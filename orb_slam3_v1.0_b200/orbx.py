@@ -67,6 +67,7 @@ def lib():
         L.orbx_extractor_assign_grid.argtypes = [C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, C.c_int]
         L.orbx_extractor_grid_fetch.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int]
         L.orbx_fuse_search.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_void_p, C.c_void_p]
+        L.orbx_search_by_sim3.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 4 + [C.c_float, C.c_void_p, C.c_void_p]
         L.orbx_search_by_bow.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_void_p, C.c_void_p]
         L.orbx_distinctive_descriptors.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 4
         L.orbx_assign_features_to_grid.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
@@ -468,6 +469,26 @@ class ORBmatcher:
                                    (C.c_void_p * len(MPs))(*[a.ctypes.data for a in bi]),
                                    (C.c_void_p * len(MPs))(*[a.ctypes.data for a in bd])))
         res = [(bi[p][:len(MPs[p]["u"])], bd[p][:len(MPs[p]["u"])]) for p in range(len(MPs))]
+        return res[0] if single else res
+
+    def SearchBySim3(self, KF1s, KF2s, MP1in2, MP2in1, th=7.5):
+        """ORBmatcher::SearchBySim3 after the host-side projections -> [(nfound, match12)]."""
+        single = isinstance(KF1s, dict)
+        if single:
+            KF1s, KF2s, MP1in2, MP2in1 = [KF1s], [KF2s], [MP1in2], [MP2in1]
+        keep = []
+        v1 = (_FrameView * len(KF1s))(*[_frame_view(f, keep) for f in KF1s])
+        v2 = (_FrameView * len(KF2s))(*[_frame_view(f, keep) for f in KF2s])
+
+        def pts(Ms):
+            return (_FusePoints * len(Ms))(*[_FusePoints(len(M["u"]), _arr(M["valid"], np.uint8, keep), _arr(M["u"], np.float32, keep),
+                                                         _arr(M["v"], np.float32, keep), None, _arr(M["level"], np.int32, keep),
+                                                         _arr(M["desc"], np.uint8, keep)) for M in Ms])
+        outs = [np.empty(max(len(f["kx"]), 1), np.int32) for f in KF1s]
+        nf = np.empty(len(KF1s), np.int32)
+        _ck(lib().orbx_search_by_sim3(self._h, len(KF1s), v1, v2, pts(MP1in2), pts(MP2in1), C.c_float(th),
+                                      (C.c_void_p * len(outs))(*[o.ctypes.data for o in outs]), _p(nf)))
+        res = [(int(nf[p]), outs[p][:len(KF1s[p]["kx"])]) for p in range(len(KF1s))]
         return res[0] if single else res
 
     def ComputeDistinctiveDescriptors(self, sets):

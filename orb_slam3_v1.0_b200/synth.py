@@ -173,3 +173,30 @@ def fuse_problem(F, nmp=1200, seed=4, jitter=1.5, flip_p=0.04, bf=47.9):
           "level": np.clip(F["koct"][src] + rng.integers(0, 2, nmp), 0, len(F["scale"]) - 1).astype(np.int32), "desc": desc}
     inv_sigma2 = (1.0 / (F["scale"].astype(np.float32) ** 2)).astype(np.float32)
     return mp, uright, inv_sigma2
+
+
+def sim3_problem(n1=900, n2=1000, seed=5, jitter=2.0, flip_p=0.05):
+    """Two KeyFrame views whose keypoints partly correspond, plus per-keypoint map points projected
+    into the other KeyFrame (ORBmatcher::SearchBySim3 after its projection loops)."""
+    rng = np.random.default_rng(seed)
+    K2 = frame_view(n2, seed=seed + 1)
+    src = rng.integers(0, n2, n1)
+    K1 = frame_view(n1, seed=seed + 2)
+    K1["kx"] = np.clip(K2["kx"][src] + rng.normal(0, 8, n1), 0, 751).astype(np.float32)
+    K1["ky"] = np.clip(K2["ky"][src] + rng.normal(0, 8, n1), 0, 479).astype(np.float32)
+    K1["koct"] = K2["koct"][src].copy()
+    K1["desc"] = _flip_bits(rng, K2["desc"][src], flip_p)
+    nl = len(K1["scale"])
+    mp1in2 = {"valid": (rng.random(n1) < 0.7).astype(np.uint8),
+              "u": (K2["kx"][src] + rng.normal(0, jitter, n1)).astype(np.float32),
+              "v": (K2["ky"][src] + rng.normal(0, jitter, n1)).astype(np.float32),
+              "level": np.clip(K1["koct"] + rng.integers(0, 2, n1), 0, nl - 1).astype(np.int32), "desc": K1["desc"].copy()}
+    inv = np.full(n2, -1, np.int64)
+    inv[src] = np.arange(n1)                      # some KF2 keypoints have a twin in KF1
+    has = inv >= 0
+    tw = np.where(has, inv, 0)
+    mp2in1 = {"valid": ((rng.random(n2) < 0.7) & has).astype(np.uint8),
+              "u": (K1["kx"][tw] + rng.normal(0, jitter, n2)).astype(np.float32),
+              "v": (K1["ky"][tw] + rng.normal(0, jitter, n2)).astype(np.float32),
+              "level": np.clip(K2["koct"] + rng.integers(0, 2, n2), 0, nl - 1).astype(np.int32), "desc": K2["desc"].copy()}
+    return K1, K2, mp1in2, mp2in1

@@ -334,3 +334,22 @@ def test_fuse_search_batched(matcher, oracle, synth):
     for (bi, bd), F, p in zip(res, Fs, P):
         obi, obd = oracle.fuse_search(F, p[0], 3.0, 0, p[1], p[2])
         assert np.array_equal(bi, obi) and np.array_equal(bd, obd)
+
+
+# ------------------------------------------------------------------ SearchBySim3
+@pytest.mark.parametrize("n1,n2,th,seed", [(900, 1000, 7.5, 151), (300, 120, 5.0, 152), (40, 50, 10.0, 153)])
+def test_search_by_sim3(matcher, oracle, synth, n1, n2, th, seed):
+    K1, K2, a, b = synth.sim3_problem(n1, n2, seed)
+    n, m = matcher.SearchBySim3(K1, K2, a, b, th)
+    on, om = oracle.search_by_sim3(K1, K2, a, b, th)
+    assert n == on and np.array_equal(m, om)
+    if n1 >= 300:
+        assert n > 10
+
+
+def test_search_by_sim3_batched(matcher, oracle, synth):
+    P = [synth.sim3_problem(200 + 70 * i, 260 + 50 * i, 160 + i) for i in range(6)]
+    res = matcher.SearchBySim3([p[0] for p in P], [p[1] for p in P], [p[2] for p in P], [p[3] for p in P], 7.5)
+    for (n, m), p in zip(res, P):
+        on, om = oracle.search_by_sim3(*p, 7.5)
+        assert n == on and np.array_equal(m, om)
