@@ -201,6 +201,14 @@ orbx_status orbx_search_by_sim3(orbx_matcher* m, int nprob, const orbx_frame_vie
                                 const orbx_fuse_points* MP1in2, const orbx_fuse_points* MP2in1, float th,
                                 int* const* match12, int* nfound);
 
+/* ORBmatcher::SearchForInitialization(F1, F2, windowSize, nnRatio, checkOrientation)
+ * src/ORBmatcher.cc:329-439, nprob frame pairs per call.  Of F1 the keypoints (mvKeysUn x, y,
+ * octave, angle) and descriptors are read, of F2 also the grid.  matches12[p] (F1[p].n entries) =
+ * vnMatches12, nmatches[p] = the returned count. */
+orbx_status orbx_search_for_initialization(orbx_matcher* m, int nprob, const orbx_frame_view* F1, const orbx_frame_view* F2,
+                                           int windowSize, float nnRatio, int checkOrientation,
+                                           int* const* matches12, int* nmatches);
+
 /* MapPoint::ComputeDistinctiveDescriptors   src/MapPoint.cc:343-412, batched over nsets map points:
  * desc rows set_off[s] .. set_off[s+1] are the observation descriptors of map point s (set_off[0]
  * = 0); best[s] = row (within the set) with the least median Hamming distance to the set, first

@@ -65,6 +65,61 @@ public:
         for (int i = 0; i < np; ++i) vMatchedPairs.emplace_back((size_t)pairs[2 * i], (size_t)pairs[2 * i + 1]);
         return nm;
     }
+    /* src/ORBmatcher.cc:133-327; match_kf[i] = KeyFrame keypoint whose MapPoint goes to vpMapPointMatches[i], or -1 */
+    int SearchByBoW(const orbx_kf_view& KF, const orbx_kf_view& F, int Nleft, float nnRatio, bool checkOrientation,
+                    std::vector<int>& match_kf) {
+        match_kf.assign(F.n > 0 ? F.n : 1, -1);
+        int* out = match_kf.data();
+        int n = 0;
+        check(orbx_search_by_bow(m_, 1, &KF, &F, &Nleft, nnRatio, checkOrientation, &out, &n));
+        match_kf.resize(F.n);
+        return n;
+    }
+    /* src/ORBmatcher.cc:329-439 -> {nmatches, vnMatches12} */
+    std::pair<int, std::vector<int>> SearchForInitialization(const orbx_frame_view& F1, const orbx_frame_view& F2, int windowSize,
+                                                             float nnRatio, bool checkOrientation) {
+        std::vector<int> m12(F1.n > 0 ? F1.n : 1, -1);
+        int* out = m12.data();
+        int n = 0;
+        check(orbx_search_for_initialization(m_, 1, &F1, &F2, windowSize, nnRatio, checkOrientation, &out, &n));
+        m12.resize(F1.n);
+        return {n, m12};
+    }
+    /* search core of both Fuse overloads (src/ORBmatcher.cc:678-862 variant 0, :864-975 variant 1): best_idx[i] =
+     * KeyFrame keypoint for map point i or -1; the caller applies Replace / AddObservation in order */
+    void FuseSearch(const orbx_frame_view& KF, const float* mvuRight, const float* mvInvLevelSigma2, const orbx_fuse_points& MP,
+                    float th, int variant, std::vector<int>& best_idx) {
+        best_idx.assign(MP.n > 0 ? MP.n : 1, -1);
+        int* out = best_idx.data();
+        check(orbx_fuse_search(m_, 1, &KF, mvuRight ? &mvuRight : nullptr, mvInvLevelSigma2 ? &mvInvLevelSigma2 : nullptr, &MP, th,
+                               variant, &out, nullptr));
+        best_idx.resize(MP.n);
+    }
+    /* src/ORBmatcher.cc:977-1200; match12[i1] = keypoint of KF2 whose MapPoint goes to vpMatches12[i1], or -1 */
+    int SearchBySim3(const orbx_frame_view& KF1, const orbx_frame_view& KF2, const orbx_fuse_points& MP1in2,
+                     const orbx_fuse_points& MP2in1, float th, std::vector<int>& match12) {
+        match12.assign(KF1.n > 0 ? KF1.n : 1, -1);
+        int* out = match12.data();
+        int n = 0;
+        check(orbx_search_by_sim3(m_, 1, &KF1, &KF2, &MP1in2, &MP2in1, th, &out, &n));
+        match12.resize(KF1.n);
+        return n;
+    }
+    /* src/MapPoint.cc:343-412 for one map point's observation descriptors (N x 32): index of the distinctive one */
+    int ComputeDistinctiveDescriptor(const uint8_t* descriptors, int N) {
+        const int off[2] = {0, N};
+        int best = -1;
+        check(orbx_distinctive_descriptors(m_, 1, off, descriptors, &best, nullptr));
+        return best;
+    }
+    /* src/Frame.cc:157-176: CSR grid (cell_off[cols*rows+1], cell_idx[n]) */
+    void AssignFeaturesToGrid(const orbx_frame_view& F, std::vector<int>& cell_off, std::vector<int>& cell_idx) {
+        cell_off.assign((size_t)F.gcols * F.grows + 1, 0);
+        cell_idx.assign(F.n > 0 ? F.n : 1, -1);
+        int *po = cell_off.data(), *pi = cell_idx.data();
+        check(orbx_assign_features_to_grid(m_, 1, &F, &po, &pi));
+        cell_idx.resize(F.n);
+    }
     orbx_matcher* handle() { return m_; }
 
 private:

@@ -285,6 +285,16 @@ def search_by_sim3(KF1, KF2, mp1in2, mp2in1, th=7.5):
     return n, out[:a.n]
 
 
+def search_for_initialization(F1, F2, windowSize=100, nnRatio=0.9, checkOrientation=True):
+    keep = []
+    a, b = _frame_view(F1, keep), _frame_view(F2, keep)
+    a1, a2 = _f32(F1["kangle"]), _f32(F2["kangle"])
+    out = np.empty(max(a.n, 1), np.int32)
+    n = lib().orc_search_for_initialization(C.byref(a), _p(a1), C.byref(b), _p(a2), int(windowSize), C.c_float(nnRatio),
+                                            int(checkOrientation), _p(out))
+    return n, out[:a.n]
+
+
 def search_by_bow(KF, F, nnRatio=0.7, checkOrientation=True, nleft=-1):
     keep = []
     a, b = _kf_view(KF, keep), _kf_view(F, keep)

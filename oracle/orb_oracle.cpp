@@ -905,6 +905,62 @@ int orc_search_by_sim3(const orc_frame_view* KF1, const orc_frame_view* KF2,
     return nFound;
 }
 
+int orc_search_for_initialization(const orc_frame_view* F1, const float* angle1, const orc_frame_view* F2,
+                                  const float* angle2, int windowSize, float nnRatio, int checkOrientation,
+                                  int* vnMatches12) {
+    /* src/ORBmatcher.cc:329-439 */
+    int nmatches = 0;
+    for (int i = 0; i < F1->n; ++i) vnMatches12[i] = -1;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = 1.0f / HISTO_LENGTH;
+    std::vector<int> vMatchedDistance(F2->n, INT_MAX), vnMatches21(F2->n, -1);
+    const std::vector<std::vector<int>> grid = build_grid(F2);
+    std::vector<int> vIndices2;
+    for (int i1 = 0; i1 < F1->n; i1++) {
+        const int level1 = F1->koct[i1];
+        if (level1 > 0) continue;
+        features_in_area(F2, grid, F1->kx[i1], F1->ky[i1], (float)windowSize, level1, level1, vIndices2);
+        if (vIndices2.empty()) continue;
+        const uint8_t* d1 = F1->desc + (size_t)i1 * 32;
+        int bestDist = INT_MAX, bestDist2 = INT_MAX, bestIdx2 = -1;
+        for (int i2 : vIndices2) {
+            const int dist = orc_descriptor_distance(d1, F2->desc + (size_t)i2 * 32);
+            if (vMatchedDistance[i2] <= dist) continue;
+            if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestIdx2 = i2; }
+            else if (dist < bestDist2) bestDist2 = dist;
+        }
+        if (bestDist <= TH_LOW) {
+            if (bestDist < (float)bestDist2 * nnRatio) {
+                if (vnMatches21[bestIdx2] >= 0) { vnMatches12[vnMatches21[bestIdx2]] = -1; nmatches--; }
+                vnMatches12[i1] = bestIdx2;
+                vnMatches21[bestIdx2] = i1;
+                vMatchedDistance[bestIdx2] = bestDist;
+                nmatches++;
+                if (checkOrientation) {
+                    float rot = angle1[i1] - angle2[bestIdx2];
+                    if (rot < 0.0) rot += 360.0f;
+                    int bin = (int)roundf(rot * factor);
+                    if (bin == HISTO_LENGTH) bin = 0;
+                    rotHist[bin].push_back(i1);
+                }
+            }
+        }
+    }
+    if (checkOrientation) {
+        int counts[HISTO_LENGTH], ind1, ind2, ind3;
+        for (int i = 0; i < HISTO_LENGTH; i++) counts[i] = (int)rotHist[i].size();
+        orc_three_maxima(counts, HISTO_LENGTH, &ind1, &ind2, &ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (size_t j = 0; j < rotHist[i].size(); j++) {
+                const int idx1 = rotHist[i][j];
+                if (vnMatches12[idx1] >= 0) { vnMatches12[idx1] = -1; nmatches--; }
+            }
+        }
+    }
+    return nmatches;
+}
+
 int orc_search_by_bow(const orc_kf_view* KF, const orc_kf_view* F, int Nleft, float nnRatio,
                       int checkOrientation, int* match_kf) {
     /* src/ORBmatcher.cc:133-327.  match_kf[i] = KeyFrame keypoint whose MapPoint lands in

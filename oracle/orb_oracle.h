@@ -162,6 +162,11 @@ int orc_search_by_sim3(const orc_frame_view* KF1, const orc_frame_view* KF2,
                        const uint8_t* valid2, const float* u2in1, const float* v2in1, const int* level2, const uint8_t* desc2,
                        float th, int* match12);
 
+/* SearchForInitialization ORBmatcher.cc:329-439: vnMatches12 (F1->n entries), returns nmatches. */
+int orc_search_for_initialization(const orc_frame_view* F1, const float* angle1, const orc_frame_view* F2,
+                                  const float* angle2, int windowSize, float nnRatio, int checkOrientation,
+                                  int* vnMatches12);
+
 /* SearchByBoW(KeyFrame, Frame, ...) ORBmatcher.cc:133-327: F is flattened like a keyframe (angles,
  * descriptors, feature vector); match_kf[i] (F->n entries) = KeyFrame keypoint whose MapPoint goes
  * to Frame keypoint i, or -1.  Nleft = F->Nleft (-1: one camera). */

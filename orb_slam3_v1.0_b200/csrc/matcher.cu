@@ -1647,3 +1647,194 @@ extern "C" orbx_status orbx_search_by_sim3(orbx_matcher* m, int nprob, const orb
     }
     return ORBX_OK;
 }
+
+/* ================================================================== SearchForInitialization */
+/* ORBmatcher::SearchForInitialization(F1, F2, windowSize, nnRatio, checkOrientation), reference
+ * src/ORBmatcher.cc:329-439.  The loop over F1's level-0 keypoints is inherently ordered (a later
+ * keypoint may only take an F2 keypoint with a strictly smaller distance than its current holder,
+ * and steals it), so one warp walks i1 in order; the candidate set of each i1 (F2 window, octave 0,
+ * vMatchedDistance filter) is evaluated by the 32 lanes with packed (distance, candidate order)
+ * keys.  CTA per frame pair; the other warps only help building F2's grid. */
+struct InitProb {
+    int n1, n2, gcols, grows, window, checkOri, pad0, pad1;
+    float minx, miny, gw_inv, gh_inv, nnRatio, pad2, pad3, pad4;
+    unsigned long long kx1, ky1, koct1, kang1, desc1;
+    unsigned long long kx2, ky2, koct2, kang2, desc2;
+    unsigned long long out_match;          /* [n1] vnMatches12 */
+};
+
+__global__ void __launch_bounds__(MT) k_search_for_initialization(const uint8_t* __restrict__ in, uint8_t* __restrict__ out,
+                                                                   const InitProb* __restrict__ probs, int* __restrict__ counts) {
+    extern __shared__ __align__(16) uint32_t sm[];
+    __shared__ uint32_t s_tmp[MT / 32];
+    __shared__ int s_hist[HISTO_LENGTH];
+    const InitProb P = probs[blockIdx.x];
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int n1 = P.n1, n2 = P.n2, ncell = P.gcols * P.grows;
+    const float* kx1 = reinterpret_cast<const float*>(in + P.kx1);
+    const float* ky1 = reinterpret_cast<const float*>(in + P.ky1);
+    const int* koct1 = reinterpret_cast<const int*>(in + P.koct1);
+    const float* kang1 = reinterpret_cast<const float*>(in + P.kang1);
+    const uint4* desc1 = reinterpret_cast<const uint4*>(in + P.desc1);
+    const float* kx2 = reinterpret_cast<const float*>(in + P.kx2);
+    const float* ky2 = reinterpret_cast<const float*>(in + P.ky2);
+    const int* koct2 = reinterpret_cast<const int*>(in + P.koct2);
+    const float* kang2 = reinterpret_cast<const float*>(in + P.kang2);
+    const uint4* desc2 = reinterpret_cast<const uint4*>(in + P.desc2);
+    int* match12 = reinterpret_cast<int*>(out + P.out_match);
+
+    uint32_t* cell_start = sm;                        /* [ncell + 1], column-major cells */
+    uint32_t* cell_fill = cell_start + ncell + 1;     /* [ncell] */
+    int* matched_dist = reinterpret_cast<int*>(cell_fill + ncell);   /* [n2] vMatchedDistance */
+    int* match21 = matched_dist + n2;                 /* [n2] vnMatches21 */
+    unsigned short* csr = reinterpret_cast<unsigned short*>(match21 + n2);   /* [n2] */
+    signed char* claim_bin = reinterpret_cast<signed char*>(csr + n2 + (n2 & 1));   /* [n1] rotHist bin of i1's claim, -1: none */
+
+    for (int i = tid; i <= ncell; i += MT) cell_start[i] = 0;
+    if (tid < HISTO_LENGTH) s_hist[tid] = 0;
+    for (int i = tid; i < n2; i += MT) { matched_dist[i] = 0x7fffffff; match21[i] = -1; }
+    for (int i = tid; i < n1; i += MT) { match12[i] = -1; claim_bin[i] = -1; }
+    __syncthreads();
+    for (int i = tid; i < n2; i += MT) {
+        const int px = (int)roundf((kx2[i] - P.minx) * P.gw_inv), py = (int)roundf((ky2[i] - P.miny) * P.gh_inv);
+        const int lin = py * P.gcols + px;
+        if (lin >= 0 && lin < ncell) atomicAdd(&cell_start[(lin % P.gcols) * P.grows + lin / P.gcols], 1u);
+    }
+    __syncthreads();
+    mt_excl_scan(cell_start, ncell + 1, s_tmp);
+    for (int i = tid; i < ncell; i += MT) cell_fill[i] = cell_start[i];
+    __syncthreads();
+    for (int i = tid; i < n2; i += MT) {
+        const int px = (int)roundf((kx2[i] - P.minx) * P.gw_inv), py = (int)roundf((ky2[i] - P.miny) * P.gh_inv);
+        const int lin = py * P.gcols + px;
+        if (lin >= 0 && lin < ncell) csr[atomicAdd(&cell_fill[(lin % P.gcols) * P.grows + lin / P.gcols], 1u)] = (unsigned short)i;
+    }
+    __syncthreads();
+    for (int c = tid; c < ncell; c += MT) {
+        const int e0 = (int)cell_start[c], e1 = (int)cell_start[c + 1];
+        for (int a = e0 + 1; a < e1; ++a) {
+            const unsigned short v = csr[a];
+            int b = a - 1;
+            while (b >= e0 && csr[b] > v) { csr[b + 1] = csr[b]; --b; }
+            csr[b + 1] = v;
+        }
+    }
+    __syncthreads();
+
+    int nmatches = 0;
+    if (tid < 32) {
+        const float r = (float)P.window;
+        for (int i1 = 0; i1 < n1; ++i1) {
+            if (koct1[i1] > 0) continue;                                   /* level1 > 0 */
+            const float x = kx1[i1], y = ky1[i1];
+            /* F2->GetFeaturesInArea(x, y, windowSize, 0, 0): octave 0 only (src/Frame.cc:404-468) */
+            const int c0 = max(0, (int)floorf((x - P.minx - r) * P.gw_inv));
+            const int c1 = min(P.gcols - 1, (int)ceilf((x - P.minx + r) * P.gw_inv));
+            const int r0 = max(0, (int)floorf((y - P.miny - r) * P.gh_inv));
+            const int r1 = min(P.grows - 1, (int)ceilf((y - P.miny + r) * P.gh_inv));
+            if (c0 >= P.gcols || c1 < 0 || r0 >= P.grows || r1 < 0) continue;
+            const uint4 q0 = desc1[2 * i1], q1 = desc1[2 * i1 + 1];
+            unsigned long long b1 = ~0ull, b2 = ~0ull;                      /* this lane's two smallest keys */
+            for (int ix = c0; ix <= c1; ++ix) {
+                const uint32_t e0 = cell_start[ix * P.grows + r0], e1 = cell_start[ix * P.grows + r1 + 1];
+                for (uint32_t e = e0 + lane; e < e1; e += 32) {
+                    const int i2 = csr[e];
+                    if (koct2[i2] != 0) continue;
+                    if (!(fabsf(kx2[i2] - x) < r && fabsf(ky2[i2] - y) < r)) continue;
+                    const int dist = hamming256(q0, q1, desc2[2 * i2], desc2[2 * i2 + 1]);
+                    if (matched_dist[i2] <= dist) continue;
+                    const unsigned long long key = ((unsigned long long)dist << 32) | e;
+                    if (key < b1) { b2 = b1; b1 = key; }
+                    else if (key < b2) b2 = key;
+                }
+            }
+            /* warp: smallest key, and the second smallest distance counting duplicates */
+            unsigned long long g1 = b1;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) { const unsigned long long t = __shfl_xor_sync(0xffffffffu, g1, o); g1 = t < g1 ? t : g1; }
+            if (g1 == ~0ull) continue;                                      /* vIndices2 empty or all filtered: bestDist stays INT_MAX */
+            unsigned long long g2 = (b1 == g1) ? b2 : b1;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) { const unsigned long long t = __shfl_xor_sync(0xffffffffu, g2, o); g2 = t < g2 ? t : g2; }
+            const int bestDist = (int)(g1 >> 32), bestIdx2 = csr[(uint32_t)g1];
+            const int bestDist2 = g2 == ~0ull ? 0x7fffffff : (int)(g2 >> 32);
+            if (bestDist <= TH_LOW && (float)bestDist < (float)bestDist2 * P.nnRatio) {
+                if (lane == 0) {
+                    const int prev = match21[bestIdx2];
+                    if (prev >= 0) match12[prev] = -1;
+                    match12[i1] = bestIdx2;
+                    match21[bestIdx2] = i1;
+                    matched_dist[bestIdx2] = bestDist;
+                    if (P.checkOri) {
+                        const int bin = rot_bin(kang1[i1], kang2[bestIdx2]);
+                        claim_bin[i1] = (signed char)bin;
+                        s_hist[bin] += 1;
+                    }
+                }
+                __syncwarp();
+            }
+        }
+        if (P.checkOri && lane == 0) {
+            int ind1, ind2, ind3;
+            three_maxima(s_hist, HISTO_LENGTH, ind1, ind2, ind3);
+            for (int i = 0; i < n1; ++i) {
+                const int b = claim_bin[i];
+                if (b >= 0 && b != ind1 && b != ind2 && b != ind3 && match12[i] >= 0) match12[i] = -1;
+            }
+        }
+        __syncwarp();
+        for (int i = lane; i < n1; i += 32) nmatches += match12[i] >= 0;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) nmatches += __shfl_xor_sync(0xffffffffu, nmatches, o);
+        if (lane == 0) counts[blockIdx.x] = nmatches;
+    }
+}
+
+extern "C" orbx_status orbx_search_for_initialization(orbx_matcher* m, int nprob, const orbx_frame_view* F1, const orbx_frame_view* F2,
+                                                      int windowSize, float nnRatio, int checkOrientation,
+                                                      int* const* matches12, int* nmatches) {
+    if (!m || nprob < 0 || (nprob > 0 && (!F1 || !F2 || !matches12 || !nmatches))) { orbx_set_error("null argument"); return ORBX_ERR_INVALID; }
+    if (nprob == 0) return ORBX_OK;
+    ORBX_CUDA(cudaSetDevice(m->device));
+    Packer in, out;
+    std::vector<InitProb> probs(nprob);
+    size_t smem = 0;
+    for (int p = 0; p < nprob; ++p) {
+        const orbx_frame_view &A = F1[p], &B = F2[p];
+        InitProb& P = probs[p];
+        memset(&P, 0, sizeof(P));
+        if (A.n < 0 || B.n < 0 || B.n > 65535 || B.gcols < 1 || B.grows < 1 || (long long)B.gcols * B.grows > 20000 ||
+            (A.n > 0 && (!A.kx || !A.ky || !A.koct || !A.desc || (checkOrientation && !A.kangle))) ||
+            (B.n > 0 && (!B.kx || !B.ky || !B.koct || !B.desc || (checkOrientation && !B.kangle)))) {
+            orbx_set_error("problem %d: unsupported view or null array", p);
+            return ORBX_ERR_INVALID;
+        }
+        P.n1 = A.n; P.n2 = B.n; P.gcols = B.gcols; P.grows = B.grows; P.window = windowSize; P.checkOri = checkOrientation;
+        P.minx = B.minx; P.miny = B.miny; P.gw_inv = B.gw_inv; P.gh_inv = B.gh_inv; P.nnRatio = nnRatio;
+        P.kx1 = in.add(A.kx, 4 * (size_t)A.n); P.ky1 = in.add(A.ky, 4 * (size_t)A.n); P.koct1 = in.add(A.koct, 4 * (size_t)A.n);
+        P.kang1 = in.add(A.kangle, A.kangle ? 4 * (size_t)A.n : 0); P.desc1 = in.add(A.desc, 32 * (size_t)A.n);
+        P.kx2 = in.add(B.kx, 4 * (size_t)B.n); P.ky2 = in.add(B.ky, 4 * (size_t)B.n); P.koct2 = in.add(B.koct, 4 * (size_t)B.n);
+        P.kang2 = in.add(B.kangle, B.kangle ? 4 * (size_t)B.n : 0); P.desc2 = in.add(B.desc, 32 * (size_t)B.n);
+        P.out_match = out.add(nullptr, 4 * (size_t)std::max(A.n, 1));
+        smem = std::max(smem, (size_t)4 * (2 * (size_t)B.gcols * B.grows + 1) + 8 * (size_t)B.n + 2 * (size_t)(B.n + 1) + (size_t)A.n + 16);
+    }
+    const size_t probs_off = in.add(probs.data(), sizeof(InitProb) * (size_t)nprob);
+    const size_t counts_off = out.add(nullptr, 4 * (size_t)nprob);
+    if (smem > 200 * 1024) { orbx_set_error("frame grid + keypoints need %zu B of shared memory (> 200 KB)", smem); return ORBX_ERR_INVALID; }
+    orbx_status st = ensure_io(m, in.total, out.total);
+    if (st != ORBX_OK) return st;
+    in.copy_to(m->h_in);
+    ORBX_CUDA(cudaMemcpyAsync(m->d_in, m->h_in, in.total, cudaMemcpyHostToDevice, m->stream));
+    ORBX_CUDA(cudaFuncSetAttribute(k_search_for_initialization, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max(smem, (size_t)48 * 1024)));
+    k_search_for_initialization<<<nprob, MT, smem, m->stream>>>(m->d_in, m->d_out, reinterpret_cast<const InitProb*>(m->d_in + probs_off),
+                                                                reinterpret_cast<int*>(m->d_out + counts_off));
+    ORBX_CUDA(cudaGetLastError());
+    m->last_launches = 1;
+    ORBX_CUDA(cudaMemcpyAsync(m->h_out, m->d_out, out.total, cudaMemcpyDeviceToHost, m->stream));
+    ORBX_CUDA(cudaStreamSynchronize(m->stream));
+    for (int p = 0; p < nprob; ++p) {
+        if (F1[p].n > 0) memcpy(matches12[p], m->h_out + probs[p].out_match, 4 * (size_t)F1[p].n);
+        nmatches[p] = reinterpret_cast<const int*>(m->h_out + counts_off)[p];
+    }
+    return ORBX_OK;
+}

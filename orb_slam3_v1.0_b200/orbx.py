@@ -68,6 +68,7 @@ def lib():
         L.orbx_extractor_grid_fetch.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int]
         L.orbx_fuse_search.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_void_p, C.c_void_p]
         L.orbx_search_by_sim3.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 4 + [C.c_float, C.c_void_p, C.c_void_p]
+        L.orbx_search_for_initialization.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_void_p, C.c_void_p]
         L.orbx_search_by_bow.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_void_p, C.c_void_p]
         L.orbx_distinctive_descriptors.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 4
         L.orbx_assign_features_to_grid.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
@@ -489,6 +490,21 @@ class ORBmatcher:
         _ck(lib().orbx_search_by_sim3(self._h, len(KF1s), v1, v2, pts(MP1in2), pts(MP2in1), C.c_float(th),
                                       (C.c_void_p * len(outs))(*[o.ctypes.data for o in outs]), _p(nf)))
         res = [(int(nf[p]), outs[p][:len(KF1s[p]["kx"])]) for p in range(len(KF1s))]
+        return res[0] if single else res
+
+    def SearchForInitialization(self, F1s, F2s, windowSize=100, nnRatio=0.9, checkOrientation=True):
+        """ORBmatcher::SearchForInitialization -> [(nmatches, vnMatches12)]."""
+        single = isinstance(F1s, dict)
+        if single:
+            F1s, F2s = [F1s], [F2s]
+        keep = []
+        v1 = (_FrameView * len(F1s))(*[_frame_view(f, keep) for f in F1s])
+        v2 = (_FrameView * len(F2s))(*[_frame_view(f, keep) for f in F2s])
+        outs = [np.empty(max(len(f["kx"]), 1), np.int32) for f in F1s]
+        nm = np.empty(len(F1s), np.int32)
+        _ck(lib().orbx_search_for_initialization(self._h, len(F1s), v1, v2, int(windowSize), C.c_float(nnRatio), int(checkOrientation),
+                                                 (C.c_void_p * len(outs))(*[o.ctypes.data for o in outs]), _p(nm)))
+        res = [(int(nm[p]), outs[p][:len(F1s[p]["kx"])]) for p in range(len(F1s))]
         return res[0] if single else res
 
     def ComputeDistinctiveDescriptors(self, sets):

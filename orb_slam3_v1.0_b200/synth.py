@@ -200,3 +200,21 @@ def sim3_problem(n1=900, n2=1000, seed=5, jitter=2.0, flip_p=0.05):
               "v": (K1["ky"][tw] + rng.normal(0, jitter, n2)).astype(np.float32),
               "level": np.clip(K2["koct"] + rng.integers(0, 2, n2), 0, nl - 1).astype(np.int32), "desc": K2["desc"].copy()}
     return K1, K2, mp1in2, mp2in1
+
+
+def initialization_pair(n1=1000, n2=1000, seed=6, motion=25.0, flip_p=0.05, p_level0=0.45):
+    """Two consecutive frames for ORBmatcher::SearchForInitialization: F1's keypoints reappear in F2
+    displaced by up to `motion` px with slightly changed descriptors and angles; several F1
+    keypoints share a twin so the steal / vMatchedDistance logic is exercised."""
+    rng = np.random.default_rng(seed)
+    F2 = frame_view(n2, seed=seed + 1)
+    F2["koct"] = np.where(rng.random(n2) < p_level0, 0, F2["koct"]).astype(np.int32)
+    src = rng.integers(0, n2, n1)
+    src[n1 // 2:] = src[rng.integers(0, n1 // 2, n1 - n1 // 2)]          # duplicates compete for the same F2 keypoint
+    F1 = frame_view(n1, seed=seed + 2)
+    F1["kx"] = np.clip(F2["kx"][src] + rng.uniform(-motion, motion, n1), 0, 751).astype(np.float32)
+    F1["ky"] = np.clip(F2["ky"][src] + rng.uniform(-motion, motion, n1), 0, 479).astype(np.float32)
+    F1["koct"] = np.where(rng.random(n1) < 0.9, F2["koct"][src], rng.integers(0, 8, n1)).astype(np.int32)
+    F1["kangle"] = ((F2["kangle"][src] + rng.normal(0, 8, n1)) % 360).astype(np.float32)
+    F1["desc"] = _flip_bits(rng, F2["desc"][src], flip_p * rng.uniform(0.2, 2.0, (n1, 1)))
+    return F1, F2

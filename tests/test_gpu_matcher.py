@@ -353,3 +353,33 @@ def test_search_by_sim3_batched(matcher, oracle, synth):
     for (n, m), p in zip(res, P):
         on, om = oracle.search_by_sim3(*p, 7.5)
         assert n == on and np.array_equal(m, om)
+
+
+# ------------------------------------------------------------------ SearchForInitialization
+@pytest.mark.parametrize("n1,n2,win,ratio,ori,seed", [
+    (1000, 1000, 100, 0.9, True, 171), (1000, 1000, 100, 0.9, False, 172), (400, 700, 50, 0.8, True, 173),
+    (30, 25, 100, 0.9, True, 174), (0, 20, 100, 0.9, True, 175), (20, 0, 100, 0.9, True, 176),
+])
+def test_search_for_initialization(matcher, oracle, synth, n1, n2, win, ratio, ori, seed):
+    F1, F2 = synth.initialization_pair(max(n1, 2), max(n2, 2), seed)
+    if n1 == 0:
+        for k in ("kx", "ky", "koct", "kangle"):
+            F1[k] = F1[k][:0]
+        F1["desc"] = F1["desc"][:0]
+    if n2 == 0:
+        for k in ("kx", "ky", "koct", "kangle"):
+            F2[k] = F2[k][:0]
+        F2["desc"] = F2["desc"][:0]
+    n, m = matcher.SearchForInitialization(F1, F2, win, ratio, ori)
+    on, om = oracle.search_for_initialization(F1, F2, win, ratio, ori)
+    assert n == on and np.array_equal(m, om)
+    if n1 >= 400:
+        assert n > 30
+
+
+def test_search_for_initialization_batched(matcher, oracle, synth):
+    P = [synth.initialization_pair(300 + 80 * i, 350 + 60 * i, 180 + i) for i in range(6)]
+    res = matcher.SearchForInitialization([p[0] for p in P], [p[1] for p in P], 100, 0.9, True)
+    for (n, m), p in zip(res, P):
+        on, om = oracle.search_for_initialization(p[0], p[1], 100, 0.9, True)
+        assert n == on and np.array_equal(m, om)

@@ -280,3 +280,19 @@ def test_fuse_search_vs_numpy(oracle, synth):
         assert bi[i] == (bidx if best <= 30 else -1) and bd[i] == (best if bidx >= 0 else -1)
         hits += bi[i] >= 0
     assert hits > 100
+
+
+def test_search_for_initialization_properties(oracle, synth):
+    """SearchForInitialization (reference src/ORBmatcher.cc:329-439): only level-0 keypoints match,
+    inside the window, one-to-one, with the stolen keypoints released."""
+    F1, F2 = synth.initialization_pair(800, 800, 71)
+    n, m = oracle.search_for_initialization(F1, F2, 100, 0.9, False)
+    idx1 = np.nonzero(m >= 0)[0]
+    assert n == len(idx1) and n > 50
+    assert len(set(m[idx1])) == n                                    # vnMatches21 keeps it one-to-one
+    assert (F1["koct"][idx1] == 0).all() and (F2["koct"][m[idx1]] == 0).all()
+    assert (np.abs(F1["kx"][idx1] - F2["kx"][m[idx1]]) < 100).all() and (np.abs(F1["ky"][idx1] - F2["ky"][m[idx1]]) < 100).all()
+    d = np.unpackbits(F1["desc"][idx1] ^ F2["desc"][m[idx1]], axis=1).sum(1)
+    assert (d <= 30).all()
+    n2, m2 = oracle.search_for_initialization(F1, F2, 100, 0.9, True)
+    assert n2 <= n and set(np.nonzero(m2 >= 0)[0]) <= set(idx1)
