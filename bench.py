@@ -182,6 +182,32 @@ def matching_bench(pkg, torch, local, ex, B):
     out["search_by_projection"] = {"problems_per_s": len(Fs) / dt, "matches_per_s": float(nm.sum()) / dt,
                                    "ms_per_call": dt * 1e3, "problems_per_call": len(Fs),
                                    "note": "through the C ABI with host buffers (packing + H2D + kernel + D2H)"}
+    # ---- the widened matcher entry points, 32 problems per call through the C ABI
+    def timed(fn, nprob, reps=5):
+        fn()
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            fn()
+        dt = (time.perf_counter() - t0) / reps
+        return {"problems_per_s": nprob / dt, "ms_per_call": dt * 1e3, "problems_per_call": nprob}
+    sy = pkg.synth
+    kfp = [sy.keyframe_pair(1000, 1100, 90, 300 + i) for i in range(4)]
+    for i, p in enumerate(kfp):
+        p[0]["has_mp"] = (np.random.default_rng(i).random(1000) < 0.8).astype(np.uint8)
+    K1s, K2s = [p[0] for p in kfp] * 8, [p[1] for p in kfp] * 8
+    out["search_by_bow"] = timed(lambda: m.SearchByBoW(K1s, K2s, 0.7, True), len(K1s))
+    fz = [sy.fuse_problem(F, 1200, 400 + i) for i, F in enumerate(Fs[:4])]
+    FF, FM = Fs[:4] * 8, [p[0] for p in fz] * 8
+    FU, FI = [p[1] for p in fz] * 8, [p[2] for p in fz] * 8
+    out["fuse_search"] = timed(lambda: m.FuseSearch(FF, FM, 3.0, 0, FU, FI), len(FF))
+    s3 = [sy.sim3_problem(900, 1000, 500 + i) for i in range(4)] * 8
+    out["search_by_sim3"] = timed(lambda: m.SearchBySim3([p[0] for p in s3], [p[1] for p in s3], [p[2] for p in s3], [p[3] for p in s3], 7.5), len(s3))
+    ini = [sy.initialization_pair(1000, 1000, 600 + i) for i in range(4)] * 8
+    out["search_for_initialization"] = timed(lambda: m.SearchForInitialization([p[0] for p in ini], [p[1] for p in ini], 100, 0.9, True), len(ini))
+    rng = np.random.default_rng(7)
+    sets = [rng.integers(0, 256, (int(k), 32), dtype=np.uint8) for k in rng.integers(3, 40, 2000)]
+    out["distinctive_descriptors"] = timed(lambda: m.ComputeDistinctiveDescriptors(sets), len(sets))
+    out["search_by_bow"]["note"] = "all through the C ABI with host buffers; Python-side view construction included"
     # ---- brute-force 2-NN: 16384 queries x 1M database rows, device resident
     nq, ndb = 16384, 1 << 20
     g = torch.Generator(device=dev); g.manual_seed(5)
