@@ -152,3 +152,25 @@ def test_cpp_shim_matches_oracle(pkg, oracle, synth, tmp_path):
     _compare_frame(None, oex, img, (0, 0), got=(kps, desc, int(mono)))
     assert np.array_equal(lvl1, oex.level(1)) and nsf == 8
     assert d01 == oracle.descriptor_distance(desc[0], desc[1])
+
+
+@pytest.mark.parametrize("w,h,nf,scale,nl,ini,mn,seed", [
+    (640, 480, 1200, 1.1, 12, 20, 7, 201),        # many shallow levels
+    (640, 480, 800, 1.5, 4, 20, 7, 202),          # few steep levels
+    (512, 384, 500, 1.2, 8, 40, 40, 203),         # iniThFAST == minThFAST: no retry pass
+    (512, 384, 3000, 1.2, 8, 12, 5, 204),         # more features than most levels can supply
+    (400, 300, 600, 1.25, 6, 130, 20, 205),       # threshold above 127 (other branch of the packed compare)
+    (333, 257, 400, 1.2, 5, 20, 7, 206),          # odd sizes
+    (1920, 1080, 2000, 1.2, 8, 20, 7, 207),       # full HD
+])
+def test_parameter_sweep(pkg, oracle, synth, w, h, nf, scale, nl, ini, mn, seed):
+    img = synth.textured_image(w, h, seed)
+    gex = pkg.orbx.ORBextractor(nf, scale, nl, ini, mn)
+    oex = oracle.Extractor(nf, scale, nl, ini, mn)
+    _compare_frame(gex, oex, img, (0, 0), got=gex(img, (0, 0)))
+    for l in range(nl):
+        assert np.array_equal(gex.image_pyramid(l), oex.level(l)), f"pyramid level {l}"
+        gx, gy, gr = gex.candidates(l)
+        ox, oy, orr = oex.candidates(l)
+        assert np.array_equal(gx, ox) and np.array_equal(gy, oy) and np.array_equal(gr, orr), f"candidates level {l}"
+    gex.close()
