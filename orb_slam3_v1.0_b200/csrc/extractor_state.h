@@ -113,6 +113,8 @@ struct orbx_extractor {
     int* h_pairs = nullptr;
     unsigned short* d_rowent = nullptr;   /* per pair: right-keypoint indices per image row (vRowIndices) */
     size_t rowent_per_pair = 0;
+    uint32_t* d_rowstart = nullptr;       /* per pair: CSR offsets of d_rowent per image row */
+    int* d_sad = nullptr;                 /* per pair: accepted bestSAD per left keypoint or -1 */
     cudaEvent_t ev_stereo = nullptr;
     int last_pairs = 0;
 };

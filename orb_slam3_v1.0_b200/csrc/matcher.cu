@@ -1735,9 +1735,10 @@ __global__ void __launch_bounds__(MT) k_search_for_initialization(const uint8_t*
             if (c0 >= P.gcols || c1 < 0 || r0 >= P.grows || r1 < 0) continue;
             const uint4 q0 = desc1[2 * i1], q1 = desc1[2 * i1 + 1];
             unsigned long long b1 = ~0ull, b2 = ~0ull;                      /* this lane's two smallest keys */
-            for (int ix = c0; ix <= c1; ++ix) {
+            /* lane = cell column of the window (a column's rows r0..r1 are one contiguous CSR run) */
+            for (int ix = c0 + lane; ix <= c1; ix += 32) {
                 const uint32_t e0 = cell_start[ix * P.grows + r0], e1 = cell_start[ix * P.grows + r1 + 1];
-                for (uint32_t e = e0 + lane; e < e1; e += 32) {
+                for (uint32_t e = e0; e < e1; ++e) {
                     const int i2 = csr[e];
                     if (koct2[i2] != 0) continue;
                     if (!(fabsf(kx2[i2] - x) < r && fabsf(ky2[i2] - y) < r)) continue;

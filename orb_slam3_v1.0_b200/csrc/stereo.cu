@@ -8,8 +8,8 @@
  * (src/ORBmatcher.cc:1375-1391) and the pyramid / scale tables of ORBextractor
  * (src/ORBextractor.cc:92-108, 587-623).
  *
- * One CTA per stereo pair, working on the device-resident outputs of the extractor (no host
- * round trip between extraction and stereo matching):
+ * Three kernels on the device-resident outputs of the extractor (no host round trip between
+ * extraction and stereo matching); 1 and 3 run one CTA per pair, 2 runs ST_SPLIT CTAs per pair:
  *   1. vRowIndices: CSR of right keypoints per image row (+-2*scale rows each), shared memory
  *      counters + a global index list;
  *   2. one warp per left keypoint: lanes scan the row's candidates (octave +-1, uR in
@@ -52,39 +52,31 @@ __device__ __forceinline__ const uint8_t* st_px(const PyrLv& L, int f, int x, in
     return L.base + (size_t)f * L.frame_bytes + (size_t)(y + ORBX_EDGE) * L.pitch + ORBX_XOFF + x;
 }
 
-__global__ void __launch_bounds__(ST_THREADS) k_stereo(StereoSide SL, StereoSide SR, StereoTables TB,
-                                                        const int* __restrict__ pairs, int pair_stride, float mbf, float mb,
-                                                        unsigned short* __restrict__ rowent, size_t rowent_per_pair,
-                                                        float* __restrict__ uright, float* __restrict__ depth) {
+#define ST_SPLIT 8          /* CTAs per pair in the matching kernel */
+
+/* ---- 1. vRowIndices: CTA per pair; CSR of right keypoints per image row -> global */
+__global__ void __launch_bounds__(ST_THREADS) k_stereo_rows(StereoSide SL, StereoSide SR, StereoTables TB,
+                                                             const int* __restrict__ pairs, int pair_stride,
+                                                             unsigned short* __restrict__ rowent, size_t rowent_per_pair,
+                                                             uint32_t* __restrict__ rowstart, float* __restrict__ uright,
+                                                             float* __restrict__ depth, int* __restrict__ sadbuf) {
     extern __shared__ __align__(16) uint32_t sm[];
     __shared__ uint32_t s_tmp[ST_THREADS / 32];
-    __shared__ int s_sadw[ST_THREADS / 32][12];
-    __shared__ int s_h1[256], s_h2[128];
-    __shared__ int s_sel[3];
-
     const int p = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    const int fL = pairs[p], fR = pairs[pair_stride + p];
-    const int nL = SL.nk[fL], nR = SR.nk[fR];
+    const int fR = pairs[pair_stride + p];
+    const int nR = SR.nk[fR];
     const int nRows = SL.lv[0].h;
-    const orbx_keypoint* kL = SL.kps + (size_t)fL * SL.kcap;
     const orbx_keypoint* kR = SR.kps + (size_t)fR * SR.kcap;
-    const uint4* dL = reinterpret_cast<const uint4*>(SL.desc + (size_t)fL * SL.kcap * 32);
-    const uint4* dR = reinterpret_cast<const uint4*>(SR.desc + (size_t)fR * SR.kcap * 32);
     float* oU = uright + (size_t)p * SL.kcap;
     float* oD = depth + (size_t)p * SL.kcap;
+    int* sad = sadbuf + (size_t)p * SL.kcap;
     unsigned short* ent = rowent + (size_t)p * rowent_per_pair;
-
     uint32_t* row_start = sm;                      /* [nRows + 1] */
     uint32_t* row_fill = row_start + nRows + 1;    /* [nRows] */
-    int* sad = reinterpret_cast<int*>(row_fill + nRows);   /* [kcap] accepted bestSAD or -1 */
 
     for (int i = tid; i <= nRows; i += ST_THREADS) row_start[i] = 0;
     for (int i = tid; i < SL.kcap; i += ST_THREADS) { sad[i] = -1; oU[i] = -1.0f; oD[i] = -1.0f; }
-    s_h1[tid] = 0;
-    if (tid < 128) s_h2[tid] = 0;
     __syncthreads();
-
-    /* ---- 1. vRowIndices */
     for (int iR = tid; iR < nR; iR += ST_THREADS) {
         const float kpY = kR[iR].y;
         const float r = 2.0f * TB.scale[kR[iR].octave];
@@ -126,19 +118,42 @@ __global__ void __launch_bounds__(ST_THREADS) k_stereo(StereoSide SL, StereoSide
         const int maxr = min((int)ceilf(kpY + r), nRows - 1), minr = max((int)floorf(kpY - r), 0);
         for (int yi = minr; yi <= maxr; ++yi) ent[atomicAdd(&row_fill[yi], 1u)] = (unsigned short)iR;
     }
-    __syncthreads();
+    uint32_t* rs = rowstart + (size_t)p * (nRows + 1);
+    for (int i = tid; i <= nRows; i += ST_THREADS) rs[i] = row_start[i];
+}
 
-    /* ---- 2. per left keypoint: row-band Hamming search + SAD refinement */
+/* ---- 2. per left keypoint: row-band Hamming search + SAD refinement; ST_SPLIT CTAs per pair,
+ * one warp per left keypoint */
+__global__ void __launch_bounds__(ST_THREADS) k_stereo_match(StereoSide SL, StereoSide SR, StereoTables TB,
+                                                              const int* __restrict__ pairs, int pair_stride, float mbf, float mb,
+                                                              const unsigned short* __restrict__ rowent, size_t rowent_per_pair,
+                                                              const uint32_t* __restrict__ rowstart, float* __restrict__ uright,
+                                                              float* __restrict__ depth, int* __restrict__ sadbuf) {
+    __shared__ int s_sadw[ST_THREADS / 32][12];
+    const int p = blockIdx.y, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int fL = pairs[p], fR = pairs[pair_stride + p];
+    const int nL = SL.nk[fL];
+    const int nRows = SL.lv[0].h;
+    const orbx_keypoint* kL = SL.kps + (size_t)fL * SL.kcap;
+    const orbx_keypoint* kR = SR.kps + (size_t)fR * SR.kcap;
+    const uint4* dL = reinterpret_cast<const uint4*>(SL.desc + (size_t)fL * SL.kcap * 32);
+    const uint4* dR = reinterpret_cast<const uint4*>(SR.desc + (size_t)fR * SR.kcap * 32);
+    float* oU = uright + (size_t)p * SL.kcap;
+    float* oD = depth + (size_t)p * SL.kcap;
+    int* sad = sadbuf + (size_t)p * SL.kcap;
+    const unsigned short* ent = rowent + (size_t)p * rowent_per_pair;
+    const uint32_t* row_start = rowstart + (size_t)p * (nRows + 1);
+
     const float minZ = mb, minD = 0.f, maxD = mbf / minZ;
     const int thOrbDist = (TH_HIGH + TH_LOW) / 2;
     int* sadw = s_sadw[wid];
-    for (int iL = wid; iL < nL; iL += ST_THREADS / 32) {
+    for (int iL = blockIdx.x * (ST_THREADS / 32) + wid; iL < nL; iL += ST_SPLIT * (ST_THREADS / 32)) {
         const orbx_keypoint kp = kL[iL];
         const int levelL = kp.octave;
         const float vL = kp.y, uL = kp.x;
         const int row = (int)vL;
         if (row < 0 || row >= nRows) continue;
-        const uint32_t e0 = row_start[row], e1 = row_start[row + 1];
+        const uint32_t e0 = __ldg(row_start + row), e1 = __ldg(row_start + row + 1);
         if (e0 == e1) continue;
         const float minU = uL - maxD, maxU = uL - minD;
         if (maxU < 0) continue;
@@ -203,9 +218,22 @@ __global__ void __launch_bounds__(ST_THREADS) k_stereo(StereoSide SL, StereoSide
         }
         __syncwarp();
     }
-    __syncthreads();
+}
 
-    /* ---- 3. median of the accepted SADs (vDistIdx[size/2].first) + outlier cut */
+/* ---- 3. median of the accepted SADs (vDistIdx[size/2].first) + outlier cut; CTA per pair */
+__global__ void __launch_bounds__(ST_THREADS) k_stereo_cut(StereoSide SL, const int* __restrict__ pairs,
+                                                            float* __restrict__ uright, float* __restrict__ depth,
+                                                            const int* __restrict__ sadbuf) {
+    __shared__ int s_h1[256], s_h2[128];
+    __shared__ int s_sel[3];
+    const int p = blockIdx.x, tid = threadIdx.x;
+    const int nL = SL.nk[pairs[p]];
+    float* oU = uright + (size_t)p * SL.kcap;
+    float* oD = depth + (size_t)p * SL.kcap;
+    const int* sad = sadbuf + (size_t)p * SL.kcap;
+    s_h1[tid] = 0;
+    if (tid < 128) s_h2[tid] = 0;
+    __syncthreads();
     for (int i = tid; i < nL; i += ST_THREADS) {
         const int s = sad[i];
         if (s >= 0) atomicAdd(&s_h1[min(s >> 7, 255)], 1);
@@ -279,6 +307,8 @@ extern "C" orbx_status orbx_stereo_matches_async(orbx_extractor* left, orbx_extr
         ORBX_CUDA(cudaMalloc(&left->d_depth, (size_t)B * left->kcap * 4));
         ORBX_CUDA(cudaMalloc(&left->d_pairs, (size_t)B * 2 * 4));
         ORBX_CUDA(cudaMalloc(&left->d_rowent, (size_t)B * left->rowent_per_pair * 2));
+        ORBX_CUDA(cudaMalloc(&left->d_rowstart, (size_t)B * (left->lv[0].h + 1) * 4));
+        ORBX_CUDA(cudaMalloc(&left->d_sad, (size_t)B * left->kcap * 4));
         ORBX_CUDA(cudaMallocHost(&left->h_uright, (size_t)B * left->kcap * 4));
         ORBX_CUDA(cudaMallocHost(&left->h_depth, (size_t)B * left->kcap * 4));
         ORBX_CUDA(cudaMallocHost(&left->h_pairs, (size_t)B * 2 * 4));
@@ -303,11 +333,15 @@ extern "C" orbx_status orbx_stereo_matches_async(orbx_extractor* left, orbx_extr
     memset(&SL, 0, sizeof(SL)); memset(&SR, 0, sizeof(SR)); memset(&TB, 0, sizeof(TB));
     fill_side(SL, left); fill_side(SR, right);
     for (int l = 0; l < left->nlevels; ++l) { TB.scale[l] = left->sf[l]; TB.inv_scale[l] = left->inv_sf[l]; }
-    const size_t smem = 4 * ((size_t)2 * left->lv[0].h + 1 + left->kcap) + 16;
-    if (smem > 200 * 1024) { orbx_set_error("image too tall / too many keypoints for the stereo row table"); return ORBX_ERR_INVALID; }
-    ORBX_CUDA(cudaFuncSetAttribute(k_stereo, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max(smem, (size_t)48 * 1024)));
-    k_stereo<<<npairs, ST_THREADS, smem, st>>>(SL, SR, TB, left->d_pairs, B, bf, b, left->d_rowent, left->rowent_per_pair,
-                                               left->d_uright, left->d_depth);
+    const size_t smem = 4 * ((size_t)2 * left->lv[0].h + 1) + 16;
+    if (smem > 200 * 1024) { orbx_set_error("image too tall for the stereo row table"); return ORBX_ERR_INVALID; }
+    ORBX_CUDA(cudaFuncSetAttribute(k_stereo_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max(smem, (size_t)48 * 1024)));
+    k_stereo_rows<<<npairs, ST_THREADS, smem, st>>>(SL, SR, TB, left->d_pairs, B, left->d_rowent, left->rowent_per_pair,
+                                                    left->d_rowstart, left->d_uright, left->d_depth, left->d_sad);
+    k_stereo_match<<<dim3(ST_SPLIT, npairs), ST_THREADS, 0, st>>>(SL, SR, TB, left->d_pairs, B, bf, b, left->d_rowent,
+                                                                  left->rowent_per_pair, left->d_rowstart, left->d_uright,
+                                                                  left->d_depth, left->d_sad);
+    k_stereo_cut<<<npairs, ST_THREADS, 0, st>>>(SL, left->d_pairs, left->d_uright, left->d_depth, left->d_sad);
     ORBX_CUDA(cudaGetLastError());
     if (right != left) {
         /* right's next extraction must not overwrite its pyramid before this kernel has read it */

@@ -18,6 +18,7 @@ ap.add_argument("--batch", type=int, default=256)
 ap.add_argument("--steps", type=int, default=3)
 ap.add_argument("--stereo", action="store_true")
 ap.add_argument("--knn", type=int, default=0, help="queries (x 64 database rows each)")
+ap.add_argument("--matcher", action="store_true", help="one batched call of every matcher entry point")
 a = ap.parse_args()
 pkg = orbx_pkg.load()
 ox = pkg.orbx
@@ -44,3 +45,26 @@ if a.knn:
     q, db, _ = pkg.synth.descriptor_sets(a.knn, a.knn * 64, seed=5)
     d1, i1, d2, i2, ps = m.knn2(q, db, 0.8)
     print("knn pass rate", float(ps.mean()))
+if a.matcher:
+    sy = pkg.synth
+    m = ox.ORBmatcher()
+    Fs = [sy.frame_view(1000, seed=100 + i) for i in range(8)]
+    MPs = [sy.projection_problem(F, 1500, seed=200 + i) for i, F in enumerate(Fs)]
+    m.SearchByProjection(Fs, MPs, 3.0, False, 0.0, 0.8)
+    kfp = [sy.keyframe_pair(1000, 1100, 90, 300 + i) for i in range(8)]
+    for i, p in enumerate(kfp):
+        p[0]["has_mp"] = (np.random.default_rng(i).random(1000) < 0.8).astype(np.uint8)
+    m.SearchByBoW([p[0] for p in kfp], [p[1] for p in kfp], 0.7, True)
+    for p in kfp:
+        p[0]["has_mp"] = (np.random.default_rng(9).random(1000) < 0.2).astype(np.uint8)
+    m.SearchForTriangulation([p[0] for p in kfp], [p[1] for p in kfp], [p[2] for p in kfp], [p[3] for p in kfp], [p[4] for p in kfp])
+    fz = [sy.fuse_problem(F, 1200, 400 + i) for i, F in enumerate(Fs)]
+    m.FuseSearch(Fs, [p[0] for p in fz], 3.0, 0, [p[1] for p in fz], [p[2] for p in fz])
+    s3 = [sy.sim3_problem(900, 1000, 500 + i) for i in range(8)]
+    m.SearchBySim3([p[0] for p in s3], [p[1] for p in s3], [p[2] for p in s3], [p[3] for p in s3], 7.5)
+    ini = [sy.initialization_pair(1000, 1000, 600 + i) for i in range(8)]
+    m.SearchForInitialization([p[0] for p in ini], [p[1] for p in ini], 100, 0.9, True)
+    rng = np.random.default_rng(7)
+    m.ComputeDistinctiveDescriptors([rng.integers(0, 256, (int(k), 32), dtype=np.uint8) for k in rng.integers(3, 40, 2000)])
+    m.AssignFeaturesToGrid(Fs)
+    print("matcher entry points done")
