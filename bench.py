@@ -140,8 +140,12 @@ def matching_bench(pkg, torch, local, ex, B):
     ox = pkg.orbx
     out = {}
     dev = torch.device("cuda", local)
-    # ---- Frame::ComputeStereoMatches: frames (2p, 2p+1) of the last batch as L/R pairs
+    # ---- Frame::ComputeStereoMatches: rectified synthetic pairs (4 distinct, tiled) extracted as
+    # frames (2p, 2p+1) of one batch; the search runs on the extractor's device-resident output
     st = torch.cuda.ExternalStream(ex.stream(), device=dev)
+    sp = [pkg.synth.stereo_pair(W, H, 0xB200 + i) for i in range(4)]
+    sbase = np.stack([im for pr in sp for im in pr])
+    ex.extract_host(np.stack([sbase[i % 8] for i in range(B)])); ex.sync()
     lf = np.arange(0, B, 2); rf = lf + 1
     for _ in range(2):
         ox.stereo_matches_async(ex, ex, lf, rf, 435.2 * 0.11, 0.11)
@@ -156,7 +160,7 @@ def matching_bench(pkg, torch, local, ex, B):
     ur, _ = ox.stereo_fetch(ex, len(lf))
     out["stereo"] = {"pairs_per_s": len(lf) / (ms * 1e-3), "ms_per_launch": ms, "pairs_per_launch": int(len(lf)),
                      "matched_per_pair": float((ur >= 0).sum() / len(lf)),
-                     "note": "consecutive synthetic frames paired as L/R (not a rectified pair): times the row search + SAD, match count is incidental"}
+                     "note": "rectified synthetic stereo pairs; device time of rows + match/SAD/median-cut kernels on resident extractor output"}
     # ---- Frame::AssignFeaturesToGrid on the device-resident keypoints of the whole batch
     gw_inv, gh_inv = float(np.float32(64) / np.float32(W)), float(np.float32(48) / np.float32(H))
     ex.assign_grid(0.0, 0.0, gw_inv, gh_inv, 64, 48)

@@ -1310,7 +1310,7 @@ static void free_all(orbx_extractor* e) {
     void* dptrs[] = {e->d_pyr, e->d_blur, e->d_input, e->d_tabs, e->d_wtabs, e->d_cells, e->d_blur_tiles, e->d_slots,
                      e->d_cell_count, e->d_cand, e->d_pnode, e->d_cand_count, e->d_sel, e->d_sel_count,
                      e->d_dest, e->d_lapping, e->d_kps, e->d_desc, e->d_nk, e->d_units, e->d_odmaps, e->d_grid_off, e->d_grid_idx, e->d_grid_probs, e->d_uright, e->d_depth, e->d_pairs,
-                     e->d_rowent, e->d_rowstart, e->d_sad};
+                     e->d_rowent, e->d_rowstart, e->d_sad, e->d_stdone};
     for (void* p : dptrs) if (p) cudaFree(p);
     void* hptrs[] = {e->h_kps, e->h_desc, e->h_nk, e->h_lapping, e->h_uright, e->h_depth, e->h_pairs, e->h_grid_probs};
     for (void* p : hptrs) if (p) cudaFreeHost(p);

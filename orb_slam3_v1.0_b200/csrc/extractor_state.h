@@ -115,6 +115,7 @@ struct orbx_extractor {
     size_t rowent_per_pair = 0;
     uint32_t* d_rowstart = nullptr;       /* per pair: CSR offsets of d_rowent per image row */
     int* d_sad = nullptr;                 /* per pair: accepted bestSAD per left keypoint or -1 */
+    int* d_stdone = nullptr;              /* per pair: matching CTAs finished (the last one applies the median cut) */
     cudaEvent_t ev_stereo = nullptr;
     int last_pairs = 0;
 };
