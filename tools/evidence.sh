@@ -1,0 +1,18 @@
+#!/bin/bash
+# One gpurun call's worth of round evidence, written under gpurun_out/ with tag $1:
+# GPU test suite, bench lines (product + reference arm), ncu launch list of the bench command,
+# --set full captures of one extraction+stereo step (with source) and of the matcher kernels.
+# Run ON the GPU box:  gpurun --timeout 1500 -- 'bash tools/evidence.sh h'
+tag=${1:-x}
+out=gpurun_out
+mkdir -p $out
+timeout 900 python -m pytest tests -m gpu -x -q > $out/r1_pytest_$tag.log 2>&1; tail -1 $out/r1_pytest_$tag.log
+timeout 600 python bench.py 2> $out/bench_$tag.err | tail -1 > $out/r1_bench_$tag.json; cut -c1-300 $out/r1_bench_$tag.json
+timeout 600 python bench.py --impl reference --steps 3 --warmup 1 2>> $out/bench_$tag.err | tail -1 > $out/r1_bench_${tag}_ref.json; cut -c1-200 $out/r1_bench_${tag}_ref.json
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $out/r1_launches_$tag.csv \
+  python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-matching > $out/ncu_launches_$tag.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -s 15 -c 15 -f -o $out/r1_step_full_$tag \
+  python tools/profile_step.py --steps 2 --stereo > $out/ncu_full_$tag.log 2>&1; tail -1 $out/ncu_full_$tag.log
+timeout 900 ncu --set full --clock-control none -k 'regex:k_search|k_fuse|k_knn|knn2|k_distinctive|k_assign_grid|k_features_in_area' -c 14 -f \
+  -o $out/r1_matcher_full_$tag python tools/profile_step.py --steps 1 --knn 4096 --matcher > $out/ncu_matcher_$tag.log 2>&1; tail -1 $out/ncu_matcher_$tag.log
+ls -la $out | grep "_$tag"

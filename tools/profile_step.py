@@ -1,7 +1,7 @@
 #!/usr/bin/env python3
 """Minimal driver for ncu: N extraction steps of the bench workload (EuRoC shape, batch B) with
 device-resident input, nothing else.  Each step = 13 kernel launches (8 pyramid, FAST, quadtree,
-order, blur, orient+describe); add --stereo for one k_stereo launch per step and --knn for a
+order, blur, orient+describe); add --stereo for the two stereo launches per step and --knn for a
 2-NN launch.  Usage under ncu: skip the first (steps-1)*launches_per_step launches."""
 import argparse
 import os
@@ -39,7 +39,7 @@ for _ in range(a.steps):
         ox.stereo_matches_async(ex, ex, lf, rf, 435.2 * 0.11, 0.11)
 ex.sync()
 n, _ = ex.counts(a.batch)
-print("keypoints/frame", float(n.mean()), "launches/step", ex.last_launches() + int(a.stereo))
+print("keypoints/frame", float(n.mean()), "launches/step", ex.last_launches() + 2 * int(a.stereo))
 if a.knn:
     m = ox.ORBmatcher()
     q, db, _ = pkg.synth.descriptor_sets(a.knn, a.knn * 64, seed=5)
