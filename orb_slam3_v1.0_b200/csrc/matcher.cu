@@ -1652,24 +1652,58 @@ extern "C" orbx_status orbx_search_by_sim3(orbx_matcher* m, int nprob, const orb
 /* ORBmatcher::SearchForInitialization(F1, F2, windowSize, nnRatio, checkOrientation), reference
  * src/ORBmatcher.cc:329-439.  The loop over F1's level-0 keypoints is inherently ordered (a later
  * keypoint may only take an F2 keypoint with a strictly smaller distance than its current holder,
- * and steals it), so one warp walks i1 in order; the candidate set of each i1 (F2 window, octave 0,
- * vMatchedDistance filter) is evaluated by the 32 lanes with packed (distance, candidate order)
- * keys.  CTA per frame pair; the other warps only help building F2's grid. */
+ * and steals it), but only the vMatchedDistance filter and the bookkeeping are: the Hamming
+ * distances are not.  CTA per frame pair, three phases:
+ *   1. all warps, one i1 each: walk the F2 window (octave 0, |dx|,|dy| < r), compute the distances
+ *      and append (dist << 16 | candidate order) keys to the i1's slice of a global scratch list.
+ *      Keys that can neither win (dist > TH_LOW) nor fail a ratio test as runner-up
+ *      (TH_LOW < dist * nnRatio) are dropped, which leaves a handful per i1;
+ *   2. warp 0 walks the i1 with keys in order: lanes apply the vMatchedDistance filter, two
+ *      warp-min reductions give best / second best, lane 0 does the steal bookkeeping;
+ *   3. rotation-histogram cut and count. */
+#define SFI_T 1024
 struct InitProb {
     int n1, n2, gcols, grows, window, checkOri, pad0, pad1;
     float minx, miny, gw_inv, gh_inv, nnRatio, pad2, pad3, pad4;
     unsigned long long kx1, ky1, koct1, kang1, desc1;
     unsigned long long kx2, ky2, koct2, kang2, desc2;
     unsigned long long out_match;          /* [n1] vnMatches12 */
+    unsigned long long scr_off;            /* first entry of this pair's key list in the scratch buffer */
 };
 
-__global__ void __launch_bounds__(MT) k_search_for_initialization(const uint8_t* __restrict__ in, uint8_t* __restrict__ out,
-                                                                   const InitProb* __restrict__ probs, int* __restrict__ counts) {
+/* exclusive scan of a[0..n) in place by the whole CTA (any multiple of 32 threads up to 1024) */
+__device__ void sfi_excl_scan(uint32_t* a, int n, uint32_t* s_tmp /* [32] */) {
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, nw = blockDim.x >> 5;
+    uint32_t carry = 0;
+    for (int base = 0; base < n; base += blockDim.x) {
+        const int i = base + tid;
+        const uint32_t v = (i < n) ? a[i] : 0u;
+        uint32_t inc = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        if (lane == 31) s_tmp[wid] = inc;
+        __syncthreads();
+        const uint32_t t = lane < nw ? s_tmp[lane] : 0u;
+        const uint32_t woff = __reduce_add_sync(0xffffffffu, lane < wid ? t : 0u);
+        const uint32_t tot = __reduce_add_sync(0xffffffffu, t);
+        if (i < n) a[i] = carry + woff + inc - v;
+        carry += tot;
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(SFI_T) k_search_for_initialization(const uint8_t* __restrict__ in, uint8_t* __restrict__ out,
+                                                                      const InitProb* __restrict__ probs, int* __restrict__ counts,
+                                                                      uint32_t* __restrict__ scratch) {
     extern __shared__ __align__(16) uint32_t sm[];
-    __shared__ uint32_t s_tmp[MT / 32];
+    __shared__ uint32_t s_tmp[32];
     __shared__ int s_hist[HISTO_LENGTH];
+    __shared__ int s_nact;
     const InitProb P = probs[blockIdx.x];
-    const int tid = threadIdx.x, lane = tid & 31;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, nwarps = SFI_T / 32;
     const int n1 = P.n1, n2 = P.n2, ncell = P.gcols * P.grows;
     const float* kx1 = reinterpret_cast<const float*>(in + P.kx1);
     const float* ky1 = reinterpret_cast<const float*>(in + P.ky1);
@@ -1682,35 +1716,44 @@ __global__ void __launch_bounds__(MT) k_search_for_initialization(const uint8_t*
     const float* kang2 = reinterpret_cast<const float*>(in + P.kang2);
     const uint4* desc2 = reinterpret_cast<const uint4*>(in + P.desc2);
     int* match12 = reinterpret_cast<int*>(out + P.out_match);
+    uint32_t* scr = scratch + P.scr_off;
 
     uint32_t* cell_start = sm;                        /* [ncell + 1], column-major cells */
     uint32_t* cell_fill = cell_start + ncell + 1;     /* [ncell] */
     int* matched_dist = reinterpret_cast<int*>(cell_fill + ncell);   /* [n2] vMatchedDistance */
     int* match21 = matched_dist + n2;                 /* [n2] vnMatches21 */
-    unsigned short* csr = reinterpret_cast<unsigned short*>(match21 + n2);   /* [n2] */
-    signed char* claim_bin = reinterpret_cast<signed char*>(csr + n2 + (n2 & 1));   /* [n1] rotHist bin of i1's claim, -1: none */
+    float* x2 = reinterpret_cast<float*>(match21 + n2);              /* [n2] NaN unless octave 0 */
+    float* y2 = x2 + n2;                              /* [n2] */
+    uint32_t* off = reinterpret_cast<uint32_t*>(y2 + n2);            /* [n1 + 1] first key of i1 (upper-bound allocation) */
+    uint32_t* nkey = off + n1 + 1;                    /* [n1] keys written */
+    unsigned short* csr = reinterpret_cast<unsigned short*>(nkey + n1);      /* [n2] */
+    unsigned short* act = csr + n2 + (n2 & 1);        /* [n1] the i1 that have keys, ascending */
+    signed char* claim_bin = reinterpret_cast<signed char*>(act + n1 + (n1 & 1));   /* [n1] rotHist bin of i1's claim, -1: none */
 
-    for (int i = tid; i <= ncell; i += MT) cell_start[i] = 0;
+    for (int i = tid; i <= ncell; i += SFI_T) cell_start[i] = 0;
     if (tid < HISTO_LENGTH) s_hist[tid] = 0;
-    for (int i = tid; i < n2; i += MT) { matched_dist[i] = 0x7fffffff; match21[i] = -1; }
-    for (int i = tid; i < n1; i += MT) { match12[i] = -1; claim_bin[i] = -1; }
+    for (int i = tid; i < n2; i += SFI_T) {
+        matched_dist[i] = 0x7fffffff; match21[i] = -1;
+        x2[i] = koct2[i] == 0 ? kx2[i] : __int_as_float(0x7fc00000); y2[i] = ky2[i];
+    }
+    for (int i = tid; i < n1; i += SFI_T) { match12[i] = -1; claim_bin[i] = -1; nkey[i] = 0; }
     __syncthreads();
-    for (int i = tid; i < n2; i += MT) {
+    for (int i = tid; i < n2; i += SFI_T) {
         const int px = (int)roundf((kx2[i] - P.minx) * P.gw_inv), py = (int)roundf((ky2[i] - P.miny) * P.gh_inv);
         const int lin = py * P.gcols + px;
         if (lin >= 0 && lin < ncell) atomicAdd(&cell_start[(lin % P.gcols) * P.grows + lin / P.gcols], 1u);
     }
     __syncthreads();
-    mt_excl_scan(cell_start, ncell + 1, s_tmp);
-    for (int i = tid; i < ncell; i += MT) cell_fill[i] = cell_start[i];
+    sfi_excl_scan(cell_start, ncell + 1, s_tmp);
+    for (int i = tid; i < ncell; i += SFI_T) cell_fill[i] = cell_start[i];
     __syncthreads();
-    for (int i = tid; i < n2; i += MT) {
+    for (int i = tid; i < n2; i += SFI_T) {
         const int px = (int)roundf((kx2[i] - P.minx) * P.gw_inv), py = (int)roundf((ky2[i] - P.miny) * P.gh_inv);
         const int lin = py * P.gcols + px;
         if (lin >= 0 && lin < ncell) csr[atomicAdd(&cell_fill[(lin % P.gcols) * P.grows + lin / P.gcols], 1u)] = (unsigned short)i;
     }
     __syncthreads();
-    for (int c = tid; c < ncell; c += MT) {
+    for (int c = tid; c < ncell; c += SFI_T) {
         const int e0 = (int)cell_start[c], e1 = (int)cell_start[c + 1];
         for (int a = e0 + 1; a < e1; ++a) {
             const unsigned short v = csr[a];
@@ -1719,46 +1762,83 @@ __global__ void __launch_bounds__(MT) k_search_for_initialization(const uint8_t*
             csr[b + 1] = v;
         }
     }
-    __syncthreads();
-
-    int nmatches = 0;
-    if (tid < 32) {
-        const float r = (float)P.window;
-        for (int i1 = 0; i1 < n1; ++i1) {
-            if (koct1[i1] > 0) continue;                                   /* level1 > 0 */
+    /* upper bound of |vIndices2| per i1: everything in the window's cells
+     * (F2->GetFeaturesInArea(x, y, windowSize, 0, 0), src/Frame.cc:404-468) */
+    const float r = (float)P.window;
+    for (int i1 = tid; i1 <= n1; i1 += SFI_T) {
+        uint32_t ub = 0;
+        if (i1 < n1 && koct1[i1] <= 0) {                                   /* level1 > 0: skipped */
             const float x = kx1[i1], y = ky1[i1];
-            /* F2->GetFeaturesInArea(x, y, windowSize, 0, 0): octave 0 only (src/Frame.cc:404-468) */
             const int c0 = max(0, (int)floorf((x - P.minx - r) * P.gw_inv));
             const int c1 = min(P.gcols - 1, (int)ceilf((x - P.minx + r) * P.gw_inv));
             const int r0 = max(0, (int)floorf((y - P.miny - r) * P.gh_inv));
             const int r1 = min(P.grows - 1, (int)ceilf((y - P.miny + r) * P.gh_inv));
-            if (c0 >= P.gcols || c1 < 0 || r0 >= P.grows || r1 < 0) continue;
-            const uint4 q0 = desc1[2 * i1], q1 = desc1[2 * i1 + 1];
-            unsigned long long b1 = ~0ull, b2 = ~0ull;                      /* this lane's two smallest keys */
-            /* lane = cell column of the window (a column's rows r0..r1 are one contiguous CSR run) */
-            for (int ix = c0 + lane; ix <= c1; ix += 32) {
-                const uint32_t e0 = cell_start[ix * P.grows + r0], e1 = cell_start[ix * P.grows + r1 + 1];
-                for (uint32_t e = e0; e < e1; ++e) {
-                    const int i2 = csr[e];
-                    if (koct2[i2] != 0) continue;
-                    if (!(fabsf(kx2[i2] - x) < r && fabsf(ky2[i2] - y) < r)) continue;
-                    const int dist = hamming256(q0, q1, desc2[2 * i2], desc2[2 * i2 + 1]);
-                    if (matched_dist[i2] <= dist) continue;
-                    const unsigned long long key = ((unsigned long long)dist << 32) | e;
-                    if (key < b1) { b2 = b1; b1 = key; }
-                    else if (key < b2) b2 = key;
-                }
+            if (!(c0 >= P.gcols || c1 < 0 || r0 >= P.grows || r1 < 0))
+                for (int ix = c0; ix <= c1; ++ix) ub += cell_start[ix * P.grows + r1 + 1] - cell_start[ix * P.grows + r0];
+        }
+        off[i1] = ub;
+    }
+    __syncthreads();
+    sfi_excl_scan(off, n1 + 1, s_tmp);
+
+    /* ---- 1. distances, warp per i1, lane = cell column of the window (a column's rows r0..r1 are one CSR run) */
+    const float fTH = (float)TH_LOW;
+    for (int i1 = wid; i1 < n1; i1 += nwarps) {
+        if (off[i1 + 1] == off[i1]) continue;
+        const float x = kx1[i1], y = ky1[i1];
+        const int c0 = max(0, (int)floorf((x - P.minx - r) * P.gw_inv));
+        const int c1 = min(P.gcols - 1, (int)ceilf((x - P.minx + r) * P.gw_inv));
+        const int r0 = max(0, (int)floorf((y - P.miny - r) * P.gh_inv));
+        const int r1 = min(P.grows - 1, (int)ceilf((y - P.miny + r) * P.gh_inv));
+        const uint4 q0 = __ldg(desc1 + 2 * i1), q1 = __ldg(desc1 + 2 * i1 + 1);
+        uint32_t* mine = scr + off[i1];
+        for (int ix = c0 + lane; ix <= c1; ix += 32) {
+            const uint32_t e0 = cell_start[ix * P.grows + r0], e1 = cell_start[ix * P.grows + r1 + 1];
+            for (uint32_t e = e0; e < e1; ++e) {
+                const int i2 = csr[e];
+                if (!(fabsf(x2[i2] - x) < r && fabsf(y2[i2] - y) < r)) continue;
+                const int dist = hamming256(q0, q1, __ldg(desc2 + 2 * i2), __ldg(desc2 + 2 * i2 + 1));
+                if (dist > TH_LOW && fTH < (float)dist * P.nnRatio) continue;      /* cannot win, cannot fail a ratio test */
+                mine[atomicAdd(&nkey[i1], 1u)] = ((uint32_t)dist << 16) | e;
+            }
+        }
+    }
+    __syncthreads();
+
+    /* ---- 2. the ordered walk */
+    int nmatches = 0;
+    if (tid < 32) {
+        int nact = 0;
+        for (int base = 0; base < n1; base += 32) {
+            const int i = base + lane;
+            const bool f = i < n1 && nkey[i] > 0;
+            const unsigned bal = __ballot_sync(0xffffffffu, f);
+            if (f) act[nact + __popc(bal & ((1u << lane) - 1u))] = (unsigned short)i;
+            nact += __popc(bal);
+        }
+        __syncwarp();
+        uint32_t pre = 0xFFFFFFFFu;
+        if (nact > 0) { const int i0 = act[0]; if (lane < (int)nkey[i0]) pre = __ldcg(scr + off[i0] + lane); }
+        for (int a = 0; a < nact; ++a) {
+            const int i1 = act[a];
+            const int cnt = (int)nkey[i1];
+            const uint32_t* mine = scr + off[i1];
+            const uint32_t cur = pre;
+            pre = 0xFFFFFFFFu;
+            if (a + 1 < nact) { const int in = act[a + 1]; if (lane < (int)nkey[in]) pre = __ldcg(scr + off[in] + lane); }
+            uint32_t b1 = 0xFFFFFFFFu, b2 = 0xFFFFFFFFu;                    /* this lane's two smallest keys */
+            for (int j = lane; j < cnt; j += 32) {
+                const uint32_t key = j < 32 ? cur : __ldcg(mine + j);
+                if (matched_dist[csr[key & 0xFFFFu]] <= (int)(key >> 16)) continue;
+                if (key < b1) { b2 = b1; b1 = key; }
+                else if (key < b2) b2 = key;
             }
             /* warp: smallest key, and the second smallest distance counting duplicates */
-            unsigned long long g1 = b1;
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) { const unsigned long long t = __shfl_xor_sync(0xffffffffu, g1, o); g1 = t < g1 ? t : g1; }
-            if (g1 == ~0ull) continue;                                      /* vIndices2 empty or all filtered: bestDist stays INT_MAX */
-            unsigned long long g2 = (b1 == g1) ? b2 : b1;
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) { const unsigned long long t = __shfl_xor_sync(0xffffffffu, g2, o); g2 = t < g2 ? t : g2; }
-            const int bestDist = (int)(g1 >> 32), bestIdx2 = csr[(uint32_t)g1];
-            const int bestDist2 = g2 == ~0ull ? 0x7fffffff : (int)(g2 >> 32);
+            const uint32_t g1 = __reduce_min_sync(0xffffffffu, b1);
+            if (g1 == 0xFFFFFFFFu) continue;                                /* all filtered: bestDist stays INT_MAX */
+            const uint32_t g2 = __reduce_min_sync(0xffffffffu, (b1 == g1) ? b2 : b1);
+            const int bestDist = (int)(g1 >> 16), bestIdx2 = csr[g1 & 0xFFFFu];
+            const int bestDist2 = g2 == 0xFFFFFFFFu ? 0x7fffffff : (int)(g2 >> 16);
             if (bestDist <= TH_LOW && (float)bestDist < (float)bestDist2 * P.nnRatio) {
                 if (lane == 0) {
                     const int prev = match21[bestIdx2];
@@ -1775,18 +1855,23 @@ __global__ void __launch_bounds__(MT) k_search_for_initialization(const uint8_t*
                 __syncwarp();
             }
         }
-        if (P.checkOri && lane == 0) {
-            int ind1, ind2, ind3;
-            three_maxima(s_hist, HISTO_LENGTH, ind1, ind2, ind3);
-            for (int i = 0; i < n1; ++i) {
-                const int b = claim_bin[i];
-                if (b >= 0 && b != ind1 && b != ind2 && b != ind3 && match12[i] >= 0) match12[i] = -1;
-            }
+        if (lane == 0) s_nact = nact;
+    }
+    __syncthreads();
+    /* ---- 3. rotation consistency and count */
+    if (P.checkOri) {
+        __shared__ int s_ind[3];
+        if (tid == 0) three_maxima(s_hist, HISTO_LENGTH, s_ind[0], s_ind[1], s_ind[2]);
+        __syncthreads();
+        for (int a = tid; a < s_nact; a += SFI_T) {
+            const int i = act[a], b = claim_bin[i];
+            if (b >= 0 && b != s_ind[0] && b != s_ind[1] && b != s_ind[2] && match12[i] >= 0) match12[i] = -1;
         }
-        __syncwarp();
-        for (int i = lane; i < n1; i += 32) nmatches += match12[i] >= 0;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) nmatches += __shfl_xor_sync(0xffffffffu, nmatches, o);
+        __syncthreads();
+    }
+    if (tid < 32) {
+        for (int a = lane; a < s_nact; a += 32) nmatches += match12[act[a]] >= 0;
+        nmatches = __reduce_add_sync(0xffffffffu, nmatches);
         if (lane == 0) counts[blockIdx.x] = nmatches;
     }
 }
@@ -1799,12 +1884,12 @@ extern "C" orbx_status orbx_search_for_initialization(orbx_matcher* m, int nprob
     ORBX_CUDA(cudaSetDevice(m->device));
     Packer in, out;
     std::vector<InitProb> probs(nprob);
-    size_t smem = 0;
+    size_t smem = 0, scr_entries = 0;
     for (int p = 0; p < nprob; ++p) {
         const orbx_frame_view &A = F1[p], &B = F2[p];
         InitProb& P = probs[p];
         memset(&P, 0, sizeof(P));
-        if (A.n < 0 || B.n < 0 || B.n > 65535 || B.gcols < 1 || B.grows < 1 || (long long)B.gcols * B.grows > 20000 ||
+        if (A.n < 0 || B.n < 0 || A.n > 65535 || B.n > 65535 || B.gcols < 1 || B.grows < 1 || (long long)B.gcols * B.grows > 20000 ||
             (A.n > 0 && (!A.kx || !A.ky || !A.koct || !A.desc || (checkOrientation && !A.kangle))) ||
             (B.n > 0 && (!B.kx || !B.ky || !B.koct || !B.desc || (checkOrientation && !B.kangle)))) {
             orbx_set_error("problem %d: unsupported view or null array", p);
@@ -1817,7 +1902,17 @@ extern "C" orbx_status orbx_search_for_initialization(orbx_matcher* m, int nprob
         P.kx2 = in.add(B.kx, 4 * (size_t)B.n); P.ky2 = in.add(B.ky, 4 * (size_t)B.n); P.koct2 = in.add(B.koct, 4 * (size_t)B.n);
         P.kang2 = in.add(B.kangle, B.kangle ? 4 * (size_t)B.n : 0); P.desc2 = in.add(B.desc, 32 * (size_t)B.n);
         P.out_match = out.add(nullptr, 4 * (size_t)std::max(A.n, 1));
-        smem = std::max(smem, (size_t)4 * (2 * (size_t)B.gcols * B.grows + 1) + 8 * (size_t)B.n + 2 * (size_t)(B.n + 1) + (size_t)A.n + 16);
+        /* key list: at most every F2 keypoint for every level-0 F1 keypoint */
+        size_t nl0 = 0;
+        for (int i = 0; i < A.n; ++i) nl0 += A.koct[i] <= 0;
+        P.scr_off = scr_entries;
+        scr_entries += std::max<size_t>(nl0 * (size_t)B.n, 1);
+        smem = std::max(smem, (size_t)4 * (2 * (size_t)B.gcols * B.grows + 1) + 16 * (size_t)B.n + 4 * (2 * (size_t)A.n + 1) +
+                                  2 * (size_t)(B.n + 1) + 2 * (size_t)(A.n + 1) + (size_t)A.n + 16);
+    }
+    {
+        orbx_status sst = ensure_scratch(m, 4 * scr_entries);
+        if (sst != ORBX_OK) return sst;
     }
     const size_t probs_off = in.add(probs.data(), sizeof(InitProb) * (size_t)nprob);
     const size_t counts_off = out.add(nullptr, 4 * (size_t)nprob);
@@ -1827,8 +1922,9 @@ extern "C" orbx_status orbx_search_for_initialization(orbx_matcher* m, int nprob
     in.copy_to(m->h_in);
     ORBX_CUDA(cudaMemcpyAsync(m->d_in, m->h_in, in.total, cudaMemcpyHostToDevice, m->stream));
     ORBX_CUDA(cudaFuncSetAttribute(k_search_for_initialization, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max(smem, (size_t)48 * 1024)));
-    k_search_for_initialization<<<nprob, MT, smem, m->stream>>>(m->d_in, m->d_out, reinterpret_cast<const InitProb*>(m->d_in + probs_off),
-                                                                reinterpret_cast<int*>(m->d_out + counts_off));
+    k_search_for_initialization<<<nprob, SFI_T, smem, m->stream>>>(m->d_in, m->d_out, reinterpret_cast<const InitProb*>(m->d_in + probs_off),
+                                                                   reinterpret_cast<int*>(m->d_out + counts_off),
+                                                                   reinterpret_cast<uint32_t*>(m->d_scratch));
     ORBX_CUDA(cudaGetLastError());
     m->last_launches = 1;
     ORBX_CUDA(cudaMemcpyAsync(m->h_out, m->d_out, out.total, cudaMemcpyDeviceToHost, m->stream));

@@ -383,3 +383,23 @@ def test_search_for_initialization_batched(matcher, oracle, synth):
     for (n, m), p in zip(res, P):
         on, om = oracle.search_for_initialization(p[0], p[1], 100, 0.9, True)
         assert n == on and np.array_equal(m, om)
+
+
+@pytest.mark.parametrize("win,ratio,ori", [(400, 0.9, True), (150, 1.0, False), (60, 0.6, True), (1000, 2.0, True)])
+def test_search_for_initialization_clustered(matcher, oracle, synth, win, ratio, ori):
+    """All keypoints on octave 0, descriptors drawn from 6 prototypes with a few flipped bits: every
+    window holds far more than 32 candidates within TH_LOW, so the key lists are long, ties are
+    everywhere and almost every claim is a steal."""
+    rng = np.random.default_rng(win)
+    F1, F2 = synth.initialization_pair(700, 800, 190 + win)
+    proto = rng.integers(0, 256, (6, 32), dtype=np.uint8)
+    for F in (F1, F2):
+        n = len(F["kx"])
+        F["koct"] = np.zeros(n, np.int32)
+        bits = np.unpackbits(proto[rng.integers(0, 6, n)], axis=1)
+        bits ^= (rng.random(bits.shape) < 0.03).astype(np.uint8)
+        F["desc"] = np.packbits(bits, axis=1)
+    n, m = matcher.SearchForInitialization(F1, F2, win, ratio, ori)
+    on, om = oracle.search_for_initialization(F1, F2, win, ratio, ori)
+    assert n == on and np.array_equal(m, om)
+    assert (om >= 0).sum() > 5
