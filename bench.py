@@ -244,6 +244,38 @@ def matching_bench(pkg, torch, local, ex, B):
     return out
 
 
+def other_shapes_bench(pkg, torch, local):
+    """BASELINE.json configs 3 and 4 as secondary numbers: device-resident frames/s of the same
+    extraction path on the TUM-VI shape (512x512, 1500 features, vLappingArea split) and the
+    KITTI shape (1241x376, 2000 features), batch 256, synthetic frames, 3 warm-ups + 10 steps."""
+    ox = pkg.orbx
+    out = {}
+    dev = torch.device("cuda", local)
+    for name, (w, h, nf, lap) in {"tumvi_512x512_nf1500_lapping": (512, 512, 1500, (0, 255)),
+                                  "kitti_1241x376_nf2000": (1241, 376, 2000, None)}.items():
+        B = 256
+        ex = ox.ORBextractor(nf, SCALE, NLEVELS, INI_TH, MIN_TH, device=local, max_batch=B).prepare(w, h, B)
+        frames = pkg.synth.frame_batch(B, w, h, seed=0xB300, distinct=8)
+        bufs = [torch.from_numpy(np.roll(frames, k, axis=0)).to(dev) for k in range(2)]
+        laps = None if lap is None else np.tile(np.array(lap, np.int32), (B, 1))
+        st = torch.cuda.ExternalStream(ex.stream(), device=dev)
+        for i in range(3):
+            ex.extract_device(bufs[i & 1].data_ptr(), B, w, h, lapping=laps)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(st)
+        for i in range(10):
+            ex.extract_device(bufs[i & 1].data_ptr(), B, w, h, lapping=laps)
+        e1.record(st)
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / 10
+        ex.sync()
+        n, _ = ex.counts(B)
+        out[name] = {"frames_per_s": B / (ms * 1e-3), "ms_per_step": ms, "frames_per_step": B,
+                     "keypoints_per_frame": float(np.mean(n))}
+        ex.close()
+    return out
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -265,6 +297,30 @@ def run_reference(args):
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line))
+
+
+def bind_to_gpu_numa(torch, local):
+    """Pin this rank to the CPUs of its GPU's NUMA node before the pinned staging buffers are
+    allocated (first touch places them next to the GPU's PCIe root).  Returns (node, ncpus, saved
+    affinity) or None when the topology is not exposed."""
+    try:
+        pr = torch.cuda.get_device_properties(local)
+        path = f"/sys/bus/pci/devices/{pr.pci_domain_id:04x}:{pr.pci_bus_id:02x}:{pr.pci_device_id:02x}.0/numa_node"
+        node = int(open(path).read())
+        if node < 0:
+            return None
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        saved = os.sched_getaffinity(0)
+        cpus &= saved
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return node, len(cpus), saved
+    except (OSError, ValueError, AttributeError):
+        return None
 
 
 def main():
@@ -297,6 +353,7 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     B = args.batch
+    numa = bind_to_gpu_numa(torch, local)
     ex = orbx.ORBextractor(NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH, device=local, max_batch=B).prepare(W, H, B)
     stream = torch.cuda.ExternalStream(ex.stream(), device=torch.device("cuda", local))
 
@@ -413,7 +470,8 @@ def main():
             "config": {"workload": WORKLOAD, "frames_per_step_per_gpu": B, "keypoints_per_frame": float(np.mean(n_kp)),
                        "l2_policy": "inputs larger than L2: 2 alternating 92 MB input batches + 360 MB pyramid working set per step",
                        "e2e_batches_in_flight": NH,
-                       "sharding": "independent frames per rank, no collective"},
+                       "sharding": "independent frames per rank, no collective",
+                       "numa": None if numa is None else {"node": numa[0], "cpus": numa[1]}},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(B * W * H),
                     "d2h_bytes_per_step": int(B * ex.capacity * (28 + 32) + 8 * B), "ms_per_step": e2e_wall_ms / args.steps,
                     "device_ms_per_step": e2e_ms / args.steps},
@@ -427,7 +485,10 @@ def main():
         }
         if not args.no_matching:
             line["matching"] = matching_bench(pkg, torch, local, ex, B)
+            line["other_shapes"] = other_shapes_bench(pkg, torch, local)
             line["single_frame_latency"] = single_frame_latency(pkg, local, frames[0])
+        if numa is not None:
+            os.sched_setaffinity(0, numa[2])          # the CPU baseline gets every core back
         if not args.no_cpu_baseline and world == 1:
             line["cpu_baseline"] = cpu_baseline(os.cpu_count() or 1)
         print(json.dumps(line))
