@@ -266,6 +266,15 @@ __device__ __forceinline__ uint32_t gt4(uint32_t d, uint32_t k7f, bool hi) {
     return (hi ? (c & d) : (c | d)) & 0x80808080u;
 }
 
+/* 2^32 / d rounded up, d = 2..64: n / d == umulhi(n, c_rcp.v[d]) for the small n used below */
+struct RcpTab { uint32_t v[65]; };
+constexpr RcpTab make_rcp_tab() {
+    RcpTab t{};
+    for (int d = 2; d < 65; ++d) t.v[d] = 0xFFFFFFFFu / (uint32_t)d + 1u;
+    return t;
+}
+__constant__ RcpTab c_rcp = make_rcp_tab();
+
 __global__ void __launch_bounds__(FAST_THREADS) k_fast_units(Tables T, const Unit* __restrict__ units,
                                                               const Cell* __restrict__ cells, int ncells, int ini_th,
                                                               int min_th, uint32_t* __restrict__ slots, uint32_t* scratch,
@@ -342,8 +351,9 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_units(Tables T, const Uni
             const uint32_t m_first = 0xFFFFFFFFu << (8 * (tlo & 3));
             const uint32_t m_last = 0xFFFFFFFFu >> (8 * (3 - ((thi - 1) & 3)));
             /* flat (row, word) walk with stride FAST_THREADS, advanced incrementally */
-            const int dy = FAST_THREADS / rw, dw = FAST_THREADS - dy * rw;
-            const int y_init = tid / rw, w_init = tid - y_init * rw;
+            const uint32_t rcp_rw = c_rcp.v[rw];                  /* rw <= tp / 4 <= 64 */
+            const int dy = rw == 1 ? FAST_THREADS : (int)__umulhi((uint32_t)FAST_THREADS, rcp_rw), dw = FAST_THREADS - dy * rw;
+            const int y_init = rw == 1 ? tid : (int)__umulhi((uint32_t)tid, rcp_rw), w_init = tid - y_init * rw;
             const int iters = (dh * rw + FAST_THREADS - 1) / FAST_THREADS;
 
             /* ---- detection: quick reject on 4 px/thread -> survivor queue -> exact FAST-9 test in
