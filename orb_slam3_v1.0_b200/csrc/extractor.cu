@@ -523,6 +523,9 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_units(Tables T, const Uni
 #ifndef OCT_THREADS
 #define OCT_THREADS 128
 #endif
+#ifndef OCT_SCAND
+#define OCT_SCAND 2048      /* candidates of a (frame, level) kept in shared memory; more: global scratch */
+#endif
 
 /* exclusive scan of a[0..n) in shared memory, in place; returns the total. All threads call. */
 __device__ int block_excl_scan(int* a, int n, int* s_tmp /* [OCT_THREADS/32 + 1] */) {
@@ -661,7 +664,7 @@ __global__ void __launch_bounds__(OCT_THREADS) k_octree(Tables T, const Cell* __
                                                          uint32_t* __restrict__ cand, uint32_t* __restrict__ pnode,
                                                          size_t cand_per_frame, int* __restrict__ cand_count,
                                                          uint32_t* __restrict__ sel, size_t sel_per_frame,
-                                                         int* __restrict__ sel_count, int maxn, int max_cells) {
+                                                         int* __restrict__ sel_count, int maxn, int max_cells, int scand) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ int s_tmp[OCT_THREADS / 32 + 1];
     __shared__ int s_T, s_CT;
@@ -671,6 +674,7 @@ __global__ void __launch_bounds__(OCT_THREADS) k_octree(Tables T, const Cell* __
     const int N = Lv.N;
 
     OctSmem S;
+    uint32_t* s_cand;
     {
         unsigned char* p = smem_raw;
         for (int k = 0; k < 2; ++k) { S.E[k] = (OctE*)p; p += sizeof(OctE) * maxn; }
@@ -687,6 +691,8 @@ __global__ void __launch_bounds__(OCT_THREADS) k_octree(Tables T, const Cell* __
             S.x1[k] = (short*)p; p += 2 * (size_t)maxn;
             S.y1[k] = (short*)p; p += 2 * (size_t)maxn;
         }
+        p += (16 - ((size_t)(p - smem_raw) & 15)) & 15;
+        s_cand = (uint32_t*)p;      /* [2][scand]: the level's candidates and their node, when they fit */
     }
     int* cellpref = S.ccnt;     /* reuse: needs max_cells+1 <= 4*maxn (checked on host) */
 
@@ -695,15 +701,28 @@ __global__ void __launch_bounds__(OCT_THREADS) k_octree(Tables T, const Cell* __
     for (int i = tid; i < ncl; i += OCT_THREADS) cellpref[i] = cell_count[(size_t)f * ncells + Lv.cell_begin + i];
     __syncthreads();
     const int ncand = block_excl_scan(cellpref, ncl, s_tmp);
-    uint32_t* pc = cand + (size_t)f * cand_per_frame + Lv.cand_off;
-    uint32_t* pn = pnode + (size_t)f * cand_per_frame + Lv.cand_off;
-    {
-        const int lane = tid & 31, wid = tid >> 5;
-        for (int ci = wid; ci < ncl; ci += OCT_THREADS / 32) {
-            const Cell c = cells[Lv.cell_begin + ci];
-            const int n = cell_count[(size_t)f * ncells + Lv.cell_begin + ci];
-            const uint32_t* src = slots + (size_t)f * slots_per_frame + c.slot_off;
-            for (int k = lane; k < n; k += 32) pc[cellpref[ci] + k] = src[k];
+    /* every sweep below walks the candidates and their node index: both live in shared memory when the
+     * level's candidates fit (the global copy of the candidates is still written: orbx_extractor_candidates) */
+    uint32_t* pcg = cand + (size_t)f * cand_per_frame + Lv.cand_off;
+    uint32_t* pc = pcg;
+    /* node of a candidate: position in the node list (14 bits) | quadrant it falls into (2 bits) */
+    unsigned short* pn = reinterpret_cast<unsigned short*>(pnode + (size_t)f * cand_per_frame + Lv.cand_off);
+    const bool in_smem = ncand <= scand;
+    if (in_smem) { pc = s_cand; pn = reinterpret_cast<unsigned short*>(s_cand + scand); }
+    /* thread per cell: the cells' runs are short, and the loads of different cells are independent */
+    for (int ci = tid; ci < ncl; ci += OCT_THREADS) {
+        const int b = cellpref[ci];
+        const int n = (ci + 1 < ncl ? cellpref[ci + 1] : ncand) - b;
+        if (n > 0) {
+            const uint32_t* src = slots + (size_t)f * slots_per_frame + cells[Lv.cell_begin + ci].slot_off;
+            for (int k = 0; k < n; k += 4) {
+                uint32_t v[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) v[u] = (k + u < n) ? __ldg(src + k + u) : 0u;
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                    if (k + u < n) { pcg[b + k + u] = v[u]; if (in_smem) pc[b + k + u] = v[u]; }
+            }
         }
     }
     if (tid == 0) cand_count[f * T.nlevels + level] = ncand;
@@ -725,7 +744,7 @@ __global__ void __launch_bounds__(OCT_THREADS) k_octree(Tables T, const Cell* __
     for (int i = tid; i < ncand; i += OCT_THREADS) {
         const uint32_t e = pc[i];
         const int ini = (int)__fdiv_rn((float)(e & 0xFFF), hX);
-        pn[i] = (uint32_t)ini;
+        pn[i] = (unsigned short)ini;
         atomicAdd(&S.a[ini], 1);
     }
     __syncthreads();
@@ -744,7 +763,7 @@ __global__ void __launch_bounds__(OCT_THREADS) k_octree(Tables T, const Cell* __
         }
     }
     __syncthreads();
-    for (int i = tid; i < ncand; i += OCT_THREADS) pn[i] = (uint32_t)S.b[pn[i]];
+    for (int i = tid; i < ncand; i += OCT_THREADS) pn[i] = (unsigned short)S.b[pn[i]];
     __syncthreads();
     (void)Wd;
 
@@ -760,13 +779,13 @@ __global__ void __launch_bounds__(OCT_THREADS) k_octree(Tables T, const Cell* __
             for (int i = tid; i < 4 * L; i += OCT_THREADS) S.ccnt[i] = 0;
             __syncthreads();
             for (int i = tid; i < ncand; i += OCT_THREADS) {
-                const uint32_t pos = pn[i] & 0xFFFF;
+                const uint32_t pos = pn[i] & 0x3FFFu;
                 if (S.cnt[cur][pos] > 1) {
                     const uint32_t e = pc[i];
                     const int q = quadrant_of(e & 0xFFF, (e >> 12) & 0xFFF, S.x0[cur][pos], S.y0[cur][pos],
                                               S.x1[cur][pos], S.y1[cur][pos]);
                     atomicAdd(&S.ccnt[4 * pos + q], 1);
-                    pn[i] = pos | ((uint32_t)q << 16);
+                    pn[i] = (unsigned short)(pos | ((uint32_t)q << 14));
                 }
             }
             __syncthreads();
@@ -815,8 +834,8 @@ __global__ void __launch_bounds__(OCT_THREADS) k_octree(Tables T, const Cell* __
             __syncthreads();
             for (int i = tid; i < ncand; i += OCT_THREADS) {
                 const uint32_t v = pn[i];
-                const uint32_t pos = v & 0xFFFF;
-                pn[i] = (S.cnt[cur][pos] > 1) ? (uint32_t)S.ccnt[4 * pos + (v >> 16)] : (uint32_t)S.em[pos];
+                const uint32_t pos = v & 0x3FFFu;
+                pn[i] = (unsigned short)((S.cnt[cur][pos] > 1) ? S.ccnt[4 * pos + (v >> 14)] : S.em[pos]);
             }
             __syncthreads();
             L = totC + totStay;
@@ -851,14 +870,14 @@ __global__ void __launch_bounds__(OCT_THREADS) k_octree(Tables T, const Cell* __
             }
             __syncthreads();
             for (int i = tid; i < ncand; i += OCT_THREADS) {
-                const uint32_t pos = pn[i] & 0xFFFF;
+                const uint32_t pos = pn[i] & 0x3FFFu;
                 const int m = S.em[pos];
                 if (m >= 0) {
                     const uint32_t e = pc[i];
                     const int q = quadrant_of(e & 0xFFF, (e >> 12) & 0xFFF, S.x0[cur][pos], S.y0[cur][pos],
                                               S.x1[cur][pos], S.y1[cur][pos]);
                     atomicAdd(&S.ccnt[4 * m + q], 1);
-                    pn[i] = pos | ((uint32_t)q << 16);
+                    pn[i] = (unsigned short)(pos | ((uint32_t)q << 14));
                 }
             }
             __syncthreads();
@@ -927,9 +946,9 @@ __global__ void __launch_bounds__(OCT_THREADS) k_octree(Tables T, const Cell* __
             __syncthreads();
             for (int i = tid; i < ncand; i += OCT_THREADS) {
                 const uint32_t v = pn[i];
-                const uint32_t pos = v & 0xFFFF;
+                const uint32_t pos = v & 0x3FFFu;
                 const int m = S.em[pos];
-                pn[i] = (m >= 0 && m < Tn) ? (uint32_t)S.ccnt[4 * m + (v >> 16)] : (uint32_t)S.b[pos];
+                pn[i] = (unsigned short)((m >= 0 && m < Tn) ? S.ccnt[4 * m + (v >> 14)] : S.b[pos]);
             }
             __syncthreads();
             L = CT + totStay;
@@ -946,7 +965,7 @@ __global__ void __launch_bounds__(OCT_THREADS) k_octree(Tables T, const Cell* __
     for (int i = tid; i < ncand; i += OCT_THREADS) {
         const uint32_t e = pc[i];
         const unsigned long long key = ((unsigned long long)(e >> 24) << 32) | (unsigned long long)(0xFFFFFFFFu - (uint32_t)i);
-        atomicMax(&S.best[pn[i] & 0xFFFF], key);
+        atomicMax(&S.best[pn[i] & 0x3FFFu], key);
     }
     __syncthreads();
     for (int p = tid; p < L; p += OCT_THREADS) {
@@ -1480,9 +1499,9 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
     e->sel_per_frame = sel_off;
     e->kcap = (int)sel_off;
     maxn = std::max(maxn, orbx_div_up(e->max_cells_level + 1, 4) + 1);
-    if (maxn > 60000) { orbx_set_error("nfeatures too large for 16-bit node positions"); free_all(e); return ORBX_ERR_INVALID; }
+    if (maxn > 16383) { orbx_set_error("nfeatures too large for 14-bit node positions"); free_all(e); return ORBX_ERR_INVALID; }
     e->maxn = maxn;
-    e->oct_smem = (size_t)maxn * (2 * sizeof(OctE) + 8 + 2 * 4 + 16 + 4 * 4 + 2 * 4 * 2) + 64;
+    e->oct_smem = (size_t)maxn * (2 * sizeof(OctE) + 8 + 2 * 4 + 16 + 4 * 4 + 2 * 4 * 2) + 64 + 6 * (size_t)OCT_SCAND;
     e->nblur_tiles = (int)blur_tiles.size();
     if (e->oct_smem > 220 * 1024) { orbx_set_error("nfeatures too large for the shared-memory quadtree (%zu B)", e->oct_smem); free_all(e); return ORBX_ERR_INVALID; }
 
@@ -1761,7 +1780,7 @@ extern "C" orbx_status orbx_extract_device(orbx_extractor* e, const uint8_t* d_i
     k_octree<<<dim3(nl, batch), OCT_THREADS, e->oct_smem, st>>>(e->T, e->d_cells, e->ncells, e->d_slots, e->slots_per_frame,
                                                                  e->d_cell_count, e->d_cand, e->d_pnode, e->cand_per_frame,
                                                                  e->d_cand_count, e->d_sel, e->sel_per_frame, e->d_sel_count,
-                                                                 e->maxn, e->max_cells_level);
+                                                                 e->maxn, e->max_cells_level, OCT_SCAND);
     ++launches;
     if (e->profiling) ORBX_CUDA(cudaEventRecord(e->ev[3], st));
     /* stage 3 */
