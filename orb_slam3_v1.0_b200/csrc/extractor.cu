@@ -195,7 +195,9 @@ __global__ void __launch_bounds__(256) k_resize_w4(LevelDev S, LevelDev D, const
  * Pass 0 runs A-C at iniThFAST over the whole unit; pass 1 re-runs them at minThFAST over the
  * runs of cells that came out empty.  A corner at threshold t has score >= t, so the score map of
  * pass 1 is a superset of pass 0's and needs no reset. */
+#ifndef FAST_UC
 #define FAST_UC 6             /* cells per unit */
+#endif
 #define FAST_THREADS 256
 #define FAST_WQ 160           /* survivor queue per warp: < 32 left over + up to 128 new */
 #define FAST_CQ 64            /* corner queue per warp: < 32 left over + up to 32 new */
@@ -1218,37 +1220,33 @@ __global__ void __launch_bounds__(32 * OD_WARPS) k_orient_describe(Tables T, con
     const uint32_t spatch = sb0 + 2 * OD_WIN_SLOT;
     const uint32_t bar0 = (uint32_t)__cvta_generic_to_shared(&s_bar[wid][0]), barp = bar0 + 16u;
 
-    int k = __ffs(okmask) - 1;
+    /* Two passes over the run, so that everything that is per KEYPOINT rather than per lane (atan2, the
+     * fp64 sincos, the keypoint record) is computed once, by lane k for keypoint k, instead of redundantly
+     * by the whole warp for each keypoint:
+     *   1. orientation moments of every keypoint (patches through the single patch buffer);
+     *   2. lanes < OD_KPW: angle, cos, sin, keypoint record;
+     *   3. descriptors (windows through the two window buffers; the first two are requested up front). */
+    const int my_x = (int)(my_e & 0xFFF) + ORBX_MINB, my_y = (int)((my_e >> 12) & 0xFFF) + ORBX_MINB;
+    const int k0 = __ffs(okmask) - 1;
     {
-        const uint32_t e = __shfl_sync(0xffffffffu, my_e, k);
-        const int l = __shfl_sync(0xffffffffu, my_l, k);
+        const unsigned rest0 = okmask & ~((2u << k0) - 1u);
+        const int k1 = rest0 ? __ffs(rest0) - 1 : -1;
+        const int x0 = __shfl_sync(0xffffffffu, my_x, k0), y0 = __shfl_sync(0xffffffffu, my_y, k0), l0 = __shfl_sync(0xffffffffu, my_l, k0);
+        const int x1 = __shfl_sync(0xffffffffu, my_x, max(k1, 0)), y1 = __shfl_sync(0xffffffffu, my_y, max(k1, 0));
+        const int l1 = __shfl_sync(0xffffffffu, my_l, max(k1, 0));
         if (lane == 0) {
-            const int x = (int)(e & 0xFFF) + ORBX_MINB, y = (int)((e >> 12) & 0xFFF) + ORBX_MINB;
-            od_issue_patch(Mp, f, l, x, y, spatch, barp);
-            od_issue_win(Mp, f, l, x, y, sb0, bar0);
+            od_issue_patch(Mp, f, l0, x0, y0, spatch, barp);
+            od_issue_win(Mp, f, l0, x0, y0, sb0, bar0);
+            if (k1 >= 0) od_issue_win(Mp, f, l1, x1, y1, sb0 + OD_WIN_SLOT, bar0 + 8u);
         }
     }
-    int par = 0;
-    uint32_t phase = 0;                                     /* bit b = parity to wait for on barrier b */
-    while (k >= 0) {
+    /* ---- 1. IC_Angle (reference src/cuda/Angle_gpu.cu:39-69): m10 = sum u*I, m01 = sum v*I over the disc */
+    int my_m10 = 0, my_m01 = 0;
+    uint32_t pphase = 0;
+    for (int k = k0; k >= 0;) {
         const unsigned rest = okmask & ~((2u << k) - 1u);
         const int kn = rest ? __ffs(rest) - 1 : -1;
-        int xn = 0, yn = 0, ln = 0;
-        if (kn >= 0) {
-            const uint32_t en = __shfl_sync(0xffffffffu, my_e, kn);
-            ln = __shfl_sync(0xffffffffu, my_l, kn);
-            xn = (int)(en & 0xFFF) + ORBX_MINB; yn = (int)((en >> 12) & 0xFFF) + ORBX_MINB;
-            if (lane == 0) od_issue_win(Mp, f, ln, xn, yn, sb0 + (uint32_t)(par ^ 1) * OD_WIN_SLOT, bar0 + 8u * (uint32_t)(par ^ 1));
-        }
-
-        const uint32_t e = __shfl_sync(0xffffffffu, my_e, k);
-        const int l = __shfl_sync(0xffffffffu, my_l, k);
-        const int d = __shfl_sync(0xffffffffu, my_d, k);
-        const LevelDev& L = T.lv[l];
-        const int x = (int)(e & 0xFFF) + ORBX_MINB, y = (int)((e >> 12) & 0xFFF) + ORBX_MINB;
-        const int resp = (int)(e >> 24);
-
-        /* IC_Angle (reference src/cuda/Angle_gpu.cu:39-69): m10 = sum u*I, m01 = sum v*I over the disc */
+        const int x = __shfl_sync(0xffffffffu, my_x, k);
         int m10 = 0, m01 = 0;
         {
             const int al16 = (x - 15) & 15, al = al16 & 3;
@@ -1263,8 +1261,8 @@ __global__ void __launch_bounds__(32 * OD_WARPS) k_orient_describe(Tables T, con
             }
             const uint32_t pa = spatch + (uint32_t)(sub * OD_PPB + (al16 & ~3) + 4 * wc);
             int rv = sub - 15;
-            od_wait(barp, (phase >> 2) & 1u);
-            phase ^= 4u;
+            od_wait(barp, pphase);
+            pphase ^= 1u;
             if (sub < 3) {
 #pragma unroll
                 for (int r0 = 0; r0 < 33; r0 += 3) {
@@ -1283,18 +1281,44 @@ __global__ void __launch_bounds__(32 * OD_WARPS) k_orient_describe(Tables T, con
             }
         }
         __syncwarp();                                       /* every lane has read the patch: refill it */
-        if (kn >= 0 && lane == 0) od_issue_patch(Mp, f, ln, xn, yn, spatch, barp);
+        if (kn >= 0) {
+            const int xn = __shfl_sync(0xffffffffu, my_x, kn), yn = __shfl_sync(0xffffffffu, my_y, kn), ln = __shfl_sync(0xffffffffu, my_l, kn);
+            if (lane == 0) od_issue_patch(Mp, f, ln, xn, yn, spatch, barp);
+        }
         m10 = __reduce_add_sync(0xffffffffu, m10);
         m01 = __reduce_add_sync(0xffffffffu, m01);
-        const float angle = fast_atan2_deg((float)m01, (float)m10);
-
-        /* rBRIEF (reference src/cuda/Orb_gpu.cu:311-350): lane = descriptor byte */
+        if (lane == k) { my_m10 = m10; my_m01 = m01; }
+        k = kn;
+    }
+    /* ---- 2. per keypoint, lane-parallel */
+    float my_a = 1.f, my_b = 0.f;
+    if (my_ok) {
+        const float angle = fast_atan2_deg((float)my_m01, (float)my_m10);
         constexpr float factorPI = (float)(3.14159265358979323846 / 180.f);
         const float ar = __fmul_rn(angle, factorPI);
         /* cosf/sinf of the reference resolve to glibc (<=0.56 ULP); here: fp64 result rounded once */
         double sd, cd;
         sincos((double)ar, &sd, &cd);
-        const float a = (float)cd, b = (float)sd;
+        my_a = (float)cd; my_b = (float)sd;
+        const LevelDev& L = T.lv[my_l];
+        orbx_keypoint kp;
+        float fx = (float)my_x, fy = (float)my_y;
+        if (my_l != 0) { fx = __fmul_rn(fx, L.scale); fy = __fmul_rn(fy, L.scale); }
+        kp.x = fx; kp.y = fy; kp.size = L.patch_size; kp.angle = angle; kp.response = (float)(int)(my_e >> 24);
+        kp.octave = my_l; kp.class_id = -1;
+        kps[(size_t)f * kcap + my_d] = kp;
+    }
+    /* ---- 3. rBRIEF (reference src/cuda/Orb_gpu.cu:311-350): lane = descriptor byte */
+    int par = 0;
+    uint32_t phase = 0;                                     /* bit b = parity to wait for on window barrier b */
+    for (int k = k0; k >= 0;) {
+        const unsigned rest = okmask & ~((2u << k) - 1u);
+        const int kn = rest ? __ffs(rest) - 1 : -1;
+        const unsigned rest2 = kn >= 0 ? okmask & ~((2u << kn) - 1u) : 0u;
+        const int kn2 = rest2 ? __ffs(rest2) - 1 : -1;
+        const int x = __shfl_sync(0xffffffffu, my_x, k);
+        const int d = __shfl_sync(0xffffffffu, my_d, k);
+        const float a = __shfl_sync(0xffffffffu, my_a, k), b = __shfl_sync(0xffffffffu, my_b, k);
         /* cvRound == round-half-even: adding 1.5*2^23 leaves K + n in the float's bit pattern
          * (K = 0x4B400000, |n| <= 19), which replaces the quarter-rate F2I; the two K's are folded
          * into the window base address (32-bit shared addresses wrap) */
@@ -1316,15 +1340,11 @@ __global__ void __launch_bounds__(32 * OD_WARPS) k_orient_describe(Tables T, con
             val |= (t0 < t1) << j;
         }
         desc[((size_t)f * kcap + d) * 32 + lane] = (uint8_t)val;
-        if (lane == 0) {
-            orbx_keypoint kp;
-            float fx = (float)x, fy = (float)y;
-            if (l != 0) { fx = __fmul_rn(fx, L.scale); fy = __fmul_rn(fy, L.scale); }
-            kp.x = fx; kp.y = fy; kp.size = L.patch_size; kp.angle = angle; kp.response = (float)resp;
-            kp.octave = l; kp.class_id = -1;
-            kps[(size_t)f * kcap + d] = kp;
-        }
         __syncwarp();          /* every lane is done with this buffer before it is refilled */
+        if (kn2 >= 0) {
+            const int x2 = __shfl_sync(0xffffffffu, my_x, kn2), y2 = __shfl_sync(0xffffffffu, my_y, kn2), l2 = __shfl_sync(0xffffffffu, my_l, kn2);
+            if (lane == 0) od_issue_win(Mp, f, l2, x2, y2, sb0 + (uint32_t)par * OD_WIN_SLOT, bar0 + 8u * (uint32_t)par);
+        }
         k = kn;
         par ^= 1;
     }
