@@ -198,7 +198,9 @@ __global__ void __launch_bounds__(256) k_resize_w4(LevelDev S, LevelDev D, const
 #ifndef FAST_UC
 #define FAST_UC 6             /* cells per unit */
 #endif
-#define FAST_THREADS 256
+#ifndef FAST_THREADS
+#define FAST_THREADS 160        /* 5 warps: 256 -> 160 threads took 9 % off the kernel (less time parked at the region barriers) */
+#endif
 #define FAST_WQ 160           /* survivor queue per warp: < 32 left over + up to 128 new */
 #define FAST_CQ 64            /* corner queue per warp: < 32 left over + up to 32 new */
 #define FAST_CL 1024          /* scored corners of a region kept as a list for the NMS pass (2 buffers); overflow -> map scan */
@@ -1037,6 +1039,43 @@ __global__ void __launch_bounds__(ORD_THREADS) k_order(Tables T, const uint32_t*
  * No shared memory, every global access is a coalesced 128-byte row segment. */
 #define BL_STRIP 120
 #define BL_ROWS 56
+/* tap pairs of the horizontal pass, (low, high) u16 half -> byte 0 / byte 1.  In constant memory
+ * so that IDP.2A takes them as c[][] operands (as immediates they cost one UMOV each per use) */
+#define T2(lo, hi) ((uint32_t)(lo) | ((uint32_t)(hi) << 8))
+__constant__ uint32_t c_bt[10] = {T2(18, 48), T2(0, 34), T2(56, 34), T2(48, 18), T2(0, 18),
+                                  T2(48, 48), T2(18, 0), T2(34, 56), T2(34, 0), 32768u};
+#undef T2
+enum { BT_18_48, BT_0_34, BT_56_34, BT_48_18, BT_0_18, BT_48_48, BT_18_0, BT_34_56, BT_34_0, BT_HALF };
+
+/* one output row of a lane's word: the new source word goes into window slot S (rows oldest..
+ * newest = slots (S+1)%7 .. S), vertical pass on the packed u16 pairs, neighbours' column sums by
+ * shuffle, 18 IDP.2A, bytes 2 of the four sums gathered by 3 PRMT */
+template <int S>
+__device__ __forceinline__ uint32_t blur_row(uint32_t w, uint32_t (&E)[7], uint32_t (&O)[7]) {
+    E[S] = __byte_perm(w, 0u, 0x4240);
+    O[S] = __byte_perm(w, 0u, 0x4341);
+    const uint32_t VE = 18u * (E[(S + 1) % 7] + E[S]) + 34u * (E[(S + 2) % 7] + E[(S + 6) % 7]) +
+                        48u * (E[(S + 3) % 7] + E[(S + 5) % 7]) + 56u * E[(S + 4) % 7];
+    const uint32_t VO = 18u * (O[(S + 1) % 7] + O[S]) + 34u * (O[(S + 2) % 7] + O[(S + 6) % 7]) +
+                        48u * (O[(S + 3) % 7] + O[(S + 5) % 7]) + 56u * O[(S + 4) % 7];
+    const uint32_t LE = __shfl_up_sync(0xffffffffu, VE, 1), LO = __shfl_up_sync(0xffffffffu, VO, 1);
+    const uint32_t RE = __shfl_down_sync(0xffffffffu, VE, 1), RO = __shfl_down_sync(0xffffffffu, VO, 1);
+    /* VE = c0|c2, VO = c1|c3 of this word, L* / R* the neighbour words' (c-4|c-2, c-3|c-1, c4|c6, c5|c7) */
+    const uint32_t half = c_bt[BT_HALF];
+    uint32_t o0 = __dp2a_lo(LO, c_bt[BT_18_48], half);
+    o0 = __dp2a_lo(LE, c_bt[BT_0_34], o0); o0 = __dp2a_lo(VE, c_bt[BT_56_34], o0); o0 = __dp2a_lo(VO, c_bt[BT_48_18], o0);
+    uint32_t o1 = __dp2a_lo(LE, c_bt[BT_0_18], half);
+    o1 = __dp2a_lo(LO, c_bt[BT_0_34], o1); o1 = __dp2a_lo(VE, c_bt[BT_48_48], o1); o1 = __dp2a_lo(VO, c_bt[BT_56_34], o1);
+    o1 = __dp2a_lo(RE, c_bt[BT_18_0], o1);
+    uint32_t o2 = __dp2a_lo(LO, c_bt[BT_0_18], half);
+    o2 = __dp2a_lo(VE, c_bt[BT_34_56], o2); o2 = __dp2a_lo(VO, c_bt[BT_48_48], o2); o2 = __dp2a_lo(RE, c_bt[BT_34_0], o2);
+    o2 = __dp2a_lo(RO, c_bt[BT_18_0], o2);
+    uint32_t o3 = __dp2a_lo(VE, c_bt[BT_18_48], half);
+    o3 = __dp2a_lo(VO, c_bt[BT_34_56], o3); o3 = __dp2a_lo(RE, c_bt[BT_48_18], o3); o3 = __dp2a_lo(RO, c_bt[BT_34_0], o3);
+    /* every sum is < 2^24: its byte 2 is the rounded result */
+    return __byte_perm(__byte_perm(o0, o1, 0x0062), __byte_perm(o2, o3, 0x0062), 0x5410);
+}
+
 __global__ void __launch_bounds__(128) k_blur7(Tables T, const int4* __restrict__ tiles, int ntiles) {
     const int wt = blockIdx.x * 4 + (threadIdx.x >> 5);
     if (wt >= ntiles) return;
@@ -1045,65 +1084,48 @@ __global__ void __launch_bounds__(128) k_blur7(Tables T, const int4* __restrict_
     const LevelDev& L = T.lv[t.x];
     const int x = t.y - 4 + 4 * lane;         /* ROI column of this lane's word */
     const int xc = min(x, L.pitch - ORBX_XOFF - 4);
-    const uint8_t* src = lv_ptr(L, f, xc, t.z - 3);
+    const uint8_t* lp = lv_ptr(L, f, xc, t.z - 3);
     uint8_t* dst = L.blur + (size_t)f * L.bframe_bytes + (size_t)t.z * L.bpitch + x;
     const bool store = lane >= 1 && lane <= 30 && x < L.w;
-    const int nrows = t.w, pitch = L.pitch, bpitch = L.bpitch;
+    const int nrows = t.w;
+    const size_t pitch = (size_t)L.pitch, bpitch = (size_t)L.bpitch;
     uint32_t E[7], O[7];
 #pragma unroll
     for (int j = 0; j < 6; ++j) {
-        const uint32_t w = __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)j * pitch));
-        E[j] = w & 0x00FF00FFu;
-        O[j] = (w >> 8) & 0x00FF00FFu;
+        const uint32_t w = __ldg(reinterpret_cast<const uint32_t*>(lp));
+        lp += pitch;
+        E[j] = __byte_perm(w, 0u, 0x4240);
+        O[j] = __byte_perm(w, 0u, 0x4341);
     }
     /* the 7 rows of the NEXT block are requested before the current block is computed, so the
-     * global-load latency hides behind ~400 instructions instead of stalling every row */
+     * global-load latency hides behind ~350 instructions instead of stalling every row.  The
+     * requests run up to 10 rows below the tile: inside the level's 19-row border. */
     uint32_t nx[7];
 #pragma unroll
-    for (int j = 0; j < 7; ++j) nx[j] = (j < nrows) ? __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)(6 + j) * pitch)) : 0u;
-    for (int r = 0; r < nrows; r += 7) {
-        uint32_t cu[7];
-#pragma unroll
-        for (int j = 0; j < 7; ++j) {
-            cu[j] = nx[j];
-            if (r + 7 + j < nrows) nx[j] = __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)(13 + r + j) * pitch));
-        }
-#pragma unroll
-        for (int j = 0; j < 7; ++j) {
-            const int rr = r + j;
-            if (rr < nrows) {
-                const int s = (6 + j) % 7;
-                const uint32_t w = cu[j];
-                E[s] = w & 0x00FF00FFu;
-                O[s] = (w >> 8) & 0x00FF00FFu;
-                /* window rows oldest..newest = slots (s+1)%7 .. s */
-                const uint32_t VE = 18u * (E[(s + 1) % 7] + E[s]) + 34u * (E[(s + 2) % 7] + E[(s + 6) % 7]) +
-                                    48u * (E[(s + 3) % 7] + E[(s + 5) % 7]) + 56u * E[(s + 4) % 7];
-                const uint32_t VO = 18u * (O[(s + 1) % 7] + O[s]) + 34u * (O[(s + 2) % 7] + O[(s + 6) % 7]) +
-                                    48u * (O[(s + 3) % 7] + O[(s + 5) % 7]) + 56u * O[(s + 4) % 7];
-                const uint32_t LE = __shfl_up_sync(0xffffffffu, VE, 1), LO = __shfl_up_sync(0xffffffffu, VO, 1);
-                const uint32_t RE = __shfl_down_sync(0xffffffffu, VE, 1), RO = __shfl_down_sync(0xffffffffu, VO, 1);
-                /* horizontal taps as 2-way dot products of the packed u16 column sums (IDP.2A):
-                 * VE = c0|c2, VO = c1|c3 of this word, L* / R* the neighbour words' (c-4|c-2, c-3|c-1, c4|c6, c5|c7);
-                 * the byte pair of each constant holds the taps that hit the (low, high) half */
-#define T2(lo, hi) ((uint32_t)(lo) | ((uint32_t)(hi) << 8))
-                uint32_t o0 = __dp2a_lo(LO, T2(18, 48), 32768u);
-                o0 = __dp2a_lo(LE, T2(0, 34), o0); o0 = __dp2a_lo(VE, T2(56, 34), o0); o0 = __dp2a_lo(VO, T2(48, 18), o0);
-                uint32_t o1 = __dp2a_lo(LE, T2(0, 18), 32768u);
-                o1 = __dp2a_lo(LO, T2(0, 34), o1); o1 = __dp2a_lo(VE, T2(48, 48), o1); o1 = __dp2a_lo(VO, T2(56, 34), o1);
-                o1 = __dp2a_lo(RE, T2(18, 0), o1);
-                uint32_t o2 = __dp2a_lo(LO, T2(0, 18), 32768u);
-                o2 = __dp2a_lo(VE, T2(34, 56), o2); o2 = __dp2a_lo(VO, T2(48, 48), o2); o2 = __dp2a_lo(RE, T2(34, 0), o2);
-                o2 = __dp2a_lo(RO, T2(18, 0), o2);
-                uint32_t o3 = __dp2a_lo(VE, T2(18, 48), 32768u);
-                o3 = __dp2a_lo(VO, T2(34, 56), o3); o3 = __dp2a_lo(RE, T2(48, 18), o3); o3 = __dp2a_lo(RO, T2(34, 0), o3);
-#undef T2
-                o0 >>= 16; o1 >>= 16; o2 >>= 16; o3 >>= 16;
-                if (store)
-                    *reinterpret_cast<uint32_t*>(dst + (size_t)rr * bpitch) = o0 | (o1 << 8) | (o2 << 16) | (o3 << 24);
-            }
-        }
+    for (int j = 0; j < 7; ++j) { nx[j] = __ldg(reinterpret_cast<const uint32_t*>(lp)); lp += pitch; }
+#define BLUR_ROW(J, NEXT)                                                                       \
+    {                                                                                           \
+        const uint32_t w = nx[J];                                                               \
+        if (NEXT) { nx[J] = __ldg(reinterpret_cast<const uint32_t*>(lp)); lp += pitch; }        \
+        const uint32_t v = blur_row<(6 + J) % 7>(w, E, O);                                      \
+        asm volatile("" ::"r"(v));      /* computed by every lane: no branch around the math */ \
+        if (store) *reinterpret_cast<uint32_t*>(dst) = v;                                       \
+        dst += bpitch;                                                                          \
     }
+    int r = 0;
+    for (; r + 7 <= nrows; r += 7) {          /* row J of the next block is requested as row J of this one is consumed */
+        BLUR_ROW(0, true) BLUR_ROW(1, true) BLUR_ROW(2, true) BLUR_ROW(3, true) BLUR_ROW(4, true) BLUR_ROW(5, true) BLUR_ROW(6, true)
+    }
+    if (r < nrows) {                          /* last block of a level's bottom tile: nrows - r < 7 rows */
+        const int rem = nrows - r;
+        BLUR_ROW(0, false)
+        if (rem > 1) BLUR_ROW(1, false)
+        if (rem > 2) BLUR_ROW(2, false)
+        if (rem > 3) BLUR_ROW(3, false)
+        if (rem > 4) BLUR_ROW(4, false)
+        if (rem > 5) BLUR_ROW(5, false)
+    }
+#undef BLUR_ROW
 }
 
 /* ================================================================== stage 5: orientation + descriptor */
@@ -1365,6 +1387,9 @@ static void free_all(orbx_extractor* e) {
     for (void* p : hptrs) if (p) cudaFreeHost(p);
     for (int i = 0; i < 7; ++i) if (e->ev[i]) cudaEventDestroy(e->ev[i]);
     if (e->ev_stereo) cudaEventDestroy(e->ev_stereo);
+    if (e->ev_fork) cudaEventDestroy(e->ev_fork);
+    if (e->ev_join) cudaEventDestroy(e->ev_join);
+    if (e->side) cudaStreamDestroy(e->side);
     if (e->stream) cudaStreamDestroy(e->stream);
     delete e;
 }
@@ -1527,6 +1552,10 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
 
 #define CK(call) do { cudaError_t _e = (call); if (_e != cudaSuccess) { orbx_set_error("%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(_e)); free_all(e); return ORBX_ERR_CUDA; } } while (0)
     CK(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&e->side, cudaStreamNonBlocking));
+    CK(cudaEventCreateWithFlags(&e->ev_fork, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&e->ev_join, cudaEventDisableTiming));
+    if (const char* v = getenv("ORBX_FORK_BLUR")) e->fork_blur = atoi(v);
     for (int i = 0; i < 7; ++i) CK(cudaEventCreate(&e->ev[i]));
     CK(cudaFuncSetAttribute(k_octree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)e->oct_smem));
     {
@@ -1788,6 +1817,19 @@ extern "C" orbx_status orbx_extract_device(orbx_extractor* e, const uint8_t* d_i
         }
     }
     if (e->profiling) ORBX_CUDA(cudaEventRecord(e->ev[1], st));
+    /* stage 4 needs the pyramid only: outside profiling mode it runs on the side stream beside the
+     * quadtree and the ordering (latency-bound, most issue slots free); mode 1 forks it before
+     * FAST instead */
+    const int fork_blur = e->profiling ? 0 : e->fork_blur;
+    auto launch_side_blur = [&]() -> orbx_status {
+        ORBX_CUDA(cudaEventRecord(e->ev_fork, st));
+        ORBX_CUDA(cudaStreamWaitEvent(e->side, e->ev_fork, 0));
+        k_blur7<<<dim3(orbx_div_up(e->nblur_tiles, 4), batch), 128, 0, e->side>>>(e->T, e->d_blur_tiles, e->nblur_tiles);
+        ORBX_CUDA(cudaEventRecord(e->ev_join, e->side));
+        ++launches;
+        return ORBX_OK;
+    };
+    if (fork_blur == 1) { orbx_status r = launch_side_blur(); if (r != ORBX_OK) return r; }
     /* stage 1 */
     if (e->ncells > 0) {
         k_fast_units<<<dim3(e->nunits, batch), FAST_THREADS, (size_t)2 * e->fast_rows * e->fast_tp + FAST_QBYTES + 128, st>>>(
@@ -1796,6 +1838,7 @@ extern "C" orbx_status orbx_extract_device(orbx_extractor* e, const uint8_t* d_i
         ++launches;
     }
     if (e->profiling) ORBX_CUDA(cudaEventRecord(e->ev[2], st));
+    if (fork_blur == 2) { orbx_status r = launch_side_blur(); if (r != ORBX_OK) return r; }
     /* stage 2 */
     k_octree<<<dim3(nl, batch), OCT_THREADS, e->oct_smem, st>>>(e->T, e->d_cells, e->ncells, e->d_slots, e->slots_per_frame,
                                                                  e->d_cell_count, e->d_cand, e->d_pnode, e->cand_per_frame,
@@ -1809,8 +1852,12 @@ extern "C" orbx_status orbx_extract_device(orbx_extractor* e, const uint8_t* d_i
     ++launches;
     if (e->profiling) ORBX_CUDA(cudaEventRecord(e->ev[4], st));
     /* stage 4 */
-    k_blur7<<<dim3(orbx_div_up(e->nblur_tiles, 4), batch), 128, 0, st>>>(e->T, e->d_blur_tiles, e->nblur_tiles);
-    ++launches;
+    if (fork_blur) {
+        ORBX_CUDA(cudaStreamWaitEvent(st, e->ev_join, 0));
+    } else {
+        k_blur7<<<dim3(orbx_div_up(e->nblur_tiles, 4), batch), 128, 0, st>>>(e->T, e->d_blur_tiles, e->nblur_tiles);
+        ++launches;
+    }
     if (e->profiling) ORBX_CUDA(cudaEventRecord(e->ev[5], st));
     /* stage 5 */
     {

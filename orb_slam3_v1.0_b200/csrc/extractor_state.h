@@ -75,6 +75,8 @@ struct orbx_extractor {
     int grid_cells = 0, grid_cells_cap = 0;
     void* d_odmaps = nullptr;       /* TMA tensor maps of the describe stage (extractor.cu: struct ODMaps) */
     cudaStream_t stream = nullptr;
+    cudaStream_t side = nullptr;    /* the blur runs here beside FAST / quadtree / order (it needs the pyramid only) */
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     /* device buffers */
     uint8_t* d_pyr = nullptr;
     uint8_t* d_blur = nullptr;
@@ -103,6 +105,7 @@ struct orbx_extractor {
     int last_batch = 0, last_launches = 0;
     bool synced = false;
     bool profiling = false;
+    int fork_blur = 2;             /* blur on the side stream: 2 = beside quadtree + order, 1 = also beside FAST, 0 = one stream (ORBX_FORK_BLUR) */
     cudaEvent_t ev[7] = {};
     /* Frame::ComputeStereoMatches state (stereo.cu), allocated on first use */
     float* d_uright = nullptr;     /* [max_batch * kcap] mvuRight of the left frames */
