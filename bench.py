@@ -360,7 +360,7 @@ def main():
     # inputs: two distinct device-resident batches (2 x 92 MB) + the 360 MB pyramid working set
     # per step exceed the 126 MB L2, so no step finds its input in cache
     frames = make_frames(B, seed=0xB200 + 1000 * rank)
-    NH = 3                                     # batches in flight on the end-to-end path
+    NH = int(os.environ.get("ORBX_BENCH_NH", "3"))                                     # batches in flight on the end-to-end path
     pin = [orbx.PinnedBuffer((B, H, W)) for _ in range(NH)]
     for k in range(NH):
         pin[k].array[:] = np.roll(frames, k, axis=0)

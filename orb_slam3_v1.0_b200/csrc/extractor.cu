@@ -41,6 +41,15 @@ void orbx_set_error(const char* fmt, ...) {
 extern "C" const char* orbx_last_error(void) { return g_err; }
 extern "C" int orbx_version(void) { return 100; }
 
+/* spin on an mbarrier phase (TMA / bulk-copy completion) */
+__device__ __forceinline__ void od_wait(uint32_t bar, uint32_t parity) {
+    uint32_t done;
+    do {
+        asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+                     : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+    } while (!done);
+}
+
 /* ================================================================== stage 0: pyramid */
 /* level 0 = copyMakeBorder(image, 19, BORDER_REFLECT_101).
  * One thread per 16 output bytes of the padded row.  Work items are ordered so that warps are
@@ -123,59 +132,92 @@ __global__ void __launch_bounds__(256) k_resize(LevelDev S, LevelDev D, unsigned
     *reinterpret_cast<uint32_t*>(D.base + (size_t)f * D.frame_bytes + (size_t)r * D.pitch + c * 4) = out;
 }
 
-/* Fast path of the level chain: one thread per 32-bit word (4 pixels) of the PADDED destination
- * row.  Per-word tables built on the host hold, for the 4 pixels, the packed fixed-point
- * coefficient pairs (a0 | a1<<16), the byte address of the left-most source pixel and each
- * pixel's offset from it (reflection of border columns is baked into the tables).  The source
- * bytes of both rows are fetched as three aligned words, funnel-shifted to the base pixel, and
- * each horizontal interpolation is one PRMT + one 2-way dot product (IDP.2A). */
-struct ResizeMeta { uint32_t m; };   /* base byte (16b) | off0<<16 | off1<<20 | off2<<24 | off3<<28; ~0 = outside */
-
-#ifndef RS_RPT
-#define RS_RPT 4        /* destination rows per thread: the per-word column tables are loaded once for all of them */
+/* Fast path of the level chain.  CTA = a band of RS_TH destination rows over the whole padded
+ * row.  The source rows the band needs are contiguous in the bordered level l-1, so they arrive
+ * in shared memory by ONE bulk copy (cp.async.bulk + mbarrier).  Thread = one 32-bit word (4
+ * pixels) of the PADDED destination row.  Per-word tables built on the host hold, for the 4
+ * pixels, the packed fixed-point coefficient pairs (a0 | a1<<16), the byte address of the
+ * left-most source pixel and each pixel's offset from it (reflection of border COLUMNS is baked
+ * into the tables).  The source bytes of a row are three aligned shared-memory words,
+ * funnel-shifted to the base pixel; each horizontal interpolation is one PRMT + one 2-way dot
+ * product (IDP.2A).  The thread marches down the band: when the next destination row's upper
+ * source row is the previous one's lower row (5 of 6 rows at scale 1.2) its horizontal pass is
+ * reused.  Border ROWS are not recomputed: the thread that produces ROI row y also stores it to
+ * the padded rows that reflect onto y (needs h >= 20, checked on the host). */
+#ifndef RS_TH
+#define RS_TH 16
 #endif
-__global__ void __launch_bounds__(256) k_resize_w4(LevelDev S, LevelDev D, const uint4* __restrict__ xcoef,
-                                                   const uint32_t* __restrict__ xmeta,
-                                                   const short4* __restrict__ ypad, unsigned rcp_chunks) {
-    const int chunks = D.pitch / 4;
-    const unsigned i = blockIdx.x * 256u + threadIdx.x;
-    const int rg = (int)__umulhi(i, rcp_chunks);
-    const int r_first = rg * RS_RPT;
-    if (r_first >= D.rows) return;
-    const int c = (int)i - rg * chunks;
+__global__ void __launch_bounds__(512) k_resize_band(LevelDev S, LevelDev D) {
+    extern __shared__ __align__(128) uint8_t rsm[];
+    __shared__ __align__(8) uint64_t s_bar;
     const int f = blockIdx.y;
-    const uint32_t meta = __ldg(xmeta + c);
+    const int y0 = blockIdx.x * RS_TH, y1 = min(y0 + RS_TH, D.h);
+    const int sy_first = __ldg(D.ytab + y0).x;
+    const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&s_bar);
+    if (threadIdx.x == 0) {
+        const uint32_t bytes = (uint32_t)(__ldg(D.ytab + y1 - 1).x + 2 - sy_first) * (uint32_t)S.pitch;
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"((uint32_t)__cvta_generic_to_shared(rsm)),
+                       "l"(S.base + (size_t)f * S.frame_bytes + (size_t)(ORBX_EDGE + sy_first) * S.pitch), "r"(bytes), "r"(bar) : "memory");
+    }
+    /* the column tables are fetched while the copy is in flight */
+    const int c = threadIdx.x;
+    const bool act = c < D.pitch / 4;
+    const uint32_t meta = act ? __ldg(D.xmeta + c) : 0xFFFFFFFFu;   /* base byte (16b) | 4-bit pixel offsets; ~0 = outside the bordered row */
+    const uint32_t selw = act ? __ldg(D.xsel + c) : 0u;
+    const uint4 cf = act ? __ldg(D.xcoef + c) : make_uint4(0, 0, 0, 0);
+    __syncthreads();            /* barrier init visible to all waiters */
+    od_wait(bar, 0u);
     if (meta == 0xFFFFFFFFu) return;
-    const uint32_t selw = __ldg(D.xsel + c);
-    const uint4 cf = __ldg(xcoef + c);
     const uint32_t cfs[4] = {cf.x, cf.y, cf.z, cf.w};
+    const uint32_t sel[4] = {selw, selw >> 8, selw >> 16, selw >> 24};   /* PRMT reads the low 2 selector nibbles */
     const uint32_t base = meta & 0xFFFFu;
     const int sh = (base & 3) * 8;
-    const uint32_t spw = (uint32_t)S.pitch >> 2;
-    const uint32_t* src = reinterpret_cast<const uint32_t*>(S.base + (size_t)f * S.frame_bytes + (size_t)ORBX_EDGE * S.pitch) + (base >> 2);
-    uint32_t* dst = reinterpret_cast<uint32_t*>(D.base + (size_t)f * D.frame_bytes + (size_t)r_first * D.pitch) + c;
+    const uint32_t spitch = (uint32_t)S.pitch;
+    const size_t dpitch = (size_t)D.pitch;
+    const uint32_t s_src = (uint32_t)__cvta_generic_to_shared(rsm) + (base & ~3u);     /* shared-window address of the word's first source word, row 0 */
+    uint8_t* drow = D.base + (size_t)f * D.frame_bytes + (size_t)(y0 + ORBX_EDGE) * dpitch + 4 * c;
+    auto hrow = [&](uint32_t r, uint32_t (&H)[4]) {          /* horizontal pass of staged row r, >> 4 */
+        uint32_t a0, a1, a2;
+        asm volatile("ld.shared.u32 %0, [%3];\n\tld.shared.u32 %1, [%3+4];\n\tld.shared.u32 %2, [%3+8];"
+                     : "=r"(a0), "=r"(a1), "=r"(a2) : "r"(s_src + r * spitch));
+        const uint32_t U = __funnelshift_r(a0, a1, sh), V = __funnelshift_r(a1, a2, sh);
 #pragma unroll
-    for (int j = 0; j < RS_RPT; ++j) {
-        if (r_first + j < D.rows) {
-            const short4 yt = __ldg(ypad + r_first + j);       /* {sy, b0, b1} for the padded row */
-            const uint32_t* row0 = src + (uint32_t)yt.x * spw;
-            const uint32_t* row1 = row0 + spw;                 /* row sy+1 exists in the bordered source */
-            const uint32_t a0 = __ldg(row0), a1 = __ldg(row0 + 1), a2 = __ldg(row0 + 2);
-            const uint32_t b0 = __ldg(row1), b1 = __ldg(row1 + 1), b2 = __ldg(row1 + 2);
-            const uint32_t U0 = __funnelshift_r(a0, a1, sh), V0 = __funnelshift_r(a1, a2, sh);
-            const uint32_t U1 = __funnelshift_r(b0, b1, sh), V1 = __funnelshift_r(b1, b2, sh);
-            /* (b * (H >> 4)) >> 16 as one IMAD.HI: b is pre-shifted by 16 */
-            const uint32_t wy0 = (uint32_t)yt.y << 16, wy1 = (uint32_t)yt.z << 16;
-            uint32_t out = 0;
+        for (int k = 0; k < 4; ++k) H[k] = __dp2a_lo(cfs[k], __byte_perm(U, V, sel[k]), 0u) >> 4;
+    };
+    uint32_t H0[4], H1[4] = {0, 0, 0, 0};
+    uint32_t prev = 0x4000u;
+    const uint2* ytp = reinterpret_cast<const uint2*>(D.ytab + y0);
+    const unsigned h_inner = (unsigned)(D.h - 2 * (ORBX_EDGE + 1));     /* rows [20, h-20) have no mirror image in the border */
+#pragma unroll 1
+    for (int y = y0; y < y1; ++y) {
+        const uint2 yt = __ldg(ytp++);                       /* {sy | b0 << 16, b1}; row sy+1 exists in the bordered source */
+        const uint32_t r = (yt.x & 0xFFFFu) - (uint32_t)sy_first;
+        if (r == prev + 1) {
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                const uint32_t sel = selw >> (8 * k);            /* PRMT reads the low 2 selector nibbles we need */
-                const uint32_t r0 = __dp2a_lo(cfs[k], __byte_perm(U0, V0, sel), 0u);
-                const uint32_t r1 = __dp2a_lo(cfs[k], __byte_perm(U1, V1, sel), 0u);
-                out |= ((__umulhi(wy0, r0 >> 4) + __umulhi(wy1, r1 >> 4) + 2u) >> 2) << (8 * k);
-            }
-            dst[(size_t)j * (D.pitch >> 2)] = out;
+            for (int k = 0; k < 4; ++k) H0[k] = H1[k];
+        } else {
+            hrow(r, H0);
         }
+        hrow(r + 1, H1);
+        prev = r;
+        /* (b * (H >> 4)) >> 16 as one IMAD.HI: b is pre-shifted by 16 */
+        const uint32_t wy0 = yt.x & 0xFFFF0000u, wy1 = yt.y << 16;
+        uint32_t o[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) o[k] = (__umulhi(wy0, H0[k]) + __umulhi(wy1, H1[k]) + 2u) >> 2;
+        const uint32_t out = __byte_perm(__byte_perm(o[0], o[1], 0x0040), __byte_perm(o[2], o[3], 0x0040), 0x5410);
+        *reinterpret_cast<uint32_t*>(drow) = out;
+        if ((unsigned)(y - (ORBX_EDGE + 1)) >= h_inner) {     /* first / last 20 rows: also the border rows that reflect onto y */
+            uint8_t* col = D.base + (size_t)f * D.frame_bytes + 4 * c;
+            if (y >= 1 && y <= ORBX_EDGE) *reinterpret_cast<uint32_t*>(col + (size_t)(ORBX_EDGE - y) * dpitch) = out;
+            const int yb = D.h - 1 - y;
+            if (yb >= 1 && yb <= ORBX_EDGE) *reinterpret_cast<uint32_t*>(col + (size_t)(ORBX_EDGE + D.h - 1 + yb) * dpitch) = out;
+        }
+        drow += dpitch;
     }
 }
 
@@ -222,13 +264,6 @@ struct ODMaps { CUtensorMap blur[ORBX_MAX_LEVELS]; CUtensorMap pyr[ORBX_MAX_LEVE
 __device__ __forceinline__ void od_tma3(uint32_t dst, const CUtensorMap* map, int c0, int c1, int c2, uint32_t bar) {
     asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
                  ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(bar) : "memory");
-}
-__device__ __forceinline__ void od_wait(uint32_t bar, uint32_t parity) {
-    uint32_t done;
-    do {
-        asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
-                     : "=r"(done) : "r"(bar), "r"(parity) : "memory");
-    } while (!done);
 }
 
 /* lane 0 adds v to a shared counter and gets the old value; other lanes keep `old`.  Written as a
@@ -1639,6 +1674,7 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
             std::vector<uint8_t> wt(std::max<size_t>(wbytes, 16), 0);
             CK(cudaMalloc(&e->d_wtabs, wt.size()));
             size_t woff = 0, toff = 0;
+            int max_band_smem = 0;
             for (int l = 0; l < nl; ++l) {
                 LevelDev& L = e->lv[l];
                 const short4* xt = tabs.data() + toff;
@@ -1680,9 +1716,18 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
                     xc[c] = make_uint4(cf[0], cf[1], cf[2], cf[3]);
                 }
                 for (int r = 0; r < L.rows; ++r) yp[r] = yt[refl(r - ORBX_EDGE, L.h)];
-                L.fast_resize = ok ? 1 : 0;
+                /* k_resize_band: row mirroring needs a single reflection, one thread per word, and the
+                 * band's source rows (contiguous, whole padded rows) must fit in shared memory */
+                int max_src = 0;
+                for (int y0 = 0; y0 < L.h; y0 += RS_TH)
+                    max_src = std::max(max_src, yt[std::min(y0 + RS_TH, L.h) - 1].x + 2 - yt[y0].x);
+                L.band_smem = max_src * e->lv[l - 1].pitch;
+                L.fast_resize = (ok && L.h > ORBX_EDGE && nw <= 512 && L.band_smem <= 200 * 1024) ? 1 : 0;
+                if (L.fast_resize && L.band_smem > 48 * 1024) max_band_smem = std::max(max_band_smem, L.band_smem);
             }
             CK(cudaMemcpyAsync(e->d_wtabs, wt.data(), wt.size(), cudaMemcpyHostToDevice, e->stream));
+            if (max_band_smem)
+                CK(cudaFuncSetAttribute(k_resize_band, cudaFuncAttributeMaxDynamicSharedMemorySize, max_band_smem));
             CK(cudaStreamSynchronize(e->stream));
         }
         CK(cudaMemcpyAsync(e->d_tabs, tabs.data(), tabs.size() * sizeof(short4), cudaMemcpyHostToDevice, e->stream));
@@ -1810,7 +1855,7 @@ extern "C" orbx_status orbx_extract_device(orbx_extractor* e, const uint8_t* d_i
             const unsigned ch = D.pitch / 4;
             const dim3 grid(orbx_div_up(D.rows * ch, 256), batch);
             if (D.fast_resize)
-                k_resize_w4<<<dim3(orbx_div_up(orbx_div_up(D.rows, RS_RPT) * ch, 256), batch), 256, 0, st>>>(e->T.lv[l - 1], D, D.xcoef, D.xmeta, D.ypad, 0xFFFFFFFFu / ch + 1u);
+                k_resize_band<<<dim3(orbx_div_up(D.h, RS_TH), batch), (int)orbx_align_up(ch, 32), D.band_smem, st>>>(e->T.lv[l - 1], D);
             else
                 k_resize<<<grid, 256, 0, st>>>(e->T.lv[l - 1], D, 0xFFFFFFFFu / ch + 1u);
             ++launches;

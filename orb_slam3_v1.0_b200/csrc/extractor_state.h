@@ -21,6 +21,7 @@ struct LevelDev {
     const uint32_t* xsel;   /* per word: 4 PRMT selectors (source byte offsets off, off+1 of each pixel) */
     const short4* ypad;     /* per padded row {sy, b0, b1, 0} */
     int fast_resize;
+    int band_smem;          /* k_resize_band: bytes of the tallest band's source rows */
     int cell_begin, cell_end;
     int fast_box_rows;      /* tallest FAST strip of the level = rows of its TMA box */
     int N, nIni;
