@@ -24,6 +24,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <type_traits>
 #include <vector>
 
 #include "orbx_internal.h"
@@ -243,10 +244,12 @@ __global__ void __launch_bounds__(512) k_resize_band(LevelDev S, LevelDev D) {
 #ifndef FAST_THREADS
 #define FAST_THREADS 160        /* 5 warps: 256 -> 160 threads took 9 % off the kernel (less time parked at the region barriers) */
 #endif
-#define FAST_WQ 160           /* survivor queue per warp: < 32 left over + up to 128 new */
+#define FAST_EQ 64            /* entry queue per warp (u32): < 32 left over + up to 32 new (one entry = 8 px + survivor mask) */
+#define FAST_WQ 288           /* survivor queue per warp (u16): < 32 left over + up to 32 entries x 8 px */
 #define FAST_CQ 64            /* corner queue per warp: < 32 left over + up to 32 new */
 #define FAST_CL 1024          /* scored corners of a region kept as a list for the NMS pass (2 buffers); overflow -> map scan */
-#define FAST_QBYTES ((FAST_THREADS / 32) * (FAST_WQ + FAST_CQ) * 2 + 2 * FAST_CL * 2)
+#define FAST_WARP_QBYTES (FAST_EQ * 4 + (FAST_WQ + FAST_CQ) * 2)
+#define FAST_QBYTES ((FAST_THREADS / 32) * FAST_WARP_QBYTES + 2 * FAST_CL * 2)
 #define FAST_MAX_ROWS 76      /* cells are at most 69+6 px high (nRows==1 levels) */
 
 struct Unit {
@@ -300,9 +303,10 @@ __device__ __forceinline__ int arc_strength(const int* e) {
 
 /* per-byte "d > th" for 4 packed u8: bit 7 of each byte of the result.  th <= 127: bit 7 of d
  * decides or the low 7 bits carry; th >= 128: bit 7 of d AND the low 7 bits beat th-128. */
-__device__ __forceinline__ uint32_t gt4(uint32_t d, uint32_t k7f, bool hi) {
+template <bool HI>
+__device__ __forceinline__ uint32_t gt4(uint32_t d, uint32_t k7f) {
     const uint32_t c = (d & 0x7f7f7f7fu) + k7f;
-    return (hi ? (c & d) : (c | d)) & 0x80808080u;
+    return (HI ? (c & d) : (c | d)) & 0x80808080u;
 }
 
 /* 2^32 / d rounded up, d = 2..64: n / d == umulhi(n, c_rcp.v[d]) for the small n used below */
@@ -327,8 +331,8 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_units(Tables T, const Uni
     const int map_bytes = rows * tp;
     uint8_t* tile = fsm;
     uint8_t* score = fsm + map_bytes;
-    unsigned short* wq = reinterpret_cast<unsigned short*>(fsm + 2 * map_bytes);   /* [warps][FAST_WQ + FAST_CQ] */
-    unsigned short* clist = wq + (FAST_THREADS / 32) * (FAST_WQ + FAST_CQ);        /* [2][FAST_CL] */
+    uint8_t* wq = fsm + 2 * map_bytes;                                             /* [warps][FAST_WARP_QBYTES] */
+    unsigned short* clist = reinterpret_cast<unsigned short*>(wq + (FAST_THREADS / 32) * FAST_WARP_QBYTES);   /* [2][FAST_CL] */
     __shared__ int s_ncl[3];        /* corners appended to the region's list (may exceed FAST_CL = overflow), by region % 3 */
     __shared__ int s_cnt[FAST_UC];
 
@@ -362,7 +366,8 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_units(Tables T, const Uni
     uint32_t* bucket = scratch + (size_t)f * slots_per_frame;     /* unordered NMS survivors, per cell at slot_off */
     const unsigned lt_mask = (1u << lane) - 1u;
     /* warp-private work queues (tile indices): quick-test survivors and corners awaiting their score */
-    unsigned short* q = wq + wid * (FAST_WQ + FAST_CQ);
+    uint32_t* eq = reinterpret_cast<uint32_t*>(wq + wid * FAST_WARP_QBYTES);
+    unsigned short* q = reinterpret_cast<unsigned short*>(eq + FAST_EQ);
     unsigned short* cq = q + FAST_WQ;
     int rseq = 0;                                                 /* regions processed so far */
     const unsigned rcp_tp = 0xFFFFFFFFu / (unsigned)tp + 1u;
@@ -386,19 +391,21 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_units(Tables T, const Uni
             const int thi = (k1 == ncell ? U.tw - 3 : 3 + k1 * wc) + shift;
             k0 = k1;
             if (thi <= tlo) continue;
-            const int w0 = tlo >> 2, wl = (thi - 1) >> 2, rw = wl - w0 + 1;
-            const uint32_t m_first = 0xFFFFFFFFu << (8 * (tlo & 3));
-            const uint32_t m_last = 0xFFFFFFFFu >> (8 * (3 - ((thi - 1) & 3)));
-            /* flat (row, word) walk with stride FAST_THREADS, advanced incrementally */
-            const uint32_t rcp_rw = c_rcp.v[rw];                  /* rw <= tp / 4 <= 64 */
-            const int dy = rw == 1 ? FAST_THREADS : (int)__umulhi((uint32_t)FAST_THREADS, rcp_rw), dw = FAST_THREADS - dy * rw;
-            const int y_init = rw == 1 ? tid : (int)__umulhi((uint32_t)tid, rcp_rw), w_init = tid - y_init * rw;
-            const int iters = (dh * rw + FAST_THREADS - 1) / FAST_THREADS;
+            /* the region is walked in aligned 8-byte units (two words = 8 px per thread and step):
+             * flat (row, pair) walk with stride FAST_THREADS, advanced incrementally */
+            const int p0 = tlo >> 3, rp = ((thi - 1) >> 3) - p0 + 1;
+            const unsigned long long mf64 = ~0ull << (8 * (tlo & 7)), ml64 = ~0ull >> (8 * (7 - ((thi - 1) & 7)));
+            const uint32_t mfA = (uint32_t)mf64, mfB = (uint32_t)(mf64 >> 32), mlA = (uint32_t)ml64, mlB = (uint32_t)(ml64 >> 32);
+            const uint32_t rcp_rp = c_rcp.v[rp];                  /* rp <= tp / 8 <= 32 */
+            const int dy = rp == 1 ? FAST_THREADS : (int)__umulhi((uint32_t)FAST_THREADS, rcp_rp), dw = FAST_THREADS - dy * rp;
+            const int y_init = rp == 1 ? tid : (int)__umulhi((uint32_t)tid, rcp_rp), w_init = tid - y_init * rp;
+            const int iters = (dh * rp + FAST_THREADS - 1) / FAST_THREADS;
 
-            /* ---- detection: quick reject on 4 px/thread -> survivor queue -> exact FAST-9 test in
-             * full batches of 32 -> corner queue -> corner score in batches of 32.  No block barrier:
-             * the queues belong to the warp, the score map is written at distinct bytes. */
-            int nq = 0, ncq = 0;                                  /* warp-uniform queue fills */
+            /* ---- detection: quick reject on 8 px/thread -> entry queue (8-px unit + survivor mask,
+             * one ballot per step) -> expanded 32 entries at a time into the survivor queue -> exact
+             * FAST-9 test in full batches of 32 -> corner queue -> corner score in batches of 32.  No
+             * block barrier: the queues belong to the warp, the score map is written at distinct bytes. */
+            int neq = 0, nq = 0, ncq = 0;                         /* warp-uniform queue fills */
             int* ncl = &s_ncl[rseq % 3];
             unsigned short* cl = clist + (rseq & 1) * FAST_CL;
             auto score_batch = [&](const unsigned short* src, int cnt) {
@@ -449,46 +456,70 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_units(Tables T, const Uni
                 __syncwarp();
                 if (ncq >= 32) { ncq -= 32; score_batch(cq + ncq, 32); }
             };
-            {
+            /* 32 (or the last < 32) entries -> survivor queue: lane = entry, exclusive scan of the
+             * survivor counts by shuffles, then every lane writes its own <= 8 tile indices */
+            auto expand_batch = [&](const uint32_t* src, int cnt) {
+                const uint32_t ent = lane < cnt ? src[lane] : 0u;
+                uint32_t m = ent >> 16;                           /* bit j: pixel j of the unit */
+                const int k = __popc(m);
+                int incl = k;
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) {
+                    const int t = __shfl_up_sync(0xffffffffu, incl, d);
+                    if (lane >= d) incl += t;
+                }
+                const int total = __shfl_sync(0xffffffffu, incl, 31);
+                int off = nq + incl - k;
+                const uint32_t base = ent & 0xFFFFu;
+                while (m) {
+                    const int bpos = __ffs(m) - 1;
+                    m &= m - 1;
+                    q[off++] = (unsigned short)(base + bpos);
+                }
+                nq += total;
+                __syncwarp();
+                while (nq >= 32) { nq -= 32; exact_batch(q + nq, 32); }
+            };
+            auto scan = [&](auto hi_tag) {
+                constexpr bool HI = decltype(hi_tag)::value;
+                const uint2* tile64 = reinterpret_cast<const uint2*>(tile);
+                const int PP = WP >> 1;                           /* pairs per tile row */
                 int y = y_init, w = w_init;
                 for (int it = 0; it < iters; ++it) {
-                    uint32_t pass4 = 0;
-                    int widx = 0;
+                    uint32_t pa = 0, pb = 0;
+                    int pidx = 0;
                     if (y < dh) {
-                        widx = (y + 3) * WP + w0 + w;
-                        const uint32_t v4 = tile32[widx];
-                        const uint32_t up = tile32[widx - 3 * WP], dn = tile32[widx + 3 * WP];
-                        const uint32_t lw = tile32[widx - 1], rgt = tile32[widx + 1];   /* in-tile: rows 3..th-4 */
-                        const uint32_t l4 = __funnelshift_r(lw, v4, 8);      /* bytes at column-3 */
-                        const uint32_t r4 = __funnelshift_r(v4, rgt, 24);    /* bytes at column+3 */
-                        const uint32_t g0 = gt4(__vabsdiffu4(dn, v4), k7f, hi), g8 = gt4(__vabsdiffu4(up, v4), k7f, hi);
-                        const uint32_t g4 = gt4(__vabsdiffu4(r4, v4), k7f, hi), g12 = gt4(__vabsdiffu4(l4, v4), k7f, hi);
-                        pass4 = (g0 | g8) & (g4 | g12);
-                        if (w == 0) pass4 &= m_first;
-                        if (w == rw - 1) pass4 &= m_last;
+                        pidx = (y + 3) * PP + p0 + w;
+                        const uint2 v = tile64[pidx], up = tile64[pidx - 3 * PP], dn = tile64[pidx + 3 * PP];
+                        const uint32_t lw = tile32[2 * pidx - 1], rgt = tile32[2 * pidx + 2];   /* in-tile: rows 3..th-4 */
+                        const uint32_t la = __funnelshift_r(lw, v.x, 8), ra = __funnelshift_r(v.x, v.y, 24);    /* bytes at column -3 / +3 */
+                        const uint32_t lb = __funnelshift_r(v.x, v.y, 8), rb = __funnelshift_r(v.y, rgt, 24);
+                        pa = (gt4<HI>(__vabsdiffu4(dn.x, v.x), k7f) | gt4<HI>(__vabsdiffu4(up.x, v.x), k7f)) &
+                             (gt4<HI>(__vabsdiffu4(ra, v.x), k7f) | gt4<HI>(__vabsdiffu4(la, v.x), k7f));
+                        pb = (gt4<HI>(__vabsdiffu4(dn.y, v.y), k7f) | gt4<HI>(__vabsdiffu4(up.y, v.y), k7f)) &
+                             (gt4<HI>(__vabsdiffu4(rb, v.y), k7f) | gt4<HI>(__vabsdiffu4(lb, v.y), k7f));
+                        if (w == 0) { pa &= mfA; pb &= mfB; }
+                        if (w == rp - 1) { pa &= mlA; pb &= mlB; }
                     }
-                    /* warp prefix of the per-lane survivor counts (0..4) from three ballots */
-                    const int n = __popc(pass4);
-                    const unsigned b0 = __ballot_sync(0xffffffffu, n & 1), b1 = __ballot_sync(0xffffffffu, n & 2),
-                                   b2 = __ballot_sync(0xffffffffu, n & 4);
-                    const int wtot = __popc(b0) + 2 * __popc(b1) + 4 * __popc(b2);
-                    if (wtot) {
-                        int b = nq + __popc(b0 & lt_mask) + 2 * __popc(b1 & lt_mask) + 4 * __popc(b2 & lt_mask);
-                        const int p4 = widx * 4;
-                        if (pass4 & 0x00000080u) q[b++] = (unsigned short)(p4);
-                        if (pass4 & 0x00008000u) q[b++] = (unsigned short)(p4 + 1);
-                        if (pass4 & 0x00800000u) q[b++] = (unsigned short)(p4 + 2);
-                        if (pass4 & 0x80000000u) q[b] = (unsigned short)(p4 + 3);
-                        nq += wtot;
+                    const unsigned bal = __ballot_sync(0xffffffffu, (pa | pb) != 0u);
+                    if (bal) {
+                        if (pa | pb) {
+                            /* bits 7/15/23/31 -> 4-bit mask: the multiplier moves them to bits 28..31 */
+                            const uint32_t m8 = ((pa * 0x00204081u) >> 28) | (((pb * 0x00204081u) >> 28) << 4);
+                            eq[neq + __popc(bal & lt_mask)] = (uint32_t)(pidx * 8) | (m8 << 16);
+                        }
+                        neq += __popc(bal);
                         __syncwarp();
-                        while (nq >= 32) { nq -= 32; exact_batch(q + nq, 32); }
+                        if (neq >= 32) { neq -= 32; expand_batch(eq + neq, 32); }
                     }
                     y += dy; w += dw;
-                    if (w >= rw) { w -= rw; ++y; }
+                    if (w >= rp) { w -= rp; ++y; }
                 }
+                if (neq) { expand_batch(eq, neq); neq = 0; }
                 if (nq) exact_batch(q, nq);
                 if (ncq) score_batch(cq, ncq);
-            }
+            };
+            if (hi) scan(std::true_type{}); else scan(std::false_type{});
             __syncthreads();
 
             /* ---- non-maximum suppression: strict 3x3 local maxima inside the pixel's own cell go to
@@ -519,7 +550,13 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_units(Tables T, const Uni
                     nms(yt, idx - yt * tp);
                 }
             } else {
-                int y = y_init, w = w_init;
+                const int w0 = tlo >> 2, rw = ((thi - 1) >> 2) - w0 + 1;
+                const uint32_t m_first = 0xFFFFFFFFu << (8 * (tlo & 3));
+                const uint32_t m_last = 0xFFFFFFFFu >> (8 * (3 - ((thi - 1) & 3)));
+                const uint32_t rcp_rw = c_rcp.v[rw];              /* rw <= tp / 4 <= 64 */
+                const int dy = rw == 1 ? FAST_THREADS : (int)__umulhi((uint32_t)FAST_THREADS, rcp_rw), dw = FAST_THREADS - dy * rw;
+                int y = rw == 1 ? tid : (int)__umulhi((uint32_t)tid, rcp_rw), w = tid - y * rw;
+                const int iters = (dh * rw + FAST_THREADS - 1) / FAST_THREADS;
                 for (int it = 0; it < iters; ++it) {
                     if (y < dh) {
                         const int widx = (y + 3) * WP + w0 + w;
