@@ -1648,6 +1648,26 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
     CK(cudaMalloc(&e->d_tabs, tab_entries * sizeof(short4)));
     CK(cudaMalloc(&e->d_cells, std::max<size_t>(e->cells.size(), 1) * sizeof(Cell)));
     e->nunits = (int)units.size();
+    /* Shared memory per CTA follows the tallest strip; the top levels have few, tall cells.  Units
+     * are ordered by strip height and launched as two groups when that buys resident CTAs:
+     * cost = strip area / CTAs per SM at the group's tile size. */
+    /* (a unit's tile must hold its level's TMA box = the level's tallest strip) */
+    auto need_rows = [&](const Unit& u) { return e->lv[u.level].fast_box_rows; };
+    std::stable_sort(units.begin(), units.end(), [&](const Unit& a, const Unit& b) { return need_rows(a) < need_rows(b); });
+    e->nunits_short = 0;
+    e->fast_rows_short = e->fast_rows;
+    if (!units.empty()) {
+        auto ctas = [&](int rows) { return std::max<size_t>(1, (size_t)(227 * 1024) / ((size_t)2 * rows * e->fast_tp + FAST_QBYTES + 128 + 1024)); };
+        double head = 0, total = 0;
+        for (const Unit& u : units) total += (double)u.th * u.tw;
+        double best = total / ctas(e->fast_rows);
+        for (size_t i = 1; i < units.size(); ++i) {
+            head += (double)units[i - 1].th * units[i - 1].tw;
+            if (need_rows(units[i]) == need_rows(units[i - 1])) continue;
+            const double c = head / ctas(need_rows(units[i - 1])) + (total - head) / ctas(e->fast_rows);
+            if (c < best * 0.97) { best = c; e->nunits_short = (int)i; e->fast_rows_short = need_rows(units[i - 1]); }
+        }
+    }
     if (e->fast_tp > 256) { orbx_set_error("FAST strip width %d exceeds the 256-byte TMA box", e->fast_tp); free_all(e); return ORBX_ERR_INVALID; }
     if ((size_t)e->fast_rows * e->fast_tp > 32767) { orbx_set_error("FAST strip %dx%d exceeds the 15-bit tile index", e->fast_tp, e->fast_rows); free_all(e); return ORBX_ERR_INVALID; }
     CK(cudaMalloc(&e->d_units, std::max<size_t>(units.size(), 1) * sizeof(Unit)));
@@ -1914,8 +1934,14 @@ extern "C" orbx_status orbx_extract_device(orbx_extractor* e, const uint8_t* d_i
     if (fork_blur == 1) { orbx_status r = launch_side_blur(); if (r != ORBX_OK) return r; }
     /* stage 1 */
     if (e->ncells > 0) {
-        k_fast_units<<<dim3(e->nunits, batch), FAST_THREADS, (size_t)2 * e->fast_rows * e->fast_tp + FAST_QBYTES + 128, st>>>(
-            e->T, static_cast<const Unit*>(e->d_units), e->d_cells, e->ncells, e->P.ini_th_fast, e->P.min_th_fast, e->d_slots,
+        if (e->nunits_short > 0) {
+            k_fast_units<<<dim3(e->nunits_short, batch), FAST_THREADS, (size_t)2 * e->fast_rows_short * e->fast_tp + FAST_QBYTES + 128, st>>>(
+                e->T, static_cast<const Unit*>(e->d_units), e->d_cells, e->ncells, e->P.ini_th_fast, e->P.min_th_fast, e->d_slots,
+                e->d_cand, e->slots_per_frame, e->d_cell_count, e->fast_tp, e->fast_rows_short, e->fast_cl_cap, (const ODMaps*)e->d_odmaps);
+            ++launches;
+        }
+        k_fast_units<<<dim3(e->nunits - e->nunits_short, batch), FAST_THREADS, (size_t)2 * e->fast_rows * e->fast_tp + FAST_QBYTES + 128, st>>>(
+            e->T, static_cast<const Unit*>(e->d_units) + e->nunits_short, e->d_cells, e->ncells, e->P.ini_th_fast, e->P.min_th_fast, e->d_slots,
             e->d_cand, e->slots_per_frame, e->d_cell_count, e->fast_tp, e->fast_rows, e->fast_cl_cap, (const ODMaps*)e->d_odmaps);
         ++launches;
     }

@@ -68,6 +68,7 @@ struct orbx_extractor {
     int nblur_tiles = 0;
     int fast_tp = 8, fast_rows = 8, fast_list_cap = 2;
     int nunits = 0;
+    int nunits_short = 0, fast_rows_short = 8;   /* units [0, nunits_short) are launched with the smaller tile */
     int fast_cl_cap = 1024;         /* FAST corner-list entries in use (<= FAST_CL) */
     void* d_units = nullptr;        /* FAST units (extractor.cu: struct Unit) */
     /* device-side Frame grid of the last batch (matcher.cu: orbx_extractor_assign_grid) */
