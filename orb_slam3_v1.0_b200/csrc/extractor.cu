@@ -59,10 +59,10 @@ __device__ __forceinline__ void od_wait(uint32_t bar, uint32_t parity) {
 struct L0Split { int c_lo, ni, nb; int bc[6]; unsigned rcp_ni, rcp_nb; };
 
 __global__ void __launch_bounds__(256) k_level0(const uint8_t* __restrict__ src, size_t frame_stride,
-                                                int row_stride, LevelDev L, L0Split S, int vec_ok) {
+                                                int row_stride, LevelDev L, L0Split S, int vec_ok, int f0) {
     const unsigned i = blockIdx.x * 256u + threadIdx.x;
     const unsigned n_int = (unsigned)L.rows * S.ni;
-    const int f = blockIdx.y;
+    const int f = blockIdx.y + f0;
     int r, c;
     bool interior;
     if (i < n_int) {
@@ -108,13 +108,13 @@ __device__ __forceinline__ uint32_t resize_px(const uint8_t* __restrict__ s0, co
     return (uint32_t)((((b0 * (r0 >> 4)) >> 16) + ((b1 * (r1 >> 4)) >> 16) + 2) >> 2);
 }
 
-__global__ void __launch_bounds__(256) k_resize(LevelDev S, LevelDev D, unsigned rcp_chunks) {
+__global__ void __launch_bounds__(256) k_resize(LevelDev S, LevelDev D, unsigned rcp_chunks, int f0) {
     const int chunks = D.pitch / 4;
     const unsigned i = blockIdx.x * 256u + threadIdx.x;
     const int r = (int)__umulhi(i, rcp_chunks);
     if (r >= D.rows) return;
     const int c = (int)i - r * chunks;
-    const int f = blockIdx.y;
+    const int f = blockIdx.y + f0;
     const int x0 = c * 4 - ORBX_XOFF;
     if (x0 + 4 <= -ORBX_EDGE || x0 >= D.w + ORBX_EDGE) return;
     const int dy = reflect101(r - ORBX_EDGE, D.h);
@@ -148,10 +148,10 @@ __global__ void __launch_bounds__(256) k_resize(LevelDev S, LevelDev D, unsigned
 #ifndef RS_TH
 #define RS_TH 16
 #endif
-__global__ void __launch_bounds__(512) k_resize_band(LevelDev S, LevelDev D) {
+__global__ void __launch_bounds__(512) k_resize_band(LevelDev S, LevelDev D, int f0) {
     extern __shared__ __align__(128) uint8_t rsm[];
     __shared__ __align__(8) uint64_t s_bar;
-    const int f = blockIdx.y;
+    const int f = blockIdx.y + f0;
     const int y0 = blockIdx.x * RS_TH, y1 = min(y0 + RS_TH, D.h);
     const int sy_first = __ldg(D.ytab + y0).x;
     const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&s_bar);
@@ -336,7 +336,7 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_units(Tables T, const Uni
     __shared__ int s_ncl[3];        /* corners appended to the region's list (may exceed FAST_CL = overflow), by region % 3 */
     __shared__ int s_cnt[FAST_UC];
 
-    const int f = blockIdx.y;
+    const int f = blockIdx.y + T.f0;
     const Unit U = units[blockIdx.x];
     const LevelDev& L = T.lv[U.level];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
@@ -745,7 +745,7 @@ __global__ void __launch_bounds__(OCT_THREADS) k_octree(Tables T, const Cell* __
     __shared__ int s_tmp[OCT_THREADS / 32 + 1];
     __shared__ int s_T, s_CT;
 
-    const int level = blockIdx.x, f = blockIdx.y, tid = threadIdx.x;
+    const int level = blockIdx.x, f = blockIdx.y + T.f0, tid = threadIdx.x;
     const LevelDev& Lv = T.lv[level];
     const int N = Lv.N;
 
@@ -1061,7 +1061,7 @@ __global__ void __launch_bounds__(ORD_THREADS) k_order(Tables T, const uint32_t*
                                                         int* __restrict__ mono_out) {
     __shared__ int s_w[ORD_THREADS / 32];
     __shared__ int s_lvl_off[ORBX_MAX_LEVELS + 1];
-    const int f = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int f = blockIdx.x + T.f0, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     if (tid == 0) {
         int o = 0;
         for (int l = 0; l < T.nlevels; ++l) { s_lvl_off[l] = o; o += sel_count[f * T.nlevels + l]; }
@@ -1152,7 +1152,7 @@ __global__ void __launch_bounds__(128) k_blur7(Tables T, const int4* __restrict_
     const int wt = blockIdx.x * 4 + (threadIdx.x >> 5);
     if (wt >= ntiles) return;
     const int4 t = tiles[wt];                 /* {level, x0, y0, nrows} */
-    const int f = blockIdx.y, lane = threadIdx.x & 31;
+    const int f = blockIdx.y + T.f0, lane = threadIdx.x & 31;
     const LevelDev& L = T.lv[t.x];
     const int x = t.y - 4 + 4 * lane;         /* ROI column of this lane's word */
     const int xc = min(x, L.pitch - ORBX_XOFF - 4);
@@ -1283,7 +1283,7 @@ __global__ void __launch_bounds__(32 * OD_WARPS) k_orient_describe(Tables T, con
     __shared__ uint32_t s_d4[32];
     __shared__ __align__(8) uint64_t s_bar[OD_WARPS][4];      /* window 0, window 1, patch */
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const int f = blockIdx.y;
+    const int f = blockIdx.y + T.f0;
     if (threadIdx.x < 32) s_d4[threadIdx.x] = c_d4[threadIdx.x];
     if (lane < 3) {
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"((uint32_t)__cvta_generic_to_shared(&s_bar[wid][lane])) : "memory");
@@ -1459,6 +1459,7 @@ static void free_all(orbx_extractor* e) {
     for (void* p : hptrs) if (p) cudaFreeHost(p);
     for (int i = 0; i < 7; ++i) if (e->ev[i]) cudaEventDestroy(e->ev[i]);
     if (e->ev_stereo) cudaEventDestroy(e->ev_stereo);
+    for (int g = 0; g < ORBX_MAX_LANES; ++g) { if (e->ev_lane[g]) cudaEventDestroy(e->ev_lane[g]); if (e->lane[g]) cudaStreamDestroy(e->lane[g]); }
     if (e->ev_fork) cudaEventDestroy(e->ev_fork);
     if (e->ev_join) cudaEventDestroy(e->ev_join);
     if (e->side) cudaStreamDestroy(e->side);
@@ -1628,6 +1629,11 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
     CK(cudaEventCreateWithFlags(&e->ev_fork, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&e->ev_join, cudaEventDisableTiming));
     if (const char* v = getenv("ORBX_FORK_BLUR")) e->fork_blur = atoi(v);
+    if (const char* v = getenv("ORBX_LANES")) e->lanes = std::max(1, std::min(atoi(v), ORBX_MAX_LANES));
+    for (int g = 0; g < e->lanes && e->lanes > 1; ++g) {
+        CK(cudaStreamCreateWithFlags(&e->lane[g], cudaStreamNonBlocking));
+        CK(cudaEventCreateWithFlags(&e->ev_lane[g], cudaEventDisableTiming));
+    }
     for (int i = 0; i < 7; ++i) CK(cudaEventCreate(&e->ev[i]));
     CK(cudaFuncSetAttribute(k_octree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)e->oct_smem));
     {
@@ -1794,6 +1800,7 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
         CK(cudaStreamSynchronize(e->stream));
     }
     e->T.nlevels = nl;
+    e->T.f0 = 0;
     for (int l = 0; l < nl; ++l) e->T.lv[l] = e->lv[l];
     {
         /* TMA tensor maps for the describe stage: (row bytes, rows, frames) u8 views of every
@@ -1872,27 +1879,17 @@ extern "C" orbx_status orbx_extractor_set_profiling(orbx_extractor* e, int on) {
     return ORBX_OK;
 }
 
-extern "C" orbx_status orbx_extract_device(orbx_extractor* e, const uint8_t* d_images, size_t frame_stride,
-                                           int row_stride, int batch, const int* lapping) {
-    if (!e || !d_images) { orbx_set_error("null argument"); return d_images ? ORBX_ERR_INVALID : ORBX_ERR_EMPTY; }
-    if (batch < 1 || batch > e->P.max_batch || row_stride < e->P.width) {
-        orbx_set_error("batch %d outside [1,%d] or row_stride < width", batch, e->P.max_batch);
-        return ORBX_ERR_INVALID;
-    }
-    ORBX_CUDA(cudaSetDevice(e->P.device));
-    cudaStream_t st = e->stream;
+/* every stage of frames [f0, f0 + nb) on stream st; the blur may fork to `side` (nullptr: never) */
+static orbx_status enqueue_frames(orbx_extractor* e, const uint8_t* d_images, size_t frame_stride, int row_stride, int f0, int nb,
+                                  const int* d_lap, cudaStream_t st, cudaStream_t side, cudaEvent_t ev_fork, cudaEvent_t ev_join,
+                                  int& launches) {
     const int nl = e->nlevels;
-    int launches = 0;
-    const int* d_lap = nullptr;
-    if (lapping) {
-        memcpy(e->h_lapping, lapping, sizeof(int) * 2 * batch);
-        ORBX_CUDA(cudaMemcpyAsync(e->d_lapping, e->h_lapping, sizeof(int) * 2 * batch, cudaMemcpyHostToDevice, st));
-        d_lap = e->d_lapping;
-    }
+    Tables T = e->T;
+    T.f0 = f0;
     if (e->profiling) ORBX_CUDA(cudaEventRecord(e->ev[0], st));
     /* stage 0 */
     {
-        const LevelDev& L0 = e->T.lv[0];
+        const LevelDev& L0 = T.lv[0];
         const int vec_ok = (row_stride % 16 == 0) && (frame_stride % 16 == 0) && (((uintptr_t)d_images) % 16 == 0);
         L0Split S;
         memset(&S, 0, sizeof(S));
@@ -1905,16 +1902,16 @@ extern "C" orbx_status orbx_extract_device(orbx_extractor* e, const uint8_t* d_i
         }
         S.rcp_ni = 0xFFFFFFFFu / (unsigned)std::max(S.ni, 1) + 1u;
         S.rcp_nb = 0xFFFFFFFFu / (unsigned)std::max(S.nb, 1) + 1u;
-        k_level0<<<dim3(orbx_div_up(L0.rows * (S.ni + S.nb), 256), batch), 256, 0, st>>>(d_images, frame_stride, row_stride, L0, S, vec_ok);
+        k_level0<<<dim3(orbx_div_up(L0.rows * (S.ni + S.nb), 256), nb), 256, 0, st>>>(d_images, frame_stride, row_stride, L0, S, vec_ok, f0);
         ++launches;
         for (int l = 1; l < nl; ++l) {
-            const LevelDev& D = e->T.lv[l];
+            const LevelDev& D = T.lv[l];
             const unsigned ch = D.pitch / 4;
-            const dim3 grid(orbx_div_up(D.rows * ch, 256), batch);
+            const dim3 grid(orbx_div_up(D.rows * ch, 256), nb);
             if (D.fast_resize)
-                k_resize_band<<<dim3(orbx_div_up(D.h, RS_TH), batch), (int)orbx_align_up(ch, 32), D.band_smem, st>>>(e->T.lv[l - 1], D);
+                k_resize_band<<<dim3(orbx_div_up(D.h, RS_TH), nb), (int)orbx_align_up(ch, 32), D.band_smem, st>>>(T.lv[l - 1], D, f0);
             else
-                k_resize<<<grid, 256, 0, st>>>(e->T.lv[l - 1], D, 0xFFFFFFFFu / ch + 1u);
+                k_resize<<<grid, 256, 0, st>>>(T.lv[l - 1], D, 0xFFFFFFFFu / ch + 1u, f0);
             ++launches;
         }
     }
@@ -1922,12 +1919,12 @@ extern "C" orbx_status orbx_extract_device(orbx_extractor* e, const uint8_t* d_i
     /* stage 4 needs the pyramid only: outside profiling mode it runs on the side stream beside the
      * quadtree and the ordering (latency-bound, most issue slots free); mode 1 forks it before
      * FAST instead */
-    const int fork_blur = e->profiling ? 0 : e->fork_blur;
+    const int fork_blur = (e->profiling || !side) ? 0 : e->fork_blur;
     auto launch_side_blur = [&]() -> orbx_status {
-        ORBX_CUDA(cudaEventRecord(e->ev_fork, st));
-        ORBX_CUDA(cudaStreamWaitEvent(e->side, e->ev_fork, 0));
-        k_blur7<<<dim3(orbx_div_up(e->nblur_tiles, 4), batch), 128, 0, e->side>>>(e->T, e->d_blur_tiles, e->nblur_tiles);
-        ORBX_CUDA(cudaEventRecord(e->ev_join, e->side));
+        ORBX_CUDA(cudaEventRecord(ev_fork, st));
+        ORBX_CUDA(cudaStreamWaitEvent(side, ev_fork, 0));
+        k_blur7<<<dim3(orbx_div_up(e->nblur_tiles, 4), nb), 128, 0, side>>>(T, e->d_blur_tiles, e->nblur_tiles);
+        ORBX_CUDA(cudaEventRecord(ev_join, side));
         ++launches;
         return ORBX_OK;
     };
@@ -1935,45 +1932,83 @@ extern "C" orbx_status orbx_extract_device(orbx_extractor* e, const uint8_t* d_i
     /* stage 1 */
     if (e->ncells > 0) {
         if (e->nunits_short > 0) {
-            k_fast_units<<<dim3(e->nunits_short, batch), FAST_THREADS, (size_t)2 * e->fast_rows_short * e->fast_tp + FAST_QBYTES + 128, st>>>(
-                e->T, static_cast<const Unit*>(e->d_units), e->d_cells, e->ncells, e->P.ini_th_fast, e->P.min_th_fast, e->d_slots,
+            k_fast_units<<<dim3(e->nunits_short, nb), FAST_THREADS, (size_t)2 * e->fast_rows_short * e->fast_tp + FAST_QBYTES + 128, st>>>(
+                T, static_cast<const Unit*>(e->d_units), e->d_cells, e->ncells, e->P.ini_th_fast, e->P.min_th_fast, e->d_slots,
                 e->d_cand, e->slots_per_frame, e->d_cell_count, e->fast_tp, e->fast_rows_short, e->fast_cl_cap, (const ODMaps*)e->d_odmaps);
             ++launches;
         }
-        k_fast_units<<<dim3(e->nunits - e->nunits_short, batch), FAST_THREADS, (size_t)2 * e->fast_rows * e->fast_tp + FAST_QBYTES + 128, st>>>(
-            e->T, static_cast<const Unit*>(e->d_units) + e->nunits_short, e->d_cells, e->ncells, e->P.ini_th_fast, e->P.min_th_fast, e->d_slots,
+        k_fast_units<<<dim3(e->nunits - e->nunits_short, nb), FAST_THREADS, (size_t)2 * e->fast_rows * e->fast_tp + FAST_QBYTES + 128, st>>>(
+            T, static_cast<const Unit*>(e->d_units) + e->nunits_short, e->d_cells, e->ncells, e->P.ini_th_fast, e->P.min_th_fast, e->d_slots,
             e->d_cand, e->slots_per_frame, e->d_cell_count, e->fast_tp, e->fast_rows, e->fast_cl_cap, (const ODMaps*)e->d_odmaps);
         ++launches;
     }
     if (e->profiling) ORBX_CUDA(cudaEventRecord(e->ev[2], st));
     if (fork_blur == 2) { orbx_status r = launch_side_blur(); if (r != ORBX_OK) return r; }
     /* stage 2 */
-    k_octree<<<dim3(nl, batch), OCT_THREADS, e->oct_smem, st>>>(e->T, e->d_cells, e->ncells, e->d_slots, e->slots_per_frame,
+    k_octree<<<dim3(nl, nb), OCT_THREADS, e->oct_smem, st>>>(T, e->d_cells, e->ncells, e->d_slots, e->slots_per_frame,
                                                                  e->d_cell_count, e->d_cand, e->d_pnode, e->cand_per_frame,
                                                                  e->d_cand_count, e->d_sel, e->sel_per_frame, e->d_sel_count,
                                                                  e->maxn, e->max_cells_level, OCT_SCAND);
     ++launches;
     if (e->profiling) ORBX_CUDA(cudaEventRecord(e->ev[3], st));
     /* stage 3 */
-    k_order<<<batch, ORD_THREADS, 0, st>>>(e->T, e->d_sel, e->sel_per_frame, e->d_sel_count, d_lap, e->d_dest, e->d_nk,
+    k_order<<<nb, ORD_THREADS, 0, st>>>(T, e->d_sel, e->sel_per_frame, e->d_sel_count, d_lap, e->d_dest, e->d_nk,
                                            e->d_nk + e->P.max_batch);
     ++launches;
     if (e->profiling) ORBX_CUDA(cudaEventRecord(e->ev[4], st));
     /* stage 4 */
     if (fork_blur) {
-        ORBX_CUDA(cudaStreamWaitEvent(st, e->ev_join, 0));
+        ORBX_CUDA(cudaStreamWaitEvent(st, ev_join, 0));
     } else {
-        k_blur7<<<dim3(orbx_div_up(e->nblur_tiles, 4), batch), 128, 0, st>>>(e->T, e->d_blur_tiles, e->nblur_tiles);
+        k_blur7<<<dim3(orbx_div_up(e->nblur_tiles, 4), nb), 128, 0, st>>>(T, e->d_blur_tiles, e->nblur_tiles);
         ++launches;
     }
     if (e->profiling) ORBX_CUDA(cudaEventRecord(e->ev[5], st));
     /* stage 5 */
     {
-        k_orient_describe<<<dim3(orbx_div_up((int)e->sel_per_frame, OD_WARPS * OD_KPW), batch), 32 * OD_WARPS, OD_SMEM, st>>>(
-            e->T, (const ODMaps*)e->d_odmaps, e->d_sel, e->sel_per_frame, e->d_sel_count, e->d_dest, e->d_kps, e->d_desc, e->kcap);
+        k_orient_describe<<<dim3(orbx_div_up((int)e->sel_per_frame, OD_WARPS * OD_KPW), nb), 32 * OD_WARPS, OD_SMEM, st>>>(
+            T, (const ODMaps*)e->d_odmaps, e->d_sel, e->sel_per_frame, e->d_sel_count, e->d_dest, e->d_kps, e->d_desc, e->kcap);
         ++launches;
     }
     if (e->profiling) ORBX_CUDA(cudaEventRecord(e->ev[6], st));
+    return ORBX_OK;
+}
+
+extern "C" orbx_status orbx_extract_device(orbx_extractor* e, const uint8_t* d_images, size_t frame_stride,
+                                           int row_stride, int batch, const int* lapping) {
+    if (!e || !d_images) { orbx_set_error("null argument"); return d_images ? ORBX_ERR_INVALID : ORBX_ERR_EMPTY; }
+    if (batch < 1 || batch > e->P.max_batch || row_stride < e->P.width) {
+        orbx_set_error("batch %d outside [1,%d] or row_stride < width", batch, e->P.max_batch);
+        return ORBX_ERR_INVALID;
+    }
+    ORBX_CUDA(cudaSetDevice(e->P.device));
+    cudaStream_t st = e->stream;
+    int launches = 0;
+    const int* d_lap = nullptr;
+    if (lapping) {
+        memcpy(e->h_lapping, lapping, sizeof(int) * 2 * batch);
+        ORBX_CUDA(cudaMemcpyAsync(e->d_lapping, e->h_lapping, sizeof(int) * 2 * batch, cudaMemcpyHostToDevice, st));
+        d_lap = e->d_lapping;
+    }
+    const int lanes = e->profiling ? 1 : std::max(1, std::min(e->lanes, batch / 16));
+    if (lanes <= 1) {
+        const orbx_status r = enqueue_frames(e, d_images, frame_stride, row_stride, 0, batch, d_lap, st, e->side, e->ev_fork, e->ev_join, launches);
+        if (r != ORBX_OK) return r;
+    } else {
+        /* frames are independent: the batch runs as `lanes` chunks on as many streams, so one chunk's
+         * latency-bound stages (quadtree, barriers, tails) fill with another chunk's kernels and a
+         * chunk's pyramid is still in L2 when its later stages read it */
+        const int chunk = orbx_div_up(batch, lanes);
+        ORBX_CUDA(cudaEventRecord(e->ev_fork, st));
+        for (int g = 0, f0 = 0; f0 < batch; ++g, f0 += chunk) {
+            ORBX_CUDA(cudaStreamWaitEvent(e->lane[g], e->ev_fork, 0));
+            const orbx_status r = enqueue_frames(e, d_images, frame_stride, row_stride, f0, std::min(chunk, batch - f0), d_lap, e->lane[g],
+                                                 nullptr, nullptr, nullptr, launches);
+            if (r != ORBX_OK) return r;
+            ORBX_CUDA(cudaEventRecord(e->ev_lane[g], e->lane[g]));
+            ORBX_CUDA(cudaStreamWaitEvent(st, e->ev_lane[g], 0));
+        }
+    }
     ORBX_CUDA(cudaGetLastError());
     e->last_batch = batch;
     e->last_launches = launches;

@@ -38,8 +38,10 @@ struct Cell {
     unsigned rcp_dw;        /* floor(2^32/(cw-6))+1: exact i/(cw-6) by __umulhi for i < 2^16 */
 };
 
+#define ORBX_MAX_LANES 8
 struct Tables {
     int nlevels;
+    int f0;                 /* first frame of the launch: frame = blockIdx + f0 (a batch runs as chunks on several streams) */
     LevelDev lv[ORBX_MAX_LEVELS];
 };
 
@@ -79,6 +81,9 @@ struct orbx_extractor {
     cudaStream_t stream = nullptr;
     cudaStream_t side = nullptr;    /* the blur runs here beside FAST / quadtree / order (it needs the pyramid only) */
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    int lanes = 4;                  /* a batch of >= 32 frames runs as up to `lanes` chunks on as many streams (ORBX_LANES) */
+    cudaStream_t lane[ORBX_MAX_LANES] = {};
+    cudaEvent_t ev_lane[ORBX_MAX_LANES] = {};
     /* device buffers */
     uint8_t* d_pyr = nullptr;
     uint8_t* d_blur = nullptr;
