@@ -455,12 +455,12 @@ def main():
             stages[n] = {"ms": round(float(stage[i]), 4), "alg_bytes_per_frame": alg[n], "gbs": round(gbs, 1),
                          "frac_hbm": round(gbs / hbm_peak, 4)}
         dom_gbs = stages[names[dom]]["gbs"]
-        kern = {"pyramid": "k_resize_w4", "fast": "k_fast_units", "octree": "k_octree", "order": "k_order",
+        kern = {"pyramid": "k_resize_band", "fast": "k_fast_units", "octree": "k_octree", "order": "k_order",
                 "blur": "k_blur7", "describe": "k_orient_describe"}[names[dom]]
         traffic = None          # DRAM bytes per launch of the dominant kernel, from the committed ncu --set full capture
         try:
             tr = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))["kernels"][kern]
-            traffic = int(tr["dram_bytes"] / tr["launches"] * B / 256)
+            traffic = int(tr["dram_bytes"] * B / 256)    # every launch of the kernel in ONE step (the capture holds one step)
         except Exception:
             pass
         line = {
@@ -470,6 +470,7 @@ def main():
             "config": {"workload": WORKLOAD, "frames_per_step_per_gpu": B, "keypoints_per_frame": float(np.mean(n_kp)),
                        "l2_policy": "inputs larger than L2: 2 alternating 92 MB input batches + 360 MB pyramid working set per step",
                        "e2e_batches_in_flight": NH,
+                       "internal_streams": ex.streams(B),
                        "sharding": "independent frames per rank, no collective",
                        "numa": None if numa is None else {"node": numa[0], "cpus": numa[1]}},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(B * W * H),
@@ -480,6 +481,7 @@ def main():
             "roofline": {"bound": "hbm", "kernel": kern, "stage": names[dom], "achieved": dom_gbs, "peak": hbm_peak, "unit": "GB/s",
                          "frac": round(dom_gbs / hbm_peak, 4), "traffic": traffic,
                          "algorithmic_bytes_per_launch": int(alg[names[dom]] * B), "launch_ms": round(float(stage[dom]), 4),
+                         "launch_scope": "all launches of the stage for one 256-frame step on one stream (FAST: 2 grids, short and tall strips)",
                          "peak_source": "measured" if peaks else "fallback"},
             "stages": stages,
         }

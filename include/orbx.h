@@ -102,6 +102,9 @@ orbx_status orbx_extractor_candidates(orbx_extractor* e, int f, int level, int* 
 
 /* the stream all work of this handle is enqueued on (a cudaStream_t) */
 void* orbx_extractor_stream(orbx_extractor* e);
+/* internal streams a batch of `batch` frames is spread over (chunks of frames run concurrently;
+ * 1 for small batches and in profiling mode).  Everything is ordered with the handle's stream. */
+int orbx_extractor_streams(const orbx_extractor* e, int batch);
 /* number of kernel launches issued by the last orbx_extract_* call */
 int orbx_extractor_last_launches(const orbx_extractor* e);
 /* device time of each stage of the last extract (ms), measured with CUDA events when

@@ -1801,6 +1801,7 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
     }
     e->T.nlevels = nl;
     e->T.f0 = 0;
+    e->fast_cl_cap = FAST_CL;
     for (int l = 0; l < nl; ++l) e->T.lv[l] = e->lv[l];
     {
         /* TMA tensor maps for the describe stage: (row bytes, rows, frames) u8 views of every
@@ -1866,6 +1867,9 @@ extern "C" orbx_status orbx_extractor_tables(const orbx_extractor* e, float* sca
 
 extern "C" int orbx_extractor_capacity(const orbx_extractor* e) { return e ? e->kcap : 0; }
 extern "C" void* orbx_extractor_stream(orbx_extractor* e) { return e ? (void*)e->stream : nullptr; }
+extern "C" int orbx_extractor_streams(const orbx_extractor* e, int batch) {
+    return (!e || e->profiling) ? 1 : std::max(1, std::min(e->lanes, batch / 16));
+}
 extern "C" int orbx_extractor_last_launches(const orbx_extractor* e) { return e ? e->last_launches : 0; }
 extern "C" orbx_status orbx_extractor_set_fast_corner_list(orbx_extractor* e, int entries) {
     if (!e || entries < 1 || entries > FAST_CL) { orbx_set_error("corner list capacity outside [1,%d]", FAST_CL); return ORBX_ERR_INVALID; }
@@ -1990,7 +1994,7 @@ extern "C" orbx_status orbx_extract_device(orbx_extractor* e, const uint8_t* d_i
         ORBX_CUDA(cudaMemcpyAsync(e->d_lapping, e->h_lapping, sizeof(int) * 2 * batch, cudaMemcpyHostToDevice, st));
         d_lap = e->d_lapping;
     }
-    const int lanes = e->profiling ? 1 : std::max(1, std::min(e->lanes, batch / 16));
+    const int lanes = orbx_extractor_streams(e, batch);
     if (lanes <= 1) {
         const orbx_status r = enqueue_frames(e, d_images, frame_stride, row_stride, 0, batch, d_lap, st, e->side, e->ev_fork, e->ev_join, launches);
         if (r != ORBX_OK) return r;

@@ -62,6 +62,7 @@ def lib():
         L.orbx_extractor_blurred_download.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
         L.orbx_extractor_candidates.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         L.orbx_extractor_last_launches.argtypes = [C.c_void_p]
+        L.orbx_extractor_streams.argtypes = [C.c_void_p, C.c_int]
         L.orbx_extractor_set_profiling.argtypes = [C.c_void_p, C.c_int]
         L.orbx_extractor_set_fast_corner_list.argtypes = [C.c_void_p, C.c_int]
         L.orbx_extractor_assign_grid.argtypes = [C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, C.c_int]
@@ -267,6 +268,10 @@ class ORBextractor:
 
     def last_launches(self):
         return lib().orbx_extractor_last_launches(self._h)
+
+    def streams(self, batch):
+        """internal streams a batch of this size is spread over"""
+        return lib().orbx_extractor_streams(self._h, int(batch))
 
     def set_profiling(self, on=True):
         _ck(lib().orbx_extractor_set_profiling(self._h, int(on)))

@@ -1,7 +1,7 @@
 #!/usr/bin/env python3
 """Minimal driver for ncu: N extraction steps of the bench workload (EuRoC shape, batch B) with
-device-resident input, nothing else.  Each step = 13 kernel launches (8 pyramid, FAST, quadtree,
-order, blur, orient+describe); add --stereo for the two stereo launches per step and --knn for a
+device-resident input, nothing else.  With ORBX_LANES=1 each step = 14 kernel launches (8 pyramid,
+2 FAST grids, quadtree, order, blur, orient+describe; by default the batch runs as 4 chunks = 56); add --stereo for the two stereo launches per step and --knn for a
 2-NN launch.  Usage under ncu: skip the first (steps-1)*launches_per_step launches."""
 import argparse
 import os
