@@ -133,6 +133,12 @@ def single_frame_latency(pkg, local, frame):
             "note": "batch 1 through the C ABI with host buffers; 13 kernel launches + H2D + D2H + sync per call"}
 
 
+def _dbg(torch, tag):
+    if os.environ.get("ORBX_BENCH_DEBUG_SYNC"):
+        torch.cuda.synchronize()
+        print("[phase ok]", tag, file=sys.stderr, flush=True)
+
+
 def matching_bench(pkg, torch, local, ex, B):
     """Secondary numbers of BASELINE.json's metric ("Hamming matches/sec"): device-timed stereo
     row search on the extractor's resident output, batched projection search through the C ABI
@@ -145,10 +151,16 @@ def matching_bench(pkg, torch, local, ex, B):
     st = torch.cuda.ExternalStream(ex.stream(), device=dev)
     sp = [pkg.synth.stereo_pair(W, H, 0xB200 + i) for i in range(4)]
     sbase = np.stack([im for pr in sp for im in pr])
-    ex.extract_host(np.stack([sbase[i % 8] for i in range(B)])); ex.sync()
+    _dbg(torch, "before matching")
+    spin = ox.PinnedBuffer((B, H, W))          # pinned staging, alive until the function returns
+    for i in range(B):
+        spin.array[i] = sbase[i % 8]
+    ex.extract_host(spin.array); ex.sync()
+    _dbg(torch, "matching: extraction")
     lf = np.arange(0, B, 2); rf = lf + 1
     for _ in range(2):
         ox.stereo_matches_async(ex, ex, lf, rf, 435.2 * 0.11, 0.11)
+        _dbg(torch, "matching: stereo warm-up call")
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     reps = 10
     e0.record(st)

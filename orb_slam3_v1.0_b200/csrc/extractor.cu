@@ -1990,8 +1990,9 @@ extern "C" orbx_status orbx_extract_device(orbx_extractor* e, const uint8_t* d_i
     int launches = 0;
     const int* d_lap = nullptr;
     if (lapping) {
-        memcpy(e->h_lapping, lapping, sizeof(int) * 2 * batch);
-        ORBX_CUDA(cudaMemcpyAsync(e->d_lapping, e->h_lapping, sizeof(int) * 2 * batch, cudaMemcpyHostToDevice, st));
+        /* pageable staging: copied by the runtime before the call returns (back-to-back asynchronous calls) */
+        std::vector<int> hl(lapping, lapping + 2 * (size_t)batch);
+        ORBX_CUDA(cudaMemcpyAsync(e->d_lapping, hl.data(), sizeof(int) * 2 * batch, cudaMemcpyHostToDevice, st));
         d_lap = e->d_lapping;
     }
     const int lanes = orbx_extractor_streams(e, batch);

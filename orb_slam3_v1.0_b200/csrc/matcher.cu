@@ -487,7 +487,7 @@ static orbx_status run_sbp(orbx_matcher* m, int nprob, const orbx_frame_view* F,
     if (st != ORBX_OK) return st;
     in.copy_to(m->h_in);
     ORBX_CUDA(cudaMemcpyAsync(m->d_in, m->h_in, in.total, cudaMemcpyHostToDevice, m->stream));
-    ORBX_CUDA(cudaFuncSetAttribute(k_search_by_projection, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max(smem, (size_t)48 * 1024)));
+    ORBX_ENSURE_SMEM(k_search_by_projection, smem);
     k_search_by_projection<<<nprob, MT, smem, m->stream>>>(m->d_in, m->d_out, reinterpret_cast<const SbpProb*>(m->d_in + probs_off),
                                                            reinterpret_cast<int*>(m->d_out + counts_off));
     ORBX_CUDA(cudaGetLastError());
@@ -692,7 +692,7 @@ extern "C" orbx_status orbx_search_for_triangulation(orbx_matcher* m, int nprob,
     if (st != ORBX_OK) return st;
     in.copy_to(m->h_in);
     ORBX_CUDA(cudaMemcpyAsync(m->d_in, m->h_in, in.total, cudaMemcpyHostToDevice, m->stream));
-    ORBX_CUDA(cudaFuncSetAttribute(k_search_for_triangulation, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max(smem, (size_t)48 * 1024)));
+    ORBX_ENSURE_SMEM(k_search_for_triangulation, smem);
     k_search_for_triangulation<<<nprob, MT, smem, m->stream>>>(m->d_in, m->d_out, reinterpret_cast<const TriProb*>(m->d_in + probs_off),
                                                                reinterpret_cast<int*>(m->d_out + counts_off));
     ORBX_CUDA(cudaGetLastError());
@@ -1102,7 +1102,7 @@ extern "C" orbx_status orbx_assign_features_to_grid(orbx_matcher* m, int nframes
     in.copy_to(m->h_in);
     memcpy(m->h_in + probs_off, probs.data(), sizeof(GridProb) * (size_t)nframes);
     ORBX_CUDA(cudaMemcpyAsync(m->d_in, m->h_in, in.total, cudaMemcpyHostToDevice, m->stream));
-    ORBX_CUDA(cudaFuncSetAttribute(k_assign_grid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max(smem, (size_t)48 * 1024)));
+    ORBX_ENSURE_SMEM(k_assign_grid, smem);
     k_assign_grid<<<nframes, MT, smem, m->stream>>>(reinterpret_cast<const GridProb*>(m->d_in + probs_off));
     ORBX_CUDA(cudaGetLastError());
     m->last_launches = 1;
@@ -1146,7 +1146,7 @@ extern "C" orbx_status orbx_features_in_area(orbx_matcher* m, const orbx_frame_v
     memcpy(m->h_in + gp, &G, sizeof(G));
     ORBX_CUDA(cudaMemcpyAsync(m->d_in, m->h_in, in.total, cudaMemcpyHostToDevice, m->stream));
     const size_t smem = 4 * (2 * ncell + 1);
-    ORBX_CUDA(cudaFuncSetAttribute(k_assign_grid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max(smem, (size_t)48 * 1024)));
+    ORBX_ENSURE_SMEM(k_assign_grid, smem);
     k_assign_grid<<<1, MT, smem, m->stream>>>(reinterpret_cast<const GridProb*>(m->d_in + gp));
     AreaProb A;
     memset(&A, 0, sizeof(A));
@@ -1190,7 +1190,11 @@ extern "C" orbx_status orbx_extractor_assign_grid(orbx_extractor* e, float minx,
         ORBX_CUDA(cudaMallocHost(&e->h_grid_probs, sizeof(GridProb) * (size_t)B));
     }
     e->grid_cells = ncell;
-    GridProb* hp = static_cast<GridProb*>(e->h_grid_probs);
+    /* staged from PAGEABLE memory (copied by the runtime before the call returns): this entry point is
+     * asynchronous, so a pinned staging buffer would be rewritten by the next call while the previous
+     * call's DMA may still be waiting in the stream */
+    std::vector<GridProb> hpv((size_t)e->last_batch);
+    GridProb* hp = hpv.data();
     for (int f = 0; f < e->last_batch; ++f) {
         GridProb& P = hp[f];
         memset(&P, 0, sizeof(P));
@@ -1203,7 +1207,7 @@ extern "C" orbx_status orbx_extractor_assign_grid(orbx_extractor* e, float minx,
     }
     ORBX_CUDA(cudaMemcpyAsync(e->d_grid_probs, hp, sizeof(GridProb) * (size_t)e->last_batch, cudaMemcpyHostToDevice, e->stream));
     const size_t smem = 4 * (2 * (size_t)ncell + 1);
-    ORBX_CUDA(cudaFuncSetAttribute(k_assign_grid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max(smem, (size_t)48 * 1024)));
+    ORBX_ENSURE_SMEM(k_assign_grid, smem);
     k_assign_grid<<<e->last_batch, MT, smem, e->stream>>>(static_cast<const GridProb*>(e->d_grid_probs));
     ORBX_CUDA(cudaGetLastError());
     return ORBX_OK;
@@ -1592,7 +1596,7 @@ static orbx_status run_fuse(orbx_matcher* m, int nprob, const orbx_frame_view* K
     if (st != ORBX_OK) return st;
     in.copy_to(m->h_in);
     ORBX_CUDA(cudaMemcpyAsync(m->d_in, m->h_in, in.total, cudaMemcpyHostToDevice, m->stream));
-    ORBX_CUDA(cudaFuncSetAttribute(k_fuse_search, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max(smem, (size_t)48 * 1024)));
+    ORBX_ENSURE_SMEM(k_fuse_search, smem);
     k_fuse_search<<<nprob, MT, smem, m->stream>>>(m->d_in, m->d_out, reinterpret_cast<const FuseProb*>(m->d_in + probs_off));
     ORBX_CUDA(cudaGetLastError());
     m->last_launches = 1;
@@ -1921,7 +1925,7 @@ extern "C" orbx_status orbx_search_for_initialization(orbx_matcher* m, int nprob
     if (st != ORBX_OK) return st;
     in.copy_to(m->h_in);
     ORBX_CUDA(cudaMemcpyAsync(m->d_in, m->h_in, in.total, cudaMemcpyHostToDevice, m->stream));
-    ORBX_CUDA(cudaFuncSetAttribute(k_search_for_initialization, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max(smem, (size_t)48 * 1024)));
+    ORBX_ENSURE_SMEM(k_search_for_initialization, smem);
     k_search_for_initialization<<<nprob, SFI_T, smem, m->stream>>>(m->d_in, m->d_out, reinterpret_cast<const InitProb*>(m->d_in + probs_off),
                                                                    reinterpret_cast<int*>(m->d_out + counts_off),
                                                                    reinterpret_cast<uint32_t*>(m->d_scratch));

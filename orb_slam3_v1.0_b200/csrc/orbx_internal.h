@@ -23,6 +23,23 @@ void orbx_set_error(const char* fmt, ...);
         }                                                                                 \
     } while (0)
 
+/* Opt a kernel in to `bytes` of dynamic shared memory.  The attribute is only touched when the
+ * need grows beyond what this process has already set for the current device (and never for
+ * <= 48 KB, the default limit): entry points that enqueue asynchronously are called back to back,
+ * and re-setting a function attribute while earlier launches of that function are still pending
+ * is needless driver work on the launch path. */
+#define ORBX_ENSURE_SMEM(kernel, bytes)                                                   \
+    do {                                                                                  \
+        static size_t _cur[64];                                                           \
+        int _dev = 0;                                                                     \
+        ORBX_CUDA(cudaGetDevice(&_dev));                                                  \
+        const size_t _need = (size_t)(bytes);                                             \
+        if (_need > 48 * 1024 && _need > _cur[_dev & 63]) {                               \
+            ORBX_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)_need)); \
+            _cur[_dev & 63] = _need;                                                      \
+        }                                                                                 \
+    } while (0)
+
 static inline int orbx_div_up(int a, int b) { return (a + b - 1) / b; }
 static inline size_t orbx_align_up(size_t a, size_t b) { return (a + b - 1) / b * b; }
 

@@ -34,6 +34,7 @@
 #include <algorithm>
 
 #include "orbx_internal.h"
+#include <stdio.h>
 #include "extractor_state.h"
 
 #define ST_THREADS 256
@@ -414,9 +415,14 @@ extern "C" orbx_status orbx_stereo_matches_async(orbx_extractor* left, orbx_extr
         ORBX_CUDA(cudaEventRecord(left->ev_stereo, right->stream));
         ORBX_CUDA(cudaStreamWaitEvent(st, left->ev_stereo, 0));
     }
-    memcpy(left->h_pairs, left_frames, sizeof(int) * npairs);
-    memcpy(left->h_pairs + B, right_frames, sizeof(int) * npairs);
-    ORBX_CUDA(cudaMemcpyAsync(left->d_pairs, left->h_pairs, sizeof(int) * 2 * B, cudaMemcpyHostToDevice, st));
+    {
+        /* staged from PAGEABLE memory: the runtime copies a pageable source before the call returns, so
+         * the next (asynchronous, back-to-back) call cannot overwrite a source still waiting for its DMA */
+        std::vector<int> hp((size_t)2 * B, 0);
+        memcpy(hp.data(), left_frames, sizeof(int) * npairs);
+        memcpy(hp.data() + B, right_frames, sizeof(int) * npairs);
+        ORBX_CUDA(cudaMemcpyAsync(left->d_pairs, hp.data(), sizeof(int) * 2 * B, cudaMemcpyHostToDevice, st));
+    }
     StereoSide SL, SR;
     StereoTables TB;
     memset(&SL, 0, sizeof(SL)); memset(&SR, 0, sizeof(SR)); memset(&TB, 0, sizeof(TB));
@@ -424,7 +430,7 @@ extern "C" orbx_status orbx_stereo_matches_async(orbx_extractor* left, orbx_extr
     for (int l = 0; l < left->nlevels; ++l) { TB.scale[l] = left->sf[l]; TB.inv_scale[l] = left->inv_sf[l]; }
     const size_t smem = 4 * ((size_t)2 * left->lv[0].h + 1) + 16;
     if (smem > 200 * 1024) { orbx_set_error("image too tall for the stereo row table"); return ORBX_ERR_INVALID; }
-    ORBX_CUDA(cudaFuncSetAttribute(k_stereo_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max(smem, (size_t)48 * 1024)));
+    ORBX_ENSURE_SMEM(k_stereo_rows, smem);
     k_stereo_rows<<<npairs, ST_RT, smem, st>>>(SL, SR, TB, left->d_pairs, B, reinterpret_cast<uint2*>(left->d_rowent), left->rowent_per_pair,
                                                     left->d_rowstart, left->d_uright, left->d_depth, left->d_sad);
     k_stereo_match<<<dim3(ST_SPLIT, npairs), ST_THREADS, 0, st>>>(SL, SR, TB, left->d_pairs, B, bf, b, reinterpret_cast<const uint2*>(left->d_rowent),

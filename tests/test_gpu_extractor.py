@@ -122,6 +122,37 @@ def test_many_frames_property(pkg, oracle, synth):
     gex.close()
 
 
+def test_chunked_batch_streams(pkg, oracle, synth):
+    """A batch large enough to run as several chunks on the handle's internal streams: every frame
+    equals the single-stream result and (sampled) the oracle; the stereo search on the
+    device-resident output of such a batch equals the one on a single-stream batch."""
+    w, h, B = 640, 400, 72
+    sp = [synth.stereo_pair(w, h, 0xB200 + 77 + i) for i in range(4)]           # frames (2p, 2p+1) = a rectified pair
+    base = [im for pr in sp for im in pr]
+    imgs = np.stack([np.roll(base[i % 8], 5 * (i // 8), axis=1) for i in range(B)])
+    gex = pkg.orbx.ORBextractor(800, 1.2, 8, 20, 7, max_batch=B)
+    assert gex.prepare(w, h, B).streams(B) == 4 and gex.streams(8) == 1
+    lap = np.tile(np.array([[100, 300]], np.int32), (B, 1))
+    r = gex.extract_batch(imgs, lap)
+    lf = np.arange(0, B, 2); rf = lf + 1
+    pkg.orbx.stereo_matches_async(gex, gex, lf, rf, 40.0, 0.1)
+    ur, dp = pkg.orbx.stereo_fetch(gex, len(lf))
+    one = pkg.orbx.ORBextractor(800, 1.2, 8, 20, 7, max_batch=8)
+    oex = oracle.Extractor(800, 1.2, 8, 20, 7)
+    for f0 in range(0, B, 8):
+        q = one.extract_batch(imgs[f0:f0 + 8], lap[f0:f0 + 8])
+        for k in range(8):
+            assert np.array_equal(r[f0 + k][0], q[k][0]) and np.array_equal(r[f0 + k][1], q[k][1]) and r[f0 + k][2] == q[k][2], f0 + k
+        pkg.orbx.stereo_matches_async(one, one, np.arange(0, 8, 2), np.arange(1, 8, 2), 40.0, 0.1)
+        ur1, dp1 = pkg.orbx.stereo_fetch(one, 4)
+        for k in range(4):
+            n = len(q[2 * k][0])
+            assert np.array_equal(ur[f0 // 2 + k][:n], ur1[k][:n]) and np.array_equal(dp[f0 // 2 + k][:n], dp1[k][:n])
+    for f in (0, 17, 35, 54, 71):
+        _compare_frame(gex, oex, imgs[f], (100, 300), got=r[f])
+    gex.close(); one.close()
+
+
 def test_hamming_pairs(pkg, oracle):
     rng = np.random.default_rng(5)
     a = rng.integers(0, 256, size=(5000, 32), dtype=np.uint8)

@@ -258,6 +258,47 @@ def test_extractor_device_grid(pkg, matcher, oracle, synth):
     ex.close()
 
 
+def test_async_entry_points_back_to_back(pkg, synth):
+    """The asynchronous entry points (stereo_matches_async, assign_grid, extract with a lapping
+    table) stage their small host tables so that a burst of calls with CHANGING arguments, issued
+    without any synchronisation in between, leaves exactly the result of the last call (a staging
+    buffer rewritten while an earlier call's copy is still queued would tear them)."""
+    ox = pkg.orbx
+    W, H, B = 640, 400, 32
+    sp = [synth.stereo_pair(W, H, 300 + i) for i in range(4)]
+    base = [im for pr in sp for im in pr]
+    imgs = np.stack([base[i % 8] for i in range(B)])
+    ex = ox.ORBextractor(800, 1.2, 8, 20, 7, max_batch=B).prepare(W, H, B)
+    lapA = np.tile(np.array([[0, 0]], np.int32), (B, 1)); lapB = np.tile(np.array([[200, 400]], np.int32), (B, 1))
+    for k in range(12):                                   # extraction burst, alternating lapping tables
+        ex.extract_host(imgs, lapB if k % 2 else lapA)
+    ex.sync()
+    got = [ex.fetch(f) for f in range(B)]
+    ref = ex.extract_batch(imgs, lapB)
+    for f in range(B):
+        assert np.array_equal(got[f][0], ref[f][0]) and np.array_equal(got[f][1], ref[f][1]) and got[f][2] == ref[f][2]
+    lf = np.arange(0, B, 2); rf = lf + 1
+    for k in range(40):                                   # stereo burst: the pair list changes every call
+        sel = np.roll(np.arange(len(lf)), k)
+        ox.stereo_matches_async(ex, ex, lf[sel], rf[sel], 40.0, 0.1)
+    ur, dp = ox.stereo_fetch(ex, len(lf))
+    sel = np.roll(np.arange(len(lf)), 39)
+    ur1, dp1 = ox.stereo_matches(ex, ex, lf[sel], rf[sel], 40.0, 0.1)
+    assert np.array_equal(ur, ur1) and np.array_equal(dp, dp1) and (ur >= 0).sum() > 100
+    gcols, grows = 64, 48
+    gw, gh = float(np.float32(gcols) / np.float32(W)), float(np.float32(grows) / np.float32(H))
+    for k in range(40):                                   # grid burst: origin and cell size change every call
+        ex.assign_grid(float(k % 3), float(k % 2), gw * (1 + 0.01 * (k % 5)), gh, gcols, grows)
+    ex.sync()
+    burst = [ex.grid_fetch(f, len(ref[f][0])) for f in range(B)]
+    ex.assign_grid(float(39 % 3), float(39 % 2), gw * (1 + 0.01 * (39 % 5)), gh, gcols, grows)
+    ex.sync()
+    for f in range(B):
+        off, idx = ex.grid_fetch(f, len(ref[f][0]))
+        assert np.array_equal(off, burst[f][0]) and np.array_equal(idx, burst[f][1])
+    ex.close()
+
+
 # ------------------------------------------------------------------ distinctive descriptors (SURVEY 8(f) n3)
 def test_distinctive_descriptors(matcher, oracle, synth):
     rng = np.random.default_rng(91)
