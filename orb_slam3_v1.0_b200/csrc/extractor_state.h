@@ -81,7 +81,7 @@ struct orbx_extractor {
     cudaStream_t stream = nullptr;
     cudaStream_t side = nullptr;    /* the blur runs here beside FAST / quadtree / order (it needs the pyramid only) */
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
-    int lanes = 4;                  /* a batch of >= 32 frames runs as up to `lanes` chunks on as many streams (ORBX_LANES) */
+    int lanes = 2;                  /* a batch of >= 32 frames runs as up to `lanes` chunks on as many streams (ORBX_LANES); 2 and 4 give the same device-resident rate, 2 the better end-to-end rate */
     cudaStream_t lane[ORBX_MAX_LANES] = {};
     cudaEvent_t ev_lane[ORBX_MAX_LANES] = {};
     /* device buffers */

@@ -122,16 +122,20 @@ def test_many_frames_property(pkg, oracle, synth):
     gex.close()
 
 
-def test_chunked_batch_streams(pkg, oracle, synth):
-    """A batch large enough to run as several chunks on the handle's internal streams: every frame
+@pytest.mark.parametrize("lanes", [None, "4"])
+def test_chunked_batch_streams(pkg, oracle, synth, monkeypatch, lanes):
+    """A batch large enough to run as two chunks on the handle's internal streams: every frame
     equals the single-stream result and (sampled) the oracle; the stereo search on the
     device-resident output of such a batch equals the one on a single-stream batch."""
     w, h, B = 640, 400, 72
     sp = [synth.stereo_pair(w, h, 0xB200 + 77 + i) for i in range(4)]           # frames (2p, 2p+1) = a rectified pair
     base = [im for pr in sp for im in pr]
     imgs = np.stack([np.roll(base[i % 8], 5 * (i // 8), axis=1) for i in range(B)])
+    if lanes:
+        monkeypatch.setenv("ORBX_LANES", lanes)      # read when the handle is created
     gex = pkg.orbx.ORBextractor(800, 1.2, 8, 20, 7, max_batch=B)
-    assert gex.prepare(w, h, B).streams(B) == 4 and gex.streams(8) == 1
+    assert gex.prepare(w, h, B).streams(B) == int(lanes or 2) and gex.streams(8) == 1
+    monkeypatch.delenv("ORBX_LANES", raising=False)
     lap = np.tile(np.array([[100, 300]], np.int32), (B, 1))
     r = gex.extract_batch(imgs, lap)
     lf = np.arange(0, B, 2); rf = lf + 1
