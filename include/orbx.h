@@ -111,7 +111,7 @@ int orbx_extractor_last_launches(const orbx_extractor* e);
  * profiling was enabled with orbx_extractor_set_profiling(e, 1). stages: 0 pyramid,
  * 1 fast, 2 octree, 3 order, 4 blur, 5 orient+describe.  */
 orbx_status orbx_extractor_set_profiling(orbx_extractor* e, int on);
-/* Tuning / test knob: capacity (entries, 1..1024, default 1024) of the per-region corner list the
+/* Tuning / test knob: capacity (entries, 1..1024, default 1024 = all of it) of the per-region corner list the
  * FAST kernel keeps for its non-maximum-suppression pass; regions with more corners take the
  * score-map scan path.  Results do not depend on it. */
 orbx_status orbx_extractor_set_fast_corner_list(orbx_extractor* e, int entries);
