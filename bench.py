@@ -373,7 +373,8 @@ def main():
     # per step exceed the 126 MB L2, so no step finds its input in cache
     frames = make_frames(B, seed=0xB200 + 1000 * rank)
     NH = int(os.environ.get("ORBX_BENCH_NH", "3"))                                     # batches in flight on the end-to-end path
-    pin = [orbx.PinnedBuffer((B, H, W)) for _ in range(NH)]
+    WC = os.environ.get("ORBX_BENCH_WC", "0") == "1"                       # write-combined staging (A/B knob)
+    pin = [orbx.PinnedBuffer((B, H, W), write_combined=WC) for _ in range(NH)]
     for k in range(NH):
         pin[k].array[:] = np.roll(frames, k, axis=0)
     dev = [torch.from_numpy(p.array).to(f"cuda:{local}") for p in pin[:2]]

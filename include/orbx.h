@@ -119,6 +119,9 @@ orbx_status orbx_extractor_stage_ms(orbx_extractor* e, float* ms6);
 
 /* pinned host memory helpers for callers without a CUDA runtime of their own */
 orbx_status orbx_host_alloc(void** p, size_t bytes);
+/* page-locked, write-combined: for staging buffers the host only WRITES (the image grabber's frame
+ * queue); CPU reads of such memory are slow */
+orbx_status orbx_host_alloc_wc(void** p, size_t bytes);
 void orbx_host_free(void* p);
 orbx_status orbx_device_alloc(int device, void** p, size_t bytes);
 void orbx_device_free(void* p);

@@ -1624,6 +1624,11 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
     if (e->oct_smem > 220 * 1024) { orbx_set_error("nfeatures too large for the shared-memory quadtree (%zu B)", e->oct_smem); free_all(e); return ORBX_ERR_INVALID; }
 
 #define CK(call) do { cudaError_t _e = (call); if (_e != cudaSuccess) { orbx_set_error("%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(_e)); free_all(e); return ORBX_ERR_CUDA; } } while (0)
+/* dynamic shared-memory opt-in that only ever grows per (kernel, device): a handle created later with
+ * a smaller need must not lower the limit under an older handle */
+#define CK_SMEM(kernel, bytes) do { size_t& _cur = orbx_smem_slot(reinterpret_cast<const void*>(kernel), e->P.device); \
+    const size_t _need = (size_t)(bytes); \
+    if (_need > 48 * 1024 && _need > _cur) { CK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)_need)); _cur = _need; } } while (0)
     CK(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
     CK(cudaStreamCreateWithFlags(&e->side, cudaStreamNonBlocking));
     CK(cudaEventCreateWithFlags(&e->ev_fork, cudaEventDisableTiming));
@@ -1635,7 +1640,7 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
         CK(cudaEventCreateWithFlags(&e->ev_lane[g], cudaEventDisableTiming));
     }
     for (int i = 0; i < 7; ++i) CK(cudaEventCreate(&e->ev[i]));
-    CK(cudaFuncSetAttribute(k_octree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)e->oct_smem));
+    CK_SMEM(k_octree, e->oct_smem);
     {
         /* rBRIEF test pairs, transposed so that a warp's j-th load is one contiguous 512-byte row */
         std::vector<float> pt(1024);
@@ -1645,7 +1650,7 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
         uint32_t d4[32] = {0};
         for (int r = 0; r < 31; ++r) d4[r] = (uint32_t)e->umax[r < 15 ? 15 - r : r - 15] * 0x01010101u + 0x80808080u;
         CK(cudaMemcpyToSymbol(c_d4, d4, sizeof(d4)));
-        CK(cudaFuncSetAttribute(k_orient_describe, cudaFuncAttributeMaxDynamicSharedMemorySize, OD_SMEM));
+        CK_SMEM(k_orient_describe, OD_SMEM);
     }
     CK(cudaMalloc(&e->d_pyr, pyr_bytes));
     CK(cudaMalloc(&e->d_blur, blur_bytes + 256));    /* + slack: window staging reads whole words */
@@ -1678,8 +1683,7 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
     if ((size_t)e->fast_rows * e->fast_tp > 32767) { orbx_set_error("FAST strip %dx%d exceeds the 15-bit tile index", e->fast_tp, e->fast_rows); free_all(e); return ORBX_ERR_INVALID; }
     CK(cudaMalloc(&e->d_units, std::max<size_t>(units.size(), 1) * sizeof(Unit)));
     if (!units.empty()) CK(cudaMemcpy(e->d_units, units.data(), units.size() * sizeof(Unit), cudaMemcpyHostToDevice));
-    CK(cudaFuncSetAttribute(k_fast_units, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                            (int)std::max<size_t>((size_t)2 * e->fast_rows * e->fast_tp + FAST_QBYTES + 128, 48 * 1024)));
+    CK_SMEM(k_fast_units, (size_t)2 * e->fast_rows * e->fast_tp + FAST_QBYTES + 128);
     CK(cudaMalloc(&e->d_blur_tiles, blur_tiles.size() * sizeof(int4)));
     CK(cudaMalloc(&e->d_slots, std::max<size_t>(e->slots_per_frame, 1) * B * 4));
     CK(cudaMalloc(&e->d_cell_count, (size_t)std::max(e->ncells, 1) * B * 4));
@@ -1789,8 +1793,7 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
                 if (L.fast_resize && L.band_smem > 48 * 1024) max_band_smem = std::max(max_band_smem, L.band_smem);
             }
             CK(cudaMemcpyAsync(e->d_wtabs, wt.data(), wt.size(), cudaMemcpyHostToDevice, e->stream));
-            if (max_band_smem)
-                CK(cudaFuncSetAttribute(k_resize_band, cudaFuncAttributeMaxDynamicSharedMemorySize, max_band_smem));
+            CK_SMEM(k_resize_band, max_band_smem);
             CK(cudaStreamSynchronize(e->stream));
         }
         CK(cudaMemcpyAsync(e->d_tabs, tabs.data(), tabs.size() * sizeof(short4), cudaMemcpyHostToDevice, e->stream));
@@ -2126,6 +2129,7 @@ extern "C" orbx_status orbx_extractor_stage_ms(orbx_extractor* e, float* ms6) {
 
 /* ------------------------------------------------------------------ memory helpers */
 extern "C" orbx_status orbx_host_alloc(void** p, size_t bytes) { ORBX_CUDA(cudaMallocHost(p, bytes)); return ORBX_OK; }
+extern "C" orbx_status orbx_host_alloc_wc(void** p, size_t bytes) { ORBX_CUDA(cudaHostAlloc(p, bytes, cudaHostAllocWriteCombined)); return ORBX_OK; }
 extern "C" void orbx_host_free(void* p) { if (p) cudaFreeHost(p); }
 extern "C" orbx_status orbx_device_alloc(int device, void** p, size_t bytes) {
     ORBX_CUDA(cudaSetDevice(device));

@@ -3,7 +3,9 @@
 #define ORBX_INTERNAL_H
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <map>
 #include <string>
+#include <utility>
 #include <vector>
 #include "../../include/orbx.h"
 
@@ -28,15 +30,19 @@ void orbx_set_error(const char* fmt, ...);
  * <= 48 KB, the default limit): entry points that enqueue asynchronously are called back to back,
  * and re-setting a function attribute while earlier launches of that function are still pending
  * is needless driver work on the launch path. */
+inline size_t& orbx_smem_slot(const void* kernel, int device) {       /* largest size set so far, per (kernel, device) */
+    static std::map<std::pair<const void*, int>, size_t> m;
+    return m[std::make_pair(kernel, device)];
+}
 #define ORBX_ENSURE_SMEM(kernel, bytes)                                                   \
     do {                                                                                  \
-        static size_t _cur[64];                                                           \
         int _dev = 0;                                                                     \
         ORBX_CUDA(cudaGetDevice(&_dev));                                                  \
         const size_t _need = (size_t)(bytes);                                             \
-        if (_need > 48 * 1024 && _need > _cur[_dev & 63]) {                               \
+        size_t& _cur = orbx_smem_slot(reinterpret_cast<const void*>(kernel), _dev);       \
+        if (_need > 48 * 1024 && _need > _cur) {                                          \
             ORBX_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)_need)); \
-            _cur[_dev & 63] = _need;                                                      \
+            _cur = _need;                                                                 \
         }                                                                                 \
     } while (0)
 

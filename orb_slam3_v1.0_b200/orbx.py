@@ -76,6 +76,7 @@ def lib():
         L.orbx_features_in_area.argtypes = [C.c_void_p, C.c_void_p, C.c_int] + [C.c_void_p] * 7 + [C.c_int]
         L.orbx_extractor_stage_ms.argtypes = [C.c_void_p, C.c_void_p]
         L.orbx_host_alloc.argtypes = [C.POINTER(C.c_void_p), C.c_size_t]
+        L.orbx_host_alloc_wc.argtypes = [C.POINTER(C.c_void_p), C.c_size_t]
         L.orbx_host_free.argtypes = [C.c_void_p]
         L.orbx_device_alloc.argtypes = [C.c_int, C.POINTER(C.c_void_p), C.c_size_t]
         L.orbx_device_free.argtypes = [C.c_void_p]
@@ -121,10 +122,10 @@ def _p(a):
 class PinnedBuffer:
     """Page-locked host memory exposed as a numpy array."""
 
-    def __init__(self, shape, dtype=np.uint8):
+    def __init__(self, shape, dtype=np.uint8, write_combined=False):
         self.nbytes = int(np.prod(shape)) * np.dtype(dtype).itemsize
         self._ptr = C.c_void_p()
-        _ck(lib().orbx_host_alloc(C.byref(self._ptr), self.nbytes))
+        _ck((lib().orbx_host_alloc_wc if write_combined else lib().orbx_host_alloc)(C.byref(self._ptr), self.nbytes))
         buf = (C.c_uint8 * self.nbytes).from_address(self._ptr.value)
         self.array = np.frombuffer(buf, dtype=dtype).reshape(shape)
 

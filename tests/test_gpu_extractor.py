@@ -157,6 +157,20 @@ def test_chunked_batch_streams(pkg, oracle, synth, monkeypatch, lanes):
     gex.close(); one.close()
 
 
+def test_handles_of_different_size_coexist(pkg, oracle, synth):
+    """Shared-memory opt-ins are per kernel, not per handle: a small handle created after a large one
+    must not shrink the limit the large one launches with."""
+    img = synth.textured_image(1241, 376, 901)
+    big = pkg.orbx.ORBextractor(5000, 1.2, 8, 20, 7)
+    rb = big(img, (0, 0))
+    small = pkg.orbx.ORBextractor(200, 1.2, 4, 20, 7)
+    small(synth.textured_image(320, 240, 902), (0, 0))
+    rb2 = big(img, (0, 0))
+    assert np.array_equal(rb[0], rb2[0]) and np.array_equal(rb[1], rb2[1]) and len(rb[0]) > 4000
+    _compare_frame(big, oracle.Extractor(5000, 1.2, 8, 20, 7), img, (0, 0), got=rb2)
+    big.close(); small.close()
+
+
 def test_hamming_pairs(pkg, oracle):
     rng = np.random.default_rng(5)
     a = rng.integers(0, 256, size=(5000, 32), dtype=np.uint8)
