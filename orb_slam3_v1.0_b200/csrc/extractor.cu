@@ -1462,6 +1462,8 @@ static void free_all(orbx_extractor* e) {
     for (int g = 0; g < ORBX_MAX_LANES; ++g) { if (e->ev_lane[g]) cudaEventDestroy(e->ev_lane[g]); if (e->lane[g]) cudaStreamDestroy(e->lane[g]); }
     if (e->ev_fork) cudaEventDestroy(e->ev_fork);
     if (e->ev_join) cudaEventDestroy(e->ev_join);
+    if (e->ev_join2) cudaEventDestroy(e->ev_join2);
+    if (e->graph_exec) cudaGraphExecDestroy(e->graph_exec);
     if (e->side) cudaStreamDestroy(e->side);
     if (e->stream) cudaStreamDestroy(e->stream);
     delete e;
@@ -1633,8 +1635,10 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
     CK(cudaStreamCreateWithFlags(&e->side, cudaStreamNonBlocking));
     CK(cudaEventCreateWithFlags(&e->ev_fork, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&e->ev_join, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&e->ev_join2, cudaEventDisableTiming));
     if (const char* v = getenv("ORBX_FORK_BLUR")) e->fork_blur = atoi(v);
     if (const char* v = getenv("ORBX_LANES")) e->lanes = std::max(1, std::min(atoi(v), ORBX_MAX_LANES));
+    if (const char* v = getenv("ORBX_GRAPH")) e->use_graph = atoi(v) != 0;
     for (int g = 0; g < e->lanes && e->lanes > 1; ++g) {
         CK(cudaStreamCreateWithFlags(&e->lane[g], cudaStreamNonBlocking));
         CK(cudaEventCreateWithFlags(&e->ev_lane[g], cudaEventDisableTiming));
@@ -1877,6 +1881,7 @@ extern "C" int orbx_extractor_last_launches(const orbx_extractor* e) { return e 
 extern "C" orbx_status orbx_extractor_set_fast_corner_list(orbx_extractor* e, int entries) {
     if (!e || entries < 1 || entries > FAST_CL) { orbx_set_error("corner list capacity outside [1,%d]", FAST_CL); return ORBX_ERR_INVALID; }
     e->fast_cl_cap = entries;
+    if (e->graph_exec) { cudaGraphExecDestroy(e->graph_exec); e->graph_exec = nullptr; }   /* the captured launches hold the old value */
     return ORBX_OK;
 }
 
@@ -1926,7 +1931,12 @@ static orbx_status enqueue_frames(orbx_extractor* e, const uint8_t* d_images, si
     /* stage 4 needs the pyramid only: outside profiling mode it runs on the side stream beside the
      * quadtree and the ordering (latency-bound, most issue slots free); mode 1 forks it before
      * FAST instead */
-    const int fork_blur = (e->profiling || !side) ? 0 : e->fork_blur;
+    /* fork modes: 0 one stream; 1 blur beside FAST..order; 2 blur beside quadtree + order (throughput:
+     * the quadtree leaves issue slots free); 3 latency mode for small batches: the tall-strip FAST
+     * grid and then the blur run on the side stream beside the short-strip grid, so neither is on
+     * the critical path pyramid -> FAST -> quadtree -> order -> describe */
+    const int fork_blur = (e->profiling || !side) ? 0 : (e->fork_blur == 2 && nb <= 16 ? 3 : e->fork_blur);
+    const bool side_tall = fork_blur == 3 && e->ncells > 0 && e->nunits_short > 0;
     auto launch_side_blur = [&]() -> orbx_status {
         ORBX_CUDA(cudaEventRecord(ev_fork, st));
         ORBX_CUDA(cudaStreamWaitEvent(side, ev_fork, 0));
@@ -1935,6 +1945,20 @@ static orbx_status enqueue_frames(orbx_extractor* e, const uint8_t* d_images, si
         ++launches;
         return ORBX_OK;
     };
+    auto launch_fast_tall = [&](cudaStream_t sx) {
+        k_fast_units<<<dim3(e->nunits - e->nunits_short, nb), FAST_THREADS, (size_t)2 * e->fast_rows * e->fast_tp + FAST_QBYTES + 128, sx>>>(
+            T, static_cast<const Unit*>(e->d_units) + e->nunits_short, e->d_cells, e->ncells, e->P.ini_th_fast, e->P.min_th_fast, e->d_slots,
+            e->d_cand, e->slots_per_frame, e->d_cell_count, e->fast_tp, e->fast_rows, e->fast_cl_cap, (const ODMaps*)e->d_odmaps);
+        ++launches;
+    };
+    if (fork_blur == 3) {
+        ORBX_CUDA(cudaEventRecord(ev_fork, st));
+        ORBX_CUDA(cudaStreamWaitEvent(side, ev_fork, 0));
+        if (side_tall) { launch_fast_tall(side); ORBX_CUDA(cudaEventRecord(e->ev_join2, side)); }
+        k_blur7<<<dim3(orbx_div_up(e->nblur_tiles, 4), nb), 128, 0, side>>>(T, e->d_blur_tiles, e->nblur_tiles);
+        ORBX_CUDA(cudaEventRecord(ev_join, side));
+        ++launches;
+    }
     if (fork_blur == 1) { orbx_status r = launch_side_blur(); if (r != ORBX_OK) return r; }
     /* stage 1 */
     if (e->ncells > 0) {
@@ -1944,10 +1968,8 @@ static orbx_status enqueue_frames(orbx_extractor* e, const uint8_t* d_images, si
                 e->d_cand, e->slots_per_frame, e->d_cell_count, e->fast_tp, e->fast_rows_short, e->fast_cl_cap, (const ODMaps*)e->d_odmaps);
             ++launches;
         }
-        k_fast_units<<<dim3(e->nunits - e->nunits_short, nb), FAST_THREADS, (size_t)2 * e->fast_rows * e->fast_tp + FAST_QBYTES + 128, st>>>(
-            T, static_cast<const Unit*>(e->d_units) + e->nunits_short, e->d_cells, e->ncells, e->P.ini_th_fast, e->P.min_th_fast, e->d_slots,
-            e->d_cand, e->slots_per_frame, e->d_cell_count, e->fast_tp, e->fast_rows, e->fast_cl_cap, (const ODMaps*)e->d_odmaps);
-        ++launches;
+        if (side_tall) ORBX_CUDA(cudaStreamWaitEvent(st, e->ev_join2, 0));
+        else launch_fast_tall(st);
     }
     if (e->profiling) ORBX_CUDA(cudaEventRecord(e->ev[2], st));
     if (fork_blur == 2) { orbx_status r = launch_side_blur(); if (r != ORBX_OK) return r; }
@@ -1999,7 +2021,28 @@ extern "C" orbx_status orbx_extract_device(orbx_extractor* e, const uint8_t* d_i
         d_lap = e->d_lapping;
     }
     const int lanes = orbx_extractor_streams(e, batch);
-    if (lanes <= 1) {
+    if (lanes <= 1 && e->use_graph && !e->profiling) {
+        /* small batches are launch-latency bound (8 dependent pyramid launches, 14 in all): the chain is
+         * captured once per (input pointer, layout, batch, lapping) into a CUDA graph and replayed */
+        const bool same = e->graph_exec && e->g_img == d_images && e->g_fs == frame_stride && e->g_rs == row_stride &&
+                          e->g_batch == batch && e->g_lap == (d_lap != nullptr);
+        if (!same) {
+            if (e->graph_exec) { cudaGraphExecDestroy(e->graph_exec); e->graph_exec = nullptr; }
+            cudaGraph_t g = nullptr;
+            ORBX_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+            const orbx_status r = enqueue_frames(e, d_images, frame_stride, row_stride, 0, batch, d_lap, st, e->side, e->ev_fork, e->ev_join, launches);
+            const cudaError_t ce = cudaStreamEndCapture(st, &g);
+            if (r != ORBX_OK) { if (g) cudaGraphDestroy(g); return r; }
+            if (ce != cudaSuccess) { orbx_set_error("stream capture -> %s", cudaGetErrorString(ce)); return ORBX_ERR_CUDA; }
+            const cudaError_t ie = cudaGraphInstantiate(&e->graph_exec, g, 0);
+            cudaGraphDestroy(g);
+            if (ie != cudaSuccess) { e->graph_exec = nullptr; orbx_set_error("graph instantiate -> %s", cudaGetErrorString(ie)); return ORBX_ERR_CUDA; }
+            e->g_img = d_images; e->g_fs = frame_stride; e->g_rs = row_stride; e->g_batch = batch; e->g_lap = d_lap != nullptr;
+            e->g_launches = launches;
+        }
+        ORBX_CUDA(cudaGraphLaunch(e->graph_exec, st));
+        launches = e->g_launches;
+    } else if (lanes <= 1) {
         const orbx_status r = enqueue_frames(e, d_images, frame_stride, row_stride, 0, batch, d_lap, st, e->side, e->ev_fork, e->ev_join, launches);
         if (r != ORBX_OK) return r;
     } else {

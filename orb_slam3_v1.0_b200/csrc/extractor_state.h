@@ -80,7 +80,15 @@ struct orbx_extractor {
     void* d_odmaps = nullptr;       /* TMA tensor maps of the describe stage (extractor.cu: struct ODMaps) */
     cudaStream_t stream = nullptr;
     cudaStream_t side = nullptr;    /* the blur runs here beside FAST / quadtree / order (it needs the pyramid only) */
-    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_join2 = nullptr;
+    /* CUDA graph of the launch chain of a small batch (one stream + side stream), replayed while the
+     * input pointer / layout / batch / lapping stay the same (ORBX_GRAPH=0 disables) */
+    bool use_graph = true;
+    cudaGraphExec_t graph_exec = nullptr;
+    const uint8_t* g_img = nullptr;
+    size_t g_fs = 0;
+    int g_rs = 0, g_batch = 0, g_launches = 0;
+    bool g_lap = false;
     int lanes = 2;                  /* a batch of >= 32 frames runs as up to `lanes` chunks on as many streams (ORBX_LANES); 2 and 4 give the same device-resident rate, 2 the better end-to-end rate */
     cudaStream_t lane[ORBX_MAX_LANES] = {};
     cudaEvent_t ev_lane[ORBX_MAX_LANES] = {};
