@@ -745,7 +745,7 @@ __global__ void __launch_bounds__(OCT_THREADS) k_octree(Tables T, const Cell* __
     __shared__ int s_tmp[OCT_THREADS / 32 + 1];
     __shared__ int s_T, s_CT;
 
-    const int level = blockIdx.x, f = blockIdx.y + T.f0, tid = threadIdx.x;
+    const int level = blockIdx.x + T.l0, f = blockIdx.y + T.f0, tid = threadIdx.x;
     const LevelDev& Lv = T.lv[level];
     const int N = Lv.N;
 
@@ -1463,6 +1463,7 @@ static void free_all(orbx_extractor* e) {
     if (e->ev_fork) cudaEventDestroy(e->ev_fork);
     if (e->ev_join) cudaEventDestroy(e->ev_join);
     if (e->ev_join2) cudaEventDestroy(e->ev_join2);
+    for (int l = 0; l < ORBX_MAX_LEVELS; ++l) { if (e->ev_lvl[l]) cudaEventDestroy(e->ev_lvl[l]); if (e->ev_oct[l]) cudaEventDestroy(e->ev_oct[l]); if (e->branch[l]) cudaStreamDestroy(e->branch[l]); }
     if (e->graph_exec) cudaGraphExecDestroy(e->graph_exec);
     if (e->side) cudaStreamDestroy(e->side);
     if (e->stream) cudaStreamDestroy(e->stream);
@@ -1636,9 +1637,15 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
     CK(cudaEventCreateWithFlags(&e->ev_fork, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&e->ev_join, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&e->ev_join2, cudaEventDisableTiming));
+    for (int l = 0; l < p->nlevels && l < ORBX_MAX_LEVELS; ++l) {
+        CK(cudaStreamCreateWithFlags(&e->branch[l], cudaStreamNonBlocking));
+        CK(cudaEventCreateWithFlags(&e->ev_lvl[l], cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&e->ev_oct[l], cudaEventDisableTiming));
+    }
     if (const char* v = getenv("ORBX_FORK_BLUR")) e->fork_blur = atoi(v);
     if (const char* v = getenv("ORBX_LANES")) e->lanes = std::max(1, std::min(atoi(v), ORBX_MAX_LANES));
     if (const char* v = getenv("ORBX_GRAPH")) e->use_graph = atoi(v) != 0;
+    if (const char* v = getenv("ORBX_DATAFLOW")) e->dataflow = atoi(v) != 0;
     for (int g = 0; g < e->lanes && e->lanes > 1; ++g) {
         CK(cudaStreamCreateWithFlags(&e->lane[g], cudaStreamNonBlocking));
         CK(cudaEventCreateWithFlags(&e->ev_lane[g], cudaEventDisableTiming));
@@ -1682,6 +1689,12 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
             const double c = head / ctas(need_rows(units[i - 1])) + (total - head) / ctas(e->fast_rows);
             if (c < best * 0.97) { best = c; e->nunits_short = (int)i; e->fast_rows_short = need_rows(units[i - 1]); }
         }
+    }
+    for (int l = 0; l < ORBX_MAX_LEVELS; ++l) { e->unit_lo[l] = 0; e->unit_hi[l] = 0; }
+    for (size_t i = 0; i < units.size(); ++i) {             /* a level's units are contiguous: stable sort by a per-level key */
+        const int l = units[i].level;
+        if (e->unit_hi[l] == e->unit_lo[l]) e->unit_lo[l] = (int)i;
+        e->unit_hi[l] = (int)i + 1;
     }
     if (e->fast_tp > 256) { orbx_set_error("FAST strip width %d exceeds the 256-byte TMA box", e->fast_tp); free_all(e); return ORBX_ERR_INVALID; }
     if ((size_t)e->fast_rows * e->fast_tp > 32767) { orbx_set_error("FAST strip %dx%d exceeds the 15-bit tile index", e->fast_tp, e->fast_rows); free_all(e); return ORBX_ERR_INVALID; }
@@ -1808,6 +1821,7 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
     }
     e->T.nlevels = nl;
     e->T.f0 = 0;
+    e->T.l0 = 0;
     e->fast_cl_cap = FAST_CL;
     for (int l = 0; l < nl; ++l) e->T.lv[l] = e->lv[l];
     {
@@ -1894,10 +1908,35 @@ extern "C" orbx_status orbx_extractor_set_profiling(orbx_extractor* e, int on) {
 /* every stage of frames [f0, f0 + nb) on stream st; the blur may fork to `side` (nullptr: never) */
 static orbx_status enqueue_frames(orbx_extractor* e, const uint8_t* d_images, size_t frame_stride, int row_stride, int f0, int nb,
                                   const int* d_lap, cudaStream_t st, cudaStream_t side, cudaEvent_t ev_fork, cudaEvent_t ev_join,
-                                  int& launches) {
+                                  int& launches, bool dataflow = false) {
     const int nl = e->nlevels;
     Tables T = e->T;
     T.f0 = f0;
+    dataflow = dataflow && side && !e->profiling && e->ncells > 0;
+    /* latency path (small batches, captured into a graph): FAST + quadtree of level l run on branch
+     * stream l as soon as level l of the pyramid exists, instead of after the whole 8-launch chain */
+    auto level_branch = [&](int l) -> orbx_status {
+        cudaStream_t b = e->branch[l];
+        ORBX_CUDA(cudaEventRecord(e->ev_lvl[l], st));
+        ORBX_CUDA(cudaStreamWaitEvent(b, e->ev_lvl[l], 0));
+        const int n = e->unit_hi[l] - e->unit_lo[l];
+        if (n > 0) {
+            const int rows = e->unit_lo[l] < e->nunits_short ? e->fast_rows_short : e->fast_rows;
+            k_fast_units<<<dim3(n, nb), FAST_THREADS, (size_t)2 * rows * e->fast_tp + FAST_QBYTES + 128, b>>>(
+                T, static_cast<const Unit*>(e->d_units) + e->unit_lo[l], e->d_cells, e->ncells, e->P.ini_th_fast, e->P.min_th_fast, e->d_slots,
+                e->d_cand, e->slots_per_frame, e->d_cell_count, e->fast_tp, rows, e->fast_cl_cap, (const ODMaps*)e->d_odmaps);
+            ++launches;
+        }
+        Tables Tl = T;
+        Tl.l0 = l;
+        k_octree<<<dim3(1, nb), OCT_THREADS, e->oct_smem, b>>>(Tl, e->d_cells, e->ncells, e->d_slots, e->slots_per_frame,
+                                                               e->d_cell_count, e->d_cand, e->d_pnode, e->cand_per_frame,
+                                                               e->d_cand_count, e->d_sel, e->sel_per_frame, e->d_sel_count,
+                                                               e->maxn, e->max_cells_level, OCT_SCAND);
+        ++launches;
+        ORBX_CUDA(cudaEventRecord(e->ev_oct[l], b));
+        return ORBX_OK;
+    };
     if (e->profiling) ORBX_CUDA(cudaEventRecord(e->ev[0], st));
     /* stage 0 */
     {
@@ -1916,6 +1955,7 @@ static orbx_status enqueue_frames(orbx_extractor* e, const uint8_t* d_images, si
         S.rcp_nb = 0xFFFFFFFFu / (unsigned)std::max(S.nb, 1) + 1u;
         k_level0<<<dim3(orbx_div_up(L0.rows * (S.ni + S.nb), 256), nb), 256, 0, st>>>(d_images, frame_stride, row_stride, L0, S, vec_ok, f0);
         ++launches;
+        if (dataflow) { const orbx_status r = level_branch(0); if (r != ORBX_OK) return r; }
         for (int l = 1; l < nl; ++l) {
             const LevelDev& D = T.lv[l];
             const unsigned ch = D.pitch / 4;
@@ -1925,6 +1965,7 @@ static orbx_status enqueue_frames(orbx_extractor* e, const uint8_t* d_images, si
             else
                 k_resize<<<grid, 256, 0, st>>>(T.lv[l - 1], D, 0xFFFFFFFFu / ch + 1u, f0);
             ++launches;
+            if (dataflow) { const orbx_status r = level_branch(l); if (r != ORBX_OK) return r; }
         }
     }
     if (e->profiling) ORBX_CUDA(cudaEventRecord(e->ev[1], st));
@@ -1935,7 +1976,7 @@ static orbx_status enqueue_frames(orbx_extractor* e, const uint8_t* d_images, si
      * the quadtree leaves issue slots free); 3 latency mode for small batches: the tall-strip FAST
      * grid and then the blur run on the side stream beside the short-strip grid, so neither is on
      * the critical path pyramid -> FAST -> quadtree -> order -> describe */
-    const int fork_blur = (e->profiling || !side) ? 0 : (e->fork_blur == 2 && nb <= 16 ? 3 : e->fork_blur);
+    const int fork_blur = (e->profiling || !side) ? 0 : dataflow ? 1 : (e->fork_blur == 2 && nb <= 16 ? 3 : e->fork_blur);
     const bool side_tall = fork_blur == 3 && e->ncells > 0 && e->nunits_short > 0;
     auto launch_side_blur = [&]() -> orbx_status {
         ORBX_CUDA(cudaEventRecord(ev_fork, st));
@@ -1961,7 +2002,7 @@ static orbx_status enqueue_frames(orbx_extractor* e, const uint8_t* d_images, si
     }
     if (fork_blur == 1) { orbx_status r = launch_side_blur(); if (r != ORBX_OK) return r; }
     /* stage 1 */
-    if (e->ncells > 0) {
+    if (e->ncells > 0 && !dataflow) {
         if (e->nunits_short > 0) {
             k_fast_units<<<dim3(e->nunits_short, nb), FAST_THREADS, (size_t)2 * e->fast_rows_short * e->fast_tp + FAST_QBYTES + 128, st>>>(
                 T, static_cast<const Unit*>(e->d_units), e->d_cells, e->ncells, e->P.ini_th_fast, e->P.min_th_fast, e->d_slots,
@@ -1974,11 +2015,15 @@ static orbx_status enqueue_frames(orbx_extractor* e, const uint8_t* d_images, si
     if (e->profiling) ORBX_CUDA(cudaEventRecord(e->ev[2], st));
     if (fork_blur == 2) { orbx_status r = launch_side_blur(); if (r != ORBX_OK) return r; }
     /* stage 2 */
-    k_octree<<<dim3(nl, nb), OCT_THREADS, e->oct_smem, st>>>(T, e->d_cells, e->ncells, e->d_slots, e->slots_per_frame,
+    if (dataflow) {
+        for (int l = 0; l < nl; ++l) ORBX_CUDA(cudaStreamWaitEvent(st, e->ev_oct[l], 0));
+    } else {
+        k_octree<<<dim3(nl, nb), OCT_THREADS, e->oct_smem, st>>>(T, e->d_cells, e->ncells, e->d_slots, e->slots_per_frame,
                                                                  e->d_cell_count, e->d_cand, e->d_pnode, e->cand_per_frame,
                                                                  e->d_cand_count, e->d_sel, e->sel_per_frame, e->d_sel_count,
                                                                  e->maxn, e->max_cells_level, OCT_SCAND);
-    ++launches;
+        ++launches;
+    }
     if (e->profiling) ORBX_CUDA(cudaEventRecord(e->ev[3], st));
     /* stage 3 */
     k_order<<<nb, ORD_THREADS, 0, st>>>(T, e->d_sel, e->sel_per_frame, e->d_sel_count, d_lap, e->d_dest, e->d_nk,
@@ -2030,7 +2075,8 @@ extern "C" orbx_status orbx_extract_device(orbx_extractor* e, const uint8_t* d_i
             if (e->graph_exec) { cudaGraphExecDestroy(e->graph_exec); e->graph_exec = nullptr; }
             cudaGraph_t g = nullptr;
             ORBX_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
-            const orbx_status r = enqueue_frames(e, d_images, frame_stride, row_stride, 0, batch, d_lap, st, e->side, e->ev_fork, e->ev_join, launches);
+            const orbx_status r = enqueue_frames(e, d_images, frame_stride, row_stride, 0, batch, d_lap, st, e->side, e->ev_fork, e->ev_join, launches,
+                                                 e->dataflow);
             const cudaError_t ce = cudaStreamEndCapture(st, &g);
             if (r != ORBX_OK) { if (g) cudaGraphDestroy(g); return r; }
             if (ce != cudaSuccess) { orbx_set_error("stream capture -> %s", cudaGetErrorString(ce)); return ORBX_ERR_CUDA; }

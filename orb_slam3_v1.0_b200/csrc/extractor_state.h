@@ -41,6 +41,7 @@ struct Cell {
 #define ORBX_MAX_LANES 8
 struct Tables {
     int nlevels;
+    int l0;                 /* first level of a quadtree launch: level = blockIdx.x + l0 (per-level launches of the latency path) */
     int f0;                 /* first frame of the launch: frame = blockIdx + f0 (a batch runs as chunks on several streams) */
     LevelDev lv[ORBX_MAX_LEVELS];
 };
@@ -84,6 +85,12 @@ struct orbx_extractor {
     /* CUDA graph of the launch chain of a small batch (one stream + side stream), replayed while the
      * input pointer / layout / batch / lapping stay the same (ORBX_GRAPH=0 disables) */
     bool use_graph = true;
+    bool dataflow = true;           /* per-level branches inside the graph (ORBX_DATAFLOW=0: one chain + side stream) */
+    /* per-level dataflow of the latency path: branch stream l runs FAST + quadtree of level l as soon as
+     * level l of the pyramid exists */
+    cudaStream_t branch[ORBX_MAX_LEVELS] = {};
+    cudaEvent_t ev_lvl[ORBX_MAX_LEVELS] = {}, ev_oct[ORBX_MAX_LEVELS] = {};
+    int unit_lo[ORBX_MAX_LEVELS] = {}, unit_hi[ORBX_MAX_LEVELS] = {};   /* FAST units of a level (contiguous after the sort) */
     cudaGraphExec_t graph_exec = nullptr;
     const uint8_t* g_img = nullptr;
     size_t g_fs = 0;
