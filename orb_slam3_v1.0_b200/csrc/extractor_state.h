@@ -96,6 +96,10 @@ struct orbx_extractor {
     size_t g_fs = 0;
     int g_rs = 0, g_batch = 0, g_launches = 0;
     bool g_lap = false;
+    const uint8_t* s_img = nullptr;  /* key of the previous call */
+    size_t s_fs = 0;
+    int s_rs = 0, s_batch = 0;
+    bool s_lap = false;
     int lanes = 2;                  /* a batch of >= 32 frames runs as up to `lanes` chunks on as many streams (ORBX_LANES); 2 and 4 give the same device-resident rate, 2 the better end-to-end rate */
     cudaStream_t lane[ORBX_MAX_LANES] = {};
     cudaEvent_t ev_lane[ORBX_MAX_LANES] = {};
