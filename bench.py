@@ -130,7 +130,7 @@ def single_frame_latency(pkg, local, frame):
     ex1.close()
     ts = np.array(ts) * 1e3
     return {"median_ms": float(np.median(ts)), "p95_ms": float(np.percentile(ts, 95)), "calls": 200,
-            "note": "batch 1 through the C ABI with host buffers; 13 kernel launches + H2D + D2H + sync per call"}
+            "note": "batch 1 through the C ABI with host buffers: H2D + one CUDA-graph launch (23 kernels, per-level branches) + D2H + sync + fetch per call"}
 
 
 def _dbg(torch, tag):

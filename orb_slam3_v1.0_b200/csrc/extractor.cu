@@ -2073,7 +2073,7 @@ extern "C" orbx_status orbx_extract_device(orbx_extractor* e, const uint8_t* d_i
     e->s_img = d_images; e->s_fs = frame_stride; e->s_rs = row_stride; e->s_batch = batch; e->s_lap = d_lap != nullptr;
     const bool key_graph = e->graph_exec && e->g_img == d_images && e->g_fs == frame_stride && e->g_rs == row_stride &&
                            e->g_batch == batch && e->g_lap == (d_lap != nullptr);
-    if (lanes <= 1 && e->use_graph && !e->profiling && (key_graph || key_seen)) {
+    if (lanes <= 1 && batch <= 16 && e->use_graph && !e->profiling && (key_graph || key_seen)) {      /* the latency path */
         /* small batches are launch-latency bound (8 dependent pyramid launches, 14 in all): the chain is
          * captured once per (input pointer, layout, batch, lapping) into a CUDA graph and replayed */
         const bool same = e->graph_exec && e->g_img == d_images && e->g_fs == frame_stride && e->g_rs == row_stride &&

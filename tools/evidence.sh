@@ -12,7 +12,7 @@ timeout 600 python bench.py --impl reference --steps 3 --warmup 1 2>> $out/bench
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $out/r1_launches_$tag.csv \
   python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-matching > $out/ncu_launches_$tag.log 2>&1
 # whole-batch kernels on one stream (ORBX_LANES=1 ORBX_FORK_BLUR=0): 14 extraction launches + 2 stereo launches per step
-ORBX_LANES=1 ORBX_FORK_BLUR=0 timeout 900 ncu --set full --clock-control none --import-source on -s 16 -c 16 -f -o $out/r1_step_full_$tag \
+ORBX_LANES=1 ORBX_FORK_BLUR=0 ORBX_GRAPH=0 timeout 900 ncu --set full --clock-control none --import-source on -s 16 -c 16 -f -o $out/r1_step_full_$tag \
   python tools/profile_step.py --steps 2 --stereo > $out/ncu_full_$tag.log 2>&1; tail -1 $out/ncu_full_$tag.log
 timeout 900 ncu --set full --clock-control none -k 'regex:k_search|k_fuse|k_knn|knn2|k_distinctive|k_assign_grid|k_features_in_area' -c 14 -f \
   -o $out/r1_matcher_full_$tag python tools/profile_step.py --steps 1 --knn 4096 --matcher > $out/ncu_matcher_$tag.log 2>&1; tail -1 $out/ncu_matcher_$tag.log
