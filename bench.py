@@ -133,6 +133,29 @@ def single_frame_latency(pkg, local, frame):
             "note": "batch 1 through the C ABI with host buffers: H2D + one CUDA-graph launch (23 kernels, per-level branches) + D2H + sync + fetch per call"}
 
 
+def cpp_operator_latency(pkg, frame):
+    """The drop-in C++ class itself: tools/shim_latency.cpp (include/orbx/ORBextractor.h over the C ABI)
+    compiled with g++ and run on one frame in pageable host memory.  None when g++ is unavailable."""
+    import subprocess
+    import tempfile
+    try:
+        so = pkg.orbx.build()
+        with tempfile.TemporaryDirectory() as td:
+            exe = os.path.join(td, "shim_latency")
+            subprocess.check_call(["g++", "-std=c++17", "-O2", "-o", exe, os.path.join(ROOT, "tools", "shim_latency.cpp"),
+                                   "-L" + os.path.dirname(so), "-lorbx", "-Wl,-rpath," + os.path.dirname(so)],
+                                  stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, timeout=120)
+            raw = os.path.join(td, "img.raw")
+            with open(raw, "wb") as fh:
+                fh.write(np.ascontiguousarray(frame).tobytes())
+            r = subprocess.run([exe, raw, str(W), str(H), str(NFEAT), "300"], capture_output=True, text=True, timeout=120)
+            out = json.loads(r.stdout.strip().splitlines()[-1])
+            out["note"] = "ORB_SLAM3::ORBextractor::operator() of include/orbx/ORBextractor.h (C++), frame in pageable host memory, keypoints + descriptors in std::vectors"
+            return out
+    except Exception as ex:     # noqa: BLE001 - a secondary leg must not take the line down
+        return {"unavailable": str(ex)[:160]}
+
+
 def _dbg(torch, tag):
     if os.environ.get("ORBX_BENCH_DEBUG_SYNC"):
         torch.cuda.synchronize()
@@ -502,6 +525,7 @@ def main():
             line["matching"] = matching_bench(pkg, torch, local, ex, B)
             line["other_shapes"] = other_shapes_bench(pkg, torch, local)
             line["single_frame_latency"] = single_frame_latency(pkg, local, frames[0])
+            line["cpp_operator_latency"] = cpp_operator_latency(pkg, frames[0])
         if numa is not None:
             os.sched_setaffinity(0, numa[2])          # the CPU baseline gets every core back
         if not args.no_cpu_baseline and world == 1:
