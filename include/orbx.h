@@ -161,6 +161,9 @@ typedef struct {
     int gcols, grows;               /* mFrameGridCols / Rows */
     const float* scale;             /* mvScaleFactors */
     int nlevels;
+    const float* uright;            /* mvuRight of a stereo / RGB-D frame (F->Nleft == -1), e.g. the output of
+                                     * orbx_stereo_matches; NULL = monocular (all -1).  Read by
+                                     * orbx_search_by_projection only (src/ORBmatcher.cc:81-86). */
 } orbx_frame_view;
 
 /* MapPoint fields SearchByProjection reads (src/ORBmatcher.cc:37-70) */
@@ -172,6 +175,9 @@ typedef struct {
     const float* viewcos;           /* mTrackViewCos */
     const float* depth;             /* mTrackDepth (bFarPoints gate) */
     const uint8_t* desc;            /* GetDescriptor(), n x 32 */
+    const float* proj_xr;           /* mTrackProjXR (src/Frame.cc:325); required when the frame view has uright */
+    const uint8_t* has_obs;         /* Observations() > 0 per map point; NULL = all.  Only such a point blocks the
+                                     * keypoint it was assigned to for later points (src/ORBmatcher.cc:77-79) */
 } orbx_mappoints;
 
 /* Map points handed to Fuse, after the host-side projection of src/ORBmatcher.cc:702-760 (:880-917
@@ -243,9 +249,13 @@ orbx_status orbx_extractor_grid_fetch(orbx_extractor* e, int f, int* cell_off, i
 /* ORBmatcher::SearchByProjection(Frame, vpMapPoints, th, bFarPoints, thFarPoints, nnRatio,
  * checkOrientation)   src/ORBmatcher.cc:31-123.
  * claimed[p][i] != 0: frame keypoint i already holds a MapPoint with observations (:77-79);
- * NULL or claimed[p] == NULL = none.  match_mp[p][i] = index of the map point assigned to
- * frame keypoint i or -1; nmatches[p] = the function's return value.  The reference's
- * sequential "first map point claims the keypoint" rule is reproduced exactly. */
+ * NULL or claimed[p] == NULL = none.  match_mp[p][i] = index of the map point frame keypoint i
+ * holds after the call or -1; nmatches[p] = the function's return value (every assignment
+ * counts, also one that a later map point overwrites).  The reference's sequential rule -- a
+ * keypoint assigned to a map point WITH observations is skipped by every later map point, one
+ * assigned to a point without observations can be taken over (:77-79, MP.has_obs) -- and the
+ * stereo gate |mTrackProjXR - mvuRight[idx]| <= r for keypoints with mvuRight > 0 (:81-86,
+ * F.uright + MP.proj_xr) are reproduced exactly. */
 orbx_status orbx_search_by_projection(orbx_matcher* m, int nprob, const orbx_frame_view* F,
                                       const orbx_mappoints* MP, const uint8_t* const* claimed,
                                       float th, int bFarPoints, float thFarPoints, float nnRatio,

@@ -185,8 +185,10 @@ class _FrameView(C.Structure):
 
 def _frame_view(F, keep):
     kx, ky, ko, d, sc = _f32(F["kx"]), _f32(F["ky"]), _i32(F["koct"]), _u8(F["desc"]), _f32(F["scale"])
-    keep += [kx, ky, ko, d, sc]
-    return _FrameView(len(kx), kx.ctypes.data, ky.ctypes.data, ko.ctypes.data, d.ctypes.data, None,
+    ur = _f32(F["uright"]) if F.get("uright") is not None else None
+    keep += [kx, ky, ko, d, sc, ur]
+    return _FrameView(len(kx), kx.ctypes.data, ky.ctypes.data, ko.ctypes.data, d.ctypes.data,
+                      ur.ctypes.data if ur is not None else None,
                       F["minx"], F["miny"], F["gw_inv"], F["gh_inv"], F["gcols"], F["grows"],
                       sc.ctypes.data, len(sc))
 
@@ -223,9 +225,12 @@ def search_by_projection(F, mp, th, bFarPoints=False, thFarPoints=0.0, nnRatio=0
     inview, x, y = _u8(mp["inview"]), _f32(mp["x"]), _f32(mp["y"])
     lvl, vc, dep, d = _i32(mp["level"]), _f32(mp["viewcos"]), _f32(mp["depth"]), _u8(mp["desc"])
     cl = _u8(claimed) if claimed is not None else None
+    xr = _f32(mp["proj_xr"]) if mp.get("proj_xr") is not None else None
+    ho = _u8(mp["has_obs"]) if mp.get("has_obs") is not None else None
+    assert fv.uright is None or xr is not None, "a stereo frame view needs the map points' proj_xr"
     out = np.empty(fv.n, np.int32)
     n = lib().orc_search_by_projection(C.byref(fv), len(x), _p(inview), _p(x), _p(y), _p(lvl), _p(vc), _p(dep),
-                                       _p(d), _p(cl), C.c_float(th), int(bFarPoints), C.c_float(thFarPoints),
+                                       _p(d), _p(xr), _p(ho), _p(cl), C.c_float(th), int(bFarPoints), C.c_float(thFarPoints),
                                        C.c_float(nnRatio), _p(out))
     return n, out
 

@@ -741,12 +741,16 @@ void orc_features_in_area(const orc_frame_view* F, int nq, const float* x, const
 int orc_search_by_projection(const orc_frame_view* F, int nmp, const uint8_t* mp_inview,
                              const float* mp_x, const float* mp_y, const int* mp_level,
                              const float* mp_viewcos, const float* mp_depth, const uint8_t* mp_desc,
+                             const float* mp_proj_xr, const uint8_t* mp_has_obs,
                              const uint8_t* claimed_in, float th, int bFarPoints, float thFarPoints,
                              float nnRatio, int* match_mp) {
-    /* src/ORBmatcher.cc:31-123 */
+    /* src/ORBmatcher.cc:31-123.  match_mp[idx] plays F->mvpMapPoints[idx]: a keypoint is skipped when
+     * it held a MapPoint with observations before the call (claimed_in) or when the MapPoint assigned
+     * to it earlier in this call has Observations() > 0 (:77-79, tested per point: mp_has_obs, NULL =
+     * every map point has observations); an assignment by a point without observations can be
+     * overwritten, and every assignment counts in nmatches (:108-110). */
     std::vector<std::vector<int>> grid = build_grid(F);
-    std::vector<uint8_t> claimed(F->n, 0);
-    for (int i = 0; i < F->n; ++i) { claimed[i] = claimed_in ? claimed_in[i] : 0; match_mp[i] = -1; }
+    for (int i = 0; i < F->n; ++i) match_mp[i] = -1;
     int nmatches = 0;
     const bool bFactor = th != 1.0;
     std::vector<int> vIndices;
@@ -762,9 +766,14 @@ int orc_search_by_projection(const orc_frame_view* F, int nmp, const uint8_t* mp
         const uint8_t* MPdescriptor = mp_desc + (size_t)iMP * 32;
         int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
         for (int idx : vIndices) {
-            if (claimed[idx]) continue;
-            /* mono fork: F->Nleft == -1 && mvuRight>0 branch (:81-86) needs mTrackProjXR; with
-             * mvuRight = -1 everywhere (src/Frame.cc:89-90) it is never taken. */
+            if (claimed_in && claimed_in[idx]) continue;
+            if (match_mp[idx] >= 0 && (!mp_has_obs || mp_has_obs[match_mp[idx]])) continue;
+            /* :81-86  F->Nleft == -1 && F->mvuRight[idx] > 0: the right-image coordinate must agree with
+             * the projection mTrackProjXR (src/Frame.cc:325).  F->uright == NULL: monocular frame. */
+            if (F->uright && F->uright[idx] > 0) {
+                const float er = fabsf(mp_proj_xr[iMP] - F->uright[idx]);
+                if (er > r) continue;
+            }
             const int dist = orc_descriptor_distance(MPdescriptor, F->desc + (size_t)idx * 32);
             if (dist < bestDist) {
                 bestDist2 = bestDist; bestDist = dist;
@@ -779,7 +788,6 @@ int orc_search_by_projection(const orc_frame_view* F, int nmp, const uint8_t* mp
             if (bestLevel == bestLevel2 && bestDist > nnRatio * bestDist2) continue;
             if (bestLevel != bestLevel2 || bestDist <= nnRatio * bestDist2) {
                 match_mp[bestIdx] = iMP;
-                claimed[bestIdx] = 1;   /* assigned MapPoint has Observations()>0 (local map points) */
                 nmatches++;
             }
         }

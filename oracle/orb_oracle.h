@@ -117,12 +117,16 @@ void orc_features_in_area(const orc_frame_view* F, int nq, const float* x, const
 /* SearchByProjection(Frame, MapPoints, th, ...) ORBmatcher.cc:31-123.
  * Map points are flattened: in-view flag, projected x,y, predicted level,
  * view cos, descriptor. `claimed[i]!=0` marks frame keypoints that already
- * hold a MapPoint with observations. match_mp[i] receives the map-point index
- * assigned to frame keypoint i (or -1). Returns nmatches. */
+ * hold a MapPoint with observations. mp_proj_xr = mTrackProjXR (read when
+ * F->uright != NULL: the stereo gate of :81-86); mp_has_obs[i] = Observations() > 0
+ * of map point i (NULL = all): only such a point blocks a keypoint it was assigned
+ * to (:77-79). match_mp[i] receives the map-point index finally held by frame
+ * keypoint i (or -1). Returns nmatches (every assignment counts). */
 int orc_search_by_projection(const orc_frame_view* F, int nmp, const uint8_t* mp_inview,
                              const float* mp_x, const float* mp_y, const int* mp_level,
                              const float* mp_viewcos, const float* mp_depth,
-                             const uint8_t* mp_desc, const uint8_t* claimed_in,
+                             const uint8_t* mp_desc, const float* mp_proj_xr,
+                             const uint8_t* mp_has_obs, const uint8_t* claimed_in,
                              float th, int bFarPoints, float thFarPoints, float nnRatio,
                              int* match_mp);
 

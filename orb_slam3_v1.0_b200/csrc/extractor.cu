@@ -1631,7 +1631,7 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
 #define CK(call) do { cudaError_t _e = (call); if (_e != cudaSuccess) { orbx_set_error("%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(_e)); free_all(e); return ORBX_ERR_CUDA; } } while (0)
 /* dynamic shared-memory opt-in that only ever grows per (kernel, device): a handle created later with
  * a smaller need must not lower the limit under an older handle */
-#define CK_SMEM(kernel, bytes) do { size_t& _cur = orbx_smem_slot(reinterpret_cast<const void*>(kernel), e->P.device); \
+#define CK_SMEM(kernel, bytes) do { std::lock_guard<std::mutex> _lk(orbx_smem_mutex()); size_t& _cur = orbx_smem_slot(reinterpret_cast<const void*>(kernel), e->P.device); \
     const size_t _need = (size_t)(bytes); \
     if (_need > 48 * 1024 && _need > _cur) { CK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)_need)); _cur = _need; } } while (0)
     CK(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));

@@ -241,15 +241,19 @@ struct SbpProb {
     float minx, miny, gw_inv, gh_inv, th, thFar, nnRatio, pad;
     unsigned long long kx, ky, koct, kangle, desc, claimed, scale;      /* offsets into the input arena */
     unsigned long long mflag, mx, my, mlevel, maux, mdepth, mdesc;
+    unsigned long long uright, mxr, mobs;                               /* stereo gate / per-point Observations() > 0; ~0 = absent */
     unsigned long long out_match;                                       /* offset into the output arena */
 };
 
 /* One CTA per problem.
  *  1. Frame grid (AssignFeaturesToGrid) as a CSR over the cells, built in shared memory.
  *  2. Rounds of "every map point picks its best / second-best unclaimed candidate" until the
- *     per-keypoint owner array stops changing.  Map point i treats keypoint k as claimed when
- *     an EARLIER map point owned k in the previous round, so the fixed point is exactly the
- *     reference's sequential result (round r fixes at least the first r map points).
+ *     per-keypoint BLOCKER array stops changing.  Map point i treats keypoint k as claimed when
+ *     an EARLIER map point with observations took k in the previous round, so the fixed point is
+ *     exactly the reference's sequential result (round r fixes at least the first r map points).
+ *     A map point without observations assigns without blocking (src/ORBmatcher.cc:77-79): the
+ *     keypoint finally holds its blocker, else the LAST such point that chose it; every accepted
+ *     map point of the final round counts in nmatches.
  *  3. KeyFrame overload: rotation histogram + ComputeThreeMaxima on the final matches.
  * Candidate order of the reference (cell columns, then rows, then insertion order) only matters
  * for ties; it is carried in the low bits of the 64-bit keys (dist << 32 | CSR position). */
@@ -278,13 +282,17 @@ __global__ void __launch_bounds__(MT) k_search_by_projection(const uint8_t* __re
     const float* maux = reinterpret_cast<const float*>(in + P.maux);
     const float* mdepth = reinterpret_cast<const float*>(in + P.mdepth);
     const uint4* mdesc = reinterpret_cast<const uint4*>(in + P.mdesc);
+    const float* uright = P.uright == ~0ull ? nullptr : reinterpret_cast<const float*>(in + P.uright);   /* mvuRight */
+    const float* mxr = reinterpret_cast<const float*>(in + P.mxr);                                        /* mTrackProjXR */
+    const uint8_t* mobs = P.mobs == ~0ull ? nullptr : in + P.mobs;
     int* match = reinterpret_cast<int*>(out + P.out_match);
 
     uint32_t* cell_start = sm;                        /* [ncell + 1], column-major cells (ix*grows + iy) */
     uint32_t* cell_fill = cell_start + ncell + 1;     /* [ncell] */
     uint32_t* owner_a = cell_fill + ncell;            /* [n] */
     uint32_t* owner_b = owner_a + n;                  /* [n] */
-    unsigned short* csr = reinterpret_cast<unsigned short*>(owner_b + n);   /* [n] */
+    uint32_t* last_nb = owner_b + n;                  /* [n] last map point WITHOUT observations that chose the keypoint, + 1 */
+    unsigned short* csr = reinterpret_cast<unsigned short*>(last_nb + n);   /* [n] */
 
     /* ---- 1. grid: PosInGrid + AssignFeaturesToGrid (reference src/Frame.cc:157-176, 470-480) */
     for (int i = tid; i <= ncell; i += MT) cell_start[i] = 0;
@@ -329,8 +337,10 @@ __global__ void __launch_bounds__(MT) k_search_by_projection(const uint8_t* __re
     uint32_t* cur = owner_b;
     const bool bFactor = P.th != 1.0f;
     for (int round = 0; round <= nmp; ++round) {
-        for (int i = tid; i < n; i += MT) cur[i] = 0xFFFFFFFFu;
+        for (int i = tid; i < n; i += MT) { cur[i] = 0xFFFFFFFFu; last_nb[i] = 0u; }
+        if (tid == 0) s_count = 0;
         __syncthreads();
+        int accepted = 0;
         for (int i = tid; i < nmp; i += MT) {
             if (!mflag[i]) continue;
             const int level = mlevel[i];
@@ -367,6 +377,10 @@ __global__ void __launch_bounds__(MT) k_search_by_projection(const uint8_t* __re
                     if (bCheckLevels && (oc < minLevel || (maxLevel >= 0 && oc > maxLevel))) continue;
                     if (!(fabsf(kx[idx] - x) < r && fabsf(ky[idx] - y) < r)) continue;
                     if (claimed[idx] || prev[idx] < (uint32_t)i) continue;
+                    if (uright) {                                   /* :81-86, F->Nleft == -1 && mvuRight[idx] > 0 */
+                        const float ur = uright[idx];
+                        if (ur > 0.f && fabsf(mxr[i] - ur) > r) continue;
+                    }
                     const int dist = hamming256(q0, q1, __ldg(kdesc + 2 * idx), __ldg(kdesc + 2 * idx + 1));
                     if (dist >= 256) continue;                      /* bestDist / bestDist2 start at 256, strict < */
                     const unsigned long long key = ((unsigned long long)dist << 32) | e;
@@ -385,8 +399,13 @@ __global__ void __launch_bounds__(MT) k_search_by_projection(const uint8_t* __re
             } else {
                 accept = bestDist <= TH_HIGH;
             }
-            if (accept) atomicMin(&cur[bestIdx], (uint32_t)i);
+            if (accept) {
+                ++accepted;
+                if (!mobs || mobs[i]) atomicMin(&cur[bestIdx], (uint32_t)i);
+                else atomicMax(&last_nb[bestIdx], (uint32_t)i + 1u);
+            }
         }
+        if (accepted) atomicAdd(&s_count, accepted);
         __syncthreads();
         int changed = 0;
         for (int i = tid; i < n; i += MT) changed |= (cur[i] != prev[i]);
@@ -395,15 +414,23 @@ __global__ void __launch_bounds__(MT) k_search_by_projection(const uint8_t* __re
     }
 
     /* ---- 3. results (+ rotation histogram for the KeyFrame overload, reference :1290-1322) */
+    /* the rounds stopped at cur == prev: the last round evaluated every map point against the final
+     * blockers, so its choices (s_count acceptances, last_nb) are the reference's */
     const bool hist = P.mode == 1 && P.checkOri;
     int mycount = 0;
+    const int accepted_total = s_count;
+    __syncthreads();
+    if (tid == 0) s_count = 0;
     for (int i = tid; i < n; i += MT) {
-        const uint32_t o = prev[i];
+        uint32_t o = prev[i];
+        if (o == 0xFFFFFFFFu && last_nb[i]) o = last_nb[i] - 1u;
+        prev[i] = o;
         if (o != 0xFFFFFFFFu) {
             ++mycount;
             if (hist) atomicAdd(&s_hist[rot_bin(maux[o], kangle[i])], 1);
         }
     }
+    if (P.mode == 0) mycount = tid == 0 ? accepted_total : 0;       /* nmatches++ per assignment (:108-110) */
     __syncthreads();
     if (hist && tid == 0) three_maxima(s_hist, HISTO_LENGTH, s_ind[0], s_ind[1], s_ind[2]);
     __syncthreads();
@@ -463,6 +490,13 @@ static orbx_status run_sbp(orbx_matcher* m, int nprob, const orbx_frame_view* F,
             P.mflag = in.add(M.inview, nmp); P.mx = in.add(M.x, 4 * (size_t)nmp); P.my = in.add(M.y, 4 * (size_t)nmp);
             P.mlevel = in.add(M.level, 4 * (size_t)nmp); P.maux = in.add(M.viewcos, 4 * (size_t)nmp);
             P.mdepth = in.add(M.depth, M.depth ? 4 * (size_t)nmp : 0); P.mdesc = in.add(M.desc, 32 * (size_t)nmp);
+            if (f.uright && nmp > 0 && !M.proj_xr) {
+                orbx_set_error("problem %d: the frame view has mvuRight but the map points have no proj_xr (mTrackProjXR)", p);
+                return ORBX_ERR_INVALID;
+            }
+            P.uright = f.uright && f.n > 0 ? in.add(f.uright, 4 * (size_t)f.n) : ~0ull;
+            P.mxr = in.add(f.uright ? M.proj_xr : nullptr, f.uright ? 4 * (size_t)nmp : 0);
+            P.mobs = M.has_obs && nmp > 0 ? in.add(M.has_obs, (size_t)nmp) : ~0ull;
         } else {
             const orbx_kf_points& M = MP1[p];
             if (nmp > 0 && (!M.valid || !M.u || !M.v || !M.level || !M.desc || (checkOri && !M.angle))) {
@@ -472,13 +506,14 @@ static orbx_status run_sbp(orbx_matcher* m, int nprob, const orbx_frame_view* F,
             P.mflag = in.add(M.valid, nmp); P.mx = in.add(M.u, 4 * (size_t)nmp); P.my = in.add(M.v, 4 * (size_t)nmp);
             P.mlevel = in.add(M.level, 4 * (size_t)nmp); P.maux = in.add(M.angle, M.angle ? 4 * (size_t)nmp : 0);
             P.mdepth = in.add(nullptr, 0); P.mdesc = in.add(M.desc, 32 * (size_t)nmp);
+            P.uright = ~0ull; P.mxr = in.add(nullptr, 0); P.mobs = ~0ull;     /* :1268 any assigned keypoint is skipped */
         }
         /* map-point levels index mvScaleFactors: validate on the host, as a bad level is UB in the reference */
         const int32_t* lv = mode == 0 ? MP0[p].level : MP1[p].level;
         for (int i = 0; i < nmp; ++i)
             if (lv[i] < 0 || lv[i] >= f.nlevels) { orbx_set_error("problem %d: map point %d level %d outside [0,%d)", p, i, lv[i], f.nlevels); return ORBX_ERR_INVALID; }
         P.out_match = out.add(nullptr, 4 * (size_t)f.n);
-        smem = std::max(smem, (size_t)4 * (2 * (size_t)f.gcols * f.grows + 1 + 2 * (size_t)f.n) + 2 * (size_t)f.n + 16);
+        smem = std::max(smem, (size_t)4 * (2 * (size_t)f.gcols * f.grows + 1 + 3 * (size_t)f.n) + 2 * (size_t)f.n + 16);
     }
     const size_t probs_off = in.add(probs.data(), sizeof(SbpProb) * (size_t)nprob);
     const size_t counts_off = out.add(nullptr, 4 * (size_t)nprob);

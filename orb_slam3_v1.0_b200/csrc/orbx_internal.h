@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <map>
+#include <mutex>
 #include <string>
 #include <utility>
 #include <vector>
@@ -34,11 +35,19 @@ inline size_t& orbx_smem_slot(const void* kernel, int device) {       /* largest
     static std::map<std::pair<const void*, int>, size_t> m;
     return m[std::make_pair(kernel, device)];
 }
+/* The library is called from several host threads (left / right extractor threads, Tracking /
+ * LocalMapping / LoopClosing matchers): the map and the cudaFuncSetAttribute that follows a
+ * lookup are serialised by this mutex. */
+inline std::mutex& orbx_smem_mutex() {
+    static std::mutex mu;
+    return mu;
+}
 #define ORBX_ENSURE_SMEM(kernel, bytes)                                                   \
     do {                                                                                  \
         int _dev = 0;                                                                     \
         ORBX_CUDA(cudaGetDevice(&_dev));                                                  \
         const size_t _need = (size_t)(bytes);                                             \
+        std::lock_guard<std::mutex> _lk(orbx_smem_mutex());                               \
         size_t& _cur = orbx_smem_slot(reinterpret_cast<const void*>(kernel), _dev);       \
         if (_need > 48 * 1024 && _need > _cur) {                                          \
             ORBX_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)_need)); \

@@ -32,7 +32,7 @@ def build(force=False):
     csrc = os.path.join(_HERE, "csrc")
     if force:
         subprocess.check_call(["make", "-s", "-C", csrc, "clean"])
-    subprocess.check_call(["make", "-s", "-C", csrc])
+    subprocess.check_call(["make", "-s", "-j4", "-C", csrc])
     return _SO
 
 
@@ -344,12 +344,13 @@ class _FrameView(C.Structure):
     _fields_ = [("n", C.c_int), ("kx", C.c_void_p), ("ky", C.c_void_p), ("koct", C.c_void_p), ("kangle", C.c_void_p),
                 ("desc", C.c_void_p), ("minx", C.c_float), ("miny", C.c_float), ("gw_inv", C.c_float),
                 ("gh_inv", C.c_float), ("gcols", C.c_int), ("grows", C.c_int), ("scale", C.c_void_p),
-                ("nlevels", C.c_int)]
+                ("nlevels", C.c_int), ("uright", C.c_void_p)]
 
 
 class _MapPoints(C.Structure):
     _fields_ = [("n", C.c_int), ("inview", C.c_void_p), ("x", C.c_void_p), ("y", C.c_void_p), ("level", C.c_void_p),
-                ("viewcos", C.c_void_p), ("depth", C.c_void_p), ("desc", C.c_void_p)]
+                ("viewcos", C.c_void_p), ("depth", C.c_void_p), ("desc", C.c_void_p), ("proj_xr", C.c_void_p),
+                ("has_obs", C.c_void_p)]
 
 
 class _KFPoints(C.Structure):
@@ -392,7 +393,8 @@ def _frame_view(F, keep):
     return _FrameView(len(F["kx"]), _arr(F["kx"], np.float32, keep), _arr(F["ky"], np.float32, keep),
                       _arr(F["koct"], np.int32, keep), _arr(F.get("kangle"), np.float32, keep),
                       _arr(F["desc"], np.uint8, keep), F["minx"], F["miny"], F["gw_inv"], F["gh_inv"],
-                      F["gcols"], F["grows"], _arr(F["scale"], np.float32, keep), len(F["scale"]))
+                      F["gcols"], F["grows"], _arr(F["scale"], np.float32, keep), len(F["scale"]),
+                      _arr(F.get("uright"), np.float32, keep))
 
 
 def _ptr_array(arrs, keep):
@@ -562,7 +564,8 @@ class ORBmatcher:
         mp = (_MapPoints * len(Fs))(*[_MapPoints(len(m["x"]), _arr(m["inview"], np.uint8, keep), _arr(m["x"], np.float32, keep),
                                                  _arr(m["y"], np.float32, keep), _arr(m["level"], np.int32, keep),
                                                  _arr(m["viewcos"], np.float32, keep), _arr(m.get("depth"), np.float32, keep),
-                                                 _arr(m["desc"], np.uint8, keep)) for m in MPs])
+                                                 _arr(m["desc"], np.uint8, keep), _arr(m.get("proj_xr"), np.float32, keep),
+                                                 _arr(m.get("has_obs"), np.uint8, keep)) for m in MPs])
         cla = [None if c is None else np.ascontiguousarray(c, np.uint8) for c in cl]
         keep.append(cla)
         outs = [np.empty(len(f["kx"]), np.int32) for f in Fs]

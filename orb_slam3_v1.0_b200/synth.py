@@ -120,7 +120,27 @@ def projection_problem(F, nmp=1500, seed=2, jitter=3.0, flip_p=0.05, dup=0.3):
         # KeyFrame overload names
         "valid": (rng.random(nmp) < 0.9).astype(np.uint8),
         "angle": ((F["kangle"][src] + rng.choice([0.0, 0.0, 0.0, 40.0, 95.0, 200.0], nmp) + rng.normal(0, 4, nmp)) % 360).astype(np.float32),
+        "src": src,
     }
+
+
+def add_stereo(F, MP, seed=7, p_stereo=0.7, p_obs=0.85, xr_sigma=4.0):
+    """Turn (frame view, projection problem) into the stereo case of SearchByProjection
+    (reference src/ORBmatcher.cc:77-86): F gets mvuRight (> 0 for `p_stereo` of the keypoints, else -1),
+    the map points get mTrackProjXR near the uRight of the keypoint they target (sigma `xr_sigma` px,
+    20 % far off, so the |mTrackProjXR - mvuRight| <= r gate rejects some candidates) and has_obs
+    (Observations() > 0)."""
+    rng = np.random.default_rng(seed)
+    n, nmp = len(F["kx"]), len(MP["x"])
+    disp = rng.uniform(2.0, 60.0, n).astype(np.float32)
+    ur = np.where(rng.random(n) < p_stereo, np.maximum(F["kx"] - disp, 0.5), -1.0).astype(np.float32)
+    F2, MP2 = dict(F), dict(MP)
+    F2["uright"] = ur
+    tgt = np.where(ur[MP["src"]] > 0, ur[MP["src"]], F["kx"][MP["src"]] - 20.0)
+    far = (rng.random(nmp) < 0.2) * rng.choice([-1.0, 1.0], nmp) * rng.uniform(20.0, 160.0, nmp)    # wrong depth: gate must reject
+    MP2["proj_xr"] = (tgt + rng.normal(0, xr_sigma, nmp) + far).astype(np.float32)
+    MP2["has_obs"] = (rng.random(nmp) < p_obs).astype(np.uint8)
+    return F2, MP2
 
 
 def keyframe_pair(n1=1000, n2=1100, nnodes=90, seed=3, width=752, height=480, nlevels=8):

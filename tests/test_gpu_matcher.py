@@ -51,6 +51,51 @@ def test_search_by_projection_chained_claims(matcher, oracle, synth):
     assert gn == on and np.array_equal(gm, om) and on >= 300
 
 
+@pytest.mark.parametrize("n,nmp,th,seed", [(1000, 1500, 1.0, 11), (1000, 2500, 3.0, 12), (600, 1500, 12.0, 13)])
+def test_search_by_projection_stereo_gate(matcher, oracle, synth, n, nmp, th, seed):
+    """Stereo frames (mvuRight > 0): the |mTrackProjXR - mvuRight[idx]| <= r gate of reference
+    src/ORBmatcher.cc:81-86, and the per-point Observations() > 0 rule of :77-79 (a point without
+    observations assigns but does not block; every assignment counts)."""
+    F = synth.frame_view(n, seed=seed)
+    MP = synth.projection_problem(F, nmp, seed=seed + 100, dup=0.5)
+    Fs, MPs = synth.add_stereo(F, MP, seed=seed + 200)
+    on, om = oracle.search_by_projection(Fs, MPs, th, False, 0.0, 0.8)
+    gn, gm = matcher.SearchByProjection(Fs, MPs, th, False, 0.0, 0.8)
+    assert gn == on and np.array_equal(gm, om)
+    # gate only (every point has observations)
+    MPg = dict(MPs); MPg.pop("has_obs")
+    on2, om2 = oracle.search_by_projection(Fs, MPg, th, False, 0.0, 0.8)
+    gn2, gm2 = matcher.SearchByProjection(Fs, MPg, th, False, 0.0, 0.8)
+    assert gn2 == on2 and np.array_equal(gm2, om2)
+    # the gate rejects at least one candidate the mono search accepts; mono results are unchanged
+    on3, om3 = oracle.search_by_projection(F, MPg, th, False, 0.0, 0.8)
+    gn3, gm3 = matcher.SearchByProjection(F, MPg, th, False, 0.0, 0.8)
+    assert gn3 == on3 and np.array_equal(gm3, om3)
+    assert not np.array_equal(om2, om3)
+    assert not np.array_equal(om, om2) or on != on2           # the observations rule is live too
+
+
+def test_search_by_projection_takeover_chain(matcher, oracle, synth):
+    """Identical descriptors, half of the map points without observations: long chains of
+    assignments that later points take over."""
+    F = synth.frame_view(300, seed=19)
+    rng = np.random.default_rng(19)
+    base = rng.integers(0, 256, 32, dtype=np.uint8)
+    F["desc"][:] = base
+    F["desc"] ^= np.packbits(rng.random((300, 256)) < 0.02, axis=1, bitorder="little")
+    F["kx"][:] = rng.uniform(300, 360, 300).astype(np.float32); F["ky"][:] = rng.uniform(200, 240, 300).astype(np.float32)
+    F["koct"][:] = 2
+    nmp = 700
+    MP = {"inview": np.ones(nmp, np.uint8), "x": rng.uniform(300, 360, nmp).astype(np.float32),
+          "y": rng.uniform(200, 240, nmp).astype(np.float32), "level": np.full(nmp, 2, np.int32),
+          "viewcos": np.ones(nmp, np.float32), "depth": np.ones(nmp, np.float32),
+          "desc": np.tile(base, (nmp, 1)), "has_obs": (rng.random(nmp) < 0.5).astype(np.uint8)}
+    on, om = oracle.search_by_projection(F, MP, 10.0, False, 0.0, 1.0)
+    gn, gm = matcher.SearchByProjection(F, MP, 10.0, False, 0.0, 1.0)
+    assert gn == on and np.array_equal(gm, om)
+    assert on > int((om >= 0).sum())                          # some assignments were taken over
+
+
 def test_search_by_projection_batched(matcher, oracle, synth):
     Fs = [synth.frame_view(600 + 50 * i, seed=20 + i) for i in range(7)]
     MPs = [synth.projection_problem(F, 900 + 10 * i, seed=40 + i) for i, F in enumerate(Fs)]

@@ -58,6 +58,8 @@ def _sbp_numpy(F, MP, th, nnRatio, claimed=None):
     py = np.round((F["ky"] - f32(F["miny"])) * f32(F["gh_inv"])).astype(int)
     ok_cell = (py * F["gcols"] + px >= 0) & (py * F["gcols"] + px < F["gcols"] * F["grows"])
     cl = np.zeros(n, bool) if claimed is None else np.asarray(claimed, bool).copy()
+    ur = F.get("uright")
+    obs = MP.get("has_obs")
     match = np.full(n, -1, np.int32)
     nm = 0
     for i in range(len(MP["x"])):
@@ -76,6 +78,9 @@ def _sbp_numpy(F, MP, th, nnRatio, claimed=None):
         cand = np.nonzero(ok_cell & (px >= c0) & (px <= c1) & (py >= r0) & (py <= r1) &
                           (F["koct"] >= lvl - 1) & (F["koct"] <= lvl) &
                           (np.abs(F["kx"] - x) < r) & (np.abs(F["ky"] - y) < r) & ~cl)[0]
+        if ur is not None and len(cand):       # :81-86 stereo gate on keypoints with mvuRight > 0
+            er = np.abs(MP["proj_xr"][i] - ur[cand])
+            cand = cand[~((ur[cand] > 0) & (er > r))]
         if len(cand) == 0:
             continue
         cand = cand[np.lexsort((cand, py[cand], px[cand]))]
@@ -88,7 +93,8 @@ def _sbp_numpy(F, MP, th, nnRatio, claimed=None):
             elif dist < best2:
                 best2, bl2 = dist, F["koct"][k]
         if best <= 100 and not (bl == bl2 and f32(best) > f32(nnRatio) * f32(best2)):
-            match[bi] = i; cl[bi] = True; nm += 1
+            match[bi] = i; nm += 1
+            cl[bi] = True if obs is None else bool(obs[i])     # :77-79 only a point with observations blocks
     return nm, match
 
 
@@ -99,6 +105,27 @@ def test_search_by_projection_vs_numpy(oracle, synth, th, seed):
     on, om = oracle.search_by_projection(F, MP, th, False, 0.0, 0.8)
     nn, nmch = _sbp_numpy(F, MP, th, 0.8)
     assert on == nn and np.array_equal(om, nmch) and on > 50
+
+
+@pytest.mark.parametrize("th,seed", [(1.0, 4), (3.0, 5), (12.0, 6)])
+def test_search_by_projection_stereo_vs_numpy(oracle, synth, th, seed):
+    """The mvuRight / mTrackProjXR gate (reference src/ORBmatcher.cc:81-86) and the per-point
+    Observations() > 0 rule (:77-79): oracle == independent restatement, and both are live."""
+    F = synth.frame_view(500, seed=seed)
+    MP = synth.projection_problem(F, 900, seed=seed + 10, dup=0.5)
+    Fs, MPs = synth.add_stereo(F, MP, seed=seed + 20)
+    on, om = oracle.search_by_projection(Fs, MPs, th, False, 0.0, 0.8)
+    nn, nmch = _sbp_numpy(Fs, MPs, th, 0.8)
+    assert on == nn and np.array_equal(om, nmch) and on > 50
+    # the gate rejects something: mono view of the same problem differs
+    MPm = dict(MPs); MPm.pop("has_obs")
+    gn, gm = oracle.search_by_projection(Fs, MPm, th, False, 0.0, 0.8)
+    mn, mm = oracle.search_by_projection(F, MPm, th, False, 0.0, 0.8)
+    assert not np.array_equal(gm, mm)
+    # the observations rule is live: a point without observations does not block, and its
+    # assignment is counted even when a later point takes the keypoint over
+    assert on != gn or not np.array_equal(om, gm)
+    assert on >= int((om >= 0).sum())
 
 
 def test_search_for_triangulation_properties(oracle, synth):
