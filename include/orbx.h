@@ -344,6 +344,20 @@ orbx_status orbx_knn2_device(orbx_matcher* m, const void* d_q, int nq, const voi
 orbx_status orbx_knn2_merge_device(orbx_matcher* m, const unsigned long long* d_parts, int nparts,
                                    int nq, float ratio, int* d_d1, int* d_i1, int* d_d2,
                                    int* d_i2, uint8_t* d_pass);
+/* orbx_knn2_device without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid it).  Same arguments and results as
+ * orbx_knn2_device; the per-slice partial keys live in a static 8 MiB device array inside
+ * liborbx.so (orbx_knn2_noalloc_scratch_bytes(); held by every GPU that loads the library until
+ * exit) instead of the handle's grow-on-demand scratch.  The call needs
+ * slices * nq * 16 bytes of it (slices = how many grid.y slices the database is cut into: about
+ * 444 / ceil(nq / 1024) for large databases, 1 -- no scratch at all -- when nq >= ~450 k and
+ * ndb <= 4 M); more returns ORBX_ERR_CAPACITY with the numbers in orbx_last_error().  Calls no
+ * cudaMalloc / cudaFree.  All calls on a device share the array: calls that overlap on the GPU
+ * (two handles, two streams) race -- serialise them or use orbx_knn2_device. */
+orbx_status orbx_knn2_device_noalloc(orbx_matcher* m, const void* d_q, int nq, const void* d_db, int ndb,
+                                     long long index_base, unsigned long long* d_keys);
+size_t orbx_knn2_noalloc_scratch_bytes(void);
 /* tuning knob for the kNN kernel: 0 = 8 POPC per pair, 1 = carry-save adder tree (4 POPC) */
 orbx_status orbx_matcher_set_knn_variant(orbx_matcher* m, int variant);
 orbx_status orbx_matcher_synchronize(orbx_matcher* m);

@@ -20,6 +20,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <mutex>
 #include <vector>
 
 #include "orbx_internal.h"
@@ -953,6 +954,67 @@ extern "C" orbx_status orbx_knn2_merge_device(orbx_matcher* m, const unsigned lo
                                                                                nullptr);
     ORBX_CUDA(cudaGetLastError());
     m->last_launches = 1;
+    return ORBX_OK;
+}
+
+/* ---- allocation-free variant of orbx_knn2_device (no counterpart in the reference; added
+ * for callers that cannot call cudaMalloc: code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid it).  Same kernels, but the per-slice partial
+ * top-2 keys go to a file-scope __device__ array instead of the matcher's grow-on-demand scratch.
+ * Every GPU that loads the library holds the array (8 MiB) until exit.  In host code the array's
+ * name is only a stand-in: its device address is fetched once per device, with that device current,
+ * by cudaGetSymbolAddress.  ALL calls on a device share the array: calls that overlap on the GPU
+ * (different matcher handles / streams) race; calls on one stream are ordered.  Nothing in it has to
+ * start at zero: k_knn2 writes every (slice, query) entry that k_knn2_merge reads. */
+#define ORBX_KNN2_STATIC_BYTES (8u << 20)
+#define ORBX_KNN2_STATIC_MAXDEV 64
+static __device__ __align__(256) unsigned char g_knn2_static_scratch[ORBX_KNN2_STATIC_BYTES];
+static unsigned long long* g_knn2_static_ptr[ORBX_KNN2_STATIC_MAXDEV];
+static std::mutex g_knn2_static_mu;
+
+extern "C" size_t orbx_knn2_noalloc_scratch_bytes(void) { return ORBX_KNN2_STATIC_BYTES; }
+
+extern "C" orbx_status orbx_knn2_device_noalloc(orbx_matcher* m, const void* d_q, int nq, const void* d_db, int ndb,
+                                                long long index_base, unsigned long long* d_keys) {
+    if (!m || nq < 0 || ndb < 0 || (nq > 0 && (!d_q || !d_keys)) || (ndb > 0 && !d_db) || index_base < 0 ||
+        index_base + ndb > 0xFFFFFFFFll) {
+        orbx_set_error("bad kNN arguments");
+        return ORBX_ERR_INVALID;
+    }
+    if (nq == 0) return ORBX_OK;
+    if (m->device < 0 || m->device >= ORBX_KNN2_STATIC_MAXDEV) { orbx_set_error("device ordinal %d outside [0,%d)", m->device, ORBX_KNN2_STATIC_MAXDEV); return ORBX_ERR_INVALID; }
+    const int srows = knn_split_rows(nq, ndb);
+    const int ns = std::max(1, (int)(((long long)ndb + srows - 1) / srows));
+    const size_t need = ns > 1 ? (size_t)ns * nq * 16 : 0;
+    if (need > ORBX_KNN2_STATIC_BYTES) {
+        orbx_set_error("orbx_knn2_device_noalloc: %d queries x %d database slices need %zu B of scratch, the static array holds %u B "
+                       "(use orbx_knn2_device, or fewer queries / database rows per call)", nq, ns, need, ORBX_KNN2_STATIC_BYTES);
+        return ORBX_ERR_CAPACITY;
+    }
+    ORBX_CUDA(cudaSetDevice(m->device));
+    unsigned long long* part = d_keys;
+    if (ns > 1) {
+        std::lock_guard<std::mutex> lk(g_knn2_static_mu);
+        if (!g_knn2_static_ptr[m->device]) {             /* once per device, that device current */
+            void* p = nullptr;
+            ORBX_CUDA(cudaGetSymbolAddress(&p, g_knn2_static_scratch));
+            if (!p) { orbx_set_error("cudaGetSymbolAddress returned a null address"); return ORBX_ERR_CUDA; }
+            g_knn2_static_ptr[m->device] = static_cast<unsigned long long*>(p);
+        }
+        part = g_knn2_static_ptr[m->device];
+    }
+    const dim3 grid((nq + KNN_THREADS * KNN_QPT - 1) / (KNN_THREADS * KNN_QPT), ns);
+    if (m->knn_variant == 0)
+        k_knn2<0><<<grid, KNN_THREADS, 0, m->stream>>>((const uint4*)d_q, nq, (const uint4*)d_db, ndb, index_base, srows, part);
+    else
+        k_knn2<1><<<grid, KNN_THREADS, 0, m->stream>>>((const uint4*)d_q, nq, (const uint4*)d_db, ndb, index_base, srows, part);
+    m->last_launches = 1;
+    if (ns > 1) {
+        k_knn2_merge<<<std::min((nq + 255) / 256, 148 * 8), 256, 0, m->stream>>>(part, ns, nq, 0.f, nullptr, nullptr, nullptr, nullptr,
+                                                                                   nullptr, d_keys);
+        m->last_launches = 2;
+    }
+    ORBX_CUDA(cudaGetLastError());
     return ORBX_OK;
 }
 

@@ -105,6 +105,8 @@ def lib():
         L.orbx_stereo_fetch.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int]
         L.orbx_knn2.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_float] + [C.c_void_p] * 5
         L.orbx_knn2_device.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_longlong, C.c_void_p]
+        L.orbx_knn2_device_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_longlong, C.c_void_p]
+        L.orbx_knn2_noalloc_scratch_bytes.restype = C.c_size_t
         L.orbx_knn2_merge_device.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_float] + [C.c_void_p] * 5
         _lib = L
     return _lib
@@ -632,6 +634,10 @@ class ORBmatcher:
     def knn2_device(self, d_q, nq, d_db, ndb, index_base, d_keys):
         """device pointers (ints); asynchronous on the matcher's stream."""
         _ck(lib().orbx_knn2_device(self._h, d_q, nq, d_db, ndb, index_base, d_keys))
+
+    def knn2_device_noalloc(self, d_q, nq, d_db, ndb, index_base, d_keys):
+        """orbx_knn2_device_noalloc: as knn2_device, partial keys in the library's static device array."""
+        _ck(lib().orbx_knn2_device_noalloc(self._h, d_q, nq, d_db, ndb, index_base, d_keys))
 
     def knn2_merge_device(self, d_parts, nparts, nq, ratio, d_d1=None, d_i1=None, d_d2=None, d_i2=None, d_pass=None):
         _ck(lib().orbx_knn2_merge_device(self._h, d_parts, nparts, nq, ratio, d_d1, d_i1, d_d2, d_i2, d_pass))
