@@ -21,8 +21,18 @@ CONFIGS = [
 ]
 
 
-def _compare_frame(gex, oex, img, lapping, f=0, got=None):
-    ok, od, omono = oex(img, lapping)
+POOL = {"kps": 0, "bad": 0}     # every keypoint compared in this session: the <= 0.1 % bound is also asserted pooled
+
+
+def _assert_pooled(nk, nbad, what):
+    """north_star: <= 0.1 % of descriptors may differ.  Per frame the test has to allow 1 (a frame has
+    ~1000 keypoints); over the pooled keypoints of a multi-frame test the bound is applied as stated, so
+    a systematic one-per-frame flip cannot hide."""
+    assert nbad <= 0.001 * nk, f"{what}: {nbad} of {nk} descriptors differ (> 0.1 %)"
+
+
+def _compare_frame(gex, oex, img, lapping, f=0, got=None, ref=None):
+    ok, od, omono = ref if ref is not None else oex(img, lapping)
     gk, gd, gmono = got
     assert len(gk) == len(ok), (len(gk), len(ok))
     assert gmono == omono
@@ -34,6 +44,7 @@ def _compare_frame(gex, oex, img, lapping, f=0, got=None):
     bits = np.unpackbits(gd ^ od, axis=1).sum(1)
     nbad = int((bits > 0).sum())
     assert nbad <= max(1, int(0.001 * len(gk))) and bits.max() <= 2, (nbad, bits.max())
+    POOL["kps"] += len(gk); POOL["bad"] += nbad
     return nbad
 
 
@@ -67,8 +78,8 @@ def test_lapping_area_and_batch(pkg, oracle, synth):
     gex = pkg.orbx.ORBextractor(1500, 1.2, 8, 20, 7, max_batch=B)
     oex = oracle.Extractor(1500, 1.2, 8, 20, 7)
     res = gex.extract_batch(imgs, laps)
-    for f in range(B):
-        _compare_frame(gex, oex, imgs[f], laps[f], got=res[f])
+    nbad = sum(_compare_frame(gex, oex, imgs[f], laps[f], got=res[f]) for f in range(B))
+    _assert_pooled(sum(len(r[0]) for r in res), nbad, "lapping batch")
     gex.close()
 
 
@@ -117,8 +128,8 @@ def test_many_frames_property(pkg, oracle, synth):
     r2 = gex.extract_batch(imgs)
     for f in range(B):
         assert np.array_equal(r1[f][0], r2[f][0]) and np.array_equal(r1[f][1], r2[f][1])
-    for f in range(0, B, 3):
-        _compare_frame(gex, oex, imgs[f], (0, 0), got=r1[f])
+    nbad = sum(_compare_frame(gex, oex, imgs[f], (0, 0), got=r1[f]) for f in range(B))
+    _assert_pooled(sum(len(r[0]) for r in r1), nbad, "24-frame batch")
     gex.close()
 
 
@@ -223,3 +234,42 @@ def test_parameter_sweep(pkg, oracle, synth, w, h, nf, scale, nl, ini, mn, seed)
         ox, oy, orr = oex.candidates(l)
         assert np.array_equal(gx, ox) and np.array_equal(gy, oy) and np.array_equal(gr, orr), f"candidates level {l}"
     gex.close()
+
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "cv2_extractor.npz")
+
+
+@pytest.mark.parametrize("name", ["euroc", "tumvi", "kitti"])
+def test_cuda_vs_cv2_composition_golden(pkg, synth, name):
+    """The CUDA extractor against the whole-extractor composition from cv2 primitives + a straight Python
+    quadtree (tests/cv2_compose.py, vectors by tools/gen_golden_extractor.py) -- no oracle in between."""
+    G = np.load(GOLDEN)
+    w, h, nf, l0, l1, seed = (int(v) for v in G[f"{name}_cfg"])
+    img = synth.textured_image(w, h, seed)
+    assert int(img.astype(np.int64).sum()) == int(G[f"{name}_imgsum"])
+    gex = pkg.orbx.ORBextractor(nf, 1.2, 8, 20, 7)
+    got = gex(img, (l0, l1))
+    nbad = _compare_frame(gex, None, img, (l0, l1), got=got, ref=(G[f"{name}_kps"], G[f"{name}_desc"], int(G[f"{name}_mono"])))
+    assert nbad <= 1
+    gex.close()
+
+
+def test_fuzz_parity_50(pkg, oracle):
+    """tools/fuzz_parity.py as a test: 50 random configurations (size, features, scale, levels,
+    thresholds, lapping, image kind) incl. pyramid, blurred levels and candidate lists."""
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
+    import fuzz_parity
+    rng = np.random.default_rng(2)
+    nk = nbad = 0
+    for it in range(50):
+        good, cfg, why, k, b = fuzz_parity.run_case(pkg, oracle, rng)
+        assert good, (it, cfg, why)
+        nk += k; nbad += b
+    _assert_pooled(nk, nbad, "fuzz")
+
+
+def test_pooled_descriptor_bound():
+    """Runs last in this file: the <= 0.1 % descriptor bound over every keypoint the tests above compared."""
+    if POOL["kps"] < 20000:
+        pytest.skip("run with the whole file to pool enough keypoints")
+    _assert_pooled(POOL["kps"], POOL["bad"], "all extractor tests")

@@ -67,3 +67,45 @@ def test_low_texture_retry_path(oracle, synth):
     got = np.stack([xs, ys, r], 1).astype(np.float32).reshape(-1, 3)
     assert len(ref) > 3 * max(len(ref20), 1) or len(ref20) == 0
     assert np.array_equal(got, ref)
+
+
+@pytest.mark.parametrize("w,h,nf,nl,ini,mn,lap,seed,faint", [
+    (640, 400, 800, 8, 20, 7, (0, 0), 41, False),
+    (400, 300, 500, 4, 20, 7, (120, 260), 42, True),       # low texture: per-cell minThFAST retry + lapping split
+    (333, 257, 400, 5, 12, 5, (0, 0), 43, False),          # odd sizes, other thresholds
+    (900, 260, 1500, 6, 20, 7, (0, 0), 44, False),         # wide: several initial quadtree nodes
+])
+def test_whole_extractor_vs_cv2_composition_live(oracle, synth, w, h, nf, nl, ini, mn, lap, seed, faint):
+    """the WHOLE extractor re-composed from cv2 primitives and a straight Python
+    quadtree with the real std::sort (tests/cv2_compose.py) equals the oracle bit for bit."""
+    import os, sys
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    import cv2_compose as cc
+    img = synth.textured_image(w, h, seed)
+    if faint:
+        img = (img.astype(np.float32) * 0.12 + 100).astype(np.uint8)
+    ck, cd, cmono = cc.extract(img, nf, 1.2, nl, ini, mn, lap)
+    ok, od, omono = oracle.Extractor(nf, 1.2, nl, ini, mn)(img, lap)
+    assert len(ck) == len(ok) > 50 and cmono == omono
+    for fld in ("x", "y", "size", "angle", "response", "octave", "class_id"):
+        assert np.array_equal(ck[fld], ok[fld]), fld
+    assert np.array_equal(cd, od)
+
+
+def test_python_quadtree_vs_oracle_quadtree(oracle):
+    """The straight Python DistributeOctTree against the oracle's on random tie-heavy candidate sets
+    (few distinct responses, clustered points: many equal (size, UL.x) nodes in the final phase)."""
+    import os, sys
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    import cv2_compose as cc
+    rng = np.random.default_rng(5)
+    for it in range(40):
+        W = int(rng.integers(100, 900)); H = int(rng.integers(80, 500)); N = int(rng.integers(5, 400))
+        n = int(rng.integers(1, 3000))
+        pts = np.unique(np.stack([rng.integers(0, W, n) // rng.integers(1, 4) * 1, rng.integers(0, H, n)], 1), axis=0)
+        pts = pts[rng.permutation(len(pts))]
+        resp = rng.integers(7, 12, len(pts))
+        sel = cc.distribute_octtree([(float(x), float(y), float(r)) for (x, y), r in zip(pts, resp)], 16, 16 + W, 16, 16 + H, N)
+        idx = oracle.distribute_octtree(pts[:, 0], pts[:, 1], resp, 16, 16 + W, 16, 16 + H, N)
+        got = [(int(x), int(y)) for x, y, _ in sel]
+        assert got == [tuple(int(v) for v in pts[i]) for i in idx], it

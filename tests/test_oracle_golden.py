@@ -87,3 +87,36 @@ def test_extractor_invariants(oracle, synth):
     key = lambda k: (k["x"], k["y"], k["octave"])
     a = sorted(zip(*key(kps))); b = sorted(zip(*key(k2)))
     assert a == b
+
+
+@pytest.fixture(scope="module")
+def GX(golden_dir):
+    return np.load(os.path.join(golden_dir, "cv2_extractor.npz"))
+
+
+@pytest.mark.parametrize("name", ["a", "b"])
+def test_ic_angle_matches_cv2_orb(oracle, GX, name):
+    """cv2.ORB_create(nlevels=1).detect() computes its keypoint angles with the same IC_Angle +
+    fastAtan2 as ORB-SLAM3: the oracle's ic_angle / umax must reproduce them exactly."""
+    img = GX[f"angle_{name}_img"]
+    b = oracle.border_reflect101(img, 19)
+    xya = GX[f"angle_{name}_xya"]
+    assert len(xya) > 300
+    got = np.array([oracle.ic_angle(b, 19, int(x), int(y)) for x, y, _ in xya], np.float32)
+    assert np.array_equal(got, xya[:, 2])
+
+
+@pytest.mark.parametrize("name", ["euroc", "tumvi", "kitti"])
+def test_whole_extractor_matches_cv2_composition(oracle, synth, GX, name):
+    """Oracle operator() == the cv2 + straight-Python-quadtree composition of the whole extractor
+    (tests/cv2_compose.py, vectors by tools/gen_golden_extractor.py) on BASELINE.json's image configs:
+    keypoints, order incl. the vLappingArea split, monoIndex, angles and descriptors, all bit-exact."""
+    w, h, nf, l0, l1, seed = (int(v) for v in GX[f"{name}_cfg"])
+    img = synth.textured_image(w, h, seed)
+    assert int(img.astype(np.int64).sum()) == int(GX[f"{name}_imgsum"])
+    k, d, mono = oracle.Extractor(nf, 1.2, 8, 20, 7)(img, (l0, l1))
+    gk = GX[f"{name}_kps"]
+    assert len(k) == len(gk) and mono == int(GX[f"{name}_mono"])
+    for fld in ("x", "y", "size", "angle", "response", "octave", "class_id"):
+        assert np.array_equal(k[fld], gk[fld]), fld
+    assert np.array_equal(d, GX[f"{name}_desc"])

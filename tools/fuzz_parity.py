@@ -5,13 +5,10 @@ import os, sys
 import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-import orbx_pkg
-pkg = orbx_pkg.load()
-from oracle import oracle as O
-N = int(sys.argv[1]) if len(sys.argv) > 1 else 30
-rng = np.random.default_rng(int(sys.argv[2]) if len(sys.argv) > 2 else 1)
-bad = 0
-for it in range(N):
+
+
+def run_case(pkg, O, rng):
+    """One random configuration; returns (good, cfg, why, keypoints compared, descriptors that differ)."""
     w = int(rng.integers(140, 1000)); h = int(rng.integers(120, 700))
     scale = float(rng.choice([1.1, 1.2, 1.25, 1.3, 1.5, 2.0]))
     nl = int(rng.integers(2, 11))
@@ -30,6 +27,7 @@ for it in range(N):
         img = (pkg.synth.textured_image(w, h, int(rng.integers(1 << 30))) // 8 + 100).astype(np.uint8)   # low contrast: minTh retry
     cfg = dict(w=w, h=h, nf=nf, scale=scale, nl=nl, ini=ini, mn=mn, lap=lap, kind=round(kind, 2))
     why = []
+    nk = nbad = 0
     try:
         gex = pkg.orbx.ORBextractor(nf, scale, nl, ini, mn)
         oex = O.Extractor(nf, scale, nl, ini, mn)
@@ -41,10 +39,11 @@ for it in range(N):
             for fld in ("x", "y", "size", "response", "octave"):
                 good &= bool(np.array_equal(gk[fld], ok[fld]))
             if len(gk):
-                da = np.abs(gk["angle"] - ok["angle"]); good &= bool(np.minimum(da, 360 - da).max() < 0.006)
-            if len(gk):
+                da = np.abs(gk["angle"] - ok["angle"]); good &= bool(np.minimum(da, 360 - da).max() <= np.degrees(1e-4))
                 bits = np.unpackbits(gd ^ od, axis=1).sum(1)
-                good &= bool((bits > 0).sum() <= max(1, len(gk) // 500) and bits.max() <= 2)
+                nk, nbad = len(gk), int((bits > 0).sum())
+                good &= bool(nbad <= max(1, len(gk) // 1000) and bits.max() <= 2)
+            if not good and not why: why.append("keypoint fields / angle / descriptors")
         for l in range(nl):
             lv = oex.level(l)
             t = bool(np.array_equal(gex.image_pyramid(l), lv)); good &= t
@@ -59,7 +58,19 @@ for it in range(N):
     except Exception as ex:       # noqa: BLE001
         good = False
         cfg["error"] = str(ex)[:200]
-    print("ok " if good else "BAD", len(gk) if good else "-", cfg, why, flush=True)
-    bad += not good
-print("failures:", bad, "of", N)
-sys.exit(1 if bad else 0)
+    return good, cfg, why, nk, nbad
+
+
+if __name__ == "__main__":
+    import orbx_pkg
+    pkg = orbx_pkg.load()
+    from oracle import oracle as O
+    N = int(sys.argv[1]) if len(sys.argv) > 1 else 30
+    rng = np.random.default_rng(int(sys.argv[2]) if len(sys.argv) > 2 else 1)
+    bad = 0
+    for it in range(N):
+        good, cfg, why, nk, nbad = run_case(pkg, O, rng)
+        print("ok " if good else "BAD", nk, cfg, why, flush=True)
+        bad += not good
+    print("failures:", bad, "of", N)
+    sys.exit(1 if bad else 0)
