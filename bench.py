@@ -26,9 +26,22 @@ sys.path.insert(0, ROOT)
 
 W, H, NFEAT, NLEVELS, SCALE, INI_TH, MIN_TH = 752, 480, 1000, 8, 1.2, 20, 7
 BATCH = 256                      # frames per launch per GPU (128 stereo pairs)
+TRAFFIC_FILE = "r1_traffic.json"   # ncu --set full capture the roofline's DRAM-traffic figure is read from (not measured in the run)
+# what each stage's kernel is limited by according to that capture (the HBM roofline is the contract's denominator)
+LIMITER = {"k_fast_units": "instruction issue + shared-memory occupancy", "k_resize_band": "instruction issue + bulk-copy wait",
+           "k_blur7": "instruction issue (DRAM ~50 % of peak)", "k_orient_describe": "DRAM sectors (2x over-fetch) + shared-memory gathers",
+           "k_octree": "dependent-step latency"}
 METRIC = "orb_frames_per_sec"
 UNIT = "frames/s"
 WORKLOAD = "euroc_752x480_nf1000_l8_sf1.2_fast20-7_batch256"
+
+
+def workload_config():
+    """The `config` object both arms print (identical by construction: it names the workload, not the run)."""
+    return {"workload": WORKLOAD, "image": f"{W}x{H} u8 synthetic textured", "nfeatures": NFEAT, "nlevels": NLEVELS,
+            "scale_factor": SCALE, "fast_thresholds": [INI_TH, MIN_TH], "frames_per_step_per_gpu": BATCH,
+            "l2_policy": "inputs larger than L2: 2 alternating 92 MB input batches + 360 MB pyramid working set per step",
+            "sharding": "independent frames per rank, no collective"}
 
 
 def level_sizes():
@@ -98,7 +111,7 @@ def make_frames(n, seed=0xB200):
     return synth.frame_batch(n, W, H, seed=seed, distinct=8)
 
 
-def cpu_baseline(nthreads, seconds_target=12.0):
+def cpu_baseline(nthreads, seconds_target=12.0, extended=False):
     """Times the CPU oracle (kind 'port') on a bounded sample of the same workload."""
     from oracle import oracle as O
     frames = make_frames(16)
@@ -107,10 +120,22 @@ def cpu_baseline(nthreads, seconds_target=12.0):
     iters = max(2, int(seconds_target / max(per_frame, 1e-3)))
     s, kps = O.bench_extract(frames, NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH, iters_per_thread=iters, nthreads=nthreads)
     n = iters * nthreads
-    return {"value": n / s, "unit": UNIT, "cores": nthreads, "kind": "port",
-            "sample": f"{n} EuRoC-shape frames ({iters}/thread x {nthreads} threads, frames-parallel), "
-                      f"single-thread latency {per_frame * 1e3:.1f} ms/frame",
-            "single_thread_fps": 1.0 / per_frame}
+    out = {"value": n / s, "unit": UNIT, "cores": nthreads, "kind": "port",
+           "sample": f"{n} EuRoC-shape frames ({iters}/thread x {nthreads} threads, frames-parallel), "
+                     f"single-thread latency {per_frame * 1e3:.1f} ms/frame",
+           "single_thread_fps": 1.0 / per_frame, "flags": "-O2 -ffp-contract=off (the parity build)"}
+    if extended:
+        # C1b (-O3 -march=native), C3 (cv2 SIMD composition), C4 (matcher loops), C5 (brute force)
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import cpu_baselines as cb
+        import orbx_pkg
+        synth = orbx_pkg.load().synth
+        params = (NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH)
+        out["extraction_o3_native"] = cb.oracle_o3_native(frames[:8], params, nthreads)
+        out["extraction_cv2_composition"] = cb.cv2_composition(frames[:4], params, nthreads)
+        out["matching"] = cb.matcher_loops(synth, nthreads)
+        out["knn2"] = cb.brute_force(synth, nthreads)
+    return out
 
 
 def single_frame_latency(pkg, local, frame):
@@ -221,6 +246,18 @@ def matching_bench(pkg, torch, local, ex, B):
     out["search_by_projection"] = {"problems_per_s": len(Fs) / dt, "matches_per_s": float(nm.sum()) / dt,
                                    "ms_per_call": dt * 1e3, "problems_per_call": len(Fs),
                                    "note": "through the C ABI with host buffers (packing + H2D + kernel + D2H)"}
+    # ---- ONE problem per call: the reference's call pattern (src/Tracking.cc:607,835,1115 call these one at a
+    # time from the tracking thread); wall clock per call through the C ABI, host buffers in and out
+    def lat(fn, reps=30):
+        for _ in range(3):
+            fn()
+        ts = []
+        for _ in range(reps):
+            t0 = time.perf_counter(); fn(); ts.append(time.perf_counter() - t0)
+        return float(np.median(ts) * 1e3)
+    P1 = dict(MPs[0]); P1["u"], P1["v"] = P1["x"], P1["y"]
+    one = {"search_by_projection_ms": lat(lambda: m.SearchByProjection(Fs[0], MPs[0], 3.0, False, 0.0, 0.8)),
+           "search_by_projection_kf_ms": lat(lambda: m.SearchByProjectionKF(Fs[0], P1, 15.0, True))}
     # ---- the widened matcher entry points, 32 problems per call through the C ABI
     def timed(fn, nprob, reps=5):
         fn()
@@ -247,8 +284,16 @@ def matching_bench(pkg, torch, local, ex, B):
     sets = [rng.integers(0, 256, (int(k), 32), dtype=np.uint8) for k in rng.integers(3, 40, 2000)]
     out["distinctive_descriptors"] = timed(lambda: m.ComputeDistinctiveDescriptors(sets), len(sets))
     out["search_by_bow"]["note"] = "all through the C ABI with host buffers; Python-side view construction included"
-    # ---- brute-force 2-NN: 16384 queries x 1M database rows, device resident
-    nq, ndb = 16384, 1 << 20
+    F12s, eps, sfs = [p[2] for p in kfp], [p[3] for p in kfp], [p[4] for p in kfp]
+    one["search_for_triangulation_ms"] = lat(lambda: m.SearchForTriangulation(kfp[0][0], kfp[0][1], F12s[0], eps[0], sfs[0], False, False, True))
+    one["search_by_bow_ms"] = lat(lambda: m.SearchByBoW(kfp[0][0], kfp[0][1], 0.7, True))
+    one["search_for_initialization_ms"] = lat(lambda: m.SearchForInitialization(ini[0][0], ini[0][1], 100, 0.9, True))
+    one["note"] = ("nprob = 1, median wall-clock ms per call incl. Python view construction, packing, H2D, kernel, D2H, sync; "
+                   "compare cpu_baseline.matching.*.ms_per_problem_1thread")
+    out["single_problem_latency"] = one
+    # ---- brute-force 2-NN kernel variants: 65536 queries x 1M database rows, device resident (the full
+    # config-5 shape, 1 M queries x 2 M rows per GPU, is the knn2_sharded leg)
+    nq, ndb = 65536, 1 << 20
     g = torch.Generator(device=dev); g.manual_seed(5)
     q = torch.randint(0, 256, (nq, 32), dtype=torch.uint8, device=dev, generator=g)
     db = torch.randint(0, 256, (ndb, 32), dtype=torch.uint8, device=dev, generator=g)
@@ -268,15 +313,125 @@ def matching_bench(pkg, torch, local, ex, B):
         t = e0.elapsed_time(e1) / 3
         knn["popc8" if variant == 0 else "csa_popc4"] = {"pairs_per_s": nq * ndb / (t * 1e-3), "ms": t}
     m.set_knn_variant(1)
-    best = max(v["pairs_per_s"] for v in knn.values())
-    # nominal POPC issue rate: 16 lanes/clk/SM (quarter rate) x 148 SMs x max SM clock
-    popc_peak = 16 * 148 * 1.965e9
-    knn.update({"queries": nq, "database_rows": ndb,
-                "popc32_per_s_equiv": best * 8, "frac_of_nominal_popc8_rate": best * 8 / popc_peak,
-                "note": "8 POPC32 per pair is the plain formulation; the carry-save variant issues 4, so its 8-POPC-equivalent rate can exceed the nominal POPC ceiling"})
+    # measured integer-pipe ceilings (tools/popc_peak.cu): POPC-only, LOP3-only and the executed mix
+    # (16 LOP3 + 4 POPC + 3 add + 1 compare per pair, rows from shared memory)
+    pk = popc_peak(pkg)
+    knn.update({"queries": nq, "database_rows": ndb, "int_pipe_peaks": pk})
+    if "popc32_per_s" in pk:
+        csa, p8 = knn["csa_popc4"]["pairs_per_s"], knn["popc8"]["pairs_per_s"]
+        knn["roofline"] = {"bound": "integer pipe (POPC + LOP3 issue)", "formulation": "csa_popc4: 16 LOP3 + 4 POPC per pair",
+                           "achieved_pairs_per_s": csa, "peak_pairs_per_s": pk["knn_mix_pairs_per_s"],
+                           "frac_of_measured_mix_peak": csa / pk["knn_mix_pairs_per_s"],
+                           "popc_per_s_executed": csa * 4, "frac_of_measured_popc_peak": csa * 4 / pk["popc32_per_s"],
+                           "popc8_variant_frac_of_measured_popc_peak": p8 * 8 / pk["popc32_per_s"]}
     out["knn2"] = knn
     m.close()
     return out
+
+
+def popc_peak(pkg):
+    """Measured POPC / LOP3 / 2-NN-mix ceilings of this GPU: tools/popc_peak.cu, built beside liborbx.so."""
+    import subprocess
+    exe = os.path.join(os.path.dirname(pkg.orbx.build()), "popc_peak")
+    try:
+        r = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+        return json.loads(r.stdout.strip().splitlines()[-1])
+    except Exception as ex:     # noqa: BLE001
+        return {"unavailable": str(ex)[:160]}
+
+
+KNN_NQ, KNN_SHARD_ROWS = 1 << 20, 1 << 21       # BASELINE.json configs[4]: 1 M queries, 16 M rows over 8 GPUs = 2 M rows per rank
+
+
+def knn2_sharded_bench(pkg, torch, dist, rank, world, local):
+    """BASELINE.json configs[4]: brute-force 2-NN of 1 M queries against a database sharded over the
+    ranks (2 M rows per rank: 16 M rows at 8 GPUs), local search -> NCCL all-gather of the packed
+    top-2 keys (16 B per query per rank) -> merge + ratio test.  Every rank calls this; device-timed
+    on the matcher's stream (local search, merge) and torch's stream (all-gather), max over ranks."""
+    ox = pkg.orbx
+    dev = torch.device("cuda", local)
+    nq, rows = KNN_NQ, KNN_SHARD_ROWS
+    base = rank * rows
+    g = torch.Generator(device=dev); g.manual_seed(5)
+    q = torch.randint(0, 256, (nq, 32), dtype=torch.uint8, device=dev, generator=g)        # same on every rank
+    gd = torch.Generator(device=dev); gd.manual_seed(500 + rank)
+    db = torch.randint(0, 256, (rows, 32), dtype=torch.uint8, device=dev, generator=gd)
+    # planted neighbours: query k*1024 is database row (k * 7919) % rows of rank k % world, a few bits flipped
+    nplant = 64
+    plant = []
+    for k in range(nplant):
+        r_, row = k % world, (k * 7919) % rows
+        plant.append((k * 1024, r_, row))
+    own = torch.zeros((nplant, 32), dtype=torch.uint8, device=dev)
+    for j, (qi, r_, row) in enumerate(plant):
+        if r_ == rank:
+            own[j] = db[row]
+    if dist is not None:
+        dist.all_reduce(own, op=dist.ReduceOp.SUM)       # one rank contributes each row
+    own[:, 0] ^= 0x05                                     # 2 bits flipped: distance 2 to the planted row
+    for j, (qi, r_, row) in enumerate(plant):
+        q[qi] = own[j]
+    m = ox.ORBmatcher(local)
+    ms_ = torch.cuda.ExternalStream(m.stream(), device=dev)
+    cur = torch.cuda.current_stream(dev)
+    keys = torch.empty((nq, 2), dtype=torch.int64, device=dev)
+    parts = torch.empty((world, nq, 2), dtype=torch.int64, device=dev) if world > 1 else keys
+    out = [torch.empty(nq, dtype=torch.int32, device=dev) for _ in range(4)]
+    ps = torch.empty(nq, dtype=torch.uint8, device=dev)
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+
+    def run(n):
+        ms_.wait_stream(cur)
+        ev[0].record(ms_)
+        m.knn2_device(q.data_ptr(), n, db.data_ptr(), rows, base, keys.data_ptr())
+        ev[1].record(ms_)
+        if world > 1:
+            cur.wait_stream(ms_)
+            dist.all_gather_into_tensor(parts, keys)
+            ev[2].record(cur)
+            ms_.wait_stream(cur)
+        else:
+            ev[2].record(ms_)
+        m.knn2_merge_device(parts.data_ptr(), world, n, 0.8, out[0].data_ptr(), out[1].data_ptr(), out[2].data_ptr(),
+                            out[3].data_ptr(), ps.data_ptr())
+        ev[3].record(ms_)
+        cur.wait_stream(ms_)
+
+    run(nq)                               # warm-up at full size (NCCL channels, kernel load)
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize()
+    run(nq)
+    torch.cuda.synchronize()
+    t = torch.tensor([ev[0].elapsed_time(ev[3]), ev[0].elapsed_time(ev[1]), ev[1].elapsed_time(ev[2]), ev[2].elapsed_time(ev[3])],
+                     device=dev, dtype=torch.float64)
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total, search, gather, merge = (float(v) for v in t)
+    # correctness spot checks: planted neighbours found with their GLOBAL index, 16 queries exhaustively on this rank's shard
+    d1, i1, d2 = out[0].cpu().numpy(), out[1].cpu().numpy(), out[2].cpu().numpy()
+    ok_plant = all(d1[qi] <= 2 and (d1[qi] < 2 or i1[qi] == r_ * rows + row) for qi, r_, row in plant)
+    ok_local = True
+    for k in range(1, nq, nq // 16):
+        dd = (q[k][None] ^ db).to(torch.int16)            # popcount through a byte table
+        tab = torch.tensor([bin(v).count("1") for v in range(256)], dtype=torch.int16, device=dev)
+        dist_k = tab[dd.long()].sum(1)
+        ok_local &= bool(int(dist_k.min()) >= int(d1[k]))     # nothing on this shard beats the merged best
+        if world == 1:
+            srt = torch.sort(dist_k.to(torch.int32) * (1 << 22) + torch.arange(rows, device=dev, dtype=torch.int32) % (1 << 22))[0][:2]
+            ok_local &= bool(int(srt[0]) >> 22 == int(d1[k]) and int(srt[1]) >> 22 == int(d2[k]))
+    flags = torch.tensor([int(ok_plant), int(ok_local)], device=dev)
+    if dist is not None:
+        dist.all_reduce(flags, op=dist.ReduceOp.MIN)
+    m.close()
+    pairs = float(nq) * rows * world
+    return {"queries": nq, "database_rows": rows * world, "rows_per_rank": rows, "ranks": world,
+            "pairs_per_s": pairs / (total * 1e-3), "ms_total": total, "ms_local_search": search,
+            "ms_all_gather": gather, "all_gather_bytes_per_rank": 16 * nq if world > 1 else 0, "ms_merge": merge,
+            "ratio_pass_fraction": float(ps.float().mean()), "planted_found": bool(flags[0]), "exhaustive_spot_check": bool(flags[1]),
+            "bound": "the popcount loop (local search) - the all-gather moves 16 B per query per rank",
+            "note": "device-resident; database generated on the device (uniform bits, seed 500 + rank), queries seed 5 with 64 planted near-duplicates"}
 
 
 def other_shapes_bench(pkg, torch, local):
@@ -323,11 +478,15 @@ def run_reference(args):
         vals.append(base["value"])
     v = float(np.mean(vals[args.warmup:]))
     base["value"] = v
+    if args.steps >= 2:          # the driver's run: the matching-side CPU numbers ride along once
+        base.update({k: v_ for k, v_ in cpu_baseline(ncores, seconds_target=1.0, extended=True).items()
+                     if k in ("extraction_o3_native", "extraction_cv2_composition", "matching", "knn2")})
     line = {"metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": None, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
             "data": "synthetic", "impl": "reference",
-            "config": {"workload": WORKLOAD, "note": "CPU oracle (port of the reference semantics) on all host cores; "
-                       "the reference's own path needs OpenCV-CUDA and cannot be built in this image"},
+            "config": workload_config(),
+            "run": {"note": "CPU oracle (port of the reference semantics) on all host cores, each step a bounded sample of the "
+                            "workload (cpu_baseline.sample); the reference's own path needs OpenCV-CUDA and cannot be built in this image"},
             "cpu_baseline": base,
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -466,11 +625,72 @@ def main():
     e2e_wall_ms = (time.perf_counter() - t0) * 1e3
     clocks = sampler.result()
     n_kp, _ = ex.counts(B)
+    # ---- copy-only ceiling of the same end-to-end pattern: the same pinned buffers, the same three streams,
+    # H2D of the frames and D2H of keypoints + descriptors, NO kernels (what the host side of the box can deliver)
+    d2h_bytes = int(B * ex.capacity * (28 + 32) + 8 * B)
+    cstreams = [torch.cuda.ExternalStream(x.stream(), device=torch.device("cuda", local)) for x in exs]
+    din = [torch.empty(B * H * W, dtype=torch.uint8, device=f"cuda:{local}") for _ in range(NH)]
+    dout = [torch.empty(d2h_bytes, dtype=torch.uint8, device=f"cuda:{local}") for _ in range(NH)]
+    hin = [torch.from_numpy(p.array.reshape(-1)) for p in pin]
+    hout = [torch.empty(d2h_bytes, dtype=torch.uint8).pin_memory() for _ in range(NH)]
+
+    def copy_step(i):
+        k = i % NH
+        with torch.cuda.stream(cstreams[k]):
+            din[k].copy_(hin[k], non_blocking=True)
+            hout[k].copy_(dout[k], non_blocking=True)
+        if i >= NH - 1:
+            cstreams[(i - (NH - 1)) % NH].synchronize()
+    for i in range(NH):
+        copy_step(i)
+    torch.cuda.synchronize()
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        copy_step(i)
+    torch.cuda.synchronize()
+    copy_wall_ms = (time.perf_counter() - t0) * 1e3
+    barrier()
+    del din, dout, hout
+    # ---- BASELINE.json configs[1] end to end: host L+R frames in -> extract both -> ComputeStereoMatches ->
+    # keypoints + descriptors + mvuRight/mvDepth out, copies in the timed region; frames (2p, 2p+1) = a pair
+    sp = [pkg.synth.stereo_pair(W, H, 0xB200 + 31 * rank + i) for i in range(4)]
+    sbase = np.stack([im for pr in sp for im in pr])
+    spin = [orbx.PinnedBuffer((B, H, W)) for _ in range(NH)]
+    for k in range(NH):
+        for i in range(B):
+            spin[k].array[i] = sbase[(i + 2 * k) % 8]
+    lf = np.arange(0, B, 2); rf = lf + 1
+
+    def stereo_step(i):
+        k = i % NH
+        exs[k].extract_host(spin[k].array)
+        orbx.stereo_matches_async(exs[k], exs[k], lf, rf, 435.2 * 0.11, 0.11)
+        if i >= NH - 1:
+            j = (i - (NH - 1)) % NH
+            exs[j].sync(); orbx.stereo_fetch(exs[j], len(lf))
+    for i in range(NH):
+        stereo_step(i)
+    for i in range(max(NH - (NH - 1), 0), NH):
+        exs[i % NH].sync(); orbx.stereo_fetch(exs[i % NH], len(lf))
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        stereo_step(i)
+    for i in range(max(args.steps - (NH - 1), 0), args.steps):
+        exs[i % NH].sync(); orbx.stereo_fetch(exs[i % NH], len(lf))
+    torch.cuda.synchronize()
+    stereo_wall_ms = (time.perf_counter() - t0) * 1e3
+    barrier()
+    del spin
+    knn_sharded = None
+    if not args.no_matching:
+        knn_sharded = knn2_sharded_bench(pkg, torch, dist, rank, world, local)
 
     if dist is not None:
-        t = torch.tensor([ms, e2e_wall_ms], device=f"cuda:{local}", dtype=torch.float64)
+        t = torch.tensor([ms, e2e_wall_ms, copy_wall_ms, stereo_wall_ms], device=f"cuda:{local}", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms, e2e_wall_ms = float(t[0]), float(t[1])
+        ms, e2e_wall_ms, copy_wall_ms, stereo_wall_ms = (float(v) for v in t)
     total_frames = B * args.steps * world
     value = total_frames / (ms * 1e-3)
     e2e_value = total_frames / (e2e_wall_ms * 1e-3)
@@ -495,7 +715,7 @@ def main():
                 "blur": "k_blur7", "describe": "k_orient_describe"}[names[dom]]
         traffic = None          # DRAM bytes per launch of the dominant kernel, from the committed ncu --set full capture
         try:
-            tr = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))["kernels"][kern]
+            tr = json.load(open(os.path.join(ROOT, "profiles", TRAFFIC_FILE)))["kernels"][kern]
             traffic = int(tr["dram_bytes"] * B / 256)    # every launch of the kernel in ONE step (the capture holds one step)
         except Exception:
             pass
@@ -503,19 +723,24 @@ def main():
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u8", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "frames_per_step_per_gpu": B, "keypoints_per_frame": float(np.mean(n_kp)),
-                       "l2_policy": "inputs larger than L2: 2 alternating 92 MB input batches + 360 MB pyramid working set per step",
-                       "e2e_batches_in_flight": NH,
-                       "internal_streams": ex.streams(B),
-                       "sharding": "independent frames per rank, no collective",
-                       "numa": None if numa is None else {"node": numa[0], "cpus": numa[1]}},
+            "config": dict(workload_config(), frames_per_step_per_gpu=B),
+            "run": {"keypoints_per_frame": float(np.mean(n_kp)), "e2e_batches_in_flight": NH, "internal_streams": ex.streams(B),
+                    "numa": None if numa is None else {"node": numa[0], "cpus": numa[1]}},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(B * W * H),
-                    "d2h_bytes_per_step": int(B * ex.capacity * (28 + 32) + 8 * B), "ms_per_step": e2e_wall_ms / args.steps,
-                    "device_ms_per_step": e2e_ms / args.steps},
+                    "d2h_bytes_per_step": d2h_bytes, "ms_per_step": e2e_wall_ms / args.steps,
+                    "device_ms_per_step": e2e_ms / args.steps,
+                    "copy_only": {"value": total_frames / (copy_wall_ms * 1e-3), "unit": UNIT, "ms_per_step": copy_wall_ms / args.steps,
+                                  "h2d_gb_per_s_all_ranks": total_frames * W * H / (copy_wall_ms * 1e-3) / 1e9,
+                                  "frac_of_copy_ceiling": (total_frames / (e2e_wall_ms * 1e-3)) / (total_frames / (copy_wall_ms * 1e-3)),
+                                  "note": "the same pinned buffers and streams, H2D + D2H only, no kernels: what the host side of this box delivers"},
+                    "stereo_pairs": {"value": (total_frames / 2) / (stereo_wall_ms * 1e-3), "unit": "stereo pairs/s", "ms_per_step": stereo_wall_ms / args.steps,
+                                     "pairs_per_step_per_gpu": B // 2,
+                                     "note": "BASELINE.json configs[1]: host L+R frames -> extract both -> ComputeStereoMatches -> keypoints, descriptors, "
+                                             "mvuRight, mvDepth on the host; H2D/D2H inside the timed region"}},
             "gpu_launches": int(launches),
             "clocks": clocks,
-            "roofline": {"bound": "hbm", "kernel": kern, "stage": names[dom], "achieved": dom_gbs, "peak": hbm_peak, "unit": "GB/s",
-                         "frac": round(dom_gbs / hbm_peak, 4), "traffic": traffic,
+            "roofline": {"bound": "hbm", "limiter_measured": LIMITER.get(kern, "issue"), "kernel": kern, "stage": names[dom], "achieved": dom_gbs, "peak": hbm_peak, "unit": "GB/s",
+                         "frac": round(dom_gbs / hbm_peak, 4), "traffic": traffic, "traffic_source": TRAFFIC_FILE if traffic else None,
                          "algorithmic_bytes_per_launch": int(alg[names[dom]] * B), "launch_ms": round(float(stage[dom]), 4),
                          "launch_scope": "all launches of the stage for one 256-frame step on one stream (FAST: 2 grids, short and tall strips)",
                          "peak_source": "measured" if peaks else "fallback"},
@@ -523,13 +748,14 @@ def main():
         }
         if not args.no_matching:
             line["matching"] = matching_bench(pkg, torch, local, ex, B)
+            line["matching"]["knn2_sharded"] = knn_sharded
             line["other_shapes"] = other_shapes_bench(pkg, torch, local)
             line["single_frame_latency"] = single_frame_latency(pkg, local, frames[0])
             line["cpp_operator_latency"] = cpp_operator_latency(pkg, frames[0])
         if numa is not None:
             os.sched_setaffinity(0, numa[2])          # the CPU baseline gets every core back
         if not args.no_cpu_baseline and world == 1:
-            line["cpu_baseline"] = cpu_baseline(os.cpu_count() or 1)
+            line["cpu_baseline"] = cpu_baseline(os.cpu_count() or 1, extended=not args.no_matching)
         print(json.dumps(line))
     if dist is not None:
         dist.barrier()
