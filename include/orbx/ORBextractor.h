@@ -7,6 +7,9 @@
  *   int operator()(image, mask, keypoints, descriptors, vLappingArea)   -> monoIndex, -1 on empty
  *   GetLevels / GetScaleFactor / GetScaleFactors / GetInverseScaleFactors /
  *   GetScaleSigmaSquares / GetInverseScaleSigmaSquares, mvImagePyramid
+ *   ComputeStereoMatches(left, right, mbf, mb, mvuRight, mvDepth)        (upstream Frame::ComputeStereoMatches)
+ * mvImagePyramid[level] is a Mat-like ROI view (data / step / cols / rows / rowRange / colRange / ptr / at;
+ * a real cv::Mat with ORBX_WITH_OPENCV) into a host copy of the bordered level, downloaded on first access.
  * Header-only.  With ORBX_WITH_OPENCV the cv::Mat / cv::KeyPoint signature is provided; without
  * it (this image has no OpenCV C++) the same calls take the POD views below, whose memory layout
  * equals cv::KeyPoint (28 bytes) and a continuous CV_8UC1 matrix.
@@ -14,6 +17,7 @@
  */
 #ifndef ORBX_ORBEXTRACTOR_H
 #define ORBX_ORBEXTRACTOR_H
+#include <cstddef>
 #include <cstdint>
 #include <cstring>
 #include <stdexcept>
@@ -39,7 +43,7 @@ class ORBextractor {
 public:
     ORBextractor(int nfeatures, float scaleFactor, int nlevels, int iniThFAST, int minThFAST, int device = 0)
         : nfeatures_(nfeatures), scaleFactor_(scaleFactor), nlevels_(nlevels), iniThFAST_(iniThFAST),
-          minThFAST_(minThFAST), device_(device) {}
+          minThFAST_(minThFAST), device_(device) { mvImagePyramid.owner_ = this; }
     ~ORBextractor() { if (h_) orbx_extractor_destroy(h_); }
     ORBextractor(const ORBextractor&) = delete;
     ORBextractor& operator=(const ORBextractor&) = delete;
@@ -91,19 +95,40 @@ public:
     std::vector<float> inline GetScaleSigmaSquares() { tables(); return mvLevelSigma2; }
     std::vector<float> inline GetInverseScaleSigmaSquares() { tables(); return mvInvLevelSigma2; }
 
-    /* mvImagePyramid[level]: host copy of the bordered (w+38)x(h+38) level; the ROI starts at
-     * (19,19), as upstream's Mat views into their bordered buffers.  Downloaded lazily. */
-    struct Level { int w = 0, h = 0; std::vector<uint8_t> bordered; const uint8_t* roi() const { return bordered.data() + 19 * (w + 38) + 19; } };
-    const Level& ImagePyramid(int level) {
-        Level& L = mvImagePyramid.at(level);
-        if (L.bordered.empty()) {
-            check(orbx_extractor_level_size(h_, level, &L.w, &L.h));
-            L.bordered.resize((size_t)(L.w + 38) * (L.h + 38));
-            check(orbx_extractor_level_download(h_, 0, level, L.bordered.data()));
+    /* One pyramid level as upstream exposes it (include/ORBextractor.h:94, ComputePyramid src/ORBextractor.cc:607-623):
+     * a w x h ROI at (19,19) of a bordered (w+38) x (h+38) buffer, so data[-19 * step - 19] is valid. */
+    struct Level {
+        const uint8_t* data = nullptr;     /* ROI pixel (0,0) */
+        int cols = 0, rows = 0;
+        size_t step = 0;                   /* bytes per row of the bordered buffer */
+        bool empty() const { return !data; }
+        const uint8_t* ptr(int y) const { return data + (ptrdiff_t)y * (ptrdiff_t)step; }
+        uint8_t at(int y, int x) const { return ptr(y)[x]; }
+        Level rowRange(int y0, int y1) const { Level r = *this; r.data = ptr(y0); r.rows = y1 - y0; return r; }
+        Level colRange(int x0, int x1) const { Level r = *this; r.data = data + x0; r.cols = x1 - x0; return r; }
+        operator ImageView() const { return ImageView{data, cols, rows, step}; }
+    };
+    /* std::vector<cv::Mat>-like access with lazy download: mvImagePyramid[l], .at(l), .size() */
+    class Pyramid {
+    public:
+#ifdef ORBX_WITH_OPENCV
+        typedef cv::Mat value_type;
+#else
+        typedef Level value_type;
+#endif
+        size_t size() const { return owner_ ? (size_t)owner_->nlevels_ : 0; }
+        const value_type& operator[](size_t level) const { return owner_->pyramid_level((int)level); }
+        const value_type& at(size_t level) const {
+            if (level >= size()) throw std::out_of_range("mvImagePyramid");
+            return (*this)[level];
         }
-        return L;
-    }
-    std::vector<Level> mvImagePyramid;
+    private:
+        friend class ORBextractor;
+        ORBextractor* owner_ = nullptr;
+    };
+    Pyramid mvImagePyramid;
+    /* POD view of a level regardless of ORBX_WITH_OPENCV */
+    const Level& ImagePyramid(int level) { pyramid_level(level); return lv_.at(level).view; }
     std::vector<float> mvScaleFactor, mvInvScaleFactor, mvLevelSigma2, mvInvLevelSigma2;
     std::vector<int> mnFeaturesPerLevel, umax;
 
@@ -136,13 +161,61 @@ private:
                                     mvInvLevelSigma2.data(), mnFeaturesPerLevel.data(), umax.data()));
         tables_ok_ = true;
     }
-    void refresh_pyramid_views() { mvImagePyramid.assign(nlevels_, Level{}); }
+    struct LevelBuf {
+        std::vector<uint8_t> bordered;
+        Level view;
+#ifdef ORBX_WITH_OPENCV
+        cv::Mat mat;
+#endif
+    };
+    void refresh_pyramid_views() { lv_.assign(nlevels_, LevelBuf{}); }
+    const Pyramid::value_type& pyramid_level(int level) {
+        if (lv_.size() != (size_t)nlevels_) lv_.assign(nlevels_, LevelBuf{});
+        LevelBuf& L = lv_.at(level);
+        if (L.bordered.empty()) {
+            if (!h_) throw std::runtime_error("orbx: mvImagePyramid read before the first operator() call");
+            int w = 0, h = 0;
+            check(orbx_extractor_level_size(h_, level, &w, &h));
+            L.bordered.resize((size_t)(w + 38) * (h + 38));
+            check(orbx_extractor_level_download(h_, 0, level, L.bordered.data()));
+            L.view.cols = w; L.view.rows = h; L.view.step = (size_t)(w + 38);
+            L.view.data = L.bordered.data() + 19 * (size_t)(w + 38) + 19;
+#ifdef ORBX_WITH_OPENCV
+            L.mat = cv::Mat(h + 38, w + 38, CV_8UC1, L.bordered.data(), (size_t)(w + 38))(cv::Rect(19, 19, w, h));
+#endif
+        }
+#ifdef ORBX_WITH_OPENCV
+        return L.mat;
+#else
+        return L.view;
+#endif
+    }
+    std::vector<LevelBuf> lv_;
 
     int nfeatures_; float scaleFactor_; int nlevels_, iniThFAST_, minThFAST_, device_;
     orbx_extractor* h_ = nullptr;
     int w_ = 0, hgt_ = 0;
     bool tables_ok_ = false;
 };
+
+/* Frame::ComputeStereoMatches of upstream ORB-SLAM3 v1.0 (absent from the fork: /root/reference include/Frame.h:53-62;
+ * semantics SURVEY.md App. A5) for the frame each extractor processed last: row-band search + SAD refinement on the
+ * device-resident keypoints / descriptors / pyramids of `left` and `right` (the two extractor instances upstream runs on
+ * two threads).  mvuRight / mvDepth get one entry per left keypoint (-1 where there is no match), as Frame's members. */
+inline void ComputeStereoMatches(ORBextractor& left, ORBextractor& right, float mbf, float mb, std::vector<float>& mvuRight,
+                                 std::vector<float>& mvDepth) {
+    if (!left.handle() || !right.handle()) throw std::runtime_error("orbx: ComputeStereoMatches before operator()");
+    const int cap = orbx_extractor_capacity(left.handle());
+    mvuRight.assign(cap, -1.f);
+    mvDepth.assign(cap, -1.f);
+    const int zero = 0;
+    if (orbx_stereo_matches(left.handle(), right.handle(), 1, &zero, &zero, mbf, mb, mvuRight.data(), mvDepth.data(), cap) != ORBX_OK)
+        throw std::runtime_error(std::string("orbx: ") + orbx_last_error());
+    int n = 0;
+    if (orbx_extractor_counts(left.handle(), &n, nullptr) != ORBX_OK) throw std::runtime_error(std::string("orbx: ") + orbx_last_error());
+    mvuRight.resize(n);
+    mvDepth.resize(n);
+}
 
 }  // namespace ORB_SLAM3
 #endif

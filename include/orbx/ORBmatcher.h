@@ -8,6 +8,8 @@
  */
 #ifndef ORBX_ORBMATCHER_H
 #define ORBX_ORBMATCHER_H
+#include <cstdint>
+#include <cstring>
 #include <stdexcept>
 #include <string>
 #include <utility>
@@ -26,12 +28,22 @@ public:
     ORBmatcher(const ORBmatcher&) = delete;
     ORBmatcher& operator=(const ORBmatcher&) = delete;
 
-    /* src/ORBmatcher.cc:1375-1391 -- one pair; use orbx_hamming_pairs for bulk */
+    /* src/ORBmatcher.cc:1375-1391 -- ONE pair of 32-byte descriptors, computed inline with the same eight 32-bit
+     * popcounts: the reference calls this inside host loops (src/MapPoint.cc:391, LoopClosing, Sim3Solver), where a GPU
+     * round trip per pair (staging, H2D, launch, D2H, sync: ~20 us) would be ~1e4 x slower than the 8 words of work.
+     * It is an ABI helper for such call sites, not a fallback of a search: bulk distances go through
+     * orbx_hamming_pairs / BulkDescriptorDistance and every search through its kernel. */
     static int DescriptorDistance(const uint8_t* a, const uint8_t* b) {
         int d = 0;
-        check(orbx_hamming_pairs(a, b, 1, &d));
+        for (int i = 0; i < 8; ++i) {
+            uint32_t x, y;
+            memcpy(&x, a + 4 * i, 4); memcpy(&y, b + 4 * i, 4);
+            d += __builtin_popcount(x ^ y);
+        }
         return d;
     }
+    /* n pairs on the GPU (k_hamming_pairs) */
+    static void BulkDescriptorDistance(const uint8_t* a, const uint8_t* b, int n, int* out) { check(orbx_hamming_pairs(a, b, n, out)); }
     /* src/ORBmatcher.cc:31-123; match_mp[i] = map point assigned to frame keypoint i or -1 */
     int SearchByProjection(const orbx_frame_view& F, const orbx_mappoints& MP, const uint8_t* claimed, float th,
                            bool bFarPoints, float thFarPoints, float nnRatio, std::vector<int>& match_mp) {

@@ -24,11 +24,13 @@ int main(int argc, char** argv) {
         const auto& L1 = ex.ImagePyramid(1);
         const int d01 = kps.size() > 1 ? ORB_SLAM3::ORBmatcher::DescriptorDistance(&desc[0], &desc[32]) : -1;
         FILE* o = fopen(argv[5], "wb");
-        int hdr[6] = {(int)kps.size(), mono, L1.w, L1.h, d01, (int)sf.size()};
+        int hdr[6] = {(int)kps.size(), mono, L1.cols, L1.rows, d01, (int)sf.size()};
         fwrite(hdr, sizeof(int), 6, o);
         fwrite(kps.data(), sizeof(orbx_keypoint), kps.size(), o);
         fwrite(desc.data(), 1, desc.size(), o);
-        fwrite(L1.bordered.data(), 1, L1.bordered.size(), o);
+        /* the ROI view sits at (19,19) of the bordered (w+38) x (h+38) buffer, as upstream's mvImagePyramid[l] */
+        fwrite(L1.data - 19 * (ptrdiff_t)L1.step - 19, 1, (size_t)(L1.cols + 38) * (L1.rows + 38), o);
+        if (ex.mvImagePyramid.size() != 8 || ex.mvImagePyramid[1].rowRange(2, 5).colRange(3, 9).at(0, 0) != L1.at(2, 3)) return 5;
         fclose(o);
         ORB_SLAM3::ImageView none;
         if (ex(none, none, kps, desc, lap) != -1) return 4;    // empty image -> -1

@@ -83,3 +83,14 @@ def test_octree_sort_closed_form_matches_std_sort(tmp_path):
                            os.path.join(ROOT, "tests", "cpp", "test_parallel_partition.cpp")])
     r = subprocess.run([exe, "20000"], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0 and r.stdout.startswith("OK"), r.stdout + r.stderr
+
+
+def test_reference_signature_layer_and_opencv_overload_compile(so, tmp_path):
+    """include/orbx/ORBmatcher_ref.h (the reference's static ORBmatcher signatures as templates, instantiated with the
+    mock SLAM types) and the ORBX_WITH_OPENCV overload of ORBextractor (against tests/cpp/opencv_stub) compile
+    warning-free; they are RUN by tests/test_gpu_cpp_api.py on the GPU."""
+    cpp = os.path.join(ROOT, "tests", "cpp")
+    link = ["-L" + os.path.dirname(so), "-lorbx", "-Wl,-rpath," + os.path.dirname(so)]
+    subprocess.check_call(["g++", "-std=c++17", "-O1", "-Wall", "-Werror", "-o", str(tmp_path / "a"), os.path.join(cpp, "test_ref_api.cpp")] + link)
+    subprocess.check_call(["g++", "-std=c++17", "-O1", "-Wall", "-Werror", "-DORBX_WITH_OPENCV", "-I" + os.path.join(cpp, "opencv_stub"), "-pthread",
+                           "-o", str(tmp_path / "b"), os.path.join(cpp, "test_shim_opencv.cpp")] + link)
