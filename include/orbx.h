@@ -228,6 +228,12 @@ orbx_status orbx_search_for_initialization(orbx_matcher* m, int nprob, const orb
 orbx_status orbx_distinctive_descriptors(orbx_matcher* m, int nsets, const int* set_off, const uint8_t* desc,
                                          int* best, int* median);
 
+/* DBoW2 FORB::meanValue   Thirdparty/DBoW2/src/DBoW2/FORB.cpp:28-79, batched over nsets descriptor sets (same CSR
+ * layout as above): mean[s*32 .. s*32+32) = the per-bit majority descriptor of set s (bit set iff at least
+ * N/2 + N%2 of its N descriptors have it; N == 1: the descriptor itself; N == 0: 32 zero bytes, where the reference
+ * releases the Mat).  (FORB::distance, FORB.cpp:81-101, is orbx_hamming_pairs.) */
+orbx_status orbx_mean_value(orbx_matcher* m, int nsets, const int* set_off, const uint8_t* desc, uint8_t* mean);
+
 /* Frame::AssignFeaturesToGrid + PosInGrid   src/Frame.cc:157-176, 470-480, for nframes frames:
  * cell_off[p][gcols*grows + 1] / cell_idx[p][F[p].n] = CSR over the cells in the reference's linear
  * order (y*cols + x), keypoints in push_back order inside a cell; the unused tail of cell_idx
@@ -278,6 +284,24 @@ orbx_status orbx_search_by_projection_kf(orbx_matcher* m, int nprob, const orbx_
                                          const orbx_kf_points* MP, const uint8_t* const* occupied,
                                          float th, int checkOrientation, int* const* match_mp,
                                          int* nmatches);
+
+/* Device-resident forms of the two searches above, for the frames an extractor has just processed (no host round trip
+ * of the Frame side, no host synchronisation between extraction and search): problem p searches frame frames[p] of
+ * e's last batch -- mvKeysUn == the extracted keypoints (rectified / distortion-free camera), mDescriptors and
+ * mNumKeypoints are read in place from e's device buffers; stereo_pairs[p] >= 0 (may be NULL = mono) names the pair of
+ * e's last orbx_stereo_matches_async call whose mvuRight the stereo gate of :81-86 reads.  Of `grid` only the grid
+ * constants (minx .. grows), scale and nlevels are read.  claimed[p] / occupied[p] / match_mp[p] hold
+ * orbx_extractor_capacity(e) entries (entries beyond the frame's keypoint count come back as -1).  The matcher's
+ * stream waits for e's stream through an event; the call returns with the results on the host. */
+orbx_status orbx_search_by_projection_resident(orbx_matcher* m, orbx_extractor* e, int nprob, const int* frames,
+                                               const int* stereo_pairs, const orbx_frame_view* grid,
+                                               const orbx_mappoints* MP, const uint8_t* const* claimed, float th,
+                                               int bFarPoints, float thFarPoints, float nnRatio, int* const* match_mp,
+                                               int* nmatches);
+orbx_status orbx_search_by_projection_kf_resident(orbx_matcher* m, orbx_extractor* e, int nprob, const int* frames,
+                                                  const orbx_frame_view* grid, const orbx_kf_points* MP,
+                                                  const uint8_t* const* occupied, float th, int checkOrientation,
+                                                  int* const* match_mp, int* nmatches);
 
 /* KeyFrame fields SearchForTriangulation reads (src/ORBmatcher.cc:441-676); the DBoW2
  * FeatureVector is flattened to sorted node ids + CSR index lists. */

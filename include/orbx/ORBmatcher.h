@@ -124,6 +124,11 @@ public:
         check(orbx_distinctive_descriptors(m_, 1, off, descriptors, &best, nullptr));
         return best;
     }
+    /* DBoW2 FORB::meanValue (Thirdparty/DBoW2/src/DBoW2/FORB.cpp:28-79) of N descriptors -> mean[32] */
+    void MeanValue(const uint8_t* descriptors, int N, uint8_t* mean) {
+        const int off[2] = {0, N};
+        check(orbx_mean_value(m_, 1, off, descriptors, mean));
+    }
     /* src/Frame.cc:157-176: CSR grid (cell_off[cols*rows+1], cell_idx[n]) */
     void AssignFeaturesToGrid(const orbx_frame_view& F, std::vector<int>& cell_off, std::vector<int>& cell_idx) {
         cell_off.assign((size_t)F.gcols * F.grows + 1, 0);

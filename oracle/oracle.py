@@ -199,6 +199,13 @@ def distinctive_descriptor(desc):
     return lib().orc_distinctive_descriptor(_p(d), len(d), C.byref(med)), med.value
 
 
+def forb_mean_value(desc):
+    d = _u8(np.asarray(desc, np.uint8).reshape(-1, 32))
+    out = np.zeros(32, np.uint8)
+    lib().orc_forb_mean_value(_p(d), len(d), _p(out))
+    return out
+
+
 def assign_features_to_grid(F):
     keep = []
     fv = _frame_view(F, keep)

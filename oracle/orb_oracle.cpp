@@ -714,6 +714,34 @@ int orc_distinctive_descriptor(const uint8_t* desc, int N, int* median_out) {
     return BestIdx;
 }
 
+/* DBoW2 FORB::meanValue, Thirdparty/DBoW2/src/DBoW2/FORB.cpp:28-79, on N descriptors of 32 bytes; mean: 32 bytes
+ * (all zero for N == 0, where the reference releases the Mat) */
+void orc_forb_mean_value(const uint8_t* desc, int N, uint8_t* mean) {
+    memset(mean, 0, 32);
+    if (N <= 0) return;
+    if (N == 1) { memcpy(mean, desc, 32); return; }
+    std::vector<int> sum(32 * 8, 0);
+    for (int i = 0; i < N; ++i) {
+        const unsigned char* p = desc + (size_t)i * 32;
+        for (int j = 0; j < 32; ++j, ++p) {
+            if (*p & (1 << 7)) ++sum[j * 8];
+            if (*p & (1 << 6)) ++sum[j * 8 + 1];
+            if (*p & (1 << 5)) ++sum[j * 8 + 2];
+            if (*p & (1 << 4)) ++sum[j * 8 + 3];
+            if (*p & (1 << 3)) ++sum[j * 8 + 4];
+            if (*p & (1 << 2)) ++sum[j * 8 + 5];
+            if (*p & (1 << 1)) ++sum[j * 8 + 6];
+            if (*p & (1)) ++sum[j * 8 + 7];
+        }
+    }
+    unsigned char* p = mean;
+    const int N2 = N / 2 + N % 2;
+    for (size_t i = 0; i < sum.size(); ++i) {
+        if (sum[i] >= N2) *p |= 1 << (7 - (i % 8));
+        if (i % 8 == 7) ++p;
+    }
+}
+
 /* Frame::AssignFeaturesToGrid as CSR (cells in linear order, push_back order inside a cell) */
 void orc_assign_features_to_grid(const orc_frame_view* F, int* cell_off, int* cell_idx) {
     const std::vector<std::vector<int>> grid = build_grid(F);

@@ -105,6 +105,9 @@ typedef struct {
  * index of the descriptor with the least median distance to the rest (first on ties), -1 if N==0. */
 int orc_distinctive_descriptor(const uint8_t* desc, int N, int* median_out);
 
+/* DBoW2 FORB::meanValue (Thirdparty/DBoW2/src/DBoW2/FORB.cpp:28-79): per-bit majority of N descriptors -> 32 bytes */
+void orc_forb_mean_value(const uint8_t* desc, int N, uint8_t* mean);
+
 /* Frame::AssignFeaturesToGrid + PosInGrid (Frame.cc:157-176, 470-480) as a CSR over the cells
  * (linear index y*cols + x, push_back order inside a cell); cell_idx has F->n entries, the unused
  * tail (keypoints outside the grid) is -1. */

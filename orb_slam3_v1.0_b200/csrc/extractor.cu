@@ -1942,6 +1942,7 @@ static orbx_status enqueue_frames(orbx_extractor* e, const uint8_t* d_images, si
     if (e->profiling) ORBX_CUDA(cudaEventRecord(e->ev[0], st));
     /* stage 0 */
     {
+        ORBX_RANGE("ComputePyramid");
         const LevelDev& L0 = T.lv[0];
         const int vec_ok = (row_stride % 16 == 0) && (frame_stride % 16 == 0) && (((uintptr_t)d_images) % 16 == 0);
         L0Split S;
@@ -2004,6 +2005,7 @@ static orbx_status enqueue_frames(orbx_extractor* e, const uint8_t* d_images, si
     }
     if (fork_blur == 1) { orbx_status r = launch_side_blur(); if (r != ORBX_OK) return r; }
     /* stage 1 */
+    ORBX_RANGE("ComputeKeyPointsOctTree");
     if (e->ncells > 0 && !dataflow) {
         if (e->nunits_short > 0) {
             k_fast_units<<<dim3(e->nunits_short, nb), FAST_THREADS, (size_t)2 * e->fast_rows_short * e->fast_tp + FAST_QBYTES + 128, st>>>(
@@ -2020,6 +2022,7 @@ static orbx_status enqueue_frames(orbx_extractor* e, const uint8_t* d_images, si
     if (dataflow) {
         for (int l = 0; l < nl; ++l) ORBX_CUDA(cudaStreamWaitEvent(st, e->ev_oct[l], 0));
     } else {
+        ORBX_RANGE("DistributeOctTree");
         k_octree<<<dim3(nl, nb), OCT_THREADS, e->oct_smem, st>>>(T, e->d_cells, e->ncells, e->d_slots, e->slots_per_frame,
                                                                  e->d_cell_count, e->d_cand, e->d_pnode, e->cand_per_frame,
                                                                  e->d_cand_count, e->d_sel, e->sel_per_frame, e->d_sel_count,
@@ -2042,6 +2045,7 @@ static orbx_status enqueue_frames(orbx_extractor* e, const uint8_t* d_images, si
     if (e->profiling) ORBX_CUDA(cudaEventRecord(e->ev[5], st));
     /* stage 5 */
     {
+        ORBX_RANGE("computeDescriptors");
         k_orient_describe<<<dim3(orbx_div_up((int)e->sel_per_frame, OD_WARPS * OD_KPW), nb), 32 * OD_WARPS, OD_SMEM, st>>>(
             T, (const ODMaps*)e->d_odmaps, e->d_sel, e->sel_per_frame, e->d_sel_count, e->d_dest, e->d_kps, e->d_desc, e->kcap);
         ++launches;
@@ -2058,6 +2062,7 @@ extern "C" orbx_status orbx_extract_device(orbx_extractor* e, const uint8_t* d_i
         return ORBX_ERR_INVALID;
     }
     ORBX_CUDA(cudaSetDevice(e->P.device));
+    ORBX_RANGE("ApplyExtractor");
     cudaStream_t st = e->stream;
     int launches = 0;
     const int* d_lap = nullptr;

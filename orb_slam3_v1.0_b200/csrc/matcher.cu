@@ -109,6 +109,7 @@ struct orbx_matcher {
     size_t scratch_cap = 0;
     int last_launches = 0;
     int knn_variant = 1;
+    cudaEvent_t ev_dep = nullptr;      /* orders resident searches after the extractor's stream */
 };
 
 struct Packer {
@@ -188,6 +189,7 @@ extern "C" void orbx_matcher_destroy(orbx_matcher* m) {
     if (m->d_in) cudaFree(m->d_in);
     if (m->d_out) cudaFree(m->d_out);
     if (m->d_scratch) cudaFree(m->d_scratch);
+    if (m->ev_dep) cudaEventDestroy(m->ev_dep);
     if (m->stream) cudaStreamDestroy(m->stream);
     delete m;
 }
@@ -244,6 +246,9 @@ struct SbpProb {
     unsigned long long mflag, mx, my, mlevel, maux, mdepth, mdesc;
     unsigned long long uright, mxr, mobs;                               /* stereo gate / per-point Observations() > 0; ~0 = absent */
     unsigned long long out_match;                                       /* offset into the output arena */
+    /* resident mode: the Frame side is read in place from an extractor's device buffers (absolute addresses) */
+    unsigned long long abs_kps, abs_desc, abs_n, abs_uright;            /* orbx_keypoint records, descriptors, keypoint count, mvuRight (0 = none) */
+    int resident, pad2;
 };
 
 /* One CTA per problem.
@@ -268,12 +273,21 @@ __global__ void __launch_bounds__(MT) k_search_by_projection(const uint8_t* __re
 
     const SbpProb P = probs[blockIdx.x];
     const int tid = threadIdx.x;
-    const int n = P.n, nmp = P.nmp, ncell = P.gcols * P.grows;
-    const float* kx = reinterpret_cast<const float*>(in + P.kx);
-    const float* ky = reinterpret_cast<const float*>(in + P.ky);
-    const int* koct = reinterpret_cast<const int*>(in + P.koct);
-    const float* kangle = reinterpret_cast<const float*>(in + P.kangle);
-    const uint4* kdesc = reinterpret_cast<const uint4*>(in + P.desc);
+    const int nmp = P.nmp, ncell = P.gcols * P.grows;
+    /* keypoint fields by base pointer + stride: packed arrays from the host (stride 4) or the extractor's
+     * 28-byte cv::KeyPoint records in place (x +0, y +4, angle +12, octave +20) */
+    const int n = P.resident ? min(P.n, __ldg(reinterpret_cast<const int*>(P.abs_n))) : P.n;
+    const size_t ks = P.resident ? sizeof(orbx_keypoint) : 4;
+    const uint8_t* kb = reinterpret_cast<const uint8_t*>(P.abs_kps);
+    const uint8_t* kxp = P.resident ? kb : in + P.kx;
+    const uint8_t* kyp = P.resident ? kb + 4 : in + P.ky;
+    const uint8_t* kop = P.resident ? kb + 20 : in + P.koct;
+    const uint8_t* kap = P.resident ? kb + 12 : in + P.kangle;
+    auto KX = [&](int i) { return *reinterpret_cast<const float*>(kxp + (size_t)i * ks); };
+    auto KY = [&](int i) { return *reinterpret_cast<const float*>(kyp + (size_t)i * ks); };
+    auto KOCT = [&](int i) { return *reinterpret_cast<const int*>(kop + (size_t)i * ks); };
+    auto KANG = [&](int i) { return *reinterpret_cast<const float*>(kap + (size_t)i * ks); };
+    const uint4* kdesc = P.resident ? reinterpret_cast<const uint4*>(P.abs_desc) : reinterpret_cast<const uint4*>(in + P.desc);
     const uint8_t* claimed = in + P.claimed;
     const float* scale = reinterpret_cast<const float*>(in + P.scale);
     const uint8_t* mflag = in + P.mflag;
@@ -283,7 +297,8 @@ __global__ void __launch_bounds__(MT) k_search_by_projection(const uint8_t* __re
     const float* maux = reinterpret_cast<const float*>(in + P.maux);
     const float* mdepth = reinterpret_cast<const float*>(in + P.mdepth);
     const uint4* mdesc = reinterpret_cast<const uint4*>(in + P.mdesc);
-    const float* uright = P.uright == ~0ull ? nullptr : reinterpret_cast<const float*>(in + P.uright);   /* mvuRight */
+    const float* uright = P.resident ? reinterpret_cast<const float*>(P.abs_uright)
+                                     : (P.uright == ~0ull ? nullptr : reinterpret_cast<const float*>(in + P.uright));   /* mvuRight */
     const float* mxr = reinterpret_cast<const float*>(in + P.mxr);                                        /* mTrackProjXR */
     const uint8_t* mobs = P.mobs == ~0ull ? nullptr : in + P.mobs;
     int* match = reinterpret_cast<int*>(out + P.out_match);
@@ -301,8 +316,8 @@ __global__ void __launch_bounds__(MT) k_search_by_projection(const uint8_t* __re
     if (tid == 0) s_count = 0;
     __syncthreads();
     for (int i = tid; i < n; i += MT) {
-        const int px = (int)roundf((kx[i] - P.minx) * P.gw_inv);
-        const int py = (int)roundf((ky[i] - P.miny) * P.gh_inv);
+        const int px = (int)roundf((KX(i) - P.minx) * P.gw_inv);
+        const int py = (int)roundf((KY(i) - P.miny) * P.gh_inv);
         const int lin = py * P.gcols + px;            /* computeLinearGridIndex: the reference's bound test */
         /* lin in range does not imply px in range: the reference then files the keypoint under
          * cell (lin % gcols, lin / gcols); reproduce that */
@@ -313,8 +328,8 @@ __global__ void __launch_bounds__(MT) k_search_by_projection(const uint8_t* __re
     for (int i = tid; i < ncell; i += MT) cell_fill[i] = cell_start[i];
     __syncthreads();
     for (int i = tid; i < n; i += MT) {
-        const int px = (int)roundf((kx[i] - P.minx) * P.gw_inv);
-        const int py = (int)roundf((ky[i] - P.miny) * P.gh_inv);
+        const int px = (int)roundf((KX(i) - P.minx) * P.gw_inv);
+        const int py = (int)roundf((KY(i) - P.miny) * P.gh_inv);
         const int lin = py * P.gcols + px;
         if (lin >= 0 && lin < ncell) csr[atomicAdd(&cell_fill[(lin % P.gcols) * P.grows + lin / P.gcols], 1u)] = (unsigned short)i;
     }
@@ -374,9 +389,9 @@ __global__ void __launch_bounds__(MT) k_search_by_projection(const uint8_t* __re
                 const uint32_t e0 = cell_start[ix * P.grows + r0], e1 = cell_start[ix * P.grows + r1 + 1];
                 for (uint32_t e = e0; e < e1; ++e) {
                     const int idx = csr[e];
-                    const int oc = koct[idx];
+                    const int oc = KOCT(idx);
                     if (bCheckLevels && (oc < minLevel || (maxLevel >= 0 && oc > maxLevel))) continue;
-                    if (!(fabsf(kx[idx] - x) < r && fabsf(ky[idx] - y) < r)) continue;
+                    if (!(fabsf(KX(idx) - x) < r && fabsf(KY(idx) - y) < r)) continue;
                     if (claimed[idx] || prev[idx] < (uint32_t)i) continue;
                     if (uright) {                                   /* :81-86, F->Nleft == -1 && mvuRight[idx] > 0 */
                         const float ur = uright[idx];
@@ -394,8 +409,8 @@ __global__ void __launch_bounds__(MT) k_search_by_projection(const uint8_t* __re
             bool accept;
             if (P.mode == 0) {
                 const int bestDist2 = (b2 == ~0ull) ? 256 : (int)(b2 >> 32);
-                const int bestLevel = koct[bestIdx];
-                const int bestLevel2 = (b2 == ~0ull) ? -1 : koct[csr[(uint32_t)b2]];
+                const int bestLevel = KOCT(bestIdx);
+                const int bestLevel2 = (b2 == ~0ull) ? -1 : KOCT(csr[(uint32_t)b2]);
                 accept = bestDist <= TH_HIGH && !(bestLevel == bestLevel2 && (float)bestDist > P.nnRatio * (float)bestDist2);
             } else {
                 accept = bestDist <= TH_HIGH;
@@ -428,7 +443,7 @@ __global__ void __launch_bounds__(MT) k_search_by_projection(const uint8_t* __re
         prev[i] = o;
         if (o != 0xFFFFFFFFu) {
             ++mycount;
-            if (hist) atomicAdd(&s_hist[rot_bin(maux[o], kangle[i])], 1);
+            if (hist) atomicAdd(&s_hist[rot_bin(maux[o], KANG(i))], 1);
         }
     }
     if (P.mode == 0) mycount = tid == 0 ? accepted_total : 0;       /* nmatches++ per assignment (:108-110) */
@@ -439,7 +454,7 @@ __global__ void __launch_bounds__(MT) k_search_by_projection(const uint8_t* __re
         const uint32_t o = prev[i];
         int mval = (o == 0xFFFFFFFFu) ? -1 : (int)o;
         if (hist && mval >= 0) {
-            const int bin = rot_bin(maux[o], kangle[i]);
+            const int bin = rot_bin(maux[o], KANG(i));
             if (bin != s_ind[0] && bin != s_ind[1] && bin != s_ind[2]) { mval = -1; --mycount; }
         }
         match[i] = mval;
@@ -452,6 +467,7 @@ __global__ void __launch_bounds__(MT) k_search_by_projection(const uint8_t* __re
 static orbx_status run_sbp(orbx_matcher* m, int nprob, const orbx_frame_view* F, int mode, const orbx_mappoints* MP0,
                            const orbx_kf_points* MP1, const uint8_t* const* claimed, float th, int bFar, float thFar,
                            float nnRatio, int checkOri, int* const* match_mp, int* nmatches) {
+    ORBX_RANGE(mode == 1 ? "SearchByProjectionCall_3" : "SearchByProjection");
     if (!m || nprob < 0 || (nprob > 0 && (!F || (!MP0 && !MP1) || !match_mp || !nmatches))) {
         orbx_set_error("null argument");
         return ORBX_ERR_INVALID;
@@ -548,6 +564,122 @@ extern "C" orbx_status orbx_search_by_projection_kf(orbx_matcher* m, int nprob, 
                                                     const orbx_kf_points* MP, const uint8_t* const* occupied, float th,
                                                     int checkOrientation, int* const* match_mp, int* nmatches) {
     return run_sbp(m, nprob, F, 1, nullptr, MP, occupied, th, 0, 0.f, 0.f, checkOrientation, match_mp, nmatches);
+}
+
+/* Resident form of both SearchByProjection overloads: the Frame side (mvKeysUn == the extractor's keypoints, i.e. a
+ * rectified / distortion-free camera, descriptors, keypoint count, mvuRight of an earlier orbx_stereo_matches_async) is
+ * read IN PLACE from the extractor's device buffers; only the map points travel H2D and the matches D2H.  The matcher's
+ * stream waits for the extractor's stream through an event -- no host synchronisation between extraction and search. */
+static orbx_status run_sbp_resident(orbx_matcher* m, orbx_extractor* e, int nprob, const int* frames, const int* stereo_pairs,
+                                    const orbx_frame_view* G, int mode, const orbx_mappoints* MP0, const orbx_kf_points* MP1,
+                                    const uint8_t* const* claimed, float th, int bFar, float thFar, float nnRatio, int checkOri,
+                                    int* const* match_mp, int* nmatches) {
+    ORBX_RANGE(mode == 1 ? "SearchByProjectionCall_3" : "SearchByProjection");
+    if (!m || !e || nprob < 0 || (nprob > 0 && (!frames || !G || (!MP0 && !MP1) || !match_mp || !nmatches))) {
+        orbx_set_error("null argument");
+        return ORBX_ERR_INVALID;
+    }
+    if (nprob == 0) return ORBX_OK;
+    if (e->P.device != m->device) { orbx_set_error("extractor on device %d, matcher on device %d", e->P.device, m->device); return ORBX_ERR_INVALID; }
+    if (e->last_batch < 1) { orbx_set_error("no extraction enqueued"); return ORBX_ERR_INVALID; }
+    if (G->gcols < 1 || G->grows < 1 || (long long)G->gcols * G->grows > 65535 || !G->scale || G->nlevels < 1 || e->kcap > 65535) {
+        orbx_set_error("unsupported grid / scale table");
+        return ORBX_ERR_INVALID;
+    }
+    ORBX_CUDA(cudaSetDevice(m->device));
+    Packer in, out;
+    std::vector<SbpProb> probs(nprob);
+    const size_t scale_off = in.add(G->scale, 4 * (size_t)G->nlevels);
+    const int kcap = e->kcap;
+    for (int p = 0; p < nprob; ++p) {
+        SbpProb& P = probs[p];
+        memset(&P, 0, sizeof(P));
+        const int f = frames[p];
+        const int nmp = mode == 0 ? MP0[p].n : MP1[p].n;
+        if (f < 0 || f >= e->last_batch || nmp < 0) { orbx_set_error("problem %d: frame %d outside the last batch of %d", p, f, e->last_batch); return ORBX_ERR_INVALID; }
+        const int pair = stereo_pairs ? stereo_pairs[p] : -1;
+        if (pair >= 0 && (!e->d_uright || pair >= e->last_pairs)) { orbx_set_error("problem %d: stereo pair %d has no mvuRight (run orbx_stereo_matches_async first)", p, pair); return ORBX_ERR_INVALID; }
+        P.n = kcap; P.nmp = nmp; P.gcols = G->gcols; P.grows = G->grows; P.nlevels = G->nlevels; P.mode = mode;
+        P.bFar = bFar; P.checkOri = checkOri;
+        P.minx = G->minx; P.miny = G->miny; P.gw_inv = G->gw_inv; P.gh_inv = G->gh_inv;
+        P.th = th; P.thFar = thFar; P.nnRatio = nnRatio;
+        P.resident = 1;
+        P.abs_kps = (unsigned long long)(uintptr_t)(e->d_kps + (size_t)f * kcap);
+        P.abs_desc = (unsigned long long)(uintptr_t)(e->d_desc + (size_t)f * kcap * 32);
+        P.abs_n = (unsigned long long)(uintptr_t)(e->d_nk + f);
+        P.abs_uright = (mode == 0 && pair >= 0) ? (unsigned long long)(uintptr_t)(e->d_uright + (size_t)pair * kcap) : 0ull;
+        P.claimed = in.add(claimed ? claimed[p] : nullptr, (size_t)kcap);
+        P.scale = scale_off;
+        P.uright = ~0ull; P.mobs = ~0ull;
+        if (mode == 0) {
+            const orbx_mappoints& M = MP0[p];
+            if (nmp > 0 && (!M.inview || !M.x || !M.y || !M.level || !M.viewcos || !M.desc || (bFar && !M.depth) || (P.abs_uright && !M.proj_xr))) {
+                orbx_set_error("problem %d: null map-point array", p);
+                return ORBX_ERR_INVALID;
+            }
+            P.mflag = in.add(M.inview, nmp); P.mx = in.add(M.x, 4 * (size_t)nmp); P.my = in.add(M.y, 4 * (size_t)nmp);
+            P.mlevel = in.add(M.level, 4 * (size_t)nmp); P.maux = in.add(M.viewcos, 4 * (size_t)nmp);
+            P.mdepth = in.add(M.depth, M.depth ? 4 * (size_t)nmp : 0); P.mdesc = in.add(M.desc, 32 * (size_t)nmp);
+            P.mxr = in.add(P.abs_uright ? M.proj_xr : nullptr, P.abs_uright ? 4 * (size_t)nmp : 0);
+            P.mobs = M.has_obs && nmp > 0 ? in.add(M.has_obs, (size_t)nmp) : ~0ull;
+        } else {
+            const orbx_kf_points& M = MP1[p];
+            if (nmp > 0 && (!M.valid || !M.u || !M.v || !M.level || !M.desc || (checkOri && !M.angle))) {
+                orbx_set_error("problem %d: null keyframe-point array", p);
+                return ORBX_ERR_INVALID;
+            }
+            P.mflag = in.add(M.valid, nmp); P.mx = in.add(M.u, 4 * (size_t)nmp); P.my = in.add(M.v, 4 * (size_t)nmp);
+            P.mlevel = in.add(M.level, 4 * (size_t)nmp); P.maux = in.add(M.angle, M.angle ? 4 * (size_t)nmp : 0);
+            P.mdepth = in.add(nullptr, 0); P.mdesc = in.add(M.desc, 32 * (size_t)nmp);
+            P.mxr = in.add(nullptr, 0);
+        }
+        const int32_t* lv = mode == 0 ? MP0[p].level : MP1[p].level;
+        for (int i = 0; i < nmp; ++i)
+            if (lv[i] < 0 || lv[i] >= G->nlevels) { orbx_set_error("problem %d: map point %d level %d outside [0,%d)", p, i, lv[i], G->nlevels); return ORBX_ERR_INVALID; }
+        P.out_match = out.add(nullptr, 4 * (size_t)kcap);
+    }
+    const size_t smem = (size_t)4 * (2 * (size_t)G->gcols * G->grows + 1 + 3 * (size_t)kcap) + 2 * (size_t)kcap + 16;
+    const size_t probs_off = in.add(probs.data(), sizeof(SbpProb) * (size_t)nprob);
+    const size_t counts_off = out.add(nullptr, 4 * (size_t)nprob);
+    if (smem > 200 * 1024) { orbx_set_error("frame grid + keypoints need %zu B of shared memory (> 200 KB)", smem); return ORBX_ERR_INVALID; }
+    orbx_status st = ensure_io(m, in.total, out.total);
+    if (st != ORBX_OK) return st;
+    in.copy_to(m->h_in);
+    if (!m->ev_dep) ORBX_CUDA(cudaEventCreateWithFlags(&m->ev_dep, cudaEventDisableTiming));
+    ORBX_CUDA(cudaEventRecord(m->ev_dep, e->stream));
+    ORBX_CUDA(cudaStreamWaitEvent(m->stream, m->ev_dep, 0));
+    ORBX_CUDA(cudaMemcpyAsync(m->d_in, m->h_in, in.total, cudaMemcpyHostToDevice, m->stream));
+    /* unwritten tail of a match array (keypoints beyond the frame's count) reads as -1 */
+    ORBX_CUDA(cudaMemsetAsync(m->d_out, 0xFF, out.total, m->stream));
+    ORBX_ENSURE_SMEM(k_search_by_projection, smem);
+    k_search_by_projection<<<nprob, MT, smem, m->stream>>>(m->d_in, m->d_out, reinterpret_cast<const SbpProb*>(m->d_in + probs_off),
+                                                           reinterpret_cast<int*>(m->d_out + counts_off));
+    ORBX_CUDA(cudaGetLastError());
+    m->last_launches = 1;
+    ORBX_CUDA(cudaMemcpyAsync(m->h_out, m->d_out, out.total, cudaMemcpyDeviceToHost, m->stream));
+    ORBX_CUDA(cudaStreamSynchronize(m->stream));
+    for (int p = 0; p < nprob; ++p) {
+        memcpy(match_mp[p], m->h_out + probs[p].out_match, 4 * (size_t)kcap);
+        nmatches[p] = reinterpret_cast<const int*>(m->h_out + counts_off)[p];
+    }
+    return ORBX_OK;
+}
+
+extern "C" orbx_status orbx_search_by_projection_resident(orbx_matcher* m, orbx_extractor* e, int nprob, const int* frames,
+                                                          const int* stereo_pairs, const orbx_frame_view* grid,
+                                                          const orbx_mappoints* MP, const uint8_t* const* claimed, float th,
+                                                          int bFarPoints, float thFarPoints, float nnRatio, int* const* match_mp,
+                                                          int* nmatches) {
+    return run_sbp_resident(m, e, nprob, frames, stereo_pairs, grid, 0, MP, nullptr, claimed, th, bFarPoints, thFarPoints, nnRatio, 0,
+                            match_mp, nmatches);
+}
+
+extern "C" orbx_status orbx_search_by_projection_kf_resident(orbx_matcher* m, orbx_extractor* e, int nprob, const int* frames,
+                                                             const orbx_frame_view* grid, const orbx_kf_points* MP,
+                                                             const uint8_t* const* occupied, float th, int checkOrientation,
+                                                             int* const* match_mp, int* nmatches) {
+    return run_sbp_resident(m, e, nprob, frames, nullptr, grid, 1, nullptr, MP, occupied, th, 0, 0.f, 0.f, checkOrientation, match_mp,
+                            nmatches);
 }
 
 /* ================================================================== SearchForTriangulation */
@@ -660,6 +792,7 @@ extern "C" orbx_status orbx_search_for_triangulation(orbx_matcher* m, int nprob,
                                                      const orbx_kf_view* k2, const float* F12, const float* ep,
                                                      const float* const* scale2, int bOnlyStereo, int bCoarse,
                                                      int checkOrientation, int* const* pairs, int* npairs, int* nmatches) {
+    ORBX_RANGE("SearchForTriangulationCall");
     if (!m || nprob < 0 || (nprob > 0 && (!k1 || !k2 || !F12 || !ep || !scale2 || !pairs || !npairs))) {
         orbx_set_error("null argument");
         return ORBX_ERR_INVALID;
@@ -915,6 +1048,7 @@ static int knn_split_rows(int nq, int ndb) {
 
 extern "C" orbx_status orbx_knn2_device(orbx_matcher* m, const void* d_q, int nq, const void* d_db, int ndb,
                                         long long index_base, unsigned long long* d_keys) {
+    ORBX_RANGE("knn2");
     if (!m || nq < 0 || ndb < 0 || (nq > 0 && (!d_q || !d_keys)) || (ndb > 0 && !d_db) || index_base < 0 ||
         index_base + ndb > 0xFFFFFFFFll) {
         orbx_set_error("bad kNN arguments");
@@ -1169,6 +1303,7 @@ static orbx_status grid_check(const orbx_frame_view& f, int p) {
 
 extern "C" orbx_status orbx_assign_features_to_grid(orbx_matcher* m, int nframes, const orbx_frame_view* F,
                                                     int* const* cell_off, int* const* cell_idx) {
+    ORBX_RANGE("AssignFeaturesToGrid");
     if (!m || nframes < 0 || (nframes > 0 && (!F || !cell_off || !cell_idx))) { orbx_set_error("null argument"); return ORBX_ERR_INVALID; }
     if (nframes == 0) return ORBX_OK;
     ORBX_CUDA(cudaSetDevice(m->device));
@@ -1215,6 +1350,7 @@ extern "C" orbx_status orbx_assign_features_to_grid(orbx_matcher* m, int nframes
 extern "C" orbx_status orbx_features_in_area(orbx_matcher* m, const orbx_frame_view* F, int nq, const float* x, const float* y,
                                              const float* r, const int* minLevel, const int* maxLevel, int* out_count,
                                              int* out_idx, int cap) {
+    ORBX_RANGE("GetFeaturesInArea");
     if (!m || !F || nq < 0 || cap < 1 || (nq > 0 && (!x || !y || !r || !minLevel || !maxLevel || !out_count || !out_idx))) {
         orbx_set_error("null argument");
         return ORBX_ERR_INVALID;
@@ -1271,6 +1407,7 @@ extern "C" orbx_status orbx_features_in_area(orbx_matcher* m, const orbx_frame_v
  * distortion-free input; distorted cameras go through orbx_assign_features_to_grid with mvKeysUn). */
 extern "C" orbx_status orbx_extractor_assign_grid(orbx_extractor* e, float minx, float miny, float gw_inv, float gh_inv,
                                                   int gcols, int grows) {
+    ORBX_RANGE("AssignFeaturesToGrid");
     if (!e || gcols < 1 || grows < 1 || (long long)gcols * grows > 20000) { orbx_set_error("invalid grid"); return ORBX_ERR_INVALID; }
     if (e->last_batch < 1) { orbx_set_error("no extraction enqueued"); return ORBX_ERR_INVALID; }
     ORBX_CUDA(cudaSetDevice(e->P.device));
@@ -1363,6 +1500,7 @@ __global__ void __launch_bounds__(DD_THREADS) k_distinctive(const int* __restric
 
 extern "C" orbx_status orbx_distinctive_descriptors(orbx_matcher* m, int nsets, const int* set_off, const uint8_t* desc,
                                                     int* best, int* median) {
+    ORBX_RANGE("ComputeDistinctiveDescriptors");
     if (!m || nsets < 0 || (nsets > 0 && (!set_off || !best))) { orbx_set_error("null argument"); return ORBX_ERR_INVALID; }
     if (nsets == 0) return ORBX_OK;
     const int total = set_off[nsets];
@@ -1387,6 +1525,86 @@ extern "C" orbx_status orbx_distinctive_descriptors(orbx_matcher* m, int nsets, 
     ORBX_CUDA(cudaStreamSynchronize(m->stream));
     memcpy(best, m->h_out + ob, 4 * (size_t)nsets);
     if (median) memcpy(median, m->h_out + om, 4 * (size_t)nsets);
+    return ORBX_OK;
+}
+
+/* ================================================================== FORB::meanValue */
+/* DBoW2 FORB::meanValue, reference Thirdparty/DBoW2/src/DBoW2/FORB.cpp:28-79: per-bit majority over a set of N
+ * descriptors, bit set iff its count >= N/2 + N%2 (N == 1: the descriptor itself; N == 0: all zero, the reference
+ * releases the Mat).  Batched over sets, one WARP per set: lane = word (lane & 7) of descriptors (lane >> 3) + 4k, so a
+ * warp step reads 4 descriptors as one 128-byte row.  Counts are kept bit-sliced (MV_PLANES bit planes per 32-bit word:
+ * adding a word is a ripple of XOR / AND over the planes that still carry), the four lane groups are summed plane-wise
+ * over shuffles, and "count >= N2" is evaluated on the planes from the top bit down -- no per-bit counters. */
+#define MV_PLANES 24            /* sets of up to 2^24 - 1 descriptors */
+__global__ void __launch_bounds__(128) k_mean_value(const int* __restrict__ set_off, const uint32_t* __restrict__ desc,
+                                                     uint32_t* __restrict__ mean, int nsets) {
+    const int s = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (s >= nsets) return;
+    const int o0 = set_off[s], N = set_off[s + 1] - o0;
+    const int w = lane & 7, g = lane >> 3;
+    uint32_t pl[MV_PLANES];
+#pragma unroll
+    for (int p = 0; p < MV_PLANES; ++p) pl[p] = 0u;
+    for (int d = g; d < N; d += 4) {
+        uint32_t c = __ldg(desc + (size_t)(o0 + d) * 8 + w);
+#pragma unroll
+        for (int p = 0; p < MV_PLANES; ++p) {            /* c = carry into plane p */
+            const uint32_t t = pl[p] & c;
+            pl[p] ^= c;
+            c = t;
+        }
+    }
+    /* add the counters of lane groups: g += g + 2, then g += g + 1 (bit-sliced full adder over the planes) */
+#pragma unroll
+    for (int sh = 16; sh >= 8; sh >>= 1) {
+        uint32_t carry = 0u;
+#pragma unroll
+        for (int p = 0; p < MV_PLANES; ++p) {
+            const uint32_t o = __shfl_down_sync(0xffffffffu, pl[p], sh);
+            const uint32_t a = pl[p];
+            pl[p] = a ^ o ^ carry;
+            carry = (a & o) | (carry & (a ^ o));
+        }
+    }
+    if (g == 0) {
+        const uint32_t N2 = (uint32_t)(N / 2 + N % 2);
+        uint32_t gt = 0u, eq = 0xFFFFFFFFu;
+#pragma unroll
+        for (int p = MV_PLANES - 1; p >= 0; --p) {
+            const uint32_t t = ((N2 >> p) & 1u) ? 0xFFFFFFFFu : 0u;
+            gt |= eq & pl[p] & ~t;
+            eq &= ~(pl[p] ^ t);
+        }
+        mean[(size_t)s * 8 + w] = N > 0 ? (gt | eq) : 0u;
+    }
+}
+
+extern "C" orbx_status orbx_mean_value(orbx_matcher* m, int nsets, const int* set_off, const uint8_t* desc, uint8_t* mean) {
+    ORBX_RANGE("FORB::meanValue");
+    if (!m || nsets < 0 || (nsets > 0 && (!set_off || !mean))) { orbx_set_error("null argument"); return ORBX_ERR_INVALID; }
+    if (nsets == 0) return ORBX_OK;
+    const int total = set_off[nsets];
+    if (set_off[0] != 0 || total < 0 || (total > 0 && !desc)) { orbx_set_error("bad set offsets"); return ORBX_ERR_INVALID; }
+    for (int s = 0; s < nsets; ++s)
+        if (set_off[s + 1] < set_off[s] || set_off[s + 1] - set_off[s] >= (1 << MV_PLANES)) {
+            orbx_set_error("set %d: offsets not ascending or more than 2^%d - 1 descriptors", s, MV_PLANES);
+            return ORBX_ERR_INVALID;
+        }
+    ORBX_CUDA(cudaSetDevice(m->device));
+    Packer in, out;
+    const size_t io = in.add(set_off, 4 * (size_t)(nsets + 1)), id = in.add(desc, 32 * (size_t)total);
+    const size_t om = out.add(nullptr, 32 * (size_t)nsets);
+    orbx_status st = ensure_io(m, in.total, out.total);
+    if (st != ORBX_OK) return st;
+    in.copy_to(m->h_in);
+    ORBX_CUDA(cudaMemcpyAsync(m->d_in, m->h_in, in.total, cudaMemcpyHostToDevice, m->stream));
+    k_mean_value<<<(nsets + 3) / 4, 128, 0, m->stream>>>(reinterpret_cast<const int*>(m->d_in + io), reinterpret_cast<const uint32_t*>(m->d_in + id),
+                                                        reinterpret_cast<uint32_t*>(m->d_out + om), nsets);
+    ORBX_CUDA(cudaGetLastError());
+    m->last_launches = 1;
+    ORBX_CUDA(cudaMemcpyAsync(m->h_out, m->d_out, out.total, cudaMemcpyDeviceToHost, m->stream));
+    ORBX_CUDA(cudaStreamSynchronize(m->stream));
+    memcpy(mean, m->h_out + om, 32 * (size_t)nsets);
     return ORBX_OK;
 }
 
@@ -1481,6 +1699,7 @@ __global__ void __launch_bounds__(MT) k_search_by_bow(const uint8_t* __restrict_
 extern "C" orbx_status orbx_search_by_bow(orbx_matcher* m, int nprob, const orbx_kf_view* KF, const orbx_kf_view* F,
                                           const int* nleft, float nnRatio, int checkOrientation, int* const* match_kf,
                                           int* nmatches) {
+    ORBX_RANGE("SearchByBoW");
     if (!m || nprob < 0 || (nprob > 0 && (!KF || !F || !match_kf || !nmatches))) { orbx_set_error("null argument"); return ORBX_ERR_INVALID; }
     if (nprob == 0) return ORBX_OK;
     ORBX_CUDA(cudaSetDevice(m->device));
@@ -1654,6 +1873,7 @@ __global__ void __launch_bounds__(MT) k_fuse_search(const uint8_t* __restrict__ 
 static orbx_status run_fuse(orbx_matcher* m, int nprob, const orbx_frame_view* KF, const float* const* uright,
                             const float* const* inv_sigma2, const orbx_fuse_points* MP, float th, int variant, int accept,
                             int* const* best_idx, int* const* best_dist) {
+    ORBX_RANGE("Fuse");
     if (!m || nprob < 0 || (nprob > 0 && (!KF || !MP || !best_idx)) || (variant != 0 && variant != 1)) { orbx_set_error("invalid argument"); return ORBX_ERR_INVALID; }
     if (nprob == 0) return ORBX_OK;
     ORBX_CUDA(cudaSetDevice(m->device));
@@ -1721,6 +1941,7 @@ extern "C" orbx_status orbx_fuse_search(orbx_matcher* m, int nprob, const orbx_f
 extern "C" orbx_status orbx_search_by_sim3(orbx_matcher* m, int nprob, const orbx_frame_view* KF1, const orbx_frame_view* KF2,
                                            const orbx_fuse_points* MP1in2, const orbx_fuse_points* MP2in1, float th,
                                            int* const* match12, int* nfound) {
+    ORBX_RANGE("SearchBySim3Call");
     if (!m || nprob < 0 || (nprob > 0 && (!KF1 || !KF2 || !MP1in2 || !MP2in1 || !match12 || !nfound))) { orbx_set_error("null argument"); return ORBX_ERR_INVALID; }
     if (nprob == 0) return ORBX_OK;
     std::vector<orbx_frame_view> views(2 * (size_t)nprob);
@@ -1980,6 +2201,7 @@ __global__ void __launch_bounds__(SFI_T) k_search_for_initialization(const uint8
 extern "C" orbx_status orbx_search_for_initialization(orbx_matcher* m, int nprob, const orbx_frame_view* F1, const orbx_frame_view* F2,
                                                       int windowSize, float nnRatio, int checkOrientation,
                                                       int* const* matches12, int* nmatches) {
+    ORBX_RANGE("SearchForInitialization");
     if (!m || nprob < 0 || (nprob > 0 && (!F1 || !F2 || !matches12 || !nmatches))) { orbx_set_error("null argument"); return ORBX_ERR_INVALID; }
     if (nprob == 0) return ORBX_OK;
     ORBX_CUDA(cudaSetDevice(m->device));

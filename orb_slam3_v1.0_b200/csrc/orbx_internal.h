@@ -55,6 +55,20 @@ inline std::mutex& orbx_smem_mutex() {
         }                                                                                 \
     } while (0)
 
+/* NVTX ranges around the C-ABI entry points, named like the reference's Tracy zones (src/ORBextractor.cc:229,435,545,
+ * 609; src/ORBmatcher.cc:331,444,979,1204; src/Frame.cc:159,406) so that a timeline of the drop-in reads like one of
+ * the reference.  Header-only NVTX v3: a no-op (one pointer test) unless a profiler is attached. */
+#include <nvtx3/nvToolsExt.h>
+struct OrbxRange {
+    explicit OrbxRange(const char* name) { nvtxRangePushA(name); }
+    ~OrbxRange() { nvtxRangePop(); }
+    OrbxRange(const OrbxRange&) = delete;
+    OrbxRange& operator=(const OrbxRange&) = delete;
+};
+#define ORBX_RANGE_CAT2(a, b) a##b
+#define ORBX_RANGE_CAT(a, b) ORBX_RANGE_CAT2(a, b)
+#define ORBX_RANGE(name) OrbxRange ORBX_RANGE_CAT(orbx_range_, __LINE__)(name)
+
 static inline int orbx_div_up(int a, int b) { return (a + b - 1) / b; }
 static inline size_t orbx_align_up(size_t a, size_t b) { return (a + b - 1) / b * b; }
 

@@ -369,6 +369,7 @@ static void fill_side(StereoSide& S, const orbx_extractor* e) {
 
 extern "C" orbx_status orbx_stereo_matches_async(orbx_extractor* left, orbx_extractor* right, int npairs,
                                                  const int* left_frames, const int* right_frames, float bf, float b) {
+    ORBX_RANGE("ComputeStereoMatches");
     if (!left || !right || !left_frames || !right_frames) { orbx_set_error("null argument"); return ORBX_ERR_INVALID; }
     if (npairs < 1 || npairs > left->P.max_batch || left->last_batch < 1 || right->last_batch < 1) {
         orbx_set_error("npairs %d outside [1,%d] or nothing extracted yet", npairs, left->P.max_batch);

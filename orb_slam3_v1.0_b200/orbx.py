@@ -72,6 +72,7 @@ def lib():
         L.orbx_search_for_initialization.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_void_p, C.c_void_p]
         L.orbx_search_by_bow.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_void_p, C.c_void_p]
         L.orbx_distinctive_descriptors.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 4
+        L.orbx_mean_value.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 3
         L.orbx_assign_features_to_grid.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orbx_features_in_area.argtypes = [C.c_void_p, C.c_void_p, C.c_int] + [C.c_void_p] * 7 + [C.c_int]
         L.orbx_extractor_stage_ms.argtypes = [C.c_void_p, C.c_void_p]
@@ -93,6 +94,10 @@ def lib():
         L.orbx_matcher_synchronize.argtypes = [C.c_void_p]
         L.orbx_search_by_projection.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float,
                                                 C.c_int, C.c_float, C.c_float, C.c_void_p, C.c_void_p]
+        L.orbx_search_by_projection_resident.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                                         C.c_void_p, C.c_float, C.c_int, C.c_float, C.c_float, C.c_void_p, C.c_void_p]
+        L.orbx_search_by_projection_kf_resident.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
+                                                            C.c_void_p, C.c_float, C.c_int, C.c_void_p, C.c_void_p]
         L.orbx_search_by_projection_kf.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float,
                                                    C.c_int, C.c_void_p, C.c_void_p]
         L.orbx_search_for_triangulation.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
@@ -528,6 +533,16 @@ class ORBmatcher:
         _ck(lib().orbx_distinctive_descriptors(self._h, len(sets), _p(off), _p(desc), _p(best), _p(med)))
         return best, med
 
+    def MeanValue(self, sets):
+        """DBoW2 FORB::meanValue for a list of (N_s, 32) descriptor sets -> (nsets, 32) u8."""
+        off = np.zeros(len(sets) + 1, np.int32)
+        off[1:] = np.cumsum([len(d) for d in sets])
+        desc = np.ascontiguousarray(np.concatenate([np.asarray(d, np.uint8).reshape(-1, 32) for d in sets]) if len(sets)
+                                    else np.zeros((0, 32), np.uint8))
+        mean = np.zeros((len(sets), 32), np.uint8)
+        _ck(lib().orbx_mean_value(self._h, len(sets), _p(off), _p(desc), _p(mean)))
+        return mean
+
     def AssignFeaturesToGrid(self, Fs):
         """Frame::AssignFeaturesToGrid for a list of frame views -> [(cell_off, cell_idx)]."""
         single = isinstance(Fs, dict)
@@ -575,6 +590,51 @@ class ORBmatcher:
         _ck(lib().orbx_search_by_projection(self._h, len(Fs), fv, mp, _ptr_array(cla, keep), th, int(bFarPoints),
                                             thFarPoints, nnRatio, _ptr_array(outs, keep), _p(nm)))
         return (int(nm[0]), outs[0]) if single else (nm, outs)
+
+    def SearchByProjectionResident(self, ex, frames, grid, MPs, th, bFarPoints=False, thFarPoints=0.0, nnRatio=0.8,
+                                   stereo_pairs=None, claimed=None):
+        """orbx_search_by_projection_resident: SearchByProjection(Frame, vpMapPoints, ...) for frames of the extractor's
+        last batch, the Frame side read in place on the device.  grid: dict with minx, miny, gw_inv, gh_inv, gcols, grows,
+        scale.  -> (nmatches[nprob], [match_mp (capacity entries)])."""
+        frames = np.ascontiguousarray(frames, np.int32)
+        keep = []
+        g = dict(grid); g.update(kx=np.zeros(0, np.float32), ky=np.zeros(0, np.float32), koct=np.zeros(0, np.int32), desc=np.zeros((0, 32), np.uint8))
+        fv = _frame_view(g, keep)
+        mp = (_MapPoints * len(frames))(*[_MapPoints(len(m["x"]), _arr(m["inview"], np.uint8, keep), _arr(m["x"], np.float32, keep),
+                                                     _arr(m["y"], np.float32, keep), _arr(m["level"], np.int32, keep),
+                                                     _arr(m["viewcos"], np.float32, keep), _arr(m.get("depth"), np.float32, keep),
+                                                     _arr(m["desc"], np.uint8, keep), _arr(m.get("proj_xr"), np.float32, keep),
+                                                     _arr(m.get("has_obs"), np.uint8, keep)) for m in MPs])
+        cap = ex.capacity
+        cla = [None if c is None else np.ascontiguousarray(c, np.uint8) for c in (claimed or [None] * len(frames))]
+        assert all(c is None or len(c) == cap for c in cla)
+        keep.append(cla)
+        sp = None if stereo_pairs is None else np.ascontiguousarray(stereo_pairs, np.int32)
+        outs = [np.empty(cap, np.int32) for _ in frames]
+        nm = np.empty(len(frames), np.int32)
+        _ck(lib().orbx_search_by_projection_resident(self._h, ex._h, len(frames), _p(frames), _p(sp), C.byref(fv), mp,
+                                                     _ptr_array(cla, keep) if claimed is not None else None, th, int(bFarPoints),
+                                                     thFarPoints, nnRatio, _ptr_array(outs, keep), _p(nm)))
+        return nm, outs
+
+    def SearchByProjectionKFResident(self, ex, frames, grid, MPs, th, checkOrientation=True, occupied=None):
+        """orbx_search_by_projection_kf_resident -> (nmatches[nprob], [match_mp (capacity entries)])."""
+        frames = np.ascontiguousarray(frames, np.int32)
+        keep = []
+        g = dict(grid); g.update(kx=np.zeros(0, np.float32), ky=np.zeros(0, np.float32), koct=np.zeros(0, np.int32), desc=np.zeros((0, 32), np.uint8))
+        fv = _frame_view(g, keep)
+        mp = (_KFPoints * len(frames))(*[_KFPoints(len(m["u"]), _arr(m["valid"], np.uint8, keep), _arr(m["u"], np.float32, keep),
+                                                   _arr(m["v"], np.float32, keep), _arr(m["level"], np.int32, keep),
+                                                   _arr(m.get("angle"), np.float32, keep), _arr(m["desc"], np.uint8, keep)) for m in MPs])
+        cap = ex.capacity
+        oca = [None if c is None else np.ascontiguousarray(c, np.uint8) for c in (occupied or [None] * len(frames))]
+        keep.append(oca)
+        outs = [np.empty(cap, np.int32) for _ in frames]
+        nm = np.empty(len(frames), np.int32)
+        _ck(lib().orbx_search_by_projection_kf_resident(self._h, ex._h, len(frames), _p(frames), C.byref(fv), mp,
+                                                        _ptr_array(oca, keep) if occupied is not None else None, th,
+                                                        int(checkOrientation), _ptr_array(outs, keep), _p(nm)))
+        return nm, outs
 
     def SearchByProjectionKF(self, F, MP, th, checkOrientation=True, occupied=None):
         """SearchByProjection(Frame, KeyFrame, sAlreadyFound, th, checkOrientation)

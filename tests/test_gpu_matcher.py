@@ -96,6 +96,69 @@ def test_search_by_projection_takeover_chain(matcher, oracle, synth):
     assert on > int((om >= 0).sum())                          # some assignments were taken over
 
 
+def test_search_by_projection_resident(pkg, matcher, oracle, synth):
+    """Device-resident chaining: extract stereo frames, ComputeStereoMatches, then SearchByProjection (both overloads)
+    straight on the extractor's device buffers -- keypoints, descriptors, counts and mvuRight never visit the host.
+    Must equal the oracle (and the host-array entry point) on the same data, incl. the mvuRight gate."""
+    ox = pkg.orbx
+    w, h, B = 640, 400, 6
+    sp = [synth.stereo_pair(w, h, 500 + i) for i in range(3)]
+    frames = np.stack([im for pr in sp for im in pr])
+    ex = ox.ORBextractor(800, 1.2, 8, 20, 7, max_batch=B)
+    res = ex.extract_batch(frames)
+    lf, rf = np.array([0, 2, 4]), np.array([1, 3, 5])
+    ox.stereo_matches_async(ex, ex, lf, rf, 40.0, 0.1)
+    ur, _ = ox.stereo_fetch(ex, 3)
+    grid = {"minx": 0.0, "miny": 0.0, "gw_inv": float(np.float32(64) / np.float32(w)), "gh_inv": float(np.float32(48) / np.float32(h)),
+            "gcols": 64, "grows": 48, "scale": ex.mvScaleFactor}
+    rng = np.random.default_rng(17)
+    Fs, MPs, cls = [], [], []
+    for p, f in enumerate(lf):
+        k, d, _ = res[f]
+        F = dict(grid, kx=k["x"].copy(), ky=k["y"].copy(), koct=k["octave"].copy(), kangle=k["angle"].copy(), desc=d.copy(),
+                 uright=ur[p][:len(k)].copy())
+        MP = synth.projection_problem(F, 1200, seed=600 + p, dup=0.4)
+        tgt = np.where(F["uright"][MP["src"]] > 0, F["uright"][MP["src"]], F["kx"][MP["src"]] - 20.0)
+        far = (rng.random(1200) < 0.25) * rng.uniform(30.0, 120.0, 1200)
+        MP["proj_xr"] = (tgt + rng.normal(0, 3.0, 1200) + far).astype(np.float32)
+        MP["has_obs"] = (rng.random(1200) < 0.85).astype(np.uint8)
+        Fs.append(F); MPs.append(MP)
+        c = np.zeros(ex.capacity, np.uint8); c[:len(k)] = rng.random(len(k)) < 0.05
+        cls.append(c)
+        assert (F["uright"] > 0).sum() > 50
+    # stereo frames
+    nm, outs = matcher.SearchByProjectionResident(ex, lf, grid, MPs, 3.0, False, 0.0, 0.8, stereo_pairs=[0, 1, 2], claimed=cls)
+    assert matcher.last_launches() == 1
+    for p in range(3):
+        n = len(Fs[p]["kx"])
+        on, om = oracle.search_by_projection(Fs[p], MPs[p], 3.0, False, 0.0, 0.8, cls[p][:n])
+        assert nm[p] == on and np.array_equal(outs[p][:n], om) and np.all(outs[p][n:] == -1) and on > 100
+        hn, hm = matcher.SearchByProjection(Fs[p], MPs[p], 3.0, False, 0.0, 0.8, cls[p][:n])
+        assert hn == on and np.array_equal(hm, om)
+    # the same frames searched as monocular ones: the gate is off, results differ
+    nm2, outs2 = matcher.SearchByProjectionResident(ex, lf, grid, MPs, 3.0, False, 0.0, 0.8)
+    for p in range(3):
+        n = len(Fs[p]["kx"])
+        Fm = dict(Fs[p]); Fm.pop("uright")
+        on, om = oracle.search_by_projection(Fm, MPs[p], 3.0, False, 0.0, 0.8)
+        assert nm2[p] == on and np.array_equal(outs2[p][:n], om)
+    assert any(not np.array_equal(a, b) for a, b in zip(outs, outs2))
+    # KeyFrame overload on the right frames
+    KPs, Fr = [], []
+    for p, f in enumerate(rf):
+        k, d, _ = res[f]
+        F = dict(grid, kx=k["x"].copy(), ky=k["y"].copy(), koct=k["octave"].copy(), kangle=k["angle"].copy(), desc=d.copy())
+        P = synth.projection_problem(F, 1000, seed=700 + p)
+        KPs.append({"valid": P["valid"], "u": P["x"], "v": P["y"], "level": P["level"], "angle": P["angle"], "desc": P["desc"]})
+        Fr.append(F)
+    nm3, outs3 = matcher.SearchByProjectionKFResident(ex, rf, grid, KPs, 15.0, True)
+    for p in range(3):
+        n = len(Fr[p]["kx"])
+        on, om = oracle.search_by_projection_kf(Fr[p], KPs[p], 15.0, True)
+        assert nm3[p] == on and np.array_equal(outs3[p][:n], om) and on > 50
+    ex.close()
+
+
 def test_search_by_projection_batched(matcher, oracle, synth):
     Fs = [synth.frame_view(600 + 50 * i, seed=20 + i) for i in range(7)]
     MPs = [synth.projection_problem(F, 900 + 10 * i, seed=40 + i) for i, F in enumerate(Fs)]
@@ -153,6 +216,21 @@ def test_three_maxima(pkg, oracle):
                                                             np.r_[100, 9, 9, np.zeros(27, int)], np.r_[100, 10, 9, np.zeros(27, int)]]
     for c in cases:
         assert pkg.orbx.three_maxima(c) == oracle.three_maxima(c)
+
+
+def test_forb_mean_value(matcher, oracle):
+    """DBoW2 FORB::meanValue batched on the GPU (bit-sliced counters) == the oracle, incl. empty / single / tie sets."""
+    rng = np.random.default_rng(8)
+    sizes = [0, 1, 2, 3, 4, 5, 8, 31, 32, 33, 64, 100, 257, 1000, 5000, 0, 7]
+    sets = [rng.integers(0, 256, (n, 32), dtype=np.uint8) for n in sizes]
+    for d in sets:
+        if len(d) >= 4:
+            d[: len(d) // 2, 1] = 0xFF; d[len(d) // 2:, 1] = 0x00            # exact ties on even N
+    sets[13][:, 5] = 0x3C                                                      # unanimous
+    got = matcher.MeanValue(sets)
+    for s_, d in enumerate(sets):
+        assert np.array_equal(got[s_], oracle.forb_mean_value(d)), (s_, len(d))
+    assert matcher.last_launches() == 1
 
 
 # ---------------------------------------------------------------- brute-force 2-NN

@@ -323,3 +323,20 @@ def test_search_for_initialization_properties(oracle, synth):
     assert (d <= 30).all()
     n2, m2 = oracle.search_for_initialization(F1, F2, 100, 0.9, True)
     assert n2 <= n and set(np.nonzero(m2 >= 0)[0]) <= set(idx1)
+
+
+def test_forb_mean_value_vs_numpy(oracle):
+    """DBoW2 FORB::meanValue (reference Thirdparty/DBoW2/src/DBoW2/FORB.cpp:28-79): per-bit majority with the
+    N/2 + N%2 threshold, against a plain numpy vote."""
+    rng = np.random.default_rng(3)
+    for N in (0, 1, 2, 3, 4, 7, 8, 33, 100, 1001):
+        d = rng.integers(0, 256, (N, 32), dtype=np.uint8)
+        if N >= 4:
+            d[:, 0] = 0xF0; d[: N // 2, 1] = 0xFF; d[N // 2:, 1] = 0x00      # unanimous bits, exact ties
+        got = oracle.forb_mean_value(d)
+        if N == 0:
+            assert not got.any()
+            continue
+        bits = np.unpackbits(d, axis=1).sum(0)
+        exp = np.packbits(bits >= N // 2 + N % 2)
+        assert np.array_equal(got, exp), N
