@@ -258,6 +258,14 @@ def matching_bench(pkg, torch, local, ex, B):
     P1 = dict(MPs[0]); P1["u"], P1["v"] = P1["x"], P1["y"]
     one = {"search_by_projection_ms": lat(lambda: m.SearchByProjection(Fs[0], MPs[0], 3.0, False, 0.0, 0.8)),
            "search_by_projection_kf_ms": lat(lambda: m.SearchByProjectionKF(Fs[0], P1, 15.0, True))}
+    # resident form: the Frame side stays on the device (frame 0 of the batch extracted above), only the map
+    # points go up and the matches come down; beside it the host-array call on the same frame
+    k0, d0, _ = ex.fetch(0)
+    grid = {"minx": 0.0, "miny": 0.0, "gw_inv": gw_inv, "gh_inv": gh_inv, "gcols": 64, "grows": 48, "scale": ex.mvScaleFactor}
+    F0 = dict(grid, kx=k0["x"].copy(), ky=k0["y"].copy(), koct=k0["octave"].copy(), kangle=k0["angle"].copy(), desc=d0.copy())
+    MP0 = pkg.synth.projection_problem(F0, 1500, seed=777)
+    one["search_by_projection_resident_ms"] = lat(lambda: m.SearchByProjectionResident(ex, [0], grid, [MP0], 3.0, False, 0.0, 0.8))
+    one["search_by_projection_same_frame_host_arrays_ms"] = lat(lambda: m.SearchByProjection(F0, MP0, 3.0, False, 0.0, 0.8))
     # ---- the widened matcher entry points, 32 problems per call through the C ABI
     def timed(fn, nprob, reps=5):
         fn()

@@ -412,6 +412,7 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_units(Tables T, const Uni
                 if (lane < cnt) {
                     const int ce = src[lane];
                     const int idx = ce & 0x7FFF;
+                    ORBX_DCHECK(idx - 3 * tp - 3 >= 0 && idx + 3 * tp + 3 < map_bytes);
                     const uint8_t* p = tile + idx;
                     const int v = p[0];
                     const int sgn = (ce & 0x8000) ? -1 : 1;
@@ -433,6 +434,7 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_units(Tables T, const Uni
                 int idx = 0;
                 if (lane < cnt) {
                     idx = src[lane];
+                    ORBX_DCHECK(idx - 3 * tp - 3 >= 0 && idx + 3 * tp + 3 < map_bytes);
                     const uint8_t* p = tile + idx;
                     const int v = p[0];
                     /* one IMAD per ring pixel: upper half = (v+th) - r  (negative <=> brighter),
@@ -451,6 +453,7 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_units(Tables T, const Uni
                     idx |= dark ? 0x8000 : 0;                     /* tile index < 2^15 (checked on the host) */
                 }
                 const unsigned bal = __ballot_sync(0xffffffffu, corner);
+                ORBX_DCHECK(ncq + __popc(bal) <= FAST_CQ);
                 if (corner) cq[ncq + __popc(bal & lt_mask)] = (unsigned short)idx;
                 ncq += __popc(bal);
                 __syncwarp();
@@ -469,6 +472,7 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_units(Tables T, const Uni
                     if (lane >= d) incl += t;
                 }
                 const int total = __shfl_sync(0xffffffffu, incl, 31);
+                ORBX_DCHECK(nq + total <= FAST_WQ);
                 int off = nq + incl - k;
                 const uint32_t base = ent & 0xFFFFu;
                 while (m) {
@@ -503,6 +507,7 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_units(Tables T, const Uni
                     }
                     const unsigned bal = __ballot_sync(0xffffffffu, (pa | pb) != 0u);
                     if (bal) {
+                        ORBX_DCHECK(neq + __popc(bal) <= FAST_EQ);
                         if (pa | pb) {
                             /* bits 7/15/23/31 -> 4-bit mask: the multiplier moves them to bits 28..31 */
                             const uint32_t m8 = ((pa * 0x00204081u) >> 28) | (((pb * 0x00204081u) >> 28) << 4);
@@ -537,6 +542,7 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_units(Tables T, const Uni
                 if (rgt) mx = mx && v > sp[1] && v > sp[-tp + 1] && v > sp[tp + 1];
                 if (mx) {
                     const int pos = atomicAdd(&s_cnt[k], 1);
+                    ORBX_DCHECK(k >= 0 && k < ncell && (size_t)cells[U.cell0 + k].slot_off + pos < slots_per_frame);
                     bucket[cells[U.cell0 + k].slot_off + pos] =
                         (uint32_t)(t - shift + U.offx0) | ((uint32_t)(yt + U.offy) << 12) | ((uint32_t)v << 24);
                 }
@@ -802,6 +808,7 @@ __global__ void __launch_bounds__(OCT_THREADS) k_octree(Tables T, const Cell* __
         }
     }
     if (tid == 0) cand_count[f * T.nlevels + level] = ncand;
+    ORBX_DCHECK(ncand <= Lv.cand_cap && ncl <= 4 * maxn);
     __syncthreads();
 
     uint32_t* psel = sel + (size_t)f * sel_per_frame + Lv.sel_off;
@@ -917,6 +924,7 @@ __global__ void __launch_bounds__(OCT_THREADS) k_octree(Tables T, const Cell* __
             L = totC + totStay;
             nE = totE;
             cur = nxt;
+            ORBX_DCHECK(L <= maxn && nE <= maxn);
             if (L >= N || L == prevL) finish = true;
             else if (L + nE * 3 > N) final_phase = true;
         } else {
@@ -1031,6 +1039,7 @@ __global__ void __launch_bounds__(OCT_THREADS) k_octree(Tables T, const Cell* __
             nE = totE;
             ecur = enx;
             cur = nxt;
+            ORBX_DCHECK(L <= maxn && nE <= maxn);
             if (L >= N || L == prevL) finish = true;
         }
     }
@@ -1048,6 +1057,7 @@ __global__ void __launch_bounds__(OCT_THREADS) k_octree(Tables T, const Cell* __
         const uint32_t i = 0xFFFFFFFFu - (uint32_t)(S.best[p] & 0xFFFFFFFFull);
         psel[p] = pc[i];
     }
+    ORBX_DCHECK(L <= Lv.sel_cap);
     if (tid == 0) sel_count[f * T.nlevels + level] = L;
 }
 
@@ -1402,6 +1412,7 @@ __global__ void __launch_bounds__(32 * OD_WARPS) k_orient_describe(Tables T, con
         if (my_l != 0) { fx = __fmul_rn(fx, L.scale); fy = __fmul_rn(fy, L.scale); }
         kp.x = fx; kp.y = fy; kp.size = L.patch_size; kp.angle = angle; kp.response = (float)(int)(my_e >> 24);
         kp.octave = my_l; kp.class_id = -1;
+        ORBX_DCHECK(my_d >= 0 && my_d < kcap);
         kps[(size_t)f * kcap + my_d] = kp;
     }
     /* ---- 3. rBRIEF (reference src/cuda/Orb_gpu.cu:311-350): lane = descriptor byte */
@@ -1431,6 +1442,13 @@ __global__ void __launch_bounds__(32 * OD_WARPS) k_orient_describe(Tables T, con
             const uint32_t iy1 = rint_bits(__fadd_rn(__fmul_rn(pp.z, b), __fmul_rn(pp.w, a)));
             const uint32_t ix1 = rint_bits(__fsub_rn(__fmul_rn(pp.z, a), __fmul_rn(pp.w, b)));
             uint32_t t0, t1;
+#ifdef ORBX_CHECKS
+            {
+                const uint32_t w0 = sb0 + (uint32_t)par * OD_WIN_SLOT;
+                const uint32_t a0 = cbase + iy0 * OD_WPB + ix0, a1 = cbase + iy1 * OD_WPB + ix1;
+                ORBX_DCHECK(a0 >= w0 && a0 < w0 + OD_WIN_BYTES && a1 >= w0 && a1 < w0 + OD_WIN_BYTES);
+            }
+#endif
             asm volatile("ld.shared.u8 %0, [%1];" : "=r"(t0) : "r"(cbase + iy0 * OD_WPB + ix0));
             asm volatile("ld.shared.u8 %0, [%1];" : "=r"(t1) : "r"(cbase + iy1 * OD_WPB + ix1));
             val |= (t0 < t1) << j;

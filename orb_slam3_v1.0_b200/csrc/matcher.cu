@@ -389,6 +389,7 @@ __global__ void __launch_bounds__(MT) k_search_by_projection(const uint8_t* __re
                 const uint32_t e0 = cell_start[ix * P.grows + r0], e1 = cell_start[ix * P.grows + r1 + 1];
                 for (uint32_t e = e0; e < e1; ++e) {
                     const int idx = csr[e];
+                    ORBX_DCHECK(e < (uint32_t)n && idx < n);
                     const int oc = KOCT(idx);
                     if (bCheckLevels && (oc < minLevel || (maxLevel >= 0 && oc > maxLevel))) continue;
                     if (!(fabsf(KX(idx) - x) < r && fabsf(KY(idx) - y) < r)) continue;

@@ -69,6 +69,24 @@ struct OrbxRange {
 #define ORBX_RANGE_CAT(a, b) ORBX_RANGE_CAT2(a, b)
 #define ORBX_RANGE(name) OrbxRange ORBX_RANGE_CAT(orbx_range_, __LINE__)(name)
 
+/* Device-side invariant checks (queue capacities, tile / list indices, gather offsets) compiled in with
+ * -DORBX_CHECKS: `make LIBDIR=../lib_checked EXTRA=-DORBX_CHECKS`; tools/checked_run.sh runs the GPU tests and
+ * tools/sanitize_run.py against that build.  compute-sanitizer is closed on this GPU pool, so these traps are the
+ * memcheck / racecheck substitute: a violated invariant prints its source line and kills the kernel (the failed
+ * launch surfaces as ORBX_ERR_CUDA at the next synchronisation).  Compiled out of the shipped library. */
+#ifdef ORBX_CHECKS
+#define ORBX_DCHECK(cond)                                                                                             \
+    do {                                                                                                              \
+        if (!(cond)) {                                                                                                \
+            printf("ORBX_DCHECK failed %s:%d: %s (block %d,%d thread %d)\n", __FILE__, __LINE__, #cond, (int)blockIdx.x, \
+                   (int)blockIdx.y, (int)threadIdx.x);                                                                \
+            __trap();                                                                                                 \
+        }                                                                                                             \
+    } while (0)
+#else
+#define ORBX_DCHECK(cond) ((void)0)
+#endif
+
 static inline int orbx_div_up(int a, int b) { return (a + b - 1) / b; }
 static inline size_t orbx_align_up(size_t a, size_t b) { return (a + b - 1) / b * b; }
 

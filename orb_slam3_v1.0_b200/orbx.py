@@ -11,7 +11,8 @@ import subprocess
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_SO = os.path.join(_HERE, "lib", "liborbx.so")
+# ORBX_LIB_DIR: load another build of the SAME library (tools/checked_run.sh: the -DORBX_CHECKS variant); default = the shipped one
+_SO = os.path.join(os.environ.get("ORBX_LIB_DIR") or os.path.join(_HERE, "lib"), "liborbx.so")
 
 KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"),
                      ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])
