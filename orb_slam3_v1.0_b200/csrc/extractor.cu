@@ -318,11 +318,15 @@ constexpr RcpTab make_rcp_tab() {
 }
 __constant__ RcpTab c_rcp = make_rcp_tab();
 
+/* TP = tile pitch in bytes as a compile-time constant (256: every ring / row offset is an immediate, index / pitch a
+ * shift), or 0 = the run-time pitch tp_rt for images whose strips are much narrower than 256 bytes */
+template <int TP>
 __global__ void __launch_bounds__(FAST_THREADS) k_fast_units(Tables T, const Unit* __restrict__ units,
                                                               const Cell* __restrict__ cells, int ncells, int ini_th,
                                                               int min_th, uint32_t* __restrict__ slots, uint32_t* scratch,
-                                                              size_t slots_per_frame, int* __restrict__ cell_count, int tp,
+                                                              size_t slots_per_frame, int* __restrict__ cell_count, int tp_rt,
                                                               int rows, int cl_cap, const ODMaps* __restrict__ maps) {
+    const int tp = TP ? TP : tp_rt;
     /* dynamic smem: tile | score (rows x tp bytes each) | per-warp queues */
     extern __shared__ __align__(128) uint8_t fsm_raw[];
     uint8_t* fsm = fsm_raw + ((128u - ((uint32_t)__cvta_generic_to_shared(fsm_raw) & 127u)) & 127u);   /* TMA destination */
@@ -552,7 +556,7 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_units(Tables T, const Uni
             if (ncorn <= cl_cap) {
                 for (int j = tid; j < ncorn; j += FAST_THREADS) {
                     const int idx = cl[j];
-                    const int yt = (int)__umulhi((unsigned)idx, rcp_tp);
+                    const int yt = TP ? idx / (TP ? TP : 1) : (int)__umulhi((unsigned)idx, rcp_tp);
                     nms(yt, idx - yt * tp);
                 }
             } else {
@@ -1681,7 +1685,8 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
         uint32_t d4[32] = {0};
         for (int r = 0; r < 31; ++r) d4[r] = (uint32_t)e->umax[r < 15 ? 15 - r : r - 15] * 0x01010101u + 0x80808080u;
         CK(cudaMemcpyToSymbol(c_d4, d4, sizeof(d4)));
-        CK_SMEM(k_orient_describe, OD_SMEM);
+        if (const char* v = getenv("ORBX_OD_PAD")) e->od_pad = std::max(0, std::min(atoi(v), 200 * 1024 - OD_SMEM));
+        CK_SMEM(k_orient_describe, OD_SMEM + e->od_pad);
     }
     CK(cudaMalloc(&e->d_pyr, pyr_bytes));
     CK(cudaMalloc(&e->d_blur, blur_bytes + 256));    /* + slack: window staging reads whole words */
@@ -1694,6 +1699,7 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
      * are ordered by strip height and launched as two groups when that buys resident CTAs:
      * cost = strip area / CTAs per SM at the group's tile size. */
     /* (a unit's tile must hold its level's TMA box = the level's tallest strip) */
+    if (e->fast_tp > 192 && e->fast_tp <= 256) e->fast_tp = 256;      /* compile-time pitch variant of the kernel (k_fast_units<256>) */
     auto need_rows = [&](const Unit& u) { return e->lv[u.level].fast_box_rows; };
     std::stable_sort(units.begin(), units.end(), [&](const Unit& a, const Unit& b) { return need_rows(a) < need_rows(b); });
     e->nunits_short = 0;
@@ -1720,7 +1726,8 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
     if ((size_t)e->fast_rows * e->fast_tp > 32767) { orbx_set_error("FAST strip %dx%d exceeds the 15-bit tile index", e->fast_tp, e->fast_rows); free_all(e); return ORBX_ERR_INVALID; }
     CK(cudaMalloc(&e->d_units, std::max<size_t>(units.size(), 1) * sizeof(Unit)));
     if (!units.empty()) CK(cudaMemcpy(e->d_units, units.data(), units.size() * sizeof(Unit), cudaMemcpyHostToDevice));
-    CK_SMEM(k_fast_units, (size_t)2 * e->fast_rows * e->fast_tp + FAST_QBYTES + 128);
+    CK_SMEM(k_fast_units<256>, (size_t)2 * e->fast_rows * e->fast_tp + FAST_QBYTES + 128);
+    CK_SMEM(k_fast_units<0>, (size_t)2 * e->fast_rows * e->fast_tp + FAST_QBYTES + 128);
     CK(cudaMalloc(&e->d_blur_tiles, blur_tiles.size() * sizeof(int4)));
     CK(cudaMalloc(&e->d_slots, std::max<size_t>(e->slots_per_frame, 1) * B * 4));
     CK(cudaMalloc(&e->d_cell_count, (size_t)std::max(e->ncells, 1) * B * 4));
@@ -1935,6 +1942,18 @@ static orbx_status enqueue_frames(orbx_extractor* e, const uint8_t* d_images, si
     dataflow = dataflow && side && !e->profiling && e->ncells > 0;
     /* latency path (small batches, captured into a graph): FAST + quadtree of level l run on branch
      * stream l as soon as level l of the pyramid exists, instead of after the whole 8-launch chain */
+    /* the FAST kernel with a compile-time tile pitch when the strips are (close to) 256 bytes wide */
+    auto launch_fast = [&](int nunits, int first, int rows, cudaStream_t sx) {
+        const size_t smem = (size_t)2 * rows * e->fast_tp + FAST_QBYTES + 128;
+        const Unit* u = static_cast<const Unit*>(e->d_units) + first;
+        if (e->fast_tp == 256)
+            k_fast_units<256><<<dim3(nunits, nb), FAST_THREADS, smem, sx>>>(T, u, e->d_cells, e->ncells, e->P.ini_th_fast, e->P.min_th_fast, e->d_slots,
+                e->d_cand, e->slots_per_frame, e->d_cell_count, e->fast_tp, rows, e->fast_cl_cap, (const ODMaps*)e->d_odmaps);
+        else
+            k_fast_units<0><<<dim3(nunits, nb), FAST_THREADS, smem, sx>>>(T, u, e->d_cells, e->ncells, e->P.ini_th_fast, e->P.min_th_fast, e->d_slots,
+                e->d_cand, e->slots_per_frame, e->d_cell_count, e->fast_tp, rows, e->fast_cl_cap, (const ODMaps*)e->d_odmaps);
+        ++launches;
+    };
     auto level_branch = [&](int l) -> orbx_status {
         cudaStream_t b = e->branch[l];
         ORBX_CUDA(cudaEventRecord(e->ev_lvl[l], st));
@@ -1942,10 +1961,7 @@ static orbx_status enqueue_frames(orbx_extractor* e, const uint8_t* d_images, si
         const int n = e->unit_hi[l] - e->unit_lo[l];
         if (n > 0) {
             const int rows = e->unit_lo[l] < e->nunits_short ? e->fast_rows_short : e->fast_rows;
-            k_fast_units<<<dim3(n, nb), FAST_THREADS, (size_t)2 * rows * e->fast_tp + FAST_QBYTES + 128, b>>>(
-                T, static_cast<const Unit*>(e->d_units) + e->unit_lo[l], e->d_cells, e->ncells, e->P.ini_th_fast, e->P.min_th_fast, e->d_slots,
-                e->d_cand, e->slots_per_frame, e->d_cell_count, e->fast_tp, rows, e->fast_cl_cap, (const ODMaps*)e->d_odmaps);
-            ++launches;
+            launch_fast(n, e->unit_lo[l], rows, b);
         }
         Tables Tl = T;
         Tl.l0 = l;
@@ -2007,12 +2023,7 @@ static orbx_status enqueue_frames(orbx_extractor* e, const uint8_t* d_images, si
         ++launches;
         return ORBX_OK;
     };
-    auto launch_fast_tall = [&](cudaStream_t sx) {
-        k_fast_units<<<dim3(e->nunits - e->nunits_short, nb), FAST_THREADS, (size_t)2 * e->fast_rows * e->fast_tp + FAST_QBYTES + 128, sx>>>(
-            T, static_cast<const Unit*>(e->d_units) + e->nunits_short, e->d_cells, e->ncells, e->P.ini_th_fast, e->P.min_th_fast, e->d_slots,
-            e->d_cand, e->slots_per_frame, e->d_cell_count, e->fast_tp, e->fast_rows, e->fast_cl_cap, (const ODMaps*)e->d_odmaps);
-        ++launches;
-    };
+    auto launch_fast_tall = [&](cudaStream_t sx) { launch_fast(e->nunits - e->nunits_short, e->nunits_short, e->fast_rows, sx); };
     if (fork_blur == 3) {
         ORBX_CUDA(cudaEventRecord(ev_fork, st));
         ORBX_CUDA(cudaStreamWaitEvent(side, ev_fork, 0));
@@ -2026,10 +2037,7 @@ static orbx_status enqueue_frames(orbx_extractor* e, const uint8_t* d_images, si
     ORBX_RANGE("ComputeKeyPointsOctTree");
     if (e->ncells > 0 && !dataflow) {
         if (e->nunits_short > 0) {
-            k_fast_units<<<dim3(e->nunits_short, nb), FAST_THREADS, (size_t)2 * e->fast_rows_short * e->fast_tp + FAST_QBYTES + 128, st>>>(
-                T, static_cast<const Unit*>(e->d_units), e->d_cells, e->ncells, e->P.ini_th_fast, e->P.min_th_fast, e->d_slots,
-                e->d_cand, e->slots_per_frame, e->d_cell_count, e->fast_tp, e->fast_rows_short, e->fast_cl_cap, (const ODMaps*)e->d_odmaps);
-            ++launches;
+            launch_fast(e->nunits_short, 0, e->fast_rows_short, st);
         }
         if (side_tall) ORBX_CUDA(cudaStreamWaitEvent(st, e->ev_join2, 0));
         else launch_fast_tall(st);
@@ -2064,7 +2072,7 @@ static orbx_status enqueue_frames(orbx_extractor* e, const uint8_t* d_images, si
     /* stage 5 */
     {
         ORBX_RANGE("computeDescriptors");
-        k_orient_describe<<<dim3(orbx_div_up((int)e->sel_per_frame, OD_WARPS * OD_KPW), nb), 32 * OD_WARPS, OD_SMEM, st>>>(
+        k_orient_describe<<<dim3(orbx_div_up((int)e->sel_per_frame, OD_WARPS * OD_KPW), nb), 32 * OD_WARPS, OD_SMEM + e->od_pad, st>>>(
             T, (const ODMaps*)e->d_odmaps, e->d_sel, e->sel_per_frame, e->d_sel_count, e->d_dest, e->d_kps, e->d_desc, e->kcap);
         ++launches;
     }

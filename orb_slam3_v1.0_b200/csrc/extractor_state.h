@@ -100,6 +100,7 @@ struct orbx_extractor {
     size_t s_fs = 0;
     int s_rs = 0, s_batch = 0;
     bool s_lap = false;
+    int od_pad = 0;                 /* extra dynamic shared memory of the describe kernel: caps its resident CTAs per SM (tuning, ORBX_OD_PAD) */
     int lanes = 2;                  /* a batch of >= 32 frames runs as up to `lanes` chunks on as many streams (ORBX_LANES); 2 and 4 give the same device-resident rate, 2 the better end-to-end rate */
     cudaStream_t lane[ORBX_MAX_LANES] = {};
     cudaEvent_t ev_lane[ORBX_MAX_LANES] = {};
