@@ -251,6 +251,12 @@ __global__ void __launch_bounds__(512) k_resize_band(LevelDev S, LevelDev D, int
 #define FAST_WARP_QBYTES (FAST_EQ * 4 + (FAST_WQ + FAST_CQ) * 2)
 #define FAST_QBYTES ((FAST_THREADS / 32) * FAST_WARP_QBYTES + 2 * FAST_CL * 2)
 #define FAST_MAX_ROWS 76      /* cells are at most 69+6 px high (nRows==1 levels) */
+#ifndef FAST_TALL_ROWS
+#define FAST_TALL_ROWS 48     /* strips taller than this get units of at most FAST_TALL_UC cells */
+#endif
+#ifndef FAST_TALL_UC
+#define FAST_TALL_UC 3
+#endif
 
 struct Unit {
     short level, x0, y0, tw, th, ncell, wc, pad;   /* tile origin (ROI coords), tile size, cells, wCell */
@@ -360,7 +366,10 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_units(Tables T, const Uni
             asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(L.fast_box_rows * tp) : "memory");
             od_tma3((uint32_t)__cvta_generic_to_shared(tile), &maps->fast[U.level], ORBX_XOFF + U.x0 - shift, ORBX_EDGE + U.y0, f, bar);
         }
-        for (int i = tid; i < U.th * WP; i += FAST_THREADS) score32[i] = 0;
+        {   /* rows x tp bytes, both multiples of 16 */
+            uint4* s4 = reinterpret_cast<uint4*>(score);
+            for (int i = tid; i < (U.th * WP + 3) / 4; i += FAST_THREADS) s4[i] = make_uint4(0u, 0u, 0u, 0u);
+        }
         if (tid < FAST_UC) s_cnt[tid] = 0;
         if (tid < 3) s_ncl[tid] = 0;
         __syncthreads();            /* barrier init visible to all waiters */
@@ -452,6 +461,8 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_units(Tables T, const Uni
                     FAST_RING(-3 * tp);     FAST_RING(-3 * tp - 1);  FAST_RING(-2 * tp - 2);  FAST_RING(-tp - 3);
                     FAST_RING(-3);          FAST_RING(tp - 3);       FAST_RING(2 * tp - 2);   FAST_RING(3 * tp - 1);
 #undef FAST_RING
+                    /* (an 8 KB bit table indexed by the mask instead of the two bit-trick chains was measured: 0.565 ->
+                     * 0.572 ms, the two L1 loads cost more latency than the ~20 ALU instructions they save) */
                     const bool dark = has9(acc & 0xFFFFu);
                     corner = dark || has9(acc >> 16);             /* bright and dark are mutually exclusive */
                     idx |= dark ? 0x8000 : 0;                     /* tile index < 2^15 (checked on the host) */
@@ -1605,7 +1616,10 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
                 /* FAST units: the row's cells in runs of <= FAST_UC, evenly sized */
                 const int nrow = (int)e->cells.size() - row_first;
                 /* a unit's strip (cells + 6 px overlap + up to 15 px of TMA alignment) must fit the 256-byte box */
-                const int ucap = std::max(1, std::min(FAST_UC, (256 - 15 - 6) / std::max(wCell, 1)));
+                int ucap = std::max(1, std::min(FAST_UC, (256 - 15 - 6) / std::max(wCell, 1)));
+                /* tall cells (the top levels: few cell rows, up to 69 + 6 px high): narrower units, so that the tile +
+                 * score map of a CTA stay near the short strips' size and as many CTAs fit an SM */
+                if (hCell + 6 > FAST_TALL_ROWS) ucap = std::min(ucap, FAST_TALL_UC);
                 const int nun = orbx_div_up(nrow, ucap);
                 for (int u = 0, k = 0; u < nun; ++u) {
                     const int nc = (nrow - k + (nun - u) - 1) / (nun - u);
@@ -1699,21 +1713,31 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
      * are ordered by strip height and launched as two groups when that buys resident CTAs:
      * cost = strip area / CTAs per SM at the group's tile size. */
     /* (a unit's tile must hold its level's TMA box = the level's tallest strip) */
-    if (e->fast_tp > 192 && e->fast_tp <= 256) e->fast_tp = 256;      /* compile-time pitch variant of the kernel (k_fast_units<256>) */
     auto need_rows = [&](const Unit& u) { return e->lv[u.level].fast_box_rows; };
+    auto unit_tp = [&](const Unit& u) { return (int)orbx_align_up(u.tw + 15, 16); };
+    /* strips (close to) 256 bytes wide use the compile-time pitch variant of the kernel (k_fast_units<256>) */
+    auto round_tp = [](int tp) { return (tp > 192 && tp <= 256) ? 256 : tp; };
     std::stable_sort(units.begin(), units.end(), [&](const Unit& a, const Unit& b) { return need_rows(a) < need_rows(b); });
     e->nunits_short = 0;
     e->fast_rows_short = e->fast_rows;
+    e->fast_tp = e->fast_tp_tall = round_tp(e->fast_tp);
     if (!units.empty()) {
-        auto ctas = [&](int rows) { return std::max<size_t>(1, (size_t)(227 * 1024) / ((size_t)2 * rows * e->fast_tp + FAST_QBYTES + 128 + 1024)); };
+        const size_t nu = units.size();
+        std::vector<int> pre(nu + 1, 16), suf(nu + 1, 16);          /* widest tile among units [0, i) / [i, nu) */
+        for (size_t i = 0; i < nu; ++i) pre[i + 1] = std::max(pre[i], unit_tp(units[i]));
+        for (size_t i = nu; i-- > 0;) suf[i] = std::max(suf[i + 1], unit_tp(units[i]));
+        auto ctas = [&](int rows, int tp) { return std::max<size_t>(1, (size_t)(227 * 1024) / ((size_t)2 * rows * tp + FAST_QBYTES + 128 + 1024)); };
         double head = 0, total = 0;
         for (const Unit& u : units) total += (double)u.th * u.tw;
-        double best = total / ctas(e->fast_rows);
-        for (size_t i = 1; i < units.size(); ++i) {
+        double best = total / ctas(e->fast_rows, round_tp(pre[nu]));
+        for (size_t i = 1; i < nu; ++i) {
             head += (double)units[i - 1].th * units[i - 1].tw;
             if (need_rows(units[i]) == need_rows(units[i - 1])) continue;
-            const double c = head / ctas(need_rows(units[i - 1])) + (total - head) / ctas(e->fast_rows);
-            if (c < best * 0.97) { best = c; e->nunits_short = (int)i; e->fast_rows_short = need_rows(units[i - 1]); }
+            const double c = head / ctas(need_rows(units[i - 1]), round_tp(pre[i])) + (total - head) / ctas(e->fast_rows, round_tp(suf[i]));
+            if (c < best * 0.97) {
+                best = c; e->nunits_short = (int)i; e->fast_rows_short = need_rows(units[i - 1]);
+                e->fast_tp = round_tp(pre[i]); e->fast_tp_tall = round_tp(suf[i]);
+            }
         }
     }
     for (int l = 0; l < ORBX_MAX_LEVELS; ++l) { e->unit_lo[l] = 0; e->unit_hi[l] = 0; }
@@ -1722,12 +1746,15 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
         if (e->unit_hi[l] == e->unit_lo[l]) e->unit_lo[l] = (int)i;
         e->unit_hi[l] = (int)i + 1;
     }
-    if (e->fast_tp > 256) { orbx_set_error("FAST strip width %d exceeds the 256-byte TMA box", e->fast_tp); free_all(e); return ORBX_ERR_INVALID; }
-    if ((size_t)e->fast_rows * e->fast_tp > 32767) { orbx_set_error("FAST strip %dx%d exceeds the 15-bit tile index", e->fast_tp, e->fast_rows); free_all(e); return ORBX_ERR_INVALID; }
+    if (std::max(e->fast_tp, e->fast_tp_tall) > 256) { orbx_set_error("FAST strip width %d exceeds the 256-byte TMA box", std::max(e->fast_tp, e->fast_tp_tall)); free_all(e); return ORBX_ERR_INVALID; }
+    if ((size_t)e->fast_rows * e->fast_tp_tall > 32767 || (size_t)e->fast_rows_short * e->fast_tp > 32767) { orbx_set_error("FAST strip %dx%d exceeds the 15-bit tile index", e->fast_tp_tall, e->fast_rows); free_all(e); return ORBX_ERR_INVALID; }
     CK(cudaMalloc(&e->d_units, std::max<size_t>(units.size(), 1) * sizeof(Unit)));
     if (!units.empty()) CK(cudaMemcpy(e->d_units, units.data(), units.size() * sizeof(Unit), cudaMemcpyHostToDevice));
-    CK_SMEM(k_fast_units<256>, (size_t)2 * e->fast_rows * e->fast_tp + FAST_QBYTES + 128);
-    CK_SMEM(k_fast_units<0>, (size_t)2 * e->fast_rows * e->fast_tp + FAST_QBYTES + 128);
+    {
+        const size_t need = std::max((size_t)2 * e->fast_rows * e->fast_tp_tall, (size_t)2 * e->fast_rows_short * e->fast_tp) + FAST_QBYTES + 128;
+        CK_SMEM(k_fast_units<256>, need);
+        CK_SMEM(k_fast_units<0>, need);
+    }
     CK(cudaMalloc(&e->d_blur_tiles, blur_tiles.size() * sizeof(int4)));
     CK(cudaMalloc(&e->d_slots, std::max<size_t>(e->slots_per_frame, 1) * B * 4));
     CK(cudaMalloc(&e->d_cell_count, (size_t)std::max(e->ncells, 1) * B * 4));
@@ -1884,11 +1911,12 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
                                                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
                                                   CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
                 if (r != CUDA_SUCCESS) { orbx_set_error("cuTensorMapEncodeTiled(pyramid level %d) -> %d", l, (int)r); free_all(e); return ORBX_ERR_CUDA; }
-                const cuuint32_t fbox[3] = {(cuuint32_t)e->fast_tp, (cuuint32_t)std::max(L.fast_box_rows, 1), 1};
+                const int ltp = (e->unit_hi[l] > e->unit_lo[l] && e->unit_lo[l] < e->nunits_short) ? e->fast_tp : e->fast_tp_tall;   /* the level's launch group */
+                const cuuint32_t fbox[3] = {(cuuint32_t)ltp, (cuuint32_t)std::max(L.fast_box_rows, 1), 1};
                 const CUresult r2 = ((EncodeFn)fn)(&M->fast[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, L.base, dims, strides, fbox, estr,
                                                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
                                                    CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-                if (r2 != CUDA_SUCCESS) { orbx_set_error("cuTensorMapEncodeTiled(FAST strip level %d, box %dx%d) -> %d", l, e->fast_tp, L.fast_box_rows, (int)r2); free_all(e); return ORBX_ERR_CUDA; }
+                if (r2 != CUDA_SUCCESS) { orbx_set_error("cuTensorMapEncodeTiled(FAST strip level %d, box %dx%d) -> %d", l, ltp, L.fast_box_rows, (int)r2); free_all(e); return ORBX_ERR_CUDA; }
             }
         }
         CK(cudaMalloc(&e->d_odmaps, sizeof(ODMaps)));
@@ -1944,14 +1972,15 @@ static orbx_status enqueue_frames(orbx_extractor* e, const uint8_t* d_images, si
      * stream l as soon as level l of the pyramid exists, instead of after the whole 8-launch chain */
     /* the FAST kernel with a compile-time tile pitch when the strips are (close to) 256 bytes wide */
     auto launch_fast = [&](int nunits, int first, int rows, cudaStream_t sx) {
-        const size_t smem = (size_t)2 * rows * e->fast_tp + FAST_QBYTES + 128;
+        const int tp = first < e->nunits_short ? e->fast_tp : e->fast_tp_tall;       /* the launch group's tile pitch */
+        const size_t smem = (size_t)2 * rows * tp + FAST_QBYTES + 128;
         const Unit* u = static_cast<const Unit*>(e->d_units) + first;
-        if (e->fast_tp == 256)
+        if (tp == 256)
             k_fast_units<256><<<dim3(nunits, nb), FAST_THREADS, smem, sx>>>(T, u, e->d_cells, e->ncells, e->P.ini_th_fast, e->P.min_th_fast, e->d_slots,
-                e->d_cand, e->slots_per_frame, e->d_cell_count, e->fast_tp, rows, e->fast_cl_cap, (const ODMaps*)e->d_odmaps);
+                e->d_cand, e->slots_per_frame, e->d_cell_count, tp, rows, e->fast_cl_cap, (const ODMaps*)e->d_odmaps);
         else
             k_fast_units<0><<<dim3(nunits, nb), FAST_THREADS, smem, sx>>>(T, u, e->d_cells, e->ncells, e->P.ini_th_fast, e->P.min_th_fast, e->d_slots,
-                e->d_cand, e->slots_per_frame, e->d_cell_count, e->fast_tp, rows, e->fast_cl_cap, (const ODMaps*)e->d_odmaps);
+                e->d_cand, e->slots_per_frame, e->d_cell_count, tp, rows, e->fast_cl_cap, (const ODMaps*)e->d_odmaps);
         ++launches;
     };
     auto level_branch = [&](int l) -> orbx_status {

@@ -69,7 +69,8 @@ struct orbx_extractor {
     int kcap = 0, maxn = 0;
     size_t oct_smem = 0;
     int nblur_tiles = 0;
-    int fast_tp = 8, fast_rows = 8, fast_list_cap = 2;
+    int fast_tp = 8, fast_rows = 8, fast_list_cap = 2;   /* tile pitch of the short-strip launch group (of every unit when there is one group) */
+    int fast_tp_tall = 8;                                /* tile pitch of the tall-strip launch group */
     int nunits = 0;
     int nunits_short = 0, fast_rows_short = 8;   /* units [0, nunits_short) are launched with the smaller tile */
     int fast_cl_cap = 1024;         /* FAST corner-list entries in use (<= FAST_CL) */
