@@ -405,7 +405,9 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_units(Tables T, const Uni
             k0 = k1;
             if (thi <= tlo) continue;
             /* the region is walked in aligned 8-byte units (two words = 8 px per thread and step):
-             * flat (row, pair) walk with stride FAST_THREADS, advanced incrementally */
+             * flat (row, pair) walk with stride FAST_THREADS, advanced incrementally.  (16 px per step with 128-bit row
+             * loads was measured: 0.547 -> 0.584 ms; its 16-bit survivor masks only fit the survivor queue when entries are
+             * expanded 16 at a time, and the half-empty expansion scans cost more than the wider loads save) */
             const int p0 = tlo >> 3, rp = ((thi - 1) >> 3) - p0 + 1;
             const unsigned long long mf64 = ~0ull << (8 * (tlo & 7)), ml64 = ~0ull >> (8 * (7 - ((thi - 1) & 7)));
             const uint32_t mfA = (uint32_t)mf64, mfB = (uint32_t)(mf64 >> 32), mlA = (uint32_t)ml64, mlB = (uint32_t)(ml64 >> 32);
