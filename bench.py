@@ -26,7 +26,7 @@ sys.path.insert(0, ROOT)
 
 W, H, NFEAT, NLEVELS, SCALE, INI_TH, MIN_TH = 752, 480, 1000, 8, 1.2, 20, 7
 BATCH = 256                      # frames per launch per GPU (128 stereo pairs)
-TRAFFIC_FILE = "r1_traffic.json"   # ncu --set full capture the roofline's DRAM-traffic figure is read from (not measured in the run)
+TRAFFIC_FILE = "r2_traffic.json"   # ncu --set full capture the roofline's DRAM-traffic figure is read from (not measured in the run)
 # what each stage's kernel is limited by according to that capture (the HBM roofline is the contract's denominator)
 LIMITER = {"k_fast_units": "instruction issue + shared-memory occupancy", "k_resize_band": "instruction issue + bulk-copy wait",
            "k_blur7": "instruction issue (DRAM ~50 % of peak)", "k_orient_describe": "DRAM sectors (2x over-fetch) + shared-memory gathers",

@@ -17,7 +17,8 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--batch", type=int, default=256)
 ap.add_argument("--steps", type=int, default=3)
 ap.add_argument("--stereo", action="store_true")
-ap.add_argument("--knn", type=int, default=0, help="queries (x 64 database rows each)")
+ap.add_argument("--knn", type=int, default=0, help="queries (x 64 database rows each unless --knn-rows)")
+ap.add_argument("--knn-rows", type=int, default=0, help="database rows of the 2-NN launch")
 ap.add_argument("--matcher", action="store_true", help="one batched call of every matcher entry point")
 a = ap.parse_args()
 pkg = orbx_pkg.load()
@@ -42,7 +43,11 @@ n, _ = ex.counts(a.batch)
 print("keypoints/frame", float(n.mean()), "launches/step", ex.last_launches() + 2 * int(a.stereo))
 if a.knn:
     m = ox.ORBmatcher()
-    q, db, _ = pkg.synth.descriptor_sets(a.knn, a.knn * 64, seed=5)
+    if a.knn_rows:          # big shapes: uniform random bits are enough for a profile
+        rng = np.random.default_rng(5)
+        q = rng.integers(0, 256, (a.knn, 32), dtype=np.uint8); db = rng.integers(0, 256, (a.knn_rows, 32), dtype=np.uint8)
+    else:
+        q, db, _ = pkg.synth.descriptor_sets(a.knn, a.knn * 64, seed=5)
     d1, i1, d2, i2, ps = m.knn2(q, db, 0.8)
     print("knn pass rate", float(ps.mean()))
 if a.matcher:
