@@ -248,9 +248,12 @@ struct SbpProb {
     unsigned long long mflag, mx, my, mlevel, maux, mdepth, mdesc;
     unsigned long long uright, mxr, mobs;                               /* stereo gate / per-point Observations() > 0; ~0 = absent */
     unsigned long long out_match;                                       /* offset into the output arena */
+    unsigned long long out_choice;                                      /* per map point: keypoint chosen at its last evaluation or -1 (scratch in the output arena) */
     /* resident mode: the Frame side is read in place from an extractor's device buffers (absolute addresses) */
     unsigned long long abs_kps, abs_desc, abs_n, abs_uright;            /* orbx_keypoint records, descriptors, keypoint count, mvuRight (0 = none) */
-    int resident, pad2;
+    unsigned long long n_smem_words_before_stage;                       /* 32-bit words of the un-staged shared-memory layout, rounded to 16 bytes */
+    int resident;
+    int staged;                     /* the Frame side (keypoint records + descriptors) is copied to shared memory once */
 };
 
 /* One CTA per problem.
@@ -262,6 +265,10 @@ struct SbpProb {
  *     A map point without observations assigns without blocking (src/ORBmatcher.cc:77-79): the
  *     keypoint finally holds its blocker, else the LAST such point that chose it; every accepted
  *     map point of the final round counts in nmatches.
+ *     A round only RE-EVALUATES the map points whose window of grid cells holds a keypoint whose blocker changed in
+ *     the previous round (per-cell change flags, double-buffered); every other map point re-applies the choice it
+ *     remembered -- it would see the same blockers and decide the same -- so the rounds after the first cost a
+ *     fraction of it.
  *  3. KeyFrame overload: rotation histogram + ComputeThreeMaxima on the final matches.
  * Candidate order of the reference (cell columns, then rows, then insertion order) only matters
  * for ties; it is carried in the low bits of the 64-bit keys (dist << 32 | CSR position). */
@@ -311,6 +318,14 @@ __global__ void __launch_bounds__(MT) k_search_by_projection(const uint8_t* __re
     uint32_t* owner_b = owner_a + n;                  /* [n] */
     uint32_t* last_nb = owner_b + n;                  /* [n] last map point WITHOUT observations that chose the keypoint, + 1 */
     unsigned short* csr = reinterpret_cast<unsigned short*>(last_nb + n);   /* [n] */
+    unsigned short* kcell = csr + n;                  /* [n] cell (column-major) of keypoint i, 0xFFFF outside the grid */
+    uint8_t* chg = reinterpret_cast<uint8_t*>(kcell + n);                   /* [2][ncell] a keypoint of the cell changed blocker in the last round */
+    /* staged Frame side: per keypoint {x, y, octave | claimed << 16, mvuRight} and the 32-byte descriptor.  Every
+     * candidate of every map point in every round reads them: from shared memory the dependent-load chain of a candidate
+     * is ~30 cycles instead of several hundred (one problem = one CTA, so latency is all there is to hide) */
+    float4* skp = reinterpret_cast<float4*>(sm + P.n_smem_words_before_stage);
+    uint4* sdesc = reinterpret_cast<uint4*>(skp + n);
+    int* choice = reinterpret_cast<int*>(out + P.out_choice);
 
     /* ---- 1. grid: PosInGrid + AssignFeaturesToGrid (reference src/Frame.cc:157-176, 470-480) */
     for (int i = tid; i <= ncell; i += MT) cell_start[i] = 0;
@@ -333,7 +348,16 @@ __global__ void __launch_bounds__(MT) k_search_by_projection(const uint8_t* __re
         const int px = (int)roundf((KX(i) - P.minx) * P.gw_inv);
         const int py = (int)roundf((KY(i) - P.miny) * P.gh_inv);
         const int lin = py * P.gcols + px;
-        if (lin >= 0 && lin < ncell) csr[atomicAdd(&cell_fill[(lin % P.gcols) * P.grows + lin / P.gcols], 1u)] = (unsigned short)i;
+        const bool ing = lin >= 0 && lin < ncell;
+        kcell[i] = ing ? (unsigned short)((lin % P.gcols) * P.grows + lin / P.gcols) : (unsigned short)0xFFFFu;
+        if (ing) csr[atomicAdd(&cell_fill[(lin % P.gcols) * P.grows + lin / P.gcols], 1u)] = (unsigned short)i;
+    }
+    for (int i = tid; i < nmp; i += MT) choice[i] = -1;
+    const bool staged = P.staged != 0;
+    if (staged) {
+        for (int i = tid; i < n; i += MT)
+            skp[i] = make_float4(KX(i), KY(i), __int_as_float(KOCT(i) | ((int)(claimed[i] != 0) << 16)), uright ? uright[i] : -1.f);
+        for (int i = tid; i < 2 * n; i += MT) sdesc[i] = __ldg(kdesc + i);
     }
     for (int i = tid; i < n; i += MT) owner_a[i] = 0xFFFFFFFFu;
     __syncthreads();
@@ -356,9 +380,16 @@ __global__ void __launch_bounds__(MT) k_search_by_projection(const uint8_t* __re
     const bool bFactor = P.th != 1.0f;
     for (int round = 0; round <= nmp; ++round) {
         for (int i = tid; i < n; i += MT) { cur[i] = 0xFFFFFFFFu; last_nb[i] = 0u; }
+        const uint8_t* chg_r = chg + (round & 1) * ncell;        /* flags of the previous round */
+        uint8_t* chg_w = chg + ((round + 1) & 1) * ncell;        /* written at the end of this one */
+        for (int i = tid; i < ncell; i += MT) chg_w[i] = 0;
         if (tid == 0) s_count = 0;
         __syncthreads();
         int accepted = 0;
+        auto apply = [&](int i, int bestIdx) {
+            if (!mobs || mobs[i]) atomicMin(&cur[bestIdx], (uint32_t)i);
+            else atomicMax(&last_nb[bestIdx], (uint32_t)i + 1u);
+        };
         for (int i = tid; i < nmp; i += MT) {
             if (!mflag[i]) continue;
             const int level = mlevel[i];
@@ -384,6 +415,17 @@ __global__ void __launch_bounds__(MT) k_search_by_projection(const uint8_t* __re
             if (r0 >= P.grows) continue;
             const int r1 = min(P.grows - 1, (int)ceilf((y - P.miny + r) * P.gh_inv));
             if (r1 < 0) continue;
+            if (round > 0) {                                       /* nothing changed in the window: same blockers, same decision */
+                bool dirty = false;
+                for (int ix = c0; ix <= c1; ++ix)
+                    for (int iy = r0; iy <= r1; ++iy) dirty |= chg_r[ix * P.grows + iy] != 0;
+                if (!dirty) {
+                    const int b = choice[i];
+                    if (b >= 0) { ++accepted; apply(i, b); }
+                    continue;
+                }
+            }
+            choice[i] = -1;
             const bool bCheckLevels = (minLevel > 0) || (maxLevel >= 0);
             const uint4 q0 = __ldg(mdesc + 2 * i), q1 = __ldg(mdesc + 2 * i + 1);
             unsigned long long b1 = ~0ull, b2 = ~0ull;
@@ -392,15 +434,23 @@ __global__ void __launch_bounds__(MT) k_search_by_projection(const uint8_t* __re
                 for (uint32_t e = e0; e < e1; ++e) {
                     const int idx = csr[e];
                     ORBX_DCHECK(e < (uint32_t)n && idx < n);
-                    const int oc = KOCT(idx);
-                    if (bCheckLevels && (oc < minLevel || (maxLevel >= 0 && oc > maxLevel))) continue;
-                    if (!(fabsf(KX(idx) - x) < r && fabsf(KY(idx) - y) < r)) continue;
-                    if (claimed[idx] || prev[idx] < (uint32_t)i) continue;
-                    if (uright) {                                   /* :81-86, F->Nleft == -1 && mvuRight[idx] > 0 */
-                        const float ur = uright[idx];
-                        if (ur > 0.f && fabsf(mxr[i] - ur) > r) continue;
+                    float kxv, kyv, ur;
+                    int oc;
+                    bool cl;
+                    if (staged) {
+                        const float4 kp = skp[idx];
+                        kxv = kp.x; kyv = kp.y; ur = kp.w;
+                        const int oc_cl = __float_as_int(kp.z);
+                        oc = oc_cl & 0xFFFF; cl = (oc_cl >> 16) != 0;
+                    } else {
+                        kxv = KX(idx); kyv = KY(idx); oc = KOCT(idx); cl = claimed[idx] != 0; ur = uright ? uright[idx] : -1.f;
                     }
-                    const int dist = hamming256(q0, q1, __ldg(kdesc + 2 * idx), __ldg(kdesc + 2 * idx + 1));
+                    if (bCheckLevels && (oc < minLevel || (maxLevel >= 0 && oc > maxLevel))) continue;
+                    if (!(fabsf(kxv - x) < r && fabsf(kyv - y) < r)) continue;
+                    if (cl || prev[idx] < (uint32_t)i) continue;
+                    if (uright && ur > 0.f && fabsf(mxr[i] - ur) > r) continue;   /* :81-86, F->Nleft == -1 && mvuRight[idx] > 0 */
+                    const int dist = staged ? hamming256(q0, q1, sdesc[2 * idx], sdesc[2 * idx + 1])
+                                            : hamming256(q0, q1, __ldg(kdesc + 2 * idx), __ldg(kdesc + 2 * idx + 1));
                     if (dist >= 256) continue;                      /* bestDist / bestDist2 start at 256, strict < */
                     const unsigned long long key = ((unsigned long long)dist << 32) | e;
                     if (key < b1) { b2 = b1; b1 = key; }
@@ -420,14 +470,18 @@ __global__ void __launch_bounds__(MT) k_search_by_projection(const uint8_t* __re
             }
             if (accept) {
                 ++accepted;
-                if (!mobs || mobs[i]) atomicMin(&cur[bestIdx], (uint32_t)i);
-                else atomicMax(&last_nb[bestIdx], (uint32_t)i + 1u);
+                choice[i] = bestIdx;
+                apply(i, bestIdx);
             }
         }
         if (accepted) atomicAdd(&s_count, accepted);
         __syncthreads();
         int changed = 0;
-        for (int i = tid; i < n; i += MT) changed |= (cur[i] != prev[i]);
+        for (int i = tid; i < n; i += MT) {
+            const bool c = cur[i] != prev[i];
+            changed |= c;
+            if (c && kcell[i] != 0xFFFFu) chg_w[kcell[i]] = 1;
+        }
         uint32_t* t = prev; prev = cur; cur = t;
         if (!__syncthreads_or(changed)) break;
     }
@@ -533,7 +587,14 @@ static orbx_status run_sbp(orbx_matcher* m, int nprob, const orbx_frame_view* F,
         for (int i = 0; i < nmp; ++i)
             if (lv[i] < 0 || lv[i] >= f.nlevels) { orbx_set_error("problem %d: map point %d level %d outside [0,%d)", p, i, lv[i], f.nlevels); return ORBX_ERR_INVALID; }
         P.out_match = out.add(nullptr, 4 * (size_t)f.n);
-        smem = std::max(smem, (size_t)4 * (2 * (size_t)f.gcols * f.grows + 1 + 3 * (size_t)f.n) + 2 * (size_t)f.n + 16);
+        P.out_choice = out.add(nullptr, 4 * (size_t)nmp);
+        {
+            const size_t base = orbx_align_up((size_t)4 * (2 * (size_t)f.gcols * f.grows + 1 + 3 * (size_t)f.n) + 4 * (size_t)f.n + 2 * (size_t)f.gcols * f.grows + 16, 16);
+            const size_t with = base + 48 * (size_t)f.n;              /* + float4 record and 32-byte descriptor per keypoint */
+            P.n_smem_words_before_stage = base / 4;
+            P.staged = with <= 160 * 1024;
+            smem = std::max(smem, P.staged ? with : base);
+        }
     }
     const size_t probs_off = in.add(probs.data(), sizeof(SbpProb) * (size_t)nprob);
     const size_t counts_off = out.add(nullptr, 4 * (size_t)nprob);
@@ -640,8 +701,12 @@ static orbx_status run_sbp_resident(orbx_matcher* m, orbx_extractor* e, int npro
         for (int i = 0; i < nmp; ++i)
             if (lv[i] < 0 || lv[i] >= G->nlevels) { orbx_set_error("problem %d: map point %d level %d outside [0,%d)", p, i, lv[i], G->nlevels); return ORBX_ERR_INVALID; }
         P.out_match = out.add(nullptr, 4 * (size_t)kcap);
+        P.out_choice = out.add(nullptr, 4 * (size_t)nmp);
     }
-    const size_t smem = (size_t)4 * (2 * (size_t)G->gcols * G->grows + 1 + 3 * (size_t)kcap) + 2 * (size_t)kcap + 16;
+    const size_t smem_base = orbx_align_up((size_t)4 * (2 * (size_t)G->gcols * G->grows + 1 + 3 * (size_t)kcap) + 4 * (size_t)kcap + 2 * (size_t)G->gcols * G->grows + 16, 16);
+    const bool stage = smem_base + 48 * (size_t)kcap <= 160 * 1024;
+    const size_t smem = stage ? smem_base + 48 * (size_t)kcap : smem_base;
+    for (SbpProb& P : probs) { P.n_smem_words_before_stage = smem_base / 4; P.staged = stage; }
     const size_t probs_off = in.add(probs.data(), sizeof(SbpProb) * (size_t)nprob);
     const size_t counts_off = out.add(nullptr, 4 * (size_t)nprob);
     if (smem > 200 * 1024) { orbx_set_error("frame grid + keypoints need %zu B of shared memory (> 200 KB)", smem); return ORBX_ERR_INVALID; }
