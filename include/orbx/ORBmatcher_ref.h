@@ -19,17 +19,19 @@
  * matrix / row (default: x.data, which fits cv::Mat; for the fork's cv::cuda::HostMem add an overload
  * returning x.createMatHeader().data before including this header).
  *
- * Covered: DescriptorDistance, SearchByProjection (both overloads), SearchByBoW,
- * SearchForInitialization, SearchForTriangulation (one camera per KeyFrame: mpCamera2 == nullptr, the
- * only configuration the fork's Tracking builds), Fuse(pKF, vpMapPoints, th, bRight = false).
- * SearchBySim3 and Fuse(pKF, Scw, ...) go through ORBmatcher::SearchBySim3 / FuseSearch with the
- * projection loops of src/ORBmatcher.cc:1022-1050, :1084-1113 and :880-917 on the caller's side.
+ * Covered: all nine static functions of include/ORBmatcher.h:40-70 -- DescriptorDistance, SearchByProjection (both
+ * overloads), SearchByBoW, SearchForInitialization, SearchForTriangulation, SearchBySim3, Fuse(pKF, vpMapPoints, th,
+ * bRight) and Fuse(pKF, Scw, vpPoints, th, vpReplacePoint) -- for KeyFrames with one camera (mpCamera2 == nullptr,
+ * bRight == false: the only configuration the fork's Tracking builds; the two-camera branches throw).
+ * Sim3: operator*(sim3, vec3), inverse(), rotationMatrix(), translation(), scale(); vec3 / float; the SE3 type must be
+ * constructible from (mat3, vec3) as Sophus::SE3f is.
  */
 #ifndef ORBX_ORBMATCHER_REF_H
 #define ORBX_ORBMATCHER_REF_H
 #include <cmath>
 #include <memory>
 #include <set>
+#include <tuple>
 #include <utility>
 #include <vector>
 
@@ -321,6 +323,119 @@ int Fuse(std::shared_ptr<KeyFrameT> pKF, const std::vector<std::shared_ptr<MapPo
                 if (pMPinKF->Observations() > pMP->Observations()) pMP->Replace(pMPinKF);
                 else pMPinKF->Replace(pMP);
             }
+        } else {
+            pMP->AddObservation(pKF, best[i]);
+            pKF->AddMapPoint(pMP, best[i]);
+        }
+        nFused++;
+    }
+    return nFused;
+}
+
+/* int ORBmatcher::SearchBySim3(shared_ptr<KeyFrame> pKF1, shared_ptr<KeyFrame> pKF2, vector<shared_ptr<MapPoint>>& vpMatches12,
+ *        const Sophus::Sim3f& S12, const float th)        src/ORBmatcher.cc:977-1200
+ * Both projection loops (:1017-1050, :1097-1130) run here; the two window searches and the agreement check in the kernel. */
+template <class KeyFrameT, class MapPointT, class Sim3T>
+int SearchBySim3(std::shared_ptr<KeyFrameT> pKF1, std::shared_ptr<KeyFrameT> pKF2, std::vector<std::shared_ptr<MapPointT>>& vpMatches12,
+                 const Sim3T& S12, const float th) {
+    const float fx = pKF1->fx, fy = pKF1->fy, cx = pKF1->cx, cy = pKF1->cy;
+    const auto T1w = pKF1->GetPose();
+    const auto T2w = pKF2->GetPose();
+    const auto S21 = S12.inverse();
+    const auto vpMapPoints1 = pKF1->GetMapPointMatches();
+    const auto vpMapPoints2 = pKF2->GetMapPointMatches();
+    const int N1 = (int)vpMapPoints1.size(), N2 = (int)vpMapPoints2.size();
+    std::vector<bool> vbAlreadyMatched1(N1, false), vbAlreadyMatched2(N2, false);
+    for (int i = 0; i < N1; i++) {
+        const auto& pMP = vpMatches12[i];
+        if (pMP) {
+            vbAlreadyMatched1[i] = true;
+            const int idx2 = std::get<0>(pMP->GetIndexInKeyFrame(pKF2));
+            if (idx2 >= 0 && idx2 < N2) vbAlreadyMatched2[idx2] = true;
+        }
+    }
+    struct Side { std::vector<uint8_t> valid, desc; std::vector<float> u, v; std::vector<int32_t> lvl; };
+    auto project = [&](const std::vector<std::shared_ptr<MapPointT>>& pts, const std::vector<bool>& already, const decltype(T1w)& Tw,
+                       const Sim3T& S, const std::shared_ptr<KeyFrameT>& into, Side& o) {
+        const int N = (int)pts.size();
+        o.valid.assign(N, 0); o.desc.assign(32 * (size_t)N + 32, 0); o.u.assign(N, 0.f); o.v.assign(N, 0.f); o.lvl.assign(N, 0);
+        for (int i = 0; i < N; i++) {
+            const auto& pMP = pts[i];
+            if (!pMP || already[i] || pMP->isBad()) continue;
+            const auto p3Dw = pMP->GetWorldPos();
+            const auto p3Da = Tw * p3Dw;
+            const auto p3Db = S * p3Da;
+            if (p3Db(2) < 0.0) continue;
+            const float invz = 1.0 / p3Db(2);
+            const float x = p3Db(0) * invz, y = p3Db(1) * invz;
+            const float u = fx * x + cx, v = fy * y + cy;
+            if (!into->IsInImage(u, v)) continue;
+            const float dist3D = p3Db.norm();
+            if (dist3D < pMP->GetMinDistanceInvariance() || dist3D > pMP->GetMaxDistanceInvariance()) continue;
+            o.lvl[i] = pMP->PredictScale(dist3D, into);
+            o.u[i] = u; o.v[i] = v;
+            const auto d = pMP->GetDescriptor();
+            memcpy(&o.desc[32 * (size_t)i], descriptor_data(d), 32);
+            o.valid[i] = 1;
+        }
+    };
+    Side a, b;
+    project(vpMapPoints1, vbAlreadyMatched1, T1w, S21, pKF2, a);
+    project(vpMapPoints2, vbAlreadyMatched2, T2w, S12, pKF1, b);
+    FlatFrame f1, f2;
+    flatten_frame(*pKF1, N1, pKF1->mnGridCols, pKF1->mnGridRows, f1, false);
+    flatten_frame(*pKF2, N2, pKF2->mnGridCols, pKF2->mnGridRows, f2, false);
+    orbx_fuse_points p12{N1, a.valid.data(), a.u.data(), a.v.data(), nullptr, a.lvl.data(), a.desc.data()};
+    orbx_fuse_points p21{N2, b.valid.data(), b.u.data(), b.v.data(), nullptr, b.lvl.data(), b.desc.data()};
+    std::vector<int> match12;
+    const int nFound = matcher().SearchBySim3(f1.view, f2.view, p12, p21, th, match12);
+    for (int i1 = 0; i1 < N1; ++i1)
+        if (match12[i1] >= 0) vpMatches12[i1] = vpMapPoints2[match12[i1]];
+    return nFound;
+}
+
+/* int ORBmatcher::Fuse(shared_ptr<KeyFrame> pKF, Sophus::Sim3f& Scw, const vector<shared_ptr<MapPoint>>& vpPoints, float th,
+ *        vector<shared_ptr<MapPoint>>& vpReplacePoint)      src/ORBmatcher.cc:864-975 */
+template <class KeyFrameT, class MapPointT, class Sim3T>
+int Fuse(std::shared_ptr<KeyFrameT> pKF, Sim3T& Scw, const std::vector<std::shared_ptr<MapPointT>>& vpPoints, float th,
+         std::vector<std::shared_ptr<MapPointT>>& vpReplacePoint) {
+    typedef decltype(pKF->GetPose()) SE3T;
+    const SE3T Tcw(Scw.rotationMatrix(), Scw.translation() / Scw.scale());
+    const auto Ow = Tcw.inverse().translation();
+    const auto spAlreadyFound = pKF->GetMapPoints();
+    const int M = (int)vpPoints.size();
+    FlatFrame ff;
+    flatten_frame(*pKF, pKF->N, pKF->mnGridCols, pKF->mnGridRows, ff, false);
+    std::vector<uint8_t> valid(M, 0), desc(32 * (size_t)M + 32);
+    std::vector<float> u(M), v(M);
+    std::vector<int32_t> lvl(M, 0);
+    for (int i = 0; i < M; ++i) {
+        const auto& pMP = vpPoints[i];
+        if (pMP->isBad() || spAlreadyFound.count(pMP)) continue;
+        const auto p3Dw = pMP->GetWorldPos();
+        const auto p3Dc = Tcw * p3Dw;
+        if (p3Dc(2) < 0.0f) continue;
+        const auto uv = pKF->mpCamera->project(p3Dc);
+        if (!pKF->IsInImage(uv(0), uv(1))) continue;
+        const auto PO = p3Dw - Ow;
+        const float dist3D = PO.norm();
+        if (dist3D < pMP->GetMinDistanceInvariance() || dist3D > pMP->GetMaxDistanceInvariance()) continue;
+        lvl[i] = pMP->PredictScale(dist3D, pKF);
+        u[i] = uv(0); v[i] = uv(1);
+        const auto d = pMP->GetDescriptor();
+        memcpy(&desc[32 * (size_t)i], descriptor_data(d), 32);
+        valid[i] = 1;
+    }
+    orbx_fuse_points fp{M, valid.data(), u.data(), v.data(), nullptr, lvl.data(), desc.data()};
+    std::vector<int> best;
+    matcher().FuseSearch(ff.view, nullptr, nullptr, fp, th, 1, best);
+    int nFused = 0;
+    for (int i = 0; i < M; ++i) {
+        if (best[i] < 0) continue;
+        const auto& pMP = vpPoints[i];
+        auto pMPinKF = pKF->GetMapPoint(best[i]);
+        if (pMPinKF) {
+            if (!pMPinKF->isBad()) vpReplacePoint[i] = pMPinKF;
         } else {
             pMP->AddObservation(pKF, best[i]);
             pKF->AddMapPoint(pMP, best[i]);

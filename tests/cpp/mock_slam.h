@@ -8,6 +8,8 @@
 #include <cstdint>
 #include <map>
 #include <memory>
+#include <set>
+#include <tuple>
 #include <vector>
 
 namespace mock {
@@ -17,12 +19,15 @@ struct Vec3 {
     float v[3];
     float operator()(int i) const { return v[i]; }
     Vec3 operator-(const Vec3& o) const { return Vec3{{v[0] - o.v[0], v[1] - o.v[1], v[2] - o.v[2]}}; }
+    Vec3 operator/(float s) const { return Vec3{{v[0] / s, v[1] / s, v[2] / s}}; }
     float norm() const { return std::sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]); }
 };
 struct Mat3 { float m[9]; float operator()(int i, int j) const { return m[3 * i + j]; } };
 struct SE3 {            /* x -> R x + t */
     Mat3 R{{1, 0, 0, 0, 1, 0, 0, 0, 1}};
     Vec3 t{{0, 0, 0}};
+    SE3() {}
+    SE3(const Mat3& R_, const Vec3& t_) : R(R_), t(t_) {}
     Vec3 operator*(const Vec3& x) const {
         Vec3 o;
         for (int i = 0; i < 3; ++i) o.v[i] = R.m[3 * i] * x.v[0] + R.m[3 * i + 1] * x.v[1] + R.m[3 * i + 2] * x.v[2] + t.v[i];
@@ -43,6 +48,26 @@ struct SE3 {            /* x -> R x + t */
     }
     Mat3 rotationMatrix() const { return R; }
     Vec3 translation() const { return t; }
+};
+struct Sim3 {           /* x -> s R x + t */
+    float s = 1;
+    Mat3 R{{1, 0, 0, 0, 1, 0, 0, 0, 1}};
+    Vec3 t{{0, 0, 0}};
+    Vec3 operator*(const Vec3& x) const {
+        Vec3 o;
+        for (int i = 0; i < 3; ++i) o.v[i] = s * (R.m[3 * i] * x.v[0] + R.m[3 * i + 1] * x.v[1] + R.m[3 * i + 2] * x.v[2]) + t.v[i];
+        return o;
+    }
+    Sim3 inverse() const {
+        Sim3 o;
+        o.s = 1.f / s;
+        for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) o.R.m[3 * i + j] = R.m[3 * j + i];
+        for (int i = 0; i < 3; ++i) o.t.v[i] = -o.s * (o.R.m[3 * i] * t.v[0] + o.R.m[3 * i + 1] * t.v[1] + o.R.m[3 * i + 2] * t.v[2]);
+        return o;
+    }
+    Mat3 rotationMatrix() const { return R; }
+    Vec3 translation() const { return t; }
+    float scale() const { return s; }
 };
 struct Pinhole {
     float fx = 1, fy = 1, cx = 0, cy = 0;
@@ -71,6 +96,10 @@ struct MapPoint {
     float GetMaxDistanceInvariance() const { return 1e9f; }
     float GetMinDistanceInvariance() const { return 0.f; }
     template <class T> int PredictScale(float, const T&) const { return level; }
+    std::tuple<int, int> GetIndexInKeyFrame(const std::shared_ptr<KeyFrame>& kf) const {
+        for (auto& o : obs) if (o.first == kf.get()) return std::make_tuple(o.second, -1);
+        return std::make_tuple(-1, -1);
+    }
     bool IsInKeyFrame(const std::shared_ptr<KeyFrame>& kf) const { for (auto& o : obs) if (o.first == kf.get()) return true; return false; }
     void AddObservation(const std::shared_ptr<KeyFrame>& kf, int idx) { obs.emplace_back(kf.get(), idx); nobs++; }
     void Replace(const std::shared_ptr<MapPoint>& by) { bad = true; replaced_by = by.get(); }
@@ -96,7 +125,12 @@ struct Frame : FrameBase {
 };
 struct KeyFrame : FrameBase {
     int N = 0, mnGridCols = 64, mnGridRows = 48;
-    float mbf = 0;
+    float mbf = 0, fx = 1, fy = 1, cx = 0, cy = 0;
+    std::set<std::shared_ptr<MapPoint>> GetMapPoints() const {
+        std::set<std::shared_ptr<MapPoint>> s;
+        for (auto& p : mvpMapPoints) if (p && !p->bad) s.insert(p);
+        return s;
+    }
     Vec3 camera_center{{0, 0, 0}};
     std::vector<std::shared_ptr<MapPoint>> mvpMapPoints;
     std::vector<std::shared_ptr<MapPoint>> GetMapPointMatches() const { return mvpMapPoints; }

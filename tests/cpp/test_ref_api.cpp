@@ -258,7 +258,58 @@ int main(int argc, char** argv) {
             const orbx_frame_view K1 = frame_view(in, "sim3.KF1."), K2 = frame_view(in, "sim3.KF2.");
             std::vector<int> match;
             out.put_int("sim3.flat.n", m.SearchBySim3(K1, K2, fuse_points(in, "sim3.MP1in2."), fuse_points(in, "sim3.MP2in1."), in.scalar<float>("sim3.params"), match));
-            out.put("sim3.flat.match", match); ++ran;
+            out.put("sim3.flat.match", match);
+            /* reference signature: identity poses and S12, map points at (u, v, 1) so that the projection loops reproduce u, v */
+            auto A = std::make_shared<mock::KeyFrame>(), B = std::make_shared<mock::KeyFrame>();
+            fill_base(*A, K1); fill_base(*B, K2);
+            A->N = K1.n; B->N = K2.n; A->mnGridCols = K1.gcols; A->mnGridRows = K1.grows; B->mnGridCols = K2.gcols; B->mnGridRows = K2.grows;
+            const orbx_fuse_points P12 = fuse_points(in, "sim3.MP1in2."), P21 = fuse_points(in, "sim3.MP2in1.");
+            auto fill_pts = [](mock::KeyFrame& K, const orbx_fuse_points& P) {
+                K.mvpMapPoints.assign(P.n, nullptr);
+                for (int i = 0; i < P.n; ++i) {
+                    if (!P.valid[i] && i % 2 == 0) continue;
+                    auto q = std::make_shared<mock::MapPoint>();
+                    q->bad = !P.valid[i]; q->pos = mock::Vec3{{P.u[i], P.v[i], 1.f}}; q->level = P.level[i];
+                    memcpy(q->desc, P.desc + 32 * i, 32);
+                    K.mvpMapPoints[i] = q;
+                }
+            };
+            fill_pts(*A, P12); fill_pts(*B, P21);
+            std::vector<MPp> m12(K1.n, nullptr);
+            mock::Sim3 S12;
+            out.put_int("sim3.ref.n", orbx_ref::SearchBySim3(A, B, m12, S12, in.scalar<float>("sim3.params")));
+            out.put("sim3.ref.match", indices_of(m12, B->mvpMapPoints)); ++ran;
+        }
+        if (in.has("fuse2.params")) {       /* Fuse(pKF, Scw, vpPoints, th, vpReplacePoint) */
+            const float th = in.scalar<float>("fuse2.params");
+            const orbx_frame_view KFv = frame_view(in, "fuse.KF.");
+            const orbx_fuse_points FP = fuse_points(in, "fuse.MP.");
+            std::vector<int> best;
+            orbx_fuse_points FP1 = FP; FP1.ur = nullptr;
+            m.FuseSearch(KFv, nullptr, nullptr, FP1, th, 1, best);
+            out.put("fuse2.flat.best", best);
+            auto KF = std::make_shared<mock::KeyFrame>();
+            fill_base(*KF, KFv);
+            KF->N = KFv.n; KF->mnGridCols = KFv.gcols; KF->mnGridRows = KFv.grows;
+            const uint8_t* kfobs = in.get<uint8_t>("fuse.kf_obs");
+            KF->mvpMapPoints.assign(KFv.n, nullptr);
+            for (int i = 0; i < KFv.n; ++i)
+                if (kfobs[i]) { KF->mvpMapPoints[i] = std::make_shared<mock::MapPoint>(); KF->mvpMapPoints[i]->id = 1000000 + i; }
+            std::vector<MPp> pts(FP.n), repl(FP.n, nullptr);
+            for (int i = 0; i < FP.n; ++i) {
+                pts[i] = std::make_shared<mock::MapPoint>();
+                auto& q = *pts[i];
+                q.bad = !FP.valid[i]; q.pos = mock::Vec3{{FP.u[i], FP.v[i], 1.f}}; q.level = FP.level[i]; q.id = i;
+                memcpy(q.desc, FP.desc + 32 * i, 32);
+            }
+            mock::Sim3 Scw;
+            out.put_int("fuse2.ref.n", orbx_ref::Fuse(KF, Scw, pts, th, repl));
+            std::vector<int> rid(FP.n, -1), at(FP.n, -1);
+            for (int i = 0; i < FP.n; ++i) {
+                if (repl[i]) rid[i] = repl[i]->id;
+                for (auto& o : pts[i]->obs) if (o.first == KF.get()) at[i] = o.second;
+            }
+            out.put("fuse2.ref.replace", rid); out.put("fuse2.ref.at", at); ++ran;
         }
         if (in.has("dd.desc")) {            /* MapPoint::ComputeDistinctiveDescriptors */
             out.put_int("dd.best", m.ComputeDistinctiveDescriptor(in.get<uint8_t>("dd.desc"), in.count<uint8_t>("dd.desc") / 32)); ++ran;

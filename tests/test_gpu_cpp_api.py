@@ -129,7 +129,10 @@ def test_every_cpp_wrapper_and_reference_signature(exe, oracle, synth, tmp_path)
     mp_obs = rng.integers(1, 6, 1000).astype(np.uint8)
     A["fuse.kf_obs"], A["fuse.mp_obs"] = kf_obs, mp_obs
     # SearchBySim3, distinctive descriptor, grid
+    A["fuse2.params"] = np.array([3.0], np.float32)
     S1, S2, s12, s21 = synth.sim3_problem(600, 650, seed=351)
+    for sp in (s12, s21):
+        sp["valid"] = (sp["valid"].astype(bool) & (sp["u"] >= 0) & (sp["v"] >= 0)).astype(np.uint8)
     _frame(A, "sim3.KF1.", S1); _frame(A, "sim3.KF2.", S2); _fuse_pts(A, "sim3.MP1in2.", s12); _fuse_pts(A, "sim3.MP2in1.", s21)
     A["sim3.params"] = np.array([7.5], np.float32)
     dd = rng.integers(0, 256, (23, 32), dtype=np.uint8); dd[7] = dd[3]
@@ -141,7 +144,7 @@ def test_every_cpp_wrapper_and_reference_signature(exe, oracle, synth, tmp_path)
     r = subprocess.run([exe, inp, outp], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0 and r.stdout.startswith("OK"), r.stdout + r.stderr
     R = read_blob(outp)
-    assert _i32(R["ran"])[0] == 10
+    assert _i32(R["ran"])[0] == 11
 
     ref = oracle.hamming_pairs(a, b)
     assert np.array_equal(_i32(R["hd.one"]), ref) and np.array_equal(_i32(R["hd.bulk"]), ref) and _i32(R["hd.ref0"])[0] == ref[0]
@@ -191,7 +194,27 @@ def test_every_cpp_wrapper_and_reference_signature(exe, oracle, synth, tmp_path)
     assert np.array_equal(_i32(R["fuse.ref.event"]), ev) and np.array_equal(_i32(R["fuse.ref.at"]), at)
     assert {1, 2, 3} <= set(ev.tolist())
     on, om = oracle.search_by_sim3(S1, S2, s12, s21, 7.5)
-    assert _i32(R["sim3.flat.n"])[0] == on and np.array_equal(_i32(R["sim3.flat.match"]), om)
+    for w in ("flat", "ref"):
+        assert _i32(R[f"sim3.{w}.n"])[0] == on and np.array_equal(_i32(R[f"sim3.{w}.match"]), om), w
+    assert on > 30
+    # Fuse(pKF, Scw, ...): search (variant 1) + the reference's bookkeeping (:958-968) replayed on the oracle's result
+    fmp1 = dict(fmp); fmp1.pop("ur")
+    b2, _ = oracle.fuse_search(KF, fmp1, 3.0, 1)
+    assert np.array_equal(_i32(R["fuse2.flat.best"]), b2)
+    rid = np.full(1000, -1, np.int32); at2 = np.full(1000, -1, np.int32)
+    held = {k: 1000000 + k for k in range(800) if kf_obs[k]}
+    nf2 = 0
+    for i in range(1000):
+        k = int(b2[i])
+        if k < 0:
+            continue
+        nf2 += 1
+        if k in held:
+            rid[i] = held[k]
+        else:
+            at2[i] = k; held[k] = i
+    assert _i32(R["fuse2.ref.n"])[0] == nf2 and nf2 > 100
+    assert np.array_equal(_i32(R["fuse2.ref.replace"]), rid) and np.array_equal(_i32(R["fuse2.ref.at"]), at2)
     assert _i32(R["dd.best"])[0] == oracle.distinctive_descriptor(dd)[0]
     off, idx = oracle.assign_features_to_grid(F)
     assert np.array_equal(_i32(R["grid.off"]), off) and np.array_equal(_i32(R["grid.idx"]), idx)
