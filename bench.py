@@ -474,6 +474,59 @@ def other_shapes_bench(pkg, torch, local):
     return out
 
 
+def preproc_bench(pkg, torch, local):
+    """SURVEY 8(f) n4: ImageGrabber::ConvertImageToGPU (image_grabber.hpp:96-110) at the reference node's own shape --
+    2048x1536 BGR, undistortion remap (cubic), resize_factor 0.3 -> 614x460 gray (mono_inertial_node.cpp:20,59-68) --
+    32 frames per step.  device: frames resident in HBM, CUDA events on the handle's stream; chained: pinned host BGR ->
+    H2D -> pre-process -> extract (1000 features) -> keypoints + descriptors on the host, wall clock; cpu_port: the
+    oracle's restatement of cv::remap / resize / cvtColor on one host thread, 2 frames."""
+    ox, synth = pkg.orbx, pkg.synth
+    dev = torch.device("cuda", local)
+    SW, SH, B = 2048, 1536, 32
+    DW, DH = int(SW * 0.3), int(SH * 0.3)
+    m1, m2 = synth.undistortion_maps(SW, SH, SW, SH, k1=-0.12, k2=0.02, zoom=0.97)
+    base = np.stack([synth.bgr_image(SW, SH, 300 + f) for f in range(2)])
+    pin = ox.PinnedBuffer((B, SH, SW, 3))
+    for f in range(B):
+        pin.array[f] = np.roll(base[f & 1], 17 * f, axis=1)
+    g = ox.ImageGrabber((SW, SH), m1, m2, DW, DH, max_batch=B, device=local)
+    d_in = torch.from_numpy(pin.array).to(dev)
+    d_out = torch.empty((B, DH, DW), dtype=torch.uint8, device=dev)
+    st = torch.cuda.ExternalStream(g.stream(), device=dev)
+    torch.cuda.synchronize()
+    for _ in range(3):
+        g.convert_device(d_in.data_ptr(), B, d_out.data_ptr())
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(st)
+    for _ in range(10):
+        g.convert_device(d_in.data_ptr(), B, d_out.data_ptr())
+    e1.record(st)
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / 10
+    from oracle import oracle as O
+    t0 = time.perf_counter()
+    ref = [O.preprocess_bgr(pin.array[f], m1, m2, DW, DH) for f in range(2)]
+    cpu_s = (time.perf_counter() - t0) / 2
+    got = d_out[:2].cpu().numpy()
+    assert np.array_equal(got[0], ref[0]) and np.array_equal(got[1], ref[1]), "pre-processing differs from the oracle"
+    ex = ox.ORBextractor(NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH, device=local, max_batch=B).prepare(DW, DH, B)
+    for _ in range(2):
+        g.convert_and_extract(pin.array, ex); ex.sync()
+    t0 = time.perf_counter()
+    for _ in range(5):
+        g.convert_and_extract(pin.array, ex); ex.sync()
+    wall = (time.perf_counter() - t0) / 5
+    n, _ = ex.counts(B)
+    ex.close(); g.close(); pin.free()
+    alg = SW * SH * 3 + DW * DH
+    return {"workload": f"{SW}x{SH} BGR -> remap INTER_CUBIC -> resize {DW}x{DH} INTER_LINEAR -> BGR2GRAY, {B} frames per step",
+            "kernel": "k_remap_resize_gray", "device": {"frames_per_s": B / (ms * 1e-3), "ms_per_step": ms,
+                                                       "algorithmic_bytes_per_frame": alg, "gbs": alg * B / (ms * 1e-3) / 1e9},
+            "chained_with_extract_e2e": {"frames_per_s": B / wall, "ms_per_step": wall * 1e3, "h2d_bytes_per_step": B * SW * SH * 3,
+                                         "keypoints_per_frame": float(np.mean(n))},
+            "cpu_port": {"frames_per_s": 1.0 / cpu_s, "cores": 1, "sample": "2 frames"}, "parity": "bit-exact on the 2 sampled frames"}
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -758,6 +811,7 @@ def main():
             line["matching"] = matching_bench(pkg, torch, local, ex, B)
             line["matching"]["knn2_sharded"] = knn_sharded
             line["other_shapes"] = other_shapes_bench(pkg, torch, local)
+            line["preprocessing"] = preproc_bench(pkg, torch, local)
             line["single_frame_latency"] = single_frame_latency(pkg, local, frames[0])
             line["cpp_operator_latency"] = cpp_operator_latency(pkg, frames[0])
         if numa is not None:

@@ -386,6 +386,36 @@ size_t orbx_knn2_noalloc_scratch_bytes(void);
 orbx_status orbx_matcher_set_knn_variant(orbx_matcher* m, int variant);
 orbx_status orbx_matcher_synchronize(orbx_matcher* m);
 
+/* ------------------------------------------------------------------------------------------
+ * ROS-side image pre-processing
+ *   ImageGrabber::ImageGrabber         ros2_ws/src/mono-inertial/include/image_grabber.hpp:38-49
+ *                                      (holds m_undistortion_map_1/2 and the output size m_width x m_height; the maps
+ *                                      are made by cv::fisheye::initUndistortRectifyMap for a 2048x1536 BGR camera at
+ *                                      ros2_ws/src/mono-inertial/src/mono_inertial_node.cpp:54-71)
+ *   ImageGrabber::ConvertImageToGPU    ros2_ws/src/mono-inertial/include/image_grabber.hpp:96-110
+ *       cv::cuda::remap(INTER_CUBIC, BORDER_CONSTANT 0) -> cv::cuda::resize(INTER_LINEAR) -> cvtColor(BGR2GRAY)
+ * One handle = one camera.  map_x / map_y are the two CV_32FC1 planes of initUndistortRectifyMap (map_w x map_h,
+ * dense, host memory; copied).  Input: 8-bit BGR interleaved, src_w x src_h; output: 8-bit gray, dst_w x dst_h, dense.
+ * The arithmetic is that of the CPU cv::remap / cv::resize / cv::cvtColor, bit for bit (csrc/preproc.cu header). */
+typedef struct orbx_preproc orbx_preproc;
+orbx_status orbx_preproc_create(int src_w, int src_h, const float* map_x, const float* map_y, int map_w, int map_h,
+                                int dst_w, int dst_h, int max_batch, int device, orbx_preproc** out);
+void orbx_preproc_destroy(orbx_preproc* p);
+void* orbx_preproc_stream(orbx_preproc* p);
+/* `batch` BGR frames in device memory (frame f at d_bgr + f*frame_stride, rows row_stride BYTES apart) -> d_gray
+ * (batch x dst_h x dst_w, dense).  Asynchronous on `stream` (a cudaStream_t; NULL = the handle's stream). */
+orbx_status orbx_preproc_device(orbx_preproc* p, const uint8_t* d_bgr, size_t frame_stride, int row_stride, int batch,
+                                uint8_t* d_gray, void* stream);
+/* the same from / to host memory; returns with h_gray filled */
+orbx_status orbx_preproc_host(orbx_preproc* p, const uint8_t* h_bgr, size_t frame_stride, int row_stride, int batch,
+                              uint8_t* h_gray);
+/* ConvertImageToGPU -> System::TrackMonocular -> ORBextractor::operator() chained on the device: the BGR frames are
+ * copied in, pre-processed and extracted on e's stream; the gray images never visit the host.  e must have been made
+ * for dst_w x dst_h on the same device.  Asynchronous like orbx_extract_host; results through orbx_extractor_sync /
+ * orbx_extractor_fetch. */
+orbx_status orbx_preproc_extract_host(orbx_preproc* p, orbx_extractor* e, const uint8_t* h_bgr, size_t frame_stride,
+                                      int row_stride, int batch, const int* lapping);
+
 #ifdef __cplusplus
 }
 #endif

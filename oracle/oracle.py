@@ -77,6 +77,21 @@ def gaussian7(img):
     return dst
 
 
+def remap_cubic_bgr(src, mapx, mapy):
+    src = _u8(src); mx, my = _f32(mapx), _f32(mapy)
+    out = np.empty(mx.shape + (3,), np.uint8)
+    lib().orc_remap_cubic_bgr(_p(src), src.shape[1], src.shape[0], _p(mx), _p(my), mx.shape[1], mx.shape[0], _p(out))
+    return out
+
+
+def preprocess_bgr(src, mapx, mapy, dw, dh):
+    """remap(INTER_CUBIC, BORDER_CONSTANT) -> resize(INTER_LINEAR) -> BGR2GRAY (image_grabber.hpp:96-110)."""
+    src = _u8(src); mx, my = _f32(mapx), _f32(mapy)
+    out = np.empty((dh, dw), np.uint8)
+    lib().orc_preprocess_bgr(_p(src), src.shape[1], src.shape[0], _p(mx), _p(my), mx.shape[1], mx.shape[0], int(dw), int(dh), _p(out))
+    return out
+
+
 def fast9_16(img, th, max_out=1 << 16):
     img = _u8(img)
     xs = np.empty(max_out, np.int32); ys = np.empty(max_out, np.int32); sc = np.empty(max_out, np.int32)

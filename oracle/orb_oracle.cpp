@@ -57,15 +57,14 @@ void resize_linear_u8(const uint8_t* src, int sw, int sh, int sstride,
         float fy = (float)((dy + 0.5) * scale_y - 0.5);
         int sy = (int)floorf(fy);
         fy -= sy;
-        if (sy < 0) { fy = 0; sy = 0; }
-        if (sy >= sh - 1) { fy = 0; sy = sh - 1; }
-        yofs[dy] = sy;
+        yofs[dy] = sy;   /* rows are NOT clamped in the table (unlike columns): the two source rows are clipped when
+                          * fetched, so an enlarging resize blends row 0 (or sh-1) with itself with both weights */
         ay[2 * dy] = (short)cvRoundf((1.f - fy) * 2048);
         ay[2 * dy + 1] = (short)cvRoundf(fy * 2048);
     }
     std::vector<int> r0(dw), r1(dw);
     for (int dy = 0; dy < dh; ++dy) {
-        const int y0 = yofs[dy], y1 = std::min(y0 + 1, sh - 1);
+        const int y0 = std::min(std::max(yofs[dy], 0), sh - 1), y1 = std::min(std::max(yofs[dy] + 1, 0), sh - 1);
         const uint8_t* s0 = src + (size_t)y0 * sstride;
         const uint8_t* s1 = src + (size_t)y1 * sstride;
         for (int dx = 0; dx < dw; ++dx) {
@@ -437,6 +436,89 @@ int orc_fast9_16(const uint8_t* img, int w, int h, int stride, int threshold, in
     return fast9_16(img, w, h, stride, threshold, xs, ys, scores, max_out);
 }
 float orc_fast_atan2(float y, float x) { return fast_atan2(y, x); }
+
+/* ------------------------------------------------------------------ ROS-side pre-processing
+ * ImageGrabber::ConvertImageToGPU, ros2_ws/src/mono-inertial/include/image_grabber.hpp:96-110:
+ *   remap(BGR, map1, map2, INTER_CUBIC, BORDER_CONSTANT 0) -> resize(new size, INTER_LINEAR) -> cvtColor(BGR2GRAY).
+ * The fork runs the cv::cuda versions (float arithmetic, not runnable here); this restates the arithmetic of the CPU
+ * functions of the same names, pinned bit for bit against Python cv2 (tests/test_oracle_golden.py):
+ *   remap: map -> fixed point with 5 fractional bits (cvRound(x * 32)), 4x4 taps from a 32 x 32 table of cubic
+ *          weights (A = -0.75) scaled to 2^15 whose sum is forced to 2^15 by adjusting the largest / smallest of the
+ *          four central weights, (sum + 2^14) >> 15, taps outside the image contribute the border value 0;
+ *   resize: the 11-bit fixed-point bilinear of App. B1, per channel;  gray: (3735 B + 19235 G + 9798 R + 2^14) >> 15. */
+static void cubic_coeffs(float x, float* c) {
+    const float A = -0.75f;
+    c[0] = ((A * (x + 1) - 5 * A) * (x + 1) + 8 * A) * (x + 1) - 4 * A;
+    c[1] = ((A + 2) * x - (A + 3)) * x * x + 1;
+    c[2] = ((A + 2) * (1 - x) - (A + 3)) * (1 - x) * (1 - x) + 1;
+    c[3] = 1.f - c[0] - c[1] - c[2];
+}
+void orc_remap_cubic_table(short* itab /* [32*32][16] */) {
+    float tab1[32][4];
+    for (int i = 0; i < 32; ++i) cubic_coeffs((float)i / 32.f, tab1[i]);
+    for (int i = 0; i < 32; ++i)
+        for (int j = 0; j < 32; ++j) {
+            short* w = itab + (size_t)(i * 32 + j) * 16;
+            int isum = 0;
+            for (int k1 = 0; k1 < 4; ++k1)
+                for (int k2 = 0; k2 < 4; ++k2) {
+                    const float v = tab1[i][k1] * tab1[j][k2];
+                    int iv = cvRoundf(v * 32768.f);
+                    iv = iv < -32768 ? -32768 : (iv > 32767 ? 32767 : iv);
+                    w[k1 * 4 + k2] = (short)iv;
+                    isum += iv;
+                }
+            if (isum != 32768) {
+                const int diff = isum - 32768;
+                int Mk1 = 2, Mk2 = 2, mk1 = 2, mk2 = 2;
+                for (int k1 = 2; k1 < 4; ++k1)
+                    for (int k2 = 2; k2 < 4; ++k2) {
+                        if (w[k1 * 4 + k2] < w[mk1 * 4 + mk2]) { mk1 = k1; mk2 = k2; }
+                        else if (w[k1 * 4 + k2] > w[Mk1 * 4 + Mk2]) { Mk1 = k1; Mk2 = k2; }
+                    }
+                if (diff < 0) w[Mk1 * 4 + Mk2] = (short)(w[Mk1 * 4 + Mk2] - diff);
+                else w[mk1 * 4 + mk2] = (short)(w[mk1 * 4 + mk2] - diff);
+            }
+        }
+}
+void orc_remap_cubic_bgr(const uint8_t* src, int sw, int sh, const float* mapx, const float* mapy, int mw, int mh, uint8_t* dst) {
+    std::vector<short> itab(32 * 32 * 16);
+    orc_remap_cubic_table(itab.data());
+    for (int y = 0; y < mh; ++y)
+        for (int x = 0; x < mw; ++x) {
+            const int sx = cvRoundf(mapx[(size_t)y * mw + x] * 32.f), sy = cvRoundf(mapy[(size_t)y * mw + x] * 32.f);
+            const int ix = sx >> 5, iy = sy >> 5;
+            const short* w = itab.data() + (size_t)((sy & 31) * 32 + (sx & 31)) * 16;
+            int acc[3] = {0, 0, 0};
+            for (int k1 = 0; k1 < 4; ++k1) {
+                const int yy = iy - 1 + k1;
+                if (yy < 0 || yy >= sh) continue;
+                for (int k2 = 0; k2 < 4; ++k2) {
+                    const int xx = ix - 1 + k2;
+                    if (xx < 0 || xx >= sw) continue;
+                    const uint8_t* p = src + ((size_t)yy * sw + xx) * 3;
+                    for (int c = 0; c < 3; ++c) acc[c] += w[k1 * 4 + k2] * p[c];
+                }
+            }
+            for (int c = 0; c < 3; ++c) {
+                const int v = (acc[c] + (1 << 14)) >> 15;
+                dst[((size_t)y * mw + x) * 3 + c] = (uint8_t)(v < 0 ? 0 : (v > 255 ? 255 : v));
+            }
+        }
+}
+void orc_preprocess_bgr(const uint8_t* src, int sw, int sh, const float* mapx, const float* mapy, int mw, int mh, int dw, int dh,
+                        uint8_t* gray) {
+    std::vector<uint8_t> und((size_t)mw * mh * 3), plane((size_t)mw * mh), rs((size_t)dw * dh * 3), rp((size_t)dw * dh);
+    orc_remap_cubic_bgr(src, sw, sh, mapx, mapy, mw, mh, und.data());
+    for (int c = 0; c < 3; ++c) {
+        for (size_t i = 0; i < (size_t)mw * mh; ++i) plane[i] = und[3 * i + c];
+        if (dw == mw && dh == mh) rp = plane;
+        else resize_linear_u8(plane.data(), mw, mh, mw, rp.data(), dw, dh, dw);
+        for (size_t i = 0; i < (size_t)dw * dh; ++i) rs[3 * i + c] = rp[i];
+    }
+    for (size_t i = 0; i < (size_t)dw * dh; ++i)
+        gray[i] = (uint8_t)((3735 * rs[3 * i] + 19235 * rs[3 * i + 1] + 9798 * rs[3 * i + 2] + (1 << 14)) >> 15);
+}
 
 orc_extractor* orc_extractor_create(int nfeatures, float scaleFactor_, int nlevels, int iniTh, int minTh) {
     orc_extractor* e = new orc_extractor;

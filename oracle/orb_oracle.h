@@ -33,6 +33,12 @@ typedef struct {
 void orc_resize_linear_u8(const uint8_t* src, int sw, int sh, int sstride,
                           uint8_t* dst, int dw, int dh, int dstride);
 void orc_border_reflect101(uint8_t* buf, int w, int h, int stride, int border);
+/* ROS-side pre-processing, ros2_ws/src/mono-inertial/include/image_grabber.hpp:96-110 (CPU arithmetic of cv::remap
+ * INTER_CUBIC / BORDER_CONSTANT 0, cv::resize INTER_LINEAR, cv::cvtColor BGR2GRAY) */
+void orc_remap_cubic_table(short* itab /* [32*32][16] */);
+void orc_remap_cubic_bgr(const uint8_t* src, int sw, int sh, const float* mapx, const float* mapy, int mw, int mh, uint8_t* dst);
+void orc_preprocess_bgr(const uint8_t* src, int sw, int sh, const float* mapx, const float* mapy, int mw, int mh, int dw, int dh,
+                        uint8_t* gray);
 void orc_gaussian7_s2_u8(const uint8_t* src, int w, int h, int sstride,
                          uint8_t* dst, int dstride);
 /* cv::FAST(img, kps, th, nonmax=true, TYPE_9_16) on a w x h sub-image.

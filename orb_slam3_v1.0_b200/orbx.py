@@ -114,6 +114,14 @@ def lib():
         L.orbx_knn2_device_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_longlong, C.c_void_p]
         L.orbx_knn2_noalloc_scratch_bytes.restype = C.c_size_t
         L.orbx_knn2_merge_device.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_float] + [C.c_void_p] * 5
+        L.orbx_preproc_create.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                          C.POINTER(C.c_void_p)]
+        L.orbx_preproc_destroy.argtypes = [C.c_void_p]
+        L.orbx_preproc_stream.restype = C.c_void_p
+        L.orbx_preproc_stream.argtypes = [C.c_void_p]
+        L.orbx_preproc_device.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+        L.orbx_preproc_host.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_void_p]
+        L.orbx_preproc_extract_host.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_void_p]
         _lib = L
     return _lib
 
@@ -307,6 +315,63 @@ class ORBextractor:
 
     def stream(self):
         return lib().orbx_extractor_stream(self._h)
+
+
+class ImageGrabber:
+    """The image half of ros2_orbslam3::ImageGrabber (ros2_ws/src/mono-inertial/include/image_grabber.hpp:38-49, 96-110):
+    holds the two undistortion maps and the output size; ConvertImageToGPU = remap(INTER_CUBIC, BORDER_CONSTANT) ->
+    resize(INTER_LINEAR) -> BGR2GRAY, batched.  No CPU fallback."""
+
+    def __init__(self, src_size, undistortion_map_1, undistortion_map_2, width, height, max_batch=1, device=0):
+        m1 = np.ascontiguousarray(undistortion_map_1, np.float32); m2 = np.ascontiguousarray(undistortion_map_2, np.float32)
+        if m1.ndim != 2 or m1.shape != m2.shape:
+            raise ValueError("the undistortion maps are two CV_32FC1 planes of one size")
+        self.src_w, self.src_h = int(src_size[0]), int(src_size[1])
+        self.m_width, self.m_height, self.max_batch, self.device = int(width), int(height), int(max_batch), device
+        h = C.c_void_p()
+        _ck(lib().orbx_preproc_create(self.src_w, self.src_h, _p(m1), _p(m2), m1.shape[1], m1.shape[0], self.m_width, self.m_height,
+                                      self.max_batch, device, C.byref(h)))
+        self._h = h
+
+    def close(self):
+        if getattr(self, "_h", None) is not None:
+            lib().orbx_preproc_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def stream(self):
+        return lib().orbx_preproc_stream(self._h)
+
+    def _batch(self, images):
+        images = np.asarray(images)
+        if images.dtype != np.uint8 or images.ndim != 4 or images.shape[1:] != (self.src_h, self.src_w, 3) or images.strides[2:] != (3, 1):
+            raise ValueError(f"expected (B, {self.src_h}, {self.src_w}, 3) u8 BGR frames with dense pixels")
+        return images
+
+    def ConvertImageToGPU(self, images):
+        """(B, H, W, 3) u8 BGR host frames -> (B, m_height, m_width) u8 gray."""
+        images = self._batch(images)
+        out = np.empty((images.shape[0], self.m_height, self.m_width), np.uint8)
+        _ck(lib().orbx_preproc_host(self._h, images.ctypes.data, images.strides[0], images.strides[1], images.shape[0], _p(out)))
+        return out
+
+    def convert_device(self, d_bgr, batch, d_gray, stream=None):
+        """device pointers (ints); dense frames; asynchronous on `stream` (None = the handle's)."""
+        _ck(lib().orbx_preproc_device(self._h, d_bgr, self.src_w * self.src_h * 3, self.src_w * 3, batch, d_gray, stream))
+
+    def convert_and_extract(self, images, extractor, lapping=None):
+        """ConvertImageToGPU -> TrackMonocular -> ORBextractor::operator() chained on the device (asynchronous:
+        extractor.sync() / fetch() afterwards)."""
+        images = self._batch(images)
+        b = images.shape[0]
+        extractor._ensure(self.m_width, self.m_height, b)
+        lap = np.ascontiguousarray(lapping, np.int32).reshape(b, 2) if lapping is not None else None
+        _ck(lib().orbx_preproc_extract_host(self._h, extractor._h, images.ctypes.data, images.strides[0], images.strides[1], b, _p(lap)))
 
 
 def hamming_pairs(a, b):

@@ -238,3 +238,24 @@ def initialization_pair(n1=1000, n2=1000, seed=6, motion=25.0, flip_p=0.05, p_le
     F1["kangle"] = ((F2["kangle"][src] + rng.normal(0, 8, n1)) % 360).astype(np.float32)
     F1["desc"] = _flip_bits(rng, F2["desc"][src], flip_p * rng.uniform(0.2, 2.0, (n1, 1)))
     return F1, F2
+
+
+def bgr_image(width, height, seed=0xB200):
+    """A colour camera frame: three differently textured planes (u8 BGR, interleaved)."""
+    return np.ascontiguousarray(np.stack([textured_image(width, height, seed + 101 * c, nshapes=120) for c in range(3)], axis=-1))
+
+
+def undistortion_maps(src_w, src_h, map_w, map_h, k1=-0.21, k2=0.05, zoom=0.92):
+    """Two CV_32FC1 planes like initUndistortRectifyMap's, from a radial polynomial evaluated with + and * only in
+    float64 (bit-reproducible everywhere).  zoom < 1 makes the corners of the map fall outside the source, so the
+    BORDER_CONSTANT taps are exercised."""
+    fx = 0.62 * src_w
+    x = (np.arange(map_w, dtype=np.float64) + 0.5) * (src_w / map_w) - 0.5
+    y = (np.arange(map_h, dtype=np.float64) + 0.5) * (src_h / map_h) - 0.5
+    xn = (x[None, :] - 0.5 * src_w) / (fx * zoom)
+    yn = (y[:, None] - 0.5 * src_h) / (fx * zoom)
+    r2 = xn * xn + yn * yn
+    d = 1.0 + k1 * r2 + k2 * r2 * r2
+    mx = xn * d * fx + 0.5 * src_w + 0.0 * yn
+    my = yn * d * fx + 0.5 * src_h + 0.0 * xn
+    return np.ascontiguousarray(mx, np.float32), np.ascontiguousarray(my, np.float32)

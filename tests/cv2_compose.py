@@ -282,3 +282,18 @@ def extract(image, nfeatures=1000, scaleFactor=1.2, nlevels=8, iniThFAST=20, min
             out_k[at] = (fx, fy, size, ang, r, l, -1)
             out_d[at] = d
     return out_k, out_d, mono
+
+
+# ---------------------------------------------------------------- ROS-side pre-processing
+def fisheye_maps(width=2048, height=1536):
+    """The two CV_32FC1 undistortion maps the way the reference node makes them (cv::fisheye::initUndistortRectifyMap
+    with R = I and P = K, ros2_ws/src/mono-inertial/src/mono_inertial_node.cpp:61-68) for a 2048x1536-class camera."""
+    K = np.array([[0.653 * width, 0, 0.4985 * width], [0, 0.869 * height, 0.5125 * height], [0, 0, 1]], np.float64)
+    D = np.array([-0.008, 0.0615, -0.072, 0.0356], np.float64)
+    return cv2.fisheye.initUndistortRectifyMap(K, D, np.eye(3), K, (width, height), cv2.CV_32FC1)
+
+
+def convert_image(bgr, map1, map2, width, height):
+    """ImageGrabber::ConvertImageToGPU (image_grabber.hpp:96-110) from the CPU cv2 functions of the same names."""
+    und = cv2.remap(bgr, map1, map2, cv2.INTER_CUBIC, borderMode=cv2.BORDER_CONSTANT, borderValue=0)
+    return cv2.cvtColor(cv2.resize(und, (width, height), interpolation=cv2.INTER_LINEAR), cv2.COLOR_BGR2GRAY)

@@ -109,3 +109,14 @@ def test_python_quadtree_vs_oracle_quadtree(oracle):
         idx = oracle.distribute_octtree(pts[:, 0], pts[:, 1], resp, 16, 16 + W, 16, 16 + H, N)
         got = [(int(x), int(y)) for x, y, _ in sel]
         assert got == [tuple(int(v) for v in pts[i]) for i in idx], it
+
+
+def test_preprocess_reference_camera_vs_cv2(oracle, synth):
+    """The reference node's own shape (mono_inertial_node.cpp:20,59-68: 2048x1536 BGR, fisheye maps, resize_factor 0.3)
+    through cv2.remap / resize / cvtColor against the oracle's restatement: bit-exact."""
+    import cv2_compose as cc
+    cv2.setNumThreads(1)
+    img = synth.bgr_image(2048, 1536, 21)
+    m1, m2 = cc.fisheye_maps(2048, 1536)
+    w, h = int(2048 * 0.3), int(1536 * 0.3)
+    assert np.array_equal(oracle.preprocess_bgr(img, m1, m2, w, h), cc.convert_image(img, m1, m2, w, h))

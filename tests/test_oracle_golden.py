@@ -120,3 +120,28 @@ def test_whole_extractor_matches_cv2_composition(oracle, synth, GX, name):
     for fld in ("x", "y", "size", "angle", "response", "octave", "class_id"):
         assert np.array_equal(k[fld], gk[fld]), fld
     assert np.array_equal(d, GX[f"{name}_desc"])
+
+
+# ---------------------------------------------------------------- ROS-side pre-processing
+@pytest.fixture(scope="module")
+def GP(golden_dir):
+    return np.load(os.path.join(golden_dir, "cv2_preproc.npz"))
+
+
+def preproc_case(synth, GP, name):
+    sw, sh, mw, mh, dw, dh, seed = (int(v) for v in GP[f"{name}_cfg"])
+    img = synth.bgr_image(sw, sh, seed)
+    m1, m2 = synth.undistortion_maps(sw, sh, mw, mh, zoom=float(GP[f"{name}_zoom"]))
+    assert int(img.astype(np.int64).sum()) == int(GP[f"{name}_imgsum"])
+    assert [int(m.view(np.uint32).astype(np.uint64).sum()) for m in (m1, m2)] == [int(v) for v in GP[f"{name}_mapsum"]]
+    return img, m1, m2, dw, dh
+
+
+@pytest.mark.parametrize("name", ["half", "odd", "same", "up"])
+def test_preprocess_matches_cv2(oracle, synth, GP, name):
+    """remap(INTER_CUBIC, BORDER_CONSTANT) -> resize(INTER_LINEAR) -> BGR2GRAY of image_grabber.hpp:96-110 against
+    vectors made by the cv2 functions of the same names (tools/gen_golden_preproc.py): bit-exact."""
+    img, m1, m2, dw, dh = preproc_case(synth, GP, name)
+    und = oracle.remap_cubic_bgr(img, m1, m2)
+    assert int(und.astype(np.int64).sum()) == int(GP[f"{name}_undsum"])
+    assert np.array_equal(oracle.preprocess_bgr(img, m1, m2, dw, dh), GP[f"{name}_gray"])
