@@ -56,6 +56,13 @@ public:
         ensure(image.cols, image.rows);
         const int lap[2] = {vLappingArea.size() > 0 ? vLappingArea[0] : 0, vLappingArea.size() > 1 ? vLappingArea[1] : 0};
         check(orbx_extract_host(h_, image.data, image.step * (size_t)image.rows, (int)image.step, 1, lap));
+        return fetch_last(keypoints, descriptors);
+    }
+    /* The two halves of operator() for callers that hand the image over on the device (orbx/ImageGrabber.h chains
+     * ConvertImageToGPU into the extraction): prepare() makes the handle for a w x h image, fetch_last() waits for the
+     * extraction enqueued on it and returns what operator() returns. */
+    orbx_extractor* prepare(int w, int h) { ensure(w, h); return h_; }
+    int fetch_last(std::vector<orbx_keypoint>& keypoints, std::vector<uint8_t>& descriptors) {
         check(orbx_extractor_sync(h_));
         const int cap = orbx_extractor_capacity(h_);
         keypoints.resize(cap);

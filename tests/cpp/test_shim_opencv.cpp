@@ -2,10 +2,14 @@
 // against tests/cpp/opencv_stub and run the way upstream Frame's stereo constructor drives it: two extractors
 // (left / right, as upstream's two threads), operator() on each, then ComputeStereoMatches, reading mvImagePyramid
 // as std::vector<cv::Mat>-like.  usage: test_shim_opencv <left.raw> <right.raw> <w> <h> <nfeatures> <bf> <b> <out.blob>
+// With six more arguments  <bgr.raw> <map1.raw> <map2.raw> <src_w> <src_h> <out2.blob>  it then runs
+// ros2_orbslam3::ImageGrabber (include/orbx/ImageGrabber.h): ConvertImageToGPU(cv::Mat) to w x h, and the chained
+// ConvertAndExtract into exL.
 #include <cstdio>
 #include <cstdlib>
 #include <thread>
 #include "../../include/orbx/ORBextractor.h"
+#include "../../include/orbx/ImageGrabber.h"
 #include "blob.h"
 
 static std::vector<uint8_t> load(const char* p, size_t n) {
@@ -53,6 +57,23 @@ int main(int argc, char** argv) {
         for (int y = 0; y < L1.rows; ++y) memcpy(&roi[(size_t)y * L1.cols], L1.ptr(y), L1.cols);
         out.put("L1roi", roi);
         out.save(argv[8]);
+        if (argc >= 15) {
+            const int sw = atoi(argv[12]), sh = atoi(argv[13]);
+            std::vector<uint8_t> bgr = load(argv[9], (size_t)sw * sh * 3), m1 = load(argv[10], (size_t)sw * sh * 4),
+                                 m2 = load(argv[11], (size_t)sw * sh * 4);
+            cv::Mat im(sh, sw, CV_8UC3, bgr.data()), map1(sh, sw, CV_32FC1, m1.data()), map2(sh, sw, CV_32FC1, m2.data());
+            ros2_orbslam3::ImageGrabber igb(cv::Size(sw, sh), map1, map2, w, h);
+            cv::Mat grey = igb.ConvertImageToGPU(im);
+            Blob o2;
+            o2.put("grey", grey.data, (size_t)grey.rows * grey.cols);
+            std::vector<orbx_keypoint> k;
+            std::vector<uint8_t> d;
+            const int mono = igb.ConvertAndExtract(im.data, im.step, exL, k, d, lap);
+            o2.put_int("mono", mono);
+            o2.put("k", (const uint8_t*)k.data(), k.size() * sizeof(orbx_keypoint));
+            o2.put("d", d);
+            o2.save(argv[14]);
+        }
         cv::Mat none;
         if (exL(none, cv::Mat(), kL, dL, lap) != -1) return 4;                /* empty image -> -1 */
     } catch (const std::exception& e) {

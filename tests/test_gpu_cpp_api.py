@@ -261,3 +261,35 @@ def test_opencv_overload_two_threads_and_stereo(pkg, oracle, synth, tmp_path):
     assert (rows, cols, step, nlv) == (l1.shape[0] - 38, l1.shape[1] - 38, l1.shape[1], 8)
     assert np.array_equal(np.frombuffer(R["L1roi"], np.uint8).reshape(rows, cols), l1[19:-19, 19:-19])
     assert psum == int(l1[19 + 20:19 + 31, 19 + 30:19 + 41].astype(np.int64).sum()) and border_px == int(l1[0, 0])
+
+
+def test_image_grabber_cpp(pkg, oracle, synth, tmp_path):
+    """ros2_orbslam3::ImageGrabber (include/orbx/ImageGrabber.h, cv::Mat form against the OpenCV stub):
+    ConvertImageToGPU equals the oracle's remap -> resize -> gray bit for bit, and the chained ConvertAndExtract equals
+    extracting that gray image through the C ABI."""
+    so = pkg.orbx.build()
+    exe = str(tmp_path / "test_shim_opencv")
+    subprocess.check_call(["g++", "-std=c++17", "-O1", "-Wall", "-Werror", "-DORBX_WITH_OPENCV", "-I" + os.path.join(ROOT, "tests", "cpp", "opencv_stub"),
+                           "-pthread", "-o", exe, os.path.join(ROOT, "tests", "cpp", "test_shim_opencv.cpp"), "-L" + os.path.dirname(so),
+                           "-lorbx", "-Wl,-rpath," + os.path.dirname(so)])
+    w, h, nf, sw, sh = 640, 480, 1000, 1024, 768
+    left, right = synth.stereo_pair(w, h, 5)
+    bgr = synth.bgr_image(sw, sh, 91)
+    m1, m2 = synth.undistortion_maps(sw, sh, sw, sh, zoom=0.9)
+    for name, arr in (("l.raw", left), ("r.raw", right), ("bgr.raw", bgr), ("m1.raw", m1), ("m2.raw", m2)):
+        (tmp_path / name).write_bytes(np.ascontiguousarray(arr).tobytes())
+    o1, o2 = str(tmp_path / "o1.blob"), str(tmp_path / "o2.blob")
+    r = subprocess.run([exe, str(tmp_path / "l.raw"), str(tmp_path / "r.raw"), str(w), str(h), str(nf), "47.9", "0.11", o1,
+                        str(tmp_path / "bgr.raw"), str(tmp_path / "m1.raw"), str(tmp_path / "m2.raw"), str(sw), str(sh), o2],
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and r.stdout.startswith("OK"), r.stdout + r.stderr
+    R = read_blob(o2)
+    grey = oracle.preprocess_bgr(bgr, m1, m2, w, h)
+    assert np.array_equal(np.frombuffer(R["grey"], np.uint8).reshape(h, w), grey)
+    ex = pkg.orbx.ORBextractor(nf, 1.2, 8, 20, 7)
+    k, d, mono = ex(grey, (0, 0))
+    ex.close()
+    dt = np.dtype([("x", "f4"), ("y", "f4"), ("size", "f4"), ("angle", "f4"), ("response", "f4"), ("octave", "i4"), ("class_id", "i4")])
+    gk = np.frombuffer(R["k"], dt)
+    assert len(gk) == len(k) > 500 and _i32(R["mono"])[0] == mono
+    assert gk.tobytes() == k.tobytes() and np.array_equal(np.frombuffer(R["d"], np.uint8).reshape(-1, 32), d)
