@@ -772,8 +772,26 @@ def main():
             stages[n] = {"ms": round(float(stage[i]), 4), "alg_bytes_per_frame": alg[n], "gbs": round(gbs, 1),
                          "frac_hbm": round(gbs / hbm_peak, 4)}
         dom_gbs = stages[names[dom]]["gbs"]
-        kern = {"pyramid": "k_resize_band", "fast": "k_fast_units", "octree": "k_octree", "order": "k_order",
-                "blur": "k_blur7", "describe": "k_orient_describe"}[names[dom]]
+        stage_kernels = {"pyramid": ["k_level0", "k_resize_band"], "fast": ["k_fast_units"], "octree": ["k_octree"], "order": ["k_order"],
+                         "blur": ["k_blur7"], "describe": ["k_orient_describe"]}
+        kern = stage_kernels[names[dom]][-1]
+        # issue-slot view of every stage: warp instructions of one 256-frame step from the committed ncu capture (they do not
+        # depend on timing), over the stage time measured in THIS run, against one instruction per clock per scheduler
+        # (4 schedulers per SM) at the SM clock sampled in this run
+        try:
+            cap = json.load(open(os.path.join(ROOT, "profiles", TRAFFIC_FILE)))["kernels"]
+            sm_mhz = float(clocks.get("sm_mhz") or 0) or 1965.0
+            issue_peak = 148 * 4 * sm_mhz * 1e6
+            for n in names:
+                wi = sum(cap[k]["warp_instructions"] for k in stage_kernels[n]) * B / 256
+                stages[n]["warp_instr"] = int(wi)
+                stages[n]["issue_frac"] = round(wi / (stage[names.index(n)] * 1e-3) / issue_peak, 3) if stage[names.index(n)] > 0 else None
+            step_wi = sum(stages[n]["warp_instr"] for n in names)
+            issue = {"warp_instr_per_step": int(step_wi), "peak_warp_instr_per_s": issue_peak, "sm_mhz_used": sm_mhz,
+                     "floor_ms_per_step": round(step_wi / issue_peak * 1e3, 4), "frac_of_issue_ceiling": round(step_wi / issue_peak * 1e3 / (ms / args.steps), 3),
+                     "source": TRAFFIC_FILE + " (instruction counts) x this run's times"}
+        except Exception:
+            issue = None
         traffic = None          # DRAM bytes per launch of the dominant kernel, from the committed ncu --set full capture
         try:
             tr = json.load(open(os.path.join(ROOT, "profiles", TRAFFIC_FILE)))["kernels"][kern]
@@ -806,6 +824,7 @@ def main():
                          "launch_scope": "all launches of the stage for one 256-frame step on one stream (FAST: 2 grids, short and tall strips)",
                          "peak_source": "measured" if peaks else "fallback"},
             "stages": stages,
+            "issue_roofline": issue,
         }
         if not args.no_matching:
             line["matching"] = matching_bench(pkg, torch, local, ex, B)

@@ -16,7 +16,7 @@ timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --c
 # whole-batch kernels on one stream (ORBX_LANES=1 ORBX_FORK_BLUR=0): 14 extraction launches + 2 stereo launches per step
 ORBX_LANES=1 ORBX_FORK_BLUR=0 ORBX_GRAPH=0 timeout 900 ncu --set full --clock-control none --import-source on -s 16 -c 16 -f -o $out/r2_step_full_$tag \
   python tools/profile_step.py --steps 2 --stereo > $out/ncu_full_$tag.log 2>&1; tail -1 $out/ncu_full_$tag.log
-timeout 900 ncu --set full --clock-control none -k 'regex:k_search|k_fuse|k_knn|knn2|k_distinctive|k_mean_value|k_assign_grid|k_features_in_area' -c 16 -f \
+timeout 900 ncu --set full --clock-control none -k 'regex:k_search|k_fuse|k_knn|knn2|k_distinctive|k_mean_value|k_assign_grid|k_features_in_area|k_remap|k_resize_gray' -c 20 -f \
   -o $out/r2_matcher_full_$tag python tools/profile_step.py --steps 1 --knn 4096 --matcher > $out/ncu_matcher_$tag.log 2>&1; tail -1 $out/ncu_matcher_$tag.log
 # the 2-NN kernel at a shape that fills the GPU (65536 queries x 1 M rows: 64 x 1 CTAs of 1024 queries)
 timeout 900 ncu --set full --clock-control none -k 'regex:k_knn2' -c 2 -f -o $out/r2_knn_full_$tag python tools/profile_step.py --steps 1 --knn 65536 --knn-rows 1048576 > $out/ncu_knn_$tag.log 2>&1; tail -1 $out/ncu_knn_$tag.log

@@ -72,4 +72,14 @@ if a.matcher:
     rng = np.random.default_rng(7)
     m.ComputeDistinctiveDescriptors([rng.integers(0, 256, (int(k), 32), dtype=np.uint8) for k in rng.integers(3, 40, 2000)])
     m.AssignFeaturesToGrid(Fs)
+    m.MeanValue([rng.integers(0, 256, (int(k), 32), dtype=np.uint8) for k in rng.integers(3, 40, 2000)])
+    # ROS-side pre-processing at the reference node's shape (32 frames of 2048x1536 BGR -> 614x460 gray), both paths
+    m1, m2 = sy.undistortion_maps(2048, 1536, 2048, 1536, k1=-0.12, k2=0.02, zoom=0.97)
+    bgr = np.stack([sy.bgr_image(2048, 1536, 300 + f) for f in range(2)] * 16)
+    for fused in ("1", "0"):
+        os.environ["ORBX_PREPROC_FUSED"] = fused
+        g = ox.ImageGrabber((2048, 1536), m1, m2, 614, 460, max_batch=32)
+        g.ConvertImageToGPU(bgr)
+        g.close()
+    os.environ.pop("ORBX_PREPROC_FUSED")
     print("matcher entry points done")
