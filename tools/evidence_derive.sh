@@ -4,7 +4,7 @@
 tag=${1:-x}
 cd "$(dirname "$0")/.."
 g=gpurun_out; p=profiles
-cp $g/r2_pytest_$tag.log $g/r2_bench_$tag.json $g/r2_bench_${tag}_ref.json $g/r2_launches_$tag.csv $p/ 2>/dev/null
+cp $g/r2_pytest_$tag.log $g/r2_bench_$tag.json $g/r2_bench_${tag}_ref.json $g/r2_launches_$tag.csv $g/r2_fuzz_extractor_$tag.log $g/r2_fuzz_matcher_$tag.log $p/ 2>/dev/null
 python tools/ncu_traffic.py $g/r2_step_full_$tag.ncu-rep "ORBX_LANES=1 ORBX_FORK_BLUR=0 ORBX_GRAPH=0 ncu --set full: one 256-frame extraction step + stereo (tools/evidence.sh $tag)" > $p/r2_traffic.json
 python tools/ncu_traffic.py $g/r2_matcher_full_$tag.ncu-rep "ncu --set full: one call of every matcher kernel, 8 problems each (tools/evidence.sh $tag)" > $p/r2_traffic_matcher.json
 python tools/ncu_traffic.py $g/r2_knn_full_$tag.ncu-rep "ncu --set full: k_knn2 65536 queries x 1 M rows (tools/evidence.sh $tag)" > $p/r2_traffic_knn.json
