@@ -13,6 +13,13 @@
  * Header-only.  With ORBX_WITH_OPENCV the cv::Mat / cv::KeyPoint signature is provided; without
  * it (this image has no OpenCV C++) the same calls take the POD views below, whose memory layout
  * equals cv::KeyPoint (28 bytes) and a continuous CV_8UC1 matrix.
+ * The FORK's own call form is kept as well, so that its call sites (src/Tracking.cc:111, src/Frame.cc:178-189)
+ * compile unchanged: the 8-argument constructor (nFeatures, nFastFeatures, scaleFactor, nlevels, iniThFAST,
+ * minThFAST, imageWidth, imageHeight; include/ORBextractor.h:55-56), extractFeatures(image) ->
+ * optional<tuple<shared_ptr<vector<KeyPoint>>, descriptors>> (:62, src/ORBextractor.cc:543-585) with the fork's 24-byte
+ * KeyPoint (include/KeyPoint.h:7-18), and mvBlurredImagePyramid (:92).  The RESULTS are upstream's (north_star):
+ * per-cell FAST with the threshold retry, no nFastFeatures cap (the argument is kept for its getter only), 7x7 sigma-2
+ * blur, EDGE_THRESHOLD 19, coordinates scaled to level 0.
  * No CPU fallback: a failing C-ABI call throws std::runtime_error with orbx_last_error().
  */
 #ifndef ORBX_ORBEXTRACTOR_H
@@ -20,8 +27,11 @@
 #include <cstddef>
 #include <cstdint>
 #include <cstring>
+#include <memory>
+#include <optional>
 #include <stdexcept>
 #include <string>
+#include <tuple>
 #include <vector>
 
 #include "../orbx.h"
@@ -39,11 +49,63 @@ struct ImageView {
     bool empty() const { return !data || cols <= 0 || rows <= 0; }
 };
 
+/* the fork's keypoint record (include/KeyPoint.h:7-18: cv::Point2f pt; int response; float size; int octave; float angle).
+ * Inside the fork's tree, where that header is on the include path, compile with -DORBX_FORK_KEYPOINT_HEADER='"KeyPoint.h"'
+ * and its own definition is used instead of this copy of the layout. */
+#ifdef ORBX_FORK_KEYPOINT_HEADER
+}  // namespace ORB_SLAM3
+#include ORBX_FORK_KEYPOINT_HEADER
+namespace ORB_SLAM3 {
+#else
+struct KeyPoint {
+    struct { float x, y; } pt;
+    int response;
+    float size;
+    int octave;
+    float angle;
+};
+#endif
+static_assert(sizeof(KeyPoint) == 24, "ORB_SLAM3::KeyPoint layout");
+
 class ORBextractor {
 public:
     ORBextractor(int nfeatures, float scaleFactor, int nlevels, int iniThFAST, int minThFAST, int device = 0)
         : nfeatures_(nfeatures), scaleFactor_(scaleFactor), nlevels_(nlevels), iniThFAST_(iniThFAST),
           minThFAST_(minThFAST), device_(device) { mvImagePyramid.owner_ = this; }
+    /* the fork's constructor (include/ORBextractor.h:55-56): the image size is known up front, so the handle, the
+     * pyramid buffers and the tables exist when it returns (the fork's AllocatePyramid, src/ORBextractor.cc:147) */
+    ORBextractor(int nFeatures, int nFastFeatures, float scaleFactor, int nlevels, int iniThFAST, int minThFAST, int imageWidth,
+                 int imageHeight, int device = 0)
+        : ORBextractor(nFeatures, scaleFactor, nlevels, iniThFAST, minThFAST, device) {
+        nFastFeatures_ = nFastFeatures;
+        ensure(imageWidth, imageHeight);
+    }
+    int GetFastFeatures() const { return nFastFeatures_; }
+    /* the fork's extractFeatures (src/ORBextractor.cc:543-585): nullopt when the image is empty, of another size than the
+     * constructor's, or yields no keypoint (the fork cannot represent zero keypoints, :501) */
+    std::optional<std::tuple<std::shared_ptr<std::vector<KeyPoint>>, std::vector<uint8_t>>> extractFeatures(const ImageView& im) {
+        if (im.empty() || (w_ && (im.cols != w_ || im.rows != hgt_))) return std::nullopt;
+        std::vector<orbx_keypoint> k;
+        std::vector<uint8_t> d;
+        (*this)(im, ImageView{}, k, d, std::vector<int>{0, 0});
+        if (k.empty()) return std::nullopt;
+        auto keys = std::make_shared<std::vector<KeyPoint>>(k.size());
+        for (size_t i = 0; i < k.size(); ++i) {
+            KeyPoint& q = (*keys)[i];
+            q.pt.x = k[i].x; q.pt.y = k[i].y; q.response = (int)k[i].response; q.size = k[i].size; q.octave = k[i].octave;
+            q.angle = k[i].angle;
+        }
+        return std::make_tuple(keys, std::move(d));
+    }
+    /* mvBlurredImagePyramid[level] of the fork (include/ORBextractor.h:92): the blurred level, w x h, dense */
+    std::vector<uint8_t> BlurredImagePyramid(int level) {
+        if (!h_) throw std::runtime_error("orbx: mvBlurredImagePyramid read before the first extraction");
+        int w = 0, h = 0;
+        check(orbx_extractor_level_size(h_, level, &w, &h));
+        std::vector<uint8_t> out((size_t)w * h);
+        check(orbx_extractor_blurred_download(h_, 0, level, out.data()));
+        return out;
+    }
     ~ORBextractor() { if (h_) orbx_extractor_destroy(h_); }
     ORBextractor(const ORBextractor&) = delete;
     ORBextractor& operator=(const ORBextractor&) = delete;
@@ -200,6 +262,7 @@ private:
     std::vector<LevelBuf> lv_;
 
     int nfeatures_; float scaleFactor_; int nlevels_, iniThFAST_, minThFAST_, device_;
+    int nFastFeatures_ = 0;
     orbx_extractor* h_ = nullptr;
     int w_ = 0, hgt_ = 0;
     bool tables_ok_ = false;

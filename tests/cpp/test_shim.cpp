@@ -34,6 +34,21 @@ int main(int argc, char** argv) {
         fclose(o);
         ORB_SLAM3::ImageView none;
         if (ex(none, none, kps, desc, lap) != -1) return 4;    // empty image -> -1
+        {   // the fork's call form: 8-argument constructor + extractFeatures, same results
+            ORB_SLAM3::ORBextractor fx(nf, 7000, 1.2f, 8, 20, 7, w, h);
+            if (fx.GetScaleFactors() != sf || fx.GetFastFeatures() != 7000) return 6;
+            auto r = fx.extractFeatures(ORB_SLAM3::ImageView{img.data(), w, h, (size_t)w});
+            if (!r.has_value()) return 7;
+            auto [keys, d] = r.value();
+            if (keys->size() != kps.size() || d != desc) return 8;
+            for (size_t i = 0; i < kps.size(); ++i) {
+                const ORB_SLAM3::KeyPoint& a = (*keys)[i];
+                if (a.pt.x != kps[i].x || a.pt.y != kps[i].y || a.response != (int)kps[i].response || a.size != kps[i].size ||
+                    a.octave != kps[i].octave || a.angle != kps[i].angle) return 9;
+            }
+            if (fx.BlurredImagePyramid(1).size() != (size_t)L1.cols * L1.rows) return 10;
+            if (fx.extractFeatures(none).has_value()) return 11;
+        }
     } catch (const std::exception& e) {
         fprintf(stderr, "%s\n", e.what());
         return 1;
