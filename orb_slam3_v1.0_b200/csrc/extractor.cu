@@ -1514,8 +1514,8 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
     *out = nullptr;
     if (p->nlevels < 1 || p->nlevels > ORBX_MAX_LEVELS || p->nfeatures < 1 || p->scale_factor <= 1.0f ||
         p->width < 64 || p->height < 64 || p->width > 4000 || p->height > 4000 || p->max_batch < 1 ||
-        p->min_th_fast < 1 || p->min_th_fast > 127 || p->ini_th_fast < p->min_th_fast || p->ini_th_fast > 255) {
-        orbx_set_error("unsupported parameters (need 64<=w,h<=4000, 1<=minTh<=127, minTh<=iniTh<=255, nlevels<=%d)", ORBX_MAX_LEVELS);
+        p->min_th_fast < 1 || p->ini_th_fast < p->min_th_fast || p->ini_th_fast > 255) {
+        orbx_set_error("unsupported parameters (need 64<=w,h<=4000, 1<=minTh<=iniTh<=255, nlevels<=%d)", ORBX_MAX_LEVELS);
         return ORBX_ERR_INVALID;
     }
     int ndev = 0;

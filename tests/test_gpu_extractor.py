@@ -220,6 +220,7 @@ def test_cpp_shim_matches_oracle(pkg, oracle, synth, tmp_path):
     (512, 384, 500, 1.2, 8, 40, 40, 203),         # iniThFAST == minThFAST: no retry pass
     (512, 384, 3000, 1.2, 8, 12, 5, 204),         # more features than most levels can supply
     (400, 300, 600, 1.25, 6, 130, 20, 205),       # threshold above 127 (other branch of the packed compare)
+    (400, 300, 600, 1.25, 6, 200, 140, 208),      # both thresholds above 127: the retry pass takes that branch too
     (333, 257, 400, 1.2, 5, 20, 7, 206),          # odd sizes
     (1920, 1080, 2000, 1.2, 8, 20, 7, 207),       # full HD
 ])
