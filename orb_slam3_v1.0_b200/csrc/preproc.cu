@@ -217,12 +217,15 @@ __device__ __forceinline__ int pp_bilinear_gray(unsigned p00, unsigned p01, unsi
  * Thread = one OUTPUT pixel, all frames: it evaluates exactly the (up to) four map pixels its 2x2 block names -- the
  * same integers k_remap_cubic would have stored -- and nothing is written but the gray byte.  Chosen at create time
  * when 4 * dw * dh < mw * mh (fewer remap evaluations than the two-kernel path).
- * Measured on a B200, 32 frames of 2048x1536 -> 614x460 (tools/preproc_bench.py): two kernels 1.02 ms, this kernel
- * 0.487 ms (239 registers, 8 warps per SM, 64 independent loads per thread and frame); a variant with four lanes per
- * output pixel (one corner each, 104 registers, values exchanged by shuffles) took 0.594 ms and was dropped, and
- * capping the registers at 128 spills the weights. */
+ * Measured on a B200, 32 frames of 2048x1536 -> 614x460 (tools/preproc_bench.py): two kernels 1.02 ms; this kernel
+ * 0.487 ms uncapped (239 registers, 8 warps per SM: ncu shows 12 % warps active and 32 % issue active, DRAM traffic
+ * equal to source + result, i.e. it waits on its own scattered loads) and 0.371 ms with two CTAs per SM (128 registers,
+ * 304 bytes of spill per thread: the occupancy is worth more than the spill costs; 128-thread CTAs x 4 give the same
+ * 0.366 ms, x 3 0.433 ms).  A variant with four lanes per output pixel (one corner each, 104 registers, values
+ * exchanged by shuffles) took 0.594 ms and was dropped; a partially unrolled row loop indexes the weight registers
+ * dynamically and sends them to local memory. */
 #ifndef PP_FUSED_MINB
-#define PP_FUSED_MINB 1
+#define PP_FUSED_MINB 2
 #endif
 __global__ void __launch_bounds__(PP_THREADS, PP_FUSED_MINB)
 k_remap_resize_gray(const uint8_t* __restrict__ src, size_t src_frame, int src_pitch, int sw, int sh,
