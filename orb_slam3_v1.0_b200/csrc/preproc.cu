@@ -158,6 +158,9 @@ __device__ __forceinline__ unsigned pp_tap_eval(const PpTap& t, const uint8_t* _
             const uint8_t* q = base + (size_t)r * src_pitch;
             const unsigned sft = ((unsigned)(uintptr_t)q & 3u) * 8u;
             const unsigned* a = reinterpret_cast<const unsigned*>((uintptr_t)q & ~(uintptr_t)3);
+            /* the 16-byte window stays inside source row iy + r */
+            ORBX_DCHECK((const uint8_t*)a >= img + (size_t)(t.iy + r) * src_pitch &&
+                        (const uint8_t*)(a + 4) <= img + (size_t)(t.iy + r) * src_pitch + (size_t)sw * 3 && t.iy + r >= 0 && t.iy + r < sh);
             const unsigned a0 = __ldg(a), a1 = __ldg(a + 1), a2 = __ldg(a + 2), a3 = __ldg(a + 3);
             const unsigned p0 = __funnelshift_r(a0, a1, sft), p1 = __funnelshift_r(a1, a2, sft), p2 = __funnelshift_r(a2, a3, sft);
             /* bytes B0 G0 R0 B1 | G1 R1 B2 G2 | R2 B3 G3 R3 -> the four taps of one channel in one word */
@@ -175,6 +178,7 @@ __device__ __forceinline__ unsigned pp_tap_eval(const PpTap& t, const uint8_t* _
             for (int c = 0; c < 4; ++c) {
                 const int xx = t.ix + c;
                 if (xx < 0 || xx >= sw) continue;
+                ORBX_DCHECK(yy >= 0 && yy < sh && xx >= 0 && xx < sw);
                 const int wq = (int)(short)((unsigned)t.w[2 * r + (c >> 1)] >> ((c & 1) * 16));
                 const uint8_t* q = img + (size_t)yy * src_pitch + (size_t)xx * 3;
                 ab += wq * q[0]; ag += wq * q[1]; ar += wq * q[2];
@@ -238,6 +242,7 @@ k_remap_resize_gray(const uint8_t* __restrict__ src, size_t src_frame, int src_p
     const int2 tx = __ldg(xtab + x), ty = __ldg(ytab + y);
     const int x0 = tx.x, x1 = min(x0 + 1, mw - 1), y0 = min(max(ty.x, 0), mh - 1), y1 = min(max(ty.x + 1, 0), mh - 1);
     const int ax0 = (short)(tx.y & 0xffff), ax1 = tx.y >> 16, ay0 = (short)(ty.y & 0xffff), ay1 = ty.y >> 16;
+    ORBX_DCHECK(x0 >= 0 && x1 < mw && y0 >= 0 && y1 < mh);
     PpTap t00, t01, t10, t11;
     pp_tap_load(t00, sxy, itab, y0 * mw + x0, sw, sh);
     pp_tap_load(t01, sxy, itab, y0 * mw + x1, sw, sh);

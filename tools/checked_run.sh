@@ -9,6 +9,6 @@ export ORBX_LIB_DIR=$PWD/orb_slam3_v1.0_b200/lib_checked
 {
   echo "== library: $ORBX_LIB_DIR/liborbx.so (-DORBX_CHECKS), $(cuobjdump -sass $ORBX_LIB_DIR/liborbx.so | grep -c 'BPT.TRAP') trap sites in SASS"
   python tools/sanitize_run.py 2>&1 | tail -4
-  python -m pytest tests/test_gpu_extractor.py tests/test_gpu_matcher.py tests/test_zz_no_alloc.py -m gpu -x -q 2>&1 | tail -4
+  python -m pytest tests/test_gpu_extractor.py tests/test_gpu_matcher.py tests/test_gpu_preproc.py tests/test_zz_no_alloc.py -m gpu -x -q 2>&1 | tail -4
   echo "== ORBX_DCHECK failures printed: $(grep -c 'ORBX_DCHECK failed' gpurun_out/r2_checked_run.log 2>/dev/null || echo 0)"
 } 2>&1 | tee gpurun_out/r2_checked_run.log
