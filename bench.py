@@ -181,6 +181,42 @@ def cpp_operator_latency(pkg, frame):
         return {"unavailable": str(ex)[:160]}
 
 
+def cpp_matcher_latency(pkg):
+    """One SearchByProjection call (nprob = 1) through the C++ layers: tools/matcher_latency.cpp times the flattened-view
+    wrapper of include/orbx/ORBmatcher.h and the reference-signature template of include/orbx/ORBmatcher_ref.h (object graphs
+    of mock SLAM types; flattening and write-back included) on 1000 keypoints x 1500 map points in ordinary host memory."""
+    import struct
+    import subprocess
+    import tempfile
+    try:
+        so = pkg.orbx.build()
+        F = pkg.synth.frame_view(1000, seed=1)
+        MP = pkg.synth.projection_problem(F, 1500, seed=101)
+        A = {"sbp.F.kx": F["kx"].astype(np.float32), "sbp.F.ky": F["ky"].astype(np.float32), "sbp.F.koct": F["koct"].astype(np.int32),
+             "sbp.F.desc": F["desc"], "sbp.F.grid": np.array([F["minx"], F["miny"], F["gw_inv"], F["gh_inv"]], np.float32),
+             "sbp.F.gridi": np.array([F["gcols"], F["grows"]], np.int32), "sbp.F.scale": F["scale"].astype(np.float32),
+             "sbp.params": np.array([3.0, 0.0, 0.0, 0.8], np.float32)}
+        for k, t in (("inview", np.uint8), ("x", np.float32), ("y", np.float32), ("level", np.int32), ("viewcos", np.float32),
+                     ("depth", np.float32), ("desc", np.uint8)):
+            A["sbp.MP." + k] = MP[k].astype(t)
+        with tempfile.TemporaryDirectory() as td:
+            exe, blob = os.path.join(td, "matcher_latency"), os.path.join(td, "in.blob")
+            subprocess.check_call(["g++", "-std=c++17", "-O2", "-o", exe, os.path.join(ROOT, "tools", "matcher_latency.cpp"),
+                                   "-L" + os.path.dirname(so), "-lorbx", "-Wl,-rpath," + os.path.dirname(so)],
+                                  stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, timeout=180)
+            with open(blob, "wb") as fh:
+                for k, v in A.items():
+                    v = np.ascontiguousarray(v)
+                    fh.write(struct.pack("<I", len(k))); fh.write(k.encode()); fh.write(struct.pack("<Q", v.nbytes)); fh.write(v.tobytes())
+            r = subprocess.run([exe, blob, "300"], capture_output=True, text=True, timeout=120)
+            out = json.loads(r.stdout.strip().splitlines()[-1])
+            out["note"] = ("C++ callers, nprob = 1, median wall-clock ms incl. packing, H2D, kernel, D2H, sync; compare "
+                           "cpu_baseline.matching.search_by_projection.ms_per_problem_1thread")
+            return out
+    except Exception as ex:     # noqa: BLE001 - a secondary leg must not take the line down
+        return {"unavailable": str(ex)[:160]}
+
+
 def _dbg(torch, tag):
     if os.environ.get("ORBX_BENCH_DEBUG_SYNC"):
         torch.cuda.synchronize()
@@ -833,6 +869,7 @@ def main():
             line["preprocessing"] = preproc_bench(pkg, torch, local)
             line["single_frame_latency"] = single_frame_latency(pkg, local, frames[0])
             line["cpp_operator_latency"] = cpp_operator_latency(pkg, frames[0])
+            line["cpp_matcher_latency"] = cpp_matcher_latency(pkg)
         if numa is not None:
             os.sched_setaffinity(0, numa[2])          # the CPU baseline gets every core back
         if not args.no_cpu_baseline and world == 1:
