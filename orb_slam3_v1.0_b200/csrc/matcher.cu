@@ -1680,8 +1680,9 @@ extern "C" orbx_status orbx_mean_value(orbx_matcher* m, int nsets, const int* se
 /* ORBmatcher::SearchByBoW(KeyFrame, Frame, vpMapPointMatches, nnRatio, checkOrientation),
  * reference src/ORBmatcher.cc:133-327.  A feature index sits under exactly one vocabulary node, so
  * the reference's sequential "first KeyFrame point claims the Frame keypoint" rule only couples
- * points of the same node: one thread walks one shared node in the reference's order (exact), the
- * nodes of a problem run in parallel, one CTA per (KeyFrame, Frame) problem.  Includes the fork's
+ * points of the same node: one warp walks one shared node in the reference's order (exact; its lanes share each
+ * point's scan of the node's Frame keypoints), the nodes of a problem run in parallel, one CTA per (KeyFrame, Frame)
+ * problem.  Includes the fork's
  * right-camera branch (Nleft != -1), whose acceptance is nested under the left test (:238-283). */
 struct BowProb {
     int nF, ntasks, nleft, checkOri;
@@ -1713,38 +1714,61 @@ __global__ void __launch_bounds__(MT) k_search_by_bow(const uint8_t* __restrict_
     for (int i = tid; i < P.nF; i += MT) match[i] = -1;
     __syncthreads();
     int mycount = 0;
-    for (int t = tid; t < P.ntasks; t += MT) {
+    /* One WARP per shared node: the KeyFrame points of the node are walked in the reference's order (their claims are
+     * sequential), and for each of them the 32 lanes scan the node's Frame keypoints in parallel.  The sequential scan
+     * keeps the FIRST minimum (strict <) and the second-smallest distance of the multiset; packed (distance, position)
+     * keys reduced by a butterfly give exactly that: the smallest key is the first minimum, and the runner-up's distance
+     * is the second-smallest distance. */
+    const int lane = tid & 31;
+    const unsigned KNONE = 0xFFFFFFFFu;
+    for (int t = tid >> 5; t < P.ntasks; t += MT / 32) {
         const int4 T = tasks[t];
         for (int a = 0; a < T.y; ++a) {
             const int realIdxKF = nidxK[T.x + a];
             if (!hasmpK[realIdxKF]) continue;                      /* !pMP || pMP->isBad() */
             const uint4 q0 = descK[2 * realIdxKF], q1 = descK[2 * realIdxKF + 1];
-            int bestDist1 = 256, bestIdxF = -1, bestDist2 = 256;
-            int bestDist1R = 256, bestIdxFR = -1, bestDist2R = 256;
-            for (int b = 0; b < T.w; ++b) {
+            unsigned k1 = KNONE, k2 = KNONE, k1R = KNONE, k2R = KNONE;      /* dist << 20 | position in the node */
+            for (int b = lane; b < T.w; b += 32) {
                 const int realIdxF = nidxF[T.z + b];
                 if (match[realIdxF] >= 0) continue;                /* vpMapPointMatches[realIdxF] */
-                const int dist = hamming256(q0, q1, descF[2 * realIdxF], descF[2 * realIdxF + 1]);
+                const unsigned key = ((unsigned)hamming256(q0, q1, descF[2 * realIdxF], descF[2 * realIdxF + 1]) << 20) | (unsigned)b;
                 if (P.nleft == -1 || realIdxF < P.nleft) {
-                    if (dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdxF = realIdxF; }
-                    else if (dist < bestDist2) bestDist2 = dist;
+                    if (key < k1) { k2 = k1; k1 = key; } else if (key < k2) k2 = key;
                 } else {
-                    if (dist < bestDist1R) { bestDist2R = bestDist1R; bestDist1R = dist; bestIdxFR = realIdxF; }
-                    else if (dist < bestDist2R) bestDist2R = dist;
+                    if (key < k1R) { k2R = k1R; k1R = key; } else if (key < k2R) k2R = key;
                 }
             }
-            if (bestDist1 <= TH_LOW) {
-                if ((float)bestDist1 < P.nnRatio * (float)bestDist2) {
-                    match[bestIdxF] = realIdxKF;
-                    if (P.checkOri) atomicAdd(&s_hist[rot_bin(kangK[realIdxKF], kangF[bestIdxF])], 1);
-                    ++mycount;
-                }
-                if (bestDist1R <= TH_LOW) {                        /* `|| true` in the fork: no ratio test */
-                    match[bestIdxFR] = realIdxKF;
-                    if (P.checkOri) atomicAdd(&s_hist[rot_bin(kangK[realIdxKF], kangF[bestIdxFR])], 1);
-                    ++mycount;
+#pragma unroll
+            for (int off = 16; off; off >>= 1) {
+                const unsigned o1 = __shfl_xor_sync(0xffffffffu, k1, off), o2 = __shfl_xor_sync(0xffffffffu, k2, off);
+                if (o1 < k1) { k2 = min(k1, o2); k1 = o1; } else k2 = min(k2, o1);
+            }
+            if (P.nleft != -1) {
+#pragma unroll
+                for (int off = 16; off; off >>= 1) {
+                    const unsigned o1 = __shfl_xor_sync(0xffffffffu, k1R, off), o2 = __shfl_xor_sync(0xffffffffu, k2R, off);
+                    if (o1 < k1R) { k2R = min(k1R, o2); k1R = o1; } else k2R = min(k2R, o1);
                 }
             }
+            if (lane == 0) {
+                const int bestDist1 = min((int)(k1 >> 20), 256), bestDist2 = min((int)(k2 >> 20), 256);
+                const int bestDist1R = min((int)(k1R >> 20), 256);
+                if (bestDist1 <= TH_LOW) {
+                    if ((float)bestDist1 < P.nnRatio * (float)bestDist2) {
+                        const int bestIdxF = nidxF[T.z + (int)(k1 & 0xFFFFFu)];
+                        match[bestIdxF] = realIdxKF;
+                        if (P.checkOri) atomicAdd(&s_hist[rot_bin(kangK[realIdxKF], kangF[bestIdxF])], 1);
+                        ++mycount;
+                    }
+                    if (bestDist1R <= TH_LOW) {                        /* `|| true` in the fork: no ratio test */
+                        const int bestIdxFR = nidxF[T.z + (int)(k1R & 0xFFFFFu)];
+                        match[bestIdxFR] = realIdxKF;
+                        if (P.checkOri) atomicAdd(&s_hist[rot_bin(kangK[realIdxKF], kangF[bestIdxFR])], 1);
+                        ++mycount;
+                    }
+                }
+            }
+            __syncwarp();                                          /* the claim is visible to the next point's scan */
         }
     }
     __syncthreads();
@@ -1778,6 +1802,7 @@ extern "C" orbx_status orbx_search_by_bow(orbx_matcher* m, int nprob, const orbx
         const orbx_kf_view &A = KF[p], &B = F[p];
         BowProb& P = probs[p];
         memset(&P, 0, sizeof(P));
+        if (B.n >= (1 << 20)) { orbx_set_error("problem %d: %d Frame keypoints (the node scan packs positions in 20 bits)", p, B.n); return ORBX_ERR_INVALID; }
         if (A.n < 0 || B.n < 0 || A.nnodes < 0 || B.nnodes < 0 || (A.n > 0 && (!A.desc || !A.has_mp || (checkOrientation && !A.kangle))) ||
             (B.n > 0 && (!B.desc || (checkOrientation && !B.kangle))) ||
             (A.nnodes > 0 && (!A.node_id || !A.node_off || !A.node_idx)) || (B.nnodes > 0 && (!B.node_id || !B.node_off || !B.node_idx))) {
