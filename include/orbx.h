@@ -396,7 +396,10 @@ orbx_status orbx_matcher_synchronize(orbx_matcher* m);
  *       cv::cuda::remap(INTER_CUBIC, BORDER_CONSTANT 0) -> cv::cuda::resize(INTER_LINEAR) -> cvtColor(BGR2GRAY)
  * One handle = one camera.  map_x / map_y are the two CV_32FC1 planes of initUndistortRectifyMap (map_w x map_h,
  * dense, host memory; copied).  Input: 8-bit BGR interleaved, src_w x src_h; output: 8-bit gray, dst_w x dst_h, dense.
- * The arithmetic is that of the CPU cv::remap / cv::resize / cv::cvtColor, bit for bit (csrc/preproc.cu header). */
+ * The arithmetic is that of the CPU cv::remap / cv::resize / cv::cvtColor, bit for bit (csrc/preproc.cu header).
+ * Calls on one handle share its staging buffers: whatever streams they are enqueued on, each call is ordered after the
+ * previous one on the device (an event), so one handle can feed several rotating extractor handles; the HOST side of
+ * a handle is not re-entrant (one calling thread per handle). */
 typedef struct orbx_preproc orbx_preproc;
 orbx_status orbx_preproc_create(int src_w, int src_h, const float* map_x, const float* map_y, int map_w, int map_h,
                                 int dst_w, int dst_h, int max_batch, int device, orbx_preproc** out);

@@ -55,7 +55,21 @@ struct orbx_preproc {
     uint8_t* d_gray = nullptr;      /* max_batch * dh * dw */
     bool fused = false;             /* one-pass kernel (shrinking resize): d_und is not allocated */
     cudaStream_t stream = nullptr;
+    /* d_src / d_und / d_gray are shared by every call on the handle, and calls may be enqueued on different streams (the
+     * handle's, a caller's, an extractor's): each call first makes its stream wait for the previous call's last use */
+    cudaEvent_t ev_last = nullptr;
+    bool used = false;
 };
+
+static orbx_status pp_begin(orbx_preproc* p, cudaStream_t st) {
+    if (p->used) ORBX_CUDA(cudaStreamWaitEvent(st, p->ev_last, 0));
+    return ORBX_OK;
+}
+static orbx_status pp_end(orbx_preproc* p, cudaStream_t st) {
+    ORBX_CUDA(cudaEventRecord(p->ev_last, st));
+    p->used = true;
+    return ORBX_OK;
+}
 
 /* round half to even, as cvRound (lrint under the default rounding mode) */
 static inline int pp_round(float v) { return (int)lrintf(v); }
@@ -284,6 +298,7 @@ static void pp_free(orbx_preproc* p) {
     cudaSetDevice(p->device);
     cudaFree(p->d_sxy); cudaFree(p->d_itab); cudaFree(p->d_xtab); cudaFree(p->d_ytab);
     cudaFree(p->d_src); cudaFree(p->d_und); cudaFree(p->d_gray);
+    if (p->ev_last) cudaEventDestroy(p->ev_last);
     if (p->stream) cudaStreamDestroy(p->stream);
     delete p;
 }
@@ -308,6 +323,7 @@ extern "C" orbx_status orbx_preproc_create(int src_w, int src_h, const float* ma
 #define CK(call) do { cudaError_t _e = (call); if (_e != cudaSuccess) { orbx_set_error("%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(_e)); pp_free(p); return ORBX_ERR_CUDA; } } while (0)
     CK(cudaSetDevice(device));
     CK(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
+    CK(cudaEventCreateWithFlags(&p->ev_last, cudaEventDisableTiming));
     const size_t npix = (size_t)map_w * map_h;
     std::vector<int2> sxy(npix);
     for (size_t i = 0; i < npix; ++i) sxy[i] = make_int2(pp_round(map_x[i] * 32.f), pp_round(map_y[i] * 32.f));
@@ -376,8 +392,11 @@ extern "C" orbx_status orbx_preproc_device(orbx_preproc* p, const uint8_t* d_bgr
     if (st != ORBX_OK) return st;
     if (!d_gray) { orbx_set_error("null argument"); return ORBX_ERR_INVALID; }
     ORBX_CUDA(cudaSetDevice(p->device));
-    return pp_enqueue(p, d_bgr, frame_stride, row_stride, batch, d_gray, p->dw, (size_t)p->dw * p->dh,
-                      stream ? (cudaStream_t)stream : p->stream);
+    cudaStream_t s = stream ? (cudaStream_t)stream : p->stream;
+    if (!p->fused) { st = pp_begin(p, s); if (st != ORBX_OK) return st; }      /* the two-kernel path goes through d_und */
+    st = pp_enqueue(p, d_bgr, frame_stride, row_stride, batch, d_gray, p->dw, (size_t)p->dw * p->dh, s);
+    if (st != ORBX_OK) return st;
+    return p->fused ? ORBX_OK : pp_end(p, s);
 }
 
 extern "C" orbx_status orbx_preproc_host(orbx_preproc* p, const uint8_t* h_bgr, size_t frame_stride, int row_stride, int batch,
@@ -388,12 +407,16 @@ extern "C" orbx_status orbx_preproc_host(orbx_preproc* p, const uint8_t* h_bgr, 
     if (!h_gray) { orbx_set_error("null argument"); return ORBX_ERR_INVALID; }
     ORBX_CUDA(cudaSetDevice(p->device));
     const size_t dense = (size_t)p->sw * 3;
+    st = pp_begin(p, p->stream);
+    if (st != ORBX_OK) return st;
     for (int f = 0; f < batch; ++f)
         ORBX_CUDA(cudaMemcpy2DAsync(p->d_src + (size_t)f * dense * p->sh, dense, h_bgr + (size_t)f * frame_stride, row_stride, dense,
                                     p->sh, cudaMemcpyHostToDevice, p->stream));
     st = pp_enqueue(p, p->d_src, dense * p->sh, (int)dense, batch, p->d_gray, p->dw, (size_t)p->dw * p->dh, p->stream);
     if (st != ORBX_OK) return st;
     ORBX_CUDA(cudaMemcpyAsync(h_gray, p->d_gray, (size_t)batch * p->dw * p->dh, cudaMemcpyDeviceToHost, p->stream));
+    st = pp_end(p, p->stream);
+    if (st != ORBX_OK) return st;
     ORBX_CUDA(cudaStreamSynchronize(p->stream));
     return ORBX_OK;
 }
@@ -414,10 +437,16 @@ extern "C" orbx_status orbx_preproc_extract_host(orbx_preproc* p, orbx_extractor
     ORBX_CUDA(cudaSetDevice(p->device));
     cudaStream_t s = (cudaStream_t)orbx_extractor_stream(e);
     const size_t dense = (size_t)p->sw * 3;
+    st = pp_begin(p, s);
+    if (st != ORBX_OK) return st;
     for (int f = 0; f < batch; ++f)
         ORBX_CUDA(cudaMemcpy2DAsync(p->d_src + (size_t)f * dense * p->sh, dense, h_bgr + (size_t)f * frame_stride, row_stride, dense,
                                     p->sh, cudaMemcpyHostToDevice, s));
     st = pp_enqueue(p, p->d_src, dense * p->sh, (int)dense, batch, p->d_gray, p->dw, (size_t)p->dw * p->dh, s);
     if (st != ORBX_OK) return st;
-    return orbx_extract_device(e, p->d_gray, (size_t)p->dw * p->dh, p->dw, batch, lapping);
+    /* level 0 of the pyramid is a copy of d_gray made by the first kernel of the extraction: the event is recorded
+     * after the whole extraction is enqueued, which is later than that kernel */
+    st = orbx_extract_device(e, p->d_gray, (size_t)p->dw * p->dh, p->dw, batch, lapping);
+    if (st != ORBX_OK) return st;
+    return pp_end(p, s);
 }

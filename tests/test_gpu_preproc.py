@@ -125,3 +125,30 @@ def test_convert_device_resident(pkg, oracle, synth):
     pkg.orbx._ck(pkg.orbx.lib().orbx_memcpy_d2h(out.ctypes.data, d_out.ptr, out.nbytes))
     assert np.array_equal(out, oracle.preprocess_bgr(img, m1, m2, dw, dh))
     d_in.free(); d_out.free(); g.close()
+
+
+def test_one_grabber_feeds_rotating_extractors(pkg, oracle, synth):
+    """One pre-processing handle in front of three extractor handles (three streams), calls issued back to back without
+    a sync in between: the handle's staging buffers are reused by every call, so each call must be ordered after the
+    previous one's last use on the device.  Every extractor ends up with its own batch's result."""
+    sw, sh, dw, dh, B = 800, 600, 480, 360, 4
+    m1, m2 = synth.undistortion_maps(sw, sh, sw, sh, zoom=0.9)
+    g = pkg.orbx.ImageGrabber((sw, sh), m1, m2, dw, dh, max_batch=B)
+    exs = [pkg.orbx.ORBextractor(700, 1.2, 6, 20, 7, max_batch=B) for _ in range(3)]
+    batches = [np.stack([synth.bgr_image(sw, sh, 500 + 10 * k + f) for f in range(B)]) for k in range(3)]
+    for rnd in range(2):
+        for k in range(3):
+            g.convert_and_extract(batches[(k + rnd) % 3], exs[k])
+    got = []
+    for k in range(3):
+        exs[k].sync()
+        got.append([exs[k].fetch(f) for f in range(B)])
+    ref = pkg.orbx.ORBextractor(700, 1.2, 6, 20, 7, max_batch=B)
+    for k in range(3):
+        gray = np.stack([oracle.preprocess_bgr(batches[(k + 1) % 3][f], m1, m2, dw, dh) for f in range(B)])
+        want = ref.extract_batch(gray)
+        for f in range(B):
+            assert np.array_equal(got[k][f][0], want[f][0]) and np.array_equal(got[k][f][1], want[f][1]), (k, f)
+    g.close(); ref.close()
+    for e in exs:
+        e.close()
