@@ -93,6 +93,18 @@ orbx_status orbx_extractor_counts(orbx_extractor* e, int* n, int* mono_index);
  * (w+38)x(h+38) buffer, densely packed (upstream layout: ROI at (19,19)). */
 orbx_status orbx_extractor_level_size(const orbx_extractor* e, int level, int* w, int* h);
 orbx_status orbx_extractor_level_download(orbx_extractor* e, int f, int level, uint8_t* out);
+/* The same level IN PLACE on the device, for callers that chain their own kernels behind the extraction (the
+ * reference's mvImagePyramid[level] is a cv::cuda::HostMem a kernel can read, include/ORBextractor.h:94): *d_roi = ROI
+ * pixel (0,0) of frame 0, rows `pitch` bytes apart, frame f at + f * frame_stride; the 19-px reflect-101 border lies
+ * around the ROI (d_roi[-19 * pitch - 19] is valid).  Contents belong to the last extract enqueued on the handle's
+ * stream: order readers after orbx_extractor_stream(e).  Any output pointer may be NULL. */
+orbx_status orbx_extractor_level_device(orbx_extractor* e, int level, const uint8_t** d_roi, int* w, int* h, int* pitch,
+                                        size_t* frame_stride);
+/* Keypoints, descriptors and counts of the last extract in place on the device: frame f's records start at
+ * d_kps + f * capacity and d_desc + 32 * f * capacity, already in their final vLappingArea order; d_counts[f] = number of
+ * keypoints, d_counts[max_batch + f] = monoIndex.  Same ordering rule as above. */
+orbx_status orbx_extractor_results_device(orbx_extractor* e, const orbx_keypoint** d_kps, const uint8_t** d_desc,
+                                          const int** d_counts, int* capacity);
 /* 7x7 sigma-2 blurred level (w x h, no border), for tests. */
 orbx_status orbx_extractor_blurred_download(orbx_extractor* e, int f, int level, uint8_t* out);
 /* FAST candidates handed to DistributeOctTree for (frame, level): coordinates relative to

@@ -2255,6 +2255,29 @@ extern "C" orbx_status orbx_extractor_level_download(orbx_extractor* e, int f, i
     return ORBX_OK;
 }
 
+/* Device views for callers that chain their own kernels behind the extraction (no copy, no synchronisation). */
+extern "C" orbx_status orbx_extractor_level_device(orbx_extractor* e, int level, const uint8_t** d_roi, int* w, int* h, int* pitch,
+                                                   size_t* frame_stride) {
+    if (!e || level < 0 || level >= e->nlevels) { orbx_set_error("bad level"); return ORBX_ERR_INVALID; }
+    const LevelDev& L = e->lv[level];
+    if (d_roi) *d_roi = L.base + (size_t)ORBX_EDGE * L.pitch + ORBX_XOFF;
+    if (w) *w = L.w;
+    if (h) *h = L.h;
+    if (pitch) *pitch = L.pitch;
+    if (frame_stride) *frame_stride = L.frame_bytes;
+    return ORBX_OK;
+}
+
+extern "C" orbx_status orbx_extractor_results_device(orbx_extractor* e, const orbx_keypoint** d_kps, const uint8_t** d_desc,
+                                                     const int** d_counts, int* capacity) {
+    if (!e) { orbx_set_error("null argument"); return ORBX_ERR_INVALID; }
+    if (d_kps) *d_kps = e->d_kps;
+    if (d_desc) *d_desc = e->d_desc;
+    if (d_counts) *d_counts = e->d_nk;
+    if (capacity) *capacity = e->kcap;
+    return ORBX_OK;
+}
+
 extern "C" orbx_status orbx_extractor_blurred_download(orbx_extractor* e, int f, int level, uint8_t* out) {
     if (!e || level < 0 || level >= e->nlevels || f < 0 || f >= e->P.max_batch || !out) return ORBX_ERR_INVALID;
     ORBX_CUDA(cudaSetDevice(e->P.device));

@@ -114,6 +114,8 @@ def lib():
         L.orbx_knn2_device_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_longlong, C.c_void_p]
         L.orbx_knn2_noalloc_scratch_bytes.restype = C.c_size_t
         L.orbx_knn2_merge_device.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_float] + [C.c_void_p] * 5
+        L.orbx_extractor_level_device.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 5
+        L.orbx_extractor_results_device.argtypes = [C.c_void_p] + [C.c_void_p] * 4
         L.orbx_preproc_create.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                           C.POINTER(C.c_void_p)]
         L.orbx_preproc_destroy.argtypes = [C.c_void_p]
@@ -270,6 +272,18 @@ class ORBextractor:
         out = np.empty((h + 38, w + 38), np.uint8)
         _ck(lib().orbx_extractor_level_download(self._h, f, level, _p(out)))
         return out
+
+    def level_device(self, level):
+        """(device pointer of ROI pixel (0,0) of frame 0, w, h, pitch, frame_stride) of mvImagePyramid[level] in place."""
+        p = C.c_void_p(); w, h, pitch = C.c_int(), C.c_int(), C.c_int(); fs = C.c_size_t()
+        _ck(lib().orbx_extractor_level_device(self._h, level, C.byref(p), C.byref(w), C.byref(h), C.byref(pitch), C.byref(fs)))
+        return p.value, w.value, h.value, pitch.value, fs.value
+
+    def results_device(self):
+        """(d_kps, d_desc, d_counts, capacity): the last extract's outputs in place on the device."""
+        k, d, n = C.c_void_p(), C.c_void_p(), C.c_void_p(); cap = C.c_int()
+        _ck(lib().orbx_extractor_results_device(self._h, C.byref(k), C.byref(d), C.byref(n), C.byref(cap)))
+        return k.value, d.value, n.value, cap.value
 
     def blurred(self, level, f=0):
         w, h = self.level_size(level)

@@ -300,3 +300,33 @@ def test_pooled_descriptor_bound():
     if POOL["kps"] < 20000:
         pytest.skip("run with the whole file to pool enough keypoints")
     _assert_pooled(POOL["kps"], POOL["bad"], "all extractor tests")
+
+
+def test_device_views_of_pyramid_and_results(pkg, synth):
+    """orbx_extractor_level_device / orbx_extractor_results_device: the in-place device views equal what the download
+    entry points return (bordered level incl. the 19-px border around the ROI; keypoints, descriptors, counts)."""
+    ox = pkg.orbx
+    B, w, h = 3, 512, 384
+    frames = synth.frame_batch(B, w, h, seed=77, distinct=3)
+    ex = ox.ORBextractor(800, 1.2, 6, 20, 7, max_batch=4)
+    res = ex.extract_batch(frames)
+    L = ox.lib()
+    for level in (0, 3):
+        ptr, lw, lh, pitch, fs = ex.level_device(level)
+        assert (lw, lh) == ex.level_size(level) and pitch >= lw + 38
+        for f in (0, 2):
+            rows = np.empty((lh + 38, pitch), np.uint8)
+            ox._ck(L.orbx_memcpy_d2h(rows.ctypes.data, ptr + f * fs - 19 * pitch - 32, rows.nbytes))
+            assert np.array_equal(rows[:, 32 - 19:32 + lw + 19], ex.image_pyramid(level, f))
+    dk, dd, dn, cap = ex.results_device()
+    assert cap == ex.capacity
+    cnt = np.empty(2 * 4, np.int32)
+    ox._ck(L.orbx_memcpy_d2h(cnt.ctypes.data, dn, cnt.nbytes))
+    for f in range(B):
+        k, d, mono = res[f]
+        assert cnt[f] == len(k) and cnt[4 + f] == mono
+        gk = np.empty(len(k), ox.KP_DTYPE); gd = np.empty((len(k), 32), np.uint8)
+        ox._ck(L.orbx_memcpy_d2h(gk.ctypes.data, dk + f * cap * 28, gk.nbytes))
+        ox._ck(L.orbx_memcpy_d2h(gd.ctypes.data, dd + f * cap * 32, gd.nbytes))
+        assert gk.tobytes() == k.tobytes() and np.array_equal(gd, d)
+    ex.close()
