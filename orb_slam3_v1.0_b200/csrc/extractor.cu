@@ -1914,7 +1914,9 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
                                                   CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
                 if (r != CUDA_SUCCESS) { orbx_set_error("cuTensorMapEncodeTiled(pyramid level %d) -> %d", l, (int)r); free_all(e); return ORBX_ERR_CUDA; }
                 const int ltp = (e->unit_hi[l] > e->unit_lo[l] && e->unit_lo[l] < e->nunits_short) ? e->fast_tp : e->fast_tp_tall;   /* the level's launch group */
-                const cuuint32_t fbox[3] = {(cuuint32_t)ltp, (cuuint32_t)std::max(L.fast_box_rows, 1), 1};
+                /* a level without FAST cells (detection area under 35 px: upstream's nCols / nRows == 0) gets a dummy box the
+                 * encoder accepts -- the inner extent must be a multiple of 16 bytes -- and is never fetched */
+                const cuuint32_t fbox[3] = {(cuuint32_t)std::max(ltp, 16), (cuuint32_t)std::max(L.fast_box_rows, 1), 1};
                 const CUresult r2 = ((EncodeFn)fn)(&M->fast[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, L.base, dims, strides, fbox, estr,
                                                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
                                                    CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
