@@ -145,3 +145,14 @@ def test_preprocess_matches_cv2(oracle, synth, GP, name):
     und = oracle.remap_cubic_bgr(img, m1, m2)
     assert int(und.astype(np.int64).sum()) == int(GP[f"{name}_undsum"])
     assert np.array_equal(oracle.preprocess_bgr(img, m1, m2, dw, dh), GP[f"{name}_gray"])
+
+
+def test_rbrief_sampling_matches_cv2_orb(oracle, golden_dir):
+    """The rBRIEF half of computeOrbDescriptor -- pattern table, fp32 rotation, round-half-even of the offsets, bit
+    order -- against cv2.ORB's own descriptors (tools/gen_golden_descriptor.py; the blurred image is the one cv2.ORB
+    sampled, see the generator's note): bit-exact on every keypoint."""
+    G = np.load(os.path.join(golden_dir, "cv2_orb_descriptors.npz"))
+    blurred, xya, want = G["blurred"], G["xya"], G["desc"]
+    assert len(xya) > 400
+    got = np.stack([oracle.orb_descriptor(blurred, int(x), int(y), float(a)) for x, y, a in xya])
+    assert np.array_equal(got, want)
