@@ -368,3 +368,19 @@ def test_search_by_projection_keyframe(oracle, synth, n, nmp, th, ori, seed):
     pn, pm = py_search_by_projection_kf(F, MP, th, ori, occ)
     on, om = oracle.search_by_projection_kf(F, MP, th, ori, occ)
     assert on == pn and np.array_equal(om, pm) and pn > 20
+
+
+def test_distinctive_descriptor(oracle):
+    """MapPoint::ComputeDistinctiveDescriptors, src/MapPoint.cc:343-412: all-pairs distances, per row the element at index
+    (int)(0.5 * (N - 1)) of the sorted row, the FIRST row with the smallest such median wins."""
+    rng = np.random.default_rng(77)
+    for n in list(range(1, 12)) + [16, 33, 64] + list(rng.integers(2, 50, 150)):
+        base = rng.integers(0, 256, 32, dtype=np.uint8)
+        d = base ^ np.packbits(rng.random((int(n), 256)) < rng.uniform(0.01, 0.4), axis=1)
+        D = np.unpackbits(d[:, None, :] ^ d[None, :, :], axis=2).sum(2)
+        best_median, best_idx = 2 ** 31 - 1, 0
+        for i in range(len(d)):
+            median = int(sorted(D[i])[int(0.5 * (len(d) - 1))])
+            if median < best_median:
+                best_median, best_idx = median, i
+        assert oracle.distinctive_descriptor(np.ascontiguousarray(d, np.uint8)) == (best_idx, best_median), n
