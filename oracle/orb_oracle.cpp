@@ -5,10 +5,17 @@
  * that BASELINE.json's north_star names, built from
  *   - the reference code that is citable under /root/reference (quadtree,
  *     tables, pattern, matcher) and
- *   - OpenCV CPU arithmetic restated from SURVEY.md Appendix A/B and pinned
- *     against Python cv2 4.13.0 by tests/test_oracle_cv2.py.
+ *   - OpenCV CPU arithmetic restated from SURVEY.md Appendix A/B.
  * Build: oracle/Makefile (g++ -O2 -ffp-contract=off).  No OpenCV dependency.
- * Parity status: "parity unpinned by the reference" (it ships no tests).
+ * Parity status: "parity unpinned by the reference" -- it ships no tests and cannot be built here.  What pins this
+ * file instead (DESIGN.md section 4 has the table):
+ *   - Python cv2 4.13.0 for everything OpenCV defines: resize, border, blur, FAST, fastAtan2, IC_Angle (through
+ *     cv2.ORB's angles), rBRIEF (through cv2.ORB's descriptors), remap / resize / cvtColor of the ROS front, and the
+ *     whole operator() re-composed from cv2 primitives (tests/test_oracle_golden.py, tests/test_oracle_cv2_live.py);
+ *   - second restatements in straight Python, written separately from the same source text, for what is ORB-SLAM's
+ *     own logic: quadtree (tests/cv2_compose.py), every matcher search (tests/test_oracle_matcher.py,
+ *     tests/test_oracle_matcher_py.py), ComputeStereoMatches (tests/test_oracle_stereo_py.py; its specification,
+ *     SURVEY App. A5, is itself a recall of upstream and cannot be checked in this tree).
  */
 #include "orb_oracle.h"
 
