@@ -1,0 +1,51 @@
+"""Several host threads, each with its own handles, calling into the library at the same time (ctypes releases the GIL
+for the duration of a call): extraction, stereo, projection search, 2-NN and pre-processing.  Every thread must get the
+results a single thread gets; first-use paths (shared-memory opt-in map, tensor-map encoder lookup, static scratch
+address) are hit concurrently because the handles are created inside the threads."""
+import threading
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def test_concurrent_threads_own_handles(pkg, synth):
+    ox = pkg.orbx
+    W, H = 400, 300
+    imgs = [synth.textured_image(W, H, 900 + i) for i in range(4)]
+    bgr = synth.bgr_image(320, 240, 5); m1, m2 = synth.undistortion_maps(320, 240, 320, 240, zoom=0.8)
+    F = synth.frame_view(600, seed=1); MP = synth.projection_problem(F, 900, seed=2)
+    q, db, _ = synth.descriptor_sets(512, 8192, seed=3)
+
+    def work(tid, out, iters):
+        try:
+            ex = ox.ORBextractor(500, 1.2, 6, 20, 7)
+            m = ox.ORBmatcher()
+            g = ox.ImageGrabber((320, 240), m1, m2, 200, 150)
+            res = []
+            for it in range(iters):
+                k, d, mono = ex(imgs[(tid + it) % 4], (0, 0))
+                n, mm = m.SearchByProjection(F, MP, 3.0, False, 0.0, 0.8)
+                kn = m.knn2(q, db, 0.8)
+                gray = g.ConvertImageToGPU(bgr[None])[0]
+                res.append((k.tobytes(), d.tobytes(), mono, n, mm.tobytes(), kn[0].tobytes(), kn[1].tobytes(), gray.tobytes()))
+            ex.close(); m.close(); g.close()
+            out[tid] = res
+        except Exception as e:       # noqa: BLE001
+            out[tid] = e
+
+    ref = {}
+    work(0, ref, 4)
+    assert not isinstance(ref[0], Exception), ref[0]
+    by_img = {i: ref[0][i] for i in range(4)}           # thread 0, iteration i used image i
+    out = {}
+    threads = [threading.Thread(target=work, args=(t, out, 12)) for t in range(6)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    for tid in range(6):
+        assert not isinstance(out[tid], Exception), out[tid]
+        for it, r in enumerate(out[tid]):
+            assert r == by_img[(tid + it) % 4], (tid, it)
