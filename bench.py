@@ -210,8 +210,9 @@ def cpp_matcher_latency(pkg):
                     fh.write(struct.pack("<I", len(k))); fh.write(k.encode()); fh.write(struct.pack("<Q", v.nbytes)); fh.write(v.tobytes())
             r = subprocess.run([exe, blob, "300"], capture_output=True, text=True, timeout=120)
             out = json.loads(r.stdout.strip().splitlines()[-1])
-            out["note"] = ("C++ callers, nprob = 1, median wall-clock ms incl. packing, H2D, kernel, D2H, sync; compare "
-                           "cpu_baseline.matching.search_by_projection.ms_per_problem_1thread")
+            out["note"] = ("C++ callers, median wall-clock ms incl. packing, H2D, kernel, D2H, sync: nprob = 1 (compare "
+                           "cpu_baseline.matching.search_by_projection.ms_per_problem_1thread) and one batched call of 64 problems "
+                           "(compare ...problems_per_s_all_cores; matching.search_by_projection is the same call through the Python mirror)")
             return out
     except Exception as ex:     # noqa: BLE001 - a secondary leg must not take the line down
         return {"unavailable": str(ex)[:160]}

@@ -69,8 +69,29 @@ int main(int argc, char** argv) {
             if (i >= 30) ref.push_back(std::chrono::duration<double, std::milli>(t1 - t0).count());
         }
         if (n_flat != n_ref) { fprintf(stderr, "flat %d != ref %d matches\n", n_flat, n_ref); return 4; }
+        /* the batched form of the C ABI: 64 problems in one call (one H2D, one launch, one D2H) */
+        const int NB = 64;
+        std::vector<orbx_frame_view> Fs(NB, F);
+        std::vector<orbx_mappoints> MPs(NB, MP);
+        std::vector<std::vector<int>> outs(NB, std::vector<int>(F.n));
+        std::vector<int*> outp(NB);
+        std::vector<int> nm(NB);
+        for (int i = 0; i < NB; ++i) outp[i] = outs[i].data();
+        std::vector<double> batch;
+        for (int i = 0; i < 40; ++i) {
+            const auto t0 = std::chrono::steady_clock::now();
+            if (orbx_search_by_projection(m.handle(), NB, Fs.data(), MPs.data(), nullptr, pr[0], pr[1] != 0, pr[2], pr[3], outp.data(), nm.data()) != ORBX_OK) {
+                fprintf(stderr, "%s\n", orbx_last_error());
+                return 5;
+            }
+            const auto t1 = std::chrono::steady_clock::now();
+            if (i >= 10) batch.push_back(std::chrono::duration<double, std::milli>(t1 - t0).count());
+        }
+        if (nm[0] != n_flat || nm[NB - 1] != n_flat) { fprintf(stderr, "batched call: %d != %d matches\n", nm[0], n_flat); return 6; }
+        const double b64 = median(batch);
         printf("{\"search_by_projection_flat_ms\": %.4f, \"search_by_projection_ref_signature_ms\": %.4f, \"keypoints\": %d, \"map_points\": %d, "
-               "\"matches\": %d, \"calls\": %d}\n", median(flat), median(ref), F.n, M, n_flat, calls);
+               "\"matches\": %d, \"calls\": %d, \"search_by_projection_batch64_ms\": %.4f, \"batch64_problems_per_s\": %.0f}\n", median(flat), median(ref), F.n, M,
+               n_flat, calls, b64, NB / (b64 * 1e-3));
     } catch (const std::exception& e) {
         fprintf(stderr, "%s\n", e.what());
         return 1;
