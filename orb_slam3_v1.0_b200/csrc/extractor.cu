@@ -1509,6 +1509,13 @@ static void free_all(orbx_extractor* e) {
 
 extern "C" void orbx_extractor_destroy(orbx_extractor* e) { free_all(e); }
 
+/* Create-time uploads: a synchronous cudaMemcpy / cudaMemcpyToSymbol from pageable memory returns once the data is
+ * staged -- "the DMA to final destination may not have completed" (CUDA runtime API, synchronisation behaviour) -- and
+ * that DMA runs on the legacy default stream, with which the handle's non-blocking streams are NOT ordered.  A kernel
+ * launched on the handle's stream right after create could therefore read a tensor map or a unit table that has not
+ * arrived yet (seen as "illegal instruction" from TMA when several host threads create and use handles while other
+ * threads keep the copy engine busy: tools/thread_stress.py).  Every upload of create is followed by this. */
+#define CK_UPLOADED() CK(cudaStreamSynchronize(cudaStreamLegacy))
 extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extractor** out) {
     if (!p || !out) { orbx_set_error("null argument"); return ORBX_ERR_INVALID; }
     *out = nullptr;
@@ -1701,6 +1708,7 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
         uint32_t d4[32] = {0};
         for (int r = 0; r < 31; ++r) d4[r] = (uint32_t)e->umax[r < 15 ? 15 - r : r - 15] * 0x01010101u + 0x80808080u;
         CK(cudaMemcpyToSymbol(c_d4, d4, sizeof(d4)));
+        CK_UPLOADED();
         if (const char* v = getenv("ORBX_OD_PAD")) e->od_pad = std::max(0, std::min(atoi(v), 200 * 1024 - OD_SMEM));
         CK_SMEM(k_orient_describe, OD_SMEM + e->od_pad);
     }
@@ -1751,7 +1759,7 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
     if (std::max(e->fast_tp, e->fast_tp_tall) > 256) { orbx_set_error("FAST strip width %d exceeds the 256-byte TMA box", std::max(e->fast_tp, e->fast_tp_tall)); free_all(e); return ORBX_ERR_INVALID; }
     if ((size_t)e->fast_rows * e->fast_tp_tall > 32767 || (size_t)e->fast_rows_short * e->fast_tp > 32767) { orbx_set_error("FAST strip %dx%d exceeds the 15-bit tile index", e->fast_tp_tall, e->fast_rows); free_all(e); return ORBX_ERR_INVALID; }
     CK(cudaMalloc(&e->d_units, std::max<size_t>(units.size(), 1) * sizeof(Unit)));
-    if (!units.empty()) CK(cudaMemcpy(e->d_units, units.data(), units.size() * sizeof(Unit), cudaMemcpyHostToDevice));
+    if (!units.empty()) { CK(cudaMemcpy(e->d_units, units.data(), units.size() * sizeof(Unit), cudaMemcpyHostToDevice)); CK_UPLOADED(); }
     {
         const size_t need = std::max((size_t)2 * e->fast_rows * e->fast_tp_tall, (size_t)2 * e->fast_rows_short * e->fast_tp) + FAST_QBYTES + 128;
         CK_SMEM(k_fast_units<256>, need);
@@ -1925,6 +1933,7 @@ extern "C" orbx_status orbx_extractor_create(const orbx_params* p, orbx_extracto
         }
         CK(cudaMalloc(&e->d_odmaps, sizeof(ODMaps)));
         CK(cudaMemcpy(e->d_odmaps, M, sizeof(ODMaps), cudaMemcpyHostToDevice));
+        CK_UPLOADED();
     }
 #undef CK
     *out = e;
@@ -2322,6 +2331,12 @@ extern "C" orbx_status orbx_device_alloc(int device, void** p, size_t bytes) {
     return ORBX_OK;
 }
 extern "C" void orbx_device_free(void* p) { if (p) cudaFree(p); }
-extern "C" orbx_status orbx_memcpy_h2d(void* d, const void* h, size_t bytes) { ORBX_CUDA(cudaMemcpy(d, h, bytes, cudaMemcpyHostToDevice)); return ORBX_OK; }
+/* returns with the data in device memory: the DMA of a synchronous pageable copy may still be in flight on the legacy
+ * default stream when cudaMemcpy returns, and callers go on to launch on non-blocking streams */
+extern "C" orbx_status orbx_memcpy_h2d(void* d, const void* h, size_t bytes) {
+    ORBX_CUDA(cudaMemcpy(d, h, bytes, cudaMemcpyHostToDevice));
+    ORBX_CUDA(cudaStreamSynchronize(cudaStreamLegacy));
+    return ORBX_OK;
+}
 extern "C" orbx_status orbx_memcpy_d2h(void* h, const void* d, size_t bytes) { ORBX_CUDA(cudaMemcpy(h, d, bytes, cudaMemcpyDeviceToHost)); return ORBX_OK; }
 extern "C" orbx_status orbx_device_synchronize(void) { ORBX_CUDA(cudaDeviceSynchronize()); return ORBX_OK; }

@@ -347,6 +347,9 @@ extern "C" orbx_status orbx_preproc_create(int src_w, int src_h, const float* ma
     CK(cudaMemcpy(p->d_itab, itab.data(), itab.size() * sizeof(short), cudaMemcpyHostToDevice));
     CK(cudaMemcpy(p->d_xtab, xtab.data(), xtab.size() * sizeof(int2), cudaMemcpyHostToDevice));
     CK(cudaMemcpy(p->d_ytab, ytab.data(), ytab.size() * sizeof(int2), cudaMemcpyHostToDevice));
+    /* a synchronous copy from pageable memory returns once the data is staged; its DMA runs on the legacy default
+     * stream, with which this handle's non-blocking stream is not ordered (see orbx_extractor_create) */
+    CK(cudaStreamSynchronize(cudaStreamLegacy));
 #undef CK
     *out = p;
     return ORBX_OK;

@@ -49,3 +49,21 @@ def test_concurrent_threads_own_handles(pkg, synth):
         assert not isinstance(out[tid], Exception), out[tid]
         for it, r in enumerate(out[tid]):
             assert r == by_img[(tid + it) % 4], (tid, it)
+
+
+@pytest.mark.parametrize("ops", ["ek", "espk"])
+def test_handles_created_and_used_while_other_threads_run(ops):
+    """Six threads re-create their extractor / matcher / pre-processing handles every 10 iterations and use them at
+    once, while the other threads' kernels and copies are in flight (tools/thread_stress.py).  Regression test: the
+    create-time uploads (tensor maps, FAST unit table, remap tables) were synchronous copies from pageable memory,
+    whose DMA may still be in flight on the legacy default stream when the call returns; the first kernels on the
+    handle's non-blocking stream then read a tensor map that had not arrived ("illegal instruction" from TMA, in about
+    two of three runs of this test)."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    for _ in range(3):
+        r = subprocess.run([sys.executable, os.path.join(root, "tools", "thread_stress.py"), "6", "120", ops, "10"], capture_output=True,
+                           text=True, timeout=300)
+        assert r.returncode == 0 and " 0 errors" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
