@@ -58,6 +58,27 @@ def stereo_empty_side():
     return good
 check("stereo with an empty left / right / both sides", stereo_empty_side)
 
+def batch_size_sequence_on_one_handle():
+    """1 -> 4 -> 1 -> 1 -> 16 -> 32 -> 3 -> 1 frames on one handle (max_batch 32): the latency path captures a graph per
+    (pointer, layout, batch), batches >= 32 take the multi-stream path; every call must give per-frame results equal to
+    a fresh single-frame extraction."""
+    frames = np.stack([sy.textured_image(W, H, 40 + i) for i in range(32)])
+    pin = ox.PinnedBuffer((32, H, W)); pin.array[:] = frames
+    ex = ox.ORBextractor(400, 1.2, 5, 20, 7, max_batch=32).prepare(W, H, 32)
+    one = ox.ORBextractor(400, 1.2, 5, 20, 7)
+    ref = [one(frames[f], (0, 0)) for f in range(32)]
+    good = True
+    for b in (1, 4, 1, 1, 16, 32, 3, 1, 32, 1):
+        ex.extract_host(pin.array[:b])
+        ex.sync()
+        n, _ = ex.counts(b)
+        for f in range(b):
+            k, d, mono = ex.fetch(f)
+            good &= k.tobytes() == ref[f][0].tobytes() and np.array_equal(d, ref[f][1]) and mono == ref[f][2] and n[f] == len(k)
+    ex.close(); one.close(); pin.free()
+    return good
+check("batch sizes 1/4/1/1/16/32/3/1/32/1 on one handle", batch_size_sequence_on_one_handle)
+
 m = ox.ORBmatcher()
 
 
