@@ -42,14 +42,8 @@ void orbx_set_error(const char* fmt, ...) {
 extern "C" const char* orbx_last_error(void) { return g_err; }
 extern "C" int orbx_version(void) { return 100; }
 
-/* spin on an mbarrier phase (TMA / bulk-copy completion) */
-__device__ __forceinline__ void od_wait(uint32_t bar, uint32_t parity) {
-    uint32_t done;
-    do {
-        asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
-                     : "=r"(done) : "r"(bar), "r"(parity) : "memory");
-    } while (!done);
-}
+/* wait for an mbarrier phase (TMA / bulk-copy completion): bounded, see orbx_mbar_wait in orbx_internal.h */
+__device__ __forceinline__ void od_wait(uint32_t bar, uint32_t parity) { orbx_mbar_wait(bar, parity); }
 
 /* ================================================================== stage 0: pyramid */
 /* level 0 = copyMakeBorder(image, 19, BORDER_REFLECT_101).

@@ -67,3 +67,15 @@ def test_handles_created_and_used_while_other_threads_run(ops):
         r = subprocess.run([sys.executable, os.path.join(root, "tools", "thread_stress.py"), "6", "120", ops, "10"], capture_output=True,
                            text=True, timeout=300)
         assert r.returncode == 0 and " 0 errors" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+def test_mbarrier_wait_is_bounded(pkg):
+    """The mbarrier wait every TMA / bulk-copy consumer of the library uses (csrc/orbx_internal.h) returns on a completed
+    barrier and ends in a launch failure -- not in a kernel that polls for ever -- on a barrier nothing arrives on
+    (tools/mbar_timeout_probe.cu, built by csrc/Makefile with the bound shortened to ~0.5 s)."""
+    import os
+    import subprocess
+    exe = os.path.join(os.path.dirname(pkg.orbx.build()), "mbar_probe")
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "completed barrier: no error, flag 1" in r.stdout and "barrier nothing arrives on:" in r.stdout and "no error after" not in r.stdout
