@@ -18,6 +18,11 @@ imgs = [synth.textured_image(W, H, 900 + i) for i in range(4)]
 bgr = synth.bgr_image(320, 240, 5); m1, m2 = synth.undistortion_maps(320, 240, 320, 240, zoom=0.8)
 F = synth.frame_view(600, seed=1); MP = synth.projection_problem(F, 900, seed=2)
 q, db, _ = synth.descriptor_sets(512, 8192, seed=3)
+left, right = synth.stereo_pair(W, H, 7)
+kfp = synth.keyframe_pair(600, 650, 40, 8); kfp[0]["has_mp"] = (np.random.default_rng(1).random(600) < 0.6).astype(np.uint8)
+ini = synth.initialization_pair(500, 500, 9)
+fz = synth.fuse_problem(F, 500, 10)
+s3 = synth.sim3_problem(400, 450, 11)
 errors = []
 leaked = []
 t0 = time.time()
@@ -32,7 +37,7 @@ def work(tid):
                     if ex is not None:
                         if os.environ.get("STRESS_LEAK"): leaked.append(ex)
                         else: ex.close()
-                    ex = ox.ORBextractor(500, 1.2, 6, 20, 7)
+                    ex = ox.ORBextractor(500, 1.2, 6, 20, 7, max_batch=2)
                 if m is None or "m" in WHICH:
                     if m is not None: m.close()
                     m = ox.ORBmatcher()
@@ -43,6 +48,15 @@ def work(tid):
             if "s" in OPS: m.SearchByProjection(F, MP, 3.0, False, 0.0, 0.8)
             if "k" in OPS: m.knn2(q, db, 0.8)
             if "p" in OPS: g.ConvertImageToGPU(bgr[None])
+            if "t" in OPS:          # stereo: both images through this thread's extractor, then the row search on the resident results
+                ex.extract_batch(np.stack([left, right]))
+                ox.stereo_matches(ex, ex, [0], [1], 40.0, 0.1)
+            if "b" in OPS:          # the other matcher entry points, two problems per call
+                m.SearchByBoW([kfp[0]] * 2, [kfp[1]] * 2, 0.7, True)
+                m.SearchForTriangulation([kfp[0]] * 2, [kfp[1]] * 2, [kfp[2]] * 2, [kfp[3]] * 2, [kfp[4]] * 2)
+                m.SearchForInitialization([ini[0]] * 2, [ini[1]] * 2, 100, 0.9, True)
+                m.FuseSearch([F] * 2, [fz[0]] * 2, 3.0, 0, [fz[1]] * 2, [fz[2]] * 2)
+                m.SearchBySim3([s3[0]] * 2, [s3[1]] * 2, [s3[2]] * 2, [s3[3]] * 2, 7.5)
     except Exception as e:       # noqa: BLE001
         errors.append((round(time.time() - t0, 4), tid, it, repr(e)[:300]))
 
