@@ -10,6 +10,11 @@
  * Conventions: plain pointers and sizes only; every function returns an orbx_status
  * (never exits, never throws); device work is enqueued on the handle's stream; there
  * is NO CPU fallback -- without a CUDA device every call fails with ORBX_ERR_CUDA.
+ * Threads: handles are independent; any number of host threads may create, use and destroy
+ * their own handles concurrently (the reference runs the left / right extractors and the
+ * Tracking / LocalMapping / LoopClosing matchers on separate threads).  ONE handle is not
+ * re-entrant: one calling thread at a time.  orbx_last_error() is per thread.  A handle
+ * returned by a create function is ready: its tables are in device memory.
  */
 #ifndef ORBX_H
 #define ORBX_H
