@@ -569,10 +569,12 @@ def run_reference(args):
     if rank != 0:
         return
     ncores = os.cpu_count() or 1
-    vals = []
+    vals, secs = [], []
     base = None
     for _ in range(args.warmup + args.steps):
+        t0 = time.perf_counter()
         base = cpu_baseline(ncores, seconds_target=3.0)
+        secs.append(time.perf_counter() - t0)
         vals.append(base["value"])
     v = float(np.mean(vals[args.warmup:]))
     base["value"] = v
@@ -580,11 +582,12 @@ def run_reference(args):
         base.update({k: v_ for k, v_ in cpu_baseline(ncores, seconds_target=1.0, extended=True).items()
                      if k in ("extraction_o3_native", "extraction_cv2_composition", "matching", "knn2")})
     line = {"metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": None, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
+            "ms_per_step": float(np.mean(secs[args.warmup:])) * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
             "data": "synthetic", "impl": "reference",
             "config": workload_config(),
             "run": {"note": "CPU oracle (port of the reference semantics) on all host cores, each step a bounded sample of the "
-                            "workload (cpu_baseline.sample); the reference's own path needs OpenCV-CUDA and cannot be built in this image"},
+                            "workload (cpu_baseline.sample; ms_per_step = wall time of one such sample incl. its single-thread probe); "
+                            "the reference's own path needs OpenCV-CUDA and cannot be built in this image"},
             "cpu_baseline": base,
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
