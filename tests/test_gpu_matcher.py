@@ -567,3 +567,17 @@ def test_search_for_initialization_clustered(matcher, oracle, synth, win, ratio,
     on, om = oracle.search_for_initialization(F1, F2, win, ratio, ori)
     assert n == on and np.array_equal(m, om)
     assert (om >= 0).sum() > 5
+
+
+# ------------------------------------------------------------------ committed vectors of the Python restatements
+import os
+
+import matcher_golden_cases as _G
+import matcher_golden_run as _R
+
+
+@pytest.mark.parametrize("name", list(_G.CASES))
+def test_cuda_vs_committed_python_vectors(matcher, synth, golden_dir, name):
+    """The CUDA kernels against tests/golden/py_matcher.npz: vectors produced by the straight-Python restatements of
+    the reference's matcher functions (tools/gen_golden_matcher.py), i.e. by neither the kernels nor the C++ oracle."""
+    _R.check(name, synth, np.load(os.path.join(golden_dir, "py_matcher.npz")), matcher, True)

@@ -384,3 +384,17 @@ def test_distinctive_descriptor(oracle):
             if median < best_median:
                 best_median, best_idx = median, i
         assert oracle.distinctive_descriptor(np.ascontiguousarray(d, np.uint8)) == (best_idx, best_median), n
+
+
+# ================================================================ committed vectors of the Python restatements
+import os
+
+import matcher_golden_cases as _G
+import matcher_golden_run as _R
+
+
+@pytest.mark.parametrize("name", list(_G.CASES))
+def test_oracle_vs_committed_python_vectors(oracle, synth, golden_dir, name):
+    """tests/golden/py_matcher.npz holds what the Python restatements return (tools/gen_golden_matcher.py): the C++ oracle
+    must reproduce it.  tests/test_gpu_matcher.py compares the CUDA kernels with the same file."""
+    _R.check(name, synth, np.load(os.path.join(golden_dir, "py_matcher.npz")), oracle, False)
