@@ -13,6 +13,9 @@ CASES = [  # w, h, nfeatures, scale, levels, ini, min, lapping
     (4000, 4000, 8000, 1.2, 8, 20, 7, (1000, 3000)),
     (4000, 64, 500, 1.2, 1, 20, 7, (0, 0)),
     (64, 4000, 500, 1.2, 1, 20, 7, (0, 0)),
+    (752, 480, 1, 1.2, 8, 20, 7, (0, 0)),           # quotas of 0 and 1 features per level (the quadtree still returns its initial nodes)
+    (752, 480, 5, 1.2, 8, 20, 7, (100, 600)),
+    (640, 480, 17, 1.5, 6, 20, 7, (0, 0)),
     (100, 64, 300, 1.2, 1, 20, 7, (0, 0)),          # no FAST cell at all: no keypoints, monoIndex 0
     (300, 90, 300, 1.5, 3, 20, 7, (0, 0)),          # upper levels lose their cells
     (2048, 1536, 3000, 1.1, 12, 30, 5, (0, 0)),
