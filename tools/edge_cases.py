@@ -79,6 +79,26 @@ def batch_size_sequence_on_one_handle():
     return good
 check("batch sizes 1/4/1/1/16/32/3/1/32/1 on one handle", batch_size_sequence_on_one_handle)
 
+def strided_inputs():
+    """Host frames with padded rows and padded frames (a crop of a larger buffer), host and device entry points, against
+    the same frames passed densely; the vec_ok / unaligned paths of the level-0 copy are both hit (odd offsets)."""
+    B = 3
+    big = np.zeros((B, H + 9, W + 37), np.uint8)
+    dense = np.stack([sy.textured_image(W, H, 70 + i) for i in range(B)])
+    big[:, 4:4 + H, 13:13 + W] = dense
+    view = big[:, 4:4 + H, 13:13 + W]
+    ex = ox.ORBextractor(400, 1.2, 5, 20, 7, max_batch=B)
+    ref = ex.extract_batch(dense)
+    ex.extract_host(view); ex.sync()
+    good = all(ex.fetch(f)[0].tobytes() == ref[f][0].tobytes() and np.array_equal(ex.fetch(f)[1], ref[f][1]) for f in range(B))
+    d = ox.DeviceBuffer(big.nbytes); d.upload(big)
+    ox._ck(ox.lib().orbx_extract_device(ex._h, d.ptr.value + 4 * big.strides[1] + 13, big.strides[0], big.strides[1], B, None))
+    ex.sync()
+    good &= all(ex.fetch(f)[0].tobytes() == ref[f][0].tobytes() and np.array_equal(ex.fetch(f)[1], ref[f][1]) for f in range(B))
+    d.free(); ex.close()
+    return good
+check("padded rows / frames, unaligned origin: host and device entry points", strided_inputs)
+
 m = ox.ORBmatcher()
 
 
