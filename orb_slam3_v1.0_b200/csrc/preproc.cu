@@ -241,7 +241,11 @@ __device__ __forceinline__ int pp_bilinear_gray(unsigned p00, unsigned p01, unsi
  * 304 bytes of spill per thread: the occupancy is worth more than the spill costs; 128-thread CTAs x 4 give the same
  * 0.366 ms, x 3 0.433 ms).  A variant with four lanes per output pixel (one corner each, 104 registers, values
  * exchanged by shuffles) took 0.594 ms and was dropped; a partially unrolled row loop indexes the weight registers
- * dynamically and sends them to local memory. */
+ * dynamically and sends them to local memory.  Also measured and dropped: staging, per 32 x 8 tile of output pixels, the
+ * rectangle of source bytes its taps can touch (known at create time, the maps being fixed) in shared memory and running
+ * the same tap code on the copy -- 0.59 ms single-buffered, 0.427 ms with the next frame's rectangle in flight by
+ * cp.async: the kernel is not waiting for global memory but for its own dependent funnel / PRMT / DP2A chains at 16
+ * warps per SM, and staging only adds instructions and block barriers. */
 #ifndef PP_FUSED_MINB
 #define PP_FUSED_MINB 2
 #endif
