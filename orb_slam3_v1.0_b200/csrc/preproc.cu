@@ -236,18 +236,27 @@ __device__ __forceinline__ int pp_bilinear_gray(unsigned p00, unsigned p01, unsi
  * same integers k_remap_cubic would have stored -- and nothing is written but the gray byte.  Chosen at create time
  * when 4 * dw * dh < mw * mh (fewer remap evaluations than the two-kernel path).
  * Measured on a B200, 32 frames of 2048x1536 -> 614x460 (tools/preproc_bench.py): two kernels 1.02 ms; this kernel
- * 0.487 ms uncapped (239 registers, 8 warps per SM: ncu shows 12 % warps active and 32 % issue active, DRAM traffic
- * equal to source + result, i.e. it waits on its own scattered loads) and 0.371 ms with two CTAs per SM (128 registers,
- * 304 bytes of spill per thread: the occupancy is worth more than the spill costs; 128-thread CTAs x 4 give the same
- * 0.366 ms, x 3 0.433 ms).  A variant with four lanes per output pixel (one corner each, 104 registers, values
- * exchanged by shuffles) took 0.594 ms and was dropped; a partially unrolled row loop indexes the weight registers
- * dynamically and sends them to local memory.  Also measured and dropped: staging, per 32 x 8 tile of output pixels, the
- * rectangle of source bytes its taps can touch (known at create time, the maps being fixed) in shared memory and running
- * the same tap code on the copy -- 0.59 ms single-buffered, 0.427 ms with the next frame's rectangle in flight by
- * cp.async: the kernel is not waiting for global memory but for its own dependent funnel / PRMT / DP2A chains at 16
- * warps per SM, and staging only adds instructions and block barriers. */
+ * 0.487 ms uncapped (239 registers, 8 warps per SM), 0.371 ms with two CTAs per SM (128 registers, 304 bytes of spill per
+ * thread), 0.317 ms with three (80 registers) and 0.313 ms with four (64 registers, 680 bytes of spill: what ships); five,
+ * six and eight CTAs (48 / 40 / 32 registers) fall back to 0.386 / 0.407 / 0.428 ms.  The occupancy is worth more than the
+ * spills cost because the limiter is the L1 gather, not the arithmetic (profiles/r2_preproc_l1.txt, the --set full
+ * captures of the two- and the four-CTA build): 12.2 sectors per 32-lane LDG.32 request (lanes are 3.33 source pixels =
+ * 10 bytes apart, so one request spans 3-4 lines), long_scoreboard 5.0 of 8.7 stalled warps per issue and the L1
+ * wavefront pipe 53 % busy at 42 % issue with two CTAs; 69 % busy at 54 % issue with four.  The 388 k wavefronts per SM
+ * of the gather alone are a floor of 0.20 ms for this access pattern whatever the occupancy (24 x the unique lines an
+ * SM reads).  DRAM reads equal the source; the writes beyond the result are the spill frames leaving L2.
+ * Measured and dropped: four lanes per output pixel (one corner each, 104 registers, values exchanged by shuffles)
+ * 0.594 ms; a partially unrolled row loop (it indexes the weight registers dynamically and sends them to local memory);
+ * two 8-byte loads and one 4-byte load per tap row on an 8-byte grid instead of four 4-byte loads (a quarter fewer
+ * requests, 4 selects more per row: 0.370 ms against 0.314 ms at the same four CTAs per SM);
+ * the 64 weights of a thread parked in shared memory and re-read every frame (0.415 / 0.360 / 0.331 ms at 2 / 3 / 4 CTAs
+ * per SM: slower than the register build at every occupancy); staging, per 32 x 8 tile of output pixels, the rectangle
+ * of source bytes its taps can touch (known at create time, the maps being fixed) in shared memory and running the same
+ * tap code on the copy -- 0.59 ms single-buffered, 0.427 ms with the next frame's rectangle in flight by cp.async: a
+ * 10-byte lane stride conflicts in the shared-memory banks exactly as it splits into lines in L1, so the gather costs
+ * the same wavefronts and the staging is extra. */
 #ifndef PP_FUSED_MINB
-#define PP_FUSED_MINB 2
+#define PP_FUSED_MINB 4
 #endif
 __global__ void __launch_bounds__(PP_THREADS, PP_FUSED_MINB)
 k_remap_resize_gray(const uint8_t* __restrict__ src, size_t src_frame, int src_pitch, int sw, int sh,
