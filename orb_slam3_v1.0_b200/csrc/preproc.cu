@@ -203,7 +203,13 @@ __device__ __forceinline__ unsigned pp_tap_eval(const PpTap& t, const uint8_t* _
 }
 
 /* cv::remap, INTER_CUBIC, BORDER_CONSTANT(0), 3 x u8 interleaved.  Thread = one pixel of the map, all frames. */
-__global__ void __launch_bounds__(PP_THREADS)
+/* CTAs per SM: the kernel waits on its gathered loads, so occupancy is worth more than registers -- measured with
+ * k_resize_gray behind it on 32 frames of 2048 x 1536: 1.011 ms uncapped (100 registers, 2 CTAs), 0.806 / 0.734 / 0.717 /
+ * 0.700 ms at 3 / 4 / 5 / 6 CTAs (80 / 64 / 48 / 40 registers, up to 264 B of spill), 0.991 ms at 8 (32 registers). */
+#ifndef PP_CUBIC_MINB
+#define PP_CUBIC_MINB 6
+#endif
+__global__ void __launch_bounds__(PP_THREADS, PP_CUBIC_MINB)
 k_remap_cubic(const uint8_t* __restrict__ src, size_t src_frame, int src_pitch, int sw, int sh,
               const int2* __restrict__ sxy, const uint4* __restrict__ itab,
               uint8_t* __restrict__ und, int npix, int batch) {
@@ -235,7 +241,7 @@ __device__ __forceinline__ int pp_bilinear_gray(unsigned p00, unsigned p01, unsi
  * Thread = one OUTPUT pixel, all frames: it evaluates exactly the (up to) four map pixels its 2x2 block names -- the
  * same integers k_remap_cubic would have stored -- and nothing is written but the gray byte.  Chosen at create time
  * when 4 * dw * dh < mw * mh (fewer remap evaluations than the two-kernel path).
- * Measured on a B200, 32 frames of 2048x1536 -> 614x460 (tools/preproc_bench.py): two kernels 1.02 ms; this kernel
+ * Measured on a B200, 32 frames of 2048x1536 -> 614x460 (tools/preproc_bench.py): two kernels 0.70 ms; this kernel
  * 0.487 ms uncapped (239 registers, 8 warps per SM), 0.371 ms with two CTAs per SM (128 registers, 304 bytes of spill per
  * thread), 0.317 ms with three (80 registers) and 0.313 ms with four (64 registers, 680 bytes of spill: what ships); five,
  * six and eight CTAs (48 / 40 / 32 registers) fall back to 0.386 / 0.407 / 0.428 ms.  The occupancy is worth more than the
