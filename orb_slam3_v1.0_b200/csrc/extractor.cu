@@ -762,7 +762,10 @@ __global__ void __launch_bounds__(OCT_THREADS) k_octree(Tables T, const Cell* __
     __shared__ int s_tmp[OCT_THREADS / 32 + 1];
     __shared__ int s_T, s_CT;
 
-    const int level = blockIdx.x + T.l0, f = blockIdx.y + T.f0, tid = threadIdx.x;
+    /* level-major CTA order: every frame's level 0 (the longest quadtrees) is scheduled first and the short upper levels
+     * fill the tail -- 0.146 -> 0.126 ms per 256 EuRoC frames against the frame-major order (1024 CTAs per chunk in ~890
+     * resident slots) */
+    const int level = blockIdx.y + T.l0, f = blockIdx.x + T.f0, tid = threadIdx.x;
     const LevelDev& Lv = T.lv[level];
     const int N = Lv.N;
 
@@ -2001,7 +2004,7 @@ static orbx_status enqueue_frames(orbx_extractor* e, const uint8_t* d_images, si
         }
         Tables Tl = T;
         Tl.l0 = l;
-        k_octree<<<dim3(1, nb), OCT_THREADS, e->oct_smem, b>>>(Tl, e->d_cells, e->ncells, e->d_slots, e->slots_per_frame,
+        k_octree<<<dim3(nb, 1), OCT_THREADS, e->oct_smem, b>>>(Tl, e->d_cells, e->ncells, e->d_slots, e->slots_per_frame,
                                                                e->d_cell_count, e->d_cand, e->d_pnode, e->cand_per_frame,
                                                                e->d_cand_count, e->d_sel, e->sel_per_frame, e->d_sel_count,
                                                                e->maxn, e->max_cells_level, OCT_SCAND);
@@ -2085,7 +2088,7 @@ static orbx_status enqueue_frames(orbx_extractor* e, const uint8_t* d_images, si
         for (int l = 0; l < nl; ++l) ORBX_CUDA(cudaStreamWaitEvent(st, e->ev_oct[l], 0));
     } else {
         ORBX_RANGE("DistributeOctTree");
-        k_octree<<<dim3(nl, nb), OCT_THREADS, e->oct_smem, st>>>(T, e->d_cells, e->ncells, e->d_slots, e->slots_per_frame,
+        k_octree<<<dim3(nb, nl), OCT_THREADS, e->oct_smem, st>>>(T, e->d_cells, e->ncells, e->d_slots, e->slots_per_frame,
                                                                  e->d_cell_count, e->d_cand, e->d_pnode, e->cand_per_frame,
                                                                  e->d_cand_count, e->d_sel, e->sel_per_frame, e->d_sel_count,
                                                                  e->maxn, e->max_cells_level, OCT_SCAND);
